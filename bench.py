@@ -1,0 +1,307 @@
+#!/usr/bin/env python
+"""bench.py -- seconds per tree and histogram rows x features / s of the GBDT hot path.
+
+A step = one boosting iteration of the hot path: the round's (g,h) pairs are pushed to
+the tree maker and ITreeMaker.make() builds one tree (histograms, subtraction, split
+search, row partition).  Default workload = BASELINE.json configs[1]: Higgs shape,
+11 M x 28 dense, 255 bins, depth 8, synthetic.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+N > 1 is launched by torchrun, one rank per GPU; rows are sharded (each rank holds
+--rows rows: weak scaling) and the per-node histogram reduce-scatter + split allgather
+run over NCCL.  `value` is timed with the round's gradients already in HBM; `e2e`
+includes the host->device copy of the gradients from pinned memory and the tree coming
+back to the host.  --impl reference times the CPU restatement of the reference's Java
+path (oracle/, "port": there is no JVM in this image) on the host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "hist_rows_x_features_per_sec"
+UNIT = "rows*features/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=11_000_000, help="rows per GPU")
+    ap.add_argument("--features", type=int, default=28)
+    ap.add_argument("--bins", type=int, default=255)
+    ap.add_argument("--depth", type=int, default=8)
+    ap.add_argument("--policy", default="level", choices=["level", "loss"])
+    ap.add_argument("--leaves", type=int, default=-1)
+    ap.add_argument("--cpu-rows", type=int, default=2_000_000, help="rows of the bounded CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def tree_kwargs(a):
+    return dict(max_depth=a.depth, max_leaf_cnt=a.leaves, grow_policy=a.policy, min_child_hessian_sum=100.0,
+                min_split_loss=0.0, l1=0.0, l2=0.0, learning_rate=0.1, min_split_samples=-1)
+
+
+def synth_bins(n, F, nb, seed):
+    """half the features uniform over the bins, half skewed (geometric),
+    generated directly as uint8 bins; labels depend on a few features so that trees have
+    real structure."""
+    rng = np.random.default_rng(seed)
+    x = np.empty((n, F), dtype=np.uint8)
+    for f in range(F):
+        if f % 2 == 0:
+            x[:, f] = rng.integers(0, nb, size=n, dtype=np.uint8)
+        else:
+            x[:, f] = np.minimum(rng.geometric(0.04, size=n) - 1, nb - 1).astype(np.uint8)
+    z = np.zeros(n, dtype=np.float32)
+    for f in range(0, min(F, 12)):
+        z += (x[:, f].astype(np.float32) / nb - 0.5) * np.float32(((-1) ** f) * (1.0 + 0.3 * f))
+    z += (x[:, 1] > 20) * np.float32(0.8) - (x[:, 3] < 3) * np.float32(0.5)
+    p = 1.0 / (1.0 + np.exp(-z))
+    y = (rng.random(n, dtype=np.float32) < p).astype(np.float32)
+    return x, y
+
+
+def sigmoid_grads(score, y, out):
+    """SigmoidFunction (J/loss/SigmoidFunction.java:63-80) with the reference's float casts."""
+    p = (1.0 / (1.0 + np.exp(-score.astype(np.float64)))).astype(np.float32).astype(np.float64)
+    out[0::2] = (p - y).astype(np.float32)
+    out[1::2] = (p * (1.0 - p)).astype(np.float32)
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.proc = None
+        self.lines = []
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            c = [t.strip() for t in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def cpu_baseline(a, xs, ys, steps=1, threads=None):
+    """The CPU restatement of the reference's path (oracle, "port") on the host cores: one
+    emulated worker per core, each with its own row shard, as the Java trainer runs one
+    mp4j rank per thread.  Bounded sample: the first --cpu-rows rows of the same workload."""
+    import oracle_binding as ob
+    cores = threads or os.cpu_count() or 1
+    n = min(a.cpu_rows, xs.shape[0])
+    x = xs[:n].astype(np.int32)
+    y = ys[:n]
+    start = (np.arange(a.features + 1) * a.bins).astype(np.int32)
+    p = ob.make_params(**tree_kwargs(a))
+    score = np.zeros(n, np.float32)
+    gp = np.empty(2 * n, np.float32)
+    cells = secs = 0.0
+    nodes = 0
+    for _ in range(steps):
+        sigmoid_grads(score, y, gp)
+        t, pos, info = ob.make_tree(p, x, gp, 0, start, W=cores, threads=cores)
+        cells += info["hist_cells"]; secs += info["t_total"]; nodes = t.n_nodes
+        score += t.node_info[pos]
+    return {"value": cells / secs, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d trees on the first %d of %d rows x %d features, W=%d emulated workers"
+                      % (steps, n, xs.shape[0], a.features, cores),
+            "seconds_per_tree_on_sample": secs / steps, "nodes": nodes}
+
+
+def config(a, world):
+    return {"workload": "higgs-shape synthetic: %d rows/GPU x %d features, %d bins, %s-wise depth %d%s"
+                        % (a.rows, a.features, a.bins, a.policy, a.depth,
+                           "" if a.leaves < 0 else " leaves %d" % a.leaves),
+            "rows_per_gpu": a.rows, "global_rows": a.rows * world, "features": a.features, "bins": a.bins,
+            "grow_policy": a.policy, "max_depth": a.depth, "max_leaf_cnt": a.leaves,
+            "min_child_hessian_sum": 100.0, "l2": 0.0, "learning_rate": 0.1, "loss": "sigmoid",
+            "parallelism": "rows sharded x%d, feature-range reduce-scatter" % world,
+            "l2_note": "inputs (bins %d MB + grads per GPU) exceed the 126 MB L2, no flush needed"
+                       % (a.rows * 32 // 2 ** 20)}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    xs, ys = synth_bins(min(a.rows, a.cpu_rows), a.features, a.bins, 1234)
+    cores = os.cpu_count() or 1
+    t0 = time.time()
+    for _ in range(a.warmup if a.warmup < 2 else 1):
+        cpu_baseline(a, xs, ys, steps=1, threads=cores)
+    res = cpu_baseline(a, xs, ys, steps=max(1, a.steps), threads=cores)
+    line = {"impl": "reference", "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": a.gpus,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": res["seconds_per_tree_on_sample"] * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": config(a, a.gpus), "cpu_baseline": res,
+            "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.time() - t0,
+            "note": "reference = CPU restatement of the Java path (no JVM in this image), %d threads" % cores}
+    print(json.dumps(line))
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        return run_reference(a)
+
+    import torch
+    import torch.distributed as dist
+    import _pkg
+    yb = _pkg.load()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.from_numpy(yb.nccl_unique_id()))
+        dist.broadcast(idt, 0)
+        nccl_id = idt.cpu().numpy()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    n, F = a.rows, a.features
+    xs, ys = synth_bins(n, F, a.bins, 1234 + rank)
+    start = (np.arange(F + 1) * a.bins).astype(np.int32)
+    params = yb.make_params(**tree_kwargs(a))
+    tm = yb.GpuTreeMaker(params, start, n, device=local, rank=rank, world=world, nccl_id=nccl_id)
+    chunk = 1 << 20
+    for r0 in range(0, n, chunk):
+        tm.upload_rows(xs[r0:r0 + chunk].astype(np.int32), r0)
+
+    gp_pinned = torch.empty(2 * n, dtype=torch.float32).pin_memory()
+    gp = gp_pinned.numpy()
+    score = np.zeros(n, np.float32)
+    h2d = gp.nbytes
+    agg = dict(t_tree=0.0, t_e2e=0.0, cells=0.0, rows=0.0, rows_idx=0.0, built=0, gpu_hist_ms=0.0, launches=0,
+               d2h=0, nodes=0)
+    sampler = None
+    for step in range(a.warmup + a.steps):
+        sigmoid_grads(score, ys, gp)                      # the Java side's job, outside the hot path
+        timed = step >= a.warmup
+        if timed and sampler is None:
+            sampler = ClockSampler(local)
+        barrier()
+        t0 = time.perf_counter()
+        tm.set_grads_ptr(gp_pinned.data_ptr(), 0, n)      # H2D from pinned memory
+        t1 = time.perf_counter()
+        tree = tm.make(0)                                  # returns with the tree on the host
+        t2 = time.perf_counter()
+        ts = tm.last_stats
+        pos = tm.get_positions()
+        score += tree.node_info[pos]
+        if timed:
+            agg["t_tree"] += t2 - t1; agg["t_e2e"] += t2 - t0
+            agg["cells"] += ts.hist_cells; agg["rows"] += ts.hist_rows; agg["rows_idx"] += ts.hist_rows_indexed
+            agg["built"] += ts.hist_built; agg["gpu_hist_ms"] += ts.gpu_hist_ms
+            agg["launches"] += ts.kernel_launches; agg["nodes"] = tree.n_nodes
+            agg["d2h"] = sum(getattr(tree, nme).nbytes for nme, _ in yb.Tree.FIELDS)
+    barrier()
+    clocks = sampler.stop() if sampler else None
+
+    vals = torch.tensor([agg["t_tree"], agg["t_e2e"]], dtype=torch.float64, device="cuda")
+    sums = torch.tensor([agg["cells"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+    t_tree, t_e2e = vals.tolist()
+    cells_all = float(sums.item())
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        # algorithmic bytes of the histogram builds: n*(Fs*1 + 8 + idx) + 16*B per node
+        B = int(start[-1])
+        alg = agg["cells"] + 8 * agg["rows"] + 4 * agg["rows_idx"] + 16.0 * B * agg["built"]
+        ach = alg / (agg["gpu_hist_ms"] * 1e-3) / 1e9 if agg["gpu_hist_ms"] > 0 else 0.0
+        line = {
+            "metric": METRIC, "value": cells_all / t_tree, "unit": UNIT, "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": t_tree / a.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "int64 fixed-point (f32 in, f64-equivalent sums)",
+            "data": "synthetic", "config": config(a, world),
+            "seconds_per_tree": t_tree / a.steps, "nodes_per_tree": agg["nodes"],
+            "e2e": {"value": cells_all / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": agg["d2h"], "seconds_per_tree": t_e2e / a.steps},
+            "gpu_launches": agg["launches"],
+            "roofline": {"bound": "hbm", "kernel": "hist_build_k", "achieved": ach, "peak": peak, "unit": "GB/s",
+                         "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_step": alg / a.steps,
+                         "kernel_ms_per_step": agg["gpu_hist_ms"] / a.steps,
+                         "kernel_share_of_step": agg["gpu_hist_ms"] * 1e-3 / t_tree,
+                         "launches_per_step": agg["built"] / a.steps},
+            "clocks": clocks,
+        }
+        if not a.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_baseline(a, xs, ys, steps=1)
+        elif not a.no_cpu_baseline:
+            line["cpu_baseline"] = None
+        print(json.dumps(line))
+    tm.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,193 @@
+/*
+ * ytk_gbdt.h -- C ABI of libytkgbdt.so: ytk-learn's data-parallel (histogram) GBDT tree
+ * builder on B200.  This is the drop-in boundary: a JNI shim binds these entry points
+ * 1:1 behind the reference's ITreeMaker seam (INTEGRATION.md shows the Java side).
+ *
+ * The reference has no FFI today; each entry point names the Java interface it
+ * replaces (paths relative to the reference root,
+ * J/ = src/main/java/com/fenbi/ytklearn/).
+ *
+ * Conventions: plain C, no exceptions; every function returns 0 on success and a
+ * negative ytk_status otherwise, with a message in ytk_gbdt_last_error() (per thread).
+ * Host pointers are only read/written during the call; nothing is retained.
+ * There is no CPU fallback: without a CUDA device every compute entry point fails
+ * with YTK_ERR_CUDA.
+ */
+#ifndef YTK_GBDT_H
+#define YTK_GBDT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    YTK_OK = 0,
+    YTK_ERR_ARG = -1,        /* bad argument / call order (CheckUtils.check failures in the reference) */
+    YTK_ERR_CUDA = -2,       /* CUDA runtime error, or no device */
+    YTK_ERR_CAPACITY = -3,   /* caller-provided output too small */
+    YTK_ERR_NCCL = -4,       /* NCCL missing or failed (world > 1 only) */
+    YTK_ERR_UNSUPPORTED = -5 /* e.g. a feature with more than 256 bins */
+} ytk_status;
+
+typedef struct ytk_gbdt ytk_gbdt;  /* one per (GPU, row shard): the reference's per-thread tree maker */
+
+/* The fields of GBDTOptimizationParams the tree maker reads
+ * (J/param/gbdt/GBDTOptimizationParams.java:49-76), already normalised as its
+ * constructor does (:148-154; ytk_gbdt_normalize_max_leaf_cnt). */
+typedef struct {
+    int32_t max_depth;               /* <0: unlimited                                  */
+    int32_t max_leaf_cnt;            /* <=0: unlimited                                 */
+    int32_t min_split_samples;       /* <=0: off                                       */
+    int32_t grow_policy;             /* 0 = "level", 1 = "loss" (TreeGrowPolicy)       */
+    double  min_child_hessian_sum;
+    double  min_split_loss;
+    double  max_abs_leaf_val;        /* <=0: off                                       */
+    double  l1;
+    double  l2;
+    double  histogram_pool_capacity; /* MB; <=0: pool holds max_leaf_cnt histograms    */
+    float   learning_rate;
+    int32_t class_num;               /* K = numTreeInGroup                             */
+} ytk_gbdt_params;
+
+/* What ITreeMaker.make hands back: Tree/TreeNode/TreeNodeStat as SoA, one slot per node
+ * in allocation order (J/data/gbdt/Tree.java:58-73, TreeNode.java:33-48,121-149,
+ * DataParallelTreeMaker.java:387-393).  Arrays are caller-allocated with `capacity`
+ * slots (2*max_leaf_cnt-1 suffices). */
+typedef struct {
+    int32_t  capacity;
+    int32_t  n_nodes;     /* out */
+    int32_t *parent;      /* -1 for the root                                           */
+    int32_t *left;        /* -1 for leaves                                             */
+    int32_t *right;
+    int32_t *fid;         /* splitFeatureIndex                                         */
+    int32_t *lo, *hi;     /* splitFeaApproSlotInterval                                 */
+    float   *node_info;   /* inner: 0.5f*(lo+hi) in slot space; leaf: nodeValue*lr     */
+    float   *loss_chg;    /* TreeNodeStat.lossChg (-inf when the node was not searched)*/
+    float   *hess_sum;    /* TreeNodeStat.hessSum                                      */
+    int64_t *sample_cnt;  /* TreeNodeStat.nodeSampleCnt (global rows)                  */
+} ytk_tree_out;
+
+/* TimeStats (J/data/gbdt/TimeStats.java:30-79), milliseconds, per make() call. */
+typedef struct {
+    double build_hist;        /* buildHist      (includes the two below)               */
+    double compute_hist;      /* buildDetail[0]                                        */
+    double communicate_hist;  /* buildDetail[1]                                        */
+    double init_stats;        /* initStats                                             */
+    double find_best_split;   /* findBestSplit - syncBestSplit                         */
+    double sync_best_split;   /* syncBestSplit                                         */
+    double partition;         /* resetPosition (not timed separately by the reference) */
+    double total;             /* totalTime                                             */
+    int32_t hist_miss;        /* histMissCnt (DataParallelTreeMaker.java:506)          */
+    int32_t hist_built;       /* nodes whose histogram was built from rows             */
+    double  hist_cells;       /* sum over those nodes of local rows x sampled features */
+    double  hist_rows;        /* sum over those nodes of local rows                    */
+    double  hist_rows_indexed;/* ... of which addressed through the row-id list        */
+    double  gpu_hist_ms;      /* CUDA-event time of the histogram-build kernels        */
+    int32_t kernel_launches;  /* kernels launched by this call                         */
+} ytk_time_stats;
+
+/* One best split: SplitInfo (J/data/gbdt/SplitInfo.java:36-70) plus the node totals the
+ * reference exchanges beside it (DataParallelTreeMaker.java:543-573). */
+typedef struct {
+    float   loss_chg;     /* -inf when no candidate                                    */
+    int32_t fid, lo, hi;  /* -1 when no candidate                                      */
+    double  sum_grad, sum_hess;
+    float   root_gain, node_value;
+} ytk_split;
+
+const char *ytk_gbdt_last_error(void);
+
+/* GBDTOptimizationParams ctor, data-parallel branch (:148-154). Host only. */
+int32_t ytk_gbdt_normalize_max_leaf_cnt(int32_t max_depth, int32_t max_leaf_cnt);
+
+/* DataUtils.avgAssign (J/dataflow/DataUtils.java:193-205): out[2*t] = from, out[2*t+1] = to.
+ * Host only; the feature-range ownership of worker t among `workers`. */
+int ytk_gbdt_avg_assign(int32_t amount, int32_t workers, int32_t *out);
+
+/* SplitInfo.needReplace reduction used by syncBestSplit
+ * (J/data/gbdt/SplitInfo.java:99-104, DataParallelTreeMaker.java:640-653): folds `n`
+ * per-worker records (rank order) into *out.  Host only. */
+int ytk_gbdt_merge_splits(const ytk_split *records, int32_t n, ytk_split *out);
+
+/* Writes the 128-byte NCCL unique id rank 0 must hand to every ytk_gbdt_create of a
+ * world > 1 clique (the rendezvous ytk-mp4j's CommMaster performs,
+ * bin/local_optimizer.sh:39).  The transport of those bytes is the host's business. */
+int ytk_gbdt_nccl_unique_id(void *out128);
+
+/* Replaces `new DataParallelTreeMaker(comm, params, trainData, position, feaApprData)`
+ * (J/optimizer/GBDTOptimizer.java:319-320, ctor DataParallelTreeMaker.java:167-227).
+ * One instance per GPU = one mp4j rank; `rank`/`world` as comm.getRank()*threadNum+threadId
+ * and slaveNum*threadNum.  nccl_id may be NULL when world == 1. */
+int ytk_gbdt_create(const ytk_gbdt_params *params, int32_t device, int32_t rank, int32_t world,
+                    const void *nccl_id, ytk_gbdt **out);
+int ytk_gbdt_destroy(ytk_gbdt *h);
+
+/* FeatureApprData.getFeaSplitValStartIndex() (J/data/gbdt/FeatureApprData.java:216-218):
+ * start[F+1] prefix array of bins per feature; n_rows = trainData.sampleNum of this shard.
+ * Feature-range ownership is avgAssign(F, world) as in
+ * GBDTDataFlow.handleOtherTrainInfo (J/dataflow/GBDTDataFlow.java:252-263). */
+int ytk_gbdt_set_bins(ytk_gbdt *h, const int32_t *start, int32_t F, int64_t n_rows);
+
+/* One chunk of GBDTCoreData.x after binning (J/dataflow/GBDTCoreData.java:164-168,
+ * FeatureApprData.java:202): int32 slot indices, row-major with stride S = maxFeatureDim.
+ * The device keeps them as uint8, row-major, padded to 32 features. */
+int ytk_gbdt_upload_rows(ytk_gbdt *h, const int32_t *x_chunk, int64_t row0, int64_t nrows,
+                         int32_t stride);
+
+/* Same rows, but still holding Float.floatToRawIntBits(value)
+ * (GBDTCoreData.java:381): applies FeatureApprData.convertFeaVal2ApprFeaIndex
+ * (J/data/gbdt/FeatureApprData.java:179-205, BinarySearch.findLastEqualOrUpper
+ * J/utils/BinarySearch.java:33-56) on the device.  cuts = all features' sorted bin
+ * centres concatenated, feature f at [start[f], start[f+1]). */
+int ytk_gbdt_quantize_rows(ytk_gbdt *h, const int32_t *xbits_chunk, int64_t row0, int64_t nrows,
+                           int32_t stride, const float *cuts);
+
+/* Reads back rows [row0, row0+nrows) of the device bin matrix as int32 [nrows][F]. */
+int ytk_gbdt_download_rows(ytk_gbdt *h, int32_t *out, int64_t row0, int64_t nrows);
+
+/* One chunk of GBDTCoreData.gradPairs (J/dataflow/GBDTCoreData.java:194-202):
+ * float (g,h) at [(row*K + gid)*2 + {0,1}], rewritten by the Java side every round
+ * (J/optimizer/GBDTOptimizer.java:550-552,598-599). */
+int ytk_gbdt_set_grads(ytk_gbdt *h, const float *gp_chunk, int64_t row0, int64_t nrows);
+
+/* ITreeMaker.make(groupId) (J/optimizer/gbdt/ITreeMaker.java:34-39,
+ * DataParallelTreeMaker.make :229-295).  fea_index = the sorted sampled feature ids of
+ * initAssistData (:425-469), NULL = all; row_mask (N bytes, 0 = not sampled) replaces the
+ * unseeded subsampling of :406-419, NULL = all rows.  ts may be NULL. */
+int ytk_gbdt_make_tree(ytk_gbdt *h, int32_t gid, const int32_t *fea_index, int32_t n_fea,
+                       const uint8_t *row_mask, ytk_tree_out *out, ytk_time_stats *ts);
+
+/* Final partition of the last make(): node id of every local row, -1 if not sampled
+ * (SamplePositionData.getPosAndSampleIndex, J/data/gbdt/SamplePositionData.java:64-74;
+ * consumed by TreeRefiner, J/optimizer/gbdt/TreeRefiner.java:104-123). */
+int ytk_gbdt_get_positions(ytk_gbdt *h, int32_t *node_of_row);
+
+/* ---- per-stage hooks (parity tests and kernel benches; same kernels make() uses) ---- */
+
+/* HistogramBuilder.buildHist (J/data/gbdt/HistogramBuilder.java:56-98) for the listed
+ * local rows (NULL = all rows, contiguous): out[2*B] doubles, (g,h) interleaved at
+ * 2*(start[fid]+slot); world > 1: reduced over ranks, every rank gets the full array. */
+int ytk_gbdt_build_hist(ytk_gbdt *h, int32_t gid, const int32_t *rows, int64_t n_rows,
+                        const int32_t *fea_index, int32_t n_fea, double *out);
+
+/* HistogramBuilder.substract (:101-107): out = parent - small over 2*B doubles, computed
+ * on the device in the integer domain the tree maker uses. */
+int ytk_gbdt_subtract_hist(ytk_gbdt *h, const double *parent, const double *small, double *out);
+
+/* updateTreeMakerNodeStats + enumerateSplit + SplitInfo.update over all sampled features
+ * (DataParallelTreeMaker.java:543-637) on a caller-supplied histogram (2*B doubles). */
+int ytk_gbdt_find_split(ytk_gbdt *h, const double *hist, int64_t sample_cnt,
+                        const int32_t *fea_index, int32_t n_fea, ytk_split *out);
+
+/* SamplePositionData.resetPosition (J/data/gbdt/SamplePositionData.java:115-133) on a
+ * caller-supplied row list: stable split into rows with (float)slot(row,fid) < cond
+ * (first) and the rest; returns the number of left rows. */
+int ytk_gbdt_partition_rows(ytk_gbdt *h, const int32_t *rows, int64_t n_rows, int32_t fid,
+                            float cond, int32_t *out_rows, int64_t *left_cnt);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

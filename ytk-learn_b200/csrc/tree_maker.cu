@@ -1,0 +1,1033 @@
+// Host side of libytkgbdt.so: the tree maker behind the reference's ITreeMaker seam.
+// Restates the control flow of DataParallelTreeMaker.make
+// (J/optimizer/gbdt/DataParallelTreeMaker.java:229-295) -- expansion queue, stop rules,
+// smaller-child / subtraction trick, HistogramPool policy -- and drives the kernels of
+// kernels.cu.  J/ = /root/reference/src/main/java/com/fenbi/ytklearn/.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "nccl_dyn.h"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess)                                                                    \
+            return fail(YTK_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+    } while (0)
+
+#define NK(call)                                                                                   \
+    do {                                                                                           \
+        ncclResult_t r__ = (call);                                                                 \
+        if (r__ != ncclSuccess)                                                                    \
+            return fail(YTK_ERR_NCCL, "%s:%d %s: %s", __FILE__, __LINE__, #call,                   \
+                        ytk::nccl_api().GetErrorString(r__));                                      \
+    } while (0)
+
+#define RET(call)                 \
+    do {                          \
+        int r__ = (call);         \
+        if (r__ != YTK_OK) return r__; \
+    } while (0)
+
+double now_ms() {
+    using namespace std::chrono;
+    return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+// HistogramPool (J/data/gbdt/HistogramPool.java:190-267): bounded cache nid -> histogram.
+// Slots keep their device buffers when recycled, exactly like the Java arrays, so the
+// (degenerate) case of a parent evicted by its own child's allocation behaves as there.
+struct HistPool {
+    struct Item { int nid; long long* buf; };
+    int capacity = 0;
+    std::vector<Item*> used;     // allocation order, oldest first
+    std::deque<Item*> avail;     // FIFO
+    std::vector<Item*> all;
+
+    void clear() {               // :200-206
+        for (Item* it : used) avail.push_back(it);
+        used.clear();
+    }
+    long long* get(int nid) {    // getHist :238-245
+        for (Item* it : used) if (it->nid == nid) return it->buf;
+        return nullptr;
+    }
+    void release(int nid) {      // releaseHist :256-267
+        for (size_t i = 0; i < used.size(); i++) {
+            if (used[i]->nid == nid) {
+                avail.push_back(used[i]);
+                used.erase(used.begin() + i);
+                return;
+            }
+        }
+    }
+    // allocHist :209-236; *fresh is set when a new device buffer is needed
+    Item* alloc(int nid, bool* fresh) {
+        Item* it;
+        *fresh = false;
+        if (!avail.empty()) {
+            it = avail.front(); avail.pop_front();
+        } else if ((int)all.size() < capacity) {
+            it = new Item{nid, nullptr};
+            all.push_back(it);
+            *fresh = true;
+        } else {
+            it = used.front(); used.erase(used.begin());   // evict the oldest
+        }
+        it->nid = nid;
+        used.push_back(it);
+        return it;
+    }
+};
+
+struct Interval { int64_t b = 0, e = 0; int buf = -1; };   // buf -1: identity (rows b..e-1)
+
+struct NodeStats {                 // TreeMakerNodeStats (DataParallelTreeMaker.java:52-81)
+    double sumG = 0, sumH = 0;
+    float root_gain = 0, node_value = 0;
+    int64_t sample_cnt = 0;
+    float best_lc = -std::numeric_limits<float>::infinity();
+    int best_fid = -1, best_lo = -1, best_hi = -1;
+};
+
+struct ExpandNode { int nid; float loss_chg; int depth; int seq; };
+
+int java_float_compare(float a, float b) {   // java.lang.Float.compare
+    if (a < b) return -1;
+    if (a > b) return 1;
+    int32_t ia, ib;
+    if (a != a) ia = 0x7fc00000; else memcpy(&ia, &a, 4);
+    if (b != b) ib = 0x7fc00000; else memcpy(&ib, &b, 4);
+    return ia == ib ? 0 : (ia < ib ? -1 : 1);
+}
+
+struct Mailbox {                   // pinned host memory the device results land in
+    ytk::PartitionCounts counts[2];    // local, global
+    long long leaf[2];
+    ytk::GradScale scale;
+    ytk_split split[2 * 64];           // [node 0/1][rank]
+};
+
+}  // namespace
+
+// Host mirror of UpdateStrategy.calcGain / calcNodeValue
+// (J/optimizer/gbdt/UpdateStrategy.java:55-100) for the two leaf totals computeLeafStats
+// derives on the host (large = parent - small, DataParallelTreeMaker.java:381-384).
+// Compiled without FMA contraction (see the build flags) so it matches the kernel's
+// _rn arithmetic.
+static double host_threshold_l1(double w, double lambda) {
+    if (w > lambda) return w - lambda;
+    if (w < -lambda) return w + lambda;
+    return 0.0;
+}
+static double host_node_value(const ytk_gbdt_params* p, double G, double H) {
+    if (H < p->min_child_hessian_sum) return 0.0;
+    double val = (p->l1 == 0.0) ? -G / (H + p->l2) : -host_threshold_l1(G, p->l1) / (H + p->l2);
+    if (p->max_abs_leaf_val > 0) {
+        if (val > p->max_abs_leaf_val) val = p->max_abs_leaf_val;
+        else if (val < -p->max_abs_leaf_val) val = -p->max_abs_leaf_val;
+    }
+    return val;
+}
+static double host_gain(const ytk_gbdt_params* p, double G, double H) {
+    if (H < p->min_child_hessian_sum) return 0.0;
+    if (p->max_abs_leaf_val <= 0) {
+        double t = (p->l1 == 0.0) ? G : host_threshold_l1(G, p->l1);
+        volatile double num = t * t;
+        return num / (H + p->l2);
+    }
+    double v = host_node_value(p, G, H);
+    volatile double a = G * v;
+    volatile double hl = 0.5 * (H + p->l2);
+    volatile double vv = v * v;
+    volatile double b = hl * vv;
+    volatile double c = p->l1 * std::fabs(v);
+    volatile double s = a + b;
+    volatile double s2 = s + c;
+    return -2 * s2;
+}
+static void ytk_host_node_value(const ytk_gbdt_params* p, double G, double H, float* root_gain, float* node_value) {
+    *root_gain = (float)host_gain(p, G, H);
+    *node_value = (float)host_node_value(p, G, H);
+}
+
+struct ytk_gbdt {
+    ytk_gbdt_params p{};
+    int device = 0, rank = 0, world = 1;
+    cudaStream_t st = nullptr;
+    ncclComm_t comm = nullptr;
+
+    int F = 0, S8 = 0, B = 0, groups = 0;
+    int64_t N = 0;
+    std::vector<int32_t> start, nbins, assign;   // assign: avgAssign(F, world)
+    int f_from = 0, f_to = 0;
+    int64_t seg_max = 0;      // owned-segment length (int64 words), equal on every rank
+    int64_t local_len = 0;    // length of a locally built histogram (world * seg_max)
+
+    uint8_t* d_bins = nullptr;
+    float* d_gp = nullptr;
+    int2* d_gq = nullptr;
+    int32_t* d_rowidx[2] = {nullptr, nullptr};
+    int32_t* d_scratch = nullptr;      // partition scratch
+    uint8_t* d_mask = nullptr;
+    int32_t* d_start = nullptr;
+    int32_t* d_nbins = nullptr;
+    int64_t* d_off_local = nullptr;    // layout of a locally built histogram ([rank][segment])
+    int64_t* d_off_owned = nullptr;    // layout inside this rank's reduced segment
+    int64_t* d_off_flat = nullptr;     // reference layout 2*start[f]
+    uint32_t* d_group_mask = nullptr;
+    uint8_t* d_fea_sel = nullptr;
+    long long* d_hist_local = nullptr; // world > 1: local histogram before the reduce-scatter
+    long long* d_hist_flat = nullptr;  // hooks
+    long long* d_hist_flat2 = nullptr;
+    double* d_hist_dbl = nullptr;
+    ytk::GradScale* d_scale = nullptr;
+    ytk::GradScale* d_scale_hook = nullptr;
+    unsigned* d_absmax = nullptr;
+    ytk::PartitionCounts* d_counts = nullptr;  // [2]: local, global
+    ytk_split* d_split = nullptr;              // [2 nodes][world]
+    ytk_split* d_split_local = nullptr;        // [2]
+    long long* d_leaf = nullptr;               // [2]
+    int* d_bad = nullptr;
+    int32_t* d_node_of_row = nullptr;
+    void* d_stage = nullptr;  size_t stage_bytes = 0;   // upload staging
+    Mailbox* mail = nullptr;
+
+    HistPool pool;
+    bool grads_set = false, rows_set = false;
+    std::vector<Interval> iv;          // last tree: interval of every node
+    std::vector<int> leaf_nodes;
+    int64_t root_begin = 0;
+    int launches = 0;
+    std::vector<cudaEvent_t> ev;       // event pairs around histogram builds
+    int ev_used = 0;
+};
+
+namespace {
+
+using ytk::GainParams;
+
+GainParams gain_params(const ytk_gbdt_params& p) {
+    GainParams g;
+    g.min_child_weight = p.min_child_hessian_sum;
+    g.max_abs_leaf_val = p.max_abs_leaf_val;
+    g.l1 = p.l1; g.l2 = p.l2;
+    g.min_split_loss = p.min_split_loss;
+    g.min_split_samples = p.min_split_samples;
+    return g;
+}
+
+int ensure_stage(ytk_gbdt* h, size_t bytes) {
+    if (h->stage_bytes >= bytes) return YTK_OK;
+    if (h->d_stage) CK(cudaFree(h->d_stage));
+    h->d_stage = nullptr; h->stage_bytes = 0;
+    CK(cudaMalloc(&h->d_stage, bytes));
+    h->stage_bytes = bytes;
+    return YTK_OK;
+}
+
+void free_all(ytk_gbdt* h) {
+    cudaSetDevice(h->device);
+    auto F = [](void* p) { if (p) cudaFree(p); };
+    F(h->d_bins); F(h->d_gp); F(h->d_gq); F(h->d_rowidx[0]); F(h->d_rowidx[1]); F(h->d_scratch);
+    F(h->d_mask); F(h->d_start); F(h->d_nbins); F(h->d_off_local); F(h->d_off_owned); F(h->d_off_flat);
+    F(h->d_group_mask); F(h->d_fea_sel); F(h->d_hist_local); F(h->d_hist_flat); F(h->d_hist_flat2);
+    F(h->d_hist_dbl); F(h->d_scale); F(h->d_scale_hook); F(h->d_absmax); F(h->d_counts); F(h->d_split);
+    F(h->d_split_local); F(h->d_leaf); F(h->d_bad); F(h->d_node_of_row); F(h->d_stage);
+    for (auto* it : h->pool.all) { F(it->buf); delete it; }
+    for (auto e : h->ev) cudaEventDestroy(e);
+    if (h->mail) cudaFreeHost(h->mail);
+    if (h->comm) ytk::nccl_api().CommDestroy(h->comm);
+    if (h->st) cudaStreamDestroy(h->st);
+}
+
+// Selected-feature tables for one make()/hook call (initAssistData, :425-469).
+int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* first_owned) {
+    std::vector<uint8_t> sel(h->F, 0);
+    if (!fea_index) {
+        std::fill(sel.begin(), sel.end(), 1);
+    } else {
+        if (n_fea < 1) return fail(YTK_ERR_ARG, "n_fea must be >= 1");
+        for (int i = 0; i < n_fea; i++) {
+            if (fea_index[i] < 0 || fea_index[i] >= h->F)
+                return fail(YTK_ERR_ARG, "fea_index[%d]=%d out of range [0,%d)", i, fea_index[i], h->F);
+            sel[fea_index[i]] = 1;
+        }
+    }
+    std::vector<uint32_t> gm(h->groups, 0);
+    for (int f = 0; f < h->F; f++) if (sel[f]) gm[f / ytk::kGroup] |= 1u << (f % ytk::kGroup);
+    *first_owned = -1;   // firstSampledFeaIndexInThread (:451-467)
+    for (int f = h->f_from; f < h->f_to; f++) if (sel[f]) { *first_owned = f; break; }
+    CK(cudaMemcpyAsync(h->d_fea_sel, sel.data(), h->F, cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemcpyAsync(h->d_group_mask, gm.data(), h->groups * sizeof(uint32_t), cudaMemcpyHostToDevice, h->st));
+    CK(cudaStreamSynchronize(h->st));   // host vectors go out of scope
+    return YTK_OK;
+}
+
+int count_selected(const ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea) {
+    if (!fea_index) return h->F;
+    std::vector<uint8_t> sel(h->F, 0);
+    int c = 0;
+    for (int i = 0; i < n_fea; i++) if (!sel[fea_index[i]]) { sel[fea_index[i]] = 1; c++; }
+    return c;
+}
+
+int hist_events(ytk_gbdt* h, cudaEvent_t* a, cudaEvent_t* b) {
+    if (h->ev_used + 2 > (int)h->ev.size()) {
+        for (int i = 0; i < 2; i++) {
+            cudaEvent_t e;
+            CK(cudaEventCreate(&e));
+            h->ev.push_back(e);
+        }
+    }
+    *a = h->ev[h->ev_used]; *b = h->ev[h->ev_used + 1];
+    h->ev_used += 2;
+    return YTK_OK;
+}
+
+// HistogramBuilder.buildHist (J/data/gbdt/HistogramBuilder.java:56-98) into `dst`
+// (this rank's reduced segment): local build, then the reduce-scatter by feature range.
+int build_node_hist(ytk_gbdt* h, const Interval& iv, long long* dst, ytk_time_stats* ts, int n_sel) {
+    const int32_t* rowidx = iv.buf < 0 ? nullptr : h->d_rowidx[iv.buf];
+    long long* local = h->world == 1 ? dst : h->d_hist_local;
+    cudaEvent_t e0, e1;
+    RET(hist_events(h, &e0, &e1));
+    CK(cudaEventRecord(e0, h->st));
+    CK(cudaMemsetAsync(local, 0, h->local_len * sizeof(long long), h->st));
+    CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, rowidx, iv.b, iv.e, h->F, h->d_group_mask, h->d_nbins,
+                              h->d_off_local, local, 0, h->st, &h->launches));
+    CK(cudaEventRecord(e1, h->st));
+    if (h->world > 1) {
+        double t0 = now_ms();
+        NK(ytk::nccl_api().ReduceScatter(local, dst, (size_t)h->seg_max, ncclInt64, ncclSum, h->comm, h->st));
+        if (ts) ts->communicate_hist += now_ms() - t0;
+    }
+    if (ts) {
+        ts->hist_built++;
+        ts->hist_cells += (double)(iv.e - iv.b) * n_sel;
+        ts->hist_rows += (double)(iv.e - iv.b);
+        if (iv.buf >= 0) ts->hist_rows_indexed += (double)(iv.e - iv.b);
+    }
+    return YTK_OK;
+}
+
+// updateTreeMakerNodeStats + findBestSplit(nid, hist) + syncBestSplit (:543-595, :640-653)
+// for up to two nodes at once; results land in the mailbox.
+int search_nodes(ytk_gbdt* h, int n_nodes, long long* const* hists, const int64_t* sample_cnt, int first_owned) {
+    GainParams gp = gain_params(h->p);
+    for (int k = 0; k < n_nodes; k++) {
+        CK(ytk::launch_split_scan(hists[k], h->d_start, h->d_off_owned, h->d_fea_sel, h->f_from, h->f_to,
+                                  first_owned, h->d_scale, gp, sample_cnt[k], nullptr,
+                                  h->d_split_local + k, h->st));
+        h->launches++;
+    }
+    if (h->world == 1) {
+        CK(cudaMemcpyAsync(h->mail->split, h->d_split_local, n_nodes * sizeof(ytk_split), cudaMemcpyDeviceToHost,
+                           h->st));
+    } else {
+        // "split allgather": every rank's record for each node, merged on the host with the
+        // needReplace rule -- replaces allreduceRpc(SplitInfo) and allreduceArrayRpc(MAX)
+        NK(ytk::nccl_api().AllGather(h->d_split_local, h->d_split, n_nodes * sizeof(ytk_split), ncclChar, h->comm,
+                                     h->st));
+        CK(cudaMemcpyAsync(h->mail->split, h->d_split, (size_t)h->world * n_nodes * sizeof(ytk_split),
+                           cudaMemcpyDeviceToHost, h->st));
+    }
+    CK(cudaStreamSynchronize(h->st));
+    return YTK_OK;
+}
+
+void merged_record(const ytk_gbdt* h, int n_nodes, int k, ytk_split* out) {
+    if (h->world == 1) { *out = h->mail->split[k]; return; }
+    std::vector<ytk_split> recs(h->world);
+    for (int r = 0; r < h->world; r++) recs[r] = h->mail->split[r * n_nodes + k];
+    ytk_gbdt_merge_splits(recs.data(), h->world, out);
+}
+
+void apply_record(NodeStats& s, const ytk_split& r) {
+    s.sumG = r.sum_grad; s.sumH = r.sum_hess;
+    s.root_gain = r.root_gain; s.node_value = r.node_value;
+    s.best_lc = r.loss_chg; s.best_fid = r.fid; s.best_lo = r.lo; s.best_hi = r.hi;
+}
+
+}  // namespace
+
+// =====================================================================================
+// C ABI
+// =====================================================================================
+extern "C" {
+
+const char* ytk_gbdt_last_error(void) { return g_err.c_str(); }
+
+int32_t ytk_gbdt_normalize_max_leaf_cnt(int32_t max_depth, int32_t max_leaf_cnt) {
+    if (max_depth > 0) {
+        int32_t cap = (int32_t)std::pow(2.0, (double)max_depth);
+        if (max_leaf_cnt < 0) return cap;
+        return std::min(max_leaf_cnt, cap);
+    }
+    return max_leaf_cnt;
+}
+
+int ytk_gbdt_avg_assign(int32_t amount, int32_t workers, int32_t* out) {
+    if (workers < 1 || amount < 0 || !out) return fail(YTK_ERR_ARG, "avg_assign: bad arguments");
+    int32_t avg = amount / workers, mod = amount % workers, fidx = 0;
+    for (int32_t t = 0; t < workers; t++) {
+        int32_t tnum = t < mod ? avg + 1 : avg;
+        out[2 * t] = fidx; out[2 * t + 1] = fidx + tnum;
+        fidx += tnum;
+    }
+    return YTK_OK;
+}
+
+int ytk_gbdt_merge_splits(const ytk_split* recs, int32_t n, ytk_split* out) {
+    if (!recs || !out || n < 1) return fail(YTK_ERR_ARG, "merge_splits: bad arguments");
+    ytk_split best = recs[0];
+    double G = recs[0].sum_grad, H = recs[0].sum_hess;
+    for (int i = 1; i < n; i++) {
+        const ytk_split& t2 = recs[i];
+        // t1.needReplace(t2.lossChg, t2.splitIndex) ? t2 : t1   (DataParallelTreeMaker.java:645-649)
+        bool rep = (best.fid <= t2.fid) ? (t2.loss_chg > best.loss_chg) : (t2.loss_chg >= best.loss_chg);
+        if (rep) best = t2;
+        if (t2.sum_grad > G) G = t2.sum_grad;      // allreduce MAX, element-wise (:560)
+        if (t2.sum_hess > H) H = t2.sum_hess;
+    }
+    // root_gain / node_value are functions of (G,H): take them from a rank that had the totals
+    for (int i = 0; i < n; i++) {
+        if (recs[i].sum_grad == G && recs[i].sum_hess == H) {
+            best.root_gain = recs[i].root_gain; best.node_value = recs[i].node_value;
+            break;
+        }
+    }
+    best.sum_grad = G; best.sum_hess = H;
+    *out = best;
+    return YTK_OK;
+}
+
+int ytk_gbdt_nccl_unique_id(void* out128) {
+    const char* why = "";
+    if (!ytk::nccl_api().load(&why)) return fail(YTK_ERR_NCCL, "NCCL unavailable: %s", why);
+    ncclUniqueId id;
+    NK(ytk::nccl_api().GetUniqueId(&id));
+    static_assert(sizeof(id) == 128, "ncclUniqueId is 128 bytes");
+    memcpy(out128, &id, 128);
+    return YTK_OK;
+}
+
+int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank, int32_t world,
+                    const void* nccl_id, ytk_gbdt** out) {
+    if (!params || !out) return fail(YTK_ERR_ARG, "create: null argument");
+    if (world < 1 || rank < 0 || rank >= world) return fail(YTK_ERR_ARG, "create: bad rank %d / world %d", rank, world);
+    if (world > 64) return fail(YTK_ERR_ARG, "create: world %d > 64", world);
+    if (params->class_num < 1) return fail(YTK_ERR_ARG, "class_num(%d) should >= 1", params->class_num);
+    if (params->max_leaf_cnt == 0) return fail(YTK_ERR_ARG, "max_leaf_cnt(0) should not be 0");
+    if (params->max_leaf_cnt < 0 && params->max_depth < 0)
+        return fail(YTK_ERR_ARG, "max_leaf_cnt(%d) and max_depth(%d) should not be both negative",
+                    params->max_leaf_cnt, params->max_depth);
+    if (params->grow_policy != 0 && params->grow_policy != 1)
+        return fail(YTK_ERR_ARG, "tree maker policy(%d) invalid!", params->grow_policy);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev < 1)
+        return fail(YTK_ERR_CUDA, "no CUDA device (%s); libytkgbdt has no CPU path",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(YTK_ERR_ARG, "create: device %d not in [0,%d)", device, ndev);
+    CK(cudaSetDevice(device));
+    ytk_gbdt* h = new ytk_gbdt();
+    h->p = *params; h->device = device; h->rank = rank; h->world = world;
+    int rc = YTK_OK;
+    auto bail = [&](int code) { free_all(h); delete h; return code; };
+    if (cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking) != cudaSuccess)
+        return bail(fail(YTK_ERR_CUDA, "cudaStreamCreate failed"));
+    if (cudaHostAlloc((void**)&h->mail, sizeof(Mailbox), cudaHostAllocDefault) != cudaSuccess)
+        return bail(fail(YTK_ERR_CUDA, "cudaHostAlloc failed"));
+    if (world > 1) {
+        const char* why = "";
+        if (!nccl_id) return bail(fail(YTK_ERR_ARG, "create: world > 1 needs the NCCL unique id"));
+        if (!ytk::nccl_api().load(&why)) return bail(fail(YTK_ERR_NCCL, "NCCL unavailable: %s", why));
+        ncclUniqueId id;
+        memcpy(&id, nccl_id, 128);
+        ncclResult_t r = ytk::nccl_api().CommInitRank(&h->comm, world, id, rank);
+        if (r != ncclSuccess)
+            return bail(fail(YTK_ERR_NCCL, "ncclCommInitRank: %s", ytk::nccl_api().GetErrorString(r)));
+    }
+    (void)rc;
+    *out = h;
+    return YTK_OK;
+}
+
+int ytk_gbdt_destroy(ytk_gbdt* h) {
+    if (!h) return YTK_OK;
+    free_all(h);
+    delete h;
+    return YTK_OK;
+}
+
+int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_rows) {
+    if (!h || !start || F < 1 || n_rows < 0) return fail(YTK_ERR_ARG, "set_bins: bad arguments");
+    if (h->rows_set) return fail(YTK_ERR_ARG, "set_bins: already called");
+    if (n_rows > 0x7fffffffLL) return fail(YTK_ERR_ARG, "set_bins: %lld rows exceed int32 row ids", (long long)n_rows);
+    CK(cudaSetDevice(h->device));
+    h->F = F; h->N = n_rows;
+    h->start.assign(start, start + F + 1);
+    h->nbins.resize(F);
+    for (int f = 0; f < F; f++) {
+        h->nbins[f] = start[f + 1] - start[f];
+        if (h->nbins[f] < 1) return fail(YTK_ERR_ARG, "[GBDT] fid:%d has no global feature vals!", f);
+        if (h->nbins[f] > ytk::kMaxBins)
+            return fail(YTK_ERR_UNSUPPORTED, "feature %d has %d bins; this build stores slots as uint8 (max %d)",
+                        f, h->nbins[f], ytk::kMaxBins);
+    }
+    if (start[0] != 0) return fail(YTK_ERR_ARG, "set_bins: start[0] must be 0");
+    h->B = start[F];
+    h->groups = (F + ytk::kGroup - 1) / ytk::kGroup;
+    h->S8 = h->groups * ytk::kGroup;
+    // GBDTDataFlow.handleOtherTrainInfo (J/dataflow/GBDTDataFlow.java:252-263) and
+    // FeatureApprData.updateGlobalHistAssign (J/data/gbdt/FeatureApprData.java:98-111)
+    h->assign.resize(2 * h->world);
+    ytk_gbdt_avg_assign(F, h->world, h->assign.data());
+    h->f_from = h->assign[2 * h->rank]; h->f_to = h->assign[2 * h->rank + 1];
+    h->seg_max = 0;
+    for (int r = 0; r < h->world; r++)
+        h->seg_max = std::max<int64_t>(h->seg_max, 2LL * (start[h->assign[2 * r + 1]] - start[h->assign[2 * r]]));
+    if (h->seg_max == 0) h->seg_max = 2;
+    h->local_len = h->seg_max * h->world;
+    std::vector<int64_t> off_local(F), off_owned(F, 0), off_flat(F);
+    for (int r = 0; r < h->world; r++)
+        for (int f = h->assign[2 * r]; f < h->assign[2 * r + 1]; f++)
+            off_local[f] = r * h->seg_max + 2LL * (start[f] - start[h->assign[2 * r]]);
+    for (int f = 0; f < F; f++) off_flat[f] = 2LL * start[f];
+    for (int f = h->f_from; f < h->f_to; f++) off_owned[f] = 2LL * (start[f] - start[h->f_from]);
+
+    const int64_t N1 = std::max<int64_t>(n_rows, 1);
+    const int K = h->p.class_num;
+    CK(cudaMalloc(&h->d_bins, N1 * h->S8));
+    CK(cudaMemsetAsync(h->d_bins, 0, N1 * h->S8, h->st));
+    CK(cudaMalloc(&h->d_gp, N1 * K * 2 * sizeof(float)));
+    CK(cudaMalloc(&h->d_gq, N1 * sizeof(int2)));
+    CK(cudaMalloc(&h->d_rowidx[0], N1 * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_rowidx[1], N1 * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_scratch, ytk::partition_scratch_ints(N1) * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_node_of_row, N1 * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_start, (F + 1) * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_nbins, F * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_off_local, F * sizeof(int64_t)));
+    CK(cudaMalloc(&h->d_off_owned, F * sizeof(int64_t)));
+    CK(cudaMalloc(&h->d_off_flat, F * sizeof(int64_t)));
+    CK(cudaMalloc(&h->d_group_mask, h->groups * sizeof(uint32_t)));
+    CK(cudaMalloc(&h->d_fea_sel, F));
+    CK(cudaMalloc(&h->d_hist_local, h->local_len * sizeof(long long)));
+    CK(cudaMalloc(&h->d_hist_flat, 2LL * h->B * sizeof(long long)));
+    CK(cudaMalloc(&h->d_hist_flat2, 2LL * h->B * sizeof(long long)));
+    CK(cudaMalloc(&h->d_hist_dbl, 2LL * h->B * sizeof(double)));
+    CK(cudaMalloc(&h->d_scale, sizeof(ytk::GradScale)));
+    CK(cudaMalloc(&h->d_scale_hook, sizeof(ytk::GradScale)));
+    CK(cudaMalloc(&h->d_absmax, 2 * sizeof(unsigned)));
+    CK(cudaMalloc(&h->d_counts, 2 * sizeof(ytk::PartitionCounts)));
+    CK(cudaMalloc(&h->d_split, 2 * h->world * sizeof(ytk_split)));
+    CK(cudaMalloc(&h->d_split_local, 2 * sizeof(ytk_split)));
+    CK(cudaMalloc(&h->d_leaf, 2 * sizeof(long long)));
+    CK(cudaMalloc(&h->d_bad, sizeof(int)));
+    CK(cudaMemsetAsync(h->d_bad, 0, sizeof(int), h->st));
+    CK(cudaMemcpyAsync(h->d_start, start, (F + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemcpyAsync(h->d_nbins, h->nbins.data(), F * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemcpyAsync(h->d_off_local, off_local.data(), F * sizeof(int64_t), cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemcpyAsync(h->d_off_owned, off_owned.data(), F * sizeof(int64_t), cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemcpyAsync(h->d_off_flat, off_flat.data(), F * sizeof(int64_t), cudaMemcpyHostToDevice, h->st));
+    CK(cudaStreamSynchronize(h->st));
+
+    // pool capacity (DataParallelTreeMaker.java:193-203); UNIT = 64, MB = 1<<20
+    int capacity;
+    if (h->p.histogram_pool_capacity > 0) {
+        capacity = (int)(h->p.histogram_pool_capacity * 1048576.0 / 64 / h->B);
+        capacity = std::max(2, capacity);
+        capacity = std::min(capacity, h->p.max_leaf_cnt);
+    } else {
+        capacity = h->p.max_leaf_cnt;
+    }
+    if (capacity < 1) return fail(YTK_ERR_ARG, "histogram pool capacity %d < 1 (max_leaf_cnt %d)", capacity, h->p.max_leaf_cnt);
+    h->pool.capacity = capacity;
+    h->rows_set = true;
+    return YTK_OK;
+}
+
+static int check_rows(ytk_gbdt* h, const void* p, int64_t row0, int64_t nrows, const char* who) {
+    if (!h || !h->rows_set) return fail(YTK_ERR_ARG, "%s: call set_bins first", who);
+    if (nrows < 0 || row0 < 0 || row0 + nrows > h->N)
+        return fail(YTK_ERR_ARG, "%s: rows [%lld,%lld) outside [0,%lld)", who, (long long)row0,
+                    (long long)(row0 + nrows), (long long)h->N);
+    if (nrows > 0 && !p) return fail(YTK_ERR_ARG, "%s: null buffer", who);
+    return YTK_OK;
+}
+
+int ytk_gbdt_upload_rows(ytk_gbdt* h, const int32_t* x_chunk, int64_t row0, int64_t nrows, int32_t stride) {
+    RET(check_rows(h, x_chunk, row0, nrows, "upload_rows"));
+    if (stride < h->F) return fail(YTK_ERR_ARG, "upload_rows: stride %d < feature dim %d", stride, h->F);
+    if (nrows == 0) return YTK_OK;
+    CK(cudaSetDevice(h->device));
+    const int64_t step = std::max<int64_t>(1, (64LL << 20) / ((int64_t)stride * 4));
+    for (int64_t r = 0; r < nrows; r += step) {
+        int64_t n = std::min(step, nrows - r);
+        size_t bytes = (size_t)n * stride * sizeof(int32_t);
+        RET(ensure_stage(h, bytes));
+        CK(cudaMemcpyAsync(h->d_stage, x_chunk + r * stride, bytes, cudaMemcpyHostToDevice, h->st));
+        CK(ytk::launch_repack_rows((const int32_t*)h->d_stage, n, stride, h->F, h->d_bins + (row0 + r) * h->S8,
+                                   h->S8, h->d_bad, h->st));
+        CK(cudaStreamSynchronize(h->st));
+    }
+    int bad = 0;
+    CK(cudaMemcpy(&bad, h->d_bad, sizeof(int), cudaMemcpyDeviceToHost));
+    if (bad) {
+        CK(cudaMemset(h->d_bad, 0, sizeof(int)));
+        return fail(YTK_ERR_ARG, "upload_rows: slot index outside [0,256)");
+    }
+    return YTK_OK;
+}
+
+int ytk_gbdt_quantize_rows(ytk_gbdt* h, const int32_t* xbits_chunk, int64_t row0, int64_t nrows, int32_t stride,
+                           const float* cuts) {
+    RET(check_rows(h, xbits_chunk, row0, nrows, "quantize_rows"));
+    if (!cuts) return fail(YTK_ERR_ARG, "quantize_rows: null cuts");
+    if (stride < h->F) return fail(YTK_ERR_ARG, "quantize_rows: stride %d < feature dim %d", stride, h->F);
+    if (nrows == 0) return YTK_OK;
+    CK(cudaSetDevice(h->device));
+    float* d_cuts = nullptr;
+    CK(cudaMalloc(&d_cuts, (size_t)h->B * sizeof(float)));
+    cudaError_t e = cudaMemcpyAsync(d_cuts, cuts, (size_t)h->B * sizeof(float), cudaMemcpyHostToDevice, h->st);
+    const int64_t step = std::max<int64_t>(1, (64LL << 20) / ((int64_t)stride * 4));
+    for (int64_t r = 0; r < nrows && e == cudaSuccess; r += step) {
+        int64_t n = std::min(step, nrows - r);
+        size_t bytes = (size_t)n * stride * sizeof(int32_t);
+        if (ensure_stage(h, bytes) != YTK_OK) { cudaFree(d_cuts); return YTK_ERR_CUDA; }
+        e = cudaMemcpyAsync(h->d_stage, xbits_chunk + r * stride, bytes, cudaMemcpyHostToDevice, h->st);
+        if (e == cudaSuccess)
+            e = ytk::launch_quantize_rows((const int32_t*)h->d_stage, n, stride, h->F, d_cuts, h->d_start,
+                                          h->d_bins + (row0 + r) * h->S8, h->S8, h->st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->st);
+    }
+    cudaFree(d_cuts);
+    CK(e);
+    return YTK_OK;
+}
+
+int ytk_gbdt_download_rows(ytk_gbdt* h, int32_t* out, int64_t row0, int64_t nrows) {
+    RET(check_rows(h, out, row0, nrows, "download_rows"));
+    if (nrows == 0) return YTK_OK;
+    CK(cudaSetDevice(h->device));
+    const int64_t step = std::max<int64_t>(1, (64LL << 20) / ((int64_t)h->F * 4));
+    for (int64_t r = 0; r < nrows; r += step) {
+        int64_t n = std::min(step, nrows - r);
+        size_t bytes = (size_t)n * h->F * sizeof(int32_t);
+        RET(ensure_stage(h, bytes));
+        CK(ytk::launch_unpack_rows(h->d_bins + (row0 + r) * h->S8, h->S8, n, h->F, (int32_t*)h->d_stage, h->st));
+        CK(cudaMemcpyAsync(out + r * h->F, h->d_stage, bytes, cudaMemcpyDeviceToHost, h->st));
+        CK(cudaStreamSynchronize(h->st));
+    }
+    return YTK_OK;
+}
+
+int ytk_gbdt_set_grads(ytk_gbdt* h, const float* gp_chunk, int64_t row0, int64_t nrows) {
+    RET(check_rows(h, gp_chunk, row0, nrows, "set_grads"));
+    CK(cudaSetDevice(h->device));
+    const int K = h->p.class_num;
+    if (nrows > 0) {
+        CK(cudaMemcpyAsync(h->d_gp + row0 * K * 2, gp_chunk, (size_t)nrows * K * 2 * sizeof(float),
+                           cudaMemcpyHostToDevice, h->st));
+        CK(cudaStreamSynchronize(h->st));
+    }
+    h->grads_set = true;
+    return YTK_OK;
+}
+
+// -------------------------------------------------------------------------------------
+// ITreeMaker.make
+// -------------------------------------------------------------------------------------
+int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask,
+                       ytk_tree_out* out, ytk_time_stats* ts) {
+    if (!h || !out) return fail(YTK_ERR_ARG, "make_tree: null argument");
+    if (!h->rows_set || !h->grads_set) return fail(YTK_ERR_ARG, "make_tree: set_bins/upload_rows/set_grads first");
+    if (gid < 0 || gid >= h->p.class_num) return fail(YTK_ERR_ARG, "make_tree: groupId %d not in [0,%d)", gid, h->p.class_num);
+    if (out->capacity < 1) return fail(YTK_ERR_CAPACITY, "make_tree: tree capacity %d", out->capacity);
+    CK(cudaSetDevice(h->device));
+    const ytk_gbdt_params& p = h->p;
+    const double t_start = now_ms();
+    ytk_time_stats local_ts;
+    memset(&local_ts, 0, sizeof(local_ts));
+    ytk_time_stats* T = &local_ts;
+    h->launches = 0;
+    h->ev_used = 0;
+    const bool loss_wise = p.grow_policy == 1;
+    const float lr = p.learning_rate;
+    const int W = h->world;
+
+    // ---- initAssistData (:395-470)
+    int first_owned = -1;
+    RET(set_features(h, fea_index, n_fea, &first_owned));
+    const int n_sel = count_selected(h, fea_index, n_fea);
+    h->pool.clear();
+    CK(ytk::launch_grad_quantize(h->d_gp, h->N, p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->st));
+    h->launches += 2;
+
+    std::vector<Interval>& iv = h->iv;
+    iv.clear();
+    h->leaf_nodes.clear();
+    Interval root;
+    if (row_mask) {
+        if (!h->d_mask) CK(cudaMalloc(&h->d_mask, std::max<int64_t>(h->N, 1)));
+        CK(cudaMemcpyAsync(h->d_mask, row_mask, h->N, cudaMemcpyHostToDevice, h->st));
+        CK(ytk::launch_compact_mask(h->d_mask, h->N, h->d_rowidx[0], h->d_scratch, h->d_counts, h->st, &h->launches));
+        CK(cudaMemcpyAsync(&h->mail->counts[0], h->d_counts, sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost, h->st));
+        CK(cudaStreamSynchronize(h->st));
+        root.b = 0; root.e = h->mail->counts[0].left; root.buf = 0;
+    } else {
+        root.b = 0; root.e = h->N; root.buf = -1;
+    }
+    h->root_begin = root.e;   // rows at or beyond are unsampled
+
+    auto alloc_node = [&](int parent) -> int {     // Tree.AllocTreeNode (J/data/gbdt/Tree.java:58-64)
+        if (out->n_nodes >= out->capacity) return -1;
+        int nid = out->n_nodes++;
+        out->parent[nid] = parent; out->left[nid] = -1; out->right[nid] = -1;
+        out->fid[nid] = 0; out->lo[nid] = 0; out->hi[nid] = 0; out->node_info[nid] = 0.f;
+        out->loss_chg[nid] = 0.f; out->hess_sum[nid] = 0.f; out->sample_cnt[nid] = 0;
+        return nid;
+    };
+    std::vector<NodeStats> ns;
+    auto set_split_if_good = [&](int nid) {        // findBestSplit tail (:587-592), TreeNode.setSplit (:144-149)
+        const NodeStats& s = ns[nid];
+        if ((double)s.best_lc > p.min_split_loss) {
+            out->fid[nid] = s.best_fid; out->lo[nid] = s.best_lo; out->hi[nid] = s.best_hi;
+            out->node_info[nid] = 0.5f * (float)(s.best_lo + s.best_hi);
+        }
+    };
+    auto set_leaf = [&](int nid) {                 // :253
+        out->node_info[nid] = ns[nid].node_value * lr;
+        out->left[nid] = -1; out->right[nid] = -1;
+        h->leaf_nodes.push_back(nid);
+    };
+    auto pool_slot = [&](int nid, long long** buf) -> int {
+        bool fresh = false;
+        HistPool::Item* it = h->pool.alloc(nid, &fresh);
+        if (fresh) CK(cudaMalloc(&it->buf, h->seg_max * sizeof(long long)));
+        *buf = it->buf;
+        return YTK_OK;
+    };
+    auto global_count = [&](int64_t local, int64_t* global) -> int {   // allreduce(long, SUM) (:518)
+        if (W == 1) { *global = local; return YTK_OK; }
+        h->mail->counts[0].left = local; h->mail->counts[0].right = 0;
+        CK(cudaMemcpyAsync(h->d_counts, &h->mail->counts[0], sizeof(ytk::PartitionCounts), cudaMemcpyHostToDevice, h->st));
+        NK(ytk::nccl_api().AllReduce(h->d_counts, h->d_counts + 1, 2, ncclInt64, ncclSum, h->comm, h->st));
+        CK(cudaMemcpyAsync(&h->mail->counts[1], h->d_counts + 1, sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost, h->st));
+        CK(cudaStreamSynchronize(h->st));
+        *global = h->mail->counts[1].left;
+        return YTK_OK;
+    };
+
+    out->n_nodes = 0;
+    int root_id = alloc_node(-1);
+    ns.emplace_back();
+    iv.push_back(root);
+    RET(global_count(root.e - root.b, &ns[root_id].sample_cnt));      // initTreeMakerNodeStats(0) (:510-520)
+
+    // ---- findBestSplit(root) (:302-318)
+    {
+        double t0 = now_ms();
+        long long* slot;
+        RET(pool_slot(root_id, &slot));
+        RET(build_node_hist(h, iv[root_id], slot, T, n_sel));
+        double t1 = now_ms();
+        long long* hs[1] = {slot};
+        int64_t sc[1] = {ns[root_id].sample_cnt};
+        RET(search_nodes(h, 1, hs, sc, first_owned));
+        ytk_split rec;
+        merged_record(h, 1, 0, &rec);
+        apply_record(ns[root_id], rec);
+        set_split_if_good(root_id);
+        T->build_hist += t1 - t0;
+        T->find_best_split += now_ms() - t1;
+    }
+
+    std::vector<ExpandNode> queue;
+    int seq = 0;
+    queue.push_back({root_id, ns[root_id].best_lc, 0, seq++});
+    int num_leaf = 1;
+
+    while (!queue.empty()) {
+        // PriorityQueue.poll with lossChgComparator / sequenceComparator (:105-115)
+        size_t bi = 0;
+        for (size_t i = 1; i < queue.size(); i++) {
+            int c = 0;
+            if (loss_wise) c = java_float_compare(queue[bi].loss_chg, queue[i].loss_chg);   // larger lossChg first
+            if (c == 0) c = (queue[i].seq > queue[bi].seq) - (queue[i].seq < queue[bi].seq);
+            if (c < 0) bi = i;
+        }
+        ExpandNode e = queue[bi];
+        queue.erase(queue.begin() + bi);
+        const int nid = e.nid;
+
+        if ((double)e.loss_chg <= p.min_split_loss
+            || (p.max_depth >= 0 && p.max_depth == e.depth)
+            || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf)
+            || (p.min_split_samples > 0 && ns[nid].sample_cnt < p.min_split_samples)) {
+            set_leaf(nid);
+            continue;
+        }
+        int l = alloc_node(nid), r = alloc_node(nid);                 // tree.addChilds (:256)
+        if (l < 0 || r < 0) return fail(YTK_ERR_CAPACITY, "make_tree: tree needs more than %d nodes", out->capacity);
+        out->left[nid] = l; out->right[nid] = r;
+        ns.emplace_back(); ns.emplace_back();
+        num_leaf++;
+
+        // ---- position.resetPosition (:260)
+        double t0 = now_ms();
+        const Interval pv = iv[nid];
+        const int cbuf = pv.buf == 0 ? 1 : 0;
+        CK(ytk::launch_partition(h->d_bins, h->S8, pv.buf < 0 ? nullptr : h->d_rowidx[pv.buf], h->d_rowidx[cbuf],
+                                 pv.b, pv.e, out->fid[nid], out->node_info[nid], h->d_scratch, h->d_counts, h->st,
+                                 &h->launches));
+        if (W > 1)   // initTreeMakerNodeStats(l, r): allreduceArray(long[2], SUM) (:538)
+            NK(ytk::nccl_api().AllReduce(h->d_counts, h->d_counts + 1, 2, ncclInt64, ncclSum, h->comm, h->st));
+        CK(cudaMemcpyAsync(h->mail->counts, h->d_counts, (W > 1 ? 2 : 1) * sizeof(ytk::PartitionCounts),
+                           cudaMemcpyDeviceToHost, h->st));
+        CK(cudaStreamSynchronize(h->st));
+        const int64_t lc = h->mail->counts[0].left;
+        Interval li, ri;
+        li.b = pv.b; li.e = pv.b + lc; li.buf = cbuf;
+        ri.b = pv.b + lc; ri.e = pv.e; ri.buf = cbuf;
+        iv.push_back(li); iv.push_back(ri);
+        const ytk::PartitionCounts gc = h->mail->counts[W > 1 ? 1 : 0];
+        ns[l].sample_cnt = gc.left; ns[r].sample_cnt = gc.right;
+        T->partition += now_ms() - t0;
+
+        // smaller child: strictly fewer global rows on the left, else the right (:344-350, :493-499)
+        const int small = ns[l].sample_cnt < ns[r].sample_cnt ? l : r;
+        const int large = small == l ? r : l;
+
+        if ((p.max_depth >= 0 && p.max_depth == e.depth + 1)
+            || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf)
+            || (p.min_split_samples > 0 && ns[l].sample_cnt < p.min_split_samples
+                && ns[r].sample_cnt < p.min_split_samples)) {
+            // ---- computeLeafStats (:341-385)
+            t0 = now_ms();
+            CK(cudaMemsetAsync(h->d_leaf, 0, 2 * sizeof(long long), h->st));
+            CK(ytk::launch_leaf_sums(h->d_gq, h->d_rowidx[iv[small].buf], iv[small].b, iv[small].e, h->d_leaf, h->st));
+            h->launches++;
+            if (W > 1) NK(ytk::nccl_api().AllReduce(h->d_leaf, h->d_leaf, 2, ncclInt64, ncclSum, h->comm, h->st));
+            CK(cudaMemcpyAsync(h->mail->leaf, h->d_leaf, 2 * sizeof(long long), cudaMemcpyDeviceToHost, h->st));
+            CK(cudaMemcpyAsync(&h->mail->scale, h->d_scale, sizeof(ytk::GradScale), cudaMemcpyDeviceToHost, h->st));
+            CK(cudaStreamSynchronize(h->st));
+            NodeStats &ss = ns[small], &ls = ns[large], &ps = ns[nid];
+            ss.sumG = (double)h->mail->leaf[0] * h->mail->scale.inv_g;
+            ss.sumH = (double)h->mail->leaf[1] * h->mail->scale.inv_h;
+            ls.sumG = ps.sumG - ss.sumG; ls.sumH = ps.sumH - ss.sumH;
+            for (NodeStats* s : {&ss, &ls}) {
+                // host mirror of UpdateStrategy.calcGain / calcNodeValue (same formulas as kernels.cu)
+                ytk_split tmp;
+                ytk_host_node_value(&p, s->sumG, s->sumH, &tmp.root_gain, &tmp.node_value);
+                s->root_gain = tmp.root_gain; s->node_value = tmp.node_value;
+            }
+            set_leaf(l); set_leaf(r);
+            T->build_hist += now_ms() - t0;
+        } else {
+            // ---- findBestSplit(parent, l, r) (:320-339), buildHist(parent, l, r) (:489-508)
+            t0 = now_ms();
+            long long* parent_h = h->pool.get(nid);
+            long long *small_h, *large_h;
+            RET(pool_slot(small, &small_h));
+            RET(build_node_hist(h, iv[small], small_h, T, n_sel));
+            if (parent_h) {
+                h->pool.release(nid);
+                RET(pool_slot(large, &large_h));
+                CK(ytk::launch_hist_subtract(parent_h, small_h, large_h, h->seg_max, h->st));   // substract (:101-107)
+                h->launches++;
+            } else {
+                RET(pool_slot(large, &large_h));
+                RET(build_node_hist(h, iv[large], large_h, T, n_sel));
+                T->hist_miss++;
+            }
+            double t1 = now_ms();
+            long long* hs[2] = {small_h, large_h};
+            int64_t sc[2] = {ns[small].sample_cnt, ns[large].sample_cnt};
+            RET(search_nodes(h, 2, hs, sc, first_owned));
+            ytk_split rec;
+            merged_record(h, 2, 0, &rec); apply_record(ns[small], rec); set_split_if_good(small);
+            merged_record(h, 2, 1, &rec); apply_record(ns[large], rec); set_split_if_good(large);
+            T->build_hist += t1 - t0;
+            T->find_best_split += now_ms() - t1;
+            queue.push_back({l, ns[l].best_lc, e.depth + 1, seq++});
+            queue.push_back({r, ns[r].best_lc, e.depth + 1, seq++});
+        }
+    }
+
+    for (int nid = 0; nid < out->n_nodes; nid++) {                    // updateTreeNodeStat (:387-393)
+        out->loss_chg[nid] = ns[nid].best_lc;
+        out->hess_sum[nid] = (float)ns[nid].sumH;
+        out->sample_cnt[nid] = ns[nid].sample_cnt;
+    }
+    CK(cudaStreamSynchronize(h->st));
+    float gpu_ms = 0.f;
+    for (int i = 0; i + 1 < h->ev_used; i += 2) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
+        gpu_ms += ms;
+    }
+    T->gpu_hist_ms = gpu_ms;
+    T->compute_hist = gpu_ms;
+    T->kernel_launches = h->launches;
+    T->total = now_ms() - t_start;
+    if (ts) *ts = *T;
+    return YTK_OK;
+}
+
+int ytk_gbdt_get_positions(ytk_gbdt* h, int32_t* node_of_row) {
+    if (!h || !node_of_row) return fail(YTK_ERR_ARG, "get_positions: null argument");
+    if (h->iv.empty()) return fail(YTK_ERR_ARG, "get_positions: no tree has been made");
+    CK(cudaSetDevice(h->device));
+    CK(ytk::launch_fill_i32(h->d_node_of_row, h->N, -1, h->st));
+    for (int nid : h->leaf_nodes) {
+        const Interval& v = h->iv[nid];
+        CK(ytk::launch_fill_positions(v.buf < 0 ? nullptr : h->d_rowidx[v.buf], v.b, v.e, nid, h->d_node_of_row, h->st));
+    }
+    CK(cudaMemcpyAsync(node_of_row, h->d_node_of_row, h->N * sizeof(int32_t), cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    return YTK_OK;
+}
+
+// -------------------------------------------------------------------------------------
+// per-stage hooks
+// -------------------------------------------------------------------------------------
+int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n_rows, const int32_t* fea_index,
+                        int32_t n_fea, double* out) {
+    if (!h || !out) return fail(YTK_ERR_ARG, "build_hist: null argument");
+    if (!h->rows_set || !h->grads_set) return fail(YTK_ERR_ARG, "build_hist: set_bins/upload_rows/set_grads first");
+    if (gid < 0 || gid >= h->p.class_num) return fail(YTK_ERR_ARG, "build_hist: groupId %d", gid);
+    if (rows && (n_rows < 0 || n_rows > h->N)) return fail(YTK_ERR_ARG, "build_hist: n_rows %lld", (long long)n_rows);
+    CK(cudaSetDevice(h->device));
+    int first_owned;
+    RET(set_features(h, fea_index, n_fea, &first_owned));
+    CK(ytk::launch_grad_quantize(h->d_gp, h->N, h->p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->st));
+    int64_t n = rows ? n_rows : h->N;
+    if (rows && n > 0) {
+        for (int64_t i = 0; i < n; i++)
+            if (rows[i] < 0 || rows[i] >= h->N) return fail(YTK_ERR_ARG, "build_hist: row %d out of range", rows[i]);
+        CK(cudaMemcpyAsync(h->d_rowidx[0], rows, n * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+    }
+    const int64_t len = 2LL * h->B;
+    CK(cudaMemsetAsync(h->d_hist_flat, 0, len * sizeof(long long), h->st));
+    int launches = 0;
+    CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, rows ? h->d_rowidx[0] : nullptr, 0, n, h->F,
+                              h->d_group_mask, h->d_nbins, h->d_off_flat, h->d_hist_flat, 0, h->st, &launches));
+    if (h->world > 1)
+        NK(ytk::nccl_api().AllReduce(h->d_hist_flat, h->d_hist_flat, (size_t)len, ncclInt64, ncclSum, h->comm, h->st));
+    CK(ytk::launch_hist_to_double(h->d_hist_flat, len, h->d_scale, h->d_hist_dbl, h->st));
+    CK(cudaMemcpyAsync(out, h->d_hist_dbl, len * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    return YTK_OK;
+}
+
+static int hook_scale(ytk_gbdt* h, const double* a, const double* b, int64_t len) {
+    // power-of-two scales that keep every value below 2^52 so prefix sums of <= 2^10 bins stay exact
+    double mg = 0, mh = 0;
+    for (int64_t i = 0; i < len; i++) {
+        double v = std::fabs(a[i]);
+        if (b) v = std::max(v, std::fabs(b[i]));
+        if (!(v < std::numeric_limits<double>::infinity())) return fail(YTK_ERR_ARG, "histogram holds a non-finite value");
+        if (i & 1) mh = std::max(mh, v); else mg = std::max(mg, v);
+    }
+    auto k_of = [](double m) { int e = 0; if (m > 0) std::frexp(m, &e); return 52 - e; };
+    ytk::GradScale s;
+    int kg = k_of(mg), kh = k_of(mh);
+    s.mul_g = std::ldexp(1.0, kg); s.inv_g = std::ldexp(1.0, -kg);
+    s.mul_h = std::ldexp(1.0, kh); s.inv_h = std::ldexp(1.0, -kh);
+    CK(cudaMemcpyAsync(h->d_scale_hook, &s, sizeof(s), cudaMemcpyHostToDevice, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    return YTK_OK;
+}
+
+int ytk_gbdt_subtract_hist(ytk_gbdt* h, const double* parent, const double* small, double* out) {
+    if (!h || !parent || !small || !out) return fail(YTK_ERR_ARG, "subtract_hist: null argument");
+    if (!h->rows_set) return fail(YTK_ERR_ARG, "subtract_hist: set_bins first");
+    CK(cudaSetDevice(h->device));
+    const int64_t len = 2LL * h->B;
+    RET(hook_scale(h, parent, small, len));
+    CK(cudaMemcpyAsync(h->d_hist_dbl, parent, len * sizeof(double), cudaMemcpyHostToDevice, h->st));
+    CK(ytk::launch_hist_from_double(h->d_hist_dbl, len, h->d_scale_hook, h->d_hist_flat, h->st));
+    CK(cudaMemcpyAsync(h->d_hist_dbl, small, len * sizeof(double), cudaMemcpyHostToDevice, h->st));
+    CK(ytk::launch_hist_from_double(h->d_hist_dbl, len, h->d_scale_hook, h->d_hist_flat2, h->st));
+    CK(ytk::launch_hist_subtract(h->d_hist_flat, h->d_hist_flat2, h->d_hist_flat, len, h->st));
+    CK(ytk::launch_hist_to_double(h->d_hist_flat, len, h->d_scale_hook, h->d_hist_dbl, h->st));
+    CK(cudaMemcpyAsync(out, h->d_hist_dbl, len * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    return YTK_OK;
+}
+
+int ytk_gbdt_find_split(ytk_gbdt* h, const double* hist, int64_t sample_cnt, const int32_t* fea_index,
+                        int32_t n_fea, ytk_split* out) {
+    if (!h || !hist || !out) return fail(YTK_ERR_ARG, "find_split: null argument");
+    if (!h->rows_set) return fail(YTK_ERR_ARG, "find_split: set_bins first");
+    CK(cudaSetDevice(h->device));
+    int first_owned;
+    RET(set_features(h, fea_index, n_fea, &first_owned));
+    const int64_t len = 2LL * h->B;
+    RET(hook_scale(h, hist, nullptr, len));
+    CK(cudaMemcpyAsync(h->d_hist_dbl, hist, len * sizeof(double), cudaMemcpyHostToDevice, h->st));
+    CK(ytk::launch_hist_from_double(h->d_hist_dbl, len, h->d_scale_hook, h->d_hist_flat, h->st));
+    // single-worker view: all features scanned here, totals from the first selected one
+    int first = -1;
+    {
+        std::vector<uint8_t> sel(h->F, fea_index ? 0 : 1);
+        if (fea_index) for (int i = 0; i < n_fea; i++) sel[fea_index[i]] = 1;
+        for (int f = 0; f < h->F; f++) if (sel[f]) { first = f; break; }
+    }
+    CK(ytk::launch_split_scan(h->d_hist_flat, h->d_start, h->d_off_flat, h->d_fea_sel, 0, h->F, first,
+                              h->d_scale_hook, gain_params(h->p), sample_cnt, nullptr, h->d_split_local, h->st));
+    CK(cudaMemcpyAsync(h->mail->split, h->d_split_local, sizeof(ytk_split), cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    *out = h->mail->split[0];
+    return YTK_OK;
+}
+
+int ytk_gbdt_partition_rows(ytk_gbdt* h, const int32_t* rows, int64_t n_rows, int32_t fid, float cond,
+                            int32_t* out_rows, int64_t* left_cnt) {
+    if (!h || !left_cnt) return fail(YTK_ERR_ARG, "partition_rows: null argument");
+    if (!h->rows_set) return fail(YTK_ERR_ARG, "partition_rows: set_bins/upload_rows first");
+    if (n_rows < 0 || n_rows > h->N || (n_rows > 0 && (!rows || !out_rows)))
+        return fail(YTK_ERR_ARG, "partition_rows: bad row list");
+    if (fid < 0 || fid >= h->F) return fail(YTK_ERR_ARG, "partition_rows: fid %d", fid);
+    for (int64_t i = 0; i < n_rows; i++)
+        if (rows[i] < 0 || rows[i] >= h->N) return fail(YTK_ERR_ARG, "partition_rows: row %d out of range", rows[i]);
+    CK(cudaSetDevice(h->device));
+    if (n_rows > 0) CK(cudaMemcpyAsync(h->d_rowidx[0], rows, n_rows * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+    int launches = 0;
+    CK(ytk::launch_partition(h->d_bins, h->S8, h->d_rowidx[0], h->d_rowidx[1], 0, n_rows, fid, cond, h->d_scratch,
+                             h->d_counts, h->st, &launches));
+    CK(cudaMemcpyAsync(h->mail->counts, h->d_counts, sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost, h->st));
+    if (n_rows > 0) CK(cudaMemcpyAsync(out_rows, h->d_rowidx[1], n_rows * sizeof(int32_t), cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    *left_cnt = h->mail->counts[0].left;
+    return YTK_OK;
+}
+
+}  // extern "C"
+

@@ -1,0 +1,148 @@
+"""Host-side mirror of the reference's tree-maker interface over the C ABI.
+
+`GpuTreeMaker` plays the role of DataParallelTreeMaker
+(J/optimizer/gbdt/DataParallelTreeMaker.java:49-664) behind ITreeMaker
+(J/optimizer/gbdt/ITreeMaker.java:34-39): constructed from the optimisation params, the
+binned train matrix and the bin layout; `make(group_id)` returns the Tree; the gradient
+pairs are pushed before each round as GBDTOptimizer does
+(J/optimizer/GBDTOptimizer.java:482-488,550-552).  J/ = src/main/java/com/fenbi/ytklearn/.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import binding as B
+
+
+def make_params(max_depth=6, max_leaf_cnt=-1, min_split_samples=-1, grow_policy="level",
+                min_child_hessian_sum=1.0, min_split_loss=0.0, max_abs_leaf_val=-1.0,
+                l1=0.0, l2=1.0, histogram_pool_capacity=-1.0, learning_rate=0.1, class_num=1,
+                normalize=True):
+    """GBDTOptimizationParams fields the tree maker reads
+    (J/param/gbdt/GBDTOptimizationParams.java:100-205); `normalize` applies the
+    data-parallel max_leaf_cnt rule (:148-154)."""
+    if normalize:
+        max_leaf_cnt = B.normalize_max_leaf_cnt(max_depth, max_leaf_cnt)
+    if isinstance(grow_policy, str):
+        if grow_policy not in ("level", "loss"):
+            raise B.YtkError(-1, "[GBDT] tree_grow_policy (%s) invalid, loss or level" % grow_policy)
+        grow_policy = 1 if grow_policy == "loss" else 0
+    return B.Params(int(max_depth), int(max_leaf_cnt), int(min_split_samples), int(grow_policy),
+                    float(min_child_hessian_sum), float(min_split_loss), float(max_abs_leaf_val),
+                    float(l1), float(l2), float(histogram_pool_capacity), float(learning_rate),
+                    int(class_num))
+
+
+class GpuTreeMaker:
+    """One instance per GPU / row shard (the reference: one per worker thread)."""
+
+    def __init__(self, params, start, n_rows, device=0, rank=0, world=1, nccl_id=None):
+        self._h = C.c_void_p()
+        self.params = params
+        self.start = np.ascontiguousarray(start, dtype=np.int32)
+        self.F = len(self.start) - 1
+        self.B = int(self.start[-1])
+        self.N = int(n_rows)
+        self.K = params.class_num
+        self.last_stats = None
+        idp = None if nccl_id is None else B.ptr(np.ascontiguousarray(nccl_id, dtype=np.uint8))
+        self._nccl_id = nccl_id
+        B.check(B.lib().ytk_gbdt_create(C.addressof(params), int(device), int(rank), int(world), idp,
+                                        C.addressof(self._h)))
+        B.check(B.lib().ytk_gbdt_set_bins(self._h, B.ptr(self.start), self.F, self.N))
+
+    def close(self):
+        if self._h:
+            B.lib().ytk_gbdt_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- data in -------------------------------------------------------------------
+    def upload_rows(self, x, row0=0):
+        """x: int32 slots [n, stride] (a GBDTCoreData.x chunk after binning)."""
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        B.check(B.lib().ytk_gbdt_upload_rows(self._h, B.ptr(x), int(row0), x.shape[0], x.shape[1]))
+
+    def quantize_rows(self, values, cuts, row0=0):
+        """values: float32 [n, stride] raw feature values; cuts: sorted bin centres."""
+        bits = np.ascontiguousarray(values, dtype=np.float32).view(np.int32)
+        cuts = np.ascontiguousarray(cuts, dtype=np.float32)
+        B.check(B.lib().ytk_gbdt_quantize_rows(self._h, B.ptr(bits), int(row0), bits.shape[0],
+                                               bits.shape[1], B.ptr(cuts)))
+
+    def download_rows(self, row0=0, nrows=None):
+        nrows = self.N - row0 if nrows is None else nrows
+        out = np.zeros((nrows, self.F), dtype=np.int32)
+        B.check(B.lib().ytk_gbdt_download_rows(self._h, B.ptr(out), int(row0), int(nrows)))
+        return out
+
+    def set_grads(self, gp, row0=0):
+        """gp: float32 (g,h) pairs laid out [(row*K + gid)*2 + {0,1}]."""
+        gp = np.ascontiguousarray(gp, dtype=np.float32).reshape(-1)
+        n = gp.size // (2 * self.K)
+        B.check(B.lib().ytk_gbdt_set_grads(self._h, B.ptr(gp), int(row0), n))
+
+    def set_grads_ptr(self, host_ptr, row0, nrows):
+        """Same, from a raw host address (e.g. pinned memory)."""
+        B.check(B.lib().ytk_gbdt_set_grads(self._h, C.c_void_p(host_ptr), int(row0), int(nrows)))
+
+    # ---- ITreeMaker ------------------------------------------------------------------
+    def make(self, group_id=0, fea_index=None, row_mask=None):
+        cap = 2 * self.params.max_leaf_cnt - 1 if self.params.max_leaf_cnt > 0 \
+            else 2 ** (self.params.max_depth + 1) - 1
+        tree = B.Tree(cap)
+        tc = tree._as_c()
+        ts = B.TimeStats()
+        fi = None if fea_index is None else np.ascontiguousarray(fea_index, dtype=np.int32)
+        rm = None if row_mask is None else np.ascontiguousarray(row_mask, dtype=np.uint8)
+        if rm is not None and rm.size != self.N:
+            raise B.YtkError(-1, "row_mask must have one byte per local row")
+        B.check(B.lib().ytk_gbdt_make_tree(self._h, int(group_id), B.ptr(fi), 0 if fi is None else len(fi),
+                                           B.ptr(rm), C.addressof(tc), C.addressof(ts)))
+        self.last_stats = ts
+        return tree._trim(tc.n_nodes)
+
+    def get_total_time_stats(self):
+        return self.last_stats
+
+    def get_positions(self):
+        out = np.zeros(self.N, dtype=np.int32)
+        B.check(B.lib().ytk_gbdt_get_positions(self._h, B.ptr(out)))
+        return out
+
+    # ---- per-stage hooks ---------------------------------------------------------------
+    def build_hist(self, group_id=0, rows=None, fea_index=None):
+        out = np.zeros(2 * self.B, dtype=np.float64)
+        r = None if rows is None else np.ascontiguousarray(rows, dtype=np.int32)
+        fi = None if fea_index is None else np.ascontiguousarray(fea_index, dtype=np.int32)
+        B.check(B.lib().ytk_gbdt_build_hist(self._h, int(group_id), B.ptr(r), 0 if r is None else len(r),
+                                            B.ptr(fi), 0 if fi is None else len(fi), B.ptr(out)))
+        return out
+
+    def subtract_hist(self, parent, small):
+        parent = np.ascontiguousarray(parent, dtype=np.float64)
+        small = np.ascontiguousarray(small, dtype=np.float64)
+        out = np.zeros(2 * self.B, dtype=np.float64)
+        B.check(B.lib().ytk_gbdt_subtract_hist(self._h, B.ptr(parent), B.ptr(small), B.ptr(out)))
+        return out
+
+    def find_split(self, hist, sample_cnt, fea_index=None):
+        hist = np.ascontiguousarray(hist, dtype=np.float64)
+        fi = None if fea_index is None else np.ascontiguousarray(fea_index, dtype=np.int32)
+        out = B.Split()
+        B.check(B.lib().ytk_gbdt_find_split(self._h, B.ptr(hist), int(sample_cnt), B.ptr(fi),
+                                            0 if fi is None else len(fi), C.addressof(out)))
+        return out
+
+    def partition_rows(self, rows, fid, cond):
+        rows = np.ascontiguousarray(rows, dtype=np.int32)
+        out = np.zeros(len(rows), dtype=np.int32)
+        left = C.c_int64(0)
+        B.check(B.lib().ytk_gbdt_partition_rows(self._h, B.ptr(rows), len(rows), int(fid), C.c_float(cond),
+                                                B.ptr(out), C.addressof(left)))
+        return out, left.value
