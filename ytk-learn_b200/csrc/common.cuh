@@ -12,11 +12,11 @@ constexpr int kGroup = 32;        // features per group = lanes of a warp
 constexpr int kMaxBins = 256;     // uint8 slots
 constexpr int kHistThreads = 1024;
 constexpr int kHistWarps = kHistThreads / 32;
-// per-CTA shared histogram: [bin][component][lane] 32-bit words, components
+// per-CTA shared histogram: [bin][component][feature] 32-bit words, components
 // {g_lo, g_hi, h_lo, h_hi} of two 64-bit fixed-point accumulators
 constexpr int kHistSmemBytes = kMaxBins * 4 * kGroup * 4;                 // 128 KB
-constexpr int kStageBytes = kHistWarps * 32 * 16;                         // per-warp row staging
 constexpr int kNumSMs = 148;
+constexpr int kDefaultFixedBits = 24;
 
 // Gradient fixed-point scales of the current tree: value = integer * inv[.]
 struct GradScale {
@@ -33,6 +33,26 @@ struct GainParams {
 
 struct PartitionCounts { long long left, right; };
 
+// ---- work tables: one launch serves every node of a batch (a tree level, or one node) ----
+
+// a run of rows rowidx[buf][begin,end) (buf < 0: rows begin..end-1) whose sums go to segment `seg`
+struct RowItem { long long begin, end; int buf; int seg; };
+
+// one node being split: rows rowidx[buf][begin,end) move to rowidx[1-buf] (buf < 0 -> buffer 0)
+struct SplitSeg {
+    long long begin, end;
+    int buf;          // source buffer (-1 identity)
+    int fid;          // split feature; < 0: `src` is a byte mask over rows (row sampling)
+    float cond;       // go left iff (float)slot < cond
+    int tile0;        // first tile of this segment in the tile table
+    int ntiles;
+    int pad;
+};
+
+struct ScanNode { const long long* hist; long long sample_cnt; };
+struct SubItem { const long long* parent; const long long* small; long long* out; };
+struct PosItem { long long begin, end; int buf; int nid; };
+
 // ---- launchers (kernels.cu); all asynchronous on `st`, return cudaGetLastError() ----
 
 cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, int32_t F,
@@ -43,47 +63,47 @@ cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t st
 cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, int32_t F, int32_t* out,
                                cudaStream_t st);
 
-// (g,h) float pairs of class gid -> fixed-point int2 + scales
+// (g,h) float pairs of class gid -> fixed-point int2 (|value| < 2^bits) + scales
 cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t gid, int2* gq,
-                                 unsigned* absmax_bits /*2, scratch*/, GradScale* scale, cudaStream_t st);
+                                 unsigned* absmax_bits /*2, scratch*/, GradScale* scale, int bits,
+                                 cudaStream_t st);
 
-// K2: histogram of the rows rowidx[begin,end) (rowidx == nullptr: rows begin..end-1) into
-// hist (int64, pre-zeroed), feature f's bins at hist[feat_off[f] + 2*bin + {0,1}].
-cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx,
-                              int64_t begin, int64_t end, int32_t F, const uint32_t* group_mask,
-                              const int32_t* nbins, const int64_t* feat_off, long long* hist,
-                              int variant, cudaStream_t st, int* launches);
+// K2: histograms of n_items row runs; item -> segment -> seg_out[seg] (int64, pre-zeroed); feature f's
+// bins at seg_out[seg] + feat_owner[f]*owner_stride + feat_inner[f] + 2*bin + {0,1}.
+cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx0,
+                              const int32_t* rowidx1, const RowItem* items, int n_items, int32_t F,
+                              const uint32_t* group_mask, const int32_t* nbins, const int32_t* feat_owner,
+                              const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
+                              cudaStream_t st);
+// rows one hist work item should cover so that `total_rows` split into about two waves of CTAs
+int64_t hist_rows_per_item(int64_t total_rows, int groups);
 
-cudaError_t launch_hist_subtract(const long long* parent, const long long* small, long long* out,
-                                 int64_t len, cudaStream_t st);
+cudaError_t launch_hist_subtract(const SubItem* items, int n_items, int64_t len, cudaStream_t st);
 cudaError_t launch_hist_to_double(const long long* hist, int64_t len, const GradScale* scale, double* out,
                                   cudaStream_t st);
 cudaError_t launch_hist_from_double(const double* in, int64_t len, const GradScale* scale, long long* hist,
                                     cudaStream_t st);
 
-// K4/K5: node totals + split scan + arg-max over the features [f_from, f_to) this rank owns.
-cudaError_t launch_split_scan(const long long* hist, const int32_t* start, const int64_t* feat_off,
-                              const uint8_t* fea_selected, int32_t f_from, int32_t f_to,
-                              int32_t first_fea, const GradScale* scale, GainParams gp,
-                              long long sample_cnt, const double* totals_in /*nullable: G,H*/,
-                              ytk_split* out, cudaStream_t st);
+// K4/K5: node totals + split scan + arg-max over the features [f_from, f_to) this rank owns, one CTA per node.
+cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t* start, const int64_t* feat_off,
+                              const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
+                              const GradScale* scale, GainParams gp, ytk_split* out, cudaStream_t st);
 
-// K6: stable partition of rowidx_in[begin,end) by (float)bin(row,fid) < cond into rowidx_out
-cudaError_t launch_partition(const uint8_t* bins, int32_t S8, const int32_t* rowidx_in,
-                             int32_t* rowidx_out, int64_t begin, int64_t end, int32_t fid, float cond,
-                             int32_t* block_cnt /*scratch*/, PartitionCounts* counts, cudaStream_t st,
-                             int* launches);
-int64_t partition_scratch_ints(int64_t n);
+// K6: stable partition of every segment by (float)bin(row,fid) < cond (or by a byte mask)
+constexpr int kPartThreads = 256;
+constexpr int kPartItems = 8;
+constexpr int kPartTile = kPartThreads * kPartItems;
+cudaError_t launch_partition(const uint8_t* src, int32_t S8, int32_t* rowidx0, int32_t* rowidx1,
+                             const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
+                             uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st);
 
-// K7: exact fixed-point sums of (g,h) over rowidx[begin,end) -> out[2] (pre-zeroed)
-cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx, int64_t begin, int64_t end,
-                             long long* out, cudaStream_t st);
+// K7: exact fixed-point sums of (g,h) over row runs -> out[2*seg + {0,1}] (pre-zeroed)
+cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1, const RowItem* items,
+                             int n_items, long long* out, cudaStream_t st);
 
-cudaError_t launch_iota(int32_t* p, int64_t n, cudaStream_t st);
-cudaError_t launch_compact_mask(const uint8_t* mask, int64_t n, int32_t* rowidx_out, int32_t* block_cnt,
-                                PartitionCounts* counts, cudaStream_t st, int* launches);
-cudaError_t launch_fill_positions(const int32_t* rowidx, int64_t begin, int64_t end, int32_t nid,
+cudaError_t launch_fill_positions(const int32_t* rowidx0, const int32_t* rowidx1, const PosItem* items, int n_items,
                                   int32_t* node_of_row, cudaStream_t st);
 cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st);
+cudaError_t launch_copy_segments(const long long* src, long long* const* dst, int n, int64_t len, cudaStream_t st);
 
 }  // namespace ytk

@@ -9,6 +9,9 @@
 
 #include <math_constants.h>
 
+#include <algorithm>
+#include <cstdlib>
+
 namespace ytk {
 
 // ------------------------------------------------------------------------------------
@@ -88,10 +91,12 @@ __global__ void unpack_rows_k(const uint8_t* __restrict__ bins, int32_t S8, int6
 // ------------------------------------------------------------------------------------
 // Gradient fixed point.  The reference adds float (g,h) into double bins
 // (J/data/gbdt/HistogramBuilder.java:87-88).  Shared memory only has native 32-bit
-// integer atomics, so each tree's gradients are scaled by a power of two chosen from
-// max|g| (resp. max|h|) to 31-bit integers and every sum downstream is an exact 64-bit
-// integer: histograms do not depend on row order, sharding or pool hits, and
-// parent - child equals the sibling bit for bit.  Per-row rounding <= 2^-31 of max|g|.
+// integer atomics (a float or 64-bit atomicAdd is a CAS loop, measured 2.9x slower:
+// profiles/r01_microbench_smem.txt), so each tree's gradients are scaled by a power of
+// two chosen from max|g| (resp. max|h|) to signed integers below 2^bits and every sum
+// downstream is an exact 64-bit integer: histograms do not depend on row order, sharding
+// or pool hits, and parent - child equals the sibling bit for bit.  Per-row rounding is
+// at most 2^-(bits+1) of max|g| (bits = 24: the float grid of the largest gradient).
 // A non-zero value never rounds to zero, so "bin has samples" (hasSample,
 // J/optimizer/gbdt/DataParallelTreeMaker.java:657-663) is preserved exactly.
 // ------------------------------------------------------------------------------------
@@ -114,11 +119,11 @@ __global__ void grad_absmax_k(const float* __restrict__ gp, int64_t n, int32_t K
     }
 }
 
-__device__ __forceinline__ int scale_exponent(float mx) {
+__device__ __forceinline__ int scale_exponent(float mx, int bits) {
     if (!(mx > 0.f)) return 0;
     int e;
-    frexpf(mx, &e);          // mx = m * 2^e, m in [0.5,1)  =>  mx * 2^(30-e) < 2^30
-    return 30 - e;
+    frexpf(mx, &e);          // mx = m * 2^e, m in [0.5,1)  =>  mx * 2^(bits-e) < 2^bits
+    return bits - e;
 }
 
 __device__ __forceinline__ int32_t to_fixed(float v, double mul) {
@@ -129,9 +134,9 @@ __device__ __forceinline__ int32_t to_fixed(float v, double mul) {
 
 __global__ void grad_quantize_k(const float* __restrict__ gp, int64_t n, int32_t K, int32_t gid,
                                 int2* __restrict__ gq, const unsigned* __restrict__ absmax_bits,
-                                GradScale* __restrict__ scale) {
-    int kg = scale_exponent(__uint_as_float(absmax_bits[0]));
-    int kh = scale_exponent(__uint_as_float(absmax_bits[1]));
+                                GradScale* __restrict__ scale, int bits) {
+    int kg = scale_exponent(__uint_as_float(absmax_bits[0]), bits);
+    int kh = scale_exponent(__uint_as_float(absmax_bits[1]), bits);
     double mg = ldexp(1.0, kg), mh = ldexp(1.0, kh);
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         scale->mul_g = mg; scale->mul_h = mh;
@@ -148,32 +153,44 @@ __global__ void grad_quantize_k(const float* __restrict__ gp, int64_t n, int32_t
 // K2: per-node (g,h) histogram -- HistogramBuilder.buildHist's accumulation loop
 //     (J/data/gbdt/HistogramBuilder.java:69-90).
 //
-// One CTA = 32 warps sharing one 128 KB shared histogram of a 32-feature group.  Lane l
-// of every warp owns feature 32*group + l, and the histogram is laid out
-// [bin][component][lane], so the 32 atomics of one warp instruction always hit 32
-// different banks whatever the bins are: no bank conflicts by construction.  A warp
-// walks its rows one at a time: the row's 32 bin bytes are one coalesced 32 B sector
-// (uint8 row-major rows, 32 B per group), its fixed-point (g,h) is broadcast from a
-// per-warp staging slot.  Each update is a native 32-bit ATOMS.ADD on the low word whose
-// returned value yields the carry into the high word (a second, rare atomic).
+// What bounds this kernel on B200 is not HBM but the shared-memory pipe: every
+// LSU-class instruction (ATOMS, LDS, SHFL, LDG) costs ~1.9 SM-cycles per warp instruction
+// (profiles/r01_microbench_smem.txt), and a (g,h) update needs two atomics.  So the
+// kernel is built to issue nothing else per row:
+//   * rows are uint8, row-major, one 32 B sector per 32-feature group, so a row reached
+//     through the row-id list costs exactly one sector; lane r of a warp loads ITS row
+//     with two 128-bit loads and its own fixed-point (g,h) with one 64-bit load -- no
+//     per-row broadcast, no staging;
+//   * at step k (0..31) lane r updates feature k^r of its row.  The 32 lanes therefore
+//     always touch 32 different features, and the shared histogram is laid out
+//     [bin][component][feature], i.e. bank = feature: the 32 atomics of a warp
+//     instruction hit 32 different banks whatever the bins are (skewed or binary
+//     features cannot serialise it);
+//   * the 8 data words of a lane are pre-permuted by (lane>>2) so that the word needed
+//     at step k has a compile-time register index; only the byte selector depends on
+//     the lane;
+//   * accumulators are 64-bit (lo,hi words).  The low word takes a native returning
+//     ATOMS.ADD; its result tells whether a carry/borrow must go to the high word.  With
+//     24-bit fixed point that happens for about 1 lane in 500, so the high-word atomic
+//     sits behind a warp-uniform vote and is almost never issued.
+// One CTA (32 warps, 128 KB of shared memory, 1 per SM) handles one work item: a run of
+// rows of one node and one feature group; it flushes non-empty bins with 64-bit global
+// reductions into that node's histogram.
 // ------------------------------------------------------------------------------------
-__device__ __forceinline__ void smem_add64(uint32_t* p, int32_t v) {
-    uint32_t old = atomicAdd(p, (uint32_t)v);
-    uint32_t sum = old + (uint32_t)v;
-    int32_t hi = (v >> 31) + (sum < old ? 1 : 0);
-    if (hi != 0) atomicAdd(reinterpret_cast<int32_t*>(p + kGroup), hi);
-}
-
 __global__ void __launch_bounds__(kHistThreads, 1)
 hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict__ gq,
-             const int32_t* __restrict__ rowidx, int64_t begin, int64_t end, int32_t F,
-             const uint32_t* __restrict__ group_mask, const int32_t* __restrict__ nbins,
-             const int64_t* __restrict__ feat_off, long long* __restrict__ hist, int64_t rows_per_cta) {
-    extern __shared__ __align__(16) uint32_t sm[];
-    uint32_t* sh = sm;
+             const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1,
+             const RowItem* __restrict__ items, int32_t F, const uint32_t* __restrict__ group_mask,
+             const int32_t* __restrict__ nbins, const int32_t* __restrict__ feat_owner,
+             const int64_t* __restrict__ feat_inner, long long owner_stride,
+             long long* const* __restrict__ seg_out) {
+    // low words [bin][{g,h}][feature] (64 KB), then the high words in the same layout (64 KB)
+    extern __shared__ __align__(128) uint32_t sh[];
+    constexpr uint32_t kHiOff = kMaxBins * 2 * kGroup * 4;       // bytes
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    int4* stage = reinterpret_cast<int4*>(sm + kMaxBins * 4 * kGroup) + warp * 32;
     const int fg = blockIdx.y;
+    const RowItem it = items[blockIdx.x];
+    const int32_t* __restrict__ ridx = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
 
     {
         uint4* z = reinterpret_cast<uint4*>(sh);
@@ -181,56 +198,112 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
     }
     __syncthreads();
 
-    const int f = fg * kGroup + lane;
-    const bool active = (f < F) && ((group_mask[fg] >> lane) & 1u);
-    const uint8_t* col = bins + fg * kGroup + lane;
-    const int64_t r0 = begin + blockIdx.x * rows_per_cta;
-    const int64_t r1 = min(end, r0 + rows_per_cta);
+    const uint32_t gmask = group_mask[fg];
+    const int m = lane >> 2, bsel = lane & 3;
+    // PRMT selectors: byte (kk ^ bsel) of a data word moved to byte 1, i.e. bin * 256 = the byte
+    // offset of that bin's 256 B row of low words
+    uint32_t selk[4];
+#pragma unroll
+    for (int kk = 0; kk < 4; kk++) selk[kk] = 0x4404u | ((uint32_t)(kk ^ bsel) << 4);
+    uint32_t lane4 = (uint32_t)lane << 2;
+    asm volatile("" : "+r"(lane4));          // keep it a plain register: (bin256 | lane4) ^ k4 is one LOP3
+    const uint8_t* __restrict__ gbase = bins + fg * kGroup + (m << 2);
+    char* const shb = reinterpret_cast<char*>(sh);
 
-    for (int64_t c = r0 + warp * 32; c < r1; c += kHistWarps * 32) {
-        int64_t i = c + lane;
-        int32_t rid = 0;
-        int2 q = make_int2(0, 0);
-        if (i < r1) {
-            rid = rowidx ? rowidx[i] : (int32_t)i;
+    // Lane r loads the 8 data words of ITS row already permuted: register j holds word j ^ m, the
+    // one holding the features this lane visits at steps 4j..4j+3.  The 8 loads of a lane fall in
+    // one 32 B sector (first one misses, the rest hit L1).
+    auto load = [&](long long base, uint32_t (&w)[8], int2& q) {
+        long long i = base + lane;
+        if (i < it.end) {
+            int32_t rid = ridx ? ridx[i] : (int32_t)i;
             q = gq[rid];
-        }
-        __syncwarp();
-        stage[lane] = make_int4(rid, q.x, q.y, 0);
-        __syncwarp();
-        const int cnt = (int)min((int64_t)32, r1 - c);
-        for (int j0 = 0; j0 < cnt; j0 += 8) {
-            int4 s[8];
-            uint32_t b[8];
+            const unsigned long long a = (unsigned long long)(gbase + (long long)rid * S8);
 #pragma unroll
-            for (int u = 0; u < 8; u++) {
-                if (j0 + u < cnt) {
-                    s[u] = stage[j0 + u];
-                    b[u] = col[(int64_t)s[u].x * S8];
+            for (int j = 0; j < 8; j++) w[j] = *reinterpret_cast<const uint32_t*>(a ^ (unsigned long long)(j << 2));
+        } else {
+            // past the end of the run: adds zero to bin 0, which changes nothing
+            q = make_int2(0, 0);
+#pragma unroll
+            for (int j = 0; j < 8; j++) w[j] = 0;
+        }
+    };
+
+    // One 32-row block of this warp: 32 steps, at step k lane r updates feature k ^ r of its row.
+    auto accumulate = [&](const uint32_t (&w)[8], const int2 q) {
+        const uint32_t g = (uint32_t)q.x, h = (uint32_t)q.y;
+        const unsigned long long g64 = (unsigned long long)(long long)q.x;
+        const unsigned long long h64 = (unsigned long long)(long long)q.y;
+        // Unsampled features and padding lanes are accumulated too (the instruction is issued
+        // for the whole warp anyway) and dropped at flush time.
+        // The atomics of feature quad j are issued before the carries of quad j-1 are looked at, so
+        // a warp always has 8 shared-memory atomics in flight while it does the bookkeeping.
+        uint32_t off_p[4] = {0, 0, 0, 0}, og_p[4] = {0, 0, 0, 0}, oh_p[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int j = 0; j <= 8; j++) {
+            uint32_t off_c[4] = {0, 0, 0, 0}, og_c[4] = {0, 0, 0, 0}, oh_c[4] = {0, 0, 0, 0};
+            if (j < 8) {
+                const uint32_t word = w[j < 8 ? j : 0];
+#pragma unroll
+                for (int kk = 0; kk < 4; kk++) {
+                    off_c[kk] = (__byte_perm(word, 0u, selk[kk]) | lane4) ^ (uint32_t)((4 * j + kk) << 2);
+                    uint32_t* p = reinterpret_cast<uint32_t*>(shb + off_c[kk]);
+                    og_c[kk] = atomicAdd(p, g);
+                    oh_c[kk] = atomicAdd(p + kGroup, h);
+                }
+            }
+            if (j > 0) {
+                int32_t hg[4], hh[4];
+#pragma unroll
+                for (int kk = 0; kk < 4; kk++) {
+                    // high word of (old low word + signed addend): carry or borrow owed to the high word
+                    hg[kk] = (int32_t)(((unsigned long long)og_p[kk] + g64) >> 32);
+                    hh[kk] = (int32_t)(((unsigned long long)oh_p[kk] + h64) >> 32);
+                }
+                if (((hg[0] | hg[1] | hg[2]) | (hg[3] | hh[0] | hh[1]) | (hh[2] | hh[3])) != 0) {
+                    // a low word wrapped for this lane (about 1 update in 700 with 24-bit fixed point)
+#pragma unroll
+                    for (int kk = 0; kk < 4; kk++) {
+                        if ((hg[kk] | hh[kk]) != 0) {
+                            int32_t* p = reinterpret_cast<int32_t*>(shb + kHiOff + off_p[kk]);
+                            if (hg[kk] != 0) atomicAdd(p, hg[kk]);
+                            if (hh[kk] != 0) atomicAdd(p + kGroup, hh[kk]);
+                        }
+                    }
                 }
             }
 #pragma unroll
-            for (int u = 0; u < 8; u++) {
-                if (j0 + u < cnt && active) {
-                    uint32_t* p = sh + (b[u] * 4) * kGroup + lane;
-                    smem_add64(p, s[u].y);
-                    smem_add64(p + 2 * kGroup, s[u].z);
-                }
-            }
+            for (int kk = 0; kk < 4; kk++) { off_p[kk] = off_c[kk]; og_p[kk] = og_c[kk]; oh_p[kk] = oh_c[kk]; }
         }
+    };
+
+    // software pipeline over this warp's 32-row blocks, two register sets in ping-pong
+    long long base = it.begin + warp * 32;
+    uint32_t wa[8], wb[8];
+    int2 qa, qb;
+    load(base, wa, qa);
+    while (base < it.end) {
+        load(base + kHistThreads, wb, qb);
+        accumulate(wa, qa);
+        base += kHistThreads;
+        if (base >= it.end) break;
+        load(base + kHistThreads, wa, qa);
+        accumulate(wb, qb);
+        base += kHistThreads;
     }
     __syncthreads();
 
     // flush: one 64-bit global reduction per non-empty (feature, bin, component)
-    const uint32_t mask = group_mask[fg];
+    long long* __restrict__ out = seg_out[it.seg];
     for (int i = tid; i < kMaxBins * kGroup; i += kHistThreads) {
         int bin = i >> 5, ln = i & 31;
         int ff = fg * kGroup + ln;
-        if (ff >= F || !((mask >> ln) & 1u) || bin >= nbins[ff]) continue;
-        const uint32_t* p = sh + (bin * 4) * kGroup + ln;
-        long long g = (long long)(((unsigned long long)p[kGroup] << 32) | p[0]);
-        long long h = (long long)(((unsigned long long)p[3 * kGroup] << 32) | p[2 * kGroup]);
-        long long* dst = hist + feat_off[ff] + 2 * bin;
+        if (ff >= F || !((gmask >> ln) & 1u) || bin >= nbins[ff]) continue;
+        const uint32_t* lo = sh + bin * (2 * kGroup) + ln;
+        const uint32_t* hi = lo + kHiOff / 4;
+        long long g = (long long)(((unsigned long long)hi[0] << 32) | lo[0]);
+        long long h = (long long)(((unsigned long long)hi[kGroup] << 32) | lo[kGroup]);
+        long long* dst = out + feat_owner[ff] * owner_stride + feat_inner[ff] + 2 * bin;
         if (g != 0) atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)g);
         if (h != 0) atomicAdd(reinterpret_cast<unsigned long long*>(dst + 1), (unsigned long long)h);
     }
@@ -238,11 +311,11 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
 
 // K3: sibling = parent - smaller child (HistogramBuilder.substract,
 //     J/data/gbdt/HistogramBuilder.java:101-107), exact in the integer domain.
-__global__ void hist_subtract_k(const long long* __restrict__ parent, const long long* __restrict__ small,
-                                long long* __restrict__ out, int64_t len) {
+__global__ void hist_subtract_k(const SubItem* __restrict__ items, int64_t len) {
+    const SubItem it = items[blockIdx.y];
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
          i += (int64_t)gridDim.x * blockDim.x)
-        out[i] = parent[i] - small[i];
+        it.out[i] = it.parent[i] - it.small[i];
 }
 
 __global__ void hist_to_double_k(const long long* __restrict__ hist, int64_t len,
@@ -261,15 +334,23 @@ __global__ void hist_from_double_k(const double* __restrict__ in, int64_t len,
         hist[i] = __double2ll_rn(in[i] * ((i & 1) ? mh : mg));
 }
 
+__global__ void copy_segments_k(const long long* __restrict__ src, long long* const* __restrict__ dst, int64_t len) {
+    const long long* s = src + blockIdx.y * len;
+    long long* d = dst[blockIdx.y];
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
+         i += (int64_t)gridDim.x * blockDim.x)
+        d[i] = s[i];
+}
+
 // ------------------------------------------------------------------------------------
 // K4/K5: node totals, split scan and arg-max.
 //   updateTreeMakerNodeStats (J/optimizer/gbdt/DataParallelTreeMaker.java:543-573),
 //   enumerateSplit (:598-637), SplitInfo.needReplace (J/data/gbdt/SplitInfo.java:99-104),
 //   UpdateStrategy.calcGain / calcNodeValue (J/optimizer/gbdt/UpdateStrategy.java:55-100).
-// One warp per feature: a segmented inclusive scan over the feature's bins in exact
-// 64-bit integers (so the prefix does not depend on scan order), gains in IEEE double
-// with explicit _rn intrinsics (never fused), loss change rounded to float as the
-// reference does.
+// One CTA per node, one warp per feature: a segmented inclusive scan over the feature's
+// bins in exact 64-bit integers (so the prefix does not depend on scan order), gains in
+// IEEE double with explicit _rn intrinsics (never fused), loss change rounded to float
+// as the reference does.
 // ------------------------------------------------------------------------------------
 __device__ __forceinline__ double threshold_l1(double w, double lambda) {
     if (w > lambda) return __dsub_rn(w, lambda);
@@ -306,22 +387,22 @@ __device__ __forceinline__ double calc_gain(const GainParams& p, double G, doubl
 constexpr int kScanWarps = 8;
 
 __global__ void __launch_bounds__(kScanWarps * 32)
-split_scan_k(const long long* __restrict__ hist, const int32_t* __restrict__ start,
+split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ start,
              const int64_t* __restrict__ feat_off, const uint8_t* __restrict__ fea_selected,
              int32_t f_from, int32_t f_to, int32_t first_fea, const GradScale* __restrict__ scale,
-             GainParams gp, long long sample_cnt, const double* __restrict__ totals_in,
-             ytk_split* __restrict__ out) {
+             GainParams gp, ytk_split* __restrict__ outs) {
     __shared__ double s_tot[2];
     __shared__ float s_lc[kScanWarps];
     __shared__ int s_fid[kScanWarps], s_lo[kScanWarps], s_hi[kScanWarps];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const double ig = scale->inv_g, ih = scale->inv_h;
+    const long long* __restrict__ hist = nodes[blockIdx.x].hist;
+    const long long sample_cnt = nodes[blockIdx.x].sample_cnt;
+    ytk_split* out = outs + blockIdx.x;
 
     if (warp == 0) {
         double G, H;
-        if (totals_in) {
-            G = totals_in[0]; H = totals_in[1];
-        } else if (first_fea >= 0) {
+        if (first_fea >= 0) {
             long long g = 0, h = 0;
             const long long* hp = hist + feat_off[first_fea];
             int nb = start[first_fea + 1] - start[first_fea];
@@ -416,30 +497,32 @@ split_scan_k(const long long* __restrict__ hist, const int32_t* __restrict__ sta
 // K6: row partition.  SamplePositionData.resetPosition
 //     (J/data/gbdt/SamplePositionData.java:115-133): row goes left iff
 //     (float)slot(row, fid) < cond.  The reference then swaps in place (unstable); only
-//     the left/right sets are contractual, so this is a stable out-of-place scatter:
-//     flags + per-block counts, a scan of the block counts, then the scatter.
+//     the left/right sets are contractual, so this is a stable out-of-place scatter over
+//     every node of the batch at once: flags + per-tile counts, a per-node scan of the
+//     tile counts, then the scatter into the other row-id buffer.
 // ------------------------------------------------------------------------------------
-constexpr int kPartThreads = 256;
-constexpr int kPartItems = 8;
-constexpr int kPartTile = kPartThreads * kPartItems;
+__device__ __forceinline__ const int32_t* seg_src(const SplitSeg& s, const int32_t* r0, const int32_t* r1) {
+    return s.buf < 0 ? nullptr : (s.buf == 0 ? r0 : r1);
+}
 
-template <int MODE>  // 0: bin compare, 1: byte mask (row sampling)
 __global__ void __launch_bounds__(kPartThreads)
-partition_count_k(const uint8_t* __restrict__ src, int32_t S8, const int32_t* __restrict__ rowidx,
-                  int64_t begin, int64_t end, int32_t fid, float cond, uint8_t* __restrict__ flags,
-                  int32_t* __restrict__ block_cnt) {
+partition_count_k(const uint8_t* __restrict__ src, int32_t S8, const int32_t* __restrict__ rowidx0,
+                  const int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs,
+                  const int* __restrict__ tile_seg, uint8_t* __restrict__ flags, int32_t* __restrict__ block_cnt) {
     __shared__ int s_cnt[kPartThreads / 32];
-    int64_t base = begin + (int64_t)blockIdx.x * kPartTile;
+    const SplitSeg sg = segs[tile_seg[blockIdx.x]];
+    const int32_t* __restrict__ rowidx = seg_src(sg, rowidx0, rowidx1);
+    const long long base = sg.begin + (long long)(blockIdx.x - sg.tile0) * kPartTile;
     int cnt = 0;
 #pragma unroll
     for (int k = 0; k < kPartItems; k++) {
-        int64_t i = base + k * kPartThreads + threadIdx.x;
-        if (i < end) {
+        long long i = base + k * kPartThreads + threadIdx.x;
+        if (i < sg.end) {
             int32_t rid = rowidx ? rowidx[i] : (int32_t)i;
             bool left;
-            if (MODE == 0) left = (float)src[(int64_t)rid * S8 + fid] < cond;
+            if (sg.fid >= 0) left = (float)src[(long long)rid * S8 + sg.fid] < sg.cond;
             else left = src[rid] != 0;
-            flags[i - begin] = left ? 1 : 0;
+            flags[i] = left ? 1 : 0;
             cnt += left ? 1 : 0;
         }
     }
@@ -453,16 +536,20 @@ partition_count_k(const uint8_t* __restrict__ src, int32_t S8, const int32_t* __
     }
 }
 
+// one CTA per segment: exclusive scan of its tiles' counts, total -> counts[seg]
 __global__ void __launch_bounds__(1024)
-partition_scan_k(int32_t* __restrict__ block_cnt, int32_t nblocks, int64_t n, PartitionCounts* counts) {
+partition_scan_k(const SplitSeg* __restrict__ segs, int32_t* __restrict__ block_cnt, PartitionCounts* counts) {
     __shared__ long long s_warp[32];
     __shared__ long long s_carry;
+    const SplitSeg sg = segs[blockIdx.x];
+    int32_t* bc = block_cnt + sg.tile0;
+    const int nblocks = sg.ntiles;
     if (threadIdx.x == 0) s_carry = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int c0 = 0; c0 < nblocks; c0 += 1024) {
         int i = c0 + threadIdx.x;
-        long long v = (i < nblocks) ? block_cnt[i] : 0;
+        long long v = (i < nblocks) ? bc[i] : 0;
         long long p = v;
         for (int d = 1; d < 32; d <<= 1) {
             long long t = __shfl_up_sync(0xffffffffu, p, d);
@@ -481,32 +568,40 @@ partition_scan_k(int32_t* __restrict__ block_cnt, int32_t nblocks, int64_t n, Pa
         }
         __syncthreads();
         long long excl = s_carry + s_warp[warp] + p - v;
-        if (i < nblocks) block_cnt[i] = (int32_t)excl;
+        if (i < nblocks) bc[i] = (int32_t)excl;
         __syncthreads();
         if (threadIdx.x == 1023) s_carry = excl + v;
         __syncthreads();
     }
-    if (threadIdx.x == 0) { counts->left = s_carry; counts->right = n - s_carry; }
+    if (threadIdx.x == 0) {
+        counts[blockIdx.x].left = s_carry;
+        counts[blockIdx.x].right = (sg.end - sg.begin) - s_carry;
+    }
 }
 
 __global__ void __launch_bounds__(kPartThreads)
-partition_scatter_k(const int32_t* __restrict__ rowidx, int32_t* __restrict__ out, int64_t begin, int64_t end,
+partition_scatter_k(int32_t* __restrict__ rowidx0, int32_t* __restrict__ rowidx1,
+                    const SplitSeg* __restrict__ segs, const int* __restrict__ tile_seg,
                     const uint8_t* __restrict__ flags, const int32_t* __restrict__ block_off,
                     const PartitionCounts* __restrict__ counts) {
     __shared__ int s_warp[kPartThreads / 32];
+    const int seg = tile_seg[blockIdx.x];
+    const SplitSeg sg = segs[seg];
+    const int32_t* __restrict__ rowidx = seg_src(sg, rowidx0, rowidx1);
+    int32_t* __restrict__ out = (sg.buf == 0) ? rowidx1 : rowidx0;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // thread t owns items [t*8, t*8+8) of the tile so that order is preserved
-    int64_t base = begin + (int64_t)blockIdx.x * kPartTile + threadIdx.x * kPartItems;
+    const long long base = sg.begin + (long long)(blockIdx.x - sg.tile0) * kPartTile + threadIdx.x * kPartItems;
     int32_t rid[kPartItems];
     bool fl[kPartItems];
     int cnt = 0;
 #pragma unroll
     for (int k = 0; k < kPartItems; k++) {
-        int64_t i = base + k;
+        long long i = base + k;
         fl[k] = false;
-        if (i < end) {
+        if (i < sg.end) {
             rid[k] = rowidx ? rowidx[i] : (int32_t)i;
-            fl[k] = flags[i - begin] != 0;
+            fl[k] = flags[i] != 0;
             cnt += fl[k] ? 1 : 0;
         }
     }
@@ -519,14 +614,14 @@ partition_scatter_k(const int32_t* __restrict__ rowidx, int32_t* __restrict__ ou
     __syncthreads();
     int woff = 0;
     for (int w = 0; w < warp; w++) woff += s_warp[w];
-    int64_t lefts_before = (int64_t)block_off[blockIdx.x] + woff + p - cnt;  // lefts before my first item
-    const int64_t left_total = counts->left;
-    int64_t lpos = begin + lefts_before;
-    int64_t rpos = begin + left_total + ((base - begin) - lefts_before);
+    long long lefts_before = (long long)block_off[blockIdx.x] + woff + p - cnt;  // lefts before my first item
+    const long long left_total = counts[seg].left;
+    long long lpos = sg.begin + lefts_before;
+    long long rpos = sg.begin + left_total + ((base - sg.begin) - lefts_before);
 #pragma unroll
     for (int k = 0; k < kPartItems; k++) {
-        int64_t i = base + k;
-        if (i < end) {
+        long long i = base + k;
+        if (i < sg.end) {
             if (fl[k]) out[lpos++] = rid[k];
             else out[rpos++] = rid[k];
         }
@@ -535,11 +630,13 @@ partition_scatter_k(const int32_t* __restrict__ rowidx, int32_t* __restrict__ ou
 
 // K7: exact sums of the fixed-point (g,h) over a node's rows -- computeLeafStats
 //     (J/optimizer/gbdt/DataParallelTreeMaker.java:352-372).
-__global__ void leaf_sums_k(const int2* __restrict__ gq, const int32_t* __restrict__ rowidx, int64_t begin,
-                            int64_t end, long long* __restrict__ out) {
+__global__ void leaf_sums_k(const int2* __restrict__ gq, const int32_t* __restrict__ rowidx0,
+                            const int32_t* __restrict__ rowidx1, const RowItem* __restrict__ items,
+                            long long* __restrict__ out) {
+    const RowItem it = items[blockIdx.x];
+    const int32_t* __restrict__ rowidx = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
     long long g = 0, h = 0;
-    for (int64_t i = begin + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < end;
-         i += (int64_t)gridDim.x * blockDim.x) {
+    for (long long i = it.begin + threadIdx.x; i < it.end; i += blockDim.x) {
         int2 q = gq[rowidx ? rowidx[i] : (int32_t)i];
         g += q.x; h += q.y;
     }
@@ -548,24 +645,22 @@ __global__ void leaf_sums_k(const int2* __restrict__ gq, const int32_t* __restri
         h += __shfl_xor_sync(0xffffffffu, h, d);
     }
     if ((threadIdx.x & 31) == 0) {
-        if (g) atomicAdd(reinterpret_cast<unsigned long long*>(out), (unsigned long long)g);
-        if (h) atomicAdd(reinterpret_cast<unsigned long long*>(out + 1), (unsigned long long)h);
+        if (g) atomicAdd(reinterpret_cast<unsigned long long*>(out + 2 * it.seg), (unsigned long long)g);
+        if (h) atomicAdd(reinterpret_cast<unsigned long long*>(out + 2 * it.seg + 1), (unsigned long long)h);
     }
 }
 
-__global__ void iota_k(int32_t* p, int64_t n) {
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-        p[i] = (int32_t)i;
-}
 __global__ void fill_i32_k(int32_t* p, int64_t n, int32_t v) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         p[i] = v;
 }
-__global__ void fill_positions_k(const int32_t* __restrict__ rowidx, int64_t begin, int64_t end, int32_t nid,
-                                 int32_t* __restrict__ node_of_row) {
-    for (int64_t i = begin + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < end;
-         i += (int64_t)gridDim.x * blockDim.x)
-        node_of_row[rowidx ? rowidx[i] : (int32_t)i] = nid;
+__global__ void fill_positions_k(const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1,
+                                 const PosItem* __restrict__ items, int32_t* __restrict__ node_of_row) {
+    const PosItem it = items[blockIdx.y];
+    const int32_t* __restrict__ rowidx = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
+    for (long long i = it.begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < it.end;
+         i += (long long)gridDim.x * blockDim.x)
+        node_of_row[rowidx ? rowidx[i] : (int32_t)i] = it.nid;
 }
 
 // ------------------------------------------------------------------------------------
@@ -599,48 +694,47 @@ cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, i
 }
 
 cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t gid, int2* gq,
-                                 unsigned* absmax_bits, GradScale* scale, cudaStream_t st) {
+                                 unsigned* absmax_bits, GradScale* scale, int bits, cudaStream_t st) {
     cudaError_t e = cudaMemsetAsync(absmax_bits, 0, 2 * sizeof(unsigned), st);
     if (e != cudaSuccess) return e;
-    int g = grid_for(n, 256, kNumSMs * 4);
+    int g = grid_for(n, 256, kNumSMs * 8);
     grad_absmax_k<<<g, 256, 0, st>>>(gp, n, K, gid, absmax_bits);
-    grad_quantize_k<<<g, 256, 0, st>>>(gp, n, K, gid, gq, absmax_bits, scale);
+    grad_quantize_k<<<g, 256, 0, st>>>(gp, n, K, gid, gq, absmax_bits, scale, bits);
     return cudaGetLastError();
 }
 
-cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx,
-                              int64_t begin, int64_t end, int32_t F, const uint32_t* group_mask,
-                              const int32_t* nbins, const int64_t* feat_off, long long* hist, int variant,
-                              cudaStream_t st, int* launches) {
-    (void)variant;
-    int64_t n = end - begin;
-    if (n <= 0) return cudaSuccess;
+int64_t hist_rows_per_item(int64_t total_rows, int groups) {
+    // one CTA per SM (128 KB of shared memory); aim at about two waves over all feature groups,
+    // never less than 4 sweeps of the CTA (4096 rows) per item so zeroing + flushing stays small
+    int64_t items = std::max<int64_t>(1, (2 * kNumSMs) / std::max(1, groups));
+    int64_t rows = (total_rows + items - 1) / items;
+    rows = std::max<int64_t>(rows, 4 * kHistThreads);
+    return (rows + kHistThreads - 1) / kHistThreads * kHistThreads;
+}
+
+cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx0,
+                              const int32_t* rowidx1, const RowItem* items, int n_items, int32_t F,
+                              const uint32_t* group_mask, const int32_t* nbins, const int32_t* feat_owner,
+                              const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
+                              cudaStream_t st) {
+    if (n_items <= 0) return cudaSuccess;
     static bool attr_set = false;
-    const int smem = kHistSmemBytes + kStageBytes;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(hist_build_k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaError_t e = cudaFuncSetAttribute(hist_build_k, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             kHistSmemBytes);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    const int groups = S8 / kGroup;
-    const int64_t chunk = kHistWarps * 32;  // rows one CTA consumes per sweep
-    // at least 4 sweeps per CTA before another CTA is worth its 128 KB zero + flush
-    int64_t gx = (n + 4 * chunk - 1) / (4 * chunk);
-    int64_t cap = kNumSMs;
-    if (gx > cap) gx = cap;
-    if (gx < 1) gx = 1;
-    int64_t rows_per_cta = ((n + gx - 1) / gx + chunk - 1) / chunk * chunk;
-    gx = (n + rows_per_cta - 1) / rows_per_cta;
-    dim3 grid((unsigned)gx, (unsigned)groups);
-    hist_build_k<<<grid, kHistThreads, smem, st>>>(bins, S8, gq, rowidx, begin, end, F, group_mask, nbins,
-                                                   feat_off, hist, rows_per_cta);
-    if (launches) (*launches)++;
+    dim3 grid((unsigned)n_items, (unsigned)(S8 / kGroup));
+    hist_build_k<<<grid, kHistThreads, kHistSmemBytes, st>>>(bins, S8, gq, rowidx0, rowidx1, items, F, group_mask,
+                                                             nbins, feat_owner, feat_inner, owner_stride, seg_out);
     return cudaGetLastError();
 }
 
-cudaError_t launch_hist_subtract(const long long* parent, const long long* small, long long* out, int64_t len,
-                                 cudaStream_t st) {
-    hist_subtract_k<<<grid_for(len, 256), 256, 0, st>>>(parent, small, out, len);
+cudaError_t launch_hist_subtract(const SubItem* items, int n_items, int64_t len, cudaStream_t st) {
+    if (n_items <= 0) return cudaSuccess;
+    dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n_items);
+    hist_subtract_k<<<grid, 256, 0, st>>>(items, len);
     return cudaGetLastError();
 }
 cudaError_t launch_hist_to_double(const long long* hist, int64_t len, const GradScale* scale, double* out,
@@ -653,75 +747,53 @@ cudaError_t launch_hist_from_double(const double* in, int64_t len, const GradSca
     hist_from_double_k<<<grid_for(len, 256), 256, 0, st>>>(in, len, scale, hist);
     return cudaGetLastError();
 }
-
-cudaError_t launch_split_scan(const long long* hist, const int32_t* start, const int64_t* feat_off,
-                              const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
-                              const GradScale* scale, GainParams gp, long long sample_cnt,
-                              const double* totals_in, ytk_split* out, cudaStream_t st) {
-    split_scan_k<<<1, kScanWarps * 32, 0, st>>>(hist, start, feat_off, fea_selected, f_from, f_to, first_fea,
-                                                scale, gp, sample_cnt, totals_in, out);
-    return cudaGetLastError();
-}
-
-int64_t partition_scratch_ints(int64_t n) {
-    int64_t nblocks = (n + kPartTile - 1) / kPartTile;
-    return nblocks + 1 + (n + 3) / 4;  // block counts, then one flag byte per row
-}
-
-template <int MODE>
-static cudaError_t partition_impl(const uint8_t* src, int32_t S8, const int32_t* rowidx_in, int32_t* rowidx_out,
-                                  int64_t begin, int64_t end, int32_t fid, float cond, int32_t* scratch,
-                                  PartitionCounts* counts, cudaStream_t st, int* launches) {
-    int64_t n = end - begin;
-    if (n <= 0) {
-        cudaError_t e = cudaMemsetAsync(counts, 0, sizeof(PartitionCounts), st);
-        return e;
-    }
-    int nblocks = (int)((n + kPartTile - 1) / kPartTile);
-    int32_t* block_cnt = scratch;
-    uint8_t* flags = reinterpret_cast<uint8_t*>(scratch + nblocks + 1);
-    partition_count_k<MODE><<<nblocks, kPartThreads, 0, st>>>(src, S8, rowidx_in, begin, end, fid, cond, flags,
-                                                              block_cnt);
-    partition_scan_k<<<1, 1024, 0, st>>>(block_cnt, nblocks, n, counts);
-    partition_scatter_k<<<nblocks, kPartThreads, 0, st>>>(rowidx_in, rowidx_out, begin, end, flags, block_cnt,
-                                                          counts);
-    if (launches) *launches += 3;
-    return cudaGetLastError();
-}
-
-cudaError_t launch_partition(const uint8_t* bins, int32_t S8, const int32_t* rowidx_in, int32_t* rowidx_out,
-                             int64_t begin, int64_t end, int32_t fid, float cond, int32_t* scratch,
-                             PartitionCounts* counts, cudaStream_t st, int* launches) {
-    return partition_impl<0>(bins, S8, rowidx_in, rowidx_out, begin, end, fid, cond, scratch, counts, st,
-                             launches);
-}
-
-cudaError_t launch_compact_mask(const uint8_t* mask, int64_t n, int32_t* rowidx_out, int32_t* scratch,
-                                PartitionCounts* counts, cudaStream_t st, int* launches) {
-    return partition_impl<1>(mask, 0, nullptr, rowidx_out, 0, n, 0, 0.f, scratch, counts, st, launches);
-}
-
-cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx, int64_t begin, int64_t end, long long* out,
-                             cudaStream_t st) {
-    if (end <= begin) return cudaSuccess;
-    leaf_sums_k<<<grid_for(end - begin, 256, kNumSMs * 4), 256, 0, st>>>(gq, rowidx, begin, end, out);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_iota(int32_t* p, int64_t n, cudaStream_t st) {
+cudaError_t launch_copy_segments(const long long* src, long long* const* dst, int n, int64_t len, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
-    iota_k<<<grid_for(n, 256), 256, 0, st>>>(p, n);
+    dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n);
+    copy_segments_k<<<grid, 256, 0, st>>>(src, dst, len);
     return cudaGetLastError();
 }
+
+cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t* start, const int64_t* feat_off,
+                              const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
+                              const GradScale* scale, GainParams gp, ytk_split* out, cudaStream_t st) {
+    if (n_nodes <= 0) return cudaSuccess;
+    split_scan_k<<<n_nodes, kScanWarps * 32, 0, st>>>(nodes, start, feat_off, fea_selected, f_from, f_to, first_fea,
+                                                      scale, gp, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_partition(const uint8_t* src, int32_t S8, int32_t* rowidx0, int32_t* rowidx1,
+                             const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
+                             uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st) {
+    if (n_segs <= 0) return cudaSuccess;
+    if (n_tiles > 0)
+        partition_count_k<<<n_tiles, kPartThreads, 0, st>>>(src, S8, rowidx0, rowidx1, segs, tile_seg, flags,
+                                                            block_cnt);
+    partition_scan_k<<<n_segs, 1024, 0, st>>>(segs, block_cnt, counts);
+    if (n_tiles > 0)
+        partition_scatter_k<<<n_tiles, kPartThreads, 0, st>>>(rowidx0, rowidx1, segs, tile_seg, flags, block_cnt,
+                                                              counts);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1, const RowItem* items,
+                             int n_items, long long* out, cudaStream_t st) {
+    if (n_items <= 0) return cudaSuccess;
+    leaf_sums_k<<<n_items, 256, 0, st>>>(gq, rowidx0, rowidx1, items, out);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
     fill_i32_k<<<grid_for(n, 256), 256, 0, st>>>(p, n, v);
     return cudaGetLastError();
 }
-cudaError_t launch_fill_positions(const int32_t* rowidx, int64_t begin, int64_t end, int32_t nid,
+cudaError_t launch_fill_positions(const int32_t* rowidx0, const int32_t* rowidx1, const PosItem* items, int n_items,
                                   int32_t* node_of_row, cudaStream_t st) {
-    if (end <= begin) return cudaSuccess;
-    fill_positions_k<<<grid_for(end - begin, 256), 256, 0, st>>>(rowidx, begin, end, nid, node_of_row);
+    if (n_items <= 0) return cudaSuccess;
+    dim3 grid(64, (unsigned)n_items);
+    fill_positions_k<<<grid, 256, 0, st>>>(rowidx0, rowidx1, items, node_of_row);
     return cudaGetLastError();
 }
 

@@ -71,6 +71,9 @@ struct HistPool {
         for (Item* it : used) avail.push_back(it);
         used.clear();
     }
+    void rename(int from, int to) {   // in-place reuse of a slot (sibling written over its parent)
+        for (Item* it : used) if (it->nid == from) { it->nid = to; return; }
+    }
     long long* get(int nid) {    // getHist :238-245
         for (Item* it : used) if (it->nid == nid) return it->buf;
         return nullptr;
@@ -84,13 +87,16 @@ struct HistPool {
             }
         }
     }
-    // allocHist :209-236; *fresh is set when a new device buffer is needed
-    Item* alloc(int nid, bool* fresh) {
+    // allocHist :209-236; *fresh is set when a new device buffer is needed.  `unbounded`: the
+    // reference's capacity (max_leaf_cnt) can never be exceeded by its own allocation order, so
+    // no eviction ever happens there; the batched path may hold a level's parents and children
+    // at once and simply takes another slot instead.
+    Item* alloc(int nid, bool* fresh, bool unbounded = false) {
         Item* it;
         *fresh = false;
         if (!avail.empty()) {
             it = avail.front(); avail.pop_front();
-        } else if ((int)all.size() < capacity) {
+        } else if (unbounded || (int)all.size() < capacity) {
             it = new Item{nid, nullptr};
             all.push_back(it);
             *fresh = true;
@@ -124,11 +130,46 @@ int java_float_compare(float a, float b) {   // java.lang.Float.compare
     return ia == ib ? 0 : (ia < ib ? -1 : 1);
 }
 
-struct Mailbox {                   // pinned host memory the device results land in
-    ytk::PartitionCounts counts[2];    // local, global
-    long long leaf[2];
-    ytk::GradScale scale;
-    ytk_split split[2 * 64];           // [node 0/1][rank]
+// growable device array + host->device upload of a work table
+template <typename T>
+struct DevTable {
+    T* d = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        size_t nc = std::max<size_t>(n, cap * 2);
+        nc = std::max<size_t>(nc, 64);
+        if (d) { cudaError_t e = cudaFree(d); if (e != cudaSuccess) return e; d = nullptr; cap = 0; }
+        cudaError_t e = cudaMalloc(&d, nc * sizeof(T));
+        if (e == cudaSuccess) cap = nc;
+        return e;
+    }
+    cudaError_t upload(const std::vector<T>& v, cudaStream_t st) {
+        if (v.empty()) return cudaSuccess;
+        cudaError_t e = reserve(v.size());
+        if (e != cudaSuccess) return e;
+        // pageable source: the runtime stages it before returning, so `v` may die afterwards
+        return cudaMemcpyAsync(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
+    }
+    void release() { if (d) cudaFree(d); d = nullptr; cap = 0; }
+};
+
+// growable pinned host array for results coming back from the device
+template <typename T>
+struct PinnedBuf {
+    T* h = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        size_t nc = std::max<size_t>(n, cap * 2);
+        nc = std::max<size_t>(nc, 64);
+        if (h) cudaFreeHost(h);
+        h = nullptr; cap = 0;
+        cudaError_t e = cudaHostAlloc((void**)&h, nc * sizeof(T), cudaHostAllocDefault);
+        if (e == cudaSuccess) cap = nc;
+        return e;
+    }
+    void release() { if (h) cudaFreeHost(h); h = nullptr; cap = 0; }
 };
 
 }  // namespace
@@ -177,6 +218,8 @@ static void ytk_host_node_value(const ytk_gbdt_params* p, double G, double H, fl
 struct ytk_gbdt {
     ytk_gbdt_params p{};
     int device = 0, rank = 0, world = 1;
+    int fixed_bits = ytk::kDefaultFixedBits;
+    bool force_sequential = false;
     cudaStream_t st = nullptr;
     ncclComm_t comm = nullptr;
 
@@ -185,42 +228,53 @@ struct ytk_gbdt {
     std::vector<int32_t> start, nbins, assign;   // assign: avgAssign(F, world)
     int f_from = 0, f_to = 0;
     int64_t seg_max = 0;      // owned-segment length (int64 words), equal on every rank
-    int64_t local_len = 0;    // length of a locally built histogram (world * seg_max)
 
     uint8_t* d_bins = nullptr;
     float* d_gp = nullptr;
     int2* d_gq = nullptr;
     int32_t* d_rowidx[2] = {nullptr, nullptr};
-    int32_t* d_scratch = nullptr;      // partition scratch
+    uint8_t* d_flags = nullptr;        // partition scratch: one byte per row
+    int32_t* d_block_cnt = nullptr;    // partition scratch: one int per tile
+    size_t block_cnt_cap = 0;
     uint8_t* d_mask = nullptr;
     int32_t* d_start = nullptr;
     int32_t* d_nbins = nullptr;
-    int64_t* d_off_local = nullptr;    // layout of a locally built histogram ([rank][segment])
-    int64_t* d_off_owned = nullptr;    // layout inside this rank's reduced segment
+    int32_t* d_feat_owner = nullptr;   // rank owning feature f
+    int32_t* d_feat_zero = nullptr;    // all zeros: "everything in one flat segment"
+    int64_t* d_off_inner = nullptr;    // offset of feature f inside its owner's segment
     int64_t* d_off_flat = nullptr;     // reference layout 2*start[f]
     uint32_t* d_group_mask = nullptr;
     uint8_t* d_fea_sel = nullptr;
-    long long* d_hist_local = nullptr; // world > 1: local histogram before the reduce-scatter
     long long* d_hist_flat = nullptr;  // hooks
     long long* d_hist_flat2 = nullptr;
     double* d_hist_dbl = nullptr;
     ytk::GradScale* d_scale = nullptr;
     ytk::GradScale* d_scale_hook = nullptr;
     unsigned* d_absmax = nullptr;
-    ytk::PartitionCounts* d_counts = nullptr;  // [2]: local, global
-    ytk_split* d_split = nullptr;              // [2 nodes][world]
-    ytk_split* d_split_local = nullptr;        // [2]
-    long long* d_leaf = nullptr;               // [2]
     int* d_bad = nullptr;
     int32_t* d_node_of_row = nullptr;
     void* d_stage = nullptr;  size_t stage_bytes = 0;   // upload staging
-    Mailbox* mail = nullptr;
+
+    // per-batch work tables and result buffers
+    DevTable<ytk::RowItem> t_items, t_leaf_items;
+    DevTable<ytk::SplitSeg> t_segs;
+    DevTable<int> t_tile_seg;
+    DevTable<ytk::ScanNode> t_scan;
+    DevTable<ytk::SubItem> t_sub;
+    DevTable<ytk::PosItem> t_pos;
+    DevTable<long long*> t_seg_out;
+    DevTable<ytk::PartitionCounts> t_counts;     // [2*m]: local, then global (world > 1)
+    DevTable<ytk_split> t_split_local, t_split_all;
+    DevTable<long long> t_leaf, t_hist_local, t_rs_out;
+    PinnedBuf<ytk::PartitionCounts> h_counts;
+    PinnedBuf<ytk_split> h_split;
+    PinnedBuf<long long> h_leaf;
+    PinnedBuf<ytk::GradScale> h_scale;
 
     HistPool pool;
     bool grads_set = false, rows_set = false;
     std::vector<Interval> iv;          // last tree: interval of every node
     std::vector<int> leaf_nodes;
-    int64_t root_begin = 0;
     int launches = 0;
     std::vector<cudaEvent_t> ev;       // event pairs around histogram builds
     int ev_used = 0;
@@ -252,20 +306,24 @@ int ensure_stage(ytk_gbdt* h, size_t bytes) {
 void free_all(ytk_gbdt* h) {
     cudaSetDevice(h->device);
     auto F = [](void* p) { if (p) cudaFree(p); };
-    F(h->d_bins); F(h->d_gp); F(h->d_gq); F(h->d_rowidx[0]); F(h->d_rowidx[1]); F(h->d_scratch);
-    F(h->d_mask); F(h->d_start); F(h->d_nbins); F(h->d_off_local); F(h->d_off_owned); F(h->d_off_flat);
-    F(h->d_group_mask); F(h->d_fea_sel); F(h->d_hist_local); F(h->d_hist_flat); F(h->d_hist_flat2);
-    F(h->d_hist_dbl); F(h->d_scale); F(h->d_scale_hook); F(h->d_absmax); F(h->d_counts); F(h->d_split);
-    F(h->d_split_local); F(h->d_leaf); F(h->d_bad); F(h->d_node_of_row); F(h->d_stage);
+    F(h->d_bins); F(h->d_gp); F(h->d_gq); F(h->d_rowidx[0]); F(h->d_rowidx[1]); F(h->d_flags); F(h->d_block_cnt);
+    F(h->d_mask); F(h->d_start); F(h->d_nbins); F(h->d_feat_owner); F(h->d_feat_zero); F(h->d_off_inner);
+    F(h->d_off_flat); F(h->d_group_mask); F(h->d_fea_sel); F(h->d_hist_flat); F(h->d_hist_flat2);
+    F(h->d_hist_dbl); F(h->d_scale); F(h->d_scale_hook); F(h->d_absmax); F(h->d_bad); F(h->d_node_of_row);
+    F(h->d_stage);
+    h->t_items.release(); h->t_leaf_items.release(); h->t_segs.release(); h->t_tile_seg.release();
+    h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
+    h->t_split_local.release(); h->t_split_all.release(); h->t_leaf.release(); h->t_hist_local.release();
+    h->t_rs_out.release();
+    h->h_counts.release(); h->h_split.release(); h->h_leaf.release(); h->h_scale.release();
     for (auto* it : h->pool.all) { F(it->buf); delete it; }
     for (auto e : h->ev) cudaEventDestroy(e);
-    if (h->mail) cudaFreeHost(h->mail);
     if (h->comm) ytk::nccl_api().CommDestroy(h->comm);
     if (h->st) cudaStreamDestroy(h->st);
 }
 
 // Selected-feature tables for one make()/hook call (initAssistData, :425-469).
-int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* first_owned) {
+int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* first_owned, int* n_sel) {
     std::vector<uint8_t> sel(h->F, 0);
     if (!fea_index) {
         std::fill(sel.begin(), sel.end(), 1);
@@ -278,21 +336,14 @@ int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* firs
         }
     }
     std::vector<uint32_t> gm(h->groups, 0);
-    for (int f = 0; f < h->F; f++) if (sel[f]) gm[f / ytk::kGroup] |= 1u << (f % ytk::kGroup);
+    int cnt = 0;
+    for (int f = 0; f < h->F; f++) if (sel[f]) { gm[f / ytk::kGroup] |= 1u << (f % ytk::kGroup); cnt++; }
+    if (n_sel) *n_sel = cnt;
     *first_owned = -1;   // firstSampledFeaIndexInThread (:451-467)
     for (int f = h->f_from; f < h->f_to; f++) if (sel[f]) { *first_owned = f; break; }
     CK(cudaMemcpyAsync(h->d_fea_sel, sel.data(), h->F, cudaMemcpyHostToDevice, h->st));
     CK(cudaMemcpyAsync(h->d_group_mask, gm.data(), h->groups * sizeof(uint32_t), cudaMemcpyHostToDevice, h->st));
-    CK(cudaStreamSynchronize(h->st));   // host vectors go out of scope
     return YTK_OK;
-}
-
-int count_selected(const ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea) {
-    if (!fea_index) return h->F;
-    std::vector<uint8_t> sel(h->F, 0);
-    int c = 0;
-    for (int i = 0; i < n_fea; i++) if (!sel[fea_index[i]]) { sel[fea_index[i]] = 1; c++; }
-    return c;
 }
 
 int hist_events(ytk_gbdt* h, cudaEvent_t* a, cudaEvent_t* b) {
@@ -308,62 +359,101 @@ int hist_events(ytk_gbdt* h, cudaEvent_t* a, cudaEvent_t* b) {
     return YTK_OK;
 }
 
-// HistogramBuilder.buildHist (J/data/gbdt/HistogramBuilder.java:56-98) into `dst`
-// (this rank's reduced segment): local build, then the reduce-scatter by feature range.
-int build_node_hist(ytk_gbdt* h, const Interval& iv, long long* dst, ytk_time_stats* ts, int n_sel) {
-    const int32_t* rowidx = iv.buf < 0 ? nullptr : h->d_rowidx[iv.buf];
-    long long* local = h->world == 1 ? dst : h->d_hist_local;
+// Splits node intervals into work items of about `rows_per_item` rows.
+void add_row_items(std::vector<ytk::RowItem>& items, const Interval& v, int seg, int64_t rows_per_item) {
+    if (v.e <= v.b) return;
+    for (int64_t b = v.b; b < v.e; b += rows_per_item)
+        items.push_back({(long long)b, (long long)std::min(v.e, b + rows_per_item), v.buf, seg});
+}
+
+struct HistJob { int nid; long long* dst; };   // build node nid's histogram into dst (this rank's segment)
+
+// HistogramBuilder.buildHist (J/data/gbdt/HistogramBuilder.java:56-98) for a batch of nodes:
+// one kernel launch over all their rows, then (world > 1) one reduce-scatter by feature range.
+int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, int n_sel) {
+    const int m = (int)jobs.size();
+    if (m == 0) return YTK_OK;
+    int64_t total = 0;
+    for (auto& j : jobs) total += h->iv[j.nid].e - h->iv[j.nid].b;
+    const int64_t rpi = ytk::hist_rows_per_item(total, h->groups);
+    std::vector<ytk::RowItem> items;
+    std::vector<long long*> outs(m);
+    const int64_t local_len = h->seg_max * h->world;
+    if (h->world > 1) CK(h->t_hist_local.reserve((size_t)m * local_len));
+    for (int k = 0; k < m; k++) {
+        const Interval& v = h->iv[jobs[k].nid];
+        add_row_items(items, v, k, rpi);
+        // world > 1: local layout [rank][node][segment] so that ONE reduce-scatter serves the batch
+        outs[k] = h->world == 1 ? jobs[k].dst : h->t_hist_local.d + (int64_t)k * h->seg_max;
+        T->hist_built++;
+        T->hist_cells += (double)(v.e - v.b) * n_sel;
+        T->hist_rows += (double)(v.e - v.b);
+        if (v.buf >= 0) T->hist_rows_indexed += (double)(v.e - v.b);
+    }
     cudaEvent_t e0, e1;
     RET(hist_events(h, &e0, &e1));
     CK(cudaEventRecord(e0, h->st));
-    CK(cudaMemsetAsync(local, 0, h->local_len * sizeof(long long), h->st));
-    CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, rowidx, iv.b, iv.e, h->F, h->d_group_mask, h->d_nbins,
-                              h->d_off_local, local, 0, h->st, &h->launches));
+    if (h->world == 1) {
+        for (int k = 0; k < m; k++) CK(cudaMemsetAsync(jobs[k].dst, 0, h->seg_max * sizeof(long long), h->st));
+    } else {
+        CK(cudaMemsetAsync(h->t_hist_local.d, 0, (size_t)m * local_len * sizeof(long long), h->st));
+    }
+    CK(h->t_items.upload(items, h->st));
+    CK(h->t_seg_out.upload(outs, h->st));
+    const long long owner_stride = h->world == 1 ? 0 : (long long)m * h->seg_max;
+    CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_items.d,
+                              (int)items.size(), h->F, h->d_group_mask, h->d_nbins, h->d_feat_owner, h->d_off_inner,
+                              owner_stride, h->t_seg_out.d, h->st));
+    if (!items.empty()) h->launches++;
     CK(cudaEventRecord(e1, h->st));
     if (h->world > 1) {
         double t0 = now_ms();
-        NK(ytk::nccl_api().ReduceScatter(local, dst, (size_t)h->seg_max, ncclInt64, ncclSum, h->comm, h->st));
-        if (ts) ts->communicate_hist += now_ms() - t0;
-    }
-    if (ts) {
-        ts->hist_built++;
-        ts->hist_cells += (double)(iv.e - iv.b) * n_sel;
-        ts->hist_rows += (double)(iv.e - iv.b);
-        if (iv.buf >= 0) ts->hist_rows_indexed += (double)(iv.e - iv.b);
+        CK(h->t_rs_out.reserve((size_t)m * h->seg_max));
+        NK(ytk::nccl_api().ReduceScatter(h->t_hist_local.d, h->t_rs_out.d, (size_t)m * h->seg_max, ncclInt64,
+                                         ncclSum, h->comm, h->st));
+        for (int k = 0; k < m; k++) outs[k] = jobs[k].dst;
+        CK(h->t_seg_out.upload(outs, h->st));
+        CK(ytk::launch_copy_segments(h->t_rs_out.d, h->t_seg_out.d, m, h->seg_max, h->st));
+        h->launches++;
+        T->communicate_hist += now_ms() - t0;
     }
     return YTK_OK;
 }
 
-// updateTreeMakerNodeStats + findBestSplit(nid, hist) + syncBestSplit (:543-595, :640-653)
-// for up to two nodes at once; results land in the mailbox.
-int search_nodes(ytk_gbdt* h, int n_nodes, long long* const* hists, const int64_t* sample_cnt, int first_owned) {
-    GainParams gp = gain_params(h->p);
-    for (int k = 0; k < n_nodes; k++) {
-        CK(ytk::launch_split_scan(hists[k], h->d_start, h->d_off_owned, h->d_fea_sel, h->f_from, h->f_to,
-                                  first_owned, h->d_scale, gp, sample_cnt[k], nullptr,
-                                  h->d_split_local + k, h->st));
-        h->launches++;
-    }
+// updateTreeMakerNodeStats + findBestSplit(nid, hist) + syncBestSplit (:543-595, :640-653) for a
+// batch of nodes; the merged record of node k lands in recs[k].
+int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first_owned, std::vector<ytk_split>& recs) {
+    const int m = (int)nodes.size();
+    recs.resize(m);
+    if (m == 0) return YTK_OK;
+    CK(h->t_scan.upload(nodes, h->st));
+    CK(h->t_split_local.reserve(m));
+    CK(ytk::launch_split_scan(h->t_scan.d, m, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to,
+                              first_owned, h->d_scale, gain_params(h->p), h->t_split_local.d, h->st));
+    h->launches++;
+    CK(h->h_split.reserve((size_t)m * h->world));
     if (h->world == 1) {
-        CK(cudaMemcpyAsync(h->mail->split, h->d_split_local, n_nodes * sizeof(ytk_split), cudaMemcpyDeviceToHost,
-                           h->st));
+        CK(cudaMemcpyAsync(h->h_split.h, h->t_split_local.d, m * sizeof(ytk_split), cudaMemcpyDeviceToHost, h->st));
     } else {
         // "split allgather": every rank's record for each node, merged on the host with the
         // needReplace rule -- replaces allreduceRpc(SplitInfo) and allreduceArrayRpc(MAX)
-        NK(ytk::nccl_api().AllGather(h->d_split_local, h->d_split, n_nodes * sizeof(ytk_split), ncclChar, h->comm,
+        CK(h->t_split_all.reserve((size_t)m * h->world));
+        NK(ytk::nccl_api().AllGather(h->t_split_local.d, h->t_split_all.d, m * sizeof(ytk_split), ncclChar, h->comm,
                                      h->st));
-        CK(cudaMemcpyAsync(h->mail->split, h->d_split, (size_t)h->world * n_nodes * sizeof(ytk_split),
+        CK(cudaMemcpyAsync(h->h_split.h, h->t_split_all.d, (size_t)h->world * m * sizeof(ytk_split),
                            cudaMemcpyDeviceToHost, h->st));
     }
     CK(cudaStreamSynchronize(h->st));
+    if (h->world == 1) {
+        for (int k = 0; k < m; k++) recs[k] = h->h_split.h[k];
+    } else {
+        std::vector<ytk_split> tmp(h->world);
+        for (int k = 0; k < m; k++) {
+            for (int r = 0; r < h->world; r++) tmp[r] = h->h_split.h[(size_t)r * m + k];
+            ytk_gbdt_merge_splits(tmp.data(), h->world, &recs[k]);
+        }
+    }
     return YTK_OK;
-}
-
-void merged_record(const ytk_gbdt* h, int n_nodes, int k, ytk_split* out) {
-    if (h->world == 1) { *out = h->mail->split[k]; return; }
-    std::vector<ytk_split> recs(h->world);
-    for (int r = 0; r < h->world; r++) recs[r] = h->mail->split[r * n_nodes + k];
-    ytk_gbdt_merge_splits(recs.data(), h->world, out);
 }
 
 void apply_record(NodeStats& s, const ytk_split& r) {
@@ -371,6 +461,51 @@ void apply_record(NodeStats& s, const ytk_split& r) {
     s.root_gain = r.root_gain; s.node_value = r.node_value;
     s.best_lc = r.loss_chg; s.best_fid = r.fid; s.best_lo = r.lo; s.best_hi = r.hi;
 }
+
+// position.resetPosition (SamplePositionData.java:115-133) for a batch of nodes, plus the global
+// child counts of initTreeMakerNodeStats(l, r) (:522-541).  counts_local/global: [m].
+int partition_nodes(ytk_gbdt* h, const uint8_t* src, const std::vector<ytk::SplitSeg>& segs_in,
+                    std::vector<ytk::PartitionCounts>& local, std::vector<ytk::PartitionCounts>& global) {
+    const int m = (int)segs_in.size();
+    local.resize(m); global.resize(m);
+    if (m == 0) return YTK_OK;
+    std::vector<ytk::SplitSeg> segs = segs_in;
+    std::vector<int> tile_seg;
+    for (int k = 0; k < m; k++) {
+        int64_t n = segs[k].end - segs[k].begin;
+        int nt = (int)((n + ytk::kPartTile - 1) / ytk::kPartTile);
+        segs[k].tile0 = (int)tile_seg.size();
+        segs[k].ntiles = nt;
+        for (int t = 0; t < nt; t++) tile_seg.push_back(k);
+    }
+    if (tile_seg.size() + 1 > h->block_cnt_cap) {
+        if (h->d_block_cnt) CK(cudaFree(h->d_block_cnt));
+        h->d_block_cnt = nullptr;
+        h->block_cnt_cap = std::max<size_t>(tile_seg.size() + 1, 2 * h->block_cnt_cap);
+        CK(cudaMalloc(&h->d_block_cnt, h->block_cnt_cap * sizeof(int32_t)));
+    }
+    CK(h->t_segs.upload(segs, h->st));
+    CK(h->t_tile_seg.upload(tile_seg, h->st));
+    CK(h->t_counts.reserve(2 * (size_t)m));
+    CK(ytk::launch_partition(src, h->S8, h->d_rowidx[0], h->d_rowidx[1], h->t_segs.d, m, h->t_tile_seg.d,
+                             (int)tile_seg.size(), h->d_flags, h->d_block_cnt, h->t_counts.d, h->st));
+    h->launches += tile_seg.empty() ? 1 : 3;
+    const int nc = h->world > 1 ? 2 * m : m;
+    if (h->world > 1)   // allreduceArray(long[2], SUM) (:538), all nodes of the batch at once
+        NK(ytk::nccl_api().AllReduce(h->t_counts.d, h->t_counts.d + m, 2 * (size_t)m, ncclInt64, ncclSum, h->comm,
+                                     h->st));
+    CK(h->h_counts.reserve(nc));
+    CK(cudaMemcpyAsync(h->h_counts.h, h->t_counts.d, nc * sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost,
+                       h->st));
+    CK(cudaStreamSynchronize(h->st));
+    for (int k = 0; k < m; k++) {
+        local[k] = h->h_counts.h[k];
+        global[k] = h->h_counts.h[h->world > 1 ? m + k : k];
+    }
+    return YTK_OK;
+}
+
+struct SplitJob { int nid, l, r, depth; bool terminal; };
 
 }  // namespace
 
@@ -427,6 +562,7 @@ int ytk_gbdt_merge_splits(const ytk_split* recs, int32_t n, ytk_split* out) {
 
 int ytk_gbdt_nccl_unique_id(void* out128) {
     const char* why = "";
+    if (!out128) return fail(YTK_ERR_ARG, "nccl_unique_id: null argument");
     if (!ytk::nccl_api().load(&why)) return fail(YTK_ERR_NCCL, "NCCL unavailable: %s", why);
     ncclUniqueId id;
     NK(ytk::nccl_api().GetUniqueId(&id));
@@ -456,12 +592,15 @@ int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank,
     CK(cudaSetDevice(device));
     ytk_gbdt* h = new ytk_gbdt();
     h->p = *params; h->device = device; h->rank = rank; h->world = world;
-    int rc = YTK_OK;
+    if (const char* s = getenv("YTK_GBDT_FIXED_BITS")) {
+        int b = atoi(s);
+        if (b < 8 || b > 30) { delete h; return fail(YTK_ERR_ARG, "YTK_GBDT_FIXED_BITS=%s not in [8,30]", s); }
+        h->fixed_bits = b;
+    }
+    if (const char* s = getenv("YTK_GBDT_SEQUENTIAL")) h->force_sequential = atoi(s) != 0;
     auto bail = [&](int code) { free_all(h); delete h; return code; };
     if (cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking) != cudaSuccess)
         return bail(fail(YTK_ERR_CUDA, "cudaStreamCreate failed"));
-    if (cudaHostAlloc((void**)&h->mail, sizeof(Mailbox), cudaHostAllocDefault) != cudaSuccess)
-        return bail(fail(YTK_ERR_CUDA, "cudaHostAlloc failed"));
     if (world > 1) {
         const char* why = "";
         if (!nccl_id) return bail(fail(YTK_ERR_ARG, "create: world > 1 needs the NCCL unique id"));
@@ -472,7 +611,6 @@ int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank,
         if (r != ncclSuccess)
             return bail(fail(YTK_ERR_NCCL, "ncclCommInitRank: %s", ytk::nccl_api().GetErrorString(r)));
     }
-    (void)rc;
     *out = h;
     return YTK_OK;
 }
@@ -492,6 +630,7 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
     h->F = F; h->N = n_rows;
     h->start.assign(start, start + F + 1);
     h->nbins.resize(F);
+    if (start[0] != 0) return fail(YTK_ERR_ARG, "set_bins: start[0] must be 0");
     for (int f = 0; f < F; f++) {
         h->nbins[f] = start[f + 1] - start[f];
         if (h->nbins[f] < 1) return fail(YTK_ERR_ARG, "[GBDT] fid:%d has no global feature vals!", f);
@@ -499,7 +638,6 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
             return fail(YTK_ERR_UNSUPPORTED, "feature %d has %d bins; this build stores slots as uint8 (max %d)",
                         f, h->nbins[f], ytk::kMaxBins);
     }
-    if (start[0] != 0) return fail(YTK_ERR_ARG, "set_bins: start[0] must be 0");
     h->B = start[F];
     h->groups = (F + ytk::kGroup - 1) / ytk::kGroup;
     h->S8 = h->groups * ytk::kGroup;
@@ -512,13 +650,14 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
     for (int r = 0; r < h->world; r++)
         h->seg_max = std::max<int64_t>(h->seg_max, 2LL * (start[h->assign[2 * r + 1]] - start[h->assign[2 * r]]));
     if (h->seg_max == 0) h->seg_max = 2;
-    h->local_len = h->seg_max * h->world;
-    std::vector<int64_t> off_local(F), off_owned(F, 0), off_flat(F);
+    std::vector<int32_t> owner(F), zeros(F, 0);
+    std::vector<int64_t> off_inner(F), off_flat(F);
     for (int r = 0; r < h->world; r++)
-        for (int f = h->assign[2 * r]; f < h->assign[2 * r + 1]; f++)
-            off_local[f] = r * h->seg_max + 2LL * (start[f] - start[h->assign[2 * r]]);
+        for (int f = h->assign[2 * r]; f < h->assign[2 * r + 1]; f++) {
+            owner[f] = r;
+            off_inner[f] = 2LL * (start[f] - start[h->assign[2 * r]]);
+        }
     for (int f = 0; f < F; f++) off_flat[f] = 2LL * start[f];
-    for (int f = h->f_from; f < h->f_to; f++) off_owned[f] = 2LL * (start[f] - start[h->f_from]);
 
     const int64_t N1 = std::max<int64_t>(n_rows, 1);
     const int K = h->p.class_num;
@@ -528,33 +667,31 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
     CK(cudaMalloc(&h->d_gq, N1 * sizeof(int2)));
     CK(cudaMalloc(&h->d_rowidx[0], N1 * sizeof(int32_t)));
     CK(cudaMalloc(&h->d_rowidx[1], N1 * sizeof(int32_t)));
-    CK(cudaMalloc(&h->d_scratch, ytk::partition_scratch_ints(N1) * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_flags, N1));
     CK(cudaMalloc(&h->d_node_of_row, N1 * sizeof(int32_t)));
     CK(cudaMalloc(&h->d_start, (F + 1) * sizeof(int32_t)));
     CK(cudaMalloc(&h->d_nbins, F * sizeof(int32_t)));
-    CK(cudaMalloc(&h->d_off_local, F * sizeof(int64_t)));
-    CK(cudaMalloc(&h->d_off_owned, F * sizeof(int64_t)));
+    CK(cudaMalloc(&h->d_feat_owner, F * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_feat_zero, F * sizeof(int32_t)));
+    CK(cudaMalloc(&h->d_off_inner, F * sizeof(int64_t)));
     CK(cudaMalloc(&h->d_off_flat, F * sizeof(int64_t)));
     CK(cudaMalloc(&h->d_group_mask, h->groups * sizeof(uint32_t)));
     CK(cudaMalloc(&h->d_fea_sel, F));
-    CK(cudaMalloc(&h->d_hist_local, h->local_len * sizeof(long long)));
     CK(cudaMalloc(&h->d_hist_flat, 2LL * h->B * sizeof(long long)));
     CK(cudaMalloc(&h->d_hist_flat2, 2LL * h->B * sizeof(long long)));
     CK(cudaMalloc(&h->d_hist_dbl, 2LL * h->B * sizeof(double)));
     CK(cudaMalloc(&h->d_scale, sizeof(ytk::GradScale)));
     CK(cudaMalloc(&h->d_scale_hook, sizeof(ytk::GradScale)));
     CK(cudaMalloc(&h->d_absmax, 2 * sizeof(unsigned)));
-    CK(cudaMalloc(&h->d_counts, 2 * sizeof(ytk::PartitionCounts)));
-    CK(cudaMalloc(&h->d_split, 2 * h->world * sizeof(ytk_split)));
-    CK(cudaMalloc(&h->d_split_local, 2 * sizeof(ytk_split)));
-    CK(cudaMalloc(&h->d_leaf, 2 * sizeof(long long)));
     CK(cudaMalloc(&h->d_bad, sizeof(int)));
     CK(cudaMemsetAsync(h->d_bad, 0, sizeof(int), h->st));
     CK(cudaMemcpyAsync(h->d_start, start, (F + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
     CK(cudaMemcpyAsync(h->d_nbins, h->nbins.data(), F * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
-    CK(cudaMemcpyAsync(h->d_off_local, off_local.data(), F * sizeof(int64_t), cudaMemcpyHostToDevice, h->st));
-    CK(cudaMemcpyAsync(h->d_off_owned, off_owned.data(), F * sizeof(int64_t), cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemcpyAsync(h->d_feat_owner, owner.data(), F * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemcpyAsync(h->d_feat_zero, zeros.data(), F * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemcpyAsync(h->d_off_inner, off_inner.data(), F * sizeof(int64_t), cudaMemcpyHostToDevice, h->st));
     CK(cudaMemcpyAsync(h->d_off_flat, off_flat.data(), F * sizeof(int64_t), cudaMemcpyHostToDevice, h->st));
+    CK(h->h_scale.reserve(1));
     CK(cudaStreamSynchronize(h->st));
 
     // pool capacity (DataParallelTreeMaker.java:193-203); UNIT = 64, MB = 1<<20
@@ -679,31 +816,36 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     h->ev_used = 0;
     const bool loss_wise = p.grow_policy == 1;
     const float lr = p.learning_rate;
-    const int W = h->world;
+    // The reference's pool never evicts when it holds max_leaf_cnt histograms (its own allocation
+    // order cannot exceed that), so slot management is then free and whole levels can be batched.
+    const bool unbounded = (h->pool.capacity >= p.max_leaf_cnt && p.max_leaf_cnt > 0) ||
+                           (p.max_leaf_cnt <= 0);
+    const bool batch_levels = unbounded && !loss_wise && !h->force_sequential;
 
     // ---- initAssistData (:395-470)
-    int first_owned = -1;
-    RET(set_features(h, fea_index, n_fea, &first_owned));
-    const int n_sel = count_selected(h, fea_index, n_fea);
+    int first_owned = -1, n_sel = 0;
+    RET(set_features(h, fea_index, n_fea, &first_owned, &n_sel));
     h->pool.clear();
-    CK(ytk::launch_grad_quantize(h->d_gp, h->N, p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->st));
+    CK(ytk::launch_grad_quantize(h->d_gp, h->N, p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->fixed_bits,
+                                 h->st));
     h->launches += 2;
+    CK(cudaMemcpyAsync(h->h_scale.h, h->d_scale, sizeof(ytk::GradScale), cudaMemcpyDeviceToHost, h->st));
 
     std::vector<Interval>& iv = h->iv;
     iv.clear();
     h->leaf_nodes.clear();
+    std::vector<ytk::PartitionCounts> cl, cg;
     Interval root;
     if (row_mask) {
         if (!h->d_mask) CK(cudaMalloc(&h->d_mask, std::max<int64_t>(h->N, 1)));
         CK(cudaMemcpyAsync(h->d_mask, row_mask, h->N, cudaMemcpyHostToDevice, h->st));
-        CK(ytk::launch_compact_mask(h->d_mask, h->N, h->d_rowidx[0], h->d_scratch, h->d_counts, h->st, &h->launches));
-        CK(cudaMemcpyAsync(&h->mail->counts[0], h->d_counts, sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost, h->st));
-        CK(cudaStreamSynchronize(h->st));
-        root.b = 0; root.e = h->mail->counts[0].left; root.buf = 0;
+        std::vector<ytk::SplitSeg> sg(1);
+        sg[0] = {0, (long long)h->N, -1, -1, 0.f, 0, 0, 0};
+        RET(partition_nodes(h, h->d_mask, sg, cl, cg));
+        root.b = 0; root.e = cl[0].left; root.buf = 0;     // sampled rows first
     } else {
         root.b = 0; root.e = h->N; root.buf = -1;
     }
-    h->root_begin = root.e;   // rows at or beyond are unsampled
 
     auto alloc_node = [&](int parent) -> int {     // Tree.AllocTreeNode (J/data/gbdt/Tree.java:58-64)
         if (out->n_nodes >= out->capacity) return -1;
@@ -725,44 +867,45 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         out->node_info[nid] = ns[nid].node_value * lr;
         out->left[nid] = -1; out->right[nid] = -1;
         h->leaf_nodes.push_back(nid);
+        if (unbounded) h->pool.release(nid);       // only recycles memory; the reference keeps it unused
     };
     auto pool_slot = [&](int nid, long long** buf) -> int {
         bool fresh = false;
-        HistPool::Item* it = h->pool.alloc(nid, &fresh);
+        HistPool::Item* it = h->pool.alloc(nid, &fresh, unbounded);
         if (fresh) CK(cudaMalloc(&it->buf, h->seg_max * sizeof(long long)));
         *buf = it->buf;
         return YTK_OK;
     };
-    auto global_count = [&](int64_t local, int64_t* global) -> int {   // allreduce(long, SUM) (:518)
-        if (W == 1) { *global = local; return YTK_OK; }
-        h->mail->counts[0].left = local; h->mail->counts[0].right = 0;
-        CK(cudaMemcpyAsync(h->d_counts, &h->mail->counts[0], sizeof(ytk::PartitionCounts), cudaMemcpyHostToDevice, h->st));
-        NK(ytk::nccl_api().AllReduce(h->d_counts, h->d_counts + 1, 2, ncclInt64, ncclSum, h->comm, h->st));
-        CK(cudaMemcpyAsync(&h->mail->counts[1], h->d_counts + 1, sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost, h->st));
-        CK(cudaStreamSynchronize(h->st));
-        *global = h->mail->counts[1].left;
-        return YTK_OK;
-    };
 
     out->n_nodes = 0;
-    int root_id = alloc_node(-1);
+    const int root_id = alloc_node(-1);
     ns.emplace_back();
     iv.push_back(root);
-    RET(global_count(root.e - root.b, &ns[root_id].sample_cnt));      // initTreeMakerNodeStats(0) (:510-520)
+    {   // initTreeMakerNodeStats(0) (:510-520): allreduce(long, SUM)
+        int64_t local = root.e - root.b, global = local;
+        if (h->world > 1) {
+            CK(h->t_counts.reserve(2));
+            CK(h->h_counts.reserve(2));
+            h->h_counts.h[0].left = local; h->h_counts.h[0].right = 0;
+            CK(cudaMemcpyAsync(h->t_counts.d, h->h_counts.h, sizeof(ytk::PartitionCounts), cudaMemcpyHostToDevice, h->st));
+            NK(ytk::nccl_api().AllReduce(h->t_counts.d, h->t_counts.d + 1, 2, ncclInt64, ncclSum, h->comm, h->st));
+            CK(cudaMemcpyAsync(h->h_counts.h + 1, h->t_counts.d + 1, sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost, h->st));
+            CK(cudaStreamSynchronize(h->st));
+            global = h->h_counts.h[1].left;
+        }
+        ns[root_id].sample_cnt = global;
+    }
 
+    std::vector<ytk_split> recs;
     // ---- findBestSplit(root) (:302-318)
     {
         double t0 = now_ms();
         long long* slot;
         RET(pool_slot(root_id, &slot));
-        RET(build_node_hist(h, iv[root_id], slot, T, n_sel));
+        RET(build_hists(h, {{root_id, slot}}, T, n_sel));
         double t1 = now_ms();
-        long long* hs[1] = {slot};
-        int64_t sc[1] = {ns[root_id].sample_cnt};
-        RET(search_nodes(h, 1, hs, sc, first_owned));
-        ytk_split rec;
-        merged_record(h, 1, 0, &rec);
-        apply_record(ns[root_id], rec);
+        RET(search_nodes(h, {{slot, (long long)ns[root_id].sample_cnt}}, first_owned, recs));
+        apply_record(ns[root_id], recs[0]);
         set_split_if_good(root_id);
         T->build_hist += t1 - t0;
         T->find_best_split += now_ms() - t1;
@@ -773,7 +916,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     queue.push_back({root_id, ns[root_id].best_lc, 0, seq++});
     int num_leaf = 1;
 
-    while (!queue.empty()) {
+    auto pop_next = [&]() -> ExpandNode {
         // PriorityQueue.poll with lossChgComparator / sequenceComparator (:105-115)
         size_t bi = 0;
         for (size_t i = 1; i < queue.size(); i++) {
@@ -784,100 +927,148 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         }
         ExpandNode e = queue[bi];
         queue.erase(queue.begin() + bi);
-        const int nid = e.nid;
+        return e;
+    };
 
-        if ((double)e.loss_chg <= p.min_split_loss
-            || (p.max_depth >= 0 && p.max_depth == e.depth)
-            || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf)
-            || (p.min_split_samples > 0 && ns[nid].sample_cnt < p.min_split_samples)) {
-            set_leaf(nid);
-            continue;
+    while (!queue.empty()) {
+        // ---- pop: one node (the reference's order), or -- level-wise with an unbounded pool -- every
+        // node of the level, which the reference would pop back to back in the same (seq) order
+        std::vector<SplitJob> jobs;
+        const size_t n_pop = batch_levels ? queue.size() : 1;
+        for (size_t q = 0; q < n_pop; q++) {
+            ExpandNode e = pop_next();
+            const int nid = e.nid;
+            if ((double)e.loss_chg <= p.min_split_loss
+                || (p.max_depth >= 0 && p.max_depth == e.depth)
+                || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf)
+                || (p.min_split_samples > 0 && ns[nid].sample_cnt < p.min_split_samples)) {
+                set_leaf(nid);
+                continue;
+            }
+            int l = alloc_node(nid), r = alloc_node(nid);                 // tree.addChilds (:256)
+            if (l < 0 || r < 0) return fail(YTK_ERR_CAPACITY, "make_tree: tree needs more than %d nodes", out->capacity);
+            out->left[nid] = l; out->right[nid] = r;
+            ns.emplace_back(); ns.emplace_back();
+            iv.emplace_back(); iv.emplace_back();
+            num_leaf++;
+            // first two clauses of the children-are-leaves test (:266-267); the third needs the counts
+            bool term = (p.max_depth >= 0 && p.max_depth == e.depth + 1) || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf);
+            jobs.push_back({nid, l, r, e.depth, term});
         }
-        int l = alloc_node(nid), r = alloc_node(nid);                 // tree.addChilds (:256)
-        if (l < 0 || r < 0) return fail(YTK_ERR_CAPACITY, "make_tree: tree needs more than %d nodes", out->capacity);
-        out->left[nid] = l; out->right[nid] = r;
-        ns.emplace_back(); ns.emplace_back();
-        num_leaf++;
+        if (jobs.empty()) continue;
+        const int m = (int)jobs.size();
 
-        // ---- position.resetPosition (:260)
+        // ---- position.resetPosition (:260) + initTreeMakerNodeStats(l, r) (:264)
         double t0 = now_ms();
-        const Interval pv = iv[nid];
-        const int cbuf = pv.buf == 0 ? 1 : 0;
-        CK(ytk::launch_partition(h->d_bins, h->S8, pv.buf < 0 ? nullptr : h->d_rowidx[pv.buf], h->d_rowidx[cbuf],
-                                 pv.b, pv.e, out->fid[nid], out->node_info[nid], h->d_scratch, h->d_counts, h->st,
-                                 &h->launches));
-        if (W > 1)   // initTreeMakerNodeStats(l, r): allreduceArray(long[2], SUM) (:538)
-            NK(ytk::nccl_api().AllReduce(h->d_counts, h->d_counts + 1, 2, ncclInt64, ncclSum, h->comm, h->st));
-        CK(cudaMemcpyAsync(h->mail->counts, h->d_counts, (W > 1 ? 2 : 1) * sizeof(ytk::PartitionCounts),
-                           cudaMemcpyDeviceToHost, h->st));
-        CK(cudaStreamSynchronize(h->st));
-        const int64_t lc = h->mail->counts[0].left;
-        Interval li, ri;
-        li.b = pv.b; li.e = pv.b + lc; li.buf = cbuf;
-        ri.b = pv.b + lc; ri.e = pv.e; ri.buf = cbuf;
-        iv.push_back(li); iv.push_back(ri);
-        const ytk::PartitionCounts gc = h->mail->counts[W > 1 ? 1 : 0];
-        ns[l].sample_cnt = gc.left; ns[r].sample_cnt = gc.right;
+        std::vector<ytk::SplitSeg> segs(m);
+        for (int k = 0; k < m; k++) {
+            const Interval& pv = iv[jobs[k].nid];
+            segs[k] = {(long long)pv.b, (long long)pv.e, pv.buf, out->fid[jobs[k].nid], out->node_info[jobs[k].nid], 0, 0, 0};
+        }
+        RET(partition_nodes(h, h->d_bins, segs, cl, cg));
+        for (int k = 0; k < m; k++) {
+            const SplitJob& j = jobs[k];
+            const Interval pv = iv[j.nid];
+            const int cbuf = pv.buf == 0 ? 1 : 0;
+            iv[j.l].b = pv.b; iv[j.l].e = pv.b + cl[k].left; iv[j.l].buf = cbuf;
+            iv[j.r].b = pv.b + cl[k].left; iv[j.r].e = pv.e; iv[j.r].buf = cbuf;
+            ns[j.l].sample_cnt = cg[k].left; ns[j.r].sample_cnt = cg[k].right;
+            if (p.min_split_samples > 0 && ns[j.l].sample_cnt < p.min_split_samples
+                && ns[j.r].sample_cnt < p.min_split_samples)
+                jobs[k].terminal = true;
+        }
         T->partition += now_ms() - t0;
 
-        // smaller child: strictly fewer global rows on the left, else the right (:344-350, :493-499)
-        const int small = ns[l].sample_cnt < ns[r].sample_cnt ? l : r;
-        const int large = small == l ? r : l;
-
-        if ((p.max_depth >= 0 && p.max_depth == e.depth + 1)
-            || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf)
-            || (p.min_split_samples > 0 && ns[l].sample_cnt < p.min_split_samples
-                && ns[r].sample_cnt < p.min_split_samples)) {
-            // ---- computeLeafStats (:341-385)
-            t0 = now_ms();
-            CK(cudaMemsetAsync(h->d_leaf, 0, 2 * sizeof(long long), h->st));
-            CK(ytk::launch_leaf_sums(h->d_gq, h->d_rowidx[iv[small].buf], iv[small].b, iv[small].e, h->d_leaf, h->st));
-            h->launches++;
-            if (W > 1) NK(ytk::nccl_api().AllReduce(h->d_leaf, h->d_leaf, 2, ncclInt64, ncclSum, h->comm, h->st));
-            CK(cudaMemcpyAsync(h->mail->leaf, h->d_leaf, 2 * sizeof(long long), cudaMemcpyDeviceToHost, h->st));
-            CK(cudaMemcpyAsync(&h->mail->scale, h->d_scale, sizeof(ytk::GradScale), cudaMemcpyDeviceToHost, h->st));
-            CK(cudaStreamSynchronize(h->st));
-            NodeStats &ss = ns[small], &ls = ns[large], &ps = ns[nid];
-            ss.sumG = (double)h->mail->leaf[0] * h->mail->scale.inv_g;
-            ss.sumH = (double)h->mail->leaf[1] * h->mail->scale.inv_h;
-            ls.sumG = ps.sumG - ss.sumG; ls.sumH = ps.sumH - ss.sumH;
-            for (NodeStats* s : {&ss, &ls}) {
-                // host mirror of UpdateStrategy.calcGain / calcNodeValue (same formulas as kernels.cu)
-                ytk_split tmp;
-                ytk_host_node_value(&p, s->sumG, s->sumH, &tmp.root_gain, &tmp.node_value);
-                s->root_gain = tmp.root_gain; s->node_value = tmp.node_value;
+        // ---- children: leaf statistics (computeLeafStats :341-385) or histograms + split search
+        t0 = now_ms();
+        std::vector<ytk::RowItem> leaf_items;
+        std::vector<HistJob> hist_jobs;
+        std::vector<ytk::SubItem> subs;
+        std::vector<ytk::ScanNode> scans;
+        std::vector<int> scan_nid, leaf_small(m, -1);
+        int n_leaf_jobs = 0;
+        for (int k = 0; k < m; k++) {
+            const SplitJob& j = jobs[k];
+            // smaller child: strictly fewer global rows on the left, else the right (:344-350, :493-499)
+            const int small = ns[j.l].sample_cnt < ns[j.r].sample_cnt ? j.l : j.r;
+            const int large = small == j.l ? j.r : j.l;
+            if (j.terminal) {
+                if (unbounded) h->pool.release(j.nid);
+                leaf_small[k] = small;
+                const int64_t n = iv[small].e - iv[small].b;
+                const int64_t per = std::max<int64_t>(4096, (n + 63) / 64);
+                add_row_items(leaf_items, iv[small], n_leaf_jobs, per);
+                n_leaf_jobs++;
+                continue;
             }
-            set_leaf(l); set_leaf(r);
-            T->build_hist += now_ms() - t0;
-        } else {
-            // ---- findBestSplit(parent, l, r) (:320-339), buildHist(parent, l, r) (:489-508)
-            t0 = now_ms();
-            long long* parent_h = h->pool.get(nid);
+            // buildHist(parent, l, r) (:489-508)
+            long long* parent_h = h->pool.get(j.nid);
             long long *small_h, *large_h;
             RET(pool_slot(small, &small_h));
-            RET(build_node_hist(h, iv[small], small_h, T, n_sel));
+            hist_jobs.push_back({small, small_h});
             if (parent_h) {
-                h->pool.release(nid);
-                RET(pool_slot(large, &large_h));
-                CK(ytk::launch_hist_subtract(parent_h, small_h, large_h, h->seg_max, h->st));   // substract (:101-107)
-                h->launches++;
+                if (unbounded) {                       // sibling written over its parent
+                    h->pool.rename(j.nid, large);
+                    large_h = parent_h;
+                } else {
+                    h->pool.release(j.nid);
+                    RET(pool_slot(large, &large_h));
+                }
+                subs.push_back({parent_h, small_h, large_h});      // substract (:101-107)
             } else {
                 RET(pool_slot(large, &large_h));
-                RET(build_node_hist(h, iv[large], large_h, T, n_sel));
+                hist_jobs.push_back({large, large_h});
                 T->hist_miss++;
             }
-            double t1 = now_ms();
-            long long* hs[2] = {small_h, large_h};
-            int64_t sc[2] = {ns[small].sample_cnt, ns[large].sample_cnt};
-            RET(search_nodes(h, 2, hs, sc, first_owned));
-            ytk_split rec;
-            merged_record(h, 2, 0, &rec); apply_record(ns[small], rec); set_split_if_good(small);
-            merged_record(h, 2, 1, &rec); apply_record(ns[large], rec); set_split_if_good(large);
-            T->build_hist += t1 - t0;
-            T->find_best_split += now_ms() - t1;
-            queue.push_back({l, ns[l].best_lc, e.depth + 1, seq++});
-            queue.push_back({r, ns[r].best_lc, e.depth + 1, seq++});
+            scans.push_back({small_h, (long long)ns[small].sample_cnt}); scan_nid.push_back(small);
+            scans.push_back({large_h, (long long)ns[large].sample_cnt}); scan_nid.push_back(large);
         }
+        if (n_leaf_jobs > 0) {
+            CK(h->t_leaf.reserve(2 * (size_t)n_leaf_jobs));
+            CK(h->h_leaf.reserve(2 * (size_t)n_leaf_jobs));
+            CK(cudaMemsetAsync(h->t_leaf.d, 0, 2 * (size_t)n_leaf_jobs * sizeof(long long), h->st));
+            CK(h->t_leaf_items.upload(leaf_items, h->st));
+            CK(ytk::launch_leaf_sums(h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_leaf_items.d, (int)leaf_items.size(),
+                                     h->t_leaf.d, h->st));
+            if (!leaf_items.empty()) h->launches++;
+            if (h->world > 1)      // allreduceArray(double[2], SUM) (:375), exact in the integer domain
+                NK(ytk::nccl_api().AllReduce(h->t_leaf.d, h->t_leaf.d, 2 * (size_t)n_leaf_jobs, ncclInt64, ncclSum,
+                                             h->comm, h->st));
+            CK(cudaMemcpyAsync(h->h_leaf.h, h->t_leaf.d, 2 * (size_t)n_leaf_jobs * sizeof(long long),
+                               cudaMemcpyDeviceToHost, h->st));
+        }
+        RET(build_hists(h, hist_jobs, T, n_sel));
+        if (!subs.empty()) {
+            CK(h->t_sub.upload(subs, h->st));
+            CK(ytk::launch_hist_subtract(h->t_sub.d, (int)subs.size(), h->seg_max, h->st));
+            h->launches++;
+        }
+        double t1 = now_ms();
+        RET(search_nodes(h, scans, first_owned, recs));     // synchronises the stream
+        if (scans.empty()) CK(cudaStreamSynchronize(h->st));
+        for (size_t i = 0; i < scan_nid.size(); i++) {
+            apply_record(ns[scan_nid[i]], recs[i]);
+            set_split_if_good(scan_nid[i]);
+        }
+        int lj = 0;
+        for (int k = 0; k < m; k++) {
+            const SplitJob& j = jobs[k];
+            if (j.terminal) {
+                const int small = leaf_small[k], large = small == j.l ? j.r : j.l;
+                NodeStats &ss = ns[small], &ls = ns[large], &ps = ns[j.nid];
+                ss.sumG = (double)h->h_leaf.h[2 * lj] * h->h_scale.h->inv_g;
+                ss.sumH = (double)h->h_leaf.h[2 * lj + 1] * h->h_scale.h->inv_h;
+                ls.sumG = ps.sumG - ss.sumG; ls.sumH = ps.sumH - ss.sumH;      // setSubstract (:382)
+                for (NodeStats* s : {&ss, &ls}) ytk_host_node_value(&p, s->sumG, s->sumH, &s->root_gain, &s->node_value);
+                set_leaf(j.l); set_leaf(j.r);
+                lj++;
+            } else {
+                queue.push_back({j.l, ns[j.l].best_lc, j.depth + 1, seq++});
+                queue.push_back({j.r, ns[j.r].best_lc, j.depth + 1, seq++});
+            }
+        }
+        T->build_hist += t1 - t0;
+        T->find_best_split += now_ms() - t1;
     }
 
     for (int nid = 0; nid < out->n_nodes; nid++) {                    // updateTreeNodeStat (:387-393)
@@ -905,10 +1096,13 @@ int ytk_gbdt_get_positions(ytk_gbdt* h, int32_t* node_of_row) {
     if (h->iv.empty()) return fail(YTK_ERR_ARG, "get_positions: no tree has been made");
     CK(cudaSetDevice(h->device));
     CK(ytk::launch_fill_i32(h->d_node_of_row, h->N, -1, h->st));
+    std::vector<ytk::PosItem> items;
     for (int nid : h->leaf_nodes) {
         const Interval& v = h->iv[nid];
-        CK(ytk::launch_fill_positions(v.buf < 0 ? nullptr : h->d_rowidx[v.buf], v.b, v.e, nid, h->d_node_of_row, h->st));
+        if (v.e > v.b) items.push_back({(long long)v.b, (long long)v.e, v.buf, nid});
     }
+    CK(h->t_pos.upload(items, h->st));
+    CK(ytk::launch_fill_positions(h->d_rowidx[0], h->d_rowidx[1], h->t_pos.d, (int)items.size(), h->d_node_of_row, h->st));
     CK(cudaMemcpyAsync(node_of_row, h->d_node_of_row, h->N * sizeof(int32_t), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
     return YTK_OK;
@@ -925,8 +1119,9 @@ int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n
     if (rows && (n_rows < 0 || n_rows > h->N)) return fail(YTK_ERR_ARG, "build_hist: n_rows %lld", (long long)n_rows);
     CK(cudaSetDevice(h->device));
     int first_owned;
-    RET(set_features(h, fea_index, n_fea, &first_owned));
-    CK(ytk::launch_grad_quantize(h->d_gp, h->N, h->p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->st));
+    RET(set_features(h, fea_index, n_fea, &first_owned, nullptr));
+    CK(ytk::launch_grad_quantize(h->d_gp, h->N, h->p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->fixed_bits,
+                                 h->st));
     int64_t n = rows ? n_rows : h->N;
     if (rows && n > 0) {
         for (int64_t i = 0; i < n; i++)
@@ -935,9 +1130,15 @@ int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n
     }
     const int64_t len = 2LL * h->B;
     CK(cudaMemsetAsync(h->d_hist_flat, 0, len * sizeof(long long), h->st));
-    int launches = 0;
-    CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, rows ? h->d_rowidx[0] : nullptr, 0, n, h->F,
-                              h->d_group_mask, h->d_nbins, h->d_off_flat, h->d_hist_flat, 0, h->st, &launches));
+    std::vector<ytk::RowItem> items;
+    Interval v; v.b = 0; v.e = n; v.buf = rows ? 0 : -1;
+    add_row_items(items, v, 0, ytk::hist_rows_per_item(n, h->groups));
+    std::vector<long long*> outs(1, h->d_hist_flat);
+    CK(h->t_items.upload(items, h->st));
+    CK(h->t_seg_out.upload(outs, h->st));
+    CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_items.d,
+                              (int)items.size(), h->F, h->d_group_mask, h->d_nbins, h->d_feat_zero, h->d_off_flat, 0,
+                              h->t_seg_out.d, h->st));
     if (h->world > 1)
         NK(ytk::nccl_api().AllReduce(h->d_hist_flat, h->d_hist_flat, (size_t)len, ncclInt64, ncclSum, h->comm, h->st));
     CK(ytk::launch_hist_to_double(h->d_hist_flat, len, h->d_scale, h->d_hist_dbl, h->st));
@@ -975,7 +1176,9 @@ int ytk_gbdt_subtract_hist(ytk_gbdt* h, const double* parent, const double* smal
     CK(ytk::launch_hist_from_double(h->d_hist_dbl, len, h->d_scale_hook, h->d_hist_flat, h->st));
     CK(cudaMemcpyAsync(h->d_hist_dbl, small, len * sizeof(double), cudaMemcpyHostToDevice, h->st));
     CK(ytk::launch_hist_from_double(h->d_hist_dbl, len, h->d_scale_hook, h->d_hist_flat2, h->st));
-    CK(ytk::launch_hist_subtract(h->d_hist_flat, h->d_hist_flat2, h->d_hist_flat, len, h->st));
+    std::vector<ytk::SubItem> subs(1, {h->d_hist_flat, h->d_hist_flat2, h->d_hist_flat});
+    CK(h->t_sub.upload(subs, h->st));
+    CK(ytk::launch_hist_subtract(h->t_sub.d, 1, len, h->st));
     CK(ytk::launch_hist_to_double(h->d_hist_flat, len, h->d_scale_hook, h->d_hist_dbl, h->st));
     CK(cudaMemcpyAsync(out, h->d_hist_dbl, len * sizeof(double), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
@@ -988,7 +1191,7 @@ int ytk_gbdt_find_split(ytk_gbdt* h, const double* hist, int64_t sample_cnt, con
     if (!h->rows_set) return fail(YTK_ERR_ARG, "find_split: set_bins first");
     CK(cudaSetDevice(h->device));
     int first_owned;
-    RET(set_features(h, fea_index, n_fea, &first_owned));
+    RET(set_features(h, fea_index, n_fea, &first_owned, nullptr));
     const int64_t len = 2LL * h->B;
     RET(hook_scale(h, hist, nullptr, len));
     CK(cudaMemcpyAsync(h->d_hist_dbl, hist, len * sizeof(double), cudaMemcpyHostToDevice, h->st));
@@ -1000,11 +1203,15 @@ int ytk_gbdt_find_split(ytk_gbdt* h, const double* hist, int64_t sample_cnt, con
         if (fea_index) for (int i = 0; i < n_fea; i++) sel[fea_index[i]] = 1;
         for (int f = 0; f < h->F; f++) if (sel[f]) { first = f; break; }
     }
-    CK(ytk::launch_split_scan(h->d_hist_flat, h->d_start, h->d_off_flat, h->d_fea_sel, 0, h->F, first,
-                              h->d_scale_hook, gain_params(h->p), sample_cnt, nullptr, h->d_split_local, h->st));
-    CK(cudaMemcpyAsync(h->mail->split, h->d_split_local, sizeof(ytk_split), cudaMemcpyDeviceToHost, h->st));
+    std::vector<ytk::ScanNode> nodes(1, {h->d_hist_flat, (long long)sample_cnt});
+    CK(h->t_scan.upload(nodes, h->st));
+    CK(h->t_split_local.reserve(1));
+    CK(h->h_split.reserve(1));
+    CK(ytk::launch_split_scan(h->t_scan.d, 1, h->d_start, h->d_off_flat, h->d_fea_sel, 0, h->F, first,
+                              h->d_scale_hook, gain_params(h->p), h->t_split_local.d, h->st));
+    CK(cudaMemcpyAsync(h->h_split.h, h->t_split_local.d, sizeof(ytk_split), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
-    *out = h->mail->split[0];
+    *out = h->h_split.h[0];
     return YTK_OK;
 }
 
@@ -1019,15 +1226,18 @@ int ytk_gbdt_partition_rows(ytk_gbdt* h, const int32_t* rows, int64_t n_rows, in
         if (rows[i] < 0 || rows[i] >= h->N) return fail(YTK_ERR_ARG, "partition_rows: row %d out of range", rows[i]);
     CK(cudaSetDevice(h->device));
     if (n_rows > 0) CK(cudaMemcpyAsync(h->d_rowidx[0], rows, n_rows * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
-    int launches = 0;
-    CK(ytk::launch_partition(h->d_bins, h->S8, h->d_rowidx[0], h->d_rowidx[1], 0, n_rows, fid, cond, h->d_scratch,
-                             h->d_counts, h->st, &launches));
-    CK(cudaMemcpyAsync(h->mail->counts, h->d_counts, sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost, h->st));
+    std::vector<ytk::SplitSeg> sg(1);
+    sg[0] = {0, (long long)n_rows, 0, fid, cond, 0, 0, 0};
+    std::vector<ytk::PartitionCounts> cl, cg;
+    const int world = h->world;
+    h->world = 1;                       // a local operation: no collective in this hook
+    int rc = partition_nodes(h, h->d_bins, sg, cl, cg);
+    h->world = world;
+    RET(rc);
     if (n_rows > 0) CK(cudaMemcpyAsync(out_rows, h->d_rowidx[1], n_rows * sizeof(int32_t), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
-    *left_cnt = h->mail->counts[0].left;
+    *left_cnt = cl[0].left;
     return YTK_OK;
 }
 
 }  // extern "C"
-
