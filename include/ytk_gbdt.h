@@ -187,6 +187,26 @@ int ytk_gbdt_find_split(ytk_gbdt *h, const double *hist, int64_t sample_cnt,
 int ytk_gbdt_partition_rows(ytk_gbdt *h, const int32_t *rows, int64_t n_rows, int32_t fid,
                             float cond, int32_t *out_rows, int64_t *left_cnt);
 
+/* No counterpart in the reference: an addition for hosts that must not allocate device memory
+ * (all of it belongs to their own pool, or the hidden device-wide synchronisation of
+ * cudaMalloc/cudaFree is not acceptable where they call from).  Same operation and same kernels
+ * as ytk_gbdt_partition_rows, but stateless and on DEVICE buffers the caller already owns:
+ *   d_bins      uint8 slots, row-major, `stride` bytes per row
+ *   d_rows_in   n_rows row ids;  d_rows_out  n_rows ids, left rows first, both sides in input order
+ *   d_left_cnt  one int64: number of rows with (float)slot(row,fid) < cond
+ * Work is queued on `cuda_stream` (a cudaStream_t, NULL = default stream); results are valid once
+ * that stream has reached this point.  The call itself calls no cudaMalloc/cudaFree: its work space
+ * is a fixed array inside the library, 4 MiB + 17 KiB held on every GPU that loads the library
+ * until the process exits.  Hence:
+ *   - at most 4,194,304 rows per call, more is refused with YTK_ERR_CAPACITY;
+ *   - the array is shared by all calls in the process: two calls that can run on the same GPU at
+ *     the same time (different streams or threads) race on it -- keep them ordered;
+ *   - the first call on each GPU also looks up the array's device address (the device that is
+ *     current at the call); make that first call before any stream capture. */
+int ytk_gbdt_partition_rows_static(const uint8_t *d_bins, int32_t stride, const int32_t *d_rows_in,
+                                   int64_t n_rows, int32_t fid, float cond, int32_t *d_rows_out,
+                                   int64_t *d_left_cnt, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

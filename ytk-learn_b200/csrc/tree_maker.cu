@@ -52,6 +52,10 @@ int fail(int code, const char* fmt, ...) {
         if (r__ != YTK_OK) return r__; \
     } while (0)
 
+}  // namespace
+namespace ytk { void set_last_error(const char* msg) { g_err = msg ? msg : ""; } }
+namespace {
+
 double now_ms() {
     using namespace std::chrono;
     return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
