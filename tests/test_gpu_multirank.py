@@ -1,0 +1,82 @@
+"""N-GPU run of the real NCCL path (needs >= 2 GPUs; `gpurun --gpus 2`): rows sharded over the ranks,
+histogram reduce-scatter by feature range + split allgather.  Integer accumulation makes the tree
+independent of the number of ranks, so the 2-GPU tree must equal the 1-GPU tree bit for bit, and both
+must match the oracle run with W = 2 emulated workers."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("gpu_required")]
+
+KW = dict(max_depth=6, max_leaf_cnt=-1, grow_policy="level", min_child_hessian_sum=1.0,
+          min_split_loss=0.0, l1=0.0, l2=1.0, learning_rate=0.1)
+CASES = {"level": KW, "loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=24),
+         "few_features": dict(KW, max_depth=4)}
+
+
+def _data(case):
+    from gpu_common import synth
+    if case == "few_features":                      # fewer features than some world sizes would own evenly
+        return synth(20000, 3, [17, 255, 4], 5)
+    return synth(60000, 28, 255, 91, skew=True)
+
+
+def _rank(rank, world, nccl_id, case, ret):
+    sys.path.insert(0, HERE)
+    sys.path.insert(0, os.path.dirname(HERE))
+    import _pkg
+    yb = _pkg.load()
+    x, start, gp = _data(case)
+    n = x.shape[0]
+    lo, hi = n * rank // world, n * (rank + 1) // world
+    p = yb.make_params(**CASES[case])
+    tm = yb.GpuTreeMaker(p, start, hi - lo, device=rank, rank=rank, world=world, nccl_id=nccl_id)
+    tm.upload_rows(x[lo:hi])
+    tm.set_grads(gp.reshape(n, 2)[lo:hi].reshape(-1))
+    tree = tm.make(0)
+    pos = tm.get_positions()
+    hist = tm.build_hist(0)                         # reduced over ranks: the global root histogram
+    ret[rank] = ({name: getattr(tree, name) for name, _ in yb.Tree.FIELDS}, pos, hist)
+    tm.close()
+
+
+@pytest.mark.parametrize("case", list(CASES))
+def test_two_gpus_equal_one_gpu_and_oracle(case):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    import oracle_binding as ob
+    from gpu_common import assert_same_tree, maker, yb
+    world = 2
+    x, start, gp = _data(case)
+    n = x.shape[0]
+    one = maker(CASES[case], x, start, gp)
+    t1 = one.make(0)
+    p1 = one.get_positions()
+    h1 = one.build_hist(0)
+    ctx = mp.get_context("spawn")
+    mgr = ctx.Manager()
+    ret = mgr.dict()
+    nid = yb.nccl_unique_id()
+    procs = [ctx.Process(target=_rank, args=(r, world, nid, case, ret)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(240)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+    assert [p.exitcode for p in procs] == [0] * world
+    pos = np.concatenate([ret[r][1] for r in range(world)])
+    for r in range(world):
+        for name, _ in yb.Tree.FIELDS:
+            assert np.array_equal(ret[r][0][name], getattr(t1, name), equal_nan=True), (r, name)
+        assert np.array_equal(ret[r][2], h1)
+    assert np.array_equal(pos, p1)
+    o, opos, _ = ob.make_tree(ob.make_params(**CASES[case]), x, gp, 0, start, W=world)
+    assert_same_tree(t1, o)
+    assert np.array_equal(p1, opos)
