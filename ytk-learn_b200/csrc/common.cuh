@@ -55,11 +55,13 @@ struct PosItem { long long begin, end; int buf; int nid; };
 
 // ---- launchers (kernels.cu); all asynchronous on `st`, return cudaGetLastError() ----
 
+// both also write the feature-major copy col[f * col_stride + row] the partition gathers from
 cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, int32_t F,
-                               uint8_t* bins, int32_t S8, int* bad_flag, cudaStream_t st);
+                               uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, int* bad_flag,
+                               cudaStream_t st);
 cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t stride, int32_t F,
                                  const float* cuts, const int32_t* start, uint8_t* bins, int32_t S8,
-                                 cudaStream_t st);
+                                 uint8_t* col, int64_t col_stride, cudaStream_t st);
 cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, int32_t F, int32_t* out,
                                cudaStream_t st);
 
@@ -93,7 +95,8 @@ cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t*
 constexpr int kPartThreads = 256;
 constexpr int kPartItems = 8;
 constexpr int kPartTile = kPartThreads * kPartItems;
-cudaError_t launch_partition(const uint8_t* src, int32_t S8, int32_t* rowidx0, int32_t* rowidx1,
+// src: col_stride > 0 -> feature-major slots src[fid * col_stride + row]; else row-major with S8 bytes per row
+cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, int32_t* rowidx0, int32_t* rowidx1,
                              const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                              uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st);
 
@@ -104,6 +107,7 @@ cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx0, const int32
 cudaError_t launch_fill_positions(const int32_t* rowidx0, const int32_t* rowidx1, const PosItem* items, int n_items,
                                   int32_t* node_of_row, cudaStream_t st);
 cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st);
+cudaError_t launch_zero_segments(long long* const* dst, int n, int64_t len, cudaStream_t st);
 cudaError_t launch_copy_segments(const long long* src, long long* const* dst, int n, int64_t len, cudaStream_t st);
 
 }  // namespace ytk

@@ -20,7 +20,8 @@ namespace ytk {
 //     feature group and row).
 // ------------------------------------------------------------------------------------
 __global__ void repack_rows_k(const int32_t* __restrict__ x, int64_t nrows, int32_t stride, int32_t F,
-                              uint8_t* __restrict__ bins, int32_t S8, int* bad_flag) {
+                              uint8_t* __restrict__ bins, int32_t S8, uint8_t* __restrict__ col, int64_t col_stride,
+                              int* bad_flag) {
     int64_t total = nrows * S8;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
@@ -31,6 +32,7 @@ __global__ void repack_rows_k(const int32_t* __restrict__ x, int64_t nrows, int3
             int32_t v = x[r * stride + f];
             if (v < 0 || v >= kMaxBins) { *bad_flag = 1; v = 0; }
             b = (uint8_t)v;
+            col[f * col_stride + r] = b;
         }
         bins[i] = b;
     }
@@ -61,7 +63,7 @@ __device__ __forceinline__ int32_t find_bin(const float* __restrict__ c, int32_t
 
 __global__ void quantize_rows_k(const int32_t* __restrict__ xbits, int64_t nrows, int32_t stride, int32_t F,
                                 const float* __restrict__ cuts, const int32_t* __restrict__ start,
-                                uint8_t* __restrict__ bins, int32_t S8) {
+                                uint8_t* __restrict__ bins, int32_t S8, uint8_t* __restrict__ col, int64_t col_stride) {
     int64_t total = nrows * S8;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
@@ -72,6 +74,7 @@ __global__ void quantize_rows_k(const int32_t* __restrict__ xbits, int64_t nrows
             float v = __int_as_float(xbits[r * stride + f]);
             int32_t s0 = start[f];
             b = (uint8_t)find_bin(cuts + s0, start[f + 1] - s0, v);
+            col[f * col_stride + r] = b;
         }
         bins[i] = b;
     }
@@ -334,6 +337,13 @@ __global__ void hist_from_double_k(const double* __restrict__ in, int64_t len,
         hist[i] = __double2ll_rn(in[i] * ((i & 1) ? mh : mg));
 }
 
+__global__ void zero_segments_k(long long* const* __restrict__ dst, int64_t len) {
+    long long* d = dst[blockIdx.y];
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
+         i += (int64_t)gridDim.x * blockDim.x)
+        d[i] = 0;
+}
+
 __global__ void copy_segments_k(const long long* __restrict__ src, long long* const* __restrict__ dst, int64_t len) {
     const long long* s = src + blockIdx.y * len;
     long long* d = dst[blockIdx.y];
@@ -384,7 +394,7 @@ __device__ __forceinline__ double calc_gain(const GainParams& p, double G, doubl
     return __dmul_rn(-2.0, __dadd_rn(__dadd_rn(a, b), c));
 }
 
-constexpr int kScanWarps = 8;
+constexpr int kScanWarps = 32;
 
 __global__ void __launch_bounds__(kScanWarps * 32)
 split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ start,
@@ -437,7 +447,10 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
             for (int c0 = 0; c0 < nb; c0 += 32) {
                 int j = c0 + lane;
                 long long g = 0, h = 0;
-                if (j < nb) { g = hp[2 * j]; h = hp[2 * j + 1]; }
+                if (j < nb) {
+                    longlong2 gh = *reinterpret_cast<const longlong2*>(hp + 2 * j);
+                    g = gh.x; h = gh.y;
+                }
                 bool ne = (g | h) != 0;                                   // hasSample
                 long long pg = g, ph = h;
                 for (int d = 1; d < 32; d <<= 1) {
@@ -506,7 +519,7 @@ __device__ __forceinline__ const int32_t* seg_src(const SplitSeg& s, const int32
 }
 
 __global__ void __launch_bounds__(kPartThreads)
-partition_count_k(const uint8_t* __restrict__ src, int32_t S8, const int32_t* __restrict__ rowidx0,
+partition_count_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, const int32_t* __restrict__ rowidx0,
                   const int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs,
                   const int* __restrict__ tile_seg, uint8_t* __restrict__ flags, int32_t* __restrict__ block_cnt) {
     __shared__ int s_cnt[kPartThreads / 32];
@@ -520,8 +533,9 @@ partition_count_k(const uint8_t* __restrict__ src, int32_t S8, const int32_t* __
         if (i < sg.end) {
             int32_t rid = rowidx ? rowidx[i] : (int32_t)i;
             bool left;
-            if (sg.fid >= 0) left = (float)src[(long long)rid * S8 + sg.fid] < sg.cond;
-            else left = src[rid] != 0;
+            if (sg.fid < 0) left = src[rid] != 0;
+            else if (col_stride > 0) left = (float)src[sg.fid * col_stride + rid] < sg.cond;   // feature-major copy
+            else left = (float)src[(long long)rid * S8 + sg.fid] < sg.cond;
             flags[i] = left ? 1 : 0;
             cnt += left ? 1 : 0;
         }
@@ -585,24 +599,41 @@ partition_scatter_k(int32_t* __restrict__ rowidx0, int32_t* __restrict__ rowidx1
                     const uint8_t* __restrict__ flags, const int32_t* __restrict__ block_off,
                     const PartitionCounts* __restrict__ counts) {
     __shared__ int s_warp[kPartThreads / 32];
+    __shared__ int32_t s_rows[kPartTile];      // the tile, left rows first, both sides in input order
     const int seg = tile_seg[blockIdx.x];
     const SplitSeg sg = segs[seg];
     const int32_t* __restrict__ rowidx = seg_src(sg, rowidx0, rowidx1);
     int32_t* __restrict__ out = (sg.buf == 0) ? rowidx1 : rowidx0;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long tile_begin = sg.begin + (long long)(blockIdx.x - sg.tile0) * kPartTile;
+    const int tile_n = (int)min((long long)kPartTile, sg.end - tile_begin);
     // thread t owns items [t*8, t*8+8) of the tile so that order is preserved
-    const long long base = sg.begin + (long long)(blockIdx.x - sg.tile0) * kPartTile + threadIdx.x * kPartItems;
+    const int first = threadIdx.x * kPartItems;
     int32_t rid[kPartItems];
     bool fl[kPartItems];
     int cnt = 0;
+    if (first + kPartItems <= tile_n && rowidx &&
+        ((reinterpret_cast<unsigned long long>(rowidx + tile_begin + first) & 15ull) == 0) &&
+        ((reinterpret_cast<unsigned long long>(flags + tile_begin + first) & 7ull) == 0)) {
+        // full, aligned run: two 128-bit loads of row ids and one 64-bit load of flags
+        const int4* rp = reinterpret_cast<const int4*>(rowidx + tile_begin + first);
+        int4 r0 = rp[0], r1 = rp[1];
+        rid[0] = r0.x; rid[1] = r0.y; rid[2] = r0.z; rid[3] = r0.w;
+        rid[4] = r1.x; rid[5] = r1.y; rid[6] = r1.z; rid[7] = r1.w;
+        unsigned long long f8 = *reinterpret_cast<const unsigned long long*>(flags + tile_begin + first);
 #pragma unroll
-    for (int k = 0; k < kPartItems; k++) {
-        long long i = base + k;
-        fl[k] = false;
-        if (i < sg.end) {
-            rid[k] = rowidx ? rowidx[i] : (int32_t)i;
-            fl[k] = flags[i] != 0;
-            cnt += fl[k] ? 1 : 0;
+        for (int k = 0; k < kPartItems; k++) { fl[k] = (f8 >> (8 * k)) & 1ull; cnt += fl[k] ? 1 : 0; }
+    } else {
+#pragma unroll
+        for (int k = 0; k < kPartItems; k++) {
+            long long i = tile_begin + first + k;
+            fl[k] = false;
+            rid[k] = 0;
+            if (first + k < tile_n) {
+                rid[k] = rowidx ? rowidx[i] : (int32_t)i;
+                fl[k] = flags[i] != 0;
+                cnt += fl[k] ? 1 : 0;
+            }
         }
     }
     int p = cnt;
@@ -612,19 +643,29 @@ partition_scatter_k(int32_t* __restrict__ rowidx0, int32_t* __restrict__ rowidx1
     }
     if (lane == 31) s_warp[warp] = p;
     __syncthreads();
-    int woff = 0;
-    for (int w = 0; w < warp; w++) woff += s_warp[w];
-    long long lefts_before = (long long)block_off[blockIdx.x] + woff + p - cnt;  // lefts before my first item
-    const long long left_total = counts[seg].left;
-    long long lpos = sg.begin + lefts_before;
-    long long rpos = sg.begin + left_total + ((base - sg.begin) - lefts_before);
+    int woff = 0, tile_left = 0;
+    for (int w = 0; w < kPartThreads / 32; w++) {
+        if (w < warp) woff += s_warp[w];
+        tile_left += s_warp[w];
+    }
+    int lpos = woff + p - cnt;                           // lefts of this tile before my first item
+    int rpos = tile_left + (first - lpos);               // rights go after all lefts of the tile
 #pragma unroll
     for (int k = 0; k < kPartItems; k++) {
-        long long i = base + k;
-        if (i < sg.end) {
-            if (fl[k]) out[lpos++] = rid[k];
-            else out[rpos++] = rid[k];
+        if (first + k < tile_n) {
+            if (fl[k]) s_rows[lpos++] = rid[k];
+            else s_rows[rpos++] = rid[k];
         }
+    }
+    __syncthreads();
+    // coalesced write-out of the two runs
+    const long long left_total = counts[seg].left;
+    const long long lefts_before_tile = block_off[blockIdx.x];
+    const long long ldst = sg.begin + lefts_before_tile;
+    const long long rdst = sg.begin + left_total + ((tile_begin - sg.begin) - lefts_before_tile);
+    for (int i = threadIdx.x; i < tile_n; i += kPartThreads) {
+        if (i < tile_left) out[ldst + i] = s_rows[i];
+        else out[rdst + (i - tile_left)] = s_rows[i];
     }
 }
 
@@ -674,16 +715,17 @@ static inline int grid_for(int64_t n, int threads, int max_blocks = kNumSMs * 8)
 }
 
 cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, int32_t F, uint8_t* bins,
-                               int32_t S8, int* bad_flag, cudaStream_t st) {
+                               int32_t S8, uint8_t* col, int64_t col_stride, int* bad_flag, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    repack_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, bins, S8, bad_flag);
+    repack_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, bins, S8, col, col_stride, bad_flag);
     return cudaGetLastError();
 }
 cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t stride, int32_t F,
                                  const float* cuts, const int32_t* start, uint8_t* bins, int32_t S8,
-                                 cudaStream_t st) {
+                                 uint8_t* col, int64_t col_stride, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    quantize_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(xbits, nrows, stride, F, cuts, start, bins, S8);
+    quantize_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(xbits, nrows, stride, F, cuts, start, bins, S8, col,
+                                                               col_stride);
     return cudaGetLastError();
 }
 cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, int32_t F, int32_t* out,
@@ -747,6 +789,12 @@ cudaError_t launch_hist_from_double(const double* in, int64_t len, const GradSca
     hist_from_double_k<<<grid_for(len, 256), 256, 0, st>>>(in, len, scale, hist);
     return cudaGetLastError();
 }
+cudaError_t launch_zero_segments(long long* const* dst, int n, int64_t len, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n);
+    zero_segments_k<<<grid, 256, 0, st>>>(dst, len);
+    return cudaGetLastError();
+}
 cudaError_t launch_copy_segments(const long long* src, long long* const* dst, int n, int64_t len, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
     dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n);
@@ -763,13 +811,13 @@ cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t*
     return cudaGetLastError();
 }
 
-cudaError_t launch_partition(const uint8_t* src, int32_t S8, int32_t* rowidx0, int32_t* rowidx1,
+cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, int32_t* rowidx0, int32_t* rowidx1,
                              const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                              uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st) {
     if (n_segs <= 0) return cudaSuccess;
     if (n_tiles > 0)
-        partition_count_k<<<n_tiles, kPartThreads, 0, st>>>(src, S8, rowidx0, rowidx1, segs, tile_seg, flags,
-                                                            block_cnt);
+        partition_count_k<<<n_tiles, kPartThreads, 0, st>>>(src, S8, col_stride, rowidx0, rowidx1, segs, tile_seg,
+                                                            flags, block_cnt);
     partition_scan_k<<<n_segs, 1024, 0, st>>>(segs, block_cnt, counts);
     if (n_tiles > 0)
         partition_scatter_k<<<n_tiles, kPartThreads, 0, st>>>(rowidx0, rowidx1, segs, tile_seg, flags, block_cnt,

@@ -134,6 +134,33 @@ int java_float_compare(float a, float b) {   // java.lang.Float.compare
     return ia == ib ? 0 : (ia < ib ? -1 : 1);
 }
 
+// Pinned staging for the small work tables: a bump allocator that is rewound whenever the stream
+// has been synchronised (twice per batch), so uploads are true async copies and never make the
+// host wait for kernels already queued.
+struct PinnedArena {
+    char* h = nullptr;
+    size_t cap = 0, off = 0;
+    void* take(size_t bytes, cudaStream_t st) {
+        bytes = (bytes + 255) & ~size_t(255);
+        if (off + bytes > cap) {
+            if (cudaStreamSynchronize(st) != cudaSuccess) return nullptr;     // everything staged so far is consumed
+            off = 0;
+            if (bytes > cap) {
+                if (h) cudaFreeHost(h);
+                h = nullptr; cap = 0;
+                size_t nc = std::max<size_t>(bytes * 2, size_t(4) << 20);
+                if (cudaHostAlloc((void**)&h, nc, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+                cap = nc;
+            }
+        }
+        void* p = h + off;
+        off += bytes;
+        return p;
+    }
+    void rewind() { off = 0; }
+    void release() { if (h) cudaFreeHost(h); h = nullptr; cap = off = 0; }
+};
+
 // growable device array + host->device upload of a work table
 template <typename T>
 struct DevTable {
@@ -148,12 +175,14 @@ struct DevTable {
         if (e == cudaSuccess) cap = nc;
         return e;
     }
-    cudaError_t upload(const std::vector<T>& v, cudaStream_t st) {
+    cudaError_t upload(const std::vector<T>& v, cudaStream_t st, PinnedArena& arena) {
         if (v.empty()) return cudaSuccess;
         cudaError_t e = reserve(v.size());
         if (e != cudaSuccess) return e;
-        // pageable source: the runtime stages it before returning, so `v` may die afterwards
-        return cudaMemcpyAsync(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
+        void* stage = arena.take(v.size() * sizeof(T), st);
+        if (!stage) return cudaErrorMemoryAllocation;
+        memcpy(stage, v.data(), v.size() * sizeof(T));
+        return cudaMemcpyAsync(d, stage, v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
     }
     void release() { if (d) cudaFree(d); d = nullptr; cap = 0; }
 };
@@ -234,6 +263,7 @@ struct ytk_gbdt {
     int64_t seg_max = 0;      // owned-segment length (int64 words), equal on every rank
 
     uint8_t* d_bins = nullptr;
+    uint8_t* d_bins_col = nullptr;     // feature-major copy [F][N] for the partition's one-byte gathers
     float* d_gp = nullptr;
     int2* d_gq = nullptr;
     int32_t* d_rowidx[2] = {nullptr, nullptr};
@@ -274,6 +304,7 @@ struct ytk_gbdt {
     PinnedBuf<ytk_split> h_split;
     PinnedBuf<long long> h_leaf;
     PinnedBuf<ytk::GradScale> h_scale;
+    PinnedArena arena;
 
     HistPool pool;
     bool grads_set = false, rows_set = false;
@@ -310,7 +341,7 @@ int ensure_stage(ytk_gbdt* h, size_t bytes) {
 void free_all(ytk_gbdt* h) {
     cudaSetDevice(h->device);
     auto F = [](void* p) { if (p) cudaFree(p); };
-    F(h->d_bins); F(h->d_gp); F(h->d_gq); F(h->d_rowidx[0]); F(h->d_rowidx[1]); F(h->d_flags); F(h->d_block_cnt);
+    F(h->d_bins); F(h->d_bins_col); F(h->d_gp); F(h->d_gq); F(h->d_rowidx[0]); F(h->d_rowidx[1]); F(h->d_flags); F(h->d_block_cnt);
     F(h->d_mask); F(h->d_start); F(h->d_nbins); F(h->d_feat_owner); F(h->d_feat_zero); F(h->d_off_inner);
     F(h->d_off_flat); F(h->d_group_mask); F(h->d_fea_sel); F(h->d_hist_flat); F(h->d_hist_flat2);
     F(h->d_hist_dbl); F(h->d_scale); F(h->d_scale_hook); F(h->d_absmax); F(h->d_bad); F(h->d_node_of_row);
@@ -319,7 +350,7 @@ void free_all(ytk_gbdt* h) {
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
     h->t_split_local.release(); h->t_split_all.release(); h->t_leaf.release(); h->t_hist_local.release();
     h->t_rs_out.release();
-    h->h_counts.release(); h->h_split.release(); h->h_leaf.release(); h->h_scale.release();
+    h->h_counts.release(); h->h_split.release(); h->h_leaf.release(); h->h_scale.release(); h->arena.release();
     for (auto* it : h->pool.all) { F(it->buf); delete it; }
     for (auto e : h->ev) cudaEventDestroy(e);
     if (h->comm) ytk::nccl_api().CommDestroy(h->comm);
@@ -345,8 +376,13 @@ int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* firs
     if (n_sel) *n_sel = cnt;
     *first_owned = -1;   // firstSampledFeaIndexInThread (:451-467)
     for (int f = h->f_from; f < h->f_to; f++) if (sel[f]) { *first_owned = f; break; }
-    CK(cudaMemcpyAsync(h->d_fea_sel, sel.data(), h->F, cudaMemcpyHostToDevice, h->st));
-    CK(cudaMemcpyAsync(h->d_group_mask, gm.data(), h->groups * sizeof(uint32_t), cudaMemcpyHostToDevice, h->st));
+    void* s1 = h->arena.take(h->F, h->st);
+    void* s2 = h->arena.take(h->groups * sizeof(uint32_t), h->st);
+    if (!s1 || !s2) return fail(YTK_ERR_CUDA, "pinned staging allocation failed");
+    memcpy(s1, sel.data(), h->F);
+    memcpy(s2, gm.data(), h->groups * sizeof(uint32_t));
+    CK(cudaMemcpyAsync(h->d_fea_sel, s1, h->F, cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemcpyAsync(h->d_group_mask, s2, h->groups * sizeof(uint32_t), cudaMemcpyHostToDevice, h->st));
     return YTK_OK;
 }
 
@@ -396,14 +432,15 @@ int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T
     }
     cudaEvent_t e0, e1;
     RET(hist_events(h, &e0, &e1));
-    CK(cudaEventRecord(e0, h->st));
+    CK(h->t_items.upload(items, h->st, h->arena));
+    CK(h->t_seg_out.upload(outs, h->st, h->arena));
     if (h->world == 1) {
-        for (int k = 0; k < m; k++) CK(cudaMemsetAsync(jobs[k].dst, 0, h->seg_max * sizeof(long long), h->st));
+        CK(ytk::launch_zero_segments(h->t_seg_out.d, m, h->seg_max, h->st));
+        h->launches++;
     } else {
         CK(cudaMemsetAsync(h->t_hist_local.d, 0, (size_t)m * local_len * sizeof(long long), h->st));
     }
-    CK(h->t_items.upload(items, h->st));
-    CK(h->t_seg_out.upload(outs, h->st));
+    CK(cudaEventRecord(e0, h->st));        // the pair brackets the hist_build_k launch only
     const long long owner_stride = h->world == 1 ? 0 : (long long)m * h->seg_max;
     CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_items.d,
                               (int)items.size(), h->F, h->d_group_mask, h->d_nbins, h->d_feat_owner, h->d_off_inner,
@@ -416,7 +453,7 @@ int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T
         NK(ytk::nccl_api().ReduceScatter(h->t_hist_local.d, h->t_rs_out.d, (size_t)m * h->seg_max, ncclInt64,
                                          ncclSum, h->comm, h->st));
         for (int k = 0; k < m; k++) outs[k] = jobs[k].dst;
-        CK(h->t_seg_out.upload(outs, h->st));
+        CK(h->t_seg_out.upload(outs, h->st, h->arena));
         CK(ytk::launch_copy_segments(h->t_rs_out.d, h->t_seg_out.d, m, h->seg_max, h->st));
         h->launches++;
         T->communicate_hist += now_ms() - t0;
@@ -430,7 +467,7 @@ int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first
     const int m = (int)nodes.size();
     recs.resize(m);
     if (m == 0) return YTK_OK;
-    CK(h->t_scan.upload(nodes, h->st));
+    CK(h->t_scan.upload(nodes, h->st, h->arena));
     CK(h->t_split_local.reserve(m));
     CK(ytk::launch_split_scan(h->t_scan.d, m, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to,
                               first_owned, h->d_scale, gain_params(h->p), h->t_split_local.d, h->st));
@@ -448,6 +485,7 @@ int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first
                            cudaMemcpyDeviceToHost, h->st));
     }
     CK(cudaStreamSynchronize(h->st));
+    h->arena.rewind();
     if (h->world == 1) {
         for (int k = 0; k < m; k++) recs[k] = h->h_split.h[k];
     } else {
@@ -468,7 +506,7 @@ void apply_record(NodeStats& s, const ytk_split& r) {
 
 // position.resetPosition (SamplePositionData.java:115-133) for a batch of nodes, plus the global
 // child counts of initTreeMakerNodeStats(l, r) (:522-541).  counts_local/global: [m].
-int partition_nodes(ytk_gbdt* h, const uint8_t* src, const std::vector<ytk::SplitSeg>& segs_in,
+int partition_nodes(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const std::vector<ytk::SplitSeg>& segs_in,
                     std::vector<ytk::PartitionCounts>& local, std::vector<ytk::PartitionCounts>& global) {
     const int m = (int)segs_in.size();
     local.resize(m); global.resize(m);
@@ -488,10 +526,10 @@ int partition_nodes(ytk_gbdt* h, const uint8_t* src, const std::vector<ytk::Spli
         h->block_cnt_cap = std::max<size_t>(tile_seg.size() + 1, 2 * h->block_cnt_cap);
         CK(cudaMalloc(&h->d_block_cnt, h->block_cnt_cap * sizeof(int32_t)));
     }
-    CK(h->t_segs.upload(segs, h->st));
-    CK(h->t_tile_seg.upload(tile_seg, h->st));
+    CK(h->t_segs.upload(segs, h->st, h->arena));
+    CK(h->t_tile_seg.upload(tile_seg, h->st, h->arena));
     CK(h->t_counts.reserve(2 * (size_t)m));
-    CK(ytk::launch_partition(src, h->S8, h->d_rowidx[0], h->d_rowidx[1], h->t_segs.d, m, h->t_tile_seg.d,
+    CK(ytk::launch_partition(src, h->S8, col_stride, h->d_rowidx[0], h->d_rowidx[1], h->t_segs.d, m, h->t_tile_seg.d,
                              (int)tile_seg.size(), h->d_flags, h->d_block_cnt, h->t_counts.d, h->st));
     h->launches += tile_seg.empty() ? 1 : 3;
     const int nc = h->world > 1 ? 2 * m : m;
@@ -502,6 +540,7 @@ int partition_nodes(ytk_gbdt* h, const uint8_t* src, const std::vector<ytk::Spli
     CK(cudaMemcpyAsync(h->h_counts.h, h->t_counts.d, nc * sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost,
                        h->st));
     CK(cudaStreamSynchronize(h->st));
+    h->arena.rewind();
     for (int k = 0; k < m; k++) {
         local[k] = h->h_counts.h[k];
         global[k] = h->h_counts.h[h->world > 1 ? m + k : k];
@@ -667,6 +706,8 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
     const int K = h->p.class_num;
     CK(cudaMalloc(&h->d_bins, N1 * h->S8));
     CK(cudaMemsetAsync(h->d_bins, 0, N1 * h->S8, h->st));
+    CK(cudaMalloc(&h->d_bins_col, N1 * F));
+    CK(cudaMemsetAsync(h->d_bins_col, 0, N1 * F, h->st));
     CK(cudaMalloc(&h->d_gp, N1 * K * 2 * sizeof(float)));
     CK(cudaMalloc(&h->d_gq, N1 * sizeof(int2)));
     CK(cudaMalloc(&h->d_rowidx[0], N1 * sizeof(int32_t)));
@@ -734,7 +775,7 @@ int ytk_gbdt_upload_rows(ytk_gbdt* h, const int32_t* x_chunk, int64_t row0, int6
         RET(ensure_stage(h, bytes));
         CK(cudaMemcpyAsync(h->d_stage, x_chunk + r * stride, bytes, cudaMemcpyHostToDevice, h->st));
         CK(ytk::launch_repack_rows((const int32_t*)h->d_stage, n, stride, h->F, h->d_bins + (row0 + r) * h->S8,
-                                   h->S8, h->d_bad, h->st));
+                                   h->S8, h->d_bins_col + (row0 + r), h->N, h->d_bad, h->st));
         CK(cudaStreamSynchronize(h->st));
     }
     int bad = 0;
@@ -764,7 +805,8 @@ int ytk_gbdt_quantize_rows(ytk_gbdt* h, const int32_t* xbits_chunk, int64_t row0
         e = cudaMemcpyAsync(h->d_stage, xbits_chunk + r * stride, bytes, cudaMemcpyHostToDevice, h->st);
         if (e == cudaSuccess)
             e = ytk::launch_quantize_rows((const int32_t*)h->d_stage, n, stride, h->F, d_cuts, h->d_start,
-                                          h->d_bins + (row0 + r) * h->S8, h->S8, h->st);
+                                          h->d_bins + (row0 + r) * h->S8, h->S8, h->d_bins_col + (row0 + r), h->N,
+                                          h->st);
         if (e == cudaSuccess) e = cudaStreamSynchronize(h->st);
     }
     cudaFree(d_cuts);
@@ -845,7 +887,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         CK(cudaMemcpyAsync(h->d_mask, row_mask, h->N, cudaMemcpyHostToDevice, h->st));
         std::vector<ytk::SplitSeg> sg(1);
         sg[0] = {0, (long long)h->N, -1, -1, 0.f, 0, 0, 0};
-        RET(partition_nodes(h, h->d_mask, sg, cl, cg));
+        RET(partition_nodes(h, h->d_mask, 0, sg, cl, cg));
         root.b = 0; root.e = cl[0].left; root.buf = 0;     // sampled rows first
     } else {
         root.b = 0; root.e = h->N; root.buf = -1;
@@ -969,7 +1011,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             const Interval& pv = iv[jobs[k].nid];
             segs[k] = {(long long)pv.b, (long long)pv.e, pv.buf, out->fid[jobs[k].nid], out->node_info[jobs[k].nid], 0, 0, 0};
         }
-        RET(partition_nodes(h, h->d_bins, segs, cl, cg));
+        RET(partition_nodes(h, h->d_bins_col, h->N, segs, cl, cg));
         for (int k = 0; k < m; k++) {
             const SplitJob& j = jobs[k];
             const Interval pv = iv[j.nid];
@@ -1031,7 +1073,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             CK(h->t_leaf.reserve(2 * (size_t)n_leaf_jobs));
             CK(h->h_leaf.reserve(2 * (size_t)n_leaf_jobs));
             CK(cudaMemsetAsync(h->t_leaf.d, 0, 2 * (size_t)n_leaf_jobs * sizeof(long long), h->st));
-            CK(h->t_leaf_items.upload(leaf_items, h->st));
+            CK(h->t_leaf_items.upload(leaf_items, h->st, h->arena));
             CK(ytk::launch_leaf_sums(h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_leaf_items.d, (int)leaf_items.size(),
                                      h->t_leaf.d, h->st));
             if (!leaf_items.empty()) h->launches++;
@@ -1043,7 +1085,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         }
         RET(build_hists(h, hist_jobs, T, n_sel));
         if (!subs.empty()) {
-            CK(h->t_sub.upload(subs, h->st));
+            CK(h->t_sub.upload(subs, h->st, h->arena));
             CK(ytk::launch_hist_subtract(h->t_sub.d, (int)subs.size(), h->seg_max, h->st));
             h->launches++;
         }
@@ -1105,7 +1147,7 @@ int ytk_gbdt_get_positions(ytk_gbdt* h, int32_t* node_of_row) {
         const Interval& v = h->iv[nid];
         if (v.e > v.b) items.push_back({(long long)v.b, (long long)v.e, v.buf, nid});
     }
-    CK(h->t_pos.upload(items, h->st));
+    CK(h->t_pos.upload(items, h->st, h->arena));
     CK(ytk::launch_fill_positions(h->d_rowidx[0], h->d_rowidx[1], h->t_pos.d, (int)items.size(), h->d_node_of_row, h->st));
     CK(cudaMemcpyAsync(node_of_row, h->d_node_of_row, h->N * sizeof(int32_t), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
@@ -1138,8 +1180,8 @@ int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n
     Interval v; v.b = 0; v.e = n; v.buf = rows ? 0 : -1;
     add_row_items(items, v, 0, ytk::hist_rows_per_item(n, h->groups));
     std::vector<long long*> outs(1, h->d_hist_flat);
-    CK(h->t_items.upload(items, h->st));
-    CK(h->t_seg_out.upload(outs, h->st));
+    CK(h->t_items.upload(items, h->st, h->arena));
+    CK(h->t_seg_out.upload(outs, h->st, h->arena));
     CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_items.d,
                               (int)items.size(), h->F, h->d_group_mask, h->d_nbins, h->d_feat_zero, h->d_off_flat, 0,
                               h->t_seg_out.d, h->st));
@@ -1181,7 +1223,7 @@ int ytk_gbdt_subtract_hist(ytk_gbdt* h, const double* parent, const double* smal
     CK(cudaMemcpyAsync(h->d_hist_dbl, small, len * sizeof(double), cudaMemcpyHostToDevice, h->st));
     CK(ytk::launch_hist_from_double(h->d_hist_dbl, len, h->d_scale_hook, h->d_hist_flat2, h->st));
     std::vector<ytk::SubItem> subs(1, {h->d_hist_flat, h->d_hist_flat2, h->d_hist_flat});
-    CK(h->t_sub.upload(subs, h->st));
+    CK(h->t_sub.upload(subs, h->st, h->arena));
     CK(ytk::launch_hist_subtract(h->t_sub.d, 1, len, h->st));
     CK(ytk::launch_hist_to_double(h->d_hist_flat, len, h->d_scale_hook, h->d_hist_dbl, h->st));
     CK(cudaMemcpyAsync(out, h->d_hist_dbl, len * sizeof(double), cudaMemcpyDeviceToHost, h->st));
@@ -1208,7 +1250,7 @@ int ytk_gbdt_find_split(ytk_gbdt* h, const double* hist, int64_t sample_cnt, con
         for (int f = 0; f < h->F; f++) if (sel[f]) { first = f; break; }
     }
     std::vector<ytk::ScanNode> nodes(1, {h->d_hist_flat, (long long)sample_cnt});
-    CK(h->t_scan.upload(nodes, h->st));
+    CK(h->t_scan.upload(nodes, h->st, h->arena));
     CK(h->t_split_local.reserve(1));
     CK(h->h_split.reserve(1));
     CK(ytk::launch_split_scan(h->t_scan.d, 1, h->d_start, h->d_off_flat, h->d_fea_sel, 0, h->F, first,
@@ -1235,7 +1277,7 @@ int ytk_gbdt_partition_rows(ytk_gbdt* h, const int32_t* rows, int64_t n_rows, in
     std::vector<ytk::PartitionCounts> cl, cg;
     const int world = h->world;
     h->world = 1;                       // a local operation: no collective in this hook
-    int rc = partition_nodes(h, h->d_bins, sg, cl, cg);
+    int rc = partition_nodes(h, h->d_bins_col, h->N, sg, cl, cg);
     h->world = world;
     RET(rc);
     if (n_rows > 0) CK(cudaMemcpyAsync(out_rows, h->d_rowidx[1], n_rows * sizeof(int32_t), cudaMemcpyDeviceToHost, h->st));
