@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--leaves", type=int, default=-1)
     ap.add_argument("--cpu-rows", type=int, default=2_000_000, help="rows of the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--uniform-bins", action="store_true", help="experiment: every feature uniform over its bins")
     return ap.parse_args()
 
 
@@ -55,14 +56,14 @@ def tree_kwargs(a):
                 min_split_loss=0.0, l1=0.0, l2=0.0, learning_rate=0.1, min_split_samples=-1)
 
 
-def synth_bins(n, F, nb, seed):
+def synth_bins(n, F, nb, seed, uniform=False):
     """half the features uniform over the bins, half skewed (geometric),
     generated directly as uint8 bins; labels depend on a few features so that trees have
     real structure."""
     rng = np.random.default_rng(seed)
     x = np.empty((n, F), dtype=np.uint8)
     for f in range(F):
-        if f % 2 == 0:
+        if f % 2 == 0 or uniform:
             x[:, f] = rng.integers(0, nb, size=n, dtype=np.uint8)
         else:
             x[:, f] = np.minimum(rng.geometric(0.04, size=n) - 1, nb - 1).astype(np.uint8)
@@ -224,7 +225,7 @@ def main():
             dist.barrier()
 
     n, F = a.rows, a.features
-    xs, ys = synth_bins(n, F, a.bins, 1234 + rank)
+    xs, ys = synth_bins(n, F, a.bins, 1234 + rank, a.uniform_bins)
     start = (np.arange(F + 1) * a.bins).astype(np.int32)
     params = yb.make_params(**tree_kwargs(a))
     tm = yb.GpuTreeMaker(params, start, n, device=local, rank=rank, world=world, nccl_id=nccl_id)

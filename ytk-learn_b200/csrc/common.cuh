@@ -12,11 +12,12 @@ constexpr int kGroup = 32;        // features per group = lanes of a warp
 constexpr int kMaxBins = 256;     // uint8 slots
 constexpr int kHistThreads = 1024;
 constexpr int kHistWarps = kHistThreads / 32;
-// per-CTA shared histogram: [bin][component][feature] 32-bit words, components
-// {g_lo, g_hi, h_lo, h_hi} of two 64-bit fixed-point accumulators
+// per-CTA shared histogram: 32-bit words [bin][{lo,hi}][feature] for g, then the same for h:
+// the low-16-bit and high limbs of the fixed-point values, accumulated carry-free
 constexpr int kHistSmemBytes = kMaxBins * 4 * kGroup * 4;                 // 128 KB
 constexpr int kNumSMs = 148;
-constexpr int kDefaultFixedBits = 24;
+constexpr int kDefaultFixedBits = 30;           // |fixed-point value| < 2^30
+constexpr int kHistMaxRowsPerItem = 65536;      // so that 16-bit limb sums fit 32-bit words
 
 // Gradient fixed-point scales of the current tree: value = integer * inv[.]
 struct GradScale {
@@ -57,11 +58,11 @@ struct PosItem { long long begin, end; int buf; int nid; };
 
 // both also write the feature-major copy col[f * col_stride + row] the partition gathers from
 cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, int32_t F,
-                               uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, int* bad_flag,
-                               cudaStream_t st);
+                               uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, int64_t row_base,
+                               int* bad_flag, cudaStream_t st);
 cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t stride, int32_t F,
                                  const float* cuts, const int32_t* start, uint8_t* bins, int32_t S8,
-                                 uint8_t* col, int64_t col_stride, cudaStream_t st);
+                                 uint8_t* col, int64_t col_stride, int64_t row_base, cudaStream_t st);
 cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, int32_t F, int32_t* out,
                                cudaStream_t st);
 

@@ -21,13 +21,16 @@ namespace ytk {
 // ------------------------------------------------------------------------------------
 __global__ void repack_rows_k(const int32_t* __restrict__ x, int64_t nrows, int32_t stride, int32_t F,
                               uint8_t* __restrict__ bins, int32_t S8, uint8_t* __restrict__ col, int64_t col_stride,
-                              int* bad_flag) {
+                              int64_t row_base, int* bad_flag) {
     int64_t total = nrows * S8;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
         int64_t r = i / S8;
         int32_t f = (int32_t)(i - r * S8);
-        uint8_t b = 0;
+        // padding columns get row-varying filler: the histogram kernel accumulates them too (and drops
+        // them at flush), and identical bins in consecutive rows would make consecutive atomics hit
+        // the same shared-memory word
+        uint8_t b = (uint8_t)((r + row_base) * 37 + f * 11);
         if (f < F) {
             int32_t v = x[r * stride + f];
             if (v < 0 || v >= kMaxBins) { *bad_flag = 1; v = 0; }
@@ -63,13 +66,14 @@ __device__ __forceinline__ int32_t find_bin(const float* __restrict__ c, int32_t
 
 __global__ void quantize_rows_k(const int32_t* __restrict__ xbits, int64_t nrows, int32_t stride, int32_t F,
                                 const float* __restrict__ cuts, const int32_t* __restrict__ start,
-                                uint8_t* __restrict__ bins, int32_t S8, uint8_t* __restrict__ col, int64_t col_stride) {
+                                uint8_t* __restrict__ bins, int32_t S8, uint8_t* __restrict__ col, int64_t col_stride,
+                                int64_t row_base) {
     int64_t total = nrows * S8;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
         int64_t r = i / S8;
         int32_t f = (int32_t)(i - r * S8);
-        uint8_t b = 0;
+        uint8_t b = (uint8_t)((r + row_base) * 37 + f * 11);     // see repack_rows_k
         if (f < F) {
             float v = __int_as_float(xbits[r * stride + f]);
             int32_t s0 = start[f];
@@ -99,7 +103,7 @@ __global__ void unpack_rows_k(const uint8_t* __restrict__ bins, int32_t S8, int6
 // two chosen from max|g| (resp. max|h|) to signed integers below 2^bits and every sum
 // downstream is an exact 64-bit integer: histograms do not depend on row order, sharding
 // or pool hits, and parent - child equals the sibling bit for bit.  Per-row rounding is
-// at most 2^-(bits+1) of max|g| (bits = 24: the float grid of the largest gradient).
+// at most 2^-(bits+1) of max|g| (bits = 30 by default).
 // A non-zero value never rounds to zero, so "bin has samples" (hasSample,
 // J/optimizer/gbdt/DataParallelTreeMaker.java:657-663) is preserved exactly.
 // ------------------------------------------------------------------------------------
@@ -156,26 +160,26 @@ __global__ void grad_quantize_k(const float* __restrict__ gp, int64_t n, int32_t
 // K2: per-node (g,h) histogram -- HistogramBuilder.buildHist's accumulation loop
 //     (J/data/gbdt/HistogramBuilder.java:69-90).
 //
-// What bounds this kernel on B200 is not HBM but the shared-memory pipe: every
-// LSU-class instruction (ATOMS, LDS, SHFL, LDG) costs ~1.9 SM-cycles per warp instruction
-// (profiles/r01_microbench_smem.txt), and a (g,h) update needs two atomics.  So the
-// kernel is built to issue nothing else per row:
+// What bounds this kernel on B200 is not HBM but the shared-memory atomic pipe
+// (profiles/r01_microbench_smem.txt), so it is built to issue little else:
 //   * rows are uint8, row-major, one 32 B sector per 32-feature group, so a row reached
-//     through the row-id list costs exactly one sector; lane r of a warp loads ITS row
-//     with two 128-bit loads and its own fixed-point (g,h) with one 64-bit load -- no
-//     per-row broadcast, no staging;
-//   * at step k (0..31) lane r updates feature k^r of its row.  The 32 lanes therefore
-//     always touch 32 different features, and the shared histogram is laid out
+//     through the row-id list costs exactly one sector; a warp fetches 32 rows with two
+//     128-bit loads, adjacent lanes taking the two 16-feature halves of a row, plus that
+//     row's fixed-point (g,h) -- no staging, no per-row broadcast;
+//   * lane L works on row L>>1 and half L&1: at step k (0..15) it updates feature
+//     16*(L&1) + (k ^ (L>>1)).  The 32 lanes therefore always touch 32 different
+//     features, and the shared histogram is laid out
 //     [bin][component][feature], i.e. bank = feature: the 32 atomics of a warp
 //     instruction hit 32 different banks whatever the bins are (skewed or binary
-//     features cannot serialise it);
-//   * the 8 data words of a lane are pre-permuted by (lane>>2) so that the word needed
-//     at step k has a compile-time register index; only the byte selector depends on
-//     the lane;
-//   * accumulators are 64-bit (lo,hi words).  The low word takes a native returning
-//     ATOMS.ADD; its result tells whether a carry/borrow must go to the high word.  With
-//     24-bit fixed point that happens for about 1 lane in 500, so the high-word atomic
-//     sits behind a warp-uniform vote and is almost never issued.
+//     features cannot serialise it); the address is one PRMT (bin*256 from the data
+//     word) and one LOP3 ((bin256 | lane*4) ^ k*4);
+//   * exact 64-bit sums WITHOUT carries: each fixed-point value (|v| < 2^30) is split into
+//     its low 16 bits (unsigned) and its high part (signed, |.| <= 2^14), and the two
+//     limbs are accumulated in separate 32-bit words by fire-and-forget atomics
+//     (RED).  A work item covers at most 65536 rows, so neither limb sum can leave 32
+//     bits; the flush recombines hi*65536 + lo in 64-bit.  Detecting carries of a single
+//     64-bit accumulator instead costs more than the atomics themselves (7.5 vs 4.6
+//     SM-cycles per row, same file).
 // One CTA (32 warps, 128 KB of shared memory, 1 per SM) handles one work item: a run of
 // rows of one node and one feature group; it flushes non-empty bins with 64-bit global
 // reductions into that node's histogram.
@@ -187,9 +191,9 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
              const int32_t* __restrict__ nbins, const int32_t* __restrict__ feat_owner,
              const int64_t* __restrict__ feat_inner, long long owner_stride,
              long long* const* __restrict__ seg_out) {
-    // low words [bin][{g,h}][feature] (64 KB), then the high words in the same layout (64 KB)
+    // g limbs [bin][{lo,hi}][feature] (64 KB), then the h limbs in the same layout (64 KB)
     extern __shared__ __align__(128) uint32_t sh[];
-    constexpr uint32_t kHiOff = kMaxBins * 2 * kGroup * 4;       // bytes
+    constexpr uint32_t kHOff = kMaxBins * 2 * kGroup * 4;        // bytes
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int fg = blockIdx.y;
     const RowItem it = items[blockIdx.x];
@@ -202,110 +206,105 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
     __syncthreads();
 
     const uint32_t gmask = group_mask[fg];
-    const int m = lane >> 2, bsel = lane & 3;
+    // Lane L works on row (L >> 1) of a 16-row block and on the 16 features of half (L & 1) of the
+    // group: at step k (0..15) it updates feature 16*(L&1) + (k ^ (L>>1)).  The 32 lanes of a warp
+    // instruction therefore always touch 32 different features = 32 different banks.
+    const int half = lane & 1, r16 = lane >> 1;
+    const int m = r16 >> 2, bsel = r16 & 3;
     // PRMT selectors: byte (kk ^ bsel) of a data word moved to byte 1, i.e. bin * 256 = the byte
-    // offset of that bin's 256 B row of low words
+    // offset of that bin's 256 B row of limbs
     uint32_t selk[4];
 #pragma unroll
     for (int kk = 0; kk < 4; kk++) selk[kk] = 0x4404u | ((uint32_t)(kk ^ bsel) << 4);
-    uint32_t lane4 = (uint32_t)lane << 2;
-    asm volatile("" : "+r"(lane4));          // keep it a plain register: (bin256 | lane4) ^ k4 is one LOP3
-    const uint8_t* __restrict__ gbase = bins + fg * kGroup + (m << 2);
+    // byte offset of feature 16*half + r16 inside a bin row; feature 16*half + (k ^ r16) is reached
+    // by XOR-ing k*4 into it: (bin256 | lane_off) ^ k4 is one LOP3
+    uint32_t lane_off = (uint32_t)(half * 16 + r16) << 2;
+    asm volatile("" : "+r"(lane_off));
+    const uint8_t* __restrict__ gbase = bins + fg * kGroup + (half << 4);
     char* const shb = reinterpret_cast<char*>(sh);
 
-    // Lane r loads the 8 data words of ITS row already permuted: register j holds word j ^ m, the
-    // one holding the features this lane visits at steps 4j..4j+3.  The 8 loads of a lane fall in
-    // one 32 B sector (first one misses, the rest hit L1).
-    auto load = [&](long long base, uint32_t (&w)[8], int2& q) {
-        long long i = base + lane;
-        if (i < it.end) {
-            int32_t rid = ridx ? ridx[i] : (int32_t)i;
-            q = gq[rid];
-            const unsigned long long a = (unsigned long long)(gbase + (long long)rid * S8);
+    // Three-stage software pipeline per warp: row ids of block t+2, row data of block t+1 and the
+    // atomics of block t are in flight together, so no load waits on another load of the same
+    // iteration (loads share the LSU queue with thousands of cycles of queued atomics).
+    // A block is 32 rows = two 128-bit loads: adjacent lanes fetch the two halves of a row, so every
+    // 32 B sector is requested once; for contiguous rows the warp reads 1 KB in 8 fully used lines.
+    struct Fetch { uint4 a, b; int2 qa, qb; };
+    auto fetch_rid = [&](long long base) -> int32_t {
+        const long long i = base + lane;
+        return i < it.end ? (ridx ? ridx[i] : (int32_t)i) : -1;
+    };
+    auto fetch = [&](int32_t rid, Fetch& f) {
+        const int32_t ra = __shfl_sync(0xffffffffu, rid, r16);
+        const int32_t rb = __shfl_sync(0xffffffffu, rid, 16 + r16);
+        // past the end of the run: zeros, i.e. "add zero to bin 0", which changes nothing
+        f.a = make_uint4(0, 0, 0, 0); f.b = f.a;
+        f.qa = make_int2(0, 0); f.qb = f.qa;
+        if (ra >= 0) { f.a = *reinterpret_cast<const uint4*>(gbase + (long long)ra * S8); f.qa = gq[ra]; }
+        if (rb >= 0) { f.b = *reinterpret_cast<const uint4*>(gbase + (long long)rb * S8); f.qb = gq[rb]; }
+    };
+
+    // 16 steps on one 16-row half block.  Register j must hold data word j ^ m (m = r16 >> 2), the
+    // word with the features this lane visits at steps 4j..4j+3: two conditional swaps.
+    // Unsampled features and padding lanes are accumulated too (the instruction is issued for the
+    // whole warp anyway) and dropped at flush time.
+    auto accumulate16 = [&](const uint4 d, const int2 q) {
+        uint32_t w[4] = {d.x, d.y, d.z, d.w};
+        {
+            const bool c0 = m & 1, c1 = m & 2;
+            uint32_t t;
+            t = c0 ? w[1] : w[0]; w[1] = c0 ? w[0] : w[1]; w[0] = t;
+            t = c0 ? w[3] : w[2]; w[3] = c0 ? w[2] : w[3]; w[2] = t;
+            t = c1 ? w[2] : w[0]; w[2] = c1 ? w[0] : w[2]; w[0] = t;
+            t = c1 ? w[3] : w[1]; w[3] = c1 ? w[1] : w[3]; w[1] = t;
+        }
+        const uint32_t g_lo = (uint32_t)q.x & 0xffffu, h_lo = (uint32_t)q.y & 0xffffu;
+        const int32_t g_hi = q.x >> 16, h_hi = q.y >> 16;
 #pragma unroll
-            for (int j = 0; j < 8; j++) w[j] = *reinterpret_cast<const uint32_t*>(a ^ (unsigned long long)(j << 2));
-        } else {
-            // past the end of the run: adds zero to bin 0, which changes nothing
-            q = make_int2(0, 0);
+        for (int j = 0; j < 4; j++) {
+            const uint32_t word = w[j];
 #pragma unroll
-            for (int j = 0; j < 8; j++) w[j] = 0;
+            for (int kk = 0; kk < 4; kk++) {
+                const uint32_t off = (__byte_perm(word, 0u, selk[kk]) | lane_off) ^ (uint32_t)((4 * j + kk) << 2);
+                uint32_t* p = reinterpret_cast<uint32_t*>(shb + off);
+                atomicAdd(p, g_lo);
+                atomicAdd(reinterpret_cast<int32_t*>(p + kGroup), g_hi);
+                atomicAdd(p + kHOff / 4, h_lo);
+                atomicAdd(reinterpret_cast<int32_t*>(p + kHOff / 4 + kGroup), h_hi);
+            }
         }
     };
 
-    // One 32-row block of this warp: 32 steps, at step k lane r updates feature k ^ r of its row.
-    auto accumulate = [&](const uint32_t (&w)[8], const int2 q) {
-        const uint32_t g = (uint32_t)q.x, h = (uint32_t)q.y;
-        const unsigned long long g64 = (unsigned long long)(long long)q.x;
-        const unsigned long long h64 = (unsigned long long)(long long)q.y;
-        // Unsampled features and padding lanes are accumulated too (the instruction is issued
-        // for the whole warp anyway) and dropped at flush time.
-        // The atomics of feature quad j are issued before the carries of quad j-1 are looked at, so
-        // a warp always has 8 shared-memory atomics in flight while it does the bookkeeping.
-        uint32_t off_p[4] = {0, 0, 0, 0}, og_p[4] = {0, 0, 0, 0}, oh_p[4] = {0, 0, 0, 0};
-#pragma unroll
-        for (int j = 0; j <= 8; j++) {
-            uint32_t off_c[4] = {0, 0, 0, 0}, og_c[4] = {0, 0, 0, 0}, oh_c[4] = {0, 0, 0, 0};
-            if (j < 8) {
-                const uint32_t word = w[j < 8 ? j : 0];
-#pragma unroll
-                for (int kk = 0; kk < 4; kk++) {
-                    off_c[kk] = (__byte_perm(word, 0u, selk[kk]) | lane4) ^ (uint32_t)((4 * j + kk) << 2);
-                    uint32_t* p = reinterpret_cast<uint32_t*>(shb + off_c[kk]);
-                    og_c[kk] = atomicAdd(p, g);
-                    oh_c[kk] = atomicAdd(p + kGroup, h);
-                }
-            }
-            if (j > 0) {
-                int32_t hg[4], hh[4];
-#pragma unroll
-                for (int kk = 0; kk < 4; kk++) {
-                    // high word of (old low word + signed addend): carry or borrow owed to the high word
-                    hg[kk] = (int32_t)(((unsigned long long)og_p[kk] + g64) >> 32);
-                    hh[kk] = (int32_t)(((unsigned long long)oh_p[kk] + h64) >> 32);
-                }
-                if (((hg[0] | hg[1] | hg[2]) | (hg[3] | hh[0] | hh[1]) | (hh[2] | hh[3])) != 0) {
-                    // a low word wrapped for this lane (about 1 update in 700 with 24-bit fixed point)
-#pragma unroll
-                    for (int kk = 0; kk < 4; kk++) {
-                        if ((hg[kk] | hh[kk]) != 0) {
-                            int32_t* p = reinterpret_cast<int32_t*>(shb + kHiOff + off_p[kk]);
-                            if (hg[kk] != 0) atomicAdd(p, hg[kk]);
-                            if (hh[kk] != 0) atomicAdd(p + kGroup, hh[kk]);
-                        }
-                    }
-                }
-            }
-#pragma unroll
-            for (int kk = 0; kk < 4; kk++) { off_p[kk] = off_c[kk]; og_p[kk] = og_c[kk]; oh_p[kk] = oh_c[kk]; }
-        }
-    };
-
-    // software pipeline over this warp's 32-row blocks, two register sets in ping-pong
+    // (two register sets in explicit ping-pong: a copy `cur = nxt` would be scheduled right behind
+    // the loads and stall the warp on them)
     long long base = it.begin + warp * 32;
-    uint32_t wa[8], wb[8];
-    int2 qa, qb;
-    load(base, wa, qa);
+    Fetch fa, fb;
+    int32_t r1 = fetch_rid(base + kHistThreads);
+    fetch(fetch_rid(base), fa);
     while (base < it.end) {
-        load(base + kHistThreads, wb, qb);
-        accumulate(wa, qa);
+        const int32_t r2 = fetch_rid(base + 2 * kHistThreads);
+        fetch(r1, fb);
+        accumulate16(fa.a, fa.qa);
+        accumulate16(fa.b, fa.qb);
         base += kHistThreads;
         if (base >= it.end) break;
-        load(base + kHistThreads, wa, qa);
-        accumulate(wb, qb);
+        r1 = fetch_rid(base + 2 * kHistThreads);
+        fetch(r2, fa);
+        accumulate16(fb.a, fb.qa);
+        accumulate16(fb.b, fb.qb);
         base += kHistThreads;
     }
     __syncthreads();
 
-    // flush: one 64-bit global reduction per non-empty (feature, bin, component)
+    // flush: recombine the limbs, one 64-bit global reduction per non-empty (feature, bin, component)
     long long* __restrict__ out = seg_out[it.seg];
     for (int i = tid; i < kMaxBins * kGroup; i += kHistThreads) {
         int bin = i >> 5, ln = i & 31;
         int ff = fg * kGroup + ln;
         if (ff >= F || !((gmask >> ln) & 1u) || bin >= nbins[ff]) continue;
-        const uint32_t* lo = sh + bin * (2 * kGroup) + ln;
-        const uint32_t* hi = lo + kHiOff / 4;
-        long long g = (long long)(((unsigned long long)hi[0] << 32) | lo[0]);
-        long long h = (long long)(((unsigned long long)hi[kGroup] << 32) | lo[kGroup]);
+        const uint32_t* pg = sh + bin * (2 * kGroup) + ln;
+        const uint32_t* ph = pg + kHOff / 4;
+        long long g = (long long)(int32_t)pg[kGroup] * 65536ll + (long long)pg[0];
+        long long h = (long long)(int32_t)ph[kGroup] * 65536ll + (long long)ph[0];
         long long* dst = out + feat_owner[ff] * owner_stride + feat_inner[ff] + 2 * bin;
         if (g != 0) atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)g);
         if (h != 0) atomicAdd(reinterpret_cast<unsigned long long*>(dst + 1), (unsigned long long)h);
@@ -715,17 +714,19 @@ static inline int grid_for(int64_t n, int threads, int max_blocks = kNumSMs * 8)
 }
 
 cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, int32_t F, uint8_t* bins,
-                               int32_t S8, uint8_t* col, int64_t col_stride, int* bad_flag, cudaStream_t st) {
+                               int32_t S8, uint8_t* col, int64_t col_stride, int64_t row_base, int* bad_flag,
+                               cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    repack_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, bins, S8, col, col_stride, bad_flag);
+    repack_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, bins, S8, col, col_stride, row_base,
+                                                             bad_flag);
     return cudaGetLastError();
 }
 cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t stride, int32_t F,
                                  const float* cuts, const int32_t* start, uint8_t* bins, int32_t S8,
-                                 uint8_t* col, int64_t col_stride, cudaStream_t st) {
+                                 uint8_t* col, int64_t col_stride, int64_t row_base, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
     quantize_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(xbits, nrows, stride, F, cuts, start, bins, S8, col,
-                                                               col_stride);
+                                                               col_stride, row_base);
     return cudaGetLastError();
 }
 cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, int32_t F, int32_t* out,
@@ -751,7 +752,8 @@ int64_t hist_rows_per_item(int64_t total_rows, int groups) {
     int64_t items = std::max<int64_t>(1, (2 * kNumSMs) / std::max(1, groups));
     int64_t rows = (total_rows + items - 1) / items;
     rows = std::max<int64_t>(rows, 4 * kHistThreads);
-    return (rows + kHistThreads - 1) / kHistThreads * kHistThreads;
+    rows = (rows + kHistThreads - 1) / kHistThreads * kHistThreads;
+    return std::min<int64_t>(rows, kHistMaxRowsPerItem);    // the 16-bit limb sums must stay inside 32 bits
 }
 
 cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx0,

@@ -775,7 +775,7 @@ int ytk_gbdt_upload_rows(ytk_gbdt* h, const int32_t* x_chunk, int64_t row0, int6
         RET(ensure_stage(h, bytes));
         CK(cudaMemcpyAsync(h->d_stage, x_chunk + r * stride, bytes, cudaMemcpyHostToDevice, h->st));
         CK(ytk::launch_repack_rows((const int32_t*)h->d_stage, n, stride, h->F, h->d_bins + (row0 + r) * h->S8,
-                                   h->S8, h->d_bins_col + (row0 + r), h->N, h->d_bad, h->st));
+                                   h->S8, h->d_bins_col + (row0 + r), h->N, row0 + r, h->d_bad, h->st));
         CK(cudaStreamSynchronize(h->st));
     }
     int bad = 0;
@@ -806,7 +806,7 @@ int ytk_gbdt_quantize_rows(ytk_gbdt* h, const int32_t* xbits_chunk, int64_t row0
         if (e == cudaSuccess)
             e = ytk::launch_quantize_rows((const int32_t*)h->d_stage, n, stride, h->F, d_cuts, h->d_start,
                                           h->d_bins + (row0 + r) * h->S8, h->S8, h->d_bins_col + (row0 + r), h->N,
-                                          h->st);
+                                          row0 + r, h->st);
         if (e == cudaSuccess) e = cudaStreamSynchronize(h->st);
     }
     cudaFree(d_cuts);
