@@ -36,8 +36,12 @@ struct PartitionCounts { long long left, right; };
 
 // ---- work tables: one launch serves every node of a batch (a tree level, or one node) ----
 
-// a run of rows rowidx[buf][begin,end) (buf < 0: rows begin..end-1) whose sums go to segment `seg`
-struct RowItem { long long begin, end; int buf; int seg; };
+// A run of rows rowidx[buf][begin,end) (buf < 0: rows begin..end-1) whose sums go to segment `seg`.
+// cseg >= 0 defers the range to the device: [begin,end) is then the interval of split segment cseg
+// (the parent) and the item means "rows [chunk*rows_per_chunk, +rows_per_chunk) of its SMALLER
+// child", resolved from the partition counts still on the device -- so the host need not wait for
+// the partition before it queues the histogram kernels.
+struct RowItem { long long begin, end; int buf; int seg; int cseg; int chunk; long long rows_per_chunk; };
 
 // one node being split: rows rowidx[buf][begin,end) move to rowidx[1-buf] (buf < 0 -> buffer 0)
 struct SplitSeg {
@@ -50,7 +54,9 @@ struct SplitSeg {
     int pad;
 };
 
-struct ScanNode { const long long* hist; long long sample_cnt; };
+// cseg >= 0: sample_cnt is the global row count of the smaller (which = 0) / larger (which = 1)
+// child of split segment cseg, read from the device counts
+struct ScanNode { const long long* hist; long long sample_cnt; int cseg; int which; };
 struct SubItem { const long long* parent; const long long* small; long long* out; };
 struct PosItem { long long begin, end; int buf; int nid; };
 
@@ -77,7 +83,7 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
                               const int32_t* rowidx1, const RowItem* items, int n_items, int32_t F,
                               const uint32_t* group_mask, const int32_t* nbins, const int32_t* feat_owner,
                               const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
-                              cudaStream_t st);
+                              const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st);
 // rows one hist work item should cover so that `total_rows` split into about two waves of CTAs
 int64_t hist_rows_per_item(int64_t total_rows, int groups);
 
@@ -90,7 +96,8 @@ cudaError_t launch_hist_from_double(const double* in, int64_t len, const GradSca
 // K4/K5: node totals + split scan + arg-max over the features [f_from, f_to) this rank owns, one CTA per node.
 cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t* start, const int64_t* feat_off,
                               const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
-                              const GradScale* scale, GainParams gp, ytk_split* out, cudaStream_t st);
+                              const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
+                              ytk_split* out, cudaStream_t st);
 
 // K6: stable partition of every segment by (float)bin(row,fid) < cond (or by a byte mask)
 constexpr int kPartThreads = 256;
@@ -103,7 +110,8 @@ cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride,
 
 // K7: exact fixed-point sums of (g,h) over row runs -> out[2*seg + {0,1}] (pre-zeroed)
 cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1, const RowItem* items,
-                             int n_items, long long* out, cudaStream_t st);
+                             int n_items, long long* out, const PartitionCounts* cnt_local,
+                             const PartitionCounts* cnt_global, cudaStream_t st);
 
 cudaError_t launch_fill_positions(const int32_t* rowidx0, const int32_t* rowidx1, const PosItem* items, int n_items,
                                   int32_t* node_of_row, cudaStream_t st);

@@ -184,19 +184,36 @@ __global__ void grad_quantize_k(const float* __restrict__ gp, int64_t n, int32_t
 // rows of one node and one feature group; it flushes non-empty bins with 64-bit global
 // reductions into that node's histogram.
 // ------------------------------------------------------------------------------------
+// smaller child = strictly fewer GLOBAL rows on the left, else the right
+// (J/optimizer/gbdt/DataParallelTreeMaker.java:344-350, :493-499)
+__device__ __forceinline__ RowItem resolve_item(RowItem it, const PartitionCounts* __restrict__ cnt_local,
+                                                const PartitionCounts* __restrict__ cnt_global) {
+    if (it.cseg < 0) return it;
+    const PartitionCounts l = cnt_local[it.cseg], g = cnt_global[it.cseg];
+    const bool small_left = g.left < g.right;
+    const long long cb = small_left ? it.begin : it.begin + l.left;
+    const long long ce = small_left ? it.begin + l.left : it.end;
+    const long long b = cb + it.chunk * it.rows_per_chunk;
+    it.begin = min(b, ce);
+    it.end = min(ce, b + it.rows_per_chunk);
+    return it;
+}
+
 __global__ void __launch_bounds__(kHistThreads, 1)
 hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict__ gq,
              const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1,
              const RowItem* __restrict__ items, int32_t F, const uint32_t* __restrict__ group_mask,
              const int32_t* __restrict__ nbins, const int32_t* __restrict__ feat_owner,
              const int64_t* __restrict__ feat_inner, long long owner_stride,
-             long long* const* __restrict__ seg_out) {
+             long long* const* __restrict__ seg_out, const PartitionCounts* __restrict__ cnt_local,
+             const PartitionCounts* __restrict__ cnt_global) {
     // g limbs [bin][{lo,hi}][feature] (64 KB), then the h limbs in the same layout (64 KB)
     extern __shared__ __align__(128) uint32_t sh[];
     constexpr uint32_t kHOff = kMaxBins * 2 * kGroup * 4;        // bytes
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int fg = blockIdx.y;
-    const RowItem it = items[blockIdx.x];
+    const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
+    if (it.begin >= it.end) return;          // a deferred chunk beyond the end of its child
     const int32_t* __restrict__ ridx = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
 
     {
@@ -399,14 +416,19 @@ __global__ void __launch_bounds__(kScanWarps * 32)
 split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ start,
              const int64_t* __restrict__ feat_off, const uint8_t* __restrict__ fea_selected,
              int32_t f_from, int32_t f_to, int32_t first_fea, const GradScale* __restrict__ scale,
-             GainParams gp, ytk_split* __restrict__ outs) {
+             GainParams gp, const PartitionCounts* __restrict__ cnt_global, ytk_split* __restrict__ outs) {
     __shared__ double s_tot[2];
     __shared__ float s_lc[kScanWarps];
     __shared__ int s_fid[kScanWarps], s_lo[kScanWarps], s_hi[kScanWarps];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const double ig = scale->inv_g, ih = scale->inv_h;
     const long long* __restrict__ hist = nodes[blockIdx.x].hist;
-    const long long sample_cnt = nodes[blockIdx.x].sample_cnt;
+    long long sample_cnt = nodes[blockIdx.x].sample_cnt;
+    if (nodes[blockIdx.x].cseg >= 0) {
+        const PartitionCounts g = cnt_global[nodes[blockIdx.x].cseg];
+        const long long small = g.left < g.right ? g.left : g.right;
+        sample_cnt = nodes[blockIdx.x].which == 0 ? small : (g.left + g.right - small);
+    }
     ytk_split* out = outs + blockIdx.x;
 
     if (warp == 0) {
@@ -672,8 +694,9 @@ partition_scatter_k(int32_t* __restrict__ rowidx0, int32_t* __restrict__ rowidx1
 //     (J/optimizer/gbdt/DataParallelTreeMaker.java:352-372).
 __global__ void leaf_sums_k(const int2* __restrict__ gq, const int32_t* __restrict__ rowidx0,
                             const int32_t* __restrict__ rowidx1, const RowItem* __restrict__ items,
-                            long long* __restrict__ out) {
-    const RowItem it = items[blockIdx.x];
+                            long long* __restrict__ out, const PartitionCounts* __restrict__ cnt_local,
+                            const PartitionCounts* __restrict__ cnt_global) {
+    const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
     const int32_t* __restrict__ rowidx = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
     long long g = 0, h = 0;
     for (long long i = it.begin + threadIdx.x; i < it.end; i += blockDim.x) {
@@ -760,7 +783,7 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
                               const int32_t* rowidx1, const RowItem* items, int n_items, int32_t F,
                               const uint32_t* group_mask, const int32_t* nbins, const int32_t* feat_owner,
                               const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
-                              cudaStream_t st) {
+                              const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st) {
     if (n_items <= 0) return cudaSuccess;
     static bool attr_set = false;
     if (!attr_set) {
@@ -771,7 +794,8 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
     }
     dim3 grid((unsigned)n_items, (unsigned)(S8 / kGroup));
     hist_build_k<<<grid, kHistThreads, kHistSmemBytes, st>>>(bins, S8, gq, rowidx0, rowidx1, items, F, group_mask,
-                                                             nbins, feat_owner, feat_inner, owner_stride, seg_out);
+                                                             nbins, feat_owner, feat_inner, owner_stride, seg_out,
+                                                             cnt_local, cnt_global);
     return cudaGetLastError();
 }
 
@@ -806,10 +830,11 @@ cudaError_t launch_copy_segments(const long long* src, long long* const* dst, in
 
 cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t* start, const int64_t* feat_off,
                               const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
-                              const GradScale* scale, GainParams gp, ytk_split* out, cudaStream_t st) {
+                              const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
+                              ytk_split* out, cudaStream_t st) {
     if (n_nodes <= 0) return cudaSuccess;
     split_scan_k<<<n_nodes, kScanWarps * 32, 0, st>>>(nodes, start, feat_off, fea_selected, f_from, f_to, first_fea,
-                                                      scale, gp, out);
+                                                      scale, gp, cnt_global, out);
     return cudaGetLastError();
 }
 
@@ -828,9 +853,10 @@ cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride,
 }
 
 cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1, const RowItem* items,
-                             int n_items, long long* out, cudaStream_t st) {
+                             int n_items, long long* out, const PartitionCounts* cnt_local,
+                             const PartitionCounts* cnt_global, cudaStream_t st) {
     if (n_items <= 0) return cudaSuccess;
-    leaf_sums_k<<<n_items, 256, 0, st>>>(gq, rowidx0, rowidx1, items, out);
+    leaf_sums_k<<<n_items, 256, 0, st>>>(gq, rowidx0, rowidx1, items, out, cnt_local, cnt_global);
     return cudaGetLastError();
 }
 

@@ -403,32 +403,50 @@ int hist_events(ytk_gbdt* h, cudaEvent_t* a, cudaEvent_t* b) {
 void add_row_items(std::vector<ytk::RowItem>& items, const Interval& v, int seg, int64_t rows_per_item) {
     if (v.e <= v.b) return;
     for (int64_t b = v.b; b < v.e; b += rows_per_item)
-        items.push_back({(long long)b, (long long)std::min(v.e, b + rows_per_item), v.buf, seg});
+        items.push_back({(long long)b, (long long)std::min(v.e, b + rows_per_item), v.buf, seg, -1, 0, 0});
+}
+// Work items for "the smaller child of split segment cseg" whose size is still on the device:
+// enough chunks for the largest it can be (half the parent on one GPU; the whole local parent when
+// the smaller child is decided by global counts).
+void add_deferred_items(std::vector<ytk::RowItem>& items, const Interval& parent, int child_buf, int seg, int cseg,
+                        int64_t rows_per_item, int world) {
+    const int64_t n = parent.e - parent.b;
+    const int64_t max_rows = world == 1 ? n / 2 : n;
+    const int chunks = (int)((max_rows + rows_per_item - 1) / rows_per_item);
+    for (int c = 0; c < chunks; c++)
+        items.push_back({(long long)parent.b, (long long)parent.e, child_buf, seg, cseg, c, (long long)rows_per_item});
 }
 
-struct HistJob { int nid; long long* dst; };   // build node nid's histogram into dst (this rank's segment)
+// Build a node's histogram into dst (this rank's segment).  cseg < 0: rows = iv[nid]; cseg >= 0: rows =
+// the smaller child of split segment cseg (parent interval `parent`, children in buffer child_buf).
+struct HistJob { int nid; long long* dst; int cseg; Interval parent; int child_buf; };
 
 // HistogramBuilder.buildHist (J/data/gbdt/HistogramBuilder.java:56-98) for a batch of nodes:
 // one kernel launch over all their rows, then (world > 1) one reduce-scatter by feature range.
-int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, int n_sel) {
+int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, int n_sel,
+                const ytk::PartitionCounts* cnt_local, const ytk::PartitionCounts* cnt_global) {
     const int m = (int)jobs.size();
     if (m == 0) return YTK_OK;
     int64_t total = 0;
-    for (auto& j : jobs) total += h->iv[j.nid].e - h->iv[j.nid].b;
+    for (auto& j : jobs) total += j.cseg < 0 ? h->iv[j.nid].e - h->iv[j.nid].b : (j.parent.e - j.parent.b) / 2;
     const int64_t rpi = ytk::hist_rows_per_item(total, h->groups);
     std::vector<ytk::RowItem> items;
     std::vector<long long*> outs(m);
     const int64_t local_len = h->seg_max * h->world;
     if (h->world > 1) CK(h->t_hist_local.reserve((size_t)m * local_len));
     for (int k = 0; k < m; k++) {
-        const Interval& v = h->iv[jobs[k].nid];
-        add_row_items(items, v, k, rpi);
+        if (jobs[k].cseg < 0) {
+            const Interval& v = h->iv[jobs[k].nid];
+            add_row_items(items, v, k, rpi);
+            T->hist_built++;
+            T->hist_cells += (double)(v.e - v.b) * n_sel;
+            T->hist_rows += (double)(v.e - v.b);
+            if (v.buf >= 0) T->hist_rows_indexed += (double)(v.e - v.b);
+        } else {
+            add_deferred_items(items, jobs[k].parent, jobs[k].child_buf, k, jobs[k].cseg, rpi, h->world);
+        }
         // world > 1: local layout [rank][node][segment] so that ONE reduce-scatter serves the batch
         outs[k] = h->world == 1 ? jobs[k].dst : h->t_hist_local.d + (int64_t)k * h->seg_max;
-        T->hist_built++;
-        T->hist_cells += (double)(v.e - v.b) * n_sel;
-        T->hist_rows += (double)(v.e - v.b);
-        if (v.buf >= 0) T->hist_rows_indexed += (double)(v.e - v.b);
     }
     cudaEvent_t e0, e1;
     RET(hist_events(h, &e0, &e1));
@@ -444,7 +462,7 @@ int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T
     const long long owner_stride = h->world == 1 ? 0 : (long long)m * h->seg_max;
     CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_items.d,
                               (int)items.size(), h->F, h->d_group_mask, h->d_nbins, h->d_feat_owner, h->d_off_inner,
-                              owner_stride, h->t_seg_out.d, h->st));
+                              owner_stride, h->t_seg_out.d, cnt_local, cnt_global, h->st));
     if (!items.empty()) h->launches++;
     CK(cudaEventRecord(e1, h->st));
     if (h->world > 1) {
@@ -463,14 +481,15 @@ int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T
 
 // updateTreeMakerNodeStats + findBestSplit(nid, hist) + syncBestSplit (:543-595, :640-653) for a
 // batch of nodes; the merged record of node k lands in recs[k].
-int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first_owned, std::vector<ytk_split>& recs) {
+int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first_owned, std::vector<ytk_split>& recs,
+                 const ytk::PartitionCounts* cnt_global = nullptr) {
     const int m = (int)nodes.size();
     recs.resize(m);
     if (m == 0) return YTK_OK;
     CK(h->t_scan.upload(nodes, h->st, h->arena));
     CK(h->t_split_local.reserve(m));
     CK(ytk::launch_split_scan(h->t_scan.d, m, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to,
-                              first_owned, h->d_scale, gain_params(h->p), h->t_split_local.d, h->st));
+                              first_owned, h->d_scale, gain_params(h->p), cnt_global, h->t_split_local.d, h->st));
     h->launches++;
     CK(h->h_split.reserve((size_t)m * h->world));
     if (h->world == 1) {
@@ -505,11 +524,11 @@ void apply_record(NodeStats& s, const ytk_split& r) {
 }
 
 // position.resetPosition (SamplePositionData.java:115-133) for a batch of nodes, plus the global
-// child counts of initTreeMakerNodeStats(l, r) (:522-541).  counts_local/global: [m].
-int partition_nodes(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const std::vector<ytk::SplitSeg>& segs_in,
-                    std::vector<ytk::PartitionCounts>& local, std::vector<ytk::PartitionCounts>& global) {
+// child counts of initTreeMakerNodeStats(l, r) (:522-541).  Queues the kernels, the count allreduce
+// and the copy of the counts to the host; does not wait.  Device counts: t_counts.d[0..m) local,
+// [m..2m) global (world > 1).
+int partition_launch(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const std::vector<ytk::SplitSeg>& segs_in) {
     const int m = (int)segs_in.size();
-    local.resize(m); global.resize(m);
     if (m == 0) return YTK_OK;
     std::vector<ytk::SplitSeg> segs = segs_in;
     std::vector<int> tile_seg;
@@ -539,12 +558,23 @@ int partition_nodes(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const s
     CK(h->h_counts.reserve(nc));
     CK(cudaMemcpyAsync(h->h_counts.h, h->t_counts.d, nc * sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost,
                        h->st));
-    CK(cudaStreamSynchronize(h->st));
-    h->arena.rewind();
+    return YTK_OK;
+}
+// after the stream has been synchronised
+void partition_collect(ytk_gbdt* h, int m, std::vector<ytk::PartitionCounts>& local,
+                       std::vector<ytk::PartitionCounts>& global) {
+    local.resize(m); global.resize(m);
     for (int k = 0; k < m; k++) {
         local[k] = h->h_counts.h[k];
         global[k] = h->h_counts.h[h->world > 1 ? m + k : k];
     }
+}
+int partition_nodes(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const std::vector<ytk::SplitSeg>& segs_in,
+                    std::vector<ytk::PartitionCounts>& local, std::vector<ytk::PartitionCounts>& global) {
+    RET(partition_launch(h, src, col_stride, segs_in));
+    CK(cudaStreamSynchronize(h->st));
+    h->arena.rewind();
+    partition_collect(h, (int)segs_in.size(), local, global);
     return YTK_OK;
 }
 
@@ -948,9 +978,9 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         double t0 = now_ms();
         long long* slot;
         RET(pool_slot(root_id, &slot));
-        RET(build_hists(h, {{root_id, slot}}, T, n_sel));
+        RET(build_hists(h, {{root_id, slot, -1, Interval(), 0}}, T, n_sel, nullptr, nullptr));
         double t1 = now_ms();
-        RET(search_nodes(h, {{slot, (long long)ns[root_id].sample_cnt}}, first_owned, recs));
+        RET(search_nodes(h, {{slot, (long long)ns[root_id].sample_cnt, -1, 0}}, first_owned, recs));
         apply_record(ns[root_id], recs[0]);
         set_split_if_good(root_id);
         T->build_hist += t1 - t0;
@@ -1011,47 +1041,71 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             const Interval& pv = iv[jobs[k].nid];
             segs[k] = {(long long)pv.b, (long long)pv.e, pv.buf, out->fid[jobs[k].nid], out->node_info[jobs[k].nid], 0, 0, 0};
         }
-        RET(partition_nodes(h, h->d_bins_col, h->N, segs, cl, cg));
-        for (int k = 0; k < m; k++) {
-            const SplitJob& j = jobs[k];
-            const Interval pv = iv[j.nid];
-            const int cbuf = pv.buf == 0 ? 1 : 0;
-            iv[j.l].b = pv.b; iv[j.l].e = pv.b + cl[k].left; iv[j.l].buf = cbuf;
-            iv[j.r].b = pv.b + cl[k].left; iv[j.r].e = pv.e; iv[j.r].buf = cbuf;
-            ns[j.l].sample_cnt = cg[k].left; ns[j.r].sample_cnt = cg[k].right;
-            if (p.min_split_samples > 0 && ns[j.l].sample_cnt < p.min_split_samples
-                && ns[j.r].sample_cnt < p.min_split_samples)
-                jobs[k].terminal = true;
+        // With an unbounded pool and no row-count stop rule nothing the host decides next depends on
+        // the child counts, so the histogram/leaf kernels are queued right behind the partition with
+        // "smaller child of segment k" work items resolved on the device: one host wait per batch
+        // instead of two.
+        const bool deferred = unbounded && p.min_split_samples <= 0;
+        auto finish_partition = [&]() {
+            partition_collect(h, m, cl, cg);
+            for (int k = 0; k < m; k++) {
+                const SplitJob& j = jobs[k];
+                const Interval pv = iv[j.nid];
+                const int cbuf = pv.buf == 0 ? 1 : 0;
+                iv[j.l].b = pv.b; iv[j.l].e = pv.b + cl[k].left; iv[j.l].buf = cbuf;
+                iv[j.r].b = pv.b + cl[k].left; iv[j.r].e = pv.e; iv[j.r].buf = cbuf;
+                ns[j.l].sample_cnt = cg[k].left; ns[j.r].sample_cnt = cg[k].right;
+                if (p.min_split_samples > 0 && ns[j.l].sample_cnt < p.min_split_samples
+                    && ns[j.r].sample_cnt < p.min_split_samples)
+                    jobs[k].terminal = true;
+            }
+        };
+        RET(partition_launch(h, h->d_bins_col, h->N, segs));
+        if (!deferred) {
+            CK(cudaStreamSynchronize(h->st));
+            h->arena.rewind();
+            finish_partition();
         }
+        const ytk::PartitionCounts* d_cl = h->t_counts.d;
+        const ytk::PartitionCounts* d_cg = h->world > 1 ? h->t_counts.d + m : h->t_counts.d;
         T->partition += now_ms() - t0;
 
         // ---- children: leaf statistics (computeLeafStats :341-385) or histograms + split search
         t0 = now_ms();
+        // smaller child: strictly fewer global rows on the left, else the right (:344-350, :493-499)
+        auto small_of = [&](const SplitJob& j) { return ns[j.l].sample_cnt < ns[j.r].sample_cnt ? j.l : j.r; };
         std::vector<ytk::RowItem> leaf_items;
         std::vector<HistJob> hist_jobs;
         std::vector<ytk::SubItem> subs;
         std::vector<ytk::ScanNode> scans;
-        std::vector<int> scan_nid, leaf_small(m, -1);
+        std::vector<int> scan_job;               // scans[2i], scans[2i+1] = smaller, larger child of jobs[scan_job[i]]
         int n_leaf_jobs = 0;
         for (int k = 0; k < m; k++) {
             const SplitJob& j = jobs[k];
-            // smaller child: strictly fewer global rows on the left, else the right (:344-350, :493-499)
-            const int small = ns[j.l].sample_cnt < ns[j.r].sample_cnt ? j.l : j.r;
-            const int large = small == j.l ? j.r : j.l;
+            const Interval pv = iv[j.nid];
+            const int cbuf = pv.buf == 0 ? 1 : 0;
             if (j.terminal) {
                 if (unbounded) h->pool.release(j.nid);
-                leaf_small[k] = small;
-                const int64_t n = iv[small].e - iv[small].b;
-                const int64_t per = std::max<int64_t>(4096, (n + 63) / 64);
-                add_row_items(leaf_items, iv[small], n_leaf_jobs, per);
+                if (deferred) {
+                    const int64_t n = pv.e - pv.b;
+                    add_deferred_items(leaf_items, pv, cbuf, n_leaf_jobs, k, std::max<int64_t>(4096, (n / 2 + 63) / 64), h->world);
+                } else {
+                    const int small = small_of(j);
+                    const int64_t n = iv[small].e - iv[small].b;
+                    add_row_items(leaf_items, iv[small], n_leaf_jobs, std::max<int64_t>(4096, (n + 63) / 64));
+                }
                 n_leaf_jobs++;
                 continue;
             }
-            // buildHist(parent, l, r) (:489-508)
+            // buildHist(parent, l, r) (:489-508).  Pool entries are keyed by node id; while the
+            // children's roles are still unknown they are keyed by placeholders and renamed below.
+            const int small = deferred ? -2 - 2 * k : small_of(j);
+            const int large = deferred ? -3 - 2 * k : (small == j.l ? j.r : j.l);
             long long* parent_h = h->pool.get(j.nid);
             long long *small_h, *large_h;
             RET(pool_slot(small, &small_h));
-            hist_jobs.push_back({small, small_h});
+            if (deferred) hist_jobs.push_back({-1, small_h, k, pv, cbuf});
+            else hist_jobs.push_back({small, small_h, -1, Interval(), 0});
             if (parent_h) {
                 if (unbounded) {                       // sibling written over its parent
                     h->pool.rename(j.nid, large);
@@ -1062,12 +1116,19 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
                 }
                 subs.push_back({parent_h, small_h, large_h});      // substract (:101-107)
             } else {
+                if (deferred) return fail(YTK_ERR_ARG, "internal: parent histogram missing with an unbounded pool");
                 RET(pool_slot(large, &large_h));
-                hist_jobs.push_back({large, large_h});
+                hist_jobs.push_back({large, large_h, -1, Interval(), 0});
                 T->hist_miss++;
             }
-            scans.push_back({small_h, (long long)ns[small].sample_cnt}); scan_nid.push_back(small);
-            scans.push_back({large_h, (long long)ns[large].sample_cnt}); scan_nid.push_back(large);
+            if (deferred) {
+                scans.push_back({small_h, 0, k, 0});
+                scans.push_back({large_h, 0, k, 1});
+            } else {
+                scans.push_back({small_h, (long long)ns[small].sample_cnt, -1, 0});
+                scans.push_back({large_h, (long long)ns[large].sample_cnt, -1, 0});
+            }
+            scan_job.push_back(k);
         }
         if (n_leaf_jobs > 0) {
             CK(h->t_leaf.reserve(2 * (size_t)n_leaf_jobs));
@@ -1075,7 +1136,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             CK(cudaMemsetAsync(h->t_leaf.d, 0, 2 * (size_t)n_leaf_jobs * sizeof(long long), h->st));
             CK(h->t_leaf_items.upload(leaf_items, h->st, h->arena));
             CK(ytk::launch_leaf_sums(h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_leaf_items.d, (int)leaf_items.size(),
-                                     h->t_leaf.d, h->st));
+                                     h->t_leaf.d, d_cl, d_cg, h->st));
             if (!leaf_items.empty()) h->launches++;
             if (h->world > 1)      // allreduceArray(double[2], SUM) (:375), exact in the integer domain
                 NK(ytk::nccl_api().AllReduce(h->t_leaf.d, h->t_leaf.d, 2 * (size_t)n_leaf_jobs, ncclInt64, ncclSum,
@@ -1083,24 +1144,36 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             CK(cudaMemcpyAsync(h->h_leaf.h, h->t_leaf.d, 2 * (size_t)n_leaf_jobs * sizeof(long long),
                                cudaMemcpyDeviceToHost, h->st));
         }
-        RET(build_hists(h, hist_jobs, T, n_sel));
+        RET(build_hists(h, hist_jobs, T, n_sel, d_cl, d_cg));
         if (!subs.empty()) {
             CK(h->t_sub.upload(subs, h->st, h->arena));
             CK(ytk::launch_hist_subtract(h->t_sub.d, (int)subs.size(), h->seg_max, h->st));
             h->launches++;
         }
         double t1 = now_ms();
-        RET(search_nodes(h, scans, first_owned, recs));     // synchronises the stream
-        if (scans.empty()) CK(cudaStreamSynchronize(h->st));
-        for (size_t i = 0; i < scan_nid.size(); i++) {
-            apply_record(ns[scan_nid[i]], recs[i]);
-            set_split_if_good(scan_nid[i]);
+        RET(search_nodes(h, scans, first_owned, recs, d_cg));     // synchronises the stream
+        if (scans.empty()) { CK(cudaStreamSynchronize(h->st)); h->arena.rewind(); }
+        if (deferred) finish_partition();
+        for (size_t i = 0; i < scan_job.size(); i++) {
+            const SplitJob& j = jobs[scan_job[i]];
+            const int small = small_of(j), large = small == j.l ? j.r : j.l;
+            if (deferred) {
+                h->pool.rename(-2 - 2 * scan_job[i], small);
+                h->pool.rename(-3 - 2 * scan_job[i], large);
+                const Interval& v = iv[small];
+                T->hist_built++;
+                T->hist_cells += (double)(v.e - v.b) * n_sel;
+                T->hist_rows += (double)(v.e - v.b);
+                T->hist_rows_indexed += (double)(v.e - v.b);
+            }
+            apply_record(ns[small], recs[2 * i]); set_split_if_good(small);
+            apply_record(ns[large], recs[2 * i + 1]); set_split_if_good(large);
         }
         int lj = 0;
         for (int k = 0; k < m; k++) {
             const SplitJob& j = jobs[k];
             if (j.terminal) {
-                const int small = leaf_small[k], large = small == j.l ? j.r : j.l;
+                const int small = small_of(j), large = small == j.l ? j.r : j.l;
                 NodeStats &ss = ns[small], &ls = ns[large], &ps = ns[j.nid];
                 ss.sumG = (double)h->h_leaf.h[2 * lj] * h->h_scale.h->inv_g;
                 ss.sumH = (double)h->h_leaf.h[2 * lj + 1] * h->h_scale.h->inv_h;
@@ -1184,7 +1257,7 @@ int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n
     CK(h->t_seg_out.upload(outs, h->st, h->arena));
     CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_items.d,
                               (int)items.size(), h->F, h->d_group_mask, h->d_nbins, h->d_feat_zero, h->d_off_flat, 0,
-                              h->t_seg_out.d, h->st));
+                              h->t_seg_out.d, nullptr, nullptr, h->st));
     if (h->world > 1)
         NK(ytk::nccl_api().AllReduce(h->d_hist_flat, h->d_hist_flat, (size_t)len, ncclInt64, ncclSum, h->comm, h->st));
     CK(ytk::launch_hist_to_double(h->d_hist_flat, len, h->d_scale, h->d_hist_dbl, h->st));
@@ -1249,12 +1322,12 @@ int ytk_gbdt_find_split(ytk_gbdt* h, const double* hist, int64_t sample_cnt, con
         if (fea_index) for (int i = 0; i < n_fea; i++) sel[fea_index[i]] = 1;
         for (int f = 0; f < h->F; f++) if (sel[f]) { first = f; break; }
     }
-    std::vector<ytk::ScanNode> nodes(1, {h->d_hist_flat, (long long)sample_cnt});
+    std::vector<ytk::ScanNode> nodes(1, {h->d_hist_flat, (long long)sample_cnt, -1, 0});
     CK(h->t_scan.upload(nodes, h->st, h->arena));
     CK(h->t_split_local.reserve(1));
     CK(h->h_split.reserve(1));
     CK(ytk::launch_split_scan(h->t_scan.d, 1, h->d_start, h->d_off_flat, h->d_fea_sel, 0, h->F, first,
-                              h->d_scale_hook, gain_params(h->p), h->t_split_local.d, h->st));
+                              h->d_scale_hook, gain_params(h->p), nullptr, h->t_split_local.d, h->st));
     CK(cudaMemcpyAsync(h->h_split.h, h->t_split_local.d, sizeof(ytk_split), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
     *out = h->h_split.h[0];
