@@ -136,6 +136,15 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic():
+    """DRAM bytes per hist_build_k launch from the committed ncu capture (tools/summarize_ncu.py)."""
+    path = os.path.join(ROOT, "profiles", "hist_build_ncu.json")
+    try:
+        return float(json.load(open(path))["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def cpu_baseline(a, xs, ys, steps=1, threads=None):
     """The CPU restatement of the reference's path (oracle, "port") on the host cores: one
     emulated worker per core, each with its own row shard, as the Java trainer runs one
@@ -291,7 +300,8 @@ def main():
             "time_stats_ms_per_tree": {"build_hist": agg["ts_build"] / a.steps, "find_best_split": agg["ts_split"] / a.steps,
                                        "partition": agg["ts_part"] / a.steps, "total": agg["ts_total"] / a.steps},
             "roofline": {"bound": "hbm", "kernel": "hist_build_k", "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": ach / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
+                         "algorithmic_bytes_per_launch": alg / max(1, agg["built"]),
                          "algorithmic_bytes_per_step": alg / a.steps,
                          "kernel_ms_per_step": agg["gpu_hist_ms"] / a.steps,
                          "kernel_share_of_step": agg["gpu_hist_ms"] * 1e-3 / t_tree,
