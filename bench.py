@@ -247,7 +247,7 @@ def main():
     score = np.zeros(n, np.float32)
     h2d = gp.nbytes
     agg = dict(t_tree=0.0, t_e2e=0.0, cells=0.0, rows=0.0, rows_idx=0.0, built=0, gpu_hist_ms=0.0, launches=0,
-               d2h=0, nodes=0, ts_build=0.0, ts_split=0.0, ts_part=0.0, ts_total=0.0)
+               d2h=0, nodes=0, ts_build=0.0, ts_split=0.0, ts_part=0.0, ts_total=0.0, hist_launches=0)
     sampler = None
     for step in range(a.warmup + a.steps):
         sigmoid_grads(score, ys, gp)                      # the Java side's job, outside the hot path
@@ -268,6 +268,7 @@ def main():
             agg["cells"] += ts.hist_cells; agg["rows"] += ts.hist_rows; agg["rows_idx"] += ts.hist_rows_indexed
             agg["built"] += ts.hist_built; agg["gpu_hist_ms"] += ts.gpu_hist_ms
             agg["launches"] += ts.kernel_launches; agg["nodes"] = tree.n_nodes
+            agg["hist_launches"] += ts.hist_launches
             agg["ts_build"] += ts.build_hist; agg["ts_split"] += ts.find_best_split
             agg["ts_part"] += ts.partition; agg["ts_total"] += ts.total
             agg["d2h"] = sum(getattr(tree, nme).nbytes for nme, _ in yb.Tree.FIELDS)
@@ -301,11 +302,13 @@ def main():
                                        "partition": agg["ts_part"] / a.steps, "total": agg["ts_total"] / a.steps},
             "roofline": {"bound": "hbm", "kernel": "hist_build_k", "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": alg / max(1, agg["built"]),
+                         "algorithmic_bytes_per_launch": alg / max(1, agg["hist_launches"]),
+                         "kernel_us_per_launch": agg["gpu_hist_ms"] * 1e3 / max(1, agg["hist_launches"]),
                          "algorithmic_bytes_per_step": alg / a.steps,
                          "kernel_ms_per_step": agg["gpu_hist_ms"] / a.steps,
                          "kernel_share_of_step": agg["gpu_hist_ms"] * 1e-3 / t_tree,
-                         "launches_per_step": agg["built"] / a.steps},
+                         "launches_per_step": agg["hist_launches"] / a.steps,
+                         "nodes_built_per_step": agg["built"] / a.steps},
             "clocks": clocks,
         }
         if not a.no_cpu_baseline and world == 1:

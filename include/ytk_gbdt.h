@@ -86,6 +86,7 @@ typedef struct {
     double  hist_rows_indexed;/* ... of which addressed through the row-id list        */
     double  gpu_hist_ms;      /* CUDA-event time of the histogram-build kernels        */
     int32_t kernel_launches;  /* kernels launched by this call                         */
+    int32_t hist_launches;    /* ... of which histogram-build launches (one per batch) */
 } ytk_time_stats;
 
 /* One best split: SplitInfo (J/data/gbdt/SplitInfo.java:36-70) plus the node totals the

@@ -1205,6 +1205,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     T->gpu_hist_ms = gpu_ms;
     T->compute_hist = gpu_ms;
     T->kernel_launches = h->launches;
+    T->hist_launches = h->ev_used / 2;
     T->total = now_ms() - t_start;
     if (ts) *ts = *T;
     return YTK_OK;
