@@ -57,6 +57,7 @@ struct SplitSeg {
 // cseg >= 0: sample_cnt is the global row count of the smaller (which = 0) / larger (which = 1)
 // child of split segment cseg, read from the device counts
 struct ScanNode { const long long* hist; long long sample_cnt; int cseg; int which; };
+struct SplitPart { float lc; int fid, lo, hi; };     // best split of one slice of a node's features
 struct SubItem { const long long* parent; const long long* small; long long* out; };
 struct PosItem { long long begin, end; int buf; int nid; };
 
@@ -97,7 +98,9 @@ cudaError_t launch_hist_from_double(const double* in, int64_t len, const GradSca
 cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t* start, const int64_t* feat_off,
                               const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
                               const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
-                              ytk_split* out, cudaStream_t st);
+                              SplitPart* parts /* n_nodes * split_scan_slices() scratch */, ytk_split* out,
+                              cudaStream_t st);
+int split_scan_slices(int32_t f_from, int32_t f_to);
 
 // K6: stable partition of every segment by (float)bin(row,fid) < cond (or by a byte mask)
 constexpr int kPartThreads = 256;

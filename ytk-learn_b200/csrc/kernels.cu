@@ -410,26 +410,27 @@ __device__ __forceinline__ double calc_gain(const GainParams& p, double G, doubl
     return __dmul_rn(-2.0, __dadd_rn(__dadd_rn(a, b), c));
 }
 
-constexpr int kScanWarps = 32;
+constexpr int kScanWarps = 4;     // features per CTA; a node's features are spread over several CTAs (slices)
 
 __global__ void __launch_bounds__(kScanWarps * 32)
 split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ start,
              const int64_t* __restrict__ feat_off, const uint8_t* __restrict__ fea_selected,
              int32_t f_from, int32_t f_to, int32_t first_fea, const GradScale* __restrict__ scale,
-             GainParams gp, const PartitionCounts* __restrict__ cnt_global, ytk_split* __restrict__ outs) {
+             GainParams gp, const PartitionCounts* __restrict__ cnt_global, SplitPart* __restrict__ parts,
+             ytk_split* __restrict__ outs) {
     __shared__ double s_tot[2];
     __shared__ float s_lc[kScanWarps];
     __shared__ int s_fid[kScanWarps], s_lo[kScanWarps], s_hi[kScanWarps];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int node = blockIdx.x, slice = blockIdx.y;
     const double ig = scale->inv_g, ih = scale->inv_h;
-    const long long* __restrict__ hist = nodes[blockIdx.x].hist;
-    long long sample_cnt = nodes[blockIdx.x].sample_cnt;
-    if (nodes[blockIdx.x].cseg >= 0) {
-        const PartitionCounts g = cnt_global[nodes[blockIdx.x].cseg];
+    const long long* __restrict__ hist = nodes[node].hist;
+    long long sample_cnt = nodes[node].sample_cnt;
+    if (nodes[node].cseg >= 0) {
+        const PartitionCounts g = cnt_global[nodes[node].cseg];
         const long long small = g.left < g.right ? g.left : g.right;
-        sample_cnt = nodes[blockIdx.x].which == 0 ? small : (g.left + g.right - small);
+        sample_cnt = nodes[node].which == 0 ? small : (g.left + g.right - small);
     }
-    ytk_split* out = outs + blockIdx.x;
 
     if (warp == 0) {
         double G, H;
@@ -437,7 +438,10 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
             long long g = 0, h = 0;
             const long long* hp = hist + feat_off[first_fea];
             int nb = start[first_fea + 1] - start[first_fea];
-            for (int j = lane; j < nb; j += 32) { g += hp[2 * j]; h += hp[2 * j + 1]; }
+            for (int j = lane; j < nb; j += 32) {
+                longlong2 gh = *reinterpret_cast<const longlong2*>(hp + 2 * j);
+                g += gh.x; h += gh.y;
+            }
             for (int d = 16; d > 0; d >>= 1) {
                 g += __shfl_xor_sync(0xffffffffu, g, d);
                 h += __shfl_xor_sync(0xffffffffu, h, d);
@@ -456,75 +460,84 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
 
     float w_lc = -CUDART_INF_F;
     int w_fid = -1, w_lo = -1, w_hi = -1;
-    if (can_split) {
-        for (int f = f_from + warp; f < f_to; f += kScanWarps) {
-            if (!fea_selected[f]) continue;
-            const long long* hp = hist + feat_off[f];
-            const int nb = start[f + 1] - start[f];
-            long long carryG = 0, carryH = 0;
-            int carry_last = -1;
-            float b_lc = -CUDART_INF_F;
-            int b_lo = -1, b_hi = 0x7fffffff;
-            for (int c0 = 0; c0 < nb; c0 += 32) {
-                int j = c0 + lane;
-                long long g = 0, h = 0;
-                if (j < nb) {
-                    longlong2 gh = *reinterpret_cast<const longlong2*>(hp + 2 * j);
-                    g = gh.x; h = gh.y;
-                }
-                bool ne = (g | h) != 0;                                   // hasSample
-                long long pg = g, ph = h;
-                for (int d = 1; d < 32; d <<= 1) {
-                    long long tg = __shfl_up_sync(0xffffffffu, pg, d);
-                    long long th = __shfl_up_sync(0xffffffffu, ph, d);
-                    if (lane >= d) { pg += tg; ph += th; }
-                }
-                long long exG = carryG + pg - g, exH = carryH + ph - h;   // left branch before bin j
-                unsigned m = __ballot_sync(0xffffffffu, ne);
-                unsigned lower = m & ((1u << lane) - 1u);
-                int prev = lower ? (c0 + 31 - __clz(lower)) : carry_last; // lastFeaValue
-                if (ne && exH != 0) {                                      // !leftBranchGradStats.empty()
-                    double lG = (double)exG * ig, lH = (double)exH * ih;
-                    if (lH >= gp.min_child_weight) {
-                        double rG = __dsub_rn(totG, lG), rH = __dsub_rn(totH, lH);
-                        if (rH >= gp.min_child_weight) {
-                            float lc = (float)__dsub_rn(__dadd_rn(calc_gain(gp, lG, lH), calc_gain(gp, rG, rH)),
-                                                        (double)root_gain);
-                            if (lc > b_lc) { b_lc = lc; b_lo = prev; b_hi = j; }
-                        }
+    const int f = f_from + slice * kScanWarps + warp;       // one feature per warp
+    if (can_split && f < f_to && fea_selected[f]) {
+        const long long* hp = hist + feat_off[f];
+        const int nb = start[f + 1] - start[f];
+        long long carryG = 0, carryH = 0;
+        int carry_last = -1;
+        float b_lc = -CUDART_INF_F;
+        int b_lo = -1, b_hi = 0x7fffffff;
+        for (int c0 = 0; c0 < nb; c0 += 32) {
+            int j = c0 + lane;
+            long long g = 0, h = 0;
+            if (j < nb) {
+                longlong2 gh = *reinterpret_cast<const longlong2*>(hp + 2 * j);
+                g = gh.x; h = gh.y;
+            }
+            bool ne = (g | h) != 0;                                   // hasSample
+            long long pg = g, ph = h;
+            for (int d = 1; d < 32; d <<= 1) {
+                long long tg = __shfl_up_sync(0xffffffffu, pg, d);
+                long long th = __shfl_up_sync(0xffffffffu, ph, d);
+                if (lane >= d) { pg += tg; ph += th; }
+            }
+            long long exG = carryG + pg - g, exH = carryH + ph - h;   // left branch before bin j
+            unsigned m = __ballot_sync(0xffffffffu, ne);
+            unsigned lower = m & ((1u << lane) - 1u);
+            int prev = lower ? (c0 + 31 - __clz(lower)) : carry_last; // lastFeaValue
+            if (ne && exH != 0) {                                      // !leftBranchGradStats.empty()
+                double lG = (double)exG * ig, lH = (double)exH * ih;
+                if (lH >= gp.min_child_weight) {
+                    double rG = __dsub_rn(totG, lG), rH = __dsub_rn(totH, lH);
+                    if (rH >= gp.min_child_weight) {
+                        float lc = (float)__dsub_rn(__dadd_rn(calc_gain(gp, lG, lH), calc_gain(gp, rG, rH)),
+                                                    (double)root_gain);
+                        if (lc > b_lc) { b_lc = lc; b_lo = prev; b_hi = j; }
                     }
                 }
-                carryG += __shfl_sync(0xffffffffu, pg, 31);
-                carryH += __shfl_sync(0xffffffffu, ph, 31);
-                if (m) carry_last = c0 + 31 - __clz(m);
             }
-            // first (lowest bin) maximum inside the feature
-            for (int d = 16; d > 0; d >>= 1) {
-                float o_lc = __shfl_xor_sync(0xffffffffu, b_lc, d);
-                int o_lo = __shfl_xor_sync(0xffffffffu, b_lo, d);
-                int o_hi = __shfl_xor_sync(0xffffffffu, b_hi, d);
-                if (o_lc > b_lc || (o_lc == b_lc && o_hi < b_hi)) { b_lc = o_lc; b_lo = o_lo; b_hi = o_hi; }
-            }
-            // features are visited in increasing fid by this warp: strict > keeps the smaller fid
-            if (b_lc > w_lc) { w_lc = b_lc; w_fid = f; w_lo = b_lo; w_hi = b_hi; }
+            carryG += __shfl_sync(0xffffffffu, pg, 31);
+            carryH += __shfl_sync(0xffffffffu, ph, 31);
+            if (m) carry_last = c0 + 31 - __clz(m);
         }
+        // first (lowest bin) maximum inside the feature
+        for (int d = 16; d > 0; d >>= 1) {
+            float o_lc = __shfl_xor_sync(0xffffffffu, b_lc, d);
+            int o_lo = __shfl_xor_sync(0xffffffffu, b_lo, d);
+            int o_hi = __shfl_xor_sync(0xffffffffu, b_hi, d);
+            if (o_lc > b_lc || (o_lc == b_lc && o_hi < b_hi)) { b_lc = o_lc; b_lo = o_lo; b_hi = o_hi; }
+        }
+        if (b_lc > w_lc) { w_lc = b_lc; w_fid = f; w_lo = b_lo; w_hi = b_hi; }
     }
     if (lane == 0) { s_lc[warp] = w_lc; s_fid[warp] = w_fid; s_lo[warp] = w_lo; s_hi[warp] = w_hi; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        float lc = -CUDART_INF_F;
-        int fid = -1, lo = -1, hi = -1;
-        for (int w = 0; w < kScanWarps; w++) {
-            if (s_fid[w] < 0) continue;
-            if (s_lc[w] > lc || (s_lc[w] == lc && s_fid[w] < fid)) {
-                lc = s_lc[w]; fid = s_fid[w]; lo = s_lo[w]; hi = s_hi[w];
-            }
+        // warps hold increasing feature ids: strict > keeps the smaller fid on ties
+        SplitPart best = {-CUDART_INF_F, -1, -1, -1};
+        for (int w = 0; w < kScanWarps; w++)
+            if (s_fid[w] >= 0 && s_lc[w] > best.lc) best = {s_lc[w], s_fid[w], s_lo[w], s_hi[w]};
+        parts[(size_t)node * gridDim.y + slice] = best;
+        if (slice == 0) {
+            ytk_split* out = outs + node;
+            out->sum_grad = totG; out->sum_hess = totH;
+            out->root_gain = root_gain;
+            out->node_value = (float)calc_node_value(gp, totG, totH);
         }
-        out->loss_chg = lc; out->fid = fid; out->lo = lo; out->hi = hi;
-        out->sum_grad = totG; out->sum_hess = totH;
-        out->root_gain = root_gain;
-        out->node_value = (float)calc_node_value(gp, totG, totH);
     }
+}
+
+// folds the slices of every node (increasing feature ids: strict > = smallest fid wins ties)
+__global__ void split_merge_k(const SplitPart* __restrict__ parts, int n_nodes, int n_slices,
+                              ytk_split* __restrict__ outs) {
+    int node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node >= n_nodes) return;
+    SplitPart best = {-CUDART_INF_F, -1, -1, -1};
+    for (int s = 0; s < n_slices; s++) {
+        SplitPart p = parts[(size_t)node * n_slices + s];
+        if (p.fid >= 0 && p.lc > best.lc) best = p;
+    }
+    outs[node].loss_chg = best.lc; outs[node].fid = best.fid; outs[node].lo = best.lo; outs[node].hi = best.hi;
 }
 
 // ------------------------------------------------------------------------------------
@@ -828,13 +841,21 @@ cudaError_t launch_copy_segments(const long long* src, long long* const* dst, in
     return cudaGetLastError();
 }
 
+int split_scan_slices(int32_t f_from, int32_t f_to) {
+    int n = f_to - f_from;
+    return n <= 0 ? 1 : (n + kScanWarps - 1) / kScanWarps;
+}
+
 cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t* start, const int64_t* feat_off,
                               const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
                               const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
-                              ytk_split* out, cudaStream_t st) {
+                              SplitPart* parts, ytk_split* out, cudaStream_t st) {
     if (n_nodes <= 0) return cudaSuccess;
-    split_scan_k<<<n_nodes, kScanWarps * 32, 0, st>>>(nodes, start, feat_off, fea_selected, f_from, f_to, first_fea,
-                                                      scale, gp, cnt_global, out);
+    const int slices = split_scan_slices(f_from, f_to);
+    dim3 grid((unsigned)n_nodes, (unsigned)slices);
+    split_scan_k<<<grid, kScanWarps * 32, 0, st>>>(nodes, start, feat_off, fea_selected, f_from, f_to, first_fea,
+                                                   scale, gp, cnt_global, parts, out);
+    split_merge_k<<<(n_nodes + 127) / 128, 128, 0, st>>>(parts, n_nodes, slices, out);
     return cudaGetLastError();
 }
 

@@ -299,6 +299,7 @@ struct ytk_gbdt {
     DevTable<long long*> t_seg_out;
     DevTable<ytk::PartitionCounts> t_counts;     // [2*m]: local, then global (world > 1)
     DevTable<ytk_split> t_split_local, t_split_all;
+    DevTable<ytk::SplitPart> t_parts;
     DevTable<long long> t_leaf, t_hist_local, t_rs_out;
     PinnedBuf<ytk::PartitionCounts> h_counts;
     PinnedBuf<ytk_split> h_split;
@@ -348,7 +349,7 @@ void free_all(ytk_gbdt* h) {
     F(h->d_stage);
     h->t_items.release(); h->t_leaf_items.release(); h->t_segs.release(); h->t_tile_seg.release();
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
-    h->t_split_local.release(); h->t_split_all.release(); h->t_leaf.release(); h->t_hist_local.release();
+    h->t_split_local.release(); h->t_split_all.release(); h->t_parts.release(); h->t_leaf.release(); h->t_hist_local.release();
     h->t_rs_out.release();
     h->h_counts.release(); h->h_split.release(); h->h_leaf.release(); h->h_scale.release(); h->arena.release();
     for (auto* it : h->pool.all) { F(it->buf); delete it; }
@@ -488,9 +489,11 @@ int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first
     if (m == 0) return YTK_OK;
     CK(h->t_scan.upload(nodes, h->st, h->arena));
     CK(h->t_split_local.reserve(m));
+    CK(h->t_parts.reserve((size_t)m * ytk::split_scan_slices(h->f_from, h->f_to)));
     CK(ytk::launch_split_scan(h->t_scan.d, m, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to,
-                              first_owned, h->d_scale, gain_params(h->p), cnt_global, h->t_split_local.d, h->st));
-    h->launches++;
+                              first_owned, h->d_scale, gain_params(h->p), cnt_global, h->t_parts.d,
+                              h->t_split_local.d, h->st));
+    h->launches += 2;
     CK(h->h_split.reserve((size_t)m * h->world));
     if (h->world == 1) {
         CK(cudaMemcpyAsync(h->h_split.h, h->t_split_local.d, m * sizeof(ytk_split), cudaMemcpyDeviceToHost, h->st));
@@ -1327,8 +1330,9 @@ int ytk_gbdt_find_split(ytk_gbdt* h, const double* hist, int64_t sample_cnt, con
     CK(h->t_scan.upload(nodes, h->st, h->arena));
     CK(h->t_split_local.reserve(1));
     CK(h->h_split.reserve(1));
+    CK(h->t_parts.reserve((size_t)ytk::split_scan_slices(0, h->F)));
     CK(ytk::launch_split_scan(h->t_scan.d, 1, h->d_start, h->d_off_flat, h->d_fea_sel, 0, h->F, first,
-                              h->d_scale_hook, gain_params(h->p), nullptr, h->t_split_local.d, h->st));
+                              h->d_scale_hook, gain_params(h->p), nullptr, h->t_parts.d, h->t_split_local.d, h->st));
     CK(cudaMemcpyAsync(h->h_split.h, h->t_split_local.d, sizeof(ytk_split), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
     *out = h->h_split.h[0];
