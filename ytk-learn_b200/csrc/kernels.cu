@@ -468,13 +468,21 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
         int carry_last = -1;
         float b_lc = -CUDART_INF_F;
         int b_lo = -1, b_hi = 0x7fffffff;
-        for (int c0 = 0; c0 < nb; c0 += 32) {
+        // all bins of the feature are fetched up front (at most kMaxBins / 32 = 8 loads in flight)
+        // instead of one dependent memory round trip per 32-bin chunk
+        longlong2 pre[kMaxBins / 32];
+#pragma unroll
+        for (int c = 0; c < kMaxBins / 32; c++) {
+            const int j = c * 32 + lane;
+            pre[c] = make_longlong2(0, 0);
+            if (j < nb) pre[c] = *reinterpret_cast<const longlong2*>(hp + 2 * j);
+        }
+#pragma unroll
+        for (int c = 0; c < kMaxBins / 32; c++) {
+            const int c0 = c * 32;
+            if (c0 >= nb) break;
             int j = c0 + lane;
-            long long g = 0, h = 0;
-            if (j < nb) {
-                longlong2 gh = *reinterpret_cast<const longlong2*>(hp + 2 * j);
-                g = gh.x; h = gh.y;
-            }
+            long long g = pre[c].x, h = pre[c].y;
             bool ne = (g | h) != 0;                                   // hasSample
             long long pg = g, ph = h;
             for (int d = 1; d < 32; d <<= 1) {

@@ -149,7 +149,7 @@ struct PinnedArena {
                 if (h) cudaFreeHost(h);
                 h = nullptr; cap = 0;
                 size_t nc = std::max<size_t>(bytes * 2, size_t(4) << 20);
-                if (cudaHostAlloc((void**)&h, nc, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+                if (cudaHostAlloc((void**)&h, nc, cudaHostAllocMapped) != cudaSuccess) return nullptr;
                 cap = nc;
             }
         }
@@ -164,27 +164,32 @@ struct PinnedArena {
 // growable device array + host->device upload of a work table
 template <typename T>
 struct DevTable {
-    T* d = nullptr;
+    T* d = nullptr;        // what kernels are given (= own)
+    T* own = nullptr;      // the device array
     size_t cap = 0;
     cudaError_t reserve(size_t n) {
-        if (n <= cap) return cudaSuccess;
-        size_t nc = std::max<size_t>(n, cap * 2);
-        nc = std::max<size_t>(nc, 64);
-        if (d) { cudaError_t e = cudaFree(d); if (e != cudaSuccess) return e; d = nullptr; cap = 0; }
-        cudaError_t e = cudaMalloc(&d, nc * sizeof(T));
-        if (e == cudaSuccess) cap = nc;
-        return e;
+        if (n > cap) {
+            size_t nc = std::max<size_t>(n, cap * 2);
+            nc = std::max<size_t>(nc, 64);
+            if (own) { cudaError_t e = cudaFree(own); if (e != cudaSuccess) return e; own = nullptr; cap = 0; }
+            cudaError_t e = cudaMalloc(&own, nc * sizeof(T));
+            if (e != cudaSuccess) return e;
+            cap = nc;
+        }
+        d = own;
+        return cudaSuccess;
     }
     cudaError_t upload(const std::vector<T>& v, cudaStream_t st, PinnedArena& arena) {
         if (v.empty()) return cudaSuccess;
+        const size_t bytes = v.size() * sizeof(T);
+        void* stage = arena.take(bytes, st);
+        if (!stage) return cudaErrorMemoryAllocation;
+        memcpy(stage, v.data(), bytes);
         cudaError_t e = reserve(v.size());
         if (e != cudaSuccess) return e;
-        void* stage = arena.take(v.size() * sizeof(T), st);
-        if (!stage) return cudaErrorMemoryAllocation;
-        memcpy(stage, v.data(), v.size() * sizeof(T));
-        return cudaMemcpyAsync(d, stage, v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
+        return cudaMemcpyAsync(own, stage, bytes, cudaMemcpyHostToDevice, st);
     }
-    void release() { if (d) cudaFree(d); d = nullptr; cap = 0; }
+    void release() { if (own) cudaFree(own); own = d = nullptr; cap = 0; }
 };
 
 // growable pinned host array for results coming back from the device
@@ -198,7 +203,7 @@ struct PinnedBuf {
         nc = std::max<size_t>(nc, 64);
         if (h) cudaFreeHost(h);
         h = nullptr; cap = 0;
-        cudaError_t e = cudaHostAlloc((void**)&h, nc * sizeof(T), cudaHostAllocDefault);
+        cudaError_t e = cudaHostAlloc((void**)&h, nc * sizeof(T), cudaHostAllocMapped);
         if (e == cudaSuccess) cap = nc;
         return e;
     }
@@ -490,14 +495,14 @@ int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first
     CK(h->t_scan.upload(nodes, h->st, h->arena));
     CK(h->t_split_local.reserve(m));
     CK(h->t_parts.reserve((size_t)m * ytk::split_scan_slices(h->f_from, h->f_to)));
-    CK(ytk::launch_split_scan(h->t_scan.d, m, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to,
-                              first_owned, h->d_scale, gain_params(h->p), cnt_global, h->t_parts.d,
-                              h->t_split_local.d, h->st));
-    h->launches += 2;
     CK(h->h_split.reserve((size_t)m * h->world));
-    if (h->world == 1) {
-        CK(cudaMemcpyAsync(h->h_split.h, h->t_split_local.d, m * sizeof(ytk_split), cudaMemcpyDeviceToHost, h->st));
-    } else {
+    // one GPU: the records are written straight into pinned host memory (nothing on the device reads
+    // them back); several GPUs: into device memory for the allgather
+    ytk_split* rec_out = h->world == 1 ? h->h_split.h : h->t_split_local.d;
+    CK(ytk::launch_split_scan(h->t_scan.d, m, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to,
+                              first_owned, h->d_scale, gain_params(h->p), cnt_global, h->t_parts.d, rec_out, h->st));
+    h->launches += 2;
+    if (h->world > 1) {
         // "split allgather": every rank's record for each node, merged on the host with the
         // needReplace rule -- replaces allreduceRpc(SplitInfo) and allreduceArrayRpc(MAX)
         CK(h->t_split_all.reserve((size_t)m * h->world));
