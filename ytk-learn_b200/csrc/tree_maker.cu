@@ -61,6 +61,20 @@ double now_ms() {
     return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
 }
 
+// All work tables of a batch packed into one buffer: one host->device copy per batch instead of
+// one per table.
+struct Blob {
+    std::vector<char> host;
+    size_t add(const void* p, size_t bytes) {
+        size_t off = (host.size() + 255) & ~size_t(255);
+        host.resize(off + bytes);
+        if (bytes) memcpy(&host[off], p, bytes);
+        return off;
+    }
+    template <typename T>
+    size_t add(const std::vector<T>& v) { return add(v.data(), v.size() * sizeof(T)); }
+};
+
 // HistogramPool (J/data/gbdt/HistogramPool.java:190-267): bounded cache nid -> histogram.
 // Slots keep their device buffers when recycled, exactly like the Java arrays, so the
 // (degenerate) case of a parent evicted by its own child's allocation behaves as there.
@@ -311,6 +325,7 @@ struct ytk_gbdt {
     PinnedBuf<long long> h_leaf;
     PinnedBuf<ytk::GradScale> h_scale;
     PinnedArena arena;
+    char* d_blob = nullptr;  size_t blob_cap = 0;     // device side of Blob
 
     HistPool pool;
     bool grads_set = false, rows_set = false;
@@ -351,7 +366,7 @@ void free_all(ytk_gbdt* h) {
     F(h->d_mask); F(h->d_start); F(h->d_nbins); F(h->d_feat_owner); F(h->d_feat_zero); F(h->d_off_inner);
     F(h->d_off_flat); F(h->d_group_mask); F(h->d_fea_sel); F(h->d_hist_flat); F(h->d_hist_flat2);
     F(h->d_hist_dbl); F(h->d_scale); F(h->d_scale_hook); F(h->d_absmax); F(h->d_bad); F(h->d_node_of_row);
-    F(h->d_stage);
+    F(h->d_stage); F(h->d_blob);
     h->t_items.release(); h->t_leaf_items.release(); h->t_segs.release(); h->t_tile_seg.release();
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
     h->t_split_local.release(); h->t_split_all.release(); h->t_parts.release(); h->t_leaf.release(); h->t_hist_local.release();
@@ -427,79 +442,125 @@ void add_deferred_items(std::vector<ytk::RowItem>& items, const Interval& parent
 // the smaller child of split segment cseg (parent interval `parent`, children in buffer child_buf).
 struct HistJob { int nid; long long* dst; int cseg; Interval parent; int child_buf; };
 
+// one host->device copy of a Blob; afterwards table at offset o lives at h->d_blob + o
+int blob_commit(ytk_gbdt* h, const Blob& bl) {
+    const size_t bytes = bl.host.size();
+    if (bytes == 0) return YTK_OK;
+    if (bytes > h->blob_cap) {
+        if (h->d_blob) CK(cudaFree(h->d_blob));          // (synchronises: nobody reads the old one any more)
+        h->d_blob = nullptr; h->blob_cap = 0;
+        size_t nc = std::max<size_t>(bytes * 2, size_t(1) << 20);
+        CK(cudaMalloc(&h->d_blob, nc));
+        h->blob_cap = nc;
+    }
+    void* stage = h->arena.take(bytes, h->st);
+    if (!stage) return fail(YTK_ERR_CUDA, "pinned staging allocation failed");
+    memcpy(stage, bl.host.data(), bytes);
+    CK(cudaMemcpyAsync(h->d_blob, stage, bytes, cudaMemcpyHostToDevice, h->st));
+    return YTK_OK;
+}
+template <typename T>
+const T* blob_ptr(const ytk_gbdt* h, size_t off) { return reinterpret_cast<const T*>(h->d_blob + off); }
+
+// ---- histogram build: plan (host tables) / enqueue (launches) ----------------------------------
+struct HistPlan {
+    int m = 0;
+    std::vector<ytk::RowItem> items;
+    std::vector<long long*> outs_local;    // where the kernel accumulates (the slot, or the local pre-reduce buffer)
+    std::vector<long long*> outs_final;    // world > 1: the slots the reduce-scatter result is copied to
+    size_t o_items = 0, o_local = 0, o_final = 0;
+};
+
 // HistogramBuilder.buildHist (J/data/gbdt/HistogramBuilder.java:56-98) for a batch of nodes:
 // one kernel launch over all their rows, then (world > 1) one reduce-scatter by feature range.
-int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, int n_sel,
-                const ytk::PartitionCounts* cnt_local, const ytk::PartitionCounts* cnt_global) {
-    const int m = (int)jobs.size();
+int hist_plan(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, int n_sel, HistPlan& pl, Blob& bl) {
+    const int m = pl.m = (int)jobs.size();
     if (m == 0) return YTK_OK;
     int64_t total = 0;
     for (auto& j : jobs) total += j.cseg < 0 ? h->iv[j.nid].e - h->iv[j.nid].b : (j.parent.e - j.parent.b) / 2;
     const int64_t rpi = ytk::hist_rows_per_item(total, h->groups);
-    std::vector<ytk::RowItem> items;
-    std::vector<long long*> outs(m);
+    pl.outs_local.resize(m);
     const int64_t local_len = h->seg_max * h->world;
     if (h->world > 1) CK(h->t_hist_local.reserve((size_t)m * local_len));
     for (int k = 0; k < m; k++) {
         if (jobs[k].cseg < 0) {
             const Interval& v = h->iv[jobs[k].nid];
-            add_row_items(items, v, k, rpi);
+            add_row_items(pl.items, v, k, rpi);
             T->hist_built++;
             T->hist_cells += (double)(v.e - v.b) * n_sel;
             T->hist_rows += (double)(v.e - v.b);
             if (v.buf >= 0) T->hist_rows_indexed += (double)(v.e - v.b);
         } else {
-            add_deferred_items(items, jobs[k].parent, jobs[k].child_buf, k, jobs[k].cseg, rpi, h->world);
+            add_deferred_items(pl.items, jobs[k].parent, jobs[k].child_buf, k, jobs[k].cseg, rpi, h->world);
         }
         // world > 1: local layout [rank][node][segment] so that ONE reduce-scatter serves the batch
-        outs[k] = h->world == 1 ? jobs[k].dst : h->t_hist_local.d + (int64_t)k * h->seg_max;
+        pl.outs_local[k] = h->world == 1 ? jobs[k].dst : h->t_hist_local.d + (int64_t)k * h->seg_max;
     }
+    pl.o_items = bl.add(pl.items);
+    pl.o_local = bl.add(pl.outs_local);
+    if (h->world > 1) {
+        pl.outs_final.resize(m);
+        for (int k = 0; k < m; k++) pl.outs_final[k] = jobs[k].dst;
+        pl.o_final = bl.add(pl.outs_final);
+    }
+    return YTK_OK;
+}
+
+int hist_enqueue(ytk_gbdt* h, const HistPlan& pl, ytk_time_stats* T, const ytk::PartitionCounts* cnt_local,
+                 const ytk::PartitionCounts* cnt_global) {
+    const int m = pl.m;
+    if (m == 0) return YTK_OK;
+    const int64_t local_len = h->seg_max * h->world;
+    long long* const* d_local = blob_ptr<long long*>(h, pl.o_local);
     cudaEvent_t e0, e1;
     RET(hist_events(h, &e0, &e1));
-    CK(h->t_items.upload(items, h->st, h->arena));
-    CK(h->t_seg_out.upload(outs, h->st, h->arena));
     if (h->world == 1) {
-        CK(ytk::launch_zero_segments(h->t_seg_out.d, m, h->seg_max, h->st));
+        CK(ytk::launch_zero_segments(d_local, m, h->seg_max, h->st));
         h->launches++;
     } else {
         CK(cudaMemsetAsync(h->t_hist_local.d, 0, (size_t)m * local_len * sizeof(long long), h->st));
     }
     CK(cudaEventRecord(e0, h->st));        // the pair brackets the hist_build_k launch only
     const long long owner_stride = h->world == 1 ? 0 : (long long)m * h->seg_max;
-    CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_items.d,
-                              (int)items.size(), h->F, h->d_group_mask, h->d_nbins, h->d_feat_owner, h->d_off_inner,
-                              owner_stride, h->t_seg_out.d, cnt_local, cnt_global, h->st));
-    if (!items.empty()) h->launches++;
+    CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1],
+                              blob_ptr<ytk::RowItem>(h, pl.o_items), (int)pl.items.size(), h->F, h->d_group_mask,
+                              h->d_nbins, h->d_feat_owner, h->d_off_inner, owner_stride, d_local, cnt_local, cnt_global,
+                              h->st));
+    if (!pl.items.empty()) h->launches++;
     CK(cudaEventRecord(e1, h->st));
     if (h->world > 1) {
         double t0 = now_ms();
         CK(h->t_rs_out.reserve((size_t)m * h->seg_max));
         NK(ytk::nccl_api().ReduceScatter(h->t_hist_local.d, h->t_rs_out.d, (size_t)m * h->seg_max, ncclInt64,
                                          ncclSum, h->comm, h->st));
-        for (int k = 0; k < m; k++) outs[k] = jobs[k].dst;
-        CK(h->t_seg_out.upload(outs, h->st, h->arena));
-        CK(ytk::launch_copy_segments(h->t_rs_out.d, h->t_seg_out.d, m, h->seg_max, h->st));
+        CK(ytk::launch_copy_segments(h->t_rs_out.d, blob_ptr<long long*>(h, pl.o_final), m, h->seg_max, h->st));
         h->launches++;
         T->communicate_hist += now_ms() - t0;
     }
     return YTK_OK;
 }
 
+int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, int n_sel,
+                const ytk::PartitionCounts* cnt_local, const ytk::PartitionCounts* cnt_global) {
+    HistPlan pl; Blob bl;
+    RET(hist_plan(h, jobs, T, n_sel, pl, bl));
+    RET(blob_commit(h, bl));
+    return hist_enqueue(h, pl, T, cnt_local, cnt_global);
+}
+
+// ---- split search: enqueue / collect ---------------------------------------------------------------
 // updateTreeMakerNodeStats + findBestSplit(nid, hist) + syncBestSplit (:543-595, :640-653) for a
-// batch of nodes; the merged record of node k lands in recs[k].
-int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first_owned, std::vector<ytk_split>& recs,
-                 const ytk::PartitionCounts* cnt_global = nullptr) {
-    const int m = (int)nodes.size();
-    recs.resize(m);
+// batch of nodes; after the stream has been synchronised the merged record of node k is recs[k].
+int search_enqueue(ytk_gbdt* h, const ytk::ScanNode* d_nodes, int m, int first_owned,
+                   const ytk::PartitionCounts* cnt_global) {
     if (m == 0) return YTK_OK;
-    CK(h->t_scan.upload(nodes, h->st, h->arena));
     CK(h->t_split_local.reserve(m));
     CK(h->t_parts.reserve((size_t)m * ytk::split_scan_slices(h->f_from, h->f_to)));
     CK(h->h_split.reserve((size_t)m * h->world));
     // one GPU: the records are written straight into pinned host memory (nothing on the device reads
     // them back); several GPUs: into device memory for the allgather
     ytk_split* rec_out = h->world == 1 ? h->h_split.h : h->t_split_local.d;
-    CK(ytk::launch_split_scan(h->t_scan.d, m, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to,
+    CK(ytk::launch_split_scan(d_nodes, m, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to,
                               first_owned, h->d_scale, gain_params(h->p), cnt_global, h->t_parts.d, rec_out, h->st));
     h->launches += 2;
     if (h->world > 1) {
@@ -511,8 +572,10 @@ int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first
         CK(cudaMemcpyAsync(h->h_split.h, h->t_split_all.d, (size_t)h->world * m * sizeof(ytk_split),
                            cudaMemcpyDeviceToHost, h->st));
     }
-    CK(cudaStreamSynchronize(h->st));
-    h->arena.rewind();
+    return YTK_OK;
+}
+void search_collect(ytk_gbdt* h, int m, std::vector<ytk_split>& recs) {
+    recs.resize(m);
     if (h->world == 1) {
         for (int k = 0; k < m; k++) recs[k] = h->h_split.h[k];
     } else {
@@ -522,6 +585,19 @@ int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first
             ytk_gbdt_merge_splits(tmp.data(), h->world, &recs[k]);
         }
     }
+}
+int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first_owned, std::vector<ytk_split>& recs,
+                 const ytk::PartitionCounts* cnt_global = nullptr) {
+    const int m = (int)nodes.size();
+    recs.resize(m);
+    if (m == 0) return YTK_OK;
+    Blob bl;
+    const size_t o = bl.add(nodes);
+    RET(blob_commit(h, bl));
+    RET(search_enqueue(h, blob_ptr<ytk::ScanNode>(h, o), m, first_owned, cnt_global));
+    CK(cudaStreamSynchronize(h->st));
+    h->arena.rewind();
+    search_collect(h, m, recs);
     return YTK_OK;
 }
 
@@ -532,33 +608,43 @@ void apply_record(NodeStats& s, const ytk_split& r) {
 }
 
 // position.resetPosition (SamplePositionData.java:115-133) for a batch of nodes, plus the global
-// child counts of initTreeMakerNodeStats(l, r) (:522-541).  Queues the kernels, the count allreduce
-// and the copy of the counts to the host; does not wait.  Device counts: t_counts.d[0..m) local,
-// [m..2m) global (world > 1).
-int partition_launch(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const std::vector<ytk::SplitSeg>& segs_in) {
-    const int m = (int)segs_in.size();
-    if (m == 0) return YTK_OK;
-    std::vector<ytk::SplitSeg> segs = segs_in;
+// child counts of initTreeMakerNodeStats(l, r) (:522-541).
+struct PartPlan {
+    int m = 0;
+    std::vector<ytk::SplitSeg> segs;
     std::vector<int> tile_seg;
-    for (int k = 0; k < m; k++) {
-        int64_t n = segs[k].end - segs[k].begin;
+    size_t o_segs = 0, o_tiles = 0;
+};
+void partition_plan(const std::vector<ytk::SplitSeg>& segs_in, PartPlan& pl, Blob& bl) {
+    pl.m = (int)segs_in.size();
+    pl.segs = segs_in;
+    for (int k = 0; k < pl.m; k++) {
+        int64_t n = pl.segs[k].end - pl.segs[k].begin;
         int nt = (int)((n + ytk::kPartTile - 1) / ytk::kPartTile);
-        segs[k].tile0 = (int)tile_seg.size();
-        segs[k].ntiles = nt;
-        for (int t = 0; t < nt; t++) tile_seg.push_back(k);
+        pl.segs[k].tile0 = (int)pl.tile_seg.size();
+        pl.segs[k].ntiles = nt;
+        for (int t = 0; t < nt; t++) pl.tile_seg.push_back(k);
     }
-    if (tile_seg.size() + 1 > h->block_cnt_cap) {
+    pl.o_segs = bl.add(pl.segs);
+    pl.o_tiles = bl.add(pl.tile_seg);
+}
+// Queues the kernels, the count allreduce and the copy of the counts to the host; does not wait.
+// Device counts: t_counts.d[0..m) local, [m..2m) global (world > 1).
+int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const PartPlan& pl) {
+    const int m = pl.m;
+    if (m == 0) return YTK_OK;
+    const size_t n_tiles = pl.tile_seg.size();
+    if (n_tiles + 1 > h->block_cnt_cap) {
         if (h->d_block_cnt) CK(cudaFree(h->d_block_cnt));
         h->d_block_cnt = nullptr;
-        h->block_cnt_cap = std::max<size_t>(tile_seg.size() + 1, 2 * h->block_cnt_cap);
+        h->block_cnt_cap = std::max<size_t>(n_tiles + 1, 2 * h->block_cnt_cap);
         CK(cudaMalloc(&h->d_block_cnt, h->block_cnt_cap * sizeof(int32_t)));
     }
-    CK(h->t_segs.upload(segs, h->st, h->arena));
-    CK(h->t_tile_seg.upload(tile_seg, h->st, h->arena));
     CK(h->t_counts.reserve(2 * (size_t)m));
-    CK(ytk::launch_partition(src, h->S8, col_stride, h->d_rowidx[0], h->d_rowidx[1], h->t_segs.d, m, h->t_tile_seg.d,
-                             (int)tile_seg.size(), h->d_flags, h->d_block_cnt, h->t_counts.d, h->st));
-    h->launches += tile_seg.empty() ? 1 : 3;
+    CK(ytk::launch_partition(src, h->S8, col_stride, h->d_rowidx[0], h->d_rowidx[1],
+                             blob_ptr<ytk::SplitSeg>(h, pl.o_segs), m, blob_ptr<int>(h, pl.o_tiles), (int)n_tiles,
+                             h->d_flags, h->d_block_cnt, h->t_counts.d, h->st));
+    h->launches += n_tiles == 0 ? 1 : 3;
     const int nc = h->world > 1 ? 2 * m : m;
     if (h->world > 1)   // allreduceArray(long[2], SUM) (:538), all nodes of the batch at once
         NK(ytk::nccl_api().AllReduce(h->t_counts.d, h->t_counts.d + m, 2 * (size_t)m, ncclInt64, ncclSum, h->comm,
@@ -567,6 +653,13 @@ int partition_launch(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const 
     CK(cudaMemcpyAsync(h->h_counts.h, h->t_counts.d, nc * sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost,
                        h->st));
     return YTK_OK;
+}
+int partition_launch(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const std::vector<ytk::SplitSeg>& segs_in) {
+    if (segs_in.empty()) return YTK_OK;
+    PartPlan pl; Blob bl;
+    partition_plan(segs_in, pl, bl);
+    RET(blob_commit(h, bl));
+    return partition_enqueue(h, src, col_stride, pl);
 }
 // after the stream has been synchronised
 void partition_collect(ytk_gbdt* h, int m, std::vector<ytk::PartitionCounts>& local,
@@ -1068,8 +1161,15 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
                     jobs[k].terminal = true;
             }
         };
-        RET(partition_launch(h, h->d_bins_col, h->N, segs));
+        // every work table of the batch goes up in one copy (two when the host must see the counts first)
+        Blob bl_part, bl_rest;
+        Blob& bl = deferred ? bl_part : bl_rest;
+        PartPlan pp;
+        partition_plan(segs, pp, bl_part);
+        CK(h->t_counts.reserve(2 * (size_t)m));     // its address is handed to the kernels queued below
         if (!deferred) {
+            RET(blob_commit(h, bl_part));
+            RET(partition_enqueue(h, h->d_bins_col, h->N, pp));
             CK(cudaStreamSynchronize(h->st));
             h->arena.rewind();
             finish_partition();
@@ -1138,13 +1238,17 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             }
             scan_job.push_back(k);
         }
+        HistPlan hp;
+        RET(hist_plan(h, hist_jobs, T, n_sel, hp, bl));
+        const size_t o_leaf = bl.add(leaf_items), o_subs = bl.add(subs), o_scans = bl.add(scans);
+        RET(blob_commit(h, bl));
+        if (deferred) RET(partition_enqueue(h, h->d_bins_col, h->N, pp));
         if (n_leaf_jobs > 0) {
             CK(h->t_leaf.reserve(2 * (size_t)n_leaf_jobs));
             CK(h->h_leaf.reserve(2 * (size_t)n_leaf_jobs));
             CK(cudaMemsetAsync(h->t_leaf.d, 0, 2 * (size_t)n_leaf_jobs * sizeof(long long), h->st));
-            CK(h->t_leaf_items.upload(leaf_items, h->st, h->arena));
-            CK(ytk::launch_leaf_sums(h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_leaf_items.d, (int)leaf_items.size(),
-                                     h->t_leaf.d, d_cl, d_cg, h->st));
+            CK(ytk::launch_leaf_sums(h->d_gq, h->d_rowidx[0], h->d_rowidx[1], blob_ptr<ytk::RowItem>(h, o_leaf),
+                                     (int)leaf_items.size(), h->t_leaf.d, d_cl, d_cg, h->st));
             if (!leaf_items.empty()) h->launches++;
             if (h->world > 1)      // allreduceArray(double[2], SUM) (:375), exact in the integer domain
                 NK(ytk::nccl_api().AllReduce(h->t_leaf.d, h->t_leaf.d, 2 * (size_t)n_leaf_jobs, ncclInt64, ncclSum,
@@ -1152,15 +1256,16 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             CK(cudaMemcpyAsync(h->h_leaf.h, h->t_leaf.d, 2 * (size_t)n_leaf_jobs * sizeof(long long),
                                cudaMemcpyDeviceToHost, h->st));
         }
-        RET(build_hists(h, hist_jobs, T, n_sel, d_cl, d_cg));
+        RET(hist_enqueue(h, hp, T, d_cl, d_cg));
         if (!subs.empty()) {
-            CK(h->t_sub.upload(subs, h->st, h->arena));
-            CK(ytk::launch_hist_subtract(h->t_sub.d, (int)subs.size(), h->seg_max, h->st));
+            CK(ytk::launch_hist_subtract(blob_ptr<ytk::SubItem>(h, o_subs), (int)subs.size(), h->seg_max, h->st));
             h->launches++;
         }
         double t1 = now_ms();
-        RET(search_nodes(h, scans, first_owned, recs, d_cg));     // synchronises the stream
-        if (scans.empty()) { CK(cudaStreamSynchronize(h->st)); h->arena.rewind(); }
+        RET(search_enqueue(h, blob_ptr<ytk::ScanNode>(h, o_scans), (int)scans.size(), first_owned, d_cg));
+        CK(cudaStreamSynchronize(h->st));            // the one host wait of the batch
+        h->arena.rewind();
+        search_collect(h, (int)scans.size(), recs);
         if (deferred) finish_partition();
         for (size_t i = 0; i < scan_job.size(); i++) {
             const SplitJob& j = jobs[scan_job[i]];
