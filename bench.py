@@ -247,7 +247,7 @@ def main():
     score = np.zeros(n, np.float32)
     h2d = gp.nbytes
     agg = dict(t_tree=0.0, t_e2e=0.0, cells=0.0, rows=0.0, rows_idx=0.0, built=0, gpu_hist_ms=0.0, launches=0,
-               d2h=0, nodes=0, ts_build=0.0, ts_split=0.0, ts_part=0.0, ts_total=0.0, hist_launches=0)
+               d2h=0, nodes=0, ts_build=0.0, ts_split=0.0, ts_part=0.0, ts_total=0.0, hist_launches=0, ts_comm=0.0)
     sampler = None
     for step in range(a.warmup + a.steps):
         sigmoid_grads(score, ys, gp)                      # the Java side's job, outside the hot path
@@ -257,6 +257,8 @@ def main():
         barrier()
         t0 = time.perf_counter()
         tm.set_grads_ptr(gp_pinned.data_ptr(), 0, n)      # H2D from pinned memory
+        th = time.perf_counter()
+        barrier()                                          # ranks finish their copies at different times
         t1 = time.perf_counter()
         tree = tm.make(0)                                  # returns with the tree on the host
         t2 = time.perf_counter()
@@ -264,13 +266,13 @@ def main():
         pos = tm.get_positions()
         score += tree.node_info[pos]
         if timed:
-            agg["t_tree"] += t2 - t1; agg["t_e2e"] += t2 - t0
+            agg["t_tree"] += t2 - t1; agg["t_e2e"] += (th - t0) + (t2 - t1)
             agg["cells"] += ts.hist_cells; agg["rows"] += ts.hist_rows; agg["rows_idx"] += ts.hist_rows_indexed
             agg["built"] += ts.hist_built; agg["gpu_hist_ms"] += ts.gpu_hist_ms
             agg["launches"] += ts.kernel_launches; agg["nodes"] = tree.n_nodes
             agg["hist_launches"] += ts.hist_launches
             agg["ts_build"] += ts.build_hist; agg["ts_split"] += ts.find_best_split
-            agg["ts_part"] += ts.partition; agg["ts_total"] += ts.total
+            agg["ts_part"] += ts.partition; agg["ts_total"] += ts.total; agg["ts_comm"] += ts.communicate_hist
             agg["d2h"] = sum(getattr(tree, nme).nbytes for nme, _ in yb.Tree.FIELDS)
     barrier()
     clocks = sampler.stop() if sampler else None
@@ -299,7 +301,8 @@ def main():
                     "d2h_bytes_per_step": agg["d2h"], "seconds_per_tree": t_e2e / a.steps},
             "gpu_launches": agg["launches"],
             "time_stats_ms_per_tree": {"build_hist": agg["ts_build"] / a.steps, "find_best_split": agg["ts_split"] / a.steps,
-                                       "partition": agg["ts_part"] / a.steps, "total": agg["ts_total"] / a.steps},
+                                       "partition": agg["ts_part"] / a.steps, "total": agg["ts_total"] / a.steps,
+                                       "collectives_gpu": agg["ts_comm"] / a.steps},
             "roofline": {"bound": "hbm", "kernel": "hist_build_k", "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg / max(1, agg["hist_launches"]),

@@ -334,6 +334,8 @@ struct ytk_gbdt {
     int launches = 0;
     std::vector<cudaEvent_t> ev;       // event pairs around histogram builds
     int ev_used = 0;
+    std::vector<cudaEvent_t> evc;      // event pairs around collectives (world > 1)
+    int evc_used = 0;
 };
 
 namespace {
@@ -374,6 +376,7 @@ void free_all(ytk_gbdt* h) {
     h->h_counts.release(); h->h_split.release(); h->h_leaf.release(); h->h_scale.release(); h->arena.release();
     for (auto* it : h->pool.all) { F(it->buf); delete it; }
     for (auto e : h->ev) cudaEventDestroy(e);
+    for (auto e : h->evc) cudaEventDestroy(e);
     if (h->comm) ytk::nccl_api().CommDestroy(h->comm);
     if (h->st) cudaStreamDestroy(h->st);
 }
@@ -417,6 +420,17 @@ int hist_events(ytk_gbdt* h, cudaEvent_t* a, cudaEvent_t* b) {
     }
     *a = h->ev[h->ev_used]; *b = h->ev[h->ev_used + 1];
     h->ev_used += 2;
+    return YTK_OK;
+}
+
+// brackets a collective with an event pair (summed into communicate_hist at the end of make())
+int comm_mark(ytk_gbdt* h) {
+    if (h->evc_used + 1 > (int)h->evc.size()) {
+        cudaEvent_t e;
+        CK(cudaEventCreate(&e));
+        h->evc.push_back(e);
+    }
+    CK(cudaEventRecord(h->evc[h->evc_used++], h->st));
     return YTK_OK;
 }
 
@@ -529,13 +543,13 @@ int hist_enqueue(ytk_gbdt* h, const HistPlan& pl, ytk_time_stats* T, const ytk::
     if (!pl.items.empty()) h->launches++;
     CK(cudaEventRecord(e1, h->st));
     if (h->world > 1) {
-        double t0 = now_ms();
         CK(h->t_rs_out.reserve((size_t)m * h->seg_max));
+        RET(comm_mark(h));
         NK(ytk::nccl_api().ReduceScatter(h->t_hist_local.d, h->t_rs_out.d, (size_t)m * h->seg_max, ncclInt64,
                                          ncclSum, h->comm, h->st));
         CK(ytk::launch_copy_segments(h->t_rs_out.d, blob_ptr<long long*>(h, pl.o_final), m, h->seg_max, h->st));
+        RET(comm_mark(h));
         h->launches++;
-        T->communicate_hist += now_ms() - t0;
     }
     return YTK_OK;
 }
@@ -567,8 +581,10 @@ int search_enqueue(ytk_gbdt* h, const ytk::ScanNode* d_nodes, int m, int first_o
         // "split allgather": every rank's record for each node, merged on the host with the
         // needReplace rule -- replaces allreduceRpc(SplitInfo) and allreduceArrayRpc(MAX)
         CK(h->t_split_all.reserve((size_t)m * h->world));
+        RET(comm_mark(h));
         NK(ytk::nccl_api().AllGather(h->t_split_local.d, h->t_split_all.d, m * sizeof(ytk_split), ncclChar, h->comm,
                                      h->st));
+        RET(comm_mark(h));
         CK(cudaMemcpyAsync(h->h_split.h, h->t_split_all.d, (size_t)h->world * m * sizeof(ytk_split),
                            cudaMemcpyDeviceToHost, h->st));
     }
@@ -646,9 +662,12 @@ int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const
                              h->d_flags, h->d_block_cnt, h->t_counts.d, h->st));
     h->launches += n_tiles == 0 ? 1 : 3;
     const int nc = h->world > 1 ? 2 * m : m;
-    if (h->world > 1)   // allreduceArray(long[2], SUM) (:538), all nodes of the batch at once
+    if (h->world > 1) {   // allreduceArray(long[2], SUM) (:538), all nodes of the batch at once
+        RET(comm_mark(h));
         NK(ytk::nccl_api().AllReduce(h->t_counts.d, h->t_counts.d + m, 2 * (size_t)m, ncclInt64, ncclSum, h->comm,
                                      h->st));
+        RET(comm_mark(h));
+    }
     CK(h->h_counts.reserve(nc));
     CK(cudaMemcpyAsync(h->h_counts.h, h->t_counts.d, nc * sizeof(ytk::PartitionCounts), cudaMemcpyDeviceToHost,
                        h->st));
@@ -991,6 +1010,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     ytk_time_stats* T = &local_ts;
     h->launches = 0;
     h->ev_used = 0;
+    h->evc_used = 0;
     const bool loss_wise = p.grow_policy == 1;
     const float lr = p.learning_rate;
     // The reference's pool never evicts when it holds max_leaf_cnt histograms (its own allocation
@@ -1315,6 +1335,13 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         CK(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
         gpu_ms += ms;
     }
+    float comm_ms = 0.f;
+    for (int i = 0; i + 1 < h->evc_used; i += 2) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, h->evc[i], h->evc[i + 1]));
+        comm_ms += ms;
+    }
+    T->communicate_hist = comm_ms;     // CUDA-event time of the collectives (stream time, includes waiting for peers)
     T->gpu_hist_ms = gpu_ms;
     T->compute_hist = gpu_ms;
     T->kernel_launches = h->launches;
