@@ -277,12 +277,27 @@ def main():
     barrier()
     clocks = sampler.stop() if sampler else None
 
-    vals = torch.tensor([agg["t_tree"], agg["t_e2e"]], dtype=torch.float64, device="cuda")
+    # SURVEY.md §8(f) row 1, for information: whole boosting rounds with the gradients computed on the
+    # device (score update + loss/gradients + make), nothing but the tree crossing PCIe
+    tm.set_targets("sigmoid", ys)
+    tm.compute_grads()
+    dev_round = 0.0
+    for step in range(2 + a.steps):
+        barrier()
+        t0 = time.perf_counter()
+        tm.make(0)
+        tm.update_scores(0)
+        tm.compute_grads()
+        if step >= 2:
+            dev_round += time.perf_counter() - t0
+    barrier()
+
+    vals = torch.tensor([agg["t_tree"], agg["t_e2e"], dev_round], dtype=torch.float64, device="cuda")
     sums = torch.tensor([agg["cells"]], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(vals, op=dist.ReduceOp.MAX)
         dist.all_reduce(sums, op=dist.ReduceOp.SUM)
-    t_tree, t_e2e = vals.tolist()
+    t_tree, t_e2e, dev_round = vals.tolist()
     cells_all = float(sums.item())
 
     if rank == 0:
@@ -299,6 +314,8 @@ def main():
             "seconds_per_tree": t_tree / a.steps, "nodes_per_tree": agg["nodes"],
             "e2e": {"value": cells_all / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": agg["d2h"], "seconds_per_tree": t_e2e / a.steps},
+            "device_gradient_round": {"ms_per_round": dev_round / a.steps * 1e3,
+                                      "what": "make + score update + sigmoid loss/gradients, all on the device"},
             "gpu_launches": agg["launches"],
             "time_stats_ms_per_tree": {"build_hist": agg["ts_build"] / a.steps, "find_best_split": agg["ts_split"] / a.steps,
                                        "partition": agg["ts_part"] / a.steps, "total": agg["ts_total"] / a.steps,

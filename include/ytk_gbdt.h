@@ -188,6 +188,33 @@ int ytk_gbdt_find_split(ytk_gbdt *h, const double *hist, int64_t sample_cnt,
 int ytk_gbdt_partition_rows(ytk_gbdt *h, const int32_t *rows, int64_t n_rows, int32_t fid,
                             float cond, int32_t *out_rows, int64_t *left_cnt);
 
+/* ---- the step either side of make(), kept on the device -------------------
+ * GBDTOptimizer.predictAndCalcLossGrad, train branch (J/optimizer/GBDTOptimizer.java:513-609): score
+ * update from the trees just made, loss, and the next round's gradient pairs, without the (g,h) arrays
+ * crossing PCIe every round.  Optional: a trainer that keeps computing gradients in Java simply keeps
+ * calling ytk_gbdt_set_grads. */
+typedef enum { YTK_LOSS_SIGMOID = 0, YTK_LOSS_L2 = 1, YTK_LOSS_SOFTMAX = 2 } ytk_loss;
+
+/* GBDTCoreData.y / weight / initScore (J/dataflow/GBDTCoreData.java:286-296,424-447): y has N*K floats
+ * (K > 1: one-hot rows), weight N floats (NULL = 1), init_score N*K floats (NULL = 0).  Resets the
+ * device score buffer to 0 (a new training run). */
+int ytk_gbdt_set_targets(ytk_gbdt *h, int32_t loss, const float *y, const float *weight, const float *init_score);
+
+/* score(data, sid, gid, ...) (J/optimizer/GBDTOptimizer.java:641-658) for the tree the last
+ * ytk_gbdt_make_tree(gid) built: score[row*K+gid] += leaf value (float).  Sampled rows take the leaf
+ * the partition left them in; rows excluded by row_mask walk the tree on their slots (`<=`,
+ * J/data/gbdt/Tree.java:156-168). */
+int ytk_gbdt_update_scores(ytk_gbdt *h, int32_t gid);
+
+/* The loss/gradient loop of predictAndCalcLossGrad (:536-607) with SigmoidFunction / L2Function /
+ * SoftmaxFunction (J/loss/SigmoidFunction.java, L2Function.java, SoftmaxFunction.java): rewrites the device gradient pairs (as ytk_gbdt_set_grads would)
+ * and returns sum_i w_i * loss_i over the local rows. */
+int ytk_gbdt_compute_grads(ytk_gbdt *h, double *loss_sum);
+
+/* Read back the device score (N*K floats) / gradient pairs (N*K*2 floats). */
+int ytk_gbdt_get_scores(ytk_gbdt *h, float *out);
+int ytk_gbdt_get_grads(ytk_gbdt *h, float *out);
+
 /* No counterpart in the reference: an addition for hosts that must not allocate device memory
  * (all of it belongs to their own pool, or the hidden device-wide synchronisation of
  * cudaMalloc/cudaFree is not acceptable where they call from).  Same operation and same kernels

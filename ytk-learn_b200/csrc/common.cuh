@@ -60,6 +60,8 @@ struct ScanNode { const long long* hist; long long sample_cnt; int cseg; int whi
 struct SplitPart { float lc; int fid, lo, hi; };     // best split of one slice of a node's features
 struct SubItem { const long long* parent; const long long* small; long long* out; };
 struct PosItem { long long begin, end; int buf; int nid; };
+struct LeafItem { long long begin, end; int buf; float value; };      // rows of one leaf and its value
+struct TreeNodeDev { int left, right, fid; float info; };             // device copy of a tree for row walks
 
 // ---- launchers (kernels.cu); all asynchronous on `st`, return cudaGetLastError() ----
 
@@ -121,5 +123,15 @@ cudaError_t launch_fill_positions(const int32_t* rowidx0, const int32_t* rowidx1
 cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st);
 cudaError_t launch_zero_segments(long long* const* dst, int n, int64_t len, cudaStream_t st);
 cudaError_t launch_copy_segments(const long long* src, long long* const* dst, int n, int64_t len, cudaStream_t st);
+
+// §8(f) row 1: score update + loss + gradient pairs on the device
+cudaError_t launch_add_leaf_values(const int32_t* rowidx0, const int32_t* rowidx1, const LeafItem* items, int n_items,
+                                   float* score, int32_t K, int32_t gid, cudaStream_t st);
+cudaError_t launch_walk_rows(const uint8_t* bins, int32_t S8, const int32_t* rows, long long begin, long long end,
+                             const TreeNodeDev* nodes, float* score, int32_t K, int32_t gid, cudaStream_t st);
+int loss_grad_blocks();
+// loss_kind 0 sigmoid, 1 l2, 2 softmax (y one-hot [n][K]); block_loss: loss_grad_blocks() doubles of scratch
+cudaError_t launch_loss_grad(int loss_kind, const float* score, const float* init, const float* y, const float* w,
+                             long long n, int32_t K, float* gp, double* block_loss, double* loss_out, cudaStream_t st);
 
 }  // namespace ytk

@@ -327,6 +327,16 @@ struct ytk_gbdt {
     PinnedArena arena;
     char* d_blob = nullptr;  size_t blob_cap = 0;     // device side of Blob
 
+    // §8(f) row 1 state
+    float* d_score = nullptr; float* d_y = nullptr; float* d_w = nullptr; float* d_init = nullptr;
+    double* d_block_loss = nullptr; double* d_loss = nullptr;
+    int loss_kind = -1;
+    std::vector<ytk::TreeNodeDev> last_tree;
+    int last_gid = -1;
+    int64_t unsampled_begin = -1;      // rows rowidx[0][unsampled_begin, N) were excluded by row_mask
+    DevTable<ytk::LeafItem> t_leafval;
+    DevTable<ytk::TreeNodeDev> t_tree;
+
     HistPool pool;
     bool grads_set = false, rows_set = false;
     std::vector<Interval> iv;          // last tree: interval of every node
@@ -368,7 +378,8 @@ void free_all(ytk_gbdt* h) {
     F(h->d_mask); F(h->d_start); F(h->d_nbins); F(h->d_feat_owner); F(h->d_feat_zero); F(h->d_off_inner);
     F(h->d_off_flat); F(h->d_group_mask); F(h->d_fea_sel); F(h->d_hist_flat); F(h->d_hist_flat2);
     F(h->d_hist_dbl); F(h->d_scale); F(h->d_scale_hook); F(h->d_absmax); F(h->d_bad); F(h->d_node_of_row);
-    F(h->d_stage); F(h->d_blob);
+    F(h->d_stage); F(h->d_blob); F(h->d_score); F(h->d_y); F(h->d_w); F(h->d_init); F(h->d_block_loss); F(h->d_loss);
+    h->t_leafval.release(); h->t_tree.release();
     h->t_items.release(); h->t_leaf_items.release(); h->t_segs.release(); h->t_tile_seg.release();
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
     h->t_split_local.release(); h->t_split_all.release(); h->t_parts.release(); h->t_leaf.release(); h->t_hist_local.release();
@@ -1328,6 +1339,11 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         out->hess_sum[nid] = (float)ns[nid].sumH;
         out->sample_cnt[nid] = ns[nid].sample_cnt;
     }
+    h->last_tree.resize(out->n_nodes);
+    for (int nid = 0; nid < out->n_nodes; nid++)
+        h->last_tree[nid] = {out->left[nid], out->right[nid], out->fid[nid], out->node_info[nid]};
+    h->last_gid = gid;
+    h->unsampled_begin = row_mask ? root.e : -1;
     CK(cudaStreamSynchronize(h->st));
     float gpu_ms = 0.f;
     for (int i = 0; i + 1 < h->ev_used; i += 2) {
@@ -1364,6 +1380,99 @@ int ytk_gbdt_get_positions(ytk_gbdt* h, int32_t* node_of_row) {
     CK(h->t_pos.upload(items, h->st, h->arena));
     CK(ytk::launch_fill_positions(h->d_rowidx[0], h->d_rowidx[1], h->t_pos.d, (int)items.size(), h->d_node_of_row, h->st));
     CK(cudaMemcpyAsync(node_of_row, h->d_node_of_row, h->N * sizeof(int32_t), cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    return YTK_OK;
+}
+
+// -------------------------------------------------------------------------------------
+// §8(f) row 1: score update, loss and gradient pairs on the device
+// -------------------------------------------------------------------------------------
+int ytk_gbdt_set_targets(ytk_gbdt* h, int32_t loss, const float* y, const float* weight, const float* init_score) {
+    if (!h || !y) return fail(YTK_ERR_ARG, "set_targets: null argument");
+    if (!h->rows_set) return fail(YTK_ERR_ARG, "set_targets: call set_bins first");
+    const int K = h->p.class_num;
+    if (loss < 0 || loss > 2) return fail(YTK_ERR_ARG, "set_targets: unknown loss %d", loss);
+    // GBDTOptimizationParams.checkParams: only softmax may have class_num > 1 (:222-224)
+    if (loss != YTK_LOSS_SOFTMAX && K > 1)
+        return fail(YTK_ERR_ARG, "[GBDT] class_num(%d) and objective(%d) inconsistent", K, loss);
+    if (K > 64) return fail(YTK_ERR_UNSUPPORTED, "set_targets: class_num %d > 64", K);
+    CK(cudaSetDevice(h->device));
+    const size_t nk = (size_t)std::max<int64_t>(h->N, 1) * K, n1 = (size_t)std::max<int64_t>(h->N, 1);
+    if (!h->d_score) {
+        CK(cudaMalloc(&h->d_score, nk * sizeof(float)));
+        CK(cudaMalloc(&h->d_y, nk * sizeof(float)));
+        CK(cudaMalloc(&h->d_block_loss, ytk::loss_grad_blocks() * sizeof(double)));
+        CK(cudaMalloc(&h->d_loss, sizeof(double)));
+    }
+    CK(cudaMemsetAsync(h->d_score, 0, nk * sizeof(float), h->st));
+    CK(cudaMemcpyAsync(h->d_y, y, (size_t)h->N * K * sizeof(float), cudaMemcpyHostToDevice, h->st));
+    if (weight) {
+        if (!h->d_w) CK(cudaMalloc(&h->d_w, n1 * sizeof(float)));
+        CK(cudaMemcpyAsync(h->d_w, weight, (size_t)h->N * sizeof(float), cudaMemcpyHostToDevice, h->st));
+    } else if (h->d_w) { CK(cudaFree(h->d_w)); h->d_w = nullptr; }
+    if (init_score) {
+        if (!h->d_init) CK(cudaMalloc(&h->d_init, nk * sizeof(float)));
+        CK(cudaMemcpyAsync(h->d_init, init_score, (size_t)h->N * K * sizeof(float), cudaMemcpyHostToDevice, h->st));
+    } else if (h->d_init) { CK(cudaFree(h->d_init)); h->d_init = nullptr; }
+    CK(cudaStreamSynchronize(h->st));
+    h->loss_kind = loss;
+    return YTK_OK;
+}
+
+int ytk_gbdt_update_scores(ytk_gbdt* h, int32_t gid) {
+    if (!h) return fail(YTK_ERR_ARG, "update_scores: null argument");
+    if (h->loss_kind < 0) return fail(YTK_ERR_ARG, "update_scores: call set_targets first");
+    if (h->last_tree.empty() || gid != h->last_gid)
+        return fail(YTK_ERR_ARG, "update_scores: groupId %d is not the tree the last make() built (%d)", gid, h->last_gid);
+    CK(cudaSetDevice(h->device));
+    std::vector<ytk::LeafItem> items;
+    for (int nid : h->leaf_nodes) {
+        const Interval& v = h->iv[nid];
+        if (v.e > v.b) items.push_back({(long long)v.b, (long long)v.e, v.buf, h->last_tree[nid].info});
+    }
+    CK(h->t_leafval.upload(items, h->st, h->arena));
+    CK(ytk::launch_add_leaf_values(h->d_rowidx[0], h->d_rowidx[1], h->t_leafval.d, (int)items.size(), h->d_score,
+                                   h->p.class_num, gid, h->st));
+    if (h->unsampled_begin >= 0 && h->unsampled_begin < h->N) {
+        CK(h->t_tree.upload(h->last_tree, h->st, h->arena));
+        // the row-mask compaction left the excluded rows behind the sampled ones in buffer 0, and
+        // later partitions only ever rewrite the sampled range
+        CK(ytk::launch_walk_rows(h->d_bins, h->S8, h->d_rowidx[0], h->unsampled_begin, h->N, h->t_tree.d, h->d_score,
+                                 h->p.class_num, gid, h->st));
+    }
+    CK(cudaStreamSynchronize(h->st));
+    h->arena.rewind();
+    return YTK_OK;
+}
+
+int ytk_gbdt_compute_grads(ytk_gbdt* h, double* loss_sum) {
+    if (!h) return fail(YTK_ERR_ARG, "compute_grads: null argument");
+    if (h->loss_kind < 0) return fail(YTK_ERR_ARG, "compute_grads: call set_targets first");
+    CK(cudaSetDevice(h->device));
+    CK(ytk::launch_loss_grad(h->loss_kind, h->d_score, h->d_init, h->d_y, h->d_w, h->N, h->p.class_num, h->d_gp,
+                             h->d_block_loss, h->d_loss, h->st));
+    double l = 0.0;
+    CK(cudaMemcpyAsync(&l, h->d_loss, sizeof(double), cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    if (loss_sum) *loss_sum = l;
+    h->grads_set = true;
+    return YTK_OK;
+}
+
+int ytk_gbdt_get_scores(ytk_gbdt* h, float* out) {
+    if (!h || !out) return fail(YTK_ERR_ARG, "get_scores: null argument");
+    if (!h->d_score) return fail(YTK_ERR_ARG, "get_scores: call set_targets first");
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(out, h->d_score, (size_t)h->N * h->p.class_num * sizeof(float), cudaMemcpyDeviceToHost, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    return YTK_OK;
+}
+
+int ytk_gbdt_get_grads(ytk_gbdt* h, float* out) {
+    if (!h || !out) return fail(YTK_ERR_ARG, "get_grads: null argument");
+    if (!h->rows_set || !h->grads_set) return fail(YTK_ERR_ARG, "get_grads: no gradients on the device yet");
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(out, h->d_gp, (size_t)h->N * h->p.class_num * 2 * sizeof(float), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
     return YTK_OK;
 }

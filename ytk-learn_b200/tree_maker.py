@@ -115,6 +115,37 @@ class GpuTreeMaker:
         B.check(B.lib().ytk_gbdt_get_positions(self._h, B.ptr(out)))
         return out
 
+    # ---- the step either side of make(), on the device ------------------
+    LOSSES = {"sigmoid": 0, "l2": 1, "softmax": 2}
+
+    def set_targets(self, loss, y, weight=None, init_score=None):
+        """GBDTCoreData.y / weight / initScore; y is [N*K] (one-hot rows when K > 1)."""
+        y = np.ascontiguousarray(y, dtype=np.float32).reshape(-1)
+        if y.size != self.N * self.K:
+            raise B.YtkError(-1, "y must have N*K entries")
+        w = None if weight is None else np.ascontiguousarray(weight, dtype=np.float32)
+        i0 = None if init_score is None else np.ascontiguousarray(init_score, dtype=np.float32).reshape(-1)
+        B.check(B.lib().ytk_gbdt_set_targets(self._h, self.LOSSES[loss], B.ptr(y), B.ptr(w), B.ptr(i0)))
+
+    def update_scores(self, group_id=0):
+        B.check(B.lib().ytk_gbdt_update_scores(self._h, int(group_id)))
+
+    def compute_grads(self):
+        """predictAndCalcLossGrad's loss/gradient loop; returns sum_i w_i * loss_i."""
+        loss = C.c_double(0.0)
+        B.check(B.lib().ytk_gbdt_compute_grads(self._h, C.addressof(loss)))
+        return loss.value
+
+    def get_scores(self):
+        out = np.zeros(self.N * self.K, dtype=np.float32)
+        B.check(B.lib().ytk_gbdt_get_scores(self._h, B.ptr(out)))
+        return out
+
+    def get_grads(self):
+        out = np.zeros(self.N * self.K * 2, dtype=np.float32)
+        B.check(B.lib().ytk_gbdt_get_grads(self._h, B.ptr(out)))
+        return out
+
     # ---- per-stage hooks ---------------------------------------------------------------
     def build_hist(self, group_id=0, rows=None, fea_index=None):
         out = np.zeros(2 * self.B, dtype=np.float64)
