@@ -501,9 +501,22 @@ struct HistPlan {
 int hist_plan(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, int n_sel, HistPlan& pl, Blob& bl) {
     const int m = pl.m = (int)jobs.size();
     if (m == 0) return YTK_OK;
-    int64_t total = 0;
-    for (auto& j : jobs) total += j.cseg < 0 ? h->iv[j.nid].e - h->iv[j.nid].b : (j.parent.e - j.parent.b) / 2;
-    const int64_t rpi = ytk::hist_rows_per_item(total, h->groups);
+    // Work-item size: the smallest multiple of 1024 rows (4096..65536) for which the items of all
+    // nodes -- each node rounds up to whole items -- fit in two waves of one CTA per SM.
+    std::vector<int64_t> sizes(m);
+    for (int k = 0; k < m; k++) {
+        const HistJob& j = jobs[k];
+        sizes[k] = j.cseg < 0 ? h->iv[j.nid].e - h->iv[j.nid].b
+                              : (h->world == 1 ? (j.parent.e - j.parent.b) / 2 : j.parent.e - j.parent.b);
+    }
+    const int64_t target = std::max<int64_t>(1, (2 * ytk::kNumSMs) / std::max(1, h->groups));
+    auto items_at = [&](int64_t rpi) { int64_t c = 0; for (int64_t n : sizes) c += (n + rpi - 1) / rpi; return c; };
+    int64_t lo_u = 4, hi_u = ytk::kHistMaxRowsPerItem / 1024;        // in units of 1024 rows
+    while (lo_u < hi_u) {
+        int64_t mid = (lo_u + hi_u) / 2;
+        if (items_at(mid * 1024) <= target) hi_u = mid; else lo_u = mid + 1;
+    }
+    const int64_t rpi = lo_u * 1024;
     pl.outs_local.resize(m);
     const int64_t local_len = h->seg_max * h->world;
     if (h->world > 1) CK(h->t_hist_local.reserve((size_t)m * local_len));
