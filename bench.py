@@ -316,7 +316,7 @@ def main():
                     "d2h_bytes_per_step": agg["d2h"], "seconds_per_tree": t_e2e / a.steps},
             "device_gradient_round": {"ms_per_round": dev_round / a.steps * 1e3,
                                       "what": "make + score update + sigmoid loss/gradients, all on the device"},
-            "gpu_launches": agg["launches"],
+            "gpu_launches": agg["launches"], "peer_memory_collectives": bool(tm.last_stats.peer_collectives),
             "time_stats_ms_per_tree": {"build_hist": agg["ts_build"] / a.steps, "find_best_split": agg["ts_split"] / a.steps,
                                        "partition": agg["ts_part"] / a.steps, "total": agg["ts_total"] / a.steps,
                                        "collectives_gpu": agg["ts_comm"] / a.steps},

@@ -87,6 +87,7 @@ typedef struct {
     double  gpu_hist_ms;      /* CUDA-event time of the histogram-build kernels        */
     int32_t kernel_launches;  /* kernels launched by this call                         */
     int32_t hist_launches;    /* ... of which histogram-build launches (one per batch) */
+    int32_t peer_collectives; /* 1: per-level collectives ran over NVLink peer memory, 0: NCCL / one GPU */
 } ytk_time_stats;
 
 /* One best split: SplitInfo (J/data/gbdt/SplitInfo.java:36-70) plus the node totals the

@@ -124,6 +124,23 @@ cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st);
 cudaError_t launch_zero_segments(long long* const* dst, int n, int64_t len, cudaStream_t st);
 cudaError_t launch_copy_segments(const long long* src, long long* const* dst, int n, int64_t len, cudaStream_t st);
 
+// ---- collectives over NVLink peer memory (kernels.cu, last section) ----
+constexpr int kMaxPeers = 64;
+constexpr int kPeerFlagSets = 4;                   // counts, histogram staging, split records, leaf sums
+constexpr size_t kPeerFlagBytes = kPeerFlagSets * kMaxPeers * 8;
+struct PeerTable {
+    int rank, world;
+    char* xchg[16];        // every rank's exchange buffer: flags, then the slot areas
+    char* hist[16];        // every rank's histogram staging buffer
+};
+cudaError_t launch_peer_allreduce(const PeerTable& pt, const void* src, size_t area_off, size_t slot_bytes, size_t words,
+                                  int flag_set, unsigned long long epoch, long long* out, int* err, cudaStream_t st);
+cudaError_t launch_peer_allgather(const PeerTable& pt, const void* src, size_t area_off, size_t slot_bytes, size_t bytes,
+                                  int flag_set, unsigned long long epoch, int* err, cudaStream_t st);
+// raises this rank's "staging complete" flag, waits for everybody's, sums the owned segments out of all staging buffers
+cudaError_t launch_peer_pull_reduce(const PeerTable& pt, int m, long long seg_max, int flag_set, unsigned long long epoch,
+                                    long long* const* dst, int* err, cudaStream_t st);
+
 // §8(f) row 1: score update + loss + gradient pairs on the device
 cudaError_t launch_add_leaf_values(const int32_t* rowidx0, const int32_t* rowidx1, const LeafItem* items, int n_items,
                                    float* score, int32_t K, int32_t gid, cudaStream_t st);

@@ -327,6 +327,16 @@ struct ytk_gbdt {
     PinnedArena arena;
     char* d_blob = nullptr;  size_t blob_cap = 0;     // device side of Blob
 
+    // collectives over NVLink peer memory (world > 1, one node): see kernels.cu, last section
+    bool peer_mode = false;
+    ytk::PeerTable pt{};
+    char* my_xchg = nullptr; char* my_hist = nullptr;
+    size_t hist_cap_words = 0;               // capacity of my_hist in int64 words
+    int peer_cap_nodes = 0;                  // nodes per batch the exchange slots can hold
+    size_t off_counts = 0, off_recs = 0, off_leaf = 0, slot_counts = 0, slot_recs = 0, slot_leaf = 0;
+    unsigned long long epoch[ytk::kPeerFlagSets] = {0, 0, 0, 0};
+    int* d_peer_err = nullptr;
+
     // §8(f) row 1 state
     float* d_score = nullptr; float* d_y = nullptr; float* d_w = nullptr; float* d_init = nullptr;
     double* d_block_loss = nullptr; double* d_loss = nullptr;
@@ -380,6 +390,10 @@ void free_all(ytk_gbdt* h) {
     F(h->d_hist_dbl); F(h->d_scale); F(h->d_scale_hook); F(h->d_absmax); F(h->d_bad); F(h->d_node_of_row);
     F(h->d_stage); F(h->d_blob); F(h->d_score); F(h->d_y); F(h->d_w); F(h->d_init); F(h->d_block_loss); F(h->d_loss);
     h->t_leafval.release(); h->t_tree.release();
+    if (h->peer_mode)
+        for (int r = 0; r < h->world; r++)
+            if (r != h->rank) { cudaIpcCloseMemHandle(h->pt.xchg[r]); cudaIpcCloseMemHandle(h->pt.hist[r]); }
+    F(h->my_xchg); F(h->my_hist); F(h->d_peer_err);
     h->t_items.release(); h->t_leaf_items.release(); h->t_segs.release(); h->t_tile_seg.release();
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
     h->t_split_local.release(); h->t_split_all.release(); h->t_parts.release(); h->t_leaf.release(); h->t_hist_local.release();
@@ -467,6 +481,90 @@ void add_deferred_items(std::vector<ytk::RowItem>& items, const Interval& parent
 // the smaller child of split segment cseg (parent interval `parent`, children in buffer child_buf).
 struct HistJob { int nid; long long* dst; int cseg; Interval parent; int child_buf; };
 
+// Maps every rank's exchange and histogram staging buffers into this process (CUDA IPC) so that the
+// per-level collectives can run as plain kernels over NVLink.  All ranks must be processes on one node;
+// if any rank cannot set this up, all of them stay on NCCL (the decision itself is an NCCL allreduce).
+int peer_setup(ytk_gbdt* h) {
+    h->peer_mode = false;
+    if (h->world < 2 || h->world > 16) return YTK_OK;
+    if (const char* e = getenv("YTK_GBDT_NO_PEER")) if (atoi(e) != 0) return YTK_OK;
+    const int cap = 4096;
+    h->peer_cap_nodes = cap;
+    h->slot_counts = (size_t)cap * sizeof(ytk::PartitionCounts);
+    h->slot_recs = (size_t)2 * cap * sizeof(ytk_split);
+    h->slot_leaf = (size_t)2 * cap * sizeof(long long);
+    h->off_counts = ytk::kPeerFlagBytes;
+    h->off_recs = h->off_counts + h->slot_counts * h->world;
+    h->off_leaf = h->off_recs + h->slot_recs * h->world;
+    const size_t xchg_bytes = h->off_leaf + h->slot_leaf * h->world;
+    const size_t local_len = (size_t)h->seg_max * h->world;
+    size_t hist_words = std::max<size_t>(local_len * 256, (size_t(128) << 20) / 8);      // >= 256 nodes, >= 128 MB
+    hist_words = std::min<size_t>(hist_words, std::max<size_t>(local_len * 2, (size_t(1) << 30) / 8));
+    int ok = 1;
+    cudaIpcMemHandle_t mine[2];
+    if (cudaMalloc(&h->my_xchg, xchg_bytes) != cudaSuccess || cudaMalloc(&h->my_hist, hist_words * 8) != cudaSuccess ||
+        cudaMalloc(&h->d_peer_err, sizeof(int)) != cudaSuccess)
+        ok = 0;
+    if (ok) {
+        cudaMemset(h->my_xchg, 0, xchg_bytes);
+        cudaMemset(h->d_peer_err, 0, sizeof(int));
+        if (cudaIpcGetMemHandle(&mine[0], h->my_xchg) != cudaSuccess || cudaIpcGetMemHandle(&mine[1], h->my_hist) != cudaSuccess)
+            ok = 0;
+    }
+    cudaGetLastError();
+    // exchange the handles (and learn whether everybody got this far) over NCCL, once
+    const size_t rec = sizeof(mine) + 8;
+    char* d_send = nullptr; char* d_recv = nullptr;
+    CK(cudaMalloc(&d_send, rec));
+    CK(cudaMalloc(&d_recv, rec * h->world));
+    std::vector<char> send(rec, 0), recv(rec * h->world);
+    if (ok) memcpy(send.data(), mine, sizeof(mine));
+    long long okv = ok;
+    memcpy(send.data() + sizeof(mine), &okv, 8);
+    CK(cudaMemcpy(d_send, send.data(), rec, cudaMemcpyHostToDevice));
+    NK(ytk::nccl_api().AllGather(d_send, d_recv, rec, ncclChar, h->comm, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    CK(cudaMemcpy(recv.data(), d_recv, rec * h->world, cudaMemcpyDeviceToHost));
+    for (int r = 0; r < h->world; r++) { long long v; memcpy(&v, recv.data() + r * rec + sizeof(mine), 8); if (!v) ok = 0; }
+    h->pt.rank = h->rank; h->pt.world = h->world;
+    int opened = 0;
+    for (int r = 0; r < h->world && ok; r++) {
+        if (r == h->rank) { h->pt.xchg[r] = h->my_xchg; h->pt.hist[r] = h->my_hist; continue; }
+        cudaIpcMemHandle_t hd[2];
+        memcpy(hd, recv.data() + r * rec, sizeof(hd));
+        void *px = nullptr, *ph = nullptr;
+        if (cudaIpcOpenMemHandle(&px, hd[0], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess ||
+            cudaIpcOpenMemHandle(&ph, hd[1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            ok = 0; cudaGetLastError();
+            if (px) cudaIpcCloseMemHandle(px);
+            break;
+        }
+        h->pt.xchg[r] = (char*)px; h->pt.hist[r] = (char*)ph;
+        opened = r + 1;
+    }
+    // second agreement: did every rank manage to open every peer?
+    okv = ok;
+    CK(cudaMemcpy(d_send, &okv, 8, cudaMemcpyHostToDevice));
+    NK(ytk::nccl_api().AllReduce(d_send, d_send, 1, ncclInt64, ncclMin, h->comm, h->st));
+    CK(cudaStreamSynchronize(h->st));
+    CK(cudaMemcpy(&okv, d_send, 8, cudaMemcpyDeviceToHost));
+    cudaFree(d_send); cudaFree(d_recv);
+    if (getenv("YTK_GBDT_VERBOSE"))
+        fprintf(stderr, "ytk_gbdt[rank %d]: peer-memory collectives %s (local setup %s)\n", h->rank, okv ? "on" : "off", ok ? "ok" : "failed");
+    if (!okv) {
+        for (int r = 0; r < opened; r++)
+            if (r != h->rank) { cudaIpcCloseMemHandle(h->pt.xchg[r]); cudaIpcCloseMemHandle(h->pt.hist[r]); }
+        return YTK_OK;      // NCCL path
+    }
+    h->hist_cap_words = hist_words;
+    h->peer_mode = true;
+    return YTK_OK;
+}
+// may this batch of m nodes use the peer-memory collectives? (same answer on every rank)
+bool peer_ok(const ytk_gbdt* h, int m) {
+    return h->peer_mode && m <= h->peer_cap_nodes && (size_t)m * h->seg_max * h->world <= h->hist_cap_words;
+}
+
 // one host->device copy of a Blob; afterwards table at offset o lives at h->d_blob + o
 int blob_commit(ytk_gbdt* h, const Blob& bl) {
     const size_t bytes = bl.host.size();
@@ -519,7 +617,9 @@ int hist_plan(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, 
     const int64_t rpi = lo_u * 1024;
     pl.outs_local.resize(m);
     const int64_t local_len = h->seg_max * h->world;
-    if (h->world > 1) CK(h->t_hist_local.reserve((size_t)m * local_len));
+    const bool peer = h->world > 1 && peer_ok(h, m);
+    if (h->world > 1 && !peer) CK(h->t_hist_local.reserve((size_t)m * local_len));
+    long long* const staging = peer ? reinterpret_cast<long long*>(h->my_hist) : h->t_hist_local.d;
     for (int k = 0; k < m; k++) {
         if (jobs[k].cseg < 0) {
             const Interval& v = h->iv[jobs[k].nid];
@@ -532,7 +632,7 @@ int hist_plan(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, 
             add_deferred_items(pl.items, jobs[k].parent, jobs[k].child_buf, k, jobs[k].cseg, rpi, h->world);
         }
         // world > 1: local layout [rank][node][segment] so that ONE reduce-scatter serves the batch
-        pl.outs_local[k] = h->world == 1 ? jobs[k].dst : h->t_hist_local.d + (int64_t)k * h->seg_max;
+        pl.outs_local[k] = h->world == 1 ? jobs[k].dst : staging + (int64_t)k * h->seg_max;
     }
     pl.o_items = bl.add(pl.items);
     pl.o_local = bl.add(pl.outs_local);
@@ -549,6 +649,7 @@ int hist_enqueue(ytk_gbdt* h, const HistPlan& pl, ytk_time_stats* T, const ytk::
     const int m = pl.m;
     if (m == 0) return YTK_OK;
     const int64_t local_len = h->seg_max * h->world;
+    const bool peer = h->world > 1 && peer_ok(h, m);
     long long* const* d_local = blob_ptr<long long*>(h, pl.o_local);
     cudaEvent_t e0, e1;
     RET(hist_events(h, &e0, &e1));
@@ -556,7 +657,8 @@ int hist_enqueue(ytk_gbdt* h, const HistPlan& pl, ytk_time_stats* T, const ytk::
         CK(ytk::launch_zero_segments(d_local, m, h->seg_max, h->st));
         h->launches++;
     } else {
-        CK(cudaMemsetAsync(h->t_hist_local.d, 0, (size_t)m * local_len * sizeof(long long), h->st));
+        CK(cudaMemsetAsync(peer ? (void*)h->my_hist : (void*)h->t_hist_local.d, 0,
+                           (size_t)m * local_len * sizeof(long long), h->st));
     }
     CK(cudaEventRecord(e0, h->st));        // the pair brackets the hist_build_k launch only
     const long long owner_stride = h->world == 1 ? 0 : (long long)m * h->seg_max;
@@ -566,7 +668,15 @@ int hist_enqueue(ytk_gbdt* h, const HistPlan& pl, ytk_time_stats* T, const ytk::
                               h->st));
     if (!pl.items.empty()) h->launches++;
     CK(cudaEventRecord(e1, h->st));
-    if (h->world > 1) {
+    if (peer) {
+        // reduce-scatter over peer memory: flag "my staging buffer is complete", then every rank
+        // sums the segments it owns straight out of all staging buffers into the histogram slots
+        RET(comm_mark(h));
+        const unsigned long long ep = ++h->epoch[1];
+        CK(ytk::launch_peer_pull_reduce(h->pt, m, h->seg_max, 1, ep, blob_ptr<long long*>(h, pl.o_final), h->d_peer_err, h->st));
+        RET(comm_mark(h));
+        h->launches++;
+    } else if (h->world > 1) {
         CK(h->t_rs_out.reserve((size_t)m * h->seg_max));
         RET(comm_mark(h));
         NK(ytk::nccl_api().ReduceScatter(h->t_hist_local.d, h->t_rs_out.d, (size_t)m * h->seg_max, ncclInt64,
@@ -606,11 +716,21 @@ int search_enqueue(ytk_gbdt* h, const ytk::ScanNode* d_nodes, int m, int first_o
         // needReplace rule -- replaces allreduceRpc(SplitInfo) and allreduceArrayRpc(MAX)
         CK(h->t_split_all.reserve((size_t)m * h->world));
         RET(comm_mark(h));
-        NK(ytk::nccl_api().AllGather(h->t_split_local.d, h->t_split_all.d, m * sizeof(ytk_split), ncclChar, h->comm,
-                                     h->st));
-        RET(comm_mark(h));
-        CK(cudaMemcpyAsync(h->h_split.h, h->t_split_all.d, (size_t)h->world * m * sizeof(ytk_split),
-                           cudaMemcpyDeviceToHost, h->st));
+        if (h->peer_mode && (size_t)m * sizeof(ytk_split) <= h->slot_recs) {
+            const unsigned long long ep = ++h->epoch[2];
+            CK(ytk::launch_peer_allgather(h->pt, h->t_split_local.d, h->off_recs, h->slot_recs, (size_t)m * sizeof(ytk_split), 2,
+                                          ep, h->d_peer_err, h->st));
+            h->launches++;
+            RET(comm_mark(h));
+            CK(cudaMemcpy2DAsync(h->h_split.h, (size_t)m * sizeof(ytk_split), h->my_xchg + h->off_recs, h->slot_recs,
+                                 (size_t)m * sizeof(ytk_split), h->world, cudaMemcpyDeviceToHost, h->st));
+        } else {
+            NK(ytk::nccl_api().AllGather(h->t_split_local.d, h->t_split_all.d, m * sizeof(ytk_split), ncclChar, h->comm,
+                                         h->st));
+            RET(comm_mark(h));
+            CK(cudaMemcpyAsync(h->h_split.h, h->t_split_all.d, (size_t)h->world * m * sizeof(ytk_split),
+                               cudaMemcpyDeviceToHost, h->st));
+        }
     }
     return YTK_OK;
 }
@@ -688,8 +808,15 @@ int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const
     const int nc = h->world > 1 ? 2 * m : m;
     if (h->world > 1) {   // allreduceArray(long[2], SUM) (:538), all nodes of the batch at once
         RET(comm_mark(h));
-        NK(ytk::nccl_api().AllReduce(h->t_counts.d, h->t_counts.d + m, 2 * (size_t)m, ncclInt64, ncclSum, h->comm,
-                                     h->st));
+        if (peer_ok(h, m)) {
+            const unsigned long long ep = ++h->epoch[0];
+            CK(ytk::launch_peer_allreduce(h->pt, h->t_counts.d, h->off_counts, h->slot_counts, 2 * (size_t)m, 0, ep,
+                                          reinterpret_cast<long long*>(h->t_counts.d + m), h->d_peer_err, h->st));
+            h->launches++;
+        } else {
+            NK(ytk::nccl_api().AllReduce(h->t_counts.d, h->t_counts.d + m, 2 * (size_t)m, ncclInt64, ncclSum, h->comm,
+                                         h->st));
+        }
         RET(comm_mark(h));
     }
     CK(h->h_counts.reserve(nc));
@@ -924,6 +1051,7 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
     }
     if (capacity < 1) return fail(YTK_ERR_ARG, "histogram pool capacity %d < 1 (max_leaf_cnt %d)", capacity, h->p.max_leaf_cnt);
     h->pool.capacity = capacity;
+    if (h->world > 1) RET(peer_setup(h));
     h->rows_set = true;
     return YTK_OK;
 }
@@ -1294,9 +1422,17 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             CK(ytk::launch_leaf_sums(h->d_gq, h->d_rowidx[0], h->d_rowidx[1], blob_ptr<ytk::RowItem>(h, o_leaf),
                                      (int)leaf_items.size(), h->t_leaf.d, d_cl, d_cg, h->st));
             if (!leaf_items.empty()) h->launches++;
-            if (h->world > 1)      // allreduceArray(double[2], SUM) (:375), exact in the integer domain
-                NK(ytk::nccl_api().AllReduce(h->t_leaf.d, h->t_leaf.d, 2 * (size_t)n_leaf_jobs, ncclInt64, ncclSum,
-                                             h->comm, h->st));
+            if (h->world > 1) {    // allreduceArray(double[2], SUM) (:375), exact in the integer domain
+                if (h->peer_mode && (size_t)n_leaf_jobs * 16 <= h->slot_leaf) {
+                    const unsigned long long ep = ++h->epoch[3];
+                    CK(ytk::launch_peer_allreduce(h->pt, h->t_leaf.d, h->off_leaf, h->slot_leaf, 2 * (size_t)n_leaf_jobs, 3, ep,
+                                                  h->t_leaf.d, h->d_peer_err, h->st));
+                    h->launches++;
+                } else {
+                    NK(ytk::nccl_api().AllReduce(h->t_leaf.d, h->t_leaf.d, 2 * (size_t)n_leaf_jobs, ncclInt64, ncclSum,
+                                                 h->comm, h->st));
+                }
+            }
             CK(cudaMemcpyAsync(h->h_leaf.h, h->t_leaf.d, 2 * (size_t)n_leaf_jobs * sizeof(long long),
                                cudaMemcpyDeviceToHost, h->st));
         }
@@ -1352,6 +1488,12 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         out->hess_sum[nid] = (float)ns[nid].sumH;
         out->sample_cnt[nid] = ns[nid].sample_cnt;
     }
+    if (h->peer_mode) {
+        int perr = 0;
+        CK(cudaMemcpyAsync(&perr, h->d_peer_err, sizeof(int), cudaMemcpyDeviceToHost, h->st));
+        CK(cudaStreamSynchronize(h->st));
+        if (perr) return fail(YTK_ERR_NCCL, "make_tree: a peer GPU did not reach a collective within 3 s");
+    }
     h->last_tree.resize(out->n_nodes);
     for (int nid = 0; nid < out->n_nodes; nid++)
         h->last_tree[nid] = {out->left[nid], out->right[nid], out->fid[nid], out->node_info[nid]};
@@ -1375,6 +1517,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     T->compute_hist = gpu_ms;
     T->kernel_launches = h->launches;
     T->hist_launches = h->ev_used / 2;
+    T->peer_collectives = h->peer_mode ? 1 : 0;
     T->total = now_ms() - t_start;
     if (ts) *ts = *T;
     return YTK_OK;
