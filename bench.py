@@ -319,7 +319,8 @@ def main():
             "gpu_launches": agg["launches"], "peer_memory_collectives": bool(tm.last_stats.peer_collectives),
             "time_stats_ms_per_tree": {"build_hist": agg["ts_build"] / a.steps, "find_best_split": agg["ts_split"] / a.steps,
                                        "partition": agg["ts_part"] / a.steps, "total": agg["ts_total"] / a.steps,
-                                       "collectives_gpu": agg["ts_comm"] / a.steps},
+                                       "collectives_gpu": agg["ts_comm"] / a.steps,
+                                       "host_waits": tm.last_stats.batches + 1},
             "roofline": {"bound": "hbm", "kernel": "hist_build_k", "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg / max(1, agg["hist_launches"]),

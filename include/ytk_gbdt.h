@@ -88,6 +88,7 @@ typedef struct {
     int32_t kernel_launches;  /* kernels launched by this call                         */
     int32_t hist_launches;    /* ... of which histogram-build launches (one per batch) */
     int32_t peer_collectives; /* 1: per-level collectives ran over NVLink peer memory, 0: NCCL / one GPU */
+    int32_t batches;          /* batches of launches = host waits after the root (a level, a node, or a look-ahead set) */
 } ytk_time_stats;
 
 /* One best split: SplitInfo (J/data/gbdt/SplitInfo.java:36-70) plus the node totals the

@@ -363,6 +363,37 @@ def test_level_batching_equals_node_at_a_time(kw, monkeypatch):
     assert a.last_stats.kernel_launches < b.last_stats.kernel_launches
 
 
+@pytest.mark.parametrize("kw", [dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=100),
+                                dict(KW, grow_policy="loss", max_depth=6, max_leaf_cnt=40),
+                                dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=64, min_split_loss=1.0)],
+                         ids=["leaves100", "depth6_leaves40", "min_split_loss"])
+@pytest.mark.parametrize("ahead", [3, 64])
+def test_loss_wise_lookahead_equals_node_at_a_time(kw, ahead, monkeypatch):
+    """Loss-wise growth computes the expansions of the best few queue entries per batch of launches and
+    applies them in the reference's order: bit-identical trees to one-node-at-a-time
+    (YTK_GBDT_LOOKAHEAD=1), and to the oracle."""
+    n, F = 60000, 28
+    x, start, gp = synth(n, F, 255, 67, skew=True)
+    monkeypatch.setenv("YTK_GBDT_LOOKAHEAD", str(ahead))
+    a = maker(kw, x, start, gp)
+    ta = a.make(0)
+    pa = a.get_positions()
+    monkeypatch.setenv("YTK_GBDT_LOOKAHEAD", "1")
+    b = maker(kw, x, start, gp)
+    tb = b.make(0)
+    for name, _ in yb.Tree.FIELDS:
+        assert np.array_equal(getattr(ta, name), getattr(tb, name), equal_nan=True), name
+    assert np.array_equal(pa, b.get_positions())
+    assert a.last_stats.kernel_launches < b.last_stats.kernel_launches
+    o, opos, _ = ob.make_tree(ob.make_params(**kw), x, gp, 0, start)
+    assert_same_tree(ta, o)
+    assert np.array_equal(pa, opos)
+    # a second tree on the same handle (expansions left over from the first must not leak into it)
+    ta2 = a.make(0)
+    for name, _ in yb.Tree.FIELDS:
+        assert np.array_equal(getattr(ta, name), getattr(ta2, name), equal_nan=True), name
+
+
 @pytest.mark.parametrize("bits", [16, 30])
 def test_fixed_point_width(bits, monkeypatch):
     monkeypatch.setenv("YTK_GBDT_FIXED_BITS", str(bits))

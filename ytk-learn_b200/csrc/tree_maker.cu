@@ -137,7 +137,7 @@ struct NodeStats {                 // TreeMakerNodeStats (DataParallelTreeMaker.
     int best_fid = -1, best_lo = -1, best_hi = -1;
 };
 
-struct ExpandNode { int nid; float loss_chg; int depth; int seq; };
+struct ExpandNode { int hd; float loss_chg; int depth; int seq; };      // hd: node handle (make_tree)
 
 int java_float_compare(float a, float b) {   // java.lang.Float.compare
     if (a < b) return -1;
@@ -272,6 +272,7 @@ struct ytk_gbdt {
     int device = 0, rank = 0, world = 1;
     int fixed_bits = ytk::kDefaultFixedBits;
     bool force_sequential = false;
+    int lookahead = 64;         // loss-wise: expansions computed per batch of launches (YTK_GBDT_LOOKAHEAD)
     cudaStream_t st = nullptr;
     ncclComm_t comm = nullptr;
 
@@ -349,8 +350,8 @@ struct ytk_gbdt {
 
     HistPool pool;
     bool grads_set = false, rows_set = false;
-    std::vector<Interval> iv;          // last tree: interval of every node
-    std::vector<int> leaf_nodes;
+    std::vector<std::pair<int, Interval>> leaf_ranges;   // (leaf node id, a run of its rows) of the last tree
+    bool tree_made = false;
     int launches = 0;
     std::vector<cudaEvent_t> ev;       // event pairs around histogram builds
     int ev_used = 0;
@@ -479,7 +480,8 @@ void add_deferred_items(std::vector<ytk::RowItem>& items, const Interval& parent
 
 // Build a node's histogram into dst (this rank's segment).  cseg < 0: rows = iv[nid]; cseg >= 0: rows =
 // the smaller child of split segment cseg (parent interval `parent`, children in buffer child_buf).
-struct HistJob { int nid; long long* dst; int cseg; Interval parent; int child_buf; };
+// cseg < 0: the rows of interval v; else: the smaller child of split segment cseg, whose parent has interval v
+struct HistJob { long long* dst; int cseg; Interval v; int child_buf; };
 
 // Maps every rank's exchange and histogram staging buffers into this process (CUDA IPC) so that the
 // per-level collectives can run as plain kernels over NVLink.  All ranks must be processes on one node;
@@ -604,8 +606,7 @@ int hist_plan(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, 
     std::vector<int64_t> sizes(m);
     for (int k = 0; k < m; k++) {
         const HistJob& j = jobs[k];
-        sizes[k] = j.cseg < 0 ? h->iv[j.nid].e - h->iv[j.nid].b
-                              : (h->world == 1 ? (j.parent.e - j.parent.b) / 2 : j.parent.e - j.parent.b);
+        sizes[k] = j.cseg < 0 ? j.v.e - j.v.b : (h->world == 1 ? (j.v.e - j.v.b) / 2 : j.v.e - j.v.b);
     }
     const int64_t target = std::max<int64_t>(1, (2 * ytk::kNumSMs) / std::max(1, h->groups));
     auto items_at = [&](int64_t rpi) { int64_t c = 0; for (int64_t n : sizes) c += (n + rpi - 1) / rpi; return c; };
@@ -622,14 +623,14 @@ int hist_plan(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, 
     long long* const staging = peer ? reinterpret_cast<long long*>(h->my_hist) : h->t_hist_local.d;
     for (int k = 0; k < m; k++) {
         if (jobs[k].cseg < 0) {
-            const Interval& v = h->iv[jobs[k].nid];
+            const Interval& v = jobs[k].v;
             add_row_items(pl.items, v, k, rpi);
             T->hist_built++;
             T->hist_cells += (double)(v.e - v.b) * n_sel;
             T->hist_rows += (double)(v.e - v.b);
             if (v.buf >= 0) T->hist_rows_indexed += (double)(v.e - v.b);
         } else {
-            add_deferred_items(pl.items, jobs[k].parent, jobs[k].child_buf, k, jobs[k].cseg, rpi, h->world);
+            add_deferred_items(pl.items, jobs[k].v, jobs[k].child_buf, k, jobs[k].cseg, rpi, h->world);
         }
         // world > 1: local layout [rank][node][segment] so that ONE reduce-scatter serves the batch
         pl.outs_local[k] = h->world == 1 ? jobs[k].dst : staging + (int64_t)k * h->seg_max;
@@ -849,7 +850,18 @@ int partition_nodes(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const s
     return YTK_OK;
 }
 
-struct SplitJob { int nid, l, r, depth; bool terminal; };
+struct SplitJob { int hd, l, r, depth; bool terminal; };      // handles of the node and its children
+
+// What splitting a node produces, kept until the split is applied (make_tree)
+struct Expansion {
+    bool have = false;          // computed and not yet applied
+    bool by_hist = false;       // children's histograms + split records (else: leaf sums of the smaller child)
+    bool placeholders = false;  // pool entries of the children still carry placeholder keys
+    ytk::PartitionCounts cl{0, 0}, cg{0, 0};
+    ytk_split rec[2];           // smaller, larger child
+    long long leaf[2] = {0, 0};
+    int hl = -1, hr = -1;       // handles of the children
+};
 
 }  // namespace
 
@@ -942,6 +954,7 @@ int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank,
         h->fixed_bits = b;
     }
     if (const char* s = getenv("YTK_GBDT_SEQUENTIAL")) h->force_sequential = atoi(s) != 0;
+    if (const char* s = getenv("YTK_GBDT_LOOKAHEAD")) h->lookahead = std::max(1, std::min(1024, atoi(s)));
     auto bail = [&](int code) { free_all(h); delete h; return code; };
     if (cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking) != cudaSuccess)
         return bail(fail(YTK_ERR_CUDA, "cudaStreamCreate failed"));
@@ -1170,6 +1183,12 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     const bool unbounded = (h->pool.capacity >= p.max_leaf_cnt && p.max_leaf_cnt > 0) ||
                            (p.max_leaf_cnt <= 0);
     const bool batch_levels = unbounded && !loss_wise && !h->force_sequential;
+    const bool deferred = unbounded && p.min_split_samples <= 0;
+    // Loss-wise growth polls one node at a time, but what a split produces (child rows, the children's
+    // histograms and best splits) does not depend on when it is applied.  With lookahead > 1 the
+    // expansions of the best few queue entries are computed by one batch of launches and applied
+    // later, strictly in the reference's order: same tree, one host wait per batch instead of per split.
+    const int lookahead = (loss_wise && deferred && !h->force_sequential) ? h->lookahead : 1;
 
     // ---- initAssistData (:395-470)
     int first_owned = -1, n_sel = 0;
@@ -1180,9 +1199,19 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     h->launches += 2;
     CK(cudaMemcpyAsync(h->h_scale.h, h->d_scale, sizeof(ytk::GradScale), cudaMemcpyDeviceToHost, h->st));
 
-    std::vector<Interval>& iv = h->iv;
-    iv.clear();
-    h->leaf_nodes.clear();
+    // Per-node working state is indexed by HANDLE.  A node gets its handle when the split that
+    // creates it is computed, and its id in the tree (Tree.AllocTreeNode order) when that split is
+    // applied; unless expansions are computed ahead of time (lookahead) both happen together and
+    // handle == node id.
+    std::vector<Interval> iv;
+    std::vector<NodeStats> ns;
+    std::vector<Expansion> exps;                // by parent handle
+    std::vector<int> nid_of;                    // handle -> node id, -1 while the node is not in the tree
+    std::vector<int> leaf_handles;
+    auto new_handle = [&]() -> int {
+        iv.emplace_back(); ns.emplace_back(); exps.emplace_back(); nid_of.push_back(-1);
+        return (int)iv.size() - 1;
+    };
     std::vector<ytk::PartitionCounts> cl, cg;
     Interval root;
     if (row_mask) {
@@ -1204,32 +1233,33 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         out->loss_chg[nid] = 0.f; out->hess_sum[nid] = 0.f; out->sample_cnt[nid] = 0;
         return nid;
     };
-    std::vector<NodeStats> ns;
-    auto set_split_if_good = [&](int nid) {        // findBestSplit tail (:587-592), TreeNode.setSplit (:144-149)
-        const NodeStats& s = ns[nid];
+    auto set_split_if_good = [&](int hd) {         // findBestSplit tail (:587-592), TreeNode.setSplit (:144-149)
+        const NodeStats& s = ns[hd];
+        const int nid = nid_of[hd];
         if ((double)s.best_lc > p.min_split_loss) {
             out->fid[nid] = s.best_fid; out->lo[nid] = s.best_lo; out->hi[nid] = s.best_hi;
             out->node_info[nid] = 0.5f * (float)(s.best_lo + s.best_hi);
         }
     };
-    auto set_leaf = [&](int nid) {                 // :253
-        out->node_info[nid] = ns[nid].node_value * lr;
+    auto set_leaf = [&](int hd) {                  // :253
+        const int nid = nid_of[hd];
+        out->node_info[nid] = ns[hd].node_value * lr;
         out->left[nid] = -1; out->right[nid] = -1;
-        h->leaf_nodes.push_back(nid);
-        if (unbounded) h->pool.release(nid);       // only recycles memory; the reference keeps it unused
+        leaf_handles.push_back(hd);
+        if (unbounded) h->pool.release(hd);        // only recycles memory; the reference keeps it unused
     };
-    auto pool_slot = [&](int nid, long long** buf) -> int {
+    auto pool_slot = [&](int key, long long** buf) -> int {      // pool entries are keyed by handle
         bool fresh = false;
-        HistPool::Item* it = h->pool.alloc(nid, &fresh, unbounded);
+        HistPool::Item* it = h->pool.alloc(key, &fresh, unbounded);
         if (fresh) CK(cudaMalloc(&it->buf, h->seg_max * sizeof(long long)));
         *buf = it->buf;
         return YTK_OK;
     };
 
     out->n_nodes = 0;
-    const int root_id = alloc_node(-1);
-    ns.emplace_back();
-    iv.push_back(root);
+    const int root_id = new_handle();
+    nid_of[root_id] = alloc_node(-1);
+    iv[root_id] = root;
     {   // initTreeMakerNodeStats(0) (:510-520): allreduce(long, SUM)
         int64_t local = root.e - root.b, global = local;
         if (h->world > 1) {
@@ -1251,7 +1281,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         double t0 = now_ms();
         long long* slot;
         RET(pool_slot(root_id, &slot));
-        RET(build_hists(h, {{root_id, slot, -1, Interval(), 0}}, T, n_sel, nullptr, nullptr));
+        RET(build_hists(h, {{slot, -1, root, 0}}, T, n_sel, nullptr, nullptr));
         double t1 = now_ms();
         RET(search_nodes(h, {{slot, (long long)ns[root_id].sample_cnt, -1, 0}}, first_owned, recs));
         apply_record(ns[root_id], recs[0]);
@@ -1265,44 +1295,153 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     queue.push_back({root_id, ns[root_id].best_lc, 0, seq++});
     int num_leaf = 1;
 
-    auto pop_next = [&]() -> ExpandNode {
-        // PriorityQueue.poll with lossChgComparator / sequenceComparator (:105-115)
+    // PriorityQueue order with lossChgComparator / sequenceComparator (:105-115): true if a is polled before b
+    auto polled_before = [&](const ExpandNode& a, const ExpandNode& b) {
+        int c = loss_wise ? java_float_compare(a.loss_chg, b.loss_chg) : 0;      // larger lossChg first
+        if (c != 0) return c > 0;
+        return a.seq < b.seq;
+    };
+    auto head_index = [](const std::vector<ExpandNode>& q, const decltype(polled_before)& before) -> size_t {
         size_t bi = 0;
-        for (size_t i = 1; i < queue.size(); i++) {
-            int c = 0;
-            if (loss_wise) c = java_float_compare(queue[bi].loss_chg, queue[i].loss_chg);   // larger lossChg first
-            if (c == 0) c = (queue[i].seq > queue[bi].seq) - (queue[i].seq < queue[bi].seq);
-            if (c < 0) bi = i;
+        for (size_t i = 1; i < q.size(); i++)
+            if (before(q[i], q[bi])) bi = i;
+        return bi;
+    };
+    // stop rules of the loop head that hold whenever the node is polled (:249-250) ...
+    auto never_splits = [&](const ExpandNode& e) {
+        return (double)e.loss_chg <= p.min_split_loss || (p.max_depth >= 0 && p.max_depth == e.depth);
+    };
+    // ... and all of them (:249-252)
+    auto becomes_leaf = [&](const ExpandNode& e) {
+        return never_splits(e)
+            || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf)
+            || (p.min_split_samples > 0 && ns[e.hd].sample_cnt < p.min_split_samples);
+    };
+    // tree.addChilds (:256): the children of a node being split get their ids, in the order splits are applied
+    auto add_children = [&](int hd, int hl, int hr) -> int {
+        const int nid = nid_of[hd];
+        const int l = alloc_node(nid), r = alloc_node(nid);
+        if (l < 0 || r < 0) return fail(YTK_ERR_CAPACITY, "make_tree: tree needs more than %d nodes", out->capacity);
+        out->left[nid] = l; out->right[nid] = r;
+        nid_of[hl] = l; nid_of[hr] = r;
+        num_leaf++;
+        return YTK_OK;
+    };
+    // first two clauses of the children-are-leaves test (:266-267); the third needs the counts
+    auto children_are_leaves = [&](int depth) {
+        return (p.max_depth >= 0 && p.max_depth == depth + 1) || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf);
+    };
+
+    // What a computed expansion says about the two children, written to their handles: row
+    // intervals, global counts and -- unless they are leaves -- histograms and best splits.
+    auto materialise = [&](const SplitJob& j) {
+        Expansion& x = exps[j.hd];
+        const Interval pv = iv[j.hd];
+        const int cbuf = pv.buf == 0 ? 1 : 0;
+        iv[j.l].b = pv.b; iv[j.l].e = pv.b + x.cl.left; iv[j.l].buf = cbuf;
+        iv[j.r].b = pv.b + x.cl.left; iv[j.r].e = pv.e; iv[j.r].buf = cbuf;
+        ns[j.l].sample_cnt = x.cg.left; ns[j.r].sample_cnt = x.cg.right;
+        if (!x.by_hist) return;
+        // smaller child: strictly fewer global rows on the left, else the right (:344-350, :493-499)
+        const int small = x.cg.left < x.cg.right ? j.l : j.r, large = small == j.l ? j.r : j.l;
+        if (x.placeholders) {
+            h->pool.rename(-2 - 2 * j.hd, small);
+            h->pool.rename(-3 - 2 * j.hd, large);
+            x.placeholders = false;
         }
-        ExpandNode e = queue[bi];
-        queue.erase(queue.begin() + bi);
-        return e;
+        apply_record(ns[small], x.rec[0]);
+        apply_record(ns[large], x.rec[1]);
+    };
+
+    // Applies a split whose expansion is there and whose children have their ids: leaf statistics
+    // (computeLeafStats :341-385), or the children's splits and two new queue entries.
+    auto commit = [&](const SplitJob& j) {
+        Expansion& x = exps[j.hd];
+        const int small = x.cg.left < x.cg.right ? j.l : j.r, large = small == j.l ? j.r : j.l;
+        if (j.terminal) {
+            NodeStats &ss = ns[small], &ls = ns[large], &ps = ns[j.hd];
+            double sG, sH;
+            if (x.by_hist) {
+                // computed ahead of time as an inner split, applied as the last split of the tree: the
+                // smaller child's totals are the same integer sums, read from its histogram instead of
+                // its rows; the children were never searched as far as the tree is concerned
+                sG = x.rec[0].sum_grad; sH = x.rec[0].sum_hess;
+                for (NodeStats* s2 : {&ss, &ls}) {
+                    const int64_t cnt = s2->sample_cnt;
+                    *s2 = NodeStats();
+                    s2->sample_cnt = cnt;
+                }
+                h->pool.release(small); h->pool.release(large);
+            } else {
+                sG = (double)x.leaf[0] * h->h_scale.h->inv_g;
+                sH = (double)x.leaf[1] * h->h_scale.h->inv_h;
+            }
+            ss.sumG = sG; ss.sumH = sH;
+            ls.sumG = ps.sumG - ss.sumG; ls.sumH = ps.sumH - ss.sumH;      // setSubstract (:382)
+            for (NodeStats* s2 : {&ss, &ls}) ytk_host_node_value(&p, s2->sumG, s2->sumH, &s2->root_gain, &s2->node_value);
+            set_leaf(j.l); set_leaf(j.r);
+        } else {
+            set_split_if_good(small);
+            set_split_if_good(large);
+            queue.push_back({j.l, ns[j.l].best_lc, j.depth + 1, seq++});
+            queue.push_back({j.r, ns[j.r].best_lc, j.depth + 1, seq++});
+        }
+        x.have = false;
     };
 
     while (!queue.empty()) {
-        // ---- pop: one node (the reference's order), or -- level-wise with an unbounded pool -- every
-        // node of the level, which the reference would pop back to back in the same (seq) order
         std::vector<SplitJob> jobs;
-        const size_t n_pop = batch_levels ? queue.size() : 1;
-        for (size_t q = 0; q < n_pop; q++) {
-            ExpandNode e = pop_next();
-            const int nid = e.nid;
-            if ((double)e.loss_chg <= p.min_split_loss
-                || (p.max_depth >= 0 && p.max_depth == e.depth)
-                || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf)
-                || (p.min_split_samples > 0 && ns[nid].sample_cnt < p.min_split_samples)) {
-                set_leaf(nid);
+        if (lookahead > 1) {
+            // ---- poll (:246-258): the head is a leaf, or its split is applied if it has been computed
+            const size_t hi = head_index(queue, polled_before);
+            const ExpandNode e = queue[hi];
+            if (becomes_leaf(e)) { queue.erase(queue.begin() + hi); set_leaf(e.hd); continue; }
+            if (exps[e.hd].have) {
+                queue.erase(queue.begin() + hi);
+                const int hl = exps[e.hd].hl, hr = exps[e.hd].hr;
+                RET(add_children(e.hd, hl, hr));
+                commit({e.hd, hl, hr, e.depth, children_are_leaves(e.depth)});
                 continue;
             }
-            int l = alloc_node(nid), r = alloc_node(nid);                 // tree.addChilds (:256)
-            if (l < 0 || r < 0) return fail(YTK_ERR_CAPACITY, "make_tree: tree needs more than %d nodes", out->capacity);
-            out->left[nid] = l; out->right[nid] = r;
-            ns.emplace_back(); ns.emplace_back();
-            iv.emplace_back(); iv.emplace_back();
-            num_leaf++;
-            // first two clauses of the children-are-leaves test (:266-267); the third needs the counts
-            bool term = (p.max_depth >= 0 && p.max_depth == e.depth + 1) || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf);
-            jobs.push_back({nid, l, r, e.depth, term});
+            // ---- the head's split has not been computed.  Play the loop forward on a copy of the queue
+            // -- splits already computed put their children into the copy -- and collect the first
+            // `lookahead` nodes that would be split and have no expansion yet.  The forecast only
+            // chooses what to compute; the order in which splits are applied is decided above.
+            std::vector<ExpandNode> sim(queue);
+            int vseq = seq;
+            long long budget = p.max_leaf_cnt > 0 ? (long long)p.max_leaf_cnt - num_leaf : (1LL << 40);
+            while (!sim.empty() && (int)jobs.size() < lookahead && budget > 0) {
+                const size_t si = head_index(sim, polled_before);
+                const ExpandNode q = sim[si];
+                sim.erase(sim.begin() + si);
+                if (never_splits(q)) continue;
+                budget--;
+                if (exps[q.hd].have) {
+                    const Expansion& x = exps[q.hd];
+                    if (x.by_hist) {
+                        sim.push_back({x.hl, ns[x.hl].best_lc, q.depth + 1, vseq++});
+                        sim.push_back({x.hr, ns[x.hr].best_lc, q.depth + 1, vseq++});
+                    }
+                    continue;
+                }
+                const int hl = new_handle(), hr = new_handle();
+                exps[q.hd].hl = hl; exps[q.hd].hr = hr;
+                jobs.push_back({q.hd, hl, hr, q.depth, p.max_depth >= 0 && p.max_depth == q.depth + 1});
+            }
+        } else {
+            // ---- poll: one node (the reference's order), or -- level-wise with an unbounded pool -- every
+            // node of the level, which the reference would poll back to back in the same (seq) order
+            const size_t n_pop = batch_levels ? queue.size() : 1;
+            for (size_t q = 0; q < n_pop; q++) {
+                const size_t hi = head_index(queue, polled_before);
+                const ExpandNode e = queue[hi];
+                queue.erase(queue.begin() + hi);
+                if (becomes_leaf(e)) { set_leaf(e.hd); continue; }
+                const int hl = new_handle(), hr = new_handle();
+                exps[e.hd].hl = hl; exps[e.hd].hr = hr;
+                RET(add_children(e.hd, hl, hr));
+                jobs.push_back({e.hd, hl, hr, e.depth, children_are_leaves(e.depth)});
+            }
         }
         if (jobs.empty()) continue;
         const int m = (int)jobs.size();
@@ -1311,28 +1450,31 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         double t0 = now_ms();
         std::vector<ytk::SplitSeg> segs(m);
         for (int k = 0; k < m; k++) {
-            const Interval& pv = iv[jobs[k].nid];
-            segs[k] = {(long long)pv.b, (long long)pv.e, pv.buf, out->fid[jobs[k].nid], out->node_info[jobs[k].nid], 0, 0, 0};
+            const Interval& pv = iv[jobs[k].hd];
+            const NodeStats& s = ns[jobs[k].hd];         // TreeNode.setSplit: cond = 0.5f * (lo + hi) (:144-149)
+            segs[k] = {(long long)pv.b, (long long)pv.e, pv.buf, s.best_fid, 0.5f * (float)(s.best_lo + s.best_hi), 0, 0, 0};
         }
         // With an unbounded pool and no row-count stop rule nothing the host decides next depends on
         // the child counts, so the histogram/leaf kernels are queued right behind the partition with
         // "smaller child of segment k" work items resolved on the device: one host wait per batch
         // instead of two.
-        const bool deferred = unbounded && p.min_split_samples <= 0;
-        auto finish_partition = [&]() {
+        auto finish_partition = [&]() {         // !deferred only: the host needs the counts before it can go on
             partition_collect(h, m, cl, cg);
             for (int k = 0; k < m; k++) {
-                const SplitJob& j = jobs[k];
-                const Interval pv = iv[j.nid];
-                const int cbuf = pv.buf == 0 ? 1 : 0;
-                iv[j.l].b = pv.b; iv[j.l].e = pv.b + cl[k].left; iv[j.l].buf = cbuf;
-                iv[j.r].b = pv.b + cl[k].left; iv[j.r].e = pv.e; iv[j.r].buf = cbuf;
-                ns[j.l].sample_cnt = cg[k].left; ns[j.r].sample_cnt = cg[k].right;
+                SplitJob& j = jobs[k];
+                Expansion& x = exps[j.hd];
+                x.cl = cl[k]; x.cg = cg[k];
+                materialise(j);
                 if (p.min_split_samples > 0 && ns[j.l].sample_cnt < p.min_split_samples
                     && ns[j.r].sample_cnt < p.min_split_samples)
-                    jobs[k].terminal = true;
+                    j.terminal = true;
             }
         };
+        for (int k = 0; k < m; k++) {
+            const int hl = exps[jobs[k].hd].hl, hr = exps[jobs[k].hd].hr;
+            exps[jobs[k].hd] = Expansion();
+            exps[jobs[k].hd].hl = hl; exps[jobs[k].hd].hr = hr;
+        }
         // every work table of the batch goes up in one copy (two when the host must see the counts first)
         Blob bl_part, bl_rest;
         Blob& bl = deferred ? bl_part : bl_rest;
@@ -1352,7 +1494,6 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
 
         // ---- children: leaf statistics (computeLeafStats :341-385) or histograms + split search
         t0 = now_ms();
-        // smaller child: strictly fewer global rows on the left, else the right (:344-350, :493-499)
         auto small_of = [&](const SplitJob& j) { return ns[j.l].sample_cnt < ns[j.r].sample_cnt ? j.l : j.r; };
         std::vector<ytk::RowItem> leaf_items;
         std::vector<HistJob> hist_jobs;
@@ -1362,10 +1503,11 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         int n_leaf_jobs = 0;
         for (int k = 0; k < m; k++) {
             const SplitJob& j = jobs[k];
-            const Interval pv = iv[j.nid];
+            const Interval pv = iv[j.hd];
             const int cbuf = pv.buf == 0 ? 1 : 0;
+            Expansion& x = exps[j.hd];
             if (j.terminal) {
-                if (unbounded) h->pool.release(j.nid);
+                if (unbounded) h->pool.release(j.hd);
                 if (deferred) {
                     const int64_t n = pv.e - pv.b;
                     add_deferred_items(leaf_items, pv, cbuf, n_leaf_jobs, k, std::max<int64_t>(4096, (n / 2 + 63) / 64), h->world);
@@ -1377,28 +1519,31 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
                 n_leaf_jobs++;
                 continue;
             }
-            // buildHist(parent, l, r) (:489-508).  Pool entries are keyed by node id; while the
-            // children's roles are still unknown they are keyed by placeholders and renamed below.
-            const int small = deferred ? -2 - 2 * k : small_of(j);
-            const int large = deferred ? -3 - 2 * k : (small == j.l ? j.r : j.l);
-            long long* parent_h = h->pool.get(j.nid);
+            // buildHist(parent, l, r) (:489-508).  Pool entries are keyed by handle; while the
+            // children's roles are still unknown they are keyed by placeholders derived from the
+            // parent's handle and renamed once the counts are known.
+            x.by_hist = true;
+            x.placeholders = deferred;
+            const int small = deferred ? -2 - 2 * j.hd : small_of(j);
+            const int large = deferred ? -3 - 2 * j.hd : (small == j.l ? j.r : j.l);
+            long long* parent_h = h->pool.get(j.hd);
             long long *small_h, *large_h;
             RET(pool_slot(small, &small_h));
-            if (deferred) hist_jobs.push_back({-1, small_h, k, pv, cbuf});
-            else hist_jobs.push_back({small, small_h, -1, Interval(), 0});
+            if (deferred) hist_jobs.push_back({small_h, k, pv, cbuf});
+            else hist_jobs.push_back({small_h, -1, iv[small], 0});
             if (parent_h) {
                 if (unbounded) {                       // sibling written over its parent
-                    h->pool.rename(j.nid, large);
+                    h->pool.rename(j.hd, large);
                     large_h = parent_h;
                 } else {
-                    h->pool.release(j.nid);
+                    h->pool.release(j.hd);
                     RET(pool_slot(large, &large_h));
                 }
                 subs.push_back({parent_h, small_h, large_h});      // substract (:101-107)
             } else {
                 if (deferred) return fail(YTK_ERR_ARG, "internal: parent histogram missing with an unbounded pool");
                 RET(pool_slot(large, &large_h));
-                hist_jobs.push_back({large, large_h, -1, Interval(), 0});
+                hist_jobs.push_back({large_h, -1, iv[large], 0});
                 T->hist_miss++;
             }
             if (deferred) {
@@ -1446,47 +1591,60 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         CK(cudaStreamSynchronize(h->st));            // the one host wait of the batch
         h->arena.rewind();
         search_collect(h, (int)scans.size(), recs);
-        if (deferred) finish_partition();
+        if (deferred) partition_collect(h, m, cl, cg);
+        T->batches++;
+        for (int k = 0; k < m; k++) {
+            Expansion& x = exps[jobs[k].hd];
+            x.have = true; x.cl = cl[k]; x.cg = cg[k];
+        }
         for (size_t i = 0; i < scan_job.size(); i++) {
-            const SplitJob& j = jobs[scan_job[i]];
-            const int small = small_of(j), large = small == j.l ? j.r : j.l;
+            Expansion& x = exps[jobs[scan_job[i]].hd];
+            x.rec[0] = recs[2 * i]; x.rec[1] = recs[2 * i + 1];
             if (deferred) {
-                h->pool.rename(-2 - 2 * scan_job[i], small);
-                h->pool.rename(-3 - 2 * scan_job[i], large);
-                const Interval& v = iv[small];
+                const double rows = (double)(x.cg.left < x.cg.right ? x.cl.left : x.cl.right);
                 T->hist_built++;
-                T->hist_cells += (double)(v.e - v.b) * n_sel;
-                T->hist_rows += (double)(v.e - v.b);
-                T->hist_rows_indexed += (double)(v.e - v.b);
+                T->hist_cells += rows * n_sel;
+                T->hist_rows += rows;
+                T->hist_rows_indexed += rows;
             }
-            apply_record(ns[small], recs[2 * i]); set_split_if_good(small);
-            apply_record(ns[large], recs[2 * i + 1]); set_split_if_good(large);
         }
         int lj = 0;
         for (int k = 0; k < m; k++) {
-            const SplitJob& j = jobs[k];
-            if (j.terminal) {
-                const int small = small_of(j), large = small == j.l ? j.r : j.l;
-                NodeStats &ss = ns[small], &ls = ns[large], &ps = ns[j.nid];
-                ss.sumG = (double)h->h_leaf.h[2 * lj] * h->h_scale.h->inv_g;
-                ss.sumH = (double)h->h_leaf.h[2 * lj + 1] * h->h_scale.h->inv_h;
-                ls.sumG = ps.sumG - ss.sumG; ls.sumH = ps.sumH - ss.sumH;      // setSubstract (:382)
-                for (NodeStats* s : {&ss, &ls}) ytk_host_node_value(&p, s->sumG, s->sumH, &s->root_gain, &s->node_value);
-                set_leaf(j.l); set_leaf(j.r);
-                lj++;
-            } else {
-                queue.push_back({j.l, ns[j.l].best_lc, j.depth + 1, seq++});
-                queue.push_back({j.r, ns[j.r].best_lc, j.depth + 1, seq++});
-            }
+            if (!jobs[k].terminal) continue;
+            Expansion& x = exps[jobs[k].hd];
+            x.leaf[0] = h->h_leaf.h[2 * lj]; x.leaf[1] = h->h_leaf.h[2 * lj + 1];
+            lj++;
         }
+        for (int k = 0; k < m; k++) materialise(jobs[k]);
+        // applied at once, in the order polled -- unless these were expansions computed ahead of time
+        if (lookahead <= 1)
+            for (int k = 0; k < m; k++) commit(jobs[k]);
         T->build_hist += t1 - t0;
         T->find_best_split += now_ms() - t1;
     }
 
-    for (int nid = 0; nid < out->n_nodes; nid++) {                    // updateTreeNodeStat (:387-393)
-        out->loss_chg[nid] = ns[nid].best_lc;
-        out->hess_sum[nid] = (float)ns[nid].sumH;
-        out->sample_cnt[nid] = ns[nid].sample_cnt;
+    for (size_t hd = 0; hd < nid_of.size(); hd++) {                   // updateTreeNodeStat (:387-393)
+        const int nid = nid_of[hd];
+        if (nid < 0) continue;                   // computed ahead of time, never applied
+        out->loss_chg[nid] = ns[hd].best_lc;
+        out->hess_sum[nid] = (float)ns[hd].sumH;
+        out->sample_cnt[nid] = ns[hd].sample_cnt;
+    }
+    // What get_positions / update_scores need: where the rows of every leaf are.  A leaf whose split was
+    // computed ahead of time but never applied has had its rows moved on to its would-be children (and
+    // its own range in the other buffer may since have been reused by their children), so its rows
+    // are the ranges of its deepest computed descendants.
+    h->leaf_ranges.clear();
+    h->tree_made = true;
+    std::vector<int> stack;
+    for (int leaf : leaf_handles) {
+        stack.assign(1, leaf);
+        while (!stack.empty()) {
+            const int hd = stack.back();
+            stack.pop_back();
+            if (exps[hd].hl >= 0) { stack.push_back(exps[hd].hl); stack.push_back(exps[hd].hr); }
+            else if (iv[hd].e > iv[hd].b) h->leaf_ranges.push_back({nid_of[leaf], iv[hd]});
+        }
     }
     if (h->peer_mode) {
         int perr = 0;
@@ -1525,14 +1683,12 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
 
 int ytk_gbdt_get_positions(ytk_gbdt* h, int32_t* node_of_row) {
     if (!h || !node_of_row) return fail(YTK_ERR_ARG, "get_positions: null argument");
-    if (h->iv.empty()) return fail(YTK_ERR_ARG, "get_positions: no tree has been made");
+    if (!h->tree_made) return fail(YTK_ERR_ARG, "get_positions: no tree has been made");
     CK(cudaSetDevice(h->device));
     CK(ytk::launch_fill_i32(h->d_node_of_row, h->N, -1, h->st));
     std::vector<ytk::PosItem> items;
-    for (int nid : h->leaf_nodes) {
-        const Interval& v = h->iv[nid];
-        if (v.e > v.b) items.push_back({(long long)v.b, (long long)v.e, v.buf, nid});
-    }
+    for (const auto& lr : h->leaf_ranges)
+        items.push_back({(long long)lr.second.b, (long long)lr.second.e, lr.second.buf, lr.first});
     CK(h->t_pos.upload(items, h->st, h->arena));
     CK(ytk::launch_fill_positions(h->d_rowidx[0], h->d_rowidx[1], h->t_pos.d, (int)items.size(), h->d_node_of_row, h->st));
     CK(cudaMemcpyAsync(node_of_row, h->d_node_of_row, h->N * sizeof(int32_t), cudaMemcpyDeviceToHost, h->st));
@@ -1582,10 +1738,8 @@ int ytk_gbdt_update_scores(ytk_gbdt* h, int32_t gid) {
         return fail(YTK_ERR_ARG, "update_scores: groupId %d is not the tree the last make() built (%d)", gid, h->last_gid);
     CK(cudaSetDevice(h->device));
     std::vector<ytk::LeafItem> items;
-    for (int nid : h->leaf_nodes) {
-        const Interval& v = h->iv[nid];
-        if (v.e > v.b) items.push_back({(long long)v.b, (long long)v.e, v.buf, h->last_tree[nid].info});
-    }
+    for (const auto& lr : h->leaf_ranges)
+        items.push_back({(long long)lr.second.b, (long long)lr.second.e, lr.second.buf, h->last_tree[lr.first].info});
     CK(h->t_leafval.upload(items, h->st, h->arena));
     CK(ytk::launch_add_leaf_values(h->d_rowidx[0], h->d_rowidx[1], h->t_leafval.d, (int)items.size(), h->d_score,
                                    h->p.class_num, gid, h->st));
