@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--leaves", type=int, default=-1)
     ap.add_argument("--cpu-rows", type=int, default=2_000_000, help="rows of the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-loss-wise", action="store_true", help="skip the extra loss-wise 255-leaf measurement")
     ap.add_argument("--uniform-bins", action="store_true", help="experiment: every feature uniform over its bins")
     return ap.parse_args()
 
@@ -292,6 +293,29 @@ def main():
             dev_round += time.perf_counter() - t0
     barrier()
 
+    # For information: the reference's own Higgs setting (experiment/higgs/local_gbdt.conf: loss-wise
+    # growth, 255 leaves) on the same rows and gradients; BASELINE.json's metric is quoted on depth 8
+    loss_wise = None
+    used_peer, host_waits = bool(tm.last_stats.peer_collectives), tm.last_stats.batches + 1
+    if a.policy == "level" and not a.no_loss_wise:
+        tm.close()
+        kw = dict(tree_kwargs(a), grow_policy="loss", max_depth=-1, max_leaf_cnt=255)
+        tm = yb.GpuTreeMaker(yb.make_params(**kw), start, n, device=local, rank=rank, world=world, nccl_id=nccl_id)
+        for r0 in range(0, n, chunk):
+            tm.upload_rows(xs[r0:r0 + chunk].astype(np.int32), r0)
+        tm.set_grads_ptr(gp_pinned.data_ptr(), 0, n)
+        t_lw = 0.0
+        for step in range(2 + a.steps):
+            barrier()
+            t0 = time.perf_counter()
+            tree = tm.make(0)
+            if step >= 2:
+                t_lw += time.perf_counter() - t0
+        barrier()
+        loss_wise = {"ms_per_tree": t_lw / a.steps * 1e3, "nodes_per_tree": int(tree.n_nodes),
+                     "host_waits_per_tree": tm.last_stats.batches + 1,
+                     "what": "loss-wise growth, 255 leaves (the reference's experiment/higgs conf), same rows"}
+
     vals = torch.tensor([agg["t_tree"], agg["t_e2e"], dev_round], dtype=torch.float64, device="cuda")
     sums = torch.tensor([agg["cells"]], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -316,11 +340,12 @@ def main():
                     "d2h_bytes_per_step": agg["d2h"], "seconds_per_tree": t_e2e / a.steps},
             "device_gradient_round": {"ms_per_round": dev_round / a.steps * 1e3,
                                       "what": "make + score update + sigmoid loss/gradients, all on the device"},
-            "gpu_launches": agg["launches"], "peer_memory_collectives": bool(tm.last_stats.peer_collectives),
+            "loss_wise_255_leaves": loss_wise,
+            "gpu_launches": agg["launches"], "peer_memory_collectives": used_peer,
             "time_stats_ms_per_tree": {"build_hist": agg["ts_build"] / a.steps, "find_best_split": agg["ts_split"] / a.steps,
                                        "partition": agg["ts_part"] / a.steps, "total": agg["ts_total"] / a.steps,
                                        "collectives_gpu": agg["ts_comm"] / a.steps,
-                                       "host_waits": tm.last_stats.batches + 1},
+                                       "host_waits": host_waits},
             "roofline": {"bound": "hbm", "kernel": "hist_build_k", "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg / max(1, agg["hist_launches"]),
