@@ -394,6 +394,25 @@ def test_loss_wise_lookahead_equals_node_at_a_time(kw, ahead, monkeypatch):
         assert np.array_equal(getattr(ta, name), getattr(ta2, name), equal_nan=True), name
 
 
+@pytest.mark.parametrize("kw", [dict(KW, max_depth=8), dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=80)],
+                         ids=["level8", "loss80"])
+def test_single_pass_partition_equals_stable_partition(kw, monkeypatch):
+    """make() partitions rows with one chained-scan kernel that writes right rows in reverse order; the
+    trees and the per-row leaves are those of the stable three-kernel version (YTK_GBDT_STABLE_PARTITION=1)."""
+    n, F = 300000, 28            # 147 tiles at the root: long look-back chains
+    x, start, gp = synth(n, F, 255, 73, skew=True)
+    a = maker(kw, x, start, gp)
+    ta = a.make(0)
+    pa = a.get_positions()
+    monkeypatch.setenv("YTK_GBDT_STABLE_PARTITION", "1")
+    b = maker(kw, x, start, gp)
+    tb = b.make(0)
+    for name, _ in yb.Tree.FIELDS:
+        assert np.array_equal(getattr(ta, name), getattr(tb, name), equal_nan=True), name
+    assert np.array_equal(pa, b.get_positions())
+    assert a.last_stats.kernel_launches < b.last_stats.kernel_launches
+
+
 @pytest.mark.parametrize("bits", [16, 30])
 def test_fixed_point_width(bits, monkeypatch):
     monkeypatch.setenv("YTK_GBDT_FIXED_BITS", str(bits))

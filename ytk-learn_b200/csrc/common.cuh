@@ -113,6 +113,17 @@ cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride,
                              const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                              uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st);
 
+constexpr int kFusedThreads = 512;
+constexpr int kFusedItems = 16;
+constexpr int kFusedTile = kFusedThreads * kFusedItems;     // larger tiles: the chain over a node's tiles is the critical path
+// single pass (chained scan over a node's tiles); right rows come out in reverse input order.
+// tile_state: n_tiles words that need no clearing; ticket: one zero-initialised word; epoch: a value
+// (< 2^30) no earlier launch on the same tile_state used
+cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_stride, int32_t* rowidx0, int32_t* rowidx1,
+                                   const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
+                                   unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
+                                   PartitionCounts* counts, cudaStream_t st);
+
 // K7: exact fixed-point sums of (g,h) over row runs -> out[2*seg + {0,1}] (pre-zeroed)
 cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1, const RowItem* items,
                              int n_items, long long* out, const PartitionCounts* cnt_local,

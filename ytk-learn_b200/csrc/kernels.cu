@@ -867,6 +867,170 @@ cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t*
     return cudaGetLastError();
 }
 
+// Single-pass variant used inside make(): one kernel reads every row id once, gathers its slot,
+// learns where the tile goes from a chained scan over the tiles of its node (decoupled look-back)
+// and writes left rows forward from the node's begin, right rows BACKWARD from its end.  Both
+// sides stay monotonic in input order (the right side reversed), which is all the gathers of the
+// next level care about; the child intervals are the same as the stable version's.
+//   tile_state[t] = epoch << 34 | status << 32 | count;  status 1: the tile's own left count,
+//   2: left count of the node's tiles up to and including t.  Entries of another epoch are "not
+//   yet written", so the array is never cleared.  Tiles are claimed in ticket order, hence every
+//   tile a CTA waits for is already running.
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(kFusedThreads)
+partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, int32_t* __restrict__ rowidx0,
+                  int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs, int n_segs,
+                  const int* __restrict__ tile_seg, int n_tiles, unsigned long long* __restrict__ tile_state,
+                  unsigned int* __restrict__ ticket, unsigned long long epoch, PartitionCounts* __restrict__ counts) {
+    __shared__ int s_tile, s_prefix, s_found;
+    __shared__ int s_warp[kFusedThreads / 32], s_lb_sum[kFusedThreads / 32], s_lb_fp[kFusedThreads / 32];
+    __shared__ int32_t s_rows[kFusedTile];      // the tile, left rows first, both sides in input order
+    if (threadIdx.x == 0) s_tile = (int)atomicInc(ticket, (unsigned)n_tiles - 1u);    // back to 0 after the last tile
+    __syncthreads();
+    const int tile = s_tile;
+    if (tile == 0)
+        for (int k = threadIdx.x; k < n_segs; k += kFusedThreads)
+            if (segs[k].ntiles == 0) counts[k] = {0, 0};
+    const int seg = tile_seg[tile];
+    const SplitSeg sg = segs[seg];
+    const int32_t* __restrict__ rowidx = seg_src(sg, rowidx0, rowidx1);
+    int32_t* __restrict__ out = (sg.buf == 0) ? rowidx1 : rowidx0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int j = tile - sg.tile0;
+    const long long tile_begin = sg.begin + (long long)j * kFusedTile;
+    const int tile_n = (int)min((long long)kFusedTile, sg.end - tile_begin);
+    // thread t owns kFusedItems consecutive items of the tile so that order is preserved
+    const int first = threadIdx.x * kFusedItems;
+    const int mine = max(0, min(kFusedItems, tile_n - first));      // items of this thread that exist
+    int32_t rid[kFusedItems];
+    if (!rowidx) {
+#pragma unroll
+        for (int k = 0; k < kFusedItems; k++) rid[k] = (int32_t)(tile_begin + first + k);
+    } else if (mine == kFusedItems && ((reinterpret_cast<unsigned long long>(rowidx + tile_begin + first) & 15ull) == 0)) {
+        const int4* rp = reinterpret_cast<const int4*>(rowidx + tile_begin + first);
+#pragma unroll
+        for (int q = 0; q < kFusedItems / 4; q++) {
+            const int4 r = rp[q];
+            rid[4 * q] = r.x; rid[4 * q + 1] = r.y; rid[4 * q + 2] = r.z; rid[4 * q + 3] = r.w;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < kFusedItems; k++) rid[k] = k < mine ? rowidx[tile_begin + first + k] : 0;
+    }
+    if (!rowidx && mine < kFusedItems) {
+#pragma unroll
+        for (int k = 0; k < kFusedItems; k++) if (k >= mine) rid[k] = 0;       // never read past the last row
+    }
+    // one addressing form for the three sources: a byte mask over rows (left iff non-zero, i.e. NOT
+    // below 0.5), the feature-major copy, row-major slots
+    const bool mask = sg.fid < 0;
+    const uint8_t* __restrict__ base = mask ? src : (col_stride > 0 ? src + (long long)sg.fid * col_stride : src + sg.fid);
+    const int mul = (mask || col_stride > 0) ? 1 : S8;
+    const float cond = mask ? 0.5f : sg.cond;
+    uint8_t slot[kFusedItems];
+#pragma unroll
+    for (int k = 0; k < kFusedItems; k++) slot[k] = base[(long long)rid[k] * mul];     // independent gathers in flight
+    unsigned fl = 0;                                     // bit k: item k goes left
+#pragma unroll
+    for (int k = 0; k < kFusedItems; k++)
+        fl |= (unsigned)((k < mine) && (((float)slot[k] < cond) != mask)) << k;
+    const int cnt = __popc(fl);
+    int p = cnt;
+    for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, p, d);
+        if (lane >= d) p += t;
+    }
+    if (lane == 31) s_warp[warp] = p;
+    __syncthreads();
+    int woff = 0, tile_left = 0;
+    for (int w = 0; w < kFusedThreads / 32; w++) {
+        if (w < warp) woff += s_warp[w];
+        tile_left += s_warp[w];
+    }
+    // ---- chained scan: publish this tile's left count, then add up the tiles before it back to
+    // the nearest one that already knows its prefix.  Every warp inspects its own window of 32
+    // predecessors, so one round trip to L2 covers 512 tiles.
+    const unsigned long long tag = epoch << 34;
+    if (threadIdx.x == 0) st_volatile_u64(tile_state + tile, tag | ((j == 0 ? 2ull : 1ull) << 32) | (unsigned)tile_left);
+    int excl = 0;                                        // thread 0's
+    if (j > 0) {                                         // (uniform over the CTA)
+        int look = tile - 1;
+        for (;;) {
+            const int t = look - warp * 32 - lane;
+            unsigned long long v;
+            int fp;
+            for (;;) {
+                v = tag | (2ull << 32);                  // before the node's first tile: a virtual "prefix 0"
+                if (t >= sg.tile0) v = ld_volatile_u64(tile_state + t);
+                const int status = (v >> 34) == epoch ? (int)((v >> 32) & 3ull) : 0;
+                const unsigned not_ready = __ballot_sync(0xffffffffu, status == 0);
+                const unsigned is_prefix = __ballot_sync(0xffffffffu, status == 2);
+                fp = is_prefix ? __ffs(is_prefix) - 1 : 32;                    // nearest tile of the window that knows its prefix
+                const unsigned need = fp >= 31 ? 0xffffffffu : ((2u << fp) - 1u);
+                if (!(not_ready & need)) break;                                 // else: a tile in between has not published yet
+            }
+            int c = (lane <= fp) ? (int)(unsigned)v : 0;
+            for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+            if (lane == 0) { s_lb_sum[warp] = c; s_lb_fp[warp] = fp; }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                int found = 0;
+                for (int w = 0; w < kFusedThreads / 32 && !found; w++) {
+                    excl += s_lb_sum[w];
+                    found = s_lb_fp[w] < 32;
+                }
+                s_found = found;
+            }
+            __syncthreads();
+            if (s_found) break;
+            look -= kFusedThreads;
+        }
+    }
+    if (threadIdx.x == 0) {
+        if (j > 0) st_volatile_u64(tile_state + tile, tag | (2ull << 32) | (unsigned)(excl + tile_left));
+        s_prefix = excl;
+        if (j == sg.ntiles - 1) {
+            const long long left = (long long)excl + tile_left;
+            counts[seg] = {left, (sg.end - sg.begin) - left};
+        }
+    }
+    int lpos = woff + p - cnt;                           // lefts of this tile before my first item
+    int rpos = tile_left + (first - lpos);               // rights go after all lefts of the tile
+#pragma unroll
+    for (int k = 0; k < kFusedItems; k++) {
+        if (k < mine) {
+            const bool l = (fl >> k) & 1u;
+            s_rows[l ? lpos : rpos] = rid[k];
+            lpos += l ? 1 : 0;
+            rpos += l ? 0 : 1;
+        }
+    }
+    __syncthreads();
+    const long long left_base = sg.begin + s_prefix;
+    const long long right_last = sg.end - 1 - ((long long)j * kFusedTile - s_prefix) + tile_left;   // minus (i - tile_left) below
+    for (int i = threadIdx.x; i < tile_n; i += kFusedThreads)
+        out[i < tile_left ? left_base + i : right_last - i] = s_rows[i];
+}
+
+cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_stride, int32_t* rowidx0, int32_t* rowidx1,
+                                   const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
+                                   unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
+                                   PartitionCounts* counts, cudaStream_t st) {
+    if (n_segs <= 0) return cudaSuccess;
+    if (n_tiles <= 0) return cudaMemsetAsync(counts, 0, (size_t)n_segs * sizeof(PartitionCounts), st);
+    partition_fused_k<<<n_tiles, kFusedThreads, 0, st>>>(src, S8, col_stride, rowidx0, rowidx1, segs, n_segs, tile_seg,
+                                                        n_tiles, tile_state, ticket, epoch, counts);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, int32_t* rowidx0, int32_t* rowidx1,
                              const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                              uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st) {

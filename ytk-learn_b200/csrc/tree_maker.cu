@@ -272,6 +272,14 @@ struct ytk_gbdt {
     int device = 0, rank = 0, world = 1;
     int fixed_bits = ytk::kDefaultFixedBits;
     bool force_sequential = false;
+    bool single_pass_partition = true;     // YTK_GBDT_STABLE_PARTITION=1: the three-kernel stable version inside make() too
+    unsigned long long* d_tile_state = nullptr;
+    size_t tile_state_cap = 0;
+    unsigned int* d_ticket = nullptr;
+    unsigned long long part_epoch = 0;
+    bool trace = false;         // YTK_GBDT_TRACE=1: per-batch host/GPU timeline on stderr
+    struct TraceRec { int m; double t_pop, t_tables, t_queued, t_done; cudaEvent_t e0, e1; };
+    std::vector<TraceRec> trace_recs;
     int lookahead = 64;         // loss-wise: expansions computed per batch of launches (YTK_GBDT_LOOKAHEAD)
     cudaStream_t st = nullptr;
     ncclComm_t comm = nullptr;
@@ -327,6 +335,7 @@ struct ytk_gbdt {
     PinnedBuf<ytk::GradScale> h_scale;
     PinnedArena arena;
     char* d_blob = nullptr;  size_t blob_cap = 0;     // device side of Blob
+    char* d_blob_part = nullptr;  size_t blob_part_cap = 0;     // ... of the partition tables, which go up (and start work) first
 
     // collectives over NVLink peer memory (world > 1, one node): see kernels.cu, last section
     bool peer_mode = false;
@@ -385,11 +394,11 @@ int ensure_stage(ytk_gbdt* h, size_t bytes) {
 void free_all(ytk_gbdt* h) {
     cudaSetDevice(h->device);
     auto F = [](void* p) { if (p) cudaFree(p); };
-    F(h->d_bins); F(h->d_bins_col); F(h->d_gp); F(h->d_gq); F(h->d_rowidx[0]); F(h->d_rowidx[1]); F(h->d_flags); F(h->d_block_cnt);
+    F(h->d_bins); F(h->d_bins_col); F(h->d_gp); F(h->d_gq); F(h->d_rowidx[0]); F(h->d_rowidx[1]); F(h->d_flags); F(h->d_block_cnt); F(h->d_tile_state); F(h->d_ticket);
     F(h->d_mask); F(h->d_start); F(h->d_nbins); F(h->d_feat_owner); F(h->d_feat_zero); F(h->d_off_inner);
     F(h->d_off_flat); F(h->d_group_mask); F(h->d_fea_sel); F(h->d_hist_flat); F(h->d_hist_flat2);
     F(h->d_hist_dbl); F(h->d_scale); F(h->d_scale_hook); F(h->d_absmax); F(h->d_bad); F(h->d_node_of_row);
-    F(h->d_stage); F(h->d_blob); F(h->d_score); F(h->d_y); F(h->d_w); F(h->d_init); F(h->d_block_loss); F(h->d_loss);
+    F(h->d_stage); F(h->d_blob); F(h->d_blob_part); F(h->d_score); F(h->d_y); F(h->d_w); F(h->d_init); F(h->d_block_loss); F(h->d_loss);
     h->t_leafval.release(); h->t_tree.release();
     if (h->peer_mode)
         for (int r = 0; r < h->world; r++)
@@ -568,22 +577,23 @@ bool peer_ok(const ytk_gbdt* h, int m) {
 }
 
 // one host->device copy of a Blob; afterwards table at offset o lives at h->d_blob + o
-int blob_commit(ytk_gbdt* h, const Blob& bl) {
+int blob_commit_to(ytk_gbdt* h, const Blob& bl, char** d_buf, size_t* cap) {
     const size_t bytes = bl.host.size();
     if (bytes == 0) return YTK_OK;
-    if (bytes > h->blob_cap) {
-        if (h->d_blob) CK(cudaFree(h->d_blob));          // (synchronises: nobody reads the old one any more)
-        h->d_blob = nullptr; h->blob_cap = 0;
+    if (bytes > *cap) {
+        if (*d_buf) CK(cudaFree(*d_buf));                // (synchronises: nobody reads the old one any more)
+        *d_buf = nullptr; *cap = 0;
         size_t nc = std::max<size_t>(bytes * 2, size_t(1) << 20);
-        CK(cudaMalloc(&h->d_blob, nc));
-        h->blob_cap = nc;
+        CK(cudaMalloc(d_buf, nc));
+        *cap = nc;
     }
     void* stage = h->arena.take(bytes, h->st);
     if (!stage) return fail(YTK_ERR_CUDA, "pinned staging allocation failed");
     memcpy(stage, bl.host.data(), bytes);
-    CK(cudaMemcpyAsync(h->d_blob, stage, bytes, cudaMemcpyHostToDevice, h->st));
+    CK(cudaMemcpyAsync(*d_buf, stage, bytes, cudaMemcpyHostToDevice, h->st));
     return YTK_OK;
 }
+int blob_commit(ytk_gbdt* h, const Blob& bl) { return blob_commit_to(h, bl, &h->d_blob, &h->blob_cap); }
 template <typename T>
 const T* blob_ptr(const ytk_gbdt* h, size_t off) { return reinterpret_cast<const T*>(h->d_blob + off); }
 
@@ -775,13 +785,26 @@ struct PartPlan {
     std::vector<ytk::SplitSeg> segs;
     std::vector<int> tile_seg;
     size_t o_segs = 0, o_tiles = 0;
+    bool single_pass = false;       // tiles sized for the chained-scan kernel
+    const ytk::SplitSeg* d_segs = nullptr;      // set by partition_commit
+    const int* d_tiles = nullptr;
 };
-void partition_plan(const std::vector<ytk::SplitSeg>& segs_in, PartPlan& pl, Blob& bl) {
+// The partition tables have their own device buffer: they go up first so that the partition is
+// already running while the host builds the tables of the kernels behind it.
+int partition_commit(ytk_gbdt* h, const Blob& bl, PartPlan& pl) {
+    RET(blob_commit_to(h, bl, &h->d_blob_part, &h->blob_part_cap));
+    pl.d_segs = reinterpret_cast<const ytk::SplitSeg*>(h->d_blob_part + pl.o_segs);
+    pl.d_tiles = reinterpret_cast<const int*>(h->d_blob_part + pl.o_tiles);
+    return YTK_OK;
+}
+void partition_plan(const std::vector<ytk::SplitSeg>& segs_in, PartPlan& pl, Blob& bl, bool single_pass = false) {
     pl.m = (int)segs_in.size();
     pl.segs = segs_in;
+    pl.single_pass = single_pass;
+    const int64_t tile = single_pass ? ytk::kFusedTile : ytk::kPartTile;
     for (int k = 0; k < pl.m; k++) {
         int64_t n = pl.segs[k].end - pl.segs[k].begin;
-        int nt = (int)((n + ytk::kPartTile - 1) / ytk::kPartTile);
+        int nt = (int)((n + tile - 1) / tile);
         pl.segs[k].tile0 = (int)pl.tile_seg.size();
         pl.segs[k].ntiles = nt;
         for (int t = 0; t < nt; t++) pl.tile_seg.push_back(k);
@@ -791,10 +814,36 @@ void partition_plan(const std::vector<ytk::SplitSeg>& segs_in, PartPlan& pl, Blo
 }
 // Queues the kernels, the count allreduce and the copy of the counts to the host; does not wait.
 // Device counts: t_counts.d[0..m) local, [m..2m) global (world > 1).
+// single_pass: the chained-scan kernel (right rows come out reversed; make() only); else the stable
+// three-kernel version the public entry points promise.
 int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const PartPlan& pl) {
+    const bool single_pass = pl.single_pass;
     const int m = pl.m;
     if (m == 0) return YTK_OK;
     const size_t n_tiles = pl.tile_seg.size();
+    if (single_pass) {
+        if (n_tiles > h->tile_state_cap) {
+            if (h->d_tile_state) CK(cudaFree(h->d_tile_state));
+            h->d_tile_state = nullptr;
+            h->tile_state_cap = std::max<size_t>(n_tiles, 2 * h->tile_state_cap);
+            CK(cudaMalloc(&h->d_tile_state, h->tile_state_cap * sizeof(unsigned long long)));
+            CK(cudaMemsetAsync(h->d_tile_state, 0, h->tile_state_cap * sizeof(unsigned long long), h->st));
+            h->part_epoch = 0;
+        }
+        if (!h->d_ticket) {
+            CK(cudaMalloc(&h->d_ticket, sizeof(unsigned int)));
+            CK(cudaMemsetAsync(h->d_ticket, 0, sizeof(unsigned int), h->st));
+        }
+        if (++h->part_epoch >= (1ull << 30)) {       // entries of other epochs read as "not written yet"
+            CK(cudaMemsetAsync(h->d_tile_state, 0, h->tile_state_cap * sizeof(unsigned long long), h->st));
+            h->part_epoch = 1;
+        }
+        CK(h->t_counts.reserve(2 * (size_t)m));
+        CK(ytk::launch_partition_fused(src, h->S8, col_stride, h->d_rowidx[0], h->d_rowidx[1],
+                                       pl.d_segs, m, pl.d_tiles, (int)n_tiles,
+                                       h->d_tile_state, h->d_ticket, h->part_epoch, h->t_counts.d, h->st));
+        h->launches++;
+    } else {
     if (n_tiles + 1 > h->block_cnt_cap) {
         if (h->d_block_cnt) CK(cudaFree(h->d_block_cnt));
         h->d_block_cnt = nullptr;
@@ -803,9 +852,10 @@ int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const
     }
     CK(h->t_counts.reserve(2 * (size_t)m));
     CK(ytk::launch_partition(src, h->S8, col_stride, h->d_rowidx[0], h->d_rowidx[1],
-                             blob_ptr<ytk::SplitSeg>(h, pl.o_segs), m, blob_ptr<int>(h, pl.o_tiles), (int)n_tiles,
+                             pl.d_segs, m, pl.d_tiles, (int)n_tiles,
                              h->d_flags, h->d_block_cnt, h->t_counts.d, h->st));
     h->launches += n_tiles == 0 ? 1 : 3;
+    }
     const int nc = h->world > 1 ? 2 * m : m;
     if (h->world > 1) {   // allreduceArray(long[2], SUM) (:538), all nodes of the batch at once
         RET(comm_mark(h));
@@ -829,7 +879,7 @@ int partition_launch(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const 
     if (segs_in.empty()) return YTK_OK;
     PartPlan pl; Blob bl;
     partition_plan(segs_in, pl, bl);
-    RET(blob_commit(h, bl));
+    RET(partition_commit(h, bl, pl));
     return partition_enqueue(h, src, col_stride, pl);
 }
 // after the stream has been synchronised
@@ -954,6 +1004,8 @@ int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank,
         h->fixed_bits = b;
     }
     if (const char* s = getenv("YTK_GBDT_SEQUENTIAL")) h->force_sequential = atoi(s) != 0;
+    if (const char* s = getenv("YTK_GBDT_STABLE_PARTITION")) h->single_pass_partition = atoi(s) == 0;
+    if (const char* s = getenv("YTK_GBDT_TRACE")) h->trace = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_LOOKAHEAD")) h->lookahead = std::max(1, std::min(1024, atoi(s)));
     auto bail = [&](int code) { free_all(h); delete h; return code; };
     if (cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking) != cudaSuccess)
@@ -1390,6 +1442,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     };
 
     while (!queue.empty()) {
+        const double tr_pop = now_ms();
         std::vector<SplitJob> jobs;
         if (lookahead > 1) {
             // ---- poll (:246-258): the head is a leaf, or its split is applied if it has been computed
@@ -1475,15 +1528,20 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             exps[jobs[k].hd] = Expansion();
             exps[jobs[k].hd].hl = hl; exps[jobs[k].hd].hr = hr;
         }
-        // every work table of the batch goes up in one copy (two when the host must see the counts first)
-        Blob bl_part, bl_rest;
-        Blob& bl = deferred ? bl_part : bl_rest;
+        ytk_gbdt::TraceRec tr{m, tr_pop, 0, 0, 0, nullptr, nullptr};
+        if (h->trace) {
+            CK(cudaEventCreate(&tr.e0)); CK(cudaEventCreate(&tr.e1));
+            CK(cudaEventRecord(tr.e0, h->st));
+        }
+        // the partition's tables go up on their own and the partition starts at once; the tables of
+        // everything behind it are built while it runs
+        Blob bl_part, bl;
         PartPlan pp;
-        partition_plan(segs, pp, bl_part);
+        partition_plan(segs, pp, bl_part, h->single_pass_partition);
         CK(h->t_counts.reserve(2 * (size_t)m));     // its address is handed to the kernels queued below
+        RET(partition_commit(h, bl_part, pp));
+        RET(partition_enqueue(h, h->d_bins_col, h->N, pp));
         if (!deferred) {
-            RET(blob_commit(h, bl_part));
-            RET(partition_enqueue(h, h->d_bins_col, h->N, pp));
             CK(cudaStreamSynchronize(h->st));
             h->arena.rewind();
             finish_partition();
@@ -1559,7 +1617,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         RET(hist_plan(h, hist_jobs, T, n_sel, hp, bl));
         const size_t o_leaf = bl.add(leaf_items), o_subs = bl.add(subs), o_scans = bl.add(scans);
         RET(blob_commit(h, bl));
-        if (deferred) RET(partition_enqueue(h, h->d_bins_col, h->N, pp));
+        tr.t_tables = now_ms();
         if (n_leaf_jobs > 0) {
             CK(h->t_leaf.reserve(2 * (size_t)n_leaf_jobs));
             CK(h->h_leaf.reserve(2 * (size_t)n_leaf_jobs));
@@ -1588,7 +1646,11 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         }
         double t1 = now_ms();
         RET(search_enqueue(h, blob_ptr<ytk::ScanNode>(h, o_scans), (int)scans.size(), first_owned, d_cg));
+        if (h->trace) CK(cudaEventRecord(tr.e1, h->st));
+        tr.t_queued = now_ms();
         CK(cudaStreamSynchronize(h->st));            // the one host wait of the batch
+        tr.t_done = now_ms();
+        if (h->trace) h->trace_recs.push_back(tr);
         h->arena.rewind();
         search_collect(h, (int)scans.size(), recs);
         if (deferred) partition_collect(h, m, cl, cg);
@@ -1651,6 +1713,19 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         CK(cudaMemcpyAsync(&perr, h->d_peer_err, sizeof(int), cudaMemcpyDeviceToHost, h->st));
         CK(cudaStreamSynchronize(h->st));
         if (perr) return fail(YTK_ERR_NCCL, "make_tree: a peer GPU did not reach a collective within 3 s");
+    }
+    if (h->trace) {
+        double prev_done = 0;
+        for (const auto& r : h->trace_recs) {
+            float gpu = 0.f;
+            cudaEventElapsedTime(&gpu, r.e0, r.e1);
+            fprintf(stderr, "[ytk trace] batch m=%3d  since_prev_wait %6.1f us | tables %6.1f | enqueue %6.1f | wait %7.1f | gpu_span %7.1f us\n",
+                    r.m, prev_done > 0 ? (r.t_pop - prev_done) * 1e3 : 0.0, (r.t_tables - r.t_pop) * 1e3,
+                    (r.t_queued - r.t_tables) * 1e3, (r.t_done - r.t_queued) * 1e3, gpu * 1e3);
+            prev_done = r.t_done;
+            cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
+        }
+        h->trace_recs.clear();
     }
     h->last_tree.resize(out->n_nodes);
     for (int nid = 0; nid < out->n_nodes; nid++)
