@@ -220,14 +220,19 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
-    nccl_id = None
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    def fresh_nccl_id():
+        """One NCCL unique id per tree-maker clique, made on rank 0 and handed round by the host."""
+        if world == 1:
+            return None
         idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
             idt.copy_(torch.from_numpy(yb.nccl_unique_id()))
         dist.broadcast(idt, 0)
-        nccl_id = idt.cpu().numpy()
+        return idt.cpu().numpy()
+
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    nccl_id = fresh_nccl_id()
 
     def barrier():
         torch.cuda.synchronize()
@@ -300,7 +305,8 @@ def main():
     if a.policy == "level" and not a.no_loss_wise:
         tm.close()
         kw = dict(tree_kwargs(a), grow_policy="loss", max_depth=-1, max_leaf_cnt=255)
-        tm = yb.GpuTreeMaker(yb.make_params(**kw), start, n, device=local, rank=rank, world=world, nccl_id=nccl_id)
+        tm = yb.GpuTreeMaker(yb.make_params(**kw), start, n, device=local, rank=rank, world=world,
+                             nccl_id=fresh_nccl_id())
         for r0 in range(0, n, chunk):
             tm.upload_rows(xs[r0:r0 + chunk].astype(np.int32), r0)
         tm.set_grads_ptr(gp_pinned.data_ptr(), 0, n)
