@@ -12,6 +12,7 @@
 #include <deque>
 #include <limits>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "common.cuh"
@@ -85,25 +86,35 @@ struct HistPool {
     std::deque<Item*> avail;     // FIFO
     std::vector<Item*> all;
 
+    std::unordered_map<int, Item*> by_key;    // the entries of `used`, by key
+
     void clear() {               // :200-206
         for (Item* it : used) avail.push_back(it);
         used.clear();
+        by_key.clear();
     }
     void rename(int from, int to) {   // in-place reuse of a slot (sibling written over its parent)
-        for (Item* it : used) if (it->nid == from) { it->nid = to; return; }
+        auto f = by_key.find(from);
+        if (f == by_key.end()) return;
+        Item* it = f->second;
+        by_key.erase(f);
+        it->nid = to;
+        by_key[to] = it;
     }
     long long* get(int nid) {    // getHist :238-245
-        for (Item* it : used) if (it->nid == nid) return it->buf;
-        return nullptr;
+        auto f = by_key.find(nid);
+        return f == by_key.end() ? nullptr : f->second->buf;
     }
     void release(int nid) {      // releaseHist :256-267
-        for (size_t i = 0; i < used.size(); i++) {
-            if (used[i]->nid == nid) {
-                avail.push_back(used[i]);
-                used.erase(used.begin() + i);
-                return;
-            }
+        auto f = by_key.find(nid);
+        if (f == by_key.end()) return;
+        Item* it = f->second;
+        by_key.erase(f);
+        // `used` keeps allocation order for the eviction rule; released entries are usually recent
+        for (size_t i = used.size(); i-- > 0;) {
+            if (used[i] == it) { used.erase(used.begin() + i); break; }
         }
+        avail.push_back(it);
     }
     // allocHist :209-236; *fresh is set when a new device buffer is needed.  `unbounded`: the
     // reference's capacity (max_leaf_cnt) can never be exceeded by its own allocation order, so
@@ -120,9 +131,11 @@ struct HistPool {
             *fresh = true;
         } else {
             it = used.front(); used.erase(used.begin());   // evict the oldest
+            by_key.erase(it->nid);
         }
         it->nid = nid;
         used.push_back(it);
+        by_key[nid] = it;
         return it;
     }
 };
@@ -278,7 +291,7 @@ struct ytk_gbdt {
     unsigned int* d_ticket = nullptr;
     unsigned long long part_epoch = 0;
     bool trace = false;         // YTK_GBDT_TRACE=1: per-batch host/GPU timeline on stderr
-    struct TraceRec { int m; double t_pop, t_tables, t_queued, t_done; cudaEvent_t e0, e1; };
+    struct TraceRec { int m; double t_pop, t_jobs, t_part, t_tables, t_queued, t_done; cudaEvent_t e0, e1; };
     std::vector<TraceRec> trace_recs;
     int lookahead = 64;         // loss-wise: expansions computed per batch of launches (YTK_GBDT_LOOKAHEAD)
     cudaStream_t st = nullptr;
@@ -1484,11 +1497,16 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         } else {
             // ---- poll: one node (the reference's order), or -- level-wise with an unbounded pool -- every
             // node of the level, which the reference would poll back to back in the same (seq) order
-            const size_t n_pop = batch_levels ? queue.size() : 1;
-            for (size_t q = 0; q < n_pop; q++) {
+            std::vector<ExpandNode> polled;
+            if (batch_levels) {
+                polled.swap(queue);
+                std::sort(polled.begin(), polled.end(), polled_before);
+            } else {
                 const size_t hi = head_index(queue, polled_before);
-                const ExpandNode e = queue[hi];
+                polled.push_back(queue[hi]);
                 queue.erase(queue.begin() + hi);
+            }
+            for (const ExpandNode& e : polled) {
                 if (becomes_leaf(e)) { set_leaf(e.hd); continue; }
                 const int hl = new_handle(), hr = new_handle();
                 exps[e.hd].hl = hl; exps[e.hd].hr = hr;
@@ -1528,7 +1546,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             exps[jobs[k].hd] = Expansion();
             exps[jobs[k].hd].hl = hl; exps[jobs[k].hd].hr = hr;
         }
-        ytk_gbdt::TraceRec tr{m, tr_pop, 0, 0, 0, nullptr, nullptr};
+        ytk_gbdt::TraceRec tr{m, tr_pop, now_ms(), 0, 0, 0, 0, nullptr, nullptr};
         if (h->trace) {
             CK(cudaEventCreate(&tr.e0)); CK(cudaEventCreate(&tr.e1));
             CK(cudaEventRecord(tr.e0, h->st));
@@ -1541,6 +1559,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         CK(h->t_counts.reserve(2 * (size_t)m));     // its address is handed to the kernels queued below
         RET(partition_commit(h, bl_part, pp));
         RET(partition_enqueue(h, h->d_bins_col, h->N, pp));
+        tr.t_part = now_ms();
         if (!deferred) {
             CK(cudaStreamSynchronize(h->st));
             h->arena.rewind();
@@ -1719,8 +1738,9 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         for (const auto& r : h->trace_recs) {
             float gpu = 0.f;
             cudaEventElapsedTime(&gpu, r.e0, r.e1);
-            fprintf(stderr, "[ytk trace] batch m=%3d  since_prev_wait %6.1f us | tables %6.1f | enqueue %6.1f | wait %7.1f | gpu_span %7.1f us\n",
-                    r.m, prev_done > 0 ? (r.t_pop - prev_done) * 1e3 : 0.0, (r.t_tables - r.t_pop) * 1e3,
+            fprintf(stderr, "[ytk trace] batch m=%3d  since_prev_wait %6.1f us | pop %5.1f | partition queued %5.1f | tables %6.1f | enqueue %6.1f | wait %7.1f | gpu_span %7.1f us\n",
+                    r.m, prev_done > 0 ? (r.t_pop - prev_done) * 1e3 : 0.0, (r.t_jobs - r.t_pop) * 1e3,
+                    (r.t_part - r.t_jobs) * 1e3, (r.t_tables - r.t_part) * 1e3,
                     (r.t_queued - r.t_tables) * 1e3, (r.t_done - r.t_queued) * 1e3, gpu * 1e3);
             prev_done = r.t_done;
             cudaEventDestroy(r.e0); cudaEventDestroy(r.e1);
