@@ -28,7 +28,7 @@ typedef enum {
     YTK_ERR_CUDA = -2,       /* CUDA runtime error, or no device */
     YTK_ERR_CAPACITY = -3,   /* caller-provided output too small */
     YTK_ERR_NCCL = -4,       /* NCCL missing or failed (world > 1 only) */
-    YTK_ERR_UNSUPPORTED = -5 /* e.g. a feature with more than 256 bins */
+    YTK_ERR_UNSUPPORTED = -5 /* e.g. a feature with more than 65536 bins */
 } ytk_status;
 
 typedef struct ytk_gbdt ytk_gbdt;  /* one per (GPU, row shard): the reference's per-thread tree maker */
@@ -135,7 +135,8 @@ int ytk_gbdt_set_bins(ytk_gbdt *h, const int32_t *start, int32_t F, int64_t n_ro
 
 /* One chunk of GBDTCoreData.x after binning (J/dataflow/GBDTCoreData.java:164-168,
  * FeatureApprData.java:202): int32 slot indices, row-major with stride S = maxFeatureDim.
- * The device keeps them as uint8, row-major, padded to 32 features. */
+ * The device keeps them as uint8, row-major, padded to 32 features (uint16 columns for the
+ * features with more than 256 bins). */
 int ytk_gbdt_upload_rows(ytk_gbdt *h, const int32_t *x_chunk, int64_t row0, int64_t nrows,
                          int32_t stride);
 

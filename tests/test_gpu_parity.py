@@ -57,10 +57,76 @@ def test_upload_download_roundtrip_and_range_check():
         tm.upload_rows(bad)
 
 
-def test_more_than_256_bins_is_refused():
+def test_more_than_65536_bins_is_refused():
     with pytest.raises(yb.YtkError) as ei:
-        yb.GpuTreeMaker(yb.make_params(**KW), np.array([0, 300], np.int32), 10)
+        yb.GpuTreeMaker(yb.make_params(**KW), np.array([0, 70000], np.int32), 10)
     assert ei.value.code == -5
+
+
+# ---------------------------------------------------------------- features with more than 256 bins
+# ("no_sample" on a continuous column, or sample_by_cnt over many threads): uint16 slots, their
+# histograms built by hist_wide_k; everything else is the same path
+WIDE_NBS = [300, 5, 1000, 256, 257, 4000, 2, 255, 40, 700]
+
+
+def test_wide_features_upload_quantize_roundtrip():
+    rng = np.random.default_rng(11)
+    n, F = 20000, len(WIDE_NBS)
+    x, start, gp = synth(n, F, WIDE_NBS, 5, S=F + 2)
+    tm = yb.GpuTreeMaker(yb.make_params(**KW), start, n)
+    tm.upload_rows(x[:7000], 0)
+    tm.upload_rows(x[7000:], 7000)
+    assert np.array_equal(tm.download_rows(), x[:, :F])
+    bad = x.copy()
+    bad[5, 0] = 300                      # feature 0 has slots 0..299
+    with pytest.raises(yb.YtkError):
+        tm.upload_rows(bad)
+    cuts = np.concatenate([np.sort(rng.normal(size=nb)).astype(np.float32) for nb in WIDE_NBS])
+    vals = rng.normal(size=(n, F)).astype(np.float32)
+    tm2 = yb.GpuTreeMaker(yb.make_params(**KW), start, n)
+    tm2.quantize_rows(vals, cuts)
+    assert np.array_equal(tm2.download_rows(), ob.find_bins(vals, cuts, start))
+
+
+def test_wide_features_histogram_partition_split():
+    n, F = 40000, len(WIDE_NBS)
+    x, start, gp = synth(n, F, WIDE_NBS, 9, skew=True)
+    tm = maker(KW, x, start, gp)
+    rows = np.sort(np.random.default_rng(2).permutation(n)[:25000]).astype(np.int32)
+    got = tm.build_hist(0, rows=rows)
+    want = ob.build_hist(x, gp, 1, 0, rows, np.arange(F), start)
+    assert_hist_close(got, want, gp)
+    for fid, cond in [(0, 120.5), (2, 999.5), (5, 0.5), (4, 256.5), (3, 255.5)]:
+        out, lc = tm.partition_rows(rows, fid, cond)
+        left_mask = x[rows, fid].astype(np.float32) < np.float32(cond)
+        assert lc == int(left_mask.sum())
+        assert np.array_equal(out[:lc], rows[left_mask]) and np.array_equal(out[lc:], rows[~left_mask])
+    got = tm.find_split(want, len(rows))
+    best, G, H, rg = _oracle_split(ob.make_params(**KW), want, start, len(rows), np.arange(F, dtype=np.int32))
+    assert got.fid == best[1] and got.lo == best[2] and got.hi == best[3], (got.as_tuple(), best)
+    assert abs(got.loss_chg - best[0]) <= REL * max(1.0, abs(best[0]))
+
+
+@pytest.mark.parametrize("kw", [dict(KW, max_depth=6), dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=40)],
+                         ids=["level6", "loss40"])
+def test_wide_features_whole_tree(kw):
+    n, F = 50000, len(WIDE_NBS)
+    x, start, gp = synth(n, F, WIDE_NBS, 13, skew=True)
+    tm = maker(kw, x, start, gp)
+    t = tm.make(0)
+    o, opos, _ = ob.make_tree(ob.make_params(**kw), x, gp, 0, start)
+    assert_same_tree(t, o)
+    assert np.array_equal(tm.get_positions(), opos)
+    inner = t.left != -1
+    assert (np.asarray(WIDE_NBS)[t.fid[inner]] > 256).any()       # the tree does split on wide features
+    # feature and row sampling on top
+    rng = np.random.default_rng(4)
+    fea = np.sort(rng.permutation(F)[:6]).astype(np.int32)
+    mask = (rng.random(n) < 0.5).astype(np.uint8)
+    t = tm.make(0, fea_index=fea, row_mask=mask)
+    o, opos, _ = ob.make_tree(ob.make_params(**kw), x, gp, 0, start, fea_index=fea, row_mask=mask)
+    assert_same_tree(t, o)
+    assert np.array_equal(tm.get_positions(), opos)
 
 
 # ---------------------------------------------------------------- A2 histogram

@@ -10,6 +10,7 @@ namespace ytk {
 
 constexpr int kGroup = 32;        // features per group = lanes of a warp
 constexpr int kMaxBins = 256;     // uint8 slots
+constexpr int kMaxWideBins = 65536;   // features with more than kMaxBins slots ("wide") keep uint16 slots
 constexpr int kHistThreads = 1024;
 constexpr int kHistWarps = kHistThreads / 32;
 // per-CTA shared histogram: 32-bit words [bin][{lo,hi}][feature] for g, then the same for h:
@@ -51,8 +52,12 @@ struct SplitSeg {
     float cond;       // go left iff (float)slot < cond
     int tile0;        // first tile of this segment in the tile table
     int ntiles;
-    int pad;
+    int wide;         // split feature is wide: its column in WideCols + 1; else 0
 };
+
+// Slots of the wide features: uint16, feature-major, one column of `stride` rows per wide feature.
+// index[f] = column of feature f, -1 if it has at most kMaxBins slots (null: no wide features).
+struct WideCols { uint16_t* data; int64_t stride; const int32_t* index; };
 
 // cseg >= 0: sample_cnt is the global row count of the smaller (which = 0) / larger (which = 1)
 // child of split segment cseg, read from the device counts
@@ -66,13 +71,14 @@ struct TreeNodeDev { int left, right, fid; float info; };             // device 
 // ---- launchers (kernels.cu); all asynchronous on `st`, return cudaGetLastError() ----
 
 // both also write the feature-major copy col[f * col_stride + row] the partition gathers from
-cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, int32_t F,
-                               uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, int64_t row_base,
-                               int* bad_flag, cudaStream_t st);
+// (`wide.data` is passed already advanced to the chunk's first row, like `bins` and `col`)
+cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, int32_t F, const int32_t* nbins,
+                               uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, WideCols wide,
+                               int64_t row_base, int* bad_flag, cudaStream_t st);
 cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t stride, int32_t F,
                                  const float* cuts, const int32_t* start, uint8_t* bins, int32_t S8,
-                                 uint8_t* col, int64_t col_stride, int64_t row_base, cudaStream_t st);
-cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, int32_t F, int32_t* out,
+                                 uint8_t* col, int64_t col_stride, WideCols wide, int64_t row_base, cudaStream_t st);
+cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, int32_t F, WideCols wide, int32_t* out,
                                cudaStream_t st);
 
 // (g,h) float pairs of class gid -> fixed-point int2 (|value| < 2^bits) + scales
@@ -87,6 +93,11 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
                               const uint32_t* group_mask, const int32_t* nbins, const int32_t* feat_owner,
                               const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
                               const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st);
+// the wide features' share of the same work items: 64-bit global reductions, one CTA per (item, feature)
+cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide, const int2* gq, const int32_t* rowidx0,
+                             const int32_t* rowidx1, const RowItem* items, int n_items, const int32_t* feat_owner,
+                             const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
+                             const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st);
 // rows one hist work item should cover so that `total_rows` split into about two waves of CTAs
 int64_t hist_rows_per_item(int64_t total_rows, int groups);
 
@@ -109,7 +120,7 @@ constexpr int kPartThreads = 256;
 constexpr int kPartItems = 8;
 constexpr int kPartTile = kPartThreads * kPartItems;
 // src: col_stride > 0 -> feature-major slots src[fid * col_stride + row]; else row-major with S8 bytes per row
-cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, int32_t* rowidx0, int32_t* rowidx1,
+cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
                              const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                              uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st);
 
@@ -119,7 +130,7 @@ constexpr int kFusedTile = kFusedThreads * kFusedItems;     // larger tiles: the
 // single pass (chained scan over a node's tiles); right rows come out in reverse input order.
 // tile_state: n_tiles words that need no clearing; ticket: one zero-initialised word; epoch: a value
 // (< 2^30) no earlier launch on the same tile_state used
-cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_stride, int32_t* rowidx0, int32_t* rowidx1,
+cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
                                    const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                                    unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
                                    PartitionCounts* counts, cudaStream_t st);
@@ -155,7 +166,7 @@ cudaError_t launch_peer_pull_reduce(const PeerTable& pt, int m, long long seg_ma
 // §8(f) row 1: score update + loss + gradient pairs on the device
 cudaError_t launch_add_leaf_values(const int32_t* rowidx0, const int32_t* rowidx1, const LeafItem* items, int n_items,
                                    float* score, int32_t K, int32_t gid, cudaStream_t st);
-cudaError_t launch_walk_rows(const uint8_t* bins, int32_t S8, const int32_t* rows, long long begin, long long end,
+cudaError_t launch_walk_rows(const uint8_t* bins, int32_t S8, WideCols wide, const int32_t* rows, long long begin, long long end,
                              const TreeNodeDev* nodes, float* score, int32_t K, int32_t gid, cudaStream_t st);
 int loss_grad_blocks();
 // loss_kind 0 sigmoid, 1 l2, 2 softmax (y one-hot [n][K]); block_loss: loss_grad_blocks() doubles of scratch

@@ -20,8 +20,9 @@ namespace ytk {
 //     feature group and row).
 // ------------------------------------------------------------------------------------
 __global__ void repack_rows_k(const int32_t* __restrict__ x, int64_t nrows, int32_t stride, int32_t F,
-                              uint8_t* __restrict__ bins, int32_t S8, uint8_t* __restrict__ col, int64_t col_stride,
-                              int64_t row_base, int* bad_flag) {
+                              const int32_t* __restrict__ nbins, uint8_t* __restrict__ bins, int32_t S8,
+                              uint8_t* __restrict__ col, int64_t col_stride, WideCols wide, int64_t row_base,
+                              int* bad_flag) {
     int64_t total = nrows * S8;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
@@ -33,9 +34,14 @@ __global__ void repack_rows_k(const int32_t* __restrict__ x, int64_t nrows, int3
         uint8_t b = (uint8_t)((r + row_base) * 37 + f * 11);
         if (f < F) {
             int32_t v = x[r * stride + f];
-            if (v < 0 || v >= kMaxBins) { *bad_flag = 1; v = 0; }
-            b = (uint8_t)v;
-            col[f * col_stride + r] = b;
+            if (v < 0 || v >= nbins[f]) { *bad_flag = 1; v = 0; }
+            const int wi = wide.index ? wide.index[f] : -1;
+            if (wi >= 0) {
+                wide.data[wi * wide.stride + r] = (uint16_t)v;     // its byte in the uint8 matrices stays filler
+            } else {
+                b = (uint8_t)v;
+                col[f * col_stride + r] = b;
+            }
         }
         bins[i] = b;
     }
@@ -67,7 +73,7 @@ __device__ __forceinline__ int32_t find_bin(const float* __restrict__ c, int32_t
 __global__ void quantize_rows_k(const int32_t* __restrict__ xbits, int64_t nrows, int32_t stride, int32_t F,
                                 const float* __restrict__ cuts, const int32_t* __restrict__ start,
                                 uint8_t* __restrict__ bins, int32_t S8, uint8_t* __restrict__ col, int64_t col_stride,
-                                int64_t row_base) {
+                                WideCols wide, int64_t row_base) {
     int64_t total = nrows * S8;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
@@ -77,21 +83,28 @@ __global__ void quantize_rows_k(const int32_t* __restrict__ xbits, int64_t nrows
         if (f < F) {
             float v = __int_as_float(xbits[r * stride + f]);
             int32_t s0 = start[f];
-            b = (uint8_t)find_bin(cuts + s0, start[f + 1] - s0, v);
-            col[f * col_stride + r] = b;
+            const int32_t slot = find_bin(cuts + s0, start[f + 1] - s0, v);
+            const int wi = wide.index ? wide.index[f] : -1;
+            if (wi >= 0) {
+                wide.data[wi * wide.stride + r] = (uint16_t)slot;
+            } else {
+                b = (uint8_t)slot;
+                col[f * col_stride + r] = b;
+            }
         }
         bins[i] = b;
     }
 }
 
-__global__ void unpack_rows_k(const uint8_t* __restrict__ bins, int32_t S8, int64_t nrows, int32_t F,
+__global__ void unpack_rows_k(const uint8_t* __restrict__ bins, int32_t S8, int64_t nrows, int32_t F, WideCols wide,
                               int32_t* __restrict__ out) {
     int64_t total = nrows * F;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
         int64_t r = i / F;
         int32_t f = (int32_t)(i - r * F);
-        out[i] = bins[r * S8 + f];
+        const int wi = wide.index ? wide.index[f] : -1;
+        out[i] = wi >= 0 ? (int32_t)wide.data[wi * wide.stride + r] : (int32_t)bins[r * S8 + f];
     }
 }
 
@@ -330,6 +343,30 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
 
 // K3: sibling = parent - smaller child (HistogramBuilder.substract,
 //     J/data/gbdt/HistogramBuilder.java:101-107), exact in the integer domain.
+// Features with more than 256 slots ("wide", e.g. un-sampled continuous columns) do not fit the
+// shared-memory layout above; their (g,h) go straight into the node's histogram with 64-bit global
+// reductions -- thousands of bins, so little contention.  Same work items as hist_build_k; one
+// CTA per (item, wide feature).
+__global__ void __launch_bounds__(256)
+hist_wide_k(WideCols wide, const int32_t* __restrict__ wide_fids, const int2* __restrict__ gq,
+            const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1,
+            const RowItem* __restrict__ items, const int32_t* __restrict__ feat_owner,
+            const int64_t* __restrict__ feat_inner, long long owner_stride, long long* const* __restrict__ seg_out,
+            const PartitionCounts* __restrict__ cnt_local, const PartitionCounts* __restrict__ cnt_global) {
+    const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
+    const int f = wide_fids[blockIdx.y];
+    const uint16_t* __restrict__ colp = wide.data + (long long)wide.index[f] * wide.stride;
+    const int32_t* __restrict__ rows = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
+    unsigned long long* out = reinterpret_cast<unsigned long long*>(seg_out[it.seg] + feat_owner[f] * owner_stride + feat_inner[f]);
+    for (long long i = it.begin + threadIdx.x; i < it.end; i += blockDim.x) {
+        const int32_t rid = rows ? rows[i] : (int32_t)i;
+        const int2 q = gq[rid];
+        const int slot = colp[rid];
+        atomicAdd(out + 2 * slot, (unsigned long long)(long long)q.x);
+        atomicAdd(out + 2 * slot + 1, (unsigned long long)(long long)q.y);
+    }
+}
+
 __global__ void hist_subtract_k(const SubItem* __restrict__ items, int64_t len) {
     const SubItem it = items[blockIdx.y];
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
@@ -468,18 +505,19 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
         int carry_last = -1;
         float b_lc = -CUDART_INF_F;
         int b_lo = -1, b_hi = 0x7fffffff;
-        // all bins of the feature are fetched up front (at most kMaxBins / 32 = 8 loads in flight)
-        // instead of one dependent memory round trip per 32-bin chunk
+        // 256 bins at a time (one pass for a feature with uint8 slots) are fetched up front -- 8 loads
+        // in flight instead of one dependent memory round trip per 32-bin chunk
+        for (int blk = 0; blk < nb; blk += kMaxBins) {
         longlong2 pre[kMaxBins / 32];
 #pragma unroll
         for (int c = 0; c < kMaxBins / 32; c++) {
-            const int j = c * 32 + lane;
+            const int j = blk + c * 32 + lane;
             pre[c] = make_longlong2(0, 0);
             if (j < nb) pre[c] = *reinterpret_cast<const longlong2*>(hp + 2 * j);
         }
 #pragma unroll
         for (int c = 0; c < kMaxBins / 32; c++) {
-            const int c0 = c * 32;
+            const int c0 = blk + c * 32;
             if (c0 >= nb) break;
             int j = c0 + lane;
             long long g = pre[c].x, h = pre[c].y;
@@ -508,6 +546,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
             carryG += __shfl_sync(0xffffffffu, pg, 31);
             carryH += __shfl_sync(0xffffffffu, ph, 31);
             if (m) carry_last = c0 + 31 - __clz(m);
+        }
         }
         // first (lowest bin) maximum inside the feature
         for (int d = 16; d > 0; d >>= 1) {
@@ -561,8 +600,8 @@ __device__ __forceinline__ const int32_t* seg_src(const SplitSeg& s, const int32
 }
 
 __global__ void __launch_bounds__(kPartThreads)
-partition_count_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, const int32_t* __restrict__ rowidx0,
-                  const int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs,
+partition_count_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, WideCols wide,
+                  const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs,
                   const int* __restrict__ tile_seg, uint8_t* __restrict__ flags, int32_t* __restrict__ block_cnt) {
     __shared__ int s_cnt[kPartThreads / 32];
     const SplitSeg sg = segs[tile_seg[blockIdx.x]];
@@ -576,6 +615,7 @@ partition_count_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
             int32_t rid = rowidx ? rowidx[i] : (int32_t)i;
             bool left;
             if (sg.fid < 0) left = src[rid] != 0;
+            else if (sg.wide > 0) left = (float)wide.data[(sg.wide - 1) * wide.stride + rid] < sg.cond;   // uint16 column
             else if (col_stride > 0) left = (float)src[sg.fid * col_stride + rid] < sg.cond;   // feature-major copy
             else left = (float)src[(long long)rid * S8 + sg.fid] < sg.cond;
             flags[i] = left ? 1 : 0;
@@ -757,26 +797,26 @@ static inline int grid_for(int64_t n, int threads, int max_blocks = kNumSMs * 8)
     return (int)b;
 }
 
-cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, int32_t F, uint8_t* bins,
-                               int32_t S8, uint8_t* col, int64_t col_stride, int64_t row_base, int* bad_flag,
-                               cudaStream_t st) {
+cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, int32_t F, const int32_t* nbins,
+                               uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, WideCols wide,
+                               int64_t row_base, int* bad_flag, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    repack_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, bins, S8, col, col_stride, row_base,
-                                                             bad_flag);
+    repack_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, nbins, bins, S8, col, col_stride, wide,
+                                                             row_base, bad_flag);
     return cudaGetLastError();
 }
 cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t stride, int32_t F,
                                  const float* cuts, const int32_t* start, uint8_t* bins, int32_t S8,
-                                 uint8_t* col, int64_t col_stride, int64_t row_base, cudaStream_t st) {
+                                 uint8_t* col, int64_t col_stride, WideCols wide, int64_t row_base, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
     quantize_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(xbits, nrows, stride, F, cuts, start, bins, S8, col,
-                                                               col_stride, row_base);
+                                                               col_stride, wide, row_base);
     return cudaGetLastError();
 }
-cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, int32_t F, int32_t* out,
+cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, int32_t F, WideCols wide, int32_t* out,
                                cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    unpack_rows_k<<<grid_for(nrows * F, 256), 256, 0, st>>>(bins, S8, nrows, F, out);
+    unpack_rows_k<<<grid_for(nrows * F, 256), 256, 0, st>>>(bins, S8, nrows, F, wide, out);
     return cudaGetLastError();
 }
 
@@ -817,6 +857,17 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
     hist_build_k<<<grid, kHistThreads, kHistSmemBytes, st>>>(bins, S8, gq, rowidx0, rowidx1, items, F, group_mask,
                                                              nbins, feat_owner, feat_inner, owner_stride, seg_out,
                                                              cnt_local, cnt_global);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide, const int2* gq, const int32_t* rowidx0,
+                             const int32_t* rowidx1, const RowItem* items, int n_items, const int32_t* feat_owner,
+                             const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
+                             const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st) {
+    if (n_items <= 0 || n_wide <= 0) return cudaSuccess;
+    dim3 grid((unsigned)n_items, (unsigned)n_wide);
+    hist_wide_k<<<grid, 256, 0, st>>>(wide, wide_fids, gq, rowidx0, rowidx1, items, feat_owner, feat_inner, owner_stride,
+                                      seg_out, cnt_local, cnt_global);
     return cudaGetLastError();
 }
 
@@ -886,7 +937,7 @@ __device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned 
 }
 
 __global__ void __launch_bounds__(kFusedThreads)
-partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, int32_t* __restrict__ rowidx0,
+partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* __restrict__ rowidx0,
                   int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs, int n_segs,
                   const int* __restrict__ tile_seg, int n_tiles, unsigned long long* __restrict__ tile_state,
                   unsigned int* __restrict__ ticket, unsigned long long epoch, PartitionCounts* __restrict__ counts) {
@@ -935,9 +986,15 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     const uint8_t* __restrict__ base = mask ? src : (col_stride > 0 ? src + (long long)sg.fid * col_stride : src + sg.fid);
     const int mul = (mask || col_stride > 0) ? 1 : S8;
     const float cond = mask ? 0.5f : sg.cond;
-    uint8_t slot[kFusedItems];
+    unsigned short slot[kFusedItems];
+    if (sg.wide > 0) {                                   // a feature with more than 256 slots: its uint16 column
+        const uint16_t* __restrict__ wb = wide.data + (long long)(sg.wide - 1) * wide.stride;
 #pragma unroll
-    for (int k = 0; k < kFusedItems; k++) slot[k] = base[(long long)rid[k] * mul];     // independent gathers in flight
+        for (int k = 0; k < kFusedItems; k++) slot[k] = wb[rid[k]];
+    } else {
+#pragma unroll
+        for (int k = 0; k < kFusedItems; k++) slot[k] = base[(long long)rid[k] * mul];     // independent gathers in flight
+    }
     unsigned fl = 0;                                     // bit k: item k goes left
 #pragma unroll
     for (int k = 0; k < kFusedItems; k++)
@@ -1020,23 +1077,23 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
         out[i < tile_left ? left_base + i : right_last - i] = s_rows[i];
 }
 
-cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_stride, int32_t* rowidx0, int32_t* rowidx1,
+cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
                                    const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                                    unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
                                    PartitionCounts* counts, cudaStream_t st) {
     if (n_segs <= 0) return cudaSuccess;
     if (n_tiles <= 0) return cudaMemsetAsync(counts, 0, (size_t)n_segs * sizeof(PartitionCounts), st);
-    partition_fused_k<<<n_tiles, kFusedThreads, 0, st>>>(src, S8, col_stride, rowidx0, rowidx1, segs, n_segs, tile_seg,
+    partition_fused_k<<<n_tiles, kFusedThreads, 0, st>>>(src, S8, col_stride, wide, rowidx0, rowidx1, segs, n_segs, tile_seg,
                                                         n_tiles, tile_state, ticket, epoch, counts);
     return cudaGetLastError();
 }
 
-cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, int32_t* rowidx0, int32_t* rowidx1,
+cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
                              const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                              uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st) {
     if (n_segs <= 0) return cudaSuccess;
     if (n_tiles > 0)
-        partition_count_k<<<n_tiles, kPartThreads, 0, st>>>(src, S8, col_stride, rowidx0, rowidx1, segs, tile_seg,
+        partition_count_k<<<n_tiles, kPartThreads, 0, st>>>(src, S8, col_stride, wide, rowidx0, rowidx1, segs, tile_seg,
                                                             flags, block_cnt);
     partition_scan_k<<<n_segs, 1024, 0, st>>>(segs, block_cnt, counts);
     if (n_tiles > 0)
@@ -1089,7 +1146,7 @@ __global__ void add_leaf_values_k(const int32_t* __restrict__ rowidx0, const int
 
 // Rows that were not sampled for the tree are in no leaf interval: walk the tree on their slots
 // with Tree.getNext's rule, slot <= cond goes left (J/data/gbdt/Tree.java:156-168).
-__global__ void walk_rows_k(const uint8_t* __restrict__ bins, int32_t S8, const int32_t* __restrict__ rows,
+__global__ void walk_rows_k(const uint8_t* __restrict__ bins, int32_t S8, WideCols wide, const int32_t* __restrict__ rows,
                             long long begin, long long end, const TreeNodeDev* __restrict__ nodes,
                             float* __restrict__ score, int32_t K, int32_t gid) {
     for (long long i = begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < end;
@@ -1098,7 +1155,8 @@ __global__ void walk_rows_k(const uint8_t* __restrict__ bins, int32_t S8, const 
         int pid = 0;
         TreeNodeDev nd = nodes[0];
         while (nd.left != -1) {
-            const float v = (float)bins[r * S8 + nd.fid];
+            const int wi = wide.index ? wide.index[nd.fid] : -1;
+            const float v = wi >= 0 ? (float)wide.data[wi * wide.stride + r] : (float)bins[r * S8 + nd.fid];
             pid = (v <= nd.info) ? nd.left : nd.right;
             nd = nodes[pid];
         }
@@ -1203,11 +1261,11 @@ cudaError_t launch_add_leaf_values(const int32_t* rowidx0, const int32_t* rowidx
     add_leaf_values_k<<<grid, 256, 0, st>>>(rowidx0, rowidx1, items, score, K, gid);
     return cudaGetLastError();
 }
-cudaError_t launch_walk_rows(const uint8_t* bins, int32_t S8, const int32_t* rows, long long begin, long long end,
+cudaError_t launch_walk_rows(const uint8_t* bins, int32_t S8, WideCols wide, const int32_t* rows, long long begin, long long end,
                              const TreeNodeDev* nodes, float* score, int32_t K, int32_t gid, cudaStream_t st) {
     if (end <= begin) return cudaSuccess;
     long long b = (end - begin + 255) / 256;
-    walk_rows_k<<<(unsigned)std::min<long long>(b, kNumSMs * 8), 256, 0, st>>>(bins, S8, rows, begin, end, nodes, score, K, gid);
+    walk_rows_k<<<(unsigned)std::min<long long>(b, kNumSMs * 8), 256, 0, st>>>(bins, S8, wide, rows, begin, end, nodes, score, K, gid);
     return cudaGetLastError();
 }
 int loss_grad_blocks() { return kNumSMs * 4; }

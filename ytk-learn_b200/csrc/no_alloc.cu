@@ -104,11 +104,11 @@ extern "C" int ytk_gbdt_partition_rows_static(const uint8_t* d_bins, int32_t str
     e = cudaMemsetAsync(tile_seg, 0, sizeof(int) * (size_t)(n_tiles + 1), st);
     if (e != cudaSuccess) return fail(YTK_ERR_CUDA, "partition_rows_static: memset: %s", cudaGetErrorString(e));
     ytk::SplitSeg v;
-    v.begin = 0; v.end = n_rows; v.buf = 0; v.fid = fid; v.cond = cond; v.tile0 = 0; v.ntiles = n_tiles; v.pad = 0;
+    v.begin = 0; v.end = n_rows; v.buf = 0; v.fid = fid; v.cond = cond; v.tile0 = 0; v.ntiles = n_tiles; v.wide = 0;
     static_begin_k<<<1, 1, 0, st>>>(seg, v);
     // buffer 0 is the caller's input list (only read when the segment's source is buffer 0),
     // buffer 1 its output list
-    e = ytk::launch_partition(d_bins, stride, /*row-major*/ 0, const_cast<int32_t*>(d_rows_in), d_rows_out, seg, 1, tile_seg, n_tiles,
+    e = ytk::launch_partition(d_bins, stride, /*row-major*/ 0, ytk::WideCols{nullptr, 0, nullptr}, const_cast<int32_t*>(d_rows_in), d_rows_out, seg, 1, tile_seg, n_tiles,
                               flags, block_cnt, counts, st);
     if (e != cudaSuccess) return fail(YTK_ERR_CUDA, "partition_rows_static: launch: %s", cudaGetErrorString(e));
     static_end_k<<<1, 1, 0, st>>>(counts, reinterpret_cast<long long*>(d_left_cnt));

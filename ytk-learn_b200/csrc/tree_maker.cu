@@ -319,6 +319,13 @@ struct ytk_gbdt {
     int64_t* d_off_inner = nullptr;    // offset of feature f inside its owner's segment
     int64_t* d_off_flat = nullptr;     // reference layout 2*start[f]
     uint32_t* d_group_mask = nullptr;
+    // features with more than 256 slots: uint16 columns beside the uint8 matrices
+    int n_wide = 0;
+    std::vector<int32_t> wide_index;       // per feature: its uint16 column, -1 if it has at most 256 slots
+    std::vector<int32_t> wide_sel;         // wide features selected for the current tree
+    uint16_t* d_wide = nullptr;            // [n_wide][N]
+    int32_t* d_wide_index = nullptr;       // device copy of wide_index (null when n_wide == 0)
+    int32_t* d_wide_fids = nullptr;        // device copy of wide_sel
     uint8_t* d_fea_sel = nullptr;
     long long* d_hist_flat = nullptr;  // hooks
     long long* d_hist_flat2 = nullptr;
@@ -409,7 +416,7 @@ void free_all(ytk_gbdt* h) {
     auto F = [](void* p) { if (p) cudaFree(p); };
     F(h->d_bins); F(h->d_bins_col); F(h->d_gp); F(h->d_gq); F(h->d_rowidx[0]); F(h->d_rowidx[1]); F(h->d_flags); F(h->d_block_cnt); F(h->d_tile_state); F(h->d_ticket);
     F(h->d_mask); F(h->d_start); F(h->d_nbins); F(h->d_feat_owner); F(h->d_feat_zero); F(h->d_off_inner);
-    F(h->d_off_flat); F(h->d_group_mask); F(h->d_fea_sel); F(h->d_hist_flat); F(h->d_hist_flat2);
+    F(h->d_off_flat); F(h->d_group_mask); F(h->d_wide); F(h->d_wide_index); F(h->d_wide_fids); F(h->d_fea_sel); F(h->d_hist_flat); F(h->d_hist_flat2);
     F(h->d_hist_dbl); F(h->d_scale); F(h->d_scale_hook); F(h->d_absmax); F(h->d_bad); F(h->d_node_of_row);
     F(h->d_stage); F(h->d_blob); F(h->d_blob_part); F(h->d_score); F(h->d_y); F(h->d_w); F(h->d_init); F(h->d_block_loss); F(h->d_loss);
     h->t_leafval.release(); h->t_tree.release();
@@ -429,6 +436,11 @@ void free_all(ytk_gbdt* h) {
     if (h->st) cudaStreamDestroy(h->st);
 }
 
+// the uint16 columns, seen from row `row0` on
+ytk::WideCols wide_cols(const ytk_gbdt* h, int64_t row0 = 0) {
+    return ytk::WideCols{h->d_wide ? h->d_wide + row0 : nullptr, h->N, h->d_wide_index};
+}
+
 // Selected-feature tables for one make()/hook call (initAssistData, :425-469).
 int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* first_owned, int* n_sel) {
     std::vector<uint8_t> sel(h->F, 0);
@@ -444,7 +456,13 @@ int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* firs
     }
     std::vector<uint32_t> gm(h->groups, 0);
     int cnt = 0;
-    for (int f = 0; f < h->F; f++) if (sel[f]) { gm[f / ytk::kGroup] |= 1u << (f % ytk::kGroup); cnt++; }
+    h->wide_sel.clear();
+    for (int f = 0; f < h->F; f++) {
+        if (!sel[f]) continue;
+        cnt++;
+        if (h->wide_index[f] >= 0) h->wide_sel.push_back(f);                  // hist_wide_k's share
+        else gm[f / ytk::kGroup] |= 1u << (f % ytk::kGroup);                  // hist_build_k's
+    }
     if (n_sel) *n_sel = cnt;
     *first_owned = -1;   // firstSampledFeaIndexInThread (:451-467)
     for (int f = h->f_from; f < h->f_to; f++) if (sel[f]) { *first_owned = f; break; }
@@ -455,6 +473,12 @@ int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* firs
     memcpy(s2, gm.data(), h->groups * sizeof(uint32_t));
     CK(cudaMemcpyAsync(h->d_fea_sel, s1, h->F, cudaMemcpyHostToDevice, h->st));
     CK(cudaMemcpyAsync(h->d_group_mask, s2, h->groups * sizeof(uint32_t), cudaMemcpyHostToDevice, h->st));
+    if (!h->wide_sel.empty()) {
+        void* s3 = h->arena.take(h->wide_sel.size() * sizeof(int32_t), h->st);
+        if (!s3) return fail(YTK_ERR_CUDA, "pinned staging allocation failed");
+        memcpy(s3, h->wide_sel.data(), h->wide_sel.size() * sizeof(int32_t));
+        CK(cudaMemcpyAsync(h->d_wide_fids, s3, h->wide_sel.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+    }
     return YTK_OK;
 }
 
@@ -692,6 +716,12 @@ int hist_enqueue(ytk_gbdt* h, const HistPlan& pl, ytk_time_stats* T, const ytk::
                               h->st));
     if (!pl.items.empty()) h->launches++;
     CK(cudaEventRecord(e1, h->st));
+    if (!h->wide_sel.empty() && !pl.items.empty()) {
+        CK(ytk::launch_hist_wide(wide_cols(h), h->d_wide_fids, (int)h->wide_sel.size(), h->d_gq, h->d_rowidx[0],
+                                 h->d_rowidx[1], blob_ptr<ytk::RowItem>(h, pl.o_items), (int)pl.items.size(),
+                                 h->d_feat_owner, h->d_off_inner, owner_stride, d_local, cnt_local, cnt_global, h->st));
+        h->launches++;
+    }
     if (peer) {
         // reduce-scatter over peer memory: flag "my staging buffer is complete", then every rank
         // sums the segments it owns straight out of all staging buffers into the histogram slots
@@ -852,7 +882,7 @@ int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const
             h->part_epoch = 1;
         }
         CK(h->t_counts.reserve(2 * (size_t)m));
-        CK(ytk::launch_partition_fused(src, h->S8, col_stride, h->d_rowidx[0], h->d_rowidx[1],
+        CK(ytk::launch_partition_fused(src, h->S8, col_stride, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1],
                                        pl.d_segs, m, pl.d_tiles, (int)n_tiles,
                                        h->d_tile_state, h->d_ticket, h->part_epoch, h->t_counts.d, h->st));
         h->launches++;
@@ -864,7 +894,7 @@ int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const
         CK(cudaMalloc(&h->d_block_cnt, h->block_cnt_cap * sizeof(int32_t)));
     }
     CK(h->t_counts.reserve(2 * (size_t)m));
-    CK(ytk::launch_partition(src, h->S8, col_stride, h->d_rowidx[0], h->d_rowidx[1],
+    CK(ytk::launch_partition(src, h->S8, col_stride, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1],
                              pl.d_segs, m, pl.d_tiles, (int)n_tiles,
                              h->d_flags, h->d_block_cnt, h->t_counts.d, h->st));
     h->launches += n_tiles == 0 ? 1 : 3;
@@ -1056,9 +1086,9 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
     for (int f = 0; f < F; f++) {
         h->nbins[f] = start[f + 1] - start[f];
         if (h->nbins[f] < 1) return fail(YTK_ERR_ARG, "[GBDT] fid:%d has no global feature vals!", f);
-        if (h->nbins[f] > ytk::kMaxBins)
-            return fail(YTK_ERR_UNSUPPORTED, "feature %d has %d bins; this build stores slots as uint8 (max %d)",
-                        f, h->nbins[f], ytk::kMaxBins);
+        if (h->nbins[f] > ytk::kMaxWideBins)
+            return fail(YTK_ERR_UNSUPPORTED, "feature %d has %d bins; slots are stored as uint8 or uint16 (max %d)",
+                        f, h->nbins[f], ytk::kMaxWideBins);
     }
     h->B = start[F];
     h->groups = (F + ytk::kGroup - 1) / ytk::kGroup;
@@ -1100,6 +1130,16 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
     CK(cudaMalloc(&h->d_off_inner, F * sizeof(int64_t)));
     CK(cudaMalloc(&h->d_off_flat, F * sizeof(int64_t)));
     CK(cudaMalloc(&h->d_group_mask, h->groups * sizeof(uint32_t)));
+    h->wide_index.assign(F, -1);
+    h->n_wide = 0;
+    for (int f = 0; f < F; f++) if (h->nbins[f] > ytk::kMaxBins) h->wide_index[f] = h->n_wide++;
+    if (h->n_wide > 0) {
+        CK(cudaMalloc(&h->d_wide, (size_t)h->n_wide * N1 * sizeof(uint16_t)));
+        CK(cudaMemsetAsync(h->d_wide, 0, (size_t)h->n_wide * N1 * sizeof(uint16_t), h->st));
+        CK(cudaMalloc(&h->d_wide_index, F * sizeof(int32_t)));
+        CK(cudaMemcpyAsync(h->d_wide_index, h->wide_index.data(), F * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+        CK(cudaMalloc(&h->d_wide_fids, h->n_wide * sizeof(int32_t)));
+    }
     CK(cudaMalloc(&h->d_fea_sel, F));
     CK(cudaMalloc(&h->d_hist_flat, 2LL * h->B * sizeof(long long)));
     CK(cudaMalloc(&h->d_hist_flat2, 2LL * h->B * sizeof(long long)));
@@ -1154,15 +1194,16 @@ int ytk_gbdt_upload_rows(ytk_gbdt* h, const int32_t* x_chunk, int64_t row0, int6
         size_t bytes = (size_t)n * stride * sizeof(int32_t);
         RET(ensure_stage(h, bytes));
         CK(cudaMemcpyAsync(h->d_stage, x_chunk + r * stride, bytes, cudaMemcpyHostToDevice, h->st));
-        CK(ytk::launch_repack_rows((const int32_t*)h->d_stage, n, stride, h->F, h->d_bins + (row0 + r) * h->S8,
-                                   h->S8, h->d_bins_col + (row0 + r), h->N, row0 + r, h->d_bad, h->st));
+        CK(ytk::launch_repack_rows((const int32_t*)h->d_stage, n, stride, h->F, h->d_nbins, h->d_bins + (row0 + r) * h->S8,
+                                   h->S8, h->d_bins_col + (row0 + r), h->N, wide_cols(h, row0 + r), row0 + r, h->d_bad,
+                                   h->st));
         CK(cudaStreamSynchronize(h->st));
     }
     int bad = 0;
     CK(cudaMemcpy(&bad, h->d_bad, sizeof(int), cudaMemcpyDeviceToHost));
     if (bad) {
         CK(cudaMemset(h->d_bad, 0, sizeof(int)));
-        return fail(YTK_ERR_ARG, "upload_rows: slot index outside [0,256)");
+        return fail(YTK_ERR_ARG, "upload_rows: slot index outside [0, bins of its feature)");
     }
     return YTK_OK;
 }
@@ -1186,7 +1227,7 @@ int ytk_gbdt_quantize_rows(ytk_gbdt* h, const int32_t* xbits_chunk, int64_t row0
         if (e == cudaSuccess)
             e = ytk::launch_quantize_rows((const int32_t*)h->d_stage, n, stride, h->F, d_cuts, h->d_start,
                                           h->d_bins + (row0 + r) * h->S8, h->S8, h->d_bins_col + (row0 + r), h->N,
-                                          row0 + r, h->st);
+                                          wide_cols(h, row0 + r), row0 + r, h->st);
         if (e == cudaSuccess) e = cudaStreamSynchronize(h->st);
     }
     cudaFree(d_cuts);
@@ -1203,7 +1244,8 @@ int ytk_gbdt_download_rows(ytk_gbdt* h, int32_t* out, int64_t row0, int64_t nrow
         int64_t n = std::min(step, nrows - r);
         size_t bytes = (size_t)n * h->F * sizeof(int32_t);
         RET(ensure_stage(h, bytes));
-        CK(ytk::launch_unpack_rows(h->d_bins + (row0 + r) * h->S8, h->S8, n, h->F, (int32_t*)h->d_stage, h->st));
+        CK(ytk::launch_unpack_rows(h->d_bins + (row0 + r) * h->S8, h->S8, n, h->F, wide_cols(h, row0 + r),
+                                   (int32_t*)h->d_stage, h->st));
         CK(cudaMemcpyAsync(out + r * h->F, h->d_stage, bytes, cudaMemcpyDeviceToHost, h->st));
         CK(cudaStreamSynchronize(h->st));
     }
@@ -1523,7 +1565,8 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         for (int k = 0; k < m; k++) {
             const Interval& pv = iv[jobs[k].hd];
             const NodeStats& s = ns[jobs[k].hd];         // TreeNode.setSplit: cond = 0.5f * (lo + hi) (:144-149)
-            segs[k] = {(long long)pv.b, (long long)pv.e, pv.buf, s.best_fid, 0.5f * (float)(s.best_lo + s.best_hi), 0, 0, 0};
+            segs[k] = {(long long)pv.b, (long long)pv.e, pv.buf, s.best_fid, 0.5f * (float)(s.best_lo + s.best_hi), 0, 0,
+                       h->wide_index[s.best_fid] + 1};
         }
         // With an unbounded pool and no row-count stop rule nothing the host decides next depends on
         // the child counts, so the histogram/leaf kernels are queued right behind the partition with
@@ -1842,7 +1885,7 @@ int ytk_gbdt_update_scores(ytk_gbdt* h, int32_t gid) {
         CK(h->t_tree.upload(h->last_tree, h->st, h->arena));
         // the row-mask compaction left the excluded rows behind the sampled ones in buffer 0, and
         // later partitions only ever rewrite the sampled range
-        CK(ytk::launch_walk_rows(h->d_bins, h->S8, h->d_rowidx[0], h->unsampled_begin, h->N, h->t_tree.d, h->d_score,
+        CK(ytk::launch_walk_rows(h->d_bins, h->S8, wide_cols(h), h->d_rowidx[0], h->unsampled_begin, h->N, h->t_tree.d, h->d_score,
                                  h->p.class_num, gid, h->st));
     }
     CK(cudaStreamSynchronize(h->st));
@@ -1913,6 +1956,10 @@ int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n
     CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_items.d,
                               (int)items.size(), h->F, h->d_group_mask, h->d_nbins, h->d_feat_zero, h->d_off_flat, 0,
                               h->t_seg_out.d, nullptr, nullptr, h->st));
+    if (!h->wide_sel.empty())
+        CK(ytk::launch_hist_wide(wide_cols(h), h->d_wide_fids, (int)h->wide_sel.size(), h->d_gq, h->d_rowidx[0],
+                                 h->d_rowidx[1], h->t_items.d, (int)items.size(), h->d_feat_zero, h->d_off_flat, 0,
+                                 h->t_seg_out.d, nullptr, nullptr, h->st));
     if (h->world > 1)
         NK(ytk::nccl_api().AllReduce(h->d_hist_flat, h->d_hist_flat, (size_t)len, ncclInt64, ncclSum, h->comm, h->st));
     CK(ytk::launch_hist_to_double(h->d_hist_flat, len, h->d_scale, h->d_hist_dbl, h->st));
@@ -1922,7 +1969,8 @@ int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n
 }
 
 static int hook_scale(ytk_gbdt* h, const double* a, const double* b, int64_t len) {
-    // power-of-two scales that keep every value below 2^52 so prefix sums of <= 2^10 bins stay exact
+    // power-of-two scales that keep every value below 2^52 (less for very wide features) so that the
+    // prefix sums over a feature's bins stay exact in int64
     double mg = 0, mh = 0;
     for (int64_t i = 0; i < len; i++) {
         double v = std::fabs(a[i]);
@@ -1930,7 +1978,11 @@ static int hook_scale(ytk_gbdt* h, const double* a, const double* b, int64_t len
         if (!(v < std::numeric_limits<double>::infinity())) return fail(YTK_ERR_ARG, "histogram holds a non-finite value");
         if (i & 1) mh = std::max(mh, v); else mg = std::max(mg, v);
     }
-    auto k_of = [](double m) { int e = 0; if (m > 0) std::frexp(m, &e); return 52 - e; };
+    int max_nb = 1, lg = 0;
+    for (int nb : h->nbins) max_nb = std::max(max_nb, nb);
+    while ((1 << lg) < max_nb) lg++;
+    const int top = std::min(52, 62 - lg);       // (wide features: up to 2^16 bins per prefix sum)
+    auto k_of = [top](double m) { int e = 0; if (m > 0) std::frexp(m, &e); return top - e; };
     ytk::GradScale s;
     int kg = k_of(mg), kh = k_of(mh);
     s.mul_g = std::ldexp(1.0, kg); s.inv_g = std::ldexp(1.0, -kg);
@@ -2002,7 +2054,7 @@ int ytk_gbdt_partition_rows(ytk_gbdt* h, const int32_t* rows, int64_t n_rows, in
     CK(cudaSetDevice(h->device));
     if (n_rows > 0) CK(cudaMemcpyAsync(h->d_rowidx[0], rows, n_rows * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
     std::vector<ytk::SplitSeg> sg(1);
-    sg[0] = {0, (long long)n_rows, 0, fid, cond, 0, 0, 0};
+    sg[0] = {0, (long long)n_rows, 0, fid, cond, 0, 0, h->wide_index[fid] + 1};
     std::vector<ytk::PartitionCounts> cl, cg;
     const int world = h->world;
     h->world = 1;                       // a local operation: no collective in this hook
