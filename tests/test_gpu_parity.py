@@ -479,6 +479,35 @@ def test_single_pass_partition_equals_stable_partition(kw, monkeypatch):
     assert a.last_stats.kernel_launches < b.last_stats.kernel_launches
 
 
+@pytest.mark.parametrize("kw,nb", [(dict(KW, max_depth=8), 255),
+                                   (dict(KW, max_depth=9, min_split_loss=3.0), 255),
+                                   (dict(KW, max_depth=7, max_leaf_cnt=37), 63),
+                                   (dict(KW, max_depth=6), [300, 5, 1000, 256, 257, 4000, 2, 255, 40, 700])],
+                         ids=["depth8", "min_split_loss", "leafcap37", "wide"])
+def test_device_planned_partition_equals_host_planned(kw, nb, monkeypatch):
+    """Level-wise growth on one GPU: the device plans and starts the next level's partition from the
+    split records (and the host cross-checks its decisions).  Same trees and per-row leaves as with
+    host-built partition tables (YTK_GBDT_NO_PLAN_AHEAD=1) and as the oracle."""
+    n = 120000
+    F = 28 if np.isscalar(nb) else len(nb)
+    x, start, gp = synth(n, F, nb, 79, skew=True)
+    a = maker(kw, x, start, gp)
+    ta = a.make(0)
+    pa = a.get_positions()
+    ta2 = a.make(0)                                      # and again on the same handle
+    monkeypatch.setenv("YTK_GBDT_NO_PLAN_AHEAD", "1")
+    b = maker(kw, x, start, gp)
+    tb = b.make(0)
+    for name, _ in yb.Tree.FIELDS:
+        assert np.array_equal(getattr(ta, name), getattr(tb, name), equal_nan=True), name
+        assert np.array_equal(getattr(ta, name), getattr(ta2, name), equal_nan=True), name
+    assert np.array_equal(pa, b.get_positions())
+    assert a.last_stats.kernel_launches != b.last_stats.kernel_launches      # (the planned path really ran)
+    o, opos, _ = ob.make_tree(ob.make_params(**kw), x, gp, 0, start)
+    assert_same_tree(ta, o)
+    assert np.array_equal(pa, opos)
+
+
 @pytest.mark.parametrize("bits", [16, 30])
 def test_fixed_point_width(bits, monkeypatch):
     monkeypatch.setenv("YTK_GBDT_FIXED_BITS", str(bits))

@@ -135,6 +135,17 @@ cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_s
                                    unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
                                    PartitionCounts* counts, cudaStream_t st);
 
+// The next level's partition planned on the device (level-wise growth, one GPU): slot 2k / 2k+1 =
+// left / right child of this level's job k.  jobs[k]: which of the current segments / count
+// entries the job is, the index of its children's record pair (-1: leaves), the children's buffer.
+struct SpecJob { int seg; int cseg; int scan; int child_buf; };
+cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
+                                     int32_t* rowidx1, const SplitSeg* cur_segs, const PartitionCounts* cur_counts,
+                                     const SpecJob* jobs, int m, const ytk_split* recs, double min_split_loss,
+                                     SplitSeg* out_segs, int* out_tile_seg, int* n_tiles_dev, int grid_bound,
+                                     unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
+                                     PartitionCounts* next_counts, cudaStream_t st);
+
 // K7: exact fixed-point sums of (g,h) over row runs -> out[2*seg + {0,1}] (pre-zeroed)
 cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1, const RowItem* items,
                              int n_items, long long* out, const PartitionCounts* cnt_local,

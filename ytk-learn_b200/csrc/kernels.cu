@@ -939,15 +939,22 @@ __device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned 
 __global__ void __launch_bounds__(kFusedThreads)
 partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* __restrict__ rowidx0,
                   int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs, int n_segs,
-                  const int* __restrict__ tile_seg, int n_tiles, unsigned long long* __restrict__ tile_state,
-                  unsigned int* __restrict__ ticket, unsigned long long epoch, PartitionCounts* __restrict__ counts) {
+                  const int* __restrict__ tile_seg, int n_tiles, const int* __restrict__ n_tiles_dev,
+                  unsigned long long* __restrict__ tile_state, unsigned int* __restrict__ ticket, unsigned long long epoch,
+                  PartitionCounts* __restrict__ counts) {
     __shared__ int s_tile, s_prefix, s_found;
     __shared__ int s_warp[kFusedThreads / 32], s_lb_sum[kFusedThreads / 32], s_lb_fp[kFusedThreads / 32];
     __shared__ int32_t s_rows[kFusedTile];      // the tile, left rows first, both sides in input order
-    if (threadIdx.x == 0) s_tile = (int)atomicInc(ticket, (unsigned)n_tiles - 1u);    // back to 0 after the last tile
+    // tables planned on the device (plan_next_partition_k): the grid is an upper bound, the real
+    // number of tiles is read here, and the planner has reset the ticket and the empty nodes' counts
+    if (n_tiles_dev) n_tiles = *n_tiles_dev;
+    if (threadIdx.x == 0)
+        s_tile = n_tiles_dev ? (int)atomicAdd(ticket, 1u)
+                             : (int)atomicInc(ticket, (unsigned)n_tiles - 1u);        // back to 0 after the last tile
     __syncthreads();
     const int tile = s_tile;
-    if (tile == 0)
+    if (tile >= n_tiles) return;
+    if (tile == 0 && !n_tiles_dev)
         for (int k = threadIdx.x; k < n_segs; k += kFusedThreads)
             if (segs[k].ntiles == 0) counts[k] = {0, 0};
     const int seg = tile_seg[tile];
@@ -1084,7 +1091,95 @@ cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_s
     if (n_segs <= 0) return cudaSuccess;
     if (n_tiles <= 0) return cudaMemsetAsync(counts, 0, (size_t)n_segs * sizeof(PartitionCounts), st);
     partition_fused_k<<<n_tiles, kFusedThreads, 0, st>>>(src, S8, col_stride, wide, rowidx0, rowidx1, segs, n_segs, tile_seg,
-                                                        n_tiles, tile_state, ticket, epoch, counts);
+                                                        n_tiles, nullptr, tile_state, ticket, epoch, counts);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------
+// Level-wise growth: the partition of the NEXT level, planned on the device.  What the next level
+// splits is decided by the records the split search has just written: a child of this level's job k
+// is split iff its lossChg > min_split_loss (the other stop rules are settled by the host before it
+// asks for this).  Queued right behind the split search, it lets the next partition run while the
+// host is still being woken up, reading the records and building the other tables.
+//   slot 2k / 2k+1 = left / right child of job k;  records: recs[2*scan], recs[2*scan+1] = the
+//   smaller / larger child of the job with scan index `scan` (-1: its children are leaves).
+//   Slots that are not split get counts {-1,-1}: the host checks them against its own decision.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512)
+plan_next_partition_k(const SplitSeg* __restrict__ cur_segs, const PartitionCounts* __restrict__ cur_counts,
+                      const SpecJob* __restrict__ jobs, int m, const ytk_split* recs, double min_split_loss,
+                      const int32_t* __restrict__ wide_index, SplitSeg* __restrict__ out_segs,
+                      int* __restrict__ out_tile_seg, int* __restrict__ n_tiles_out, unsigned int* __restrict__ ticket,
+                      PartitionCounts* __restrict__ next_counts) {
+    __shared__ int s_warp[16];
+    __shared__ int s_carry;
+    const int nslots = 2 * m;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { s_carry = 0; *ticket = 0; }
+    __syncthreads();
+    for (int s0 = 0; s0 < nslots; s0 += 512) {
+        const int s = s0 + threadIdx.x;
+        SplitSeg sg = {0, 0, 0, 0, 0.f, 0, 0, 0};
+        if (s < nslots) {
+            const int k = s >> 1, side = s & 1;
+            const SpecJob jb = jobs[k];
+            if (jb.scan >= 0) {
+                const SplitSeg pr = cur_segs[jb.seg];
+                const PartitionCounts c = cur_counts[jb.cseg];
+                const bool small_is_left = c.left < c.right;         // (one GPU: local counts are the global ones)
+                const bool is_small = (side == 0) == small_is_left;
+                // the host copy may be in mapped host memory; volatile: written by the kernel before this one
+                const ytk_split r = recs[2 * jb.scan + (is_small ? 0 : 1)];
+                if ((double)r.loss_chg > min_split_loss) {
+                    sg.begin = side == 0 ? pr.begin : pr.begin + c.left;
+                    sg.end = side == 0 ? pr.begin + c.left : pr.end;
+                    sg.buf = jb.child_buf;
+                    sg.fid = r.fid;
+                    sg.cond = 0.5f * (float)(r.lo + r.hi);            // TreeNode.setSplit (:144-149)
+                    sg.wide = wide_index ? wide_index[r.fid] + 1 : 0;
+                    sg.ntiles = (int)((sg.end - sg.begin + kFusedTile - 1) / kFusedTile);
+                }
+            }
+        }
+        // exclusive scan of ntiles over the slots
+        int p = sg.ntiles;
+        for (int d = 1; d < 32; d <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, p, d);
+            if (lane >= d) p += t;
+        }
+        if (lane == 31) s_warp[warp] = p;
+        __syncthreads();
+        int woff = 0, total = 0;
+        for (int w = 0; w < 16; w++) {
+            if (w < warp) woff += s_warp[w];
+            total += s_warp[w];
+        }
+        sg.tile0 = s_carry + woff + p - sg.ntiles;
+        if (s < nslots) {
+            out_segs[s] = sg;
+            if (sg.ntiles == 0) next_counts[s] = {-1, -1};
+            for (int t = 0; t < sg.ntiles; t++) out_tile_seg[sg.tile0 + t] = s;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_carry += total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *n_tiles_out = s_carry;
+}
+
+cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
+                                     int32_t* rowidx1, const SplitSeg* cur_segs, const PartitionCounts* cur_counts,
+                                     const SpecJob* jobs, int m, const ytk_split* recs, double min_split_loss,
+                                     SplitSeg* out_segs, int* out_tile_seg, int* n_tiles_dev, int grid_bound,
+                                     unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
+                                     PartitionCounts* next_counts, cudaStream_t st) {
+    if (m <= 0) return cudaSuccess;
+    plan_next_partition_k<<<1, 512, 0, st>>>(cur_segs, cur_counts, jobs, m, recs, min_split_loss, wide.index, out_segs,
+                                             out_tile_seg, n_tiles_dev, ticket, next_counts);
+    if (grid_bound > 0)
+        partition_fused_k<<<grid_bound, kFusedThreads, 0, st>>>(src, S8, col_stride, wide, rowidx0, rowidx1, out_segs, 2 * m,
+                                                                out_tile_seg, 0, n_tiles_dev, tile_state, ticket, epoch,
+                                                                next_counts);
     return cudaGetLastError();
 }
 

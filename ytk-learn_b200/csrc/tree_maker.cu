@@ -150,7 +150,8 @@ struct NodeStats {                 // TreeMakerNodeStats (DataParallelTreeMaker.
     int best_fid = -1, best_lo = -1, best_hi = -1;
 };
 
-struct ExpandNode { int hd; float loss_chg; int depth; int seq; };      // hd: node handle (make_tree)
+// hd: node handle (make_tree); slot: the node's segment in a partition the device planned ahead (-1: none)
+struct ExpandNode { int hd; float loss_chg; int depth; int seq; int slot = -1; };
 
 int java_float_compare(float a, float b) {   // java.lang.Float.compare
     if (a < b) return -1;
@@ -290,6 +291,14 @@ struct ytk_gbdt {
     size_t tile_state_cap = 0;
     unsigned int* d_ticket = nullptr;
     unsigned long long part_epoch = 0;
+    // level-wise growth on one GPU: the next level's partition planned and started by the device
+    bool plan_ahead = true;                 // YTK_GBDT_NO_PLAN_AHEAD=1 turns it off
+    DevTable<ytk::SplitSeg> t_spec_segs[2];
+    DevTable<ytk::PartitionCounts> t_spec_counts[2];
+    PinnedBuf<ytk::PartitionCounts> h_spec_counts[2];
+    DevTable<int> t_spec_tiles;
+    int* d_spec_ntiles = nullptr;
+    cudaEvent_t ev_level = nullptr;
     bool trace = false;         // YTK_GBDT_TRACE=1: per-batch host/GPU timeline on stderr
     struct TraceRec { int m; double t_pop, t_jobs, t_part, t_tables, t_queued, t_done; cudaEvent_t e0, e1; };
     std::vector<TraceRec> trace_recs;
@@ -428,6 +437,10 @@ void free_all(ytk_gbdt* h) {
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
     h->t_split_local.release(); h->t_split_all.release(); h->t_parts.release(); h->t_leaf.release(); h->t_hist_local.release();
     h->t_rs_out.release();
+    for (int i = 0; i < 2; i++) { h->t_spec_segs[i].release(); h->t_spec_counts[i].release(); h->h_spec_counts[i].release(); }
+    h->t_spec_tiles.release();
+    F(h->d_spec_ntiles);
+    if (h->ev_level) cudaEventDestroy(h->ev_level);
     h->h_counts.release(); h->h_split.release(); h->h_leaf.release(); h->h_scale.release(); h->arena.release();
     for (auto* it : h->pool.all) { F(it->buf); delete it; }
     for (auto e : h->ev) cudaEventDestroy(e);
@@ -857,6 +870,27 @@ void partition_plan(const std::vector<ytk::SplitSeg>& segs_in, PartPlan& pl, Blo
 }
 // Queues the kernels, the count allreduce and the copy of the counts to the host; does not wait.
 // Device counts: t_counts.d[0..m) local, [m..2m) global (world > 1).
+// Work space of the chained-scan partition for a launch of up to n_tiles tiles, and a fresh epoch.
+int next_partition_epoch(ytk_gbdt* h, size_t n_tiles) {
+    if (n_tiles > h->tile_state_cap) {
+        if (h->d_tile_state) CK(cudaFree(h->d_tile_state));
+        h->d_tile_state = nullptr;
+        h->tile_state_cap = std::max<size_t>(n_tiles, 2 * h->tile_state_cap);
+        CK(cudaMalloc(&h->d_tile_state, h->tile_state_cap * sizeof(unsigned long long)));
+        CK(cudaMemsetAsync(h->d_tile_state, 0, h->tile_state_cap * sizeof(unsigned long long), h->st));
+        h->part_epoch = 0;
+    }
+    if (!h->d_ticket) {        // [0]: launches with host-built tables (wraps back to 0), [1]: device-planned ones
+        CK(cudaMalloc(&h->d_ticket, 2 * sizeof(unsigned int)));
+        CK(cudaMemsetAsync(h->d_ticket, 0, 2 * sizeof(unsigned int), h->st));
+    }
+    if (++h->part_epoch >= (1ull << 30)) {       // entries of other epochs read as "not written yet"
+        CK(cudaMemsetAsync(h->d_tile_state, 0, h->tile_state_cap * sizeof(unsigned long long), h->st));
+        h->part_epoch = 1;
+    }
+    return YTK_OK;
+}
+
 // single_pass: the chained-scan kernel (right rows come out reversed; make() only); else the stable
 // three-kernel version the public entry points promise.
 int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const PartPlan& pl) {
@@ -865,22 +899,7 @@ int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const
     if (m == 0) return YTK_OK;
     const size_t n_tiles = pl.tile_seg.size();
     if (single_pass) {
-        if (n_tiles > h->tile_state_cap) {
-            if (h->d_tile_state) CK(cudaFree(h->d_tile_state));
-            h->d_tile_state = nullptr;
-            h->tile_state_cap = std::max<size_t>(n_tiles, 2 * h->tile_state_cap);
-            CK(cudaMalloc(&h->d_tile_state, h->tile_state_cap * sizeof(unsigned long long)));
-            CK(cudaMemsetAsync(h->d_tile_state, 0, h->tile_state_cap * sizeof(unsigned long long), h->st));
-            h->part_epoch = 0;
-        }
-        if (!h->d_ticket) {
-            CK(cudaMalloc(&h->d_ticket, sizeof(unsigned int)));
-            CK(cudaMemsetAsync(h->d_ticket, 0, sizeof(unsigned int), h->st));
-        }
-        if (++h->part_epoch >= (1ull << 30)) {       // entries of other epochs read as "not written yet"
-            CK(cudaMemsetAsync(h->d_tile_state, 0, h->tile_state_cap * sizeof(unsigned long long), h->st));
-            h->part_epoch = 1;
-        }
+        RET(next_partition_epoch(h, n_tiles));
         CK(h->t_counts.reserve(2 * (size_t)m));
         CK(ytk::launch_partition_fused(src, h->S8, col_stride, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1],
                                        pl.d_segs, m, pl.d_tiles, (int)n_tiles,
@@ -943,7 +962,8 @@ int partition_nodes(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const s
     return YTK_OK;
 }
 
-struct SplitJob { int hd, l, r, depth; bool terminal; };      // handles of the node and its children
+// handles of the node and its children; k: position in its batch; slot: as ExpandNode's
+struct SplitJob { int hd, l, r, depth; bool terminal; int k = 0; int slot = -1; };
 
 // What splitting a node produces, kept until the split is applied (make_tree)
 struct Expansion {
@@ -1048,6 +1068,7 @@ int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank,
     }
     if (const char* s = getenv("YTK_GBDT_SEQUENTIAL")) h->force_sequential = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_STABLE_PARTITION")) h->single_pass_partition = atoi(s) == 0;
+    if (const char* s = getenv("YTK_GBDT_NO_PLAN_AHEAD")) h->plan_ahead = atoi(s) == 0;
     if (const char* s = getenv("YTK_GBDT_TRACE")) h->trace = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_LOOKAHEAD")) h->lookahead = std::max(1, std::min(1024, atoi(s)));
     auto bail = [&](int code) { free_all(h); delete h; return code; };
@@ -1424,6 +1445,15 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf)
             || (p.min_split_samples > 0 && ns[e.hd].sample_cnt < p.min_split_samples);
     };
+    // Level-wise growth on one GPU: right behind a level's split search the device itself plans and
+    // starts the partition of the next level (plan_next_partition_k), so that it runs while the host
+    // is woken up, reads the records and builds the other tables.  The host takes the same decisions
+    // from the same records and checks them against the device's (counts of unused slots are -1).
+    const bool plan_ahead_ok = batch_levels && deferred && h->world == 1 && h->single_pass_partition && h->plan_ahead;
+    bool planned_next = false;      // the partition of the level about to be polled has been planned by the device
+    int planned_par = 0;            // which of the two planned-table sets it uses
+    int planned_slots = 0;
+
     // tree.addChilds (:256): the children of a node being split get their ids, in the order splits are applied
     auto add_children = [&](int hd, int hl, int hr) -> int {
         const int nid = nid_of[hd];
@@ -1490,8 +1520,8 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         } else {
             set_split_if_good(small);
             set_split_if_good(large);
-            queue.push_back({j.l, ns[j.l].best_lc, j.depth + 1, seq++});
-            queue.push_back({j.r, ns[j.r].best_lc, j.depth + 1, seq++});
+            queue.push_back({j.l, ns[j.l].best_lc, j.depth + 1, seq++, planned_next ? 2 * j.k : -1});
+            queue.push_back({j.r, ns[j.r].best_lc, j.depth + 1, seq++, planned_next ? 2 * j.k + 1 : -1});
         }
         x.have = false;
     };
@@ -1553,9 +1583,13 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
                 const int hl = new_handle(), hr = new_handle();
                 exps[e.hd].hl = hl; exps[e.hd].hr = hr;
                 RET(add_children(e.hd, hl, hr));
-                jobs.push_back({e.hd, hl, hr, e.depth, children_are_leaves(e.depth)});
+                jobs.push_back({e.hd, hl, hr, e.depth, children_are_leaves(e.depth), (int)jobs.size(), e.slot});
             }
         }
+        // this level's partition may already be running (planned by the device behind the previous level)
+        const bool use_planned = planned_next;
+        const int cur_par = planned_par, cur_slots = planned_slots;
+        planned_next = false;
         if (jobs.empty()) continue;
         const int m = (int)jobs.size();
 
@@ -1598,18 +1632,32 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         // everything behind it are built while it runs
         Blob bl_part, bl;
         PartPlan pp;
-        partition_plan(segs, pp, bl_part, h->single_pass_partition);
-        CK(h->t_counts.reserve(2 * (size_t)m));     // its address is handed to the kernels queued below
-        RET(partition_commit(h, bl_part, pp));
-        RET(partition_enqueue(h, h->d_bins_col, h->N, pp));
+        // where job k's segment and counts are: entry k of the tables built here, or the slot the
+        // device gave the node when it planned this partition
+        std::vector<int> cs(m);
+        for (int k = 0; k < m; k++) cs[k] = use_planned ? jobs[k].slot : k;
+        const ytk::SplitSeg* d_cur_segs;
+        const ytk::PartitionCounts *d_cl, *d_cg;
+        if (use_planned) {
+            for (int k = 0; k < m; k++)
+                if (cs[k] < 0 || cs[k] >= cur_slots) return fail(YTK_ERR_ARG, "internal: node without a planned partition slot");
+            d_cur_segs = h->t_spec_segs[cur_par].d;
+            d_cl = d_cg = h->t_spec_counts[cur_par].d;
+        } else {
+            partition_plan(segs, pp, bl_part, h->single_pass_partition);
+            CK(h->t_counts.reserve(2 * (size_t)m));     // its address is handed to the kernels queued below
+            RET(partition_commit(h, bl_part, pp));
+            RET(partition_enqueue(h, h->d_bins_col, h->N, pp));
+            d_cur_segs = pp.d_segs;
+            d_cl = h->t_counts.d;
+            d_cg = h->world > 1 ? h->t_counts.d + m : h->t_counts.d;
+        }
         tr.t_part = now_ms();
         if (!deferred) {
             CK(cudaStreamSynchronize(h->st));
             h->arena.rewind();
             finish_partition();
         }
-        const ytk::PartitionCounts* d_cl = h->t_counts.d;
-        const ytk::PartitionCounts* d_cg = h->world > 1 ? h->t_counts.d + m : h->t_counts.d;
         T->partition += now_ms() - t0;
 
         // ---- children: leaf statistics (computeLeafStats :341-385) or histograms + split search
@@ -1630,7 +1678,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
                 if (unbounded) h->pool.release(j.hd);
                 if (deferred) {
                     const int64_t n = pv.e - pv.b;
-                    add_deferred_items(leaf_items, pv, cbuf, n_leaf_jobs, k, std::max<int64_t>(4096, (n / 2 + 63) / 64), h->world);
+                    add_deferred_items(leaf_items, pv, cbuf, n_leaf_jobs, cs[k], std::max<int64_t>(4096, (n / 2 + 63) / 64), h->world);
                 } else {
                     const int small = small_of(j);
                     const int64_t n = iv[small].e - iv[small].b;
@@ -1649,7 +1697,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             long long* parent_h = h->pool.get(j.hd);
             long long *small_h, *large_h;
             RET(pool_slot(small, &small_h));
-            if (deferred) hist_jobs.push_back({small_h, k, pv, cbuf});
+            if (deferred) hist_jobs.push_back({small_h, cs[k], pv, cbuf});
             else hist_jobs.push_back({small_h, -1, iv[small], 0});
             if (parent_h) {
                 if (unbounded) {                       // sibling written over its parent
@@ -1667,8 +1715,8 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
                 T->hist_miss++;
             }
             if (deferred) {
-                scans.push_back({small_h, 0, k, 0});
-                scans.push_back({large_h, 0, k, 1});
+                scans.push_back({small_h, 0, cs[k], 0});
+                scans.push_back({large_h, 0, cs[k], 1});
             } else {
                 scans.push_back({small_h, (long long)ns[small].sample_cnt, -1, 0});
                 scans.push_back({large_h, (long long)ns[large].sample_cnt, -1, 0});
@@ -1678,6 +1726,28 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         HistPlan hp;
         RET(hist_plan(h, hist_jobs, T, n_sel, hp, bl));
         const size_t o_leaf = bl.add(leaf_items), o_subs = bl.add(subs), o_scans = bl.add(scans);
+        // Can the device plan the next level's partition?  Its candidates are the children searched in
+        // this batch; of the stop rules only "lossChg <= min_split_loss" is still open (the depth rule made
+        // the job terminal, row counts do not matter here), provided the leaf budget cannot run out
+        // while the next level is polled.
+        std::vector<ytk::SpecJob> spec_jobs;
+        long long grid_bound = 0;
+        bool plan_now = plan_ahead_ok && !scan_job.empty()
+                        && (p.max_leaf_cnt <= 0 || num_leaf + 2 * (long long)scan_job.size() <= p.max_leaf_cnt);
+        if (plan_now) {
+            spec_jobs.resize(m);
+            for (int k = 0; k < m; k++) {
+                const Interval& pv = iv[jobs[k].hd];
+                spec_jobs[k] = {cs[k], cs[k], -1, pv.buf == 0 ? 1 : 0};
+            }
+            for (size_t i = 0; i < scan_job.size(); i++) {
+                const Interval& pv = iv[jobs[scan_job[i]].hd];
+                spec_jobs[scan_job[i]].scan = (int)i;
+                grid_bound += (pv.e - pv.b + ytk::kFusedTile - 1) / ytk::kFusedTile + 1;
+            }
+            if (grid_bound > 0x3fffffff) plan_now = false;
+        }
+        const size_t o_spec = plan_now ? bl.add(spec_jobs) : 0;
         RET(blob_commit(h, bl));
         tr.t_tables = now_ms();
         if (n_leaf_jobs > 0) {
@@ -1709,13 +1779,48 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         double t1 = now_ms();
         RET(search_enqueue(h, blob_ptr<ytk::ScanNode>(h, o_scans), (int)scans.size(), first_owned, d_cg));
         if (h->trace) CK(cudaEventRecord(tr.e1, h->st));
-        tr.t_queued = now_ms();
-        CK(cudaStreamSynchronize(h->st));            // the one host wait of the batch
+        if (plan_now) {
+            // everything the host waits for is in front of this event; the next partition goes behind it
+            const int np = use_planned ? 1 - cur_par : 0;
+            CK(h->t_spec_segs[np].reserve(2 * (size_t)m));
+            CK(h->t_spec_counts[np].reserve(2 * (size_t)m));
+            CK(h->h_spec_counts[np].reserve(2 * (size_t)m));
+            CK(h->t_spec_tiles.reserve((size_t)grid_bound));
+            if (!h->d_spec_ntiles) CK(cudaMalloc(&h->d_spec_ntiles, sizeof(int)));
+            if (!h->ev_level) CK(cudaEventCreateWithFlags(&h->ev_level, cudaEventDisableTiming));
+            RET(next_partition_epoch(h, (size_t)grid_bound));
+            CK(cudaEventRecord(h->ev_level, h->st));
+            CK(ytk::launch_partition_planned(h->d_bins_col, h->S8, h->N, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1],
+                                             d_cur_segs, d_cl, blob_ptr<ytk::SpecJob>(h, o_spec), m, h->h_split.h,
+                                             p.min_split_loss, h->t_spec_segs[np].d, h->t_spec_tiles.d, h->d_spec_ntiles,
+                                             (int)grid_bound, h->d_tile_state, h->d_ticket + 1, h->part_epoch,
+                                             h->t_spec_counts[np].d, h->st));
+            CK(cudaMemcpyAsync(h->h_spec_counts[np].h, h->t_spec_counts[np].d, 2 * (size_t)m * sizeof(ytk::PartitionCounts),
+                               cudaMemcpyDeviceToHost, h->st));
+            h->launches += 2;
+            planned_next = true; planned_par = np; planned_slots = 2 * m;
+            tr.t_queued = now_ms();
+            CK(cudaEventSynchronize(h->ev_level));   // the one host wait of the batch
+        } else {
+            tr.t_queued = now_ms();
+            CK(cudaStreamSynchronize(h->st));        // the one host wait of the batch
+        }
         tr.t_done = now_ms();
         if (h->trace) h->trace_recs.push_back(tr);
         h->arena.rewind();
         search_collect(h, (int)scans.size(), recs);
-        if (deferred) partition_collect(h, m, cl, cg);
+        if (use_planned) {
+            // the device planned this partition: its decisions must be the ones taken here
+            const ytk::PartitionCounts* hc = h->h_spec_counts[cur_par].h;
+            std::vector<char> used(cur_slots, 0);
+            cl.resize(m); cg.resize(m);
+            for (int k = 0; k < m; k++) { used[cs[k]] = 1; cl[k] = cg[k] = hc[cs[k]]; }
+            for (int sl = 0; sl < cur_slots; sl++)
+                if ((hc[sl].left >= 0) != (used[sl] != 0))
+                    return fail(YTK_ERR_ARG, "internal: the device planned a different partition than the host (slot %d)", sl);
+        } else if (deferred) {
+            partition_collect(h, m, cl, cg);
+        }
         T->batches++;
         for (int k = 0; k < m; k++) {
             Expansion& x = exps[jobs[k].hd];
