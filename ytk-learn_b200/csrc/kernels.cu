@@ -14,6 +14,27 @@
 
 namespace ytk {
 
+// Programmatic dependent launch for the chain of short kernels that ends every level (zero ->
+// histogram -> subtract -> scan -> merge -> plan -> partition): a kernel launched with the attribute
+// may start being scheduled while its predecessor in the stream drains; pdl_sync() -- the first
+// statement of each of them -- lets the dependents go and then waits until the predecessor has
+// completed and its writes are visible, so the kernels see exactly the serial order.
+__device__ __forceinline__ void pdl_sync() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+static bool g_pdl = [] { const char* e = getenv("YTK_GBDT_NO_PDL"); return !(e && atoi(e) != 0); }();
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_chain(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = g_pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ------------------------------------------------------------------------------------
 // K0: int32 slot matrix (GBDTCoreData.x chunk, J/dataflow/GBDTCoreData.java:164-168)
 //     -> uint8 row-major, rows padded to a multiple of 32 features (one 32 B sector per
@@ -220,6 +241,7 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
              const int64_t* __restrict__ feat_inner, long long owner_stride,
              long long* const* __restrict__ seg_out, const PartitionCounts* __restrict__ cnt_local,
              const PartitionCounts* __restrict__ cnt_global) {
+    pdl_sync();
     // g limbs [bin][{lo,hi}][feature] (64 KB), then the h limbs in the same layout (64 KB)
     extern __shared__ __align__(128) uint32_t sh[];
     constexpr uint32_t kHOff = kMaxBins * 2 * kGroup * 4;        // bytes
@@ -353,6 +375,7 @@ hist_wide_k(WideCols wide, const int32_t* __restrict__ wide_fids, const int2* __
             const RowItem* __restrict__ items, const int32_t* __restrict__ feat_owner,
             const int64_t* __restrict__ feat_inner, long long owner_stride, long long* const* __restrict__ seg_out,
             const PartitionCounts* __restrict__ cnt_local, const PartitionCounts* __restrict__ cnt_global) {
+    pdl_sync();
     const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
     const int f = wide_fids[blockIdx.y];
     const uint16_t* __restrict__ colp = wide.data + (long long)wide.index[f] * wide.stride;
@@ -368,6 +391,7 @@ hist_wide_k(WideCols wide, const int32_t* __restrict__ wide_fids, const int2* __
 }
 
 __global__ void hist_subtract_k(const SubItem* __restrict__ items, int64_t len) {
+    pdl_sync();
     const SubItem it = items[blockIdx.y];
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
          i += (int64_t)gridDim.x * blockDim.x)
@@ -391,6 +415,7 @@ __global__ void hist_from_double_k(const double* __restrict__ in, int64_t len,
 }
 
 __global__ void zero_segments_k(long long* const* __restrict__ dst, int64_t len) {
+    pdl_sync();
     long long* d = dst[blockIdx.y];
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
          i += (int64_t)gridDim.x * blockDim.x)
@@ -455,6 +480,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
              int32_t f_from, int32_t f_to, int32_t first_fea, const GradScale* __restrict__ scale,
              GainParams gp, const PartitionCounts* __restrict__ cnt_global, SplitPart* __restrict__ parts,
              ytk_split* __restrict__ outs) {
+    pdl_sync();
     __shared__ double s_tot[2];
     __shared__ float s_lc[kScanWarps];
     __shared__ int s_fid[kScanWarps], s_lo[kScanWarps], s_hi[kScanWarps];
@@ -577,6 +603,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
 // folds the slices of every node (increasing feature ids: strict > = smallest fid wins ties)
 __global__ void split_merge_k(const SplitPart* __restrict__ parts, int n_nodes, int n_slices,
                               ytk_split* __restrict__ outs) {
+    pdl_sync();
     int node = blockIdx.x * blockDim.x + threadIdx.x;
     if (node >= n_nodes) return;
     SplitPart best = {-CUDART_INF_F, -1, -1, -1};
@@ -757,6 +784,7 @@ __global__ void leaf_sums_k(const int2* __restrict__ gq, const int32_t* __restri
                             const int32_t* __restrict__ rowidx1, const RowItem* __restrict__ items,
                             long long* __restrict__ out, const PartitionCounts* __restrict__ cnt_local,
                             const PartitionCounts* __restrict__ cnt_global) {
+    pdl_sync();
     const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
     const int32_t* __restrict__ rowidx = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
     long long g = 0, h = 0;
@@ -854,10 +882,9 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
         attr_set = true;
     }
     dim3 grid((unsigned)n_items, (unsigned)(S8 / kGroup));
-    hist_build_k<<<grid, kHistThreads, kHistSmemBytes, st>>>(bins, S8, gq, rowidx0, rowidx1, items, F, group_mask,
+    return launch_chain(hist_build_k, grid, dim3(kHistThreads), kHistSmemBytes, st, bins, S8, gq, rowidx0, rowidx1, items, F, group_mask,
                                                              nbins, feat_owner, feat_inner, owner_stride, seg_out,
                                                              cnt_local, cnt_global);
-    return cudaGetLastError();
 }
 
 cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide, const int2* gq, const int32_t* rowidx0,
@@ -866,16 +893,14 @@ cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide
                              const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st) {
     if (n_items <= 0 || n_wide <= 0) return cudaSuccess;
     dim3 grid((unsigned)n_items, (unsigned)n_wide);
-    hist_wide_k<<<grid, 256, 0, st>>>(wide, wide_fids, gq, rowidx0, rowidx1, items, feat_owner, feat_inner, owner_stride,
+    return launch_chain(hist_wide_k, grid, dim3(256), 0, st, wide, wide_fids, gq, rowidx0, rowidx1, items, feat_owner, feat_inner, owner_stride,
                                       seg_out, cnt_local, cnt_global);
-    return cudaGetLastError();
 }
 
 cudaError_t launch_hist_subtract(const SubItem* items, int n_items, int64_t len, cudaStream_t st) {
     if (n_items <= 0) return cudaSuccess;
     dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n_items);
-    hist_subtract_k<<<grid, 256, 0, st>>>(items, len);
-    return cudaGetLastError();
+    return launch_chain(hist_subtract_k, grid, dim3(256), 0, st, items, len);
 }
 cudaError_t launch_hist_to_double(const long long* hist, int64_t len, const GradScale* scale, double* out,
                                   cudaStream_t st) {
@@ -890,8 +915,7 @@ cudaError_t launch_hist_from_double(const double* in, int64_t len, const GradSca
 cudaError_t launch_zero_segments(long long* const* dst, int n, int64_t len, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
     dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n);
-    zero_segments_k<<<grid, 256, 0, st>>>(dst, len);
-    return cudaGetLastError();
+    return launch_chain(zero_segments_k, grid, dim3(256), 0, st, dst, len);
 }
 cudaError_t launch_copy_segments(const long long* src, long long* const* dst, int n, int64_t len, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
@@ -912,10 +936,11 @@ cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t*
     if (n_nodes <= 0) return cudaSuccess;
     const int slices = split_scan_slices(f_from, f_to);
     dim3 grid((unsigned)n_nodes, (unsigned)slices);
-    split_scan_k<<<grid, kScanWarps * 32, 0, st>>>(nodes, start, feat_off, fea_selected, f_from, f_to, first_fea,
-                                                   scale, gp, cnt_global, parts, out);
-    split_merge_k<<<(n_nodes + 127) / 128, 128, 0, st>>>(parts, n_nodes, slices, out);
-    return cudaGetLastError();
+    cudaError_t e = launch_chain(split_scan_k, grid, dim3(kScanWarps * 32), 0, st, nodes, start, feat_off, fea_selected, f_from,
+                                 f_to, first_fea, scale, gp, cnt_global, parts, out);
+    if (e != cudaSuccess) return e;
+    return launch_chain(split_merge_k, dim3((n_nodes + 127) / 128), dim3(128), 0, st, (const SplitPart*)parts, n_nodes, slices,
+                        out);
 }
 
 // Single-pass variant used inside make(): one kernel reads every row id once, gathers its slot,
@@ -942,6 +967,7 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
                   const int* __restrict__ tile_seg, int n_tiles, const int* __restrict__ n_tiles_dev,
                   unsigned long long* __restrict__ tile_state, unsigned int* __restrict__ ticket, unsigned long long epoch,
                   PartitionCounts* __restrict__ counts) {
+    pdl_sync();
     __shared__ int s_tile, s_prefix, s_found;
     __shared__ int s_warp[kFusedThreads / 32], s_lb_sum[kFusedThreads / 32], s_lb_fp[kFusedThreads / 32];
     __shared__ int32_t s_rows[kFusedTile];      // the tile, left rows first, both sides in input order
@@ -1090,9 +1116,8 @@ cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_s
                                    PartitionCounts* counts, cudaStream_t st) {
     if (n_segs <= 0) return cudaSuccess;
     if (n_tiles <= 0) return cudaMemsetAsync(counts, 0, (size_t)n_segs * sizeof(PartitionCounts), st);
-    partition_fused_k<<<n_tiles, kFusedThreads, 0, st>>>(src, S8, col_stride, wide, rowidx0, rowidx1, segs, n_segs, tile_seg,
-                                                        n_tiles, nullptr, tile_state, ticket, epoch, counts);
-    return cudaGetLastError();
+    return launch_chain(partition_fused_k, dim3(n_tiles), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, rowidx0,
+                        rowidx1, segs, n_segs, tile_seg, n_tiles, (const int*)nullptr, tile_state, ticket, epoch, counts);
 }
 
 // ------------------------------------------------------------------------------------
@@ -1111,6 +1136,7 @@ plan_next_partition_k(const SplitSeg* __restrict__ cur_segs, const PartitionCoun
                       const int32_t* __restrict__ wide_index, SplitSeg* __restrict__ out_segs,
                       int* __restrict__ out_tile_seg, int* __restrict__ n_tiles_out, unsigned int* __restrict__ ticket,
                       PartitionCounts* __restrict__ next_counts) {
+    pdl_sync();
     __shared__ int s_warp[16];
     __shared__ int s_carry;
     const int nslots = 2 * m;
@@ -1174,13 +1200,12 @@ cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col
                                      unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
                                      PartitionCounts* next_counts, cudaStream_t st) {
     if (m <= 0) return cudaSuccess;
-    plan_next_partition_k<<<1, 512, 0, st>>>(cur_segs, cur_counts, jobs, m, recs, min_split_loss, wide.index, out_segs,
-                                             out_tile_seg, n_tiles_dev, ticket, next_counts);
-    if (grid_bound > 0)
-        partition_fused_k<<<grid_bound, kFusedThreads, 0, st>>>(src, S8, col_stride, wide, rowidx0, rowidx1, out_segs, 2 * m,
-                                                                out_tile_seg, 0, n_tiles_dev, tile_state, ticket, epoch,
-                                                                next_counts);
-    return cudaGetLastError();
+    cudaError_t e = launch_chain(plan_next_partition_k, dim3(1), dim3(512), 0, st, cur_segs, cur_counts, jobs, m, recs,
+                                 min_split_loss, wide.index, out_segs, out_tile_seg, n_tiles_dev, ticket, next_counts);
+    if (e != cudaSuccess || grid_bound <= 0) return e;
+    return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, rowidx0,
+                        rowidx1, (const SplitSeg*)out_segs, 2 * m, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
+                        tile_state, ticket, epoch, next_counts);
 }
 
 cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
@@ -1201,8 +1226,7 @@ cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx0, const int32
                              int n_items, long long* out, const PartitionCounts* cnt_local,
                              const PartitionCounts* cnt_global, cudaStream_t st) {
     if (n_items <= 0) return cudaSuccess;
-    leaf_sums_k<<<n_items, 256, 0, st>>>(gq, rowidx0, rowidx1, items, out, cnt_local, cnt_global);
-    return cudaGetLastError();
+    return launch_chain(leaf_sums_k, dim3(n_items), dim3(256), 0, st, gq, rowidx0, rowidx1, items, out, cnt_local, cnt_global);
 }
 
 cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st) {
