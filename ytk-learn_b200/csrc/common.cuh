@@ -141,7 +141,8 @@ cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_s
 struct SpecJob { int seg; int cseg; int scan; int child_buf; };
 cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
                                      int32_t* rowidx1, const SplitSeg* cur_segs, const PartitionCounts* cur_counts,
-                                     const SpecJob* jobs, int m, const ytk_split* recs, double min_split_loss,
+                                     const PartitionCounts* cur_counts_global, const SpecJob* jobs, int m,
+                                     const ytk_split* recs, double min_split_loss,
                                      SplitSeg* out_segs, int* out_tile_seg, int* n_tiles_dev, int grid_bound,
                                      unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
                                      PartitionCounts* next_counts, cudaStream_t st);
@@ -171,6 +172,10 @@ cudaError_t launch_peer_allreduce(const PeerTable& pt, const void* src, size_t a
 cudaError_t launch_peer_allgather(const PeerTable& pt, const void* src, size_t area_off, size_t slot_bytes, size_t bytes,
                                   int flag_set, unsigned long long epoch, int* err, cudaStream_t st);
 // raises this rank's "staging complete" flag, waits for everybody's, sums the owned segments out of all staging buffers
+// all-gather + the needReplace / MAX merge of the split records: merged record k -> out_dev[k], out_host[k]
+cudaError_t launch_peer_allgather_merge(const PeerTable& pt, const ytk_split* src, size_t area_off, size_t slot_bytes, int m,
+                                        int flag_set, unsigned long long epoch, ytk_split* out_dev, ytk_split* out_host,
+                                        int* err, cudaStream_t st);
 cudaError_t launch_peer_pull_reduce(const PeerTable& pt, int m, long long seg_max, int flag_set, unsigned long long epoch,
                                     long long* const* dst, int* err, cudaStream_t st);
 

@@ -1132,7 +1132,7 @@ cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_s
 // ------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(512)
 plan_next_partition_k(const SplitSeg* __restrict__ cur_segs, const PartitionCounts* __restrict__ cur_counts,
-                      const SpecJob* __restrict__ jobs, int m, const ytk_split* recs, double min_split_loss,
+                      const PartitionCounts* __restrict__ cur_counts_global, const SpecJob* __restrict__ jobs, int m, const ytk_split* recs, double min_split_loss,
                       const int32_t* __restrict__ wide_index, SplitSeg* __restrict__ out_segs,
                       int* __restrict__ out_tile_seg, int* __restrict__ n_tiles_out, unsigned int* __restrict__ ticket,
                       PartitionCounts* __restrict__ next_counts) {
@@ -1152,7 +1152,8 @@ plan_next_partition_k(const SplitSeg* __restrict__ cur_segs, const PartitionCoun
             if (jb.scan >= 0) {
                 const SplitSeg pr = cur_segs[jb.seg];
                 const PartitionCounts c = cur_counts[jb.cseg];
-                const bool small_is_left = c.left < c.right;         // (one GPU: local counts are the global ones)
+                const PartitionCounts cgl = cur_counts_global[jb.cseg];
+                const bool small_is_left = cgl.left < cgl.right;     // by global rows (:344-350)
                 const bool is_small = (side == 0) == small_is_left;
                 // the host copy may be in mapped host memory; volatile: written by the kernel before this one
                 const ytk_split r = recs[2 * jb.scan + (is_small ? 0 : 1)];
@@ -1195,12 +1196,13 @@ plan_next_partition_k(const SplitSeg* __restrict__ cur_segs, const PartitionCoun
 
 cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
                                      int32_t* rowidx1, const SplitSeg* cur_segs, const PartitionCounts* cur_counts,
-                                     const SpecJob* jobs, int m, const ytk_split* recs, double min_split_loss,
+                                     const PartitionCounts* cur_counts_global, const SpecJob* jobs, int m,
+                                     const ytk_split* recs, double min_split_loss,
                                      SplitSeg* out_segs, int* out_tile_seg, int* n_tiles_dev, int grid_bound,
                                      unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
                                      PartitionCounts* next_counts, cudaStream_t st) {
     if (m <= 0) return cudaSuccess;
-    cudaError_t e = launch_chain(plan_next_partition_k, dim3(1), dim3(512), 0, st, cur_segs, cur_counts, jobs, m, recs,
+    cudaError_t e = launch_chain(plan_next_partition_k, dim3(1), dim3(512), 0, st, cur_segs, cur_counts, cur_counts_global, jobs, m, recs,
                                  min_split_loss, wide.index, out_segs, out_tile_seg, n_tiles_dev, ticket, next_counts);
     if (e != cudaSuccess || grid_bound <= 0) return e;
     return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, rowidx0,
@@ -1478,6 +1480,38 @@ __global__ void peer_allgather_k(PeerTable pt, const unsigned long long* __restr
     peer_wait(pt, flag_set, epoch, err);
 }
 
+// The same all-gather for the split records, followed by the merge every rank would otherwise do on
+// its host (ytk_gbdt_merge_splits: needReplace in rank order, element-wise MAX of the node totals,
+// DataParallelTreeMaker.java:560,640-653): merged record k -> out_dev[k] and out_host[k] (pinned).
+__global__ void peer_allgather_merge_k(PeerTable pt, const ytk_split* __restrict__ src, size_t area_off, size_t slot_bytes,
+                                       int m, int flag_set, unsigned long long epoch, ytk_split* __restrict__ out_dev,
+                                       ytk_split* __restrict__ out_host, int* err) {
+    peer_push(pt, reinterpret_cast<const unsigned long long*>(src), area_off, slot_bytes, (size_t)m * sizeof(ytk_split),
+              flag_set, epoch);
+    if (!peer_wait(pt, flag_set, epoch, err)) return;
+    const char* base = pt.xchg[pt.rank] + area_off;
+    for (int k = threadIdx.x; k < m; k += blockDim.x) {
+        const ytk_split first = reinterpret_cast<const ytk_split*>(base)[k];
+        ytk_split best = first;
+        double G = first.sum_grad, H = first.sum_hess;
+        for (int r = 1; r < pt.world; r++) {
+            const ytk_split t2 = reinterpret_cast<const ytk_split*>(base + (size_t)r * slot_bytes)[k];
+            const bool rep = (best.fid <= t2.fid) ? (t2.loss_chg > best.loss_chg) : (t2.loss_chg >= best.loss_chg);
+            if (rep) best = t2;
+            if (t2.sum_grad > G) G = t2.sum_grad;
+            if (t2.sum_hess > H) H = t2.sum_hess;
+        }
+        // root_gain / node_value are functions of (G,H): from the first rank that had the totals
+        for (int r = 0; r < pt.world; r++) {
+            const ytk_split t2 = reinterpret_cast<const ytk_split*>(base + (size_t)r * slot_bytes)[k];
+            if (t2.sum_grad == G && t2.sum_hess == H) { best.root_gain = t2.root_gain; best.node_value = t2.node_value; break; }
+        }
+        best.sum_grad = G; best.sum_hess = H;
+        out_dev[k] = best;
+        out_host[k] = best;
+    }
+}
+
 // Reduce-scatter by pulling: this rank owns segment [rank] of every node; staging layout of every
 // rank is [owner][node][seg_max].  grid = (chunks, nodes); block 0 of each launch waits for the flags
 // ... every block waits (cheap: the flags are already up for all but the first to arrive).
@@ -1516,6 +1550,12 @@ cudaError_t launch_peer_allgather(const PeerTable& pt, const void* src, size_t a
                                   int flag_set, unsigned long long epoch, int* err, cudaStream_t st) {
     peer_allgather_k<<<1, 256, 0, st>>>(pt, static_cast<const unsigned long long*>(src), area_off, slot_bytes, bytes, flag_set,
                                         epoch, err);
+    return cudaGetLastError();
+}
+cudaError_t launch_peer_allgather_merge(const PeerTable& pt, const ytk_split* src, size_t area_off, size_t slot_bytes, int m,
+                                        int flag_set, unsigned long long epoch, ytk_split* out_dev, ytk_split* out_host,
+                                        int* err, cudaStream_t st) {
+    peer_allgather_merge_k<<<1, 256, 0, st>>>(pt, src, area_off, slot_bytes, m, flag_set, epoch, out_dev, out_host, err);
     return cudaGetLastError();
 }
 cudaError_t launch_peer_pull_reduce(const PeerTable& pt, int m, long long seg_max, int flag_set, unsigned long long epoch,

@@ -293,6 +293,7 @@ struct ytk_gbdt {
     unsigned long long part_epoch = 0;
     // level-wise growth on one GPU: the next level's partition planned and started by the device
     bool plan_ahead = true;                 // YTK_GBDT_NO_PLAN_AHEAD=1 turns it off
+    bool recs_merged = false;               // the last split exchange merged the records on the device
     DevTable<ytk::SplitSeg> t_spec_segs[2];
     DevTable<ytk::PartitionCounts> t_spec_counts[2];
     PinnedBuf<ytk::PartitionCounts> h_spec_counts[2];
@@ -783,14 +784,15 @@ int search_enqueue(ytk_gbdt* h, const ytk::ScanNode* d_nodes, int m, int first_o
         // needReplace rule -- replaces allreduceRpc(SplitInfo) and allreduceArrayRpc(MAX)
         CK(h->t_split_all.reserve((size_t)m * h->world));
         RET(comm_mark(h));
+        h->recs_merged = false;
         if (h->peer_mode && (size_t)m * sizeof(ytk_split) <= h->slot_recs) {
+            // gathered and merged on the device; the merged records land in pinned host memory
             const unsigned long long ep = ++h->epoch[2];
-            CK(ytk::launch_peer_allgather(h->pt, h->t_split_local.d, h->off_recs, h->slot_recs, (size_t)m * sizeof(ytk_split), 2,
-                                          ep, h->d_peer_err, h->st));
+            CK(ytk::launch_peer_allgather_merge(h->pt, h->t_split_local.d, h->off_recs, h->slot_recs, m, 2, ep,
+                                                h->t_split_all.d, h->h_split.h, h->d_peer_err, h->st));
             h->launches++;
+            h->recs_merged = true;
             RET(comm_mark(h));
-            CK(cudaMemcpy2DAsync(h->h_split.h, (size_t)m * sizeof(ytk_split), h->my_xchg + h->off_recs, h->slot_recs,
-                                 (size_t)m * sizeof(ytk_split), h->world, cudaMemcpyDeviceToHost, h->st));
         } else {
             NK(ytk::nccl_api().AllGather(h->t_split_local.d, h->t_split_all.d, m * sizeof(ytk_split), ncclChar, h->comm,
                                          h->st));
@@ -803,7 +805,7 @@ int search_enqueue(ytk_gbdt* h, const ytk::ScanNode* d_nodes, int m, int first_o
 }
 void search_collect(ytk_gbdt* h, int m, std::vector<ytk_split>& recs) {
     recs.resize(m);
-    if (h->world == 1) {
+    if (h->world == 1 || h->recs_merged) {
         for (int k = 0; k < m; k++) recs[k] = h->h_split.h[k];
     } else {
         std::vector<ytk_split> tmp(h->world);
@@ -1449,7 +1451,8 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     // starts the partition of the next level (plan_next_partition_k), so that it runs while the host
     // is woken up, reads the records and builds the other tables.  The host takes the same decisions
     // from the same records and checks them against the device's (counts of unused slots are -1).
-    const bool plan_ahead_ok = batch_levels && deferred && h->world == 1 && h->single_pass_partition && h->plan_ahead;
+    const bool plan_ahead_ok = batch_levels && deferred && (h->world == 1 || h->peer_mode) && h->single_pass_partition
+                               && h->plan_ahead;
     bool planned_next = false;      // the partition of the level about to be polled has been planned by the device
     int planned_par = 0;            // which of the two planned-table sets it uses
     int planned_slots = 0;
@@ -1642,7 +1645,8 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             for (int k = 0; k < m; k++)
                 if (cs[k] < 0 || cs[k] >= cur_slots) return fail(YTK_ERR_ARG, "internal: node without a planned partition slot");
             d_cur_segs = h->t_spec_segs[cur_par].d;
-            d_cl = d_cg = h->t_spec_counts[cur_par].d;
+            d_cl = h->t_spec_counts[cur_par].d;                               // [0,slots) local, [slots,2 slots) global
+            d_cg = h->world > 1 ? d_cl + cur_slots : d_cl;
         } else {
             partition_plan(segs, pp, bl_part, h->single_pass_partition);
             CK(h->t_counts.reserve(2 * (size_t)m));     // its address is handed to the kernels queued below
@@ -1733,7 +1737,8 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         std::vector<ytk::SpecJob> spec_jobs;
         long long grid_bound = 0;
         bool plan_now = plan_ahead_ok && !scan_job.empty()
-                        && (p.max_leaf_cnt <= 0 || num_leaf + 2 * (long long)scan_job.size() <= p.max_leaf_cnt);
+                        && (p.max_leaf_cnt <= 0 || num_leaf + 2 * (long long)scan_job.size() <= p.max_leaf_cnt)
+                        && (h->world == 1 || (2 * m <= h->peer_cap_nodes && (size_t)scans.size() * sizeof(ytk_split) <= h->slot_recs));
         if (plan_now) {
             spec_jobs.resize(m);
             for (int k = 0; k < m; k++) {
@@ -1783,19 +1788,28 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             // everything the host waits for is in front of this event; the next partition goes behind it
             const int np = use_planned ? 1 - cur_par : 0;
             CK(h->t_spec_segs[np].reserve(2 * (size_t)m));
-            CK(h->t_spec_counts[np].reserve(2 * (size_t)m));
-            CK(h->h_spec_counts[np].reserve(2 * (size_t)m));
+            const int nsl = 2 * m, ncnt = h->world > 1 ? 2 * nsl : nsl;
+            CK(h->t_spec_counts[np].reserve((size_t)ncnt));
+            CK(h->h_spec_counts[np].reserve((size_t)ncnt));
             CK(h->t_spec_tiles.reserve((size_t)grid_bound));
             if (!h->d_spec_ntiles) CK(cudaMalloc(&h->d_spec_ntiles, sizeof(int)));
             if (!h->ev_level) CK(cudaEventCreateWithFlags(&h->ev_level, cudaEventDisableTiming));
             RET(next_partition_epoch(h, (size_t)grid_bound));
             CK(cudaEventRecord(h->ev_level, h->st));
             CK(ytk::launch_partition_planned(h->d_bins_col, h->S8, h->N, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1],
-                                             d_cur_segs, d_cl, blob_ptr<ytk::SpecJob>(h, o_spec), m, h->h_split.h,
-                                             p.min_split_loss, h->t_spec_segs[np].d, h->t_spec_tiles.d, h->d_spec_ntiles,
+                                             d_cur_segs, d_cl, d_cg, blob_ptr<ytk::SpecJob>(h, o_spec), m,
+                                             h->world > 1 ? h->t_split_all.d : h->h_split.h, p.min_split_loss, h->t_spec_segs[np].d, h->t_spec_tiles.d, h->d_spec_ntiles,
                                              (int)grid_bound, h->d_tile_state, h->d_ticket + 1, h->part_epoch,
                                              h->t_spec_counts[np].d, h->st));
-            CK(cudaMemcpyAsync(h->h_spec_counts[np].h, h->t_spec_counts[np].d, 2 * (size_t)m * sizeof(ytk::PartitionCounts),
+            if (h->world > 1) {   // allreduceArray(long[2], SUM) (:538) of the planned partition's counts
+                RET(comm_mark(h));
+                const unsigned long long ep = ++h->epoch[0];
+                CK(ytk::launch_peer_allreduce(h->pt, h->t_spec_counts[np].d, h->off_counts, h->slot_counts, 2 * (size_t)nsl, 0, ep,
+                                              reinterpret_cast<long long*>(h->t_spec_counts[np].d + nsl), h->d_peer_err, h->st));
+                h->launches++;
+                RET(comm_mark(h));
+            }
+            CK(cudaMemcpyAsync(h->h_spec_counts[np].h, h->t_spec_counts[np].d, (size_t)ncnt * sizeof(ytk::PartitionCounts),
                                cudaMemcpyDeviceToHost, h->st));
             h->launches += 2;
             planned_next = true; planned_par = np; planned_slots = 2 * m;
@@ -1814,7 +1828,11 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             const ytk::PartitionCounts* hc = h->h_spec_counts[cur_par].h;
             std::vector<char> used(cur_slots, 0);
             cl.resize(m); cg.resize(m);
-            for (int k = 0; k < m; k++) { used[cs[k]] = 1; cl[k] = cg[k] = hc[cs[k]]; }
+            for (int k = 0; k < m; k++) {
+                used[cs[k]] = 1;
+                cl[k] = hc[cs[k]];
+                cg[k] = hc[h->world > 1 ? cur_slots + cs[k] : cs[k]];
+            }
             for (int sl = 0; sl < cur_slots; sl++)
                 if ((hc[sl].left >= 0) != (used[sl] != 0))
                     return fail(YTK_ERR_ARG, "internal: the device planned a different partition than the host (slot %d)", sl);
