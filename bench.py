@@ -85,21 +85,29 @@ def sigmoid_grads(score, y, out):
 
 
 class ClockSampler:
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+    """nvidia-smi clocks and throttle reasons while the steps run.  The process is started (and NVML
+    initialised -- which can stall CUDA calls of other processes for tens of ms) well before the
+    timed region; only samples taken after mark() are used."""
+    Q = ("timestamp,index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu):
         self.proc = None
-        self.lines = []
+        self.t_mark = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "250"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None
 
+    def mark(self):
+        import datetime
+        self.t_mark = datetime.datetime.now()
+
     def stop(self):
+        import datetime
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -112,13 +120,16 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in out.strip().splitlines():
             c = [t.strip() for t in line.split(",")]
-            if len(c) < 9:
+            if len(c) < 10:
                 continue
             try:
-                sm.append(float(c[1])); mx.append(float(c[2]))
+                ts = datetime.datetime.strptime(c[0], "%Y/%m/%d %H:%M:%S.%f")
+                if self.t_mark is not None and ts < self.t_mark:
+                    continue
+                sm.append(float(c[2])); mx.append(float(c[3]))
             except ValueError:
                 continue
-            for nme, v in zip(names, c[5:9]):
+            for nme, v in zip(names, c[6:10]):
                 if v.lower().startswith("active"):
                     reasons.add(nme)
         if not sm:
@@ -254,12 +265,12 @@ def main():
     h2d = gp.nbytes
     agg = dict(t_tree=0.0, t_e2e=0.0, cells=0.0, rows=0.0, rows_idx=0.0, built=0, gpu_hist_ms=0.0, launches=0,
                d2h=0, nodes=0, ts_build=0.0, ts_split=0.0, ts_part=0.0, ts_total=0.0, hist_launches=0, ts_comm=0.0)
-    sampler = None
+    sampler = ClockSampler(local)                         # started now, used from the first timed step on
     for step in range(a.warmup + a.steps):
         sigmoid_grads(score, ys, gp)                      # the Java side's job, outside the hot path
         timed = step >= a.warmup
-        if timed and sampler is None:
-            sampler = ClockSampler(local)
+        if timed and sampler.t_mark is None:
+            sampler.mark()
         barrier()
         t0 = time.perf_counter()
         tm.set_grads_ptr(gp_pinned.data_ptr(), 0, n)      # H2D from pinned memory
@@ -277,11 +288,14 @@ def main():
             agg["built"] += ts.hist_built; agg["gpu_hist_ms"] += ts.gpu_hist_ms
             agg["launches"] += ts.kernel_launches; agg["nodes"] = tree.n_nodes
             agg["hist_launches"] += ts.hist_launches
+            agg["allocs"] = agg.get("allocs", 0) + ts.device_allocs
+            agg["max_batch"] = max(agg.get("max_batch", 0.0), ts.max_batch_ms)
+            agg["slow_steps"] = agg.get("slow_steps", []) + [round((t2 - t1) * 1e3, 2)]
             agg["ts_build"] += ts.build_hist; agg["ts_split"] += ts.find_best_split
             agg["ts_part"] += ts.partition; agg["ts_total"] += ts.total; agg["ts_comm"] += ts.communicate_hist
             agg["d2h"] = sum(getattr(tree, nme).nbytes for nme, _ in yb.Tree.FIELDS)
     barrier()
-    clocks = sampler.stop() if sampler else None
+    clocks = sampler.stop()
 
     # SURVEY.md §8(f) row 1, for information: whole boosting rounds with the gradients computed on the
     # device (score update + loss/gradients + make), nothing but the tree crossing PCIe
@@ -351,7 +365,9 @@ def main():
             "time_stats_ms_per_tree": {"build_hist": agg["ts_build"] / a.steps, "find_best_split": agg["ts_split"] / a.steps,
                                        "partition": agg["ts_part"] / a.steps, "total": agg["ts_total"] / a.steps,
                                        "collectives_gpu": agg["ts_comm"] / a.steps,
-                                       "host_waits": host_waits},
+                                       "host_waits": host_waits, "device_allocs_in_timed_steps": agg.get("allocs", 0),
+                                       "longest_batch_ms": agg.get("max_batch", 0.0),
+                                       "ms_of_each_step": agg.get("slow_steps", [])},
             "roofline": {"bound": "hbm", "kernel": "hist_build_k", "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg / max(1, agg["hist_launches"]),

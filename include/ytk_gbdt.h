@@ -89,6 +89,8 @@ typedef struct {
     int32_t hist_launches;    /* ... of which histogram-build launches (one per batch) */
     int32_t peer_collectives; /* 1: per-level collectives ran over NVLink peer memory, 0: NCCL / one GPU */
     int32_t batches;          /* batches of launches = host waits after the root (a level, a node, or a look-ahead set) */
+    int32_t device_allocs;    /* cudaMalloc calls made by this call (histogram slots, grown tables): 0 once warmed up */
+    double  max_batch_ms;     /* longest single batch, enqueue to host wake-up (a stall shows up here) */
 } ytk_time_stats;
 
 /* One best split: SplitInfo (J/data/gbdt/SplitInfo.java:36-70) plus the node totals the

@@ -80,7 +80,7 @@ struct Blob {
 // Slots keep their device buffers when recycled, exactly like the Java arrays, so the
 // (degenerate) case of a parent evicted by its own child's allocation behaves as there.
 struct HistPool {
-    struct Item { int nid; long long* buf; };
+    struct Item { int nid; long long* buf; bool own_buf = true; };     // own_buf: buf is its own cudaMalloc
     int capacity = 0;
     std::vector<Item*> used;     // allocation order, oldest first
     std::deque<Item*> avail;     // FIFO
@@ -388,6 +388,7 @@ struct ytk_gbdt {
     DevTable<ytk::TreeNodeDev> t_tree;
 
     HistPool pool;
+    long long* d_pool_chunk = nullptr;      // the histogram slots allocated up front (one allocation)
     bool grads_set = false, rows_set = false;
     std::vector<std::pair<int, Interval>> leaf_ranges;   // (leaf node id, a run of its rows) of the last tree
     bool tree_made = false;
@@ -443,7 +444,8 @@ void free_all(ytk_gbdt* h) {
     F(h->d_spec_ntiles);
     if (h->ev_level) cudaEventDestroy(h->ev_level);
     h->h_counts.release(); h->h_split.release(); h->h_leaf.release(); h->h_scale.release(); h->arena.release();
-    for (auto* it : h->pool.all) { F(it->buf); delete it; }
+    for (auto* it : h->pool.all) { if (it->own_buf) F(it->buf); delete it; }
+    F(h->d_pool_chunk);
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto e : h->evc) cudaEventDestroy(e);
     if (h->comm) ytk::nccl_api().CommDestroy(h->comm);
@@ -1192,6 +1194,21 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
     }
     if (capacity < 1) return fail(YTK_ERR_ARG, "histogram pool capacity %d < 1 (max_leaf_cnt %d)", capacity, h->p.max_leaf_cnt);
     h->pool.capacity = capacity;
+    {   // Histogram slots up front, in one allocation: a cudaMalloc in the middle of a tree costs a
+        // device-wide synchronisation (measured ~0.35 ms each).  A level holds parents and children at
+        // once and expansions computed ahead of time add a few more, hence twice the capacity; anything
+        // beyond that (or beyond 1 GiB here) is still allocated on demand.
+        const size_t slot_bytes = (size_t)h->seg_max * sizeof(long long);
+        size_t n_pre = 2 * (size_t)capacity + 2;
+        n_pre = std::min(n_pre, std::max<size_t>(2, (size_t(1) << 30) / slot_bytes));
+        if (h->p.histogram_pool_capacity > 0) n_pre = (size_t)capacity;      // a bounded pool never holds more
+        CK(cudaMalloc(&h->d_pool_chunk, n_pre * slot_bytes));
+        for (size_t i = 0; i < n_pre; i++) {
+            HistPool::Item* it = new HistPool::Item{-1, h->d_pool_chunk + i * (size_t)h->seg_max, false};
+            h->pool.all.push_back(it);
+            h->pool.avail.push_back(it);
+        }
+    }
     if (h->world > 1) RET(peer_setup(h));
     h->rows_set = true;
     return YTK_OK;
@@ -1381,7 +1398,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     auto pool_slot = [&](int key, long long** buf) -> int {      // pool entries are keyed by handle
         bool fresh = false;
         HistPool::Item* it = h->pool.alloc(key, &fresh, unbounded);
-        if (fresh) CK(cudaMalloc(&it->buf, h->seg_max * sizeof(long long)));
+        if (fresh) { CK(cudaMalloc(&it->buf, h->seg_max * sizeof(long long))); T->device_allocs++; }
         *buf = it->buf;
         return YTK_OK;
     };
@@ -1820,6 +1837,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             CK(cudaStreamSynchronize(h->st));        // the one host wait of the batch
         }
         tr.t_done = now_ms();
+        T->max_batch_ms = std::max(T->max_batch_ms, tr.t_done - tr.t_pop);
         if (h->trace) h->trace_recs.push_back(tr);
         h->arena.rewind();
         search_collect(h, (int)scans.size(), recs);
