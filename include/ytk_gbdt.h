@@ -220,6 +220,19 @@ int ytk_gbdt_compute_grads(ytk_gbdt *h, double *loss_sum);
 int ytk_gbdt_get_scores(ytk_gbdt *h, float *out);
 int ytk_gbdt_get_grads(ytk_gbdt *h, float *out);
 
+/* ---- test-set scoring -----------------------------------------------------
+ * GBDTOptimizer.score with isOriginTree = true (J/optimizer/GBDTOptimizer.java:630-650) through
+ * Tree.getLeafIndex / getNext (J/data/gbdt/Tree.java:142-168): rows hold ORIGINAL feature values as
+ * float bits (GBDTCoreData.x before binning, int32 row-major with `stride` per row); value <=
+ * threshold goes left; a value equal to Constants.INT_MISSING_VALUE (the raw bits of Float.NaN,
+ * 0x7fc00000) takes default_child[node] (null: the left child).  `tree` is what make_tree returned;
+ * threshold[node] is the real-valued split of inner nodes after
+ * Tree.convertFeatureSplitValueInModel (:293-309).  score[row*class_num + gid] += leaf value (float),
+ * in place on the host array.  Stateless: any rows, not the training shard. */
+int ytk_gbdt_score_values(ytk_gbdt *h, const int32_t *xbits, int64_t nrows, int32_t stride,
+                          const ytk_tree_out *tree, const float *threshold, const int32_t *default_child,
+                          int32_t class_num, int32_t gid, float *score);
+
 /* No counterpart in the reference: an addition for hosts that must not allocate device memory
  * (all of it belongs to their own pool, or the hidden device-wide synchronisation of
  * cudaMalloc/cudaFree is not acceptable where they call from).  Same operation and same kernels

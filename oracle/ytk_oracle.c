@@ -657,6 +657,27 @@ void orc_score_values(const orc_tree *t, const float *thr, const float *xv, int6
     }
 }
 
+/* The same walk on the int32 view of the values (GBDTCoreData.x): a value equal to
+ * Constants.INT_MISSING_VALUE = floatToRawIntBits(Float.NaN) = 0x7fc00000 takes the node's default
+ * child (Tree.getLeafIndex :147-148, getNext :156-160; TreeNode.getDefualtChild). */
+void orc_score_value_bits(const orc_tree *t, const float *thr, const int32_t *def_child, const int32_t *xbits,
+                          int64_t n, int32_t S, float *score, int32_t K, int32_t gid) {
+    for (int64_t r = 0; r < n; r++) {
+        int32_t pid = 0;
+        while (t->left[pid] != -1) {
+            int32_t bits = xbits[r * S + t->fid[pid]];
+            if (bits == 0x7fc00000) {
+                pid = def_child ? def_child[pid] : t->left[pid];
+            } else {
+                float v;
+                memcpy(&v, &bits, 4);
+                pid = (v <= thr[pid]) ? t->left[pid] : t->right[pid];
+            }
+        }
+        score[r * K + gid] += t->node_info[pid];
+    }
+}
+
 double orc_loss_grad_scalar(int32_t loss_kind, const float *score, const float *init_score,
                             const float *y, const float *w, int64_t n, float *gp) {
     double loss = 0.0;

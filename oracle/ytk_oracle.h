@@ -129,6 +129,11 @@ void orc_score_slots(const orc_tree *t, const int32_t *x, int64_t n, int32_t S,
 void orc_score_values(const orc_tree *t, const float *thr, const float *xv, int64_t n,
                       int32_t S, float *score, int32_t K, int32_t gid);
 
+/* ... and on the int32 view of the values, with Constants.INT_MISSING_VALUE (0x7fc00000) taking
+ * def_child[nid] (null: the left child) -- J/data/gbdt/Tree.java:142-168. */
+void orc_score_value_bits(const orc_tree *t, const float *thr, const int32_t *def_child, const int32_t *xbits,
+                          int64_t n, int32_t S, float *score, int32_t K, int32_t gid);
+
 /* GBDTOptimizer.predictAndCalcLossGrad, numTreeInGroup==1 branch (:536-557) with
  * SigmoidFunction (J/loss/SigmoidFunction.java:39-93, zMax==0) or L2Function
  * (J/loss/L2Function.java:30-55).  loss_kind 0 = sigmoid, 1 = l2.

@@ -263,6 +263,18 @@ def score_values(tree, thr, xv, score, K=1, gid=0):
                            C.c_int32(xv.shape[1]), _p(score), C.c_int32(K), C.c_int32(gid))
 
 
+def score_value_bits(tree, thr, def_child, xbits, score, K=1, gid=0):
+    xbits = np.ascontiguousarray(xbits, dtype=np.int32)
+    thr = np.ascontiguousarray(thr, dtype=np.float32)
+    dc = None if def_child is None else np.ascontiguousarray(def_child, dtype=np.int32)
+    t = _tree_to_orc(tree)
+    ot = t.as_orc()
+    f = lib().orc_score_value_bits
+    f.restype = None
+    f(C.byref(ot), _p(thr), _p(dc) if dc is not None else None, _p(xbits), C.c_int64(xbits.shape[0]),
+      C.c_int32(xbits.shape[1]), _p(score), C.c_int32(K), C.c_int32(gid))
+
+
 def loss_grad_scalar(kind, score, init_score, y, w, want_grad=True):
     n = len(y)
     gp = np.zeros(2 * n, dtype=np.float32) if want_grad else None

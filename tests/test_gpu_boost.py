@@ -112,3 +112,37 @@ def test_kat1_agaricus_with_device_gradients():
         losses[it] = tm.compute_grads() / wsum
     for it, (tr, _) in kat.KAT1.items():
         assert abs(losses[it] - tr) < 1e-9, (it, losses[it], tr)
+
+
+# ---------------------------------------------------------------- §8(f) row 3: test-set scoring
+def test_score_values_matches_oracle_with_missing_values():
+    """GBDTOptimizer.score on original values (isOriginTree=true): value <= threshold goes left, the
+    canonical NaN bit pattern (Constants.INT_MISSING_VALUE) takes the default child."""
+    rng = np.random.default_rng(3)
+    n, F, nb, K = 30000, 12, 64, 3
+    x, start, gp = synth(n, F, nb, 17, K=K)
+    tm = maker(dict(KW, max_depth=6), x, start, gp, K=K)
+    cuts = np.sort(rng.normal(size=(F, nb)).astype(np.float32), axis=1)
+    nt, S = 70001, F + 3                                     # not the training shard; padded rows
+    vals = rng.normal(size=(nt, S)).astype(np.float32)
+    bits = vals.view(np.int32)
+    bits[rng.random((nt, S)) < 0.08] = 0x7FC00000            # missing
+    got = rng.normal(size=nt * K).astype(np.float32)
+    want = got.copy()
+    for gid in range(K):
+        t = tm.make(gid)
+        inner = t.left != -1
+        thr = np.zeros(t.n_nodes, np.float32)                # FeatureSplitType MEAN: 0.5f * (c[lo] + c[hi])
+        thr[inner] = np.float32(0.5) * (cuts[t.fid[inner], t.lo[inner]] + cuts[t.fid[inner], t.hi[inner]])
+        dc = np.where(rng.random(t.n_nodes) < 0.5, t.left, t.right).astype(np.int32)
+        tm.score_values(t, thr, vals, got, default_child=dc, gid=gid)
+        ob.score_value_bits(t, thr, dc, bits, want, K=K, gid=gid)
+    assert np.array_equal(got, want)
+    # without a default direction missing values go left; and the plain-value oracle agrees where nothing is missing
+    full = rng.normal(size=(5000, S)).astype(np.float32)
+    g2 = np.zeros(5000 * K, np.float32); w2 = np.zeros(5000 * K, np.float32)
+    tm.score_values(t, thr, full, g2, gid=K - 1)
+    ob.score_values(t, thr, full, w2, K=K, gid=K - 1)
+    assert np.array_equal(g2, w2)
+    with pytest.raises(yb.YtkError):                          # a default child that is not a child
+        tm.score_values(t, thr, full, g2, default_child=np.full(t.n_nodes, t.n_nodes + 5, np.int32))

@@ -38,3 +38,45 @@ def test_kat2_dermatology_prediction():
     # every matching row carries the README's label (fourth class)
     assert all(int(d["yt"][r]) == 3 for r in hits)
     assert [[t.n_nodes for t in g] for g in trees][0] == [7, 17, 5, 21, 3, 3]
+
+
+def test_value_walk_with_missing_values_default_child():
+    """orc_score_value_bits (Tree.getLeafIndex/getNext, J/data/gbdt/Tree.java:142-168) against a direct
+    numpy restatement, and against the plain value walk where nothing is missing."""
+    import oracle_binding as ob
+    rng = np.random.default_rng(1)
+
+    class T:
+        pass
+    t = T()
+    t.n_nodes = 7
+    t.parent = np.array([-1, 0, 0, 1, 1, 2, 2], np.int32)
+    t.left = np.array([1, 3, 5, -1, -1, -1, -1], np.int32)
+    t.right = np.array([2, 4, 6, -1, -1, -1, -1], np.int32)
+    t.fid = np.array([2, 0, 1, 0, 0, 0, 0], np.int32)
+    t.lo = np.zeros(7, np.int32); t.hi = np.zeros(7, np.int32)
+    t.node_info = np.array([0, 0, 0, 1.5, -2.25, 0.125, 7.0], np.float32)
+    t.loss_chg = np.zeros(7, np.float32); t.hess_sum = np.zeros(7, np.float32); t.sample_cnt = np.zeros(7, np.int64)
+    thr = np.array([0.1, -0.3, 0.7, 0, 0, 0, 0], np.float32)
+    dc = np.array([2, 3, 6, 0, 0, 0, 0], np.int32)
+    v = rng.normal(size=(400, 3)).astype(np.float32)
+    bits = v.view(np.int32).copy()
+    bits[rng.random(bits.shape) < 0.2] = 0x7FC00000
+    vv = bits.view(np.float32)
+    want = np.zeros(400, np.float32)
+    for r in range(400):
+        pid = 0
+        while t.left[pid] != -1:
+            b = bits[r, t.fid[pid]]
+            if b == 0x7FC00000:
+                pid = dc[pid]
+            else:
+                pid = t.left[pid] if vv[r, t.fid[pid]] <= thr[pid] else t.right[pid]
+        want[r] = t.node_info[pid]
+    got = np.zeros(400, np.float32)
+    ob.score_value_bits(t, thr, dc, bits, got)
+    assert np.array_equal(got, want)
+    a = np.zeros(400, np.float32); b2 = np.zeros(400, np.float32)
+    ob.score_value_bits(t, thr, None, v.view(np.int32), a)
+    ob.score_values(t, thr, v, b2)
+    assert np.array_equal(a, b2)

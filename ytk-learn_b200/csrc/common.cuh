@@ -184,6 +184,9 @@ cudaError_t launch_add_leaf_values(const int32_t* rowidx0, const int32_t* rowidx
                                    float* score, int32_t K, int32_t gid, cudaStream_t st);
 cudaError_t launch_walk_rows(const uint8_t* bins, int32_t S8, WideCols wide, const int32_t* rows, long long begin, long long end,
                              const TreeNodeDev* nodes, float* score, int32_t K, int32_t gid, cudaStream_t st);
+// test rows: original values (float bits), real-valued thresholds in nodes[].info of inner nodes, leaf values in leaves
+cudaError_t launch_score_values(const int32_t* xbits, long long n, int32_t stride, const TreeNodeDev* nodes,
+                                const int32_t* default_child, float* score, int32_t K, int32_t gid, cudaStream_t st);
 int loss_grad_blocks();
 // loss_kind 0 sigmoid, 1 l2, 2 softmax (y one-hot [n][K]); block_loss: loss_grad_blocks() doubles of scratch
 cudaError_t launch_loss_grad(int loss_kind, const float* score, const float* init, const float* y, const float* w,

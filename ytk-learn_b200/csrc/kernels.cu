@@ -1285,6 +1285,25 @@ __global__ void walk_rows_k(const uint8_t* __restrict__ bins, int32_t S8, WideCo
     }
 }
 
+// Test-set scoring on ORIGINAL feature values (GBDTOptimizer.score :630-650 with isOriginTree = true;
+// Tree.getLeafIndex / getNext, J/data/gbdt/Tree.java:142-168): value <= threshold goes left, a value
+// whose bits are Float.NaN's raw pattern (Constants.INT_MISSING_VALUE) takes the node's default child.
+__global__ void score_values_k(const int32_t* __restrict__ xbits, long long n, int32_t stride,
+                               const TreeNodeDev* __restrict__ nodes, const int32_t* __restrict__ default_child,
+                               float* __restrict__ score, int32_t K, int32_t gid) {
+    for (long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x; r < n; r += (long long)gridDim.x * blockDim.x) {
+        int pid = 0;
+        TreeNodeDev nd = nodes[0];
+        while (nd.left != -1) {
+            const int32_t bits = xbits[r * stride + nd.fid];
+            if (bits == 0x7fc00000) pid = default_child ? default_child[pid] : nd.left;
+            else pid = (__int_as_float(bits) <= nd.info) ? nd.left : nd.right;
+            nd = nodes[pid];
+        }
+        score[r * K + gid] += nd.info;
+    }
+}
+
 __device__ __forceinline__ double block_sum(double v, double* s_part) {
     for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
     if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = v;
@@ -1387,6 +1406,14 @@ cudaError_t launch_walk_rows(const uint8_t* bins, int32_t S8, WideCols wide, con
     if (end <= begin) return cudaSuccess;
     long long b = (end - begin + 255) / 256;
     walk_rows_k<<<(unsigned)std::min<long long>(b, kNumSMs * 8), 256, 0, st>>>(bins, S8, wide, rows, begin, end, nodes, score, K, gid);
+    return cudaGetLastError();
+}
+cudaError_t launch_score_values(const int32_t* xbits, long long n, int32_t stride, const TreeNodeDev* nodes,
+                                const int32_t* default_child, float* score, int32_t K, int32_t gid, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    long long b = (n + 255) / 256;
+    score_values_k<<<(unsigned)std::min<long long>(b, kNumSMs * 16), 256, 0, st>>>(xbits, n, stride, nodes, default_child, score,
+                                                                                 K, gid);
     return cudaGetLastError();
 }
 int loss_grad_blocks() { return kNumSMs * 4; }

@@ -2034,6 +2034,55 @@ int ytk_gbdt_update_scores(ytk_gbdt* h, int32_t gid) {
     return YTK_OK;
 }
 
+int ytk_gbdt_score_values(ytk_gbdt* h, const int32_t* xbits, int64_t nrows, int32_t stride, const ytk_tree_out* tree,
+                          const float* threshold, const int32_t* default_child, int32_t class_num, int32_t gid,
+                          float* score) {
+    if (!h || !tree || !threshold || !score) return fail(YTK_ERR_ARG, "score_values: null argument");
+    if (nrows < 0 || (nrows > 0 && !xbits)) return fail(YTK_ERR_ARG, "score_values: bad row buffer");
+    if (class_num < 1 || gid < 0 || gid >= class_num) return fail(YTK_ERR_ARG, "score_values: groupId %d not in [0,%d)", gid, class_num);
+    const int nn = tree->n_nodes;
+    if (nn < 1) return fail(YTK_ERR_ARG, "score_values: empty tree");
+    std::vector<ytk::TreeNodeDev> nodes(nn);
+    for (int i = 0; i < nn; i++) {
+        const bool leaf = tree->left[i] == -1;
+        if (!leaf) {
+            if (tree->left[i] < 0 || tree->left[i] >= nn || tree->right[i] < 0 || tree->right[i] >= nn)
+                return fail(YTK_ERR_ARG, "score_values: node %d has children outside the tree", i);
+            if (tree->fid[i] < 0 || tree->fid[i] >= stride)
+                return fail(YTK_ERR_ARG, "score_values: node %d splits feature %d, rows have %d", i, tree->fid[i], stride);
+            if (default_child && default_child[i] != tree->left[i] && default_child[i] != tree->right[i])
+                return fail(YTK_ERR_ARG, "score_values: default child of node %d is neither of its children", i);
+        }
+        nodes[i] = {tree->left[i], tree->right[i], tree->fid[i], leaf ? tree->node_info[i] : threshold[i]};
+    }
+    if (nrows == 0) return YTK_OK;
+    CK(cudaSetDevice(h->device));
+    CK(h->t_tree.upload(nodes, h->st, h->arena));
+    int32_t* d_def = nullptr;
+    float* d_sc = nullptr;
+    auto done = [&](int rc) { if (d_def) cudaFree(d_def); if (d_sc) cudaFree(d_sc); h->arena.rewind(); return rc; };
+    if (default_child) {
+        if (cudaMalloc(&d_def, nn * sizeof(int32_t)) != cudaSuccess) return done(fail(YTK_ERR_CUDA, "score_values: out of device memory"));
+        if (cudaMemcpyAsync(d_def, default_child, nn * sizeof(int32_t), cudaMemcpyHostToDevice, h->st) != cudaSuccess)
+            return done(fail(YTK_ERR_CUDA, "score_values: copy failed"));
+    }
+    // rows go through the staging buffer in chunks, their scores beside them
+    const int64_t step = std::max<int64_t>(1, (64LL << 20) / ((int64_t)stride * 4));
+    if (cudaMalloc(&d_sc, (size_t)std::min(step, nrows) * class_num * sizeof(float)) != cudaSuccess)
+        return done(fail(YTK_ERR_CUDA, "score_values: out of device memory"));
+    for (int64_t r = 0; r < nrows; r += step) {
+        const int64_t n = std::min(step, nrows - r);
+        if (ensure_stage(h, (size_t)n * stride * sizeof(int32_t)) != YTK_OK) return done(YTK_ERR_CUDA);
+        cudaError_t e = cudaMemcpyAsync(h->d_stage, xbits + r * stride, (size_t)n * stride * sizeof(int32_t), cudaMemcpyHostToDevice, h->st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_sc, score + r * class_num, (size_t)n * class_num * sizeof(float), cudaMemcpyHostToDevice, h->st);
+        if (e == cudaSuccess) e = ytk::launch_score_values((const int32_t*)h->d_stage, n, stride, h->t_tree.d, d_def, d_sc, class_num, gid, h->st);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(score + r * class_num, d_sc, (size_t)n * class_num * sizeof(float), cudaMemcpyDeviceToHost, h->st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->st);
+        if (e != cudaSuccess) return done(fail(YTK_ERR_CUDA, "score_values: %s", cudaGetErrorString(e)));
+    }
+    return done(YTK_OK);
+}
+
 int ytk_gbdt_compute_grads(ytk_gbdt* h, double* loss_sum) {
     if (!h) return fail(YTK_ERR_ARG, "compute_grads: null argument");
     if (h->loss_kind < 0) return fail(YTK_ERR_ARG, "compute_grads: call set_targets first");

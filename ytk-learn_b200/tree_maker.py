@@ -146,6 +146,22 @@ class GpuTreeMaker:
         B.check(B.lib().ytk_gbdt_get_grads(self._h, B.ptr(out)))
         return out
 
+    def score_values(self, tree, threshold, values, score, default_child=None, gid=0):
+        """Test-set scoring (GBDTOptimizer.score, isOriginTree=true): `values` float32 [n, S] (NaN with the
+        canonical bit pattern = missing), `threshold` per node, `score` float32 [n*K] updated in place."""
+        v = np.ascontiguousarray(values, dtype=np.float32)
+        thr = np.ascontiguousarray(threshold, dtype=np.float32)
+        dc = None if default_child is None else np.ascontiguousarray(default_child, dtype=np.int32)
+        t = B.Tree(tree.n_nodes)
+        for name, _ in B.Tree.FIELDS:
+            getattr(t, name)[:] = getattr(tree, name)[: tree.n_nodes]
+        ct = t._as_c()
+        ct.n_nodes = tree.n_nodes
+        assert score.dtype == np.float32 and score.flags.c_contiguous
+        B.check(B.lib().ytk_gbdt_score_values(self._h, B.ptr(v.view(np.int32)), v.shape[0], v.shape[1], C.addressof(ct),
+                                              B.ptr(thr), B.ptr(dc), self.K, int(gid), B.ptr(score)))
+        return score
+
     # ---- per-stage hooks ---------------------------------------------------------------
     def build_hist(self, group_id=0, rows=None, fea_index=None):
         out = np.zeros(2 * self.B, dtype=np.float64)
