@@ -94,3 +94,31 @@ def test_config5_shape_multiclass_63_bins_depth10_reduced_rows():
         o, opos, _ = ob.make_tree(p, x, gp, gid, start)
         assert_same_tree(t, o)
         assert np.array_equal(tm.get_positions(), opos)
+
+
+def test_config4_sparse_shape_reduced_rows_through_the_dense_path():
+    """configs[3]: 10 000 features at ~1 % density (absent -> the default bin 0, present -> 1..b_f-1 with
+    b_f in [2,255]), binary labels, level-wise depth 6.  There is no sparse (CSR) layout in the
+    reference's GBDTCoreData and none here yet; the shape runs through the dense path -- 313 feature
+    groups, 1.3 M bins per node -- at a row count the oracle can check."""
+    rng = np.random.default_rng(7)
+    n, F = 12000, 10000
+    nbs = rng.integers(2, 256, size=F)
+    start = np.concatenate([[0], np.cumsum(nbs)]).astype(np.int32)
+    x = np.zeros((n, F), dtype=np.int32)
+    nnz = rng.random((n, F)) < 0.01
+    r, f = np.nonzero(nnz)
+    x[r, f] = 1 + (rng.random(len(r)) * (nbs[f] - 1)).astype(np.int64)
+    w = rng.normal(size=F) * (rng.random(F) < 0.02)
+    y = (rng.random(n) < 1.0 / (1.0 + np.exp(-(nnz * w).sum(axis=1) * 3))).astype(np.float64)
+    gp = np.empty((n, 2), np.float32)
+    gp[:, 0] = (0.5 - y).astype(np.float32)
+    gp[:, 1] = 0.25
+    gp = gp.reshape(-1)
+    kw = dict(max_depth=6, max_leaf_cnt=-1, grow_policy="level", min_child_hessian_sum=1.0, l2=1.0, learning_rate=0.1)
+    tm = maker(kw, x, start, gp)
+    t = tm.make(0)
+    o, opos, _ = ob.make_tree(ob.make_params(**kw), x, gp, 0, start)
+    assert_same_tree(t, o)
+    assert np.array_equal(tm.get_positions(), opos)
+    assert t.n_nodes > 15
