@@ -14,7 +14,8 @@ pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("gpu_required")]
 KW = dict(max_depth=6, max_leaf_cnt=-1, grow_policy="level", min_child_hessian_sum=1.0,
           min_split_loss=0.0, l1=0.0, l2=1.0, learning_rate=0.1)
 CASES = {"level": KW, "loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=24),
-         "few_features": dict(KW, max_depth=4), "wide_features": dict(KW, max_depth=5)}
+         "few_features": dict(KW, max_depth=4), "wide_features": dict(KW, max_depth=5),
+         "sorted_shards": dict(KW, max_depth=7), "sorted_shards_loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=40)}
 
 
 def _data(case):
@@ -23,6 +24,10 @@ def _data(case):
         return synth(20000, 3, [17, 255, 4], 5)
     if case == "wide_features":                     # features with more than 256 bins (uint16 slots)
         return synth(40000, 7, [300, 5, 1000, 256, 257, 4000, 40], 13, skew=True)
+    if case.startswith("sorted_shards"):            # rows sorted by a feature: whole nodes live on one GPU only
+        x, start, gp = synth(40000, 12, 64, 23)
+        order = np.lexsort((x[:, 3], x[:, 0]))
+        return np.ascontiguousarray(x[order]), start, np.ascontiguousarray(gp.reshape(-1, 2)[order]).reshape(-1)
     return synth(60000, 28, 255, 91, skew=True)
 
 

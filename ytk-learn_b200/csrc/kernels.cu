@@ -1146,6 +1146,7 @@ plan_next_partition_k(const SplitSeg* __restrict__ cur_segs, const PartitionCoun
     for (int s0 = 0; s0 < nslots; s0 += 512) {
         const int s = s0 + threadIdx.x;
         SplitSeg sg = {0, 0, 0, 0, 0.f, 0, 0, 0};
+        bool split = false;
         if (s < nslots) {
             const int k = s >> 1, side = s & 1;
             const SpecJob jb = jobs[k];
@@ -1158,6 +1159,7 @@ plan_next_partition_k(const SplitSeg* __restrict__ cur_segs, const PartitionCoun
                 // the host copy may be in mapped host memory; volatile: written by the kernel before this one
                 const ytk_split r = recs[2 * jb.scan + (is_small ? 0 : 1)];
                 if ((double)r.loss_chg > min_split_loss) {
+                    split = true;
                     sg.begin = side == 0 ? pr.begin : pr.begin + c.left;
                     sg.end = side == 0 ? pr.begin + c.left : pr.end;
                     sg.buf = jb.child_buf;
@@ -1184,7 +1186,9 @@ plan_next_partition_k(const SplitSeg* __restrict__ cur_segs, const PartitionCoun
         sg.tile0 = s_carry + woff + p - sg.ntiles;
         if (s < nslots) {
             out_segs[s] = sg;
-            if (sg.ntiles == 0) next_counts[s] = {-1, -1};
+            // not split: marked; split but without rows on this GPU: counted here, no tile will
+            if (!split) next_counts[s] = {-1, -1};
+            else if (sg.ntiles == 0) next_counts[s] = {0, 0};
             for (int t = 0; t < sg.ntiles; t++) out_tile_seg[sg.tile0 + t] = s;
         }
         __syncthreads();
