@@ -147,6 +147,13 @@ cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col
                                      unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
                                      PartitionCounts* next_counts, cudaStream_t st);
 
+// ... and the root's own partition, planned from its record (one slot)
+cudaError_t launch_partition_planned_root(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
+                                          int32_t* rowidx1, long long begin, long long end, int buf, const ytk_split* rec,
+                                          double min_split_loss, SplitSeg* out_segs, int* out_tile_seg, int* n_tiles_dev,
+                                          int grid_bound, unsigned long long* tile_state, unsigned int* ticket,
+                                          unsigned long long epoch, PartitionCounts* next_counts, cudaStream_t st);
+
 // K7: exact fixed-point sums of (g,h) over row runs -> out[2*seg + {0,1}] (pre-zeroed)
 cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1, const RowItem* items,
                              int n_items, long long* out, const PartitionCounts* cnt_local,

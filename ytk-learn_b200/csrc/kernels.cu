@@ -1198,6 +1198,41 @@ plan_next_partition_k(const SplitSeg* __restrict__ cur_segs, const PartitionCoun
     if (threadIdx.x == 0) *n_tiles_out = s_carry;
 }
 
+// The root's partition, planned from the root's own record: one slot.
+__global__ void __launch_bounds__(256)
+plan_root_partition_k(long long begin, long long end, int buf, const ytk_split* rec, double min_split_loss,
+                      const int32_t* __restrict__ wide_index, SplitSeg* __restrict__ out_segs,
+                      int* __restrict__ out_tile_seg, int* __restrict__ n_tiles_out, unsigned int* __restrict__ ticket,
+                      PartitionCounts* __restrict__ next_counts) {
+    pdl_sync();
+    const ytk_split r = rec[0];
+    const bool split = (double)r.loss_chg > min_split_loss;
+    const int ntiles = split ? (int)((end - begin + kFusedTile - 1) / kFusedTile) : 0;
+    if (threadIdx.x == 0) {
+        SplitSeg sg = {0, 0, 0, 0, 0.f, 0, 0, 0};
+        if (split) sg = {begin, end, buf, r.fid, 0.5f * (float)(r.lo + r.hi), 0, ntiles, wide_index ? wide_index[r.fid] + 1 : 0};
+        out_segs[0] = sg;
+        if (!split) next_counts[0] = {-1, -1};
+        else if (ntiles == 0) next_counts[0] = {0, 0};
+        *n_tiles_out = ntiles;
+        *ticket = 0;
+    }
+    for (int t = threadIdx.x; t < ntiles; t += blockDim.x) out_tile_seg[t] = 0;
+}
+
+cudaError_t launch_partition_planned_root(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
+                                          int32_t* rowidx1, long long begin, long long end, int buf, const ytk_split* rec,
+                                          double min_split_loss, SplitSeg* out_segs, int* out_tile_seg, int* n_tiles_dev,
+                                          int grid_bound, unsigned long long* tile_state, unsigned int* ticket,
+                                          unsigned long long epoch, PartitionCounts* next_counts, cudaStream_t st) {
+    cudaError_t e = launch_chain(plan_root_partition_k, dim3(1), dim3(256), 0, st, begin, end, buf, rec, min_split_loss,
+                                 wide.index, out_segs, out_tile_seg, n_tiles_dev, ticket, next_counts);
+    if (e != cudaSuccess || grid_bound <= 0) return e;
+    return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, rowidx0,
+                        rowidx1, (const SplitSeg*)out_segs, 1, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
+                        tile_state, ticket, epoch, next_counts);
+}
+
 cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
                                      int32_t* rowidx1, const SplitSeg* cur_segs, const PartitionCounts* cur_counts,
                                      const PartitionCounts* cur_counts_global, const SpecJob* jobs, int m,

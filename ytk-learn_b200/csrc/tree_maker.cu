@@ -817,21 +817,6 @@ void search_collect(ytk_gbdt* h, int m, std::vector<ytk_split>& recs) {
         }
     }
 }
-int search_nodes(ytk_gbdt* h, const std::vector<ytk::ScanNode>& nodes, int first_owned, std::vector<ytk_split>& recs,
-                 const ytk::PartitionCounts* cnt_global = nullptr) {
-    const int m = (int)nodes.size();
-    recs.resize(m);
-    if (m == 0) return YTK_OK;
-    Blob bl;
-    const size_t o = bl.add(nodes);
-    RET(blob_commit(h, bl));
-    RET(search_enqueue(h, blob_ptr<ytk::ScanNode>(h, o), m, first_owned, cnt_global));
-    CK(cudaStreamSynchronize(h->st));
-    h->arena.rewind();
-    search_collect(h, m, recs);
-    return YTK_OK;
-}
-
 void apply_record(NodeStats& s, const ytk_split& r) {
     s.sumG = r.sum_grad; s.sumH = r.sum_hess;
     s.root_gain = r.root_gain; s.node_value = r.node_value;
@@ -1423,14 +1408,64 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     }
 
     std::vector<ytk_split> recs;
+    // Level-wise growth: right behind a level's split search the device itself plans and
+    // starts the partition of the next level (plan_next_partition_k), so that it runs while the host
+    // is woken up, reads the records and builds the other tables.  The host takes the same decisions
+    // from the same records and checks them against the device's (counts of unused slots are -1).
+    const bool plan_ahead_ok = batch_levels && deferred && (h->world == 1 || h->peer_mode) && h->single_pass_partition
+                               && h->plan_ahead;
+    bool planned_next = false;      // the partition of the level about to be polled has been planned by the device
+    int planned_par = 0;            // which of the two planned-table sets it uses
+    int planned_slots = 0;
+
     // ---- findBestSplit(root) (:302-318)
     {
         double t0 = now_ms();
-        long long* slot;
+        long long* slot = nullptr;
         RET(pool_slot(root_id, &slot));
         RET(build_hists(h, {{slot, -1, root, 0}}, T, n_sel, nullptr, nullptr));
         double t1 = now_ms();
-        RET(search_nodes(h, {{slot, (long long)ns[root_id].sample_cnt, -1, 0}}, first_owned, recs));
+        Blob bl;
+        const size_t o_scan = bl.add(std::vector<ytk::ScanNode>{{slot, (long long)ns[root_id].sample_cnt, -1, 0}});
+        RET(blob_commit(h, bl));
+        RET(search_enqueue(h, blob_ptr<ytk::ScanNode>(h, o_scan), 1, first_owned, nullptr));
+        // the root's own partition, planned by the device from its record (as for the levels below)
+        const bool plan_root = plan_ahead_ok && p.max_depth != 0 && (p.max_leaf_cnt <= 0 || p.max_leaf_cnt > 1)
+                               && (h->world == 1 || (h->recs_merged && 1 <= h->peer_cap_nodes));
+        if (plan_root) {
+            const long long grid_bound = (root.e - root.b + ytk::kFusedTile - 1) / ytk::kFusedTile;
+            const int ncnt = h->world > 1 ? 2 : 1;
+            CK(h->t_spec_segs[0].reserve(1));
+            CK(h->t_spec_counts[0].reserve((size_t)ncnt));
+            CK(h->h_spec_counts[0].reserve((size_t)ncnt));
+            CK(h->t_spec_tiles.reserve((size_t)std::max<long long>(1, grid_bound)));
+            if (!h->d_spec_ntiles) CK(cudaMalloc(&h->d_spec_ntiles, sizeof(int)));
+            if (!h->ev_level) CK(cudaEventCreateWithFlags(&h->ev_level, cudaEventDisableTiming));
+            RET(next_partition_epoch(h, (size_t)std::max<long long>(1, grid_bound)));
+            CK(cudaEventRecord(h->ev_level, h->st));
+            CK(ytk::launch_partition_planned_root(h->d_bins_col, h->S8, h->N, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1],
+                                                  root.b, root.e, root.buf, h->world > 1 ? h->t_split_all.d : h->h_split.h,
+                                                  p.min_split_loss, h->t_spec_segs[0].d, h->t_spec_tiles.d,
+                                                  h->d_spec_ntiles, (int)grid_bound, h->d_tile_state, h->d_ticket + 1,
+                                                  h->part_epoch, h->t_spec_counts[0].d, h->st));
+            if (h->world > 1) {
+                RET(comm_mark(h));
+                const unsigned long long ep = ++h->epoch[0];
+                CK(ytk::launch_peer_allreduce(h->pt, h->t_spec_counts[0].d, h->off_counts, h->slot_counts, 2, 0, ep,
+                                              reinterpret_cast<long long*>(h->t_spec_counts[0].d + 1), h->d_peer_err, h->st));
+                h->launches++;
+                RET(comm_mark(h));
+            }
+            CK(cudaMemcpyAsync(h->h_spec_counts[0].h, h->t_spec_counts[0].d, (size_t)ncnt * sizeof(ytk::PartitionCounts),
+                               cudaMemcpyDeviceToHost, h->st));
+            h->launches += 2;
+            planned_next = true; planned_par = 0; planned_slots = 1;
+            CK(cudaEventSynchronize(h->ev_level));
+        } else {
+            CK(cudaStreamSynchronize(h->st));
+        }
+        h->arena.rewind();
+        search_collect(h, 1, recs);
         apply_record(ns[root_id], recs[0]);
         set_split_if_good(root_id);
         T->build_hist += t1 - t0;
@@ -1439,7 +1474,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
 
     std::vector<ExpandNode> queue;
     int seq = 0;
-    queue.push_back({root_id, ns[root_id].best_lc, 0, seq++});
+    queue.push_back({root_id, ns[root_id].best_lc, 0, seq++, planned_next ? 0 : -1});
     int num_leaf = 1;
 
     // PriorityQueue order with lossChgComparator / sequenceComparator (:105-115): true if a is polled before b
@@ -1464,16 +1499,6 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             || (p.max_leaf_cnt > 0 && p.max_leaf_cnt == num_leaf)
             || (p.min_split_samples > 0 && ns[e.hd].sample_cnt < p.min_split_samples);
     };
-    // Level-wise growth on one GPU: right behind a level's split search the device itself plans and
-    // starts the partition of the next level (plan_next_partition_k), so that it runs while the host
-    // is woken up, reads the records and builds the other tables.  The host takes the same decisions
-    // from the same records and checks them against the device's (counts of unused slots are -1).
-    const bool plan_ahead_ok = batch_levels && deferred && (h->world == 1 || h->peer_mode) && h->single_pass_partition
-                               && h->plan_ahead;
-    bool planned_next = false;      // the partition of the level about to be polled has been planned by the device
-    int planned_par = 0;            // which of the two planned-table sets it uses
-    int planned_slots = 0;
-
     // tree.addChilds (:256): the children of a node being split get their ids, in the order splits are applied
     auto add_children = [&](int hd, int hl, int hr) -> int {
         const int nid = nid_of[hd];
