@@ -135,6 +135,22 @@ int ytk_gbdt_destroy(ytk_gbdt *h);
  * GBDTDataFlow.handleOtherTrainInfo (J/dataflow/GBDTDataFlow.java:252-263). */
 int ytk_gbdt_set_bins(ytk_gbdt *h, const int32_t *start, int32_t F, int64_t n_rows);
 
+/* Sparse rows instead of the dense matrix (BASELINE config 4: 10 000 features at ~1 % density; the
+ * reference's GBDTCoreData is dense, J/dataflow/GBDTCoreData.java:164-168, and cannot hold that shape --
+ * this is the layout a sparse-aware trainer would hand over).  default_slot[f] is the slot of a
+ * feature that a row does not store: the bin of the value missing entries are filled with
+ * (FillMissingValue, J/feature/gbdt/missing/).  nnz = stored entries of this shard (capacity).  At
+ * most 65536 features.  Everything downstream (make_tree, hooks, scores) is the same; results are
+ * those of the dense path on the densified rows. */
+int ytk_gbdt_set_bins_sparse(ytk_gbdt *h, const int32_t *start, int32_t F, int64_t n_rows,
+                             const int32_t *default_slot, int64_t nnz);
+
+/* CSR chunk: rows [row0, row0+nrows), chunks in row order.  Row r holds entries
+ * [row_ptr[r], row_ptr[r+1]) of fids/slots (row_ptr has nrows+1 entries and may start at any
+ * offset), sorted by feature, slot = the entry's bin (may equal the default slot). */
+int ytk_gbdt_upload_csr(ytk_gbdt *h, const int64_t *row_ptr, const int32_t *fids, const int32_t *slots,
+                        int64_t row0, int64_t nrows);
+
 /* One chunk of GBDTCoreData.x after binning (J/dataflow/GBDTCoreData.java:164-168,
  * FeatureApprData.java:202): int32 slot indices, row-major with stride S = maxFeatureDim.
  * The device keeps them as uint8, row-major, padded to 32 features (uint16 columns for the

@@ -15,6 +15,7 @@ KW = dict(max_depth=6, max_leaf_cnt=-1, grow_policy="level", min_child_hessian_s
           min_split_loss=0.0, l1=0.0, l2=1.0, learning_rate=0.1)
 CASES = {"level": KW, "loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=24),
          "few_features": dict(KW, max_depth=4), "wide_features": dict(KW, max_depth=5),
+         "sparse_rows": dict(KW, max_depth=5),
          "sorted_shards": dict(KW, max_depth=7), "sorted_shards_loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=40)}
 
 
@@ -24,6 +25,10 @@ def _data(case):
         return synth(20000, 3, [17, 255, 4], 5)
     if case == "wide_features":                     # features with more than 256 bins (uint16 slots)
         return synth(40000, 7, [300, 5, 1000, 256, 257, 4000, 40], 13, skew=True)
+    if case == "sparse_rows":                       # mostly slot 0
+        x, start, gp = synth(30000, 60, 40, 29)
+        x = x * (np.random.default_rng(3).random(x.shape) < 0.05)
+        return np.ascontiguousarray(x.astype(np.int32)), start, gp
     if case.startswith("sorted_shards"):            # rows sorted by a feature: whole nodes live on one GPU only
         x, start, gp = synth(40000, 12, 64, 23)
         order = np.lexsort((x[:, 3], x[:, 0]))
@@ -40,8 +45,16 @@ def _rank(rank, world, nccl_id, case, ret):
     n = x.shape[0]
     lo, hi = n * rank // world, n * (rank + 1) // world
     p = yb.make_params(**CASES[case])
-    tm = yb.GpuTreeMaker(p, start, hi - lo, device=rank, rank=rank, world=world, nccl_id=nccl_id)
-    tm.upload_rows(x[lo:hi])
+    if case == "sparse_rows":                       # the shard as CSR: everything that is not slot 0 is stored
+        xs = x[lo:hi]
+        r, f = np.nonzero(xs)
+        row_ptr = np.concatenate([[0], np.cumsum((xs != 0).sum(axis=1))]).astype(np.int64)
+        tm = yb.GpuTreeMaker(p, start, hi - lo, device=rank, rank=rank, world=world, nccl_id=nccl_id,
+                             sparse_default=np.zeros(x.shape[1], np.int32), nnz=len(r))
+        tm.upload_csr(row_ptr, f.astype(np.int32), xs[r, f].astype(np.int32))
+    else:
+        tm = yb.GpuTreeMaker(p, start, hi - lo, device=rank, rank=rank, world=world, nccl_id=nccl_id)
+        tm.upload_rows(x[lo:hi])
     tm.set_grads(gp.reshape(n, 2)[lo:hi].reshape(-1))
     tree = tm.make(0)
     pos = tm.get_positions()

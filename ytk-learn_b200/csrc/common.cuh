@@ -59,6 +59,12 @@ struct SplitSeg {
 // index[f] = column of feature f, -1 if it has at most kMaxBins slots (null: no wide features).
 struct WideCols { uint16_t* data; int64_t stride; const int32_t* index; };
 
+// Sparse rows (CSR): row r holds nz[row_ptr[r] .. row_ptr[r+1]), each entry = feature << 16 | slot,
+// sorted by feature; a feature that is absent from a row has the slot default_slot[feature] (the bin
+// of the value the reference fills missing values with).  row_ptr == null: the dense layout.
+struct SparseRows { const int64_t* row_ptr; const uint32_t* nz; const int32_t* default_slot; };
+constexpr int kMaxSparseFeatures = 65536;
+
 // cseg >= 0: sample_cnt is the global row count of the smaller (which = 0) / larger (which = 1)
 // child of split segment cseg, read from the device counts
 struct ScanNode { const long long* hist; long long sample_cnt; int cseg; int which; };
@@ -98,6 +104,20 @@ cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide
                              const int32_t* rowidx1, const RowItem* items, int n_items, const int32_t* feat_owner,
                              const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
                              const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st);
+// Sparse rows: every stored entry of the items' rows goes into the node's histogram with 64-bit global
+// reductions, the rows' (g,h) totals into tot[2*seg + {0,1}]; then, per node and selected feature, the
+// default slot receives what the stored entries did not account for ("fill-value bin by subtraction").
+cudaError_t launch_hist_csr(SparseRows sparse, const uint8_t* fea_selected, const int2* gq, const int32_t* rowidx0,
+                            const int32_t* rowidx1, const RowItem* items, int n_items, const int32_t* feat_owner,
+                            const int64_t* feat_inner, long long owner_stride, long long* const* seg_out, long long* tot,
+                            const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st);
+cudaError_t launch_csr_default_fix(SparseRows sparse, const uint8_t* fea_selected, int32_t F, const int32_t* start,
+                                   const int32_t* feat_owner, const int64_t* feat_inner, long long owner_stride,
+                                   long long* const* seg_out, int n_segs, const long long* tot, cudaStream_t st);
+// checks one uploaded chunk (entries sorted by feature inside a row, features / slots in range) and packs it
+cudaError_t launch_csr_pack(const int64_t* row_ptr, const int32_t* fids, const int32_t* slots, int64_t nrows, int32_t F,
+                            const int32_t* nbins, uint32_t* nz_out, int* bad_flag, cudaStream_t st);
+cudaError_t launch_csr_to_dense(SparseRows sparse, int64_t row0, int64_t nrows, int32_t F, int32_t* out, cudaStream_t st);
 // rows one hist work item should cover so that `total_rows` split into about two waves of CTAs
 int64_t hist_rows_per_item(int64_t total_rows, int groups);
 
@@ -122,7 +142,8 @@ constexpr int kPartTile = kPartThreads * kPartItems;
 // src: col_stride > 0 -> feature-major slots src[fid * col_stride + row]; else row-major with S8 bytes per row
 cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
                              const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
-                             uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st);
+                             uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st,
+                             SparseRows sparse = SparseRows{nullptr, nullptr, nullptr});
 
 constexpr int kFusedThreads = 512;
 constexpr int kFusedItems = 16;
@@ -133,7 +154,8 @@ constexpr int kFusedTile = kFusedThreads * kFusedItems;     // larger tiles: the
 cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
                                    const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                                    unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
-                                   PartitionCounts* counts, cudaStream_t st);
+                                   PartitionCounts* counts, cudaStream_t st,
+                                   SparseRows sparse = SparseRows{nullptr, nullptr, nullptr});
 
 // The next level's partition planned on the device (level-wise growth, one GPU): slot 2k / 2k+1 =
 // left / right child of this level's job k.  jobs[k]: which of the current segments / count
@@ -145,14 +167,16 @@ cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col
                                      const ytk_split* recs, double min_split_loss,
                                      SplitSeg* out_segs, int* out_tile_seg, int* n_tiles_dev, int grid_bound,
                                      unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
-                                     PartitionCounts* next_counts, cudaStream_t st);
+                                     PartitionCounts* next_counts, cudaStream_t st,
+                                     SparseRows sparse = SparseRows{nullptr, nullptr, nullptr});
 
 // ... and the root's own partition, planned from its record (one slot)
 cudaError_t launch_partition_planned_root(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
                                           int32_t* rowidx1, long long begin, long long end, int buf, const ytk_split* rec,
                                           double min_split_loss, SplitSeg* out_segs, int* out_tile_seg, int* n_tiles_dev,
                                           int grid_bound, unsigned long long* tile_state, unsigned int* ticket,
-                                          unsigned long long epoch, PartitionCounts* next_counts, cudaStream_t st);
+                                          unsigned long long epoch, PartitionCounts* next_counts, cudaStream_t st,
+                                          SparseRows sparse = SparseRows{nullptr, nullptr, nullptr});
 
 // K7: exact fixed-point sums of (g,h) over row runs -> out[2*seg + {0,1}] (pre-zeroed)
 cudaError_t launch_leaf_sums(const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1, const RowItem* items,
@@ -190,7 +214,8 @@ cudaError_t launch_peer_pull_reduce(const PeerTable& pt, int m, long long seg_ma
 cudaError_t launch_add_leaf_values(const int32_t* rowidx0, const int32_t* rowidx1, const LeafItem* items, int n_items,
                                    float* score, int32_t K, int32_t gid, cudaStream_t st);
 cudaError_t launch_walk_rows(const uint8_t* bins, int32_t S8, WideCols wide, const int32_t* rows, long long begin, long long end,
-                             const TreeNodeDev* nodes, float* score, int32_t K, int32_t gid, cudaStream_t st);
+                             const TreeNodeDev* nodes, float* score, int32_t K, int32_t gid, cudaStream_t st,
+                             SparseRows sparse = SparseRows{nullptr, nullptr, nullptr});
 // test rows: original values (float bits), real-valued thresholds in nodes[].info of inner nodes, leaf values in leaves
 cudaError_t launch_score_values(const int32_t* xbits, long long n, int32_t stride, const TreeNodeDev* nodes,
                                 const int32_t* default_child, float* score, int32_t K, int32_t gid, cudaStream_t st);

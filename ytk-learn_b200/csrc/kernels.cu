@@ -363,6 +363,136 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
     }
 }
 
+// ------------------------------------------------------------------------------------
+// Sparse rows (BASELINE config 4: 10 000 features at ~1 % density).  The reference's matrix is dense
+// (J/dataflow/GBDTCoreData.java:164-168) and cannot hold that shape; here the rows are CSR, an
+// absent feature has its default slot, and the histogram is what the dense path would produce.
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ int sparse_slot(const SparseRows& sp, int32_t rid, int fid) {
+    long long lo = sp.row_ptr[rid];
+    const long long end = sp.row_ptr[rid + 1];
+    long long hi = end;
+    const unsigned key = (unsigned)fid;
+    while (lo < hi) {                                    // entries are sorted by feature
+        const long long mid = (lo + hi) >> 1;
+        if ((sp.nz[mid] >> 16) < key) lo = mid + 1; else hi = mid;
+    }
+    if (lo < end) {
+        const unsigned e = sp.nz[lo];
+        if ((e >> 16) == key) return (int)(e & 0xffffu);
+    }
+    return sp.default_slot[fid];
+}
+
+// One CTA per work item (same items as hist_build_k), one warp per row at a time, lanes over the
+// row's stored entries.  Thousands of bins per node: global 64-bit reductions, little contention.
+__global__ void __launch_bounds__(256)
+hist_csr_k(SparseRows sp, const uint8_t* __restrict__ fea_selected, const int2* __restrict__ gq,
+           const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1, const RowItem* __restrict__ items,
+           const int32_t* __restrict__ feat_owner, const int64_t* __restrict__ feat_inner, long long owner_stride,
+           long long* const* __restrict__ seg_out, long long* __restrict__ tot,
+           const PartitionCounts* __restrict__ cnt_local, const PartitionCounts* __restrict__ cnt_global) {
+    pdl_sync();
+    const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
+    const int32_t* __restrict__ rows = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
+    long long* const base = seg_out[it.seg];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    long long tg = 0, th = 0;
+    // a warp walks its rows one after the other; the next row's id, extent and (g,h) are fetched while
+    // the current row's entries are being added, so the dependent loads of a row overlap the previous row
+    long long i = it.begin + warp;
+    int32_t rid = 0;
+    long long p0 = 0, p1 = 0;
+    int2 q = make_int2(0, 0);
+    if (i < it.end) {
+        rid = rows ? rows[i] : (int32_t)i;
+        p0 = sp.row_ptr[rid]; p1 = sp.row_ptr[rid + 1];
+        q = gq[rid];
+    }
+    while (i < it.end) {
+        const long long ni = i + nwarps;
+        int32_t nrid = 0;
+        long long np0 = 0, np1 = 0;
+        int2 nq = make_int2(0, 0);
+        if (ni < it.end) {
+            nrid = rows ? rows[ni] : (int32_t)ni;
+            np0 = sp.row_ptr[nrid]; np1 = sp.row_ptr[nrid + 1];
+            nq = gq[nrid];
+        }
+        tg += q.x; th += q.y;
+        for (long long p = p0 + lane; p < p1; p += 32) {
+            const unsigned e = sp.nz[p];
+            const int f = (int)(e >> 16), slot = (int)(e & 0xffffu);
+            if (fea_selected[f]) {
+                unsigned long long* out = reinterpret_cast<unsigned long long*>(base + feat_owner[f] * owner_stride + feat_inner[f]) + 2 * slot;
+                atomicAdd(out, (unsigned long long)(long long)q.x);
+                atomicAdd(out + 1, (unsigned long long)(long long)q.y);
+            }
+        }
+        i = ni; rid = nrid; p0 = np0; p1 = np1; q = nq;
+    }
+    if (lane == 0 && (tg | th) != 0) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(tot + 2 * it.seg), (unsigned long long)tg);
+        atomicAdd(reinterpret_cast<unsigned long long*>(tot + 2 * it.seg + 1), (unsigned long long)th);
+    }
+}
+
+// "Fill-value bin by subtraction": per node and selected feature, default slot += node totals - (sum of
+// what the stored entries put into the feature's bins).  Exact (integers); linear, so with several
+// GPUs it is applied to the local sums before the reduce-scatter.  grid (feature blocks, nodes), one
+// warp per feature.
+__global__ void __launch_bounds__(256)
+csr_default_fix_k(SparseRows sp, const uint8_t* __restrict__ fea_selected, int32_t F, const int32_t* __restrict__ start,
+                  const int32_t* __restrict__ feat_owner, const int64_t* __restrict__ feat_inner, long long owner_stride,
+                  long long* const* __restrict__ seg_out, const long long* __restrict__ tot) {
+    pdl_sync();
+    const int lane = threadIdx.x & 31;
+    const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (f >= F || !fea_selected[f]) return;
+    const int seg = blockIdx.y;
+    long long* hp = seg_out[seg] + feat_owner[f] * owner_stride + feat_inner[f];
+    const int nb = start[f + 1] - start[f];
+    long long g = 0, h = 0;
+    for (int j = lane; j < nb; j += 32) {
+        const longlong2 v = *reinterpret_cast<const longlong2*>(hp + 2 * j);
+        g += v.x; h += v.y;
+    }
+    for (int d = 16; d > 0; d >>= 1) {
+        g += __shfl_xor_sync(0xffffffffu, g, d);
+        h += __shfl_xor_sync(0xffffffffu, h, d);
+    }
+    if (lane == 0) {
+        const int dslot = sp.default_slot[f];
+        hp[2 * dslot] += tot[2 * seg] - g;
+        hp[2 * dslot + 1] += tot[2 * seg + 1] - h;
+    }
+}
+
+// upload: range and order checks, (feature, slot) packed into one word
+__global__ void csr_pack_k(const int64_t* __restrict__ row_ptr, const int32_t* __restrict__ fids,
+                           const int32_t* __restrict__ slots, int64_t nrows, int32_t F, const int32_t* __restrict__ nbins,
+                           uint32_t* __restrict__ nz_out, int* bad_flag) {
+    for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < nrows; r += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t p0 = row_ptr[r] - row_ptr[0], p1 = row_ptr[r + 1] - row_ptr[0];
+        int prev = -1;
+        for (int64_t p = p0; p < p1; p++) {
+            const int f = fids[p], sl = slots[p];
+            if (f <= prev || f >= F || sl < 0 || sl >= (f >= 0 && f < F ? nbins[f] : 0)) { *bad_flag = 1; nz_out[p] = 0; continue; }
+            prev = f;
+            nz_out[p] = ((unsigned)f << 16) | (unsigned)sl;
+        }
+    }
+}
+
+__global__ void csr_to_dense_k(SparseRows sp, int64_t row0, int64_t nrows, int32_t F, int32_t* __restrict__ out) {
+    const int64_t total = nrows * F;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / F;
+        const int f = (int)(i - r * F);
+        out[i] = sparse_slot(sp, (int32_t)(row0 + r), f);
+    }
+}
+
 // K3: sibling = parent - smaller child (HistogramBuilder.substract,
 //     J/data/gbdt/HistogramBuilder.java:101-107), exact in the integer domain.
 // Features with more than 256 slots ("wide", e.g. un-sampled continuous columns) do not fit the
@@ -627,7 +757,7 @@ __device__ __forceinline__ const int32_t* seg_src(const SplitSeg& s, const int32
 }
 
 __global__ void __launch_bounds__(kPartThreads)
-partition_count_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, WideCols wide,
+partition_count_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, WideCols wide, SparseRows sparse,
                   const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs,
                   const int* __restrict__ tile_seg, uint8_t* __restrict__ flags, int32_t* __restrict__ block_cnt) {
     __shared__ int s_cnt[kPartThreads / 32];
@@ -642,6 +772,7 @@ partition_count_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
             int32_t rid = rowidx ? rowidx[i] : (int32_t)i;
             bool left;
             if (sg.fid < 0) left = src[rid] != 0;
+            else if (sparse.row_ptr) left = (float)sparse_slot(sparse, rid, sg.fid) < sg.cond;
             else if (sg.wide > 0) left = (float)wide.data[(sg.wide - 1) * wide.stride + rid] < sg.cond;   // uint16 column
             else if (col_stride > 0) left = (float)src[sg.fid * col_stride + rid] < sg.cond;   // feature-major copy
             else left = (float)src[(long long)rid * S8 + sg.fid] < sg.cond;
@@ -897,6 +1028,34 @@ cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide
                                       seg_out, cnt_local, cnt_global);
 }
 
+cudaError_t launch_hist_csr(SparseRows sparse, const uint8_t* fea_selected, const int2* gq, const int32_t* rowidx0,
+                            const int32_t* rowidx1, const RowItem* items, int n_items, const int32_t* feat_owner,
+                            const int64_t* feat_inner, long long owner_stride, long long* const* seg_out, long long* tot,
+                            const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st) {
+    if (n_items <= 0) return cudaSuccess;
+    return launch_chain(hist_csr_k, dim3(n_items), dim3(256), 0, st, sparse, fea_selected, gq, rowidx0, rowidx1, items,
+                        feat_owner, feat_inner, owner_stride, seg_out, tot, cnt_local, cnt_global);
+}
+cudaError_t launch_csr_default_fix(SparseRows sparse, const uint8_t* fea_selected, int32_t F, const int32_t* start,
+                                   const int32_t* feat_owner, const int64_t* feat_inner, long long owner_stride,
+                                   long long* const* seg_out, int n_segs, const long long* tot, cudaStream_t st) {
+    if (n_segs <= 0) return cudaSuccess;
+    dim3 grid((unsigned)((F + 7) / 8), (unsigned)n_segs);
+    return launch_chain(csr_default_fix_k, grid, dim3(256), 0, st, sparse, fea_selected, F, start, feat_owner, feat_inner,
+                        owner_stride, seg_out, tot);
+}
+cudaError_t launch_csr_pack(const int64_t* row_ptr, const int32_t* fids, const int32_t* slots, int64_t nrows, int32_t F,
+                            const int32_t* nbins, uint32_t* nz_out, int* bad_flag, cudaStream_t st) {
+    if (nrows <= 0) return cudaSuccess;
+    csr_pack_k<<<grid_for(nrows, 128), 128, 0, st>>>(row_ptr, fids, slots, nrows, F, nbins, nz_out, bad_flag);
+    return cudaGetLastError();
+}
+cudaError_t launch_csr_to_dense(SparseRows sparse, int64_t row0, int64_t nrows, int32_t F, int32_t* out, cudaStream_t st) {
+    if (nrows <= 0) return cudaSuccess;
+    csr_to_dense_k<<<grid_for(nrows * F, 256), 256, 0, st>>>(sparse, row0, nrows, F, out);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_hist_subtract(const SubItem* items, int n_items, int64_t len, cudaStream_t st) {
     if (n_items <= 0) return cudaSuccess;
     dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n_items);
@@ -962,7 +1121,8 @@ __device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned 
 }
 
 __global__ void __launch_bounds__(kFusedThreads)
-partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* __restrict__ rowidx0,
+partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, WideCols wide, SparseRows sparse,
+                  int32_t* __restrict__ rowidx0,
                   int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs, int n_segs,
                   const int* __restrict__ tile_seg, int n_tiles, const int* __restrict__ n_tiles_dev,
                   unsigned long long* __restrict__ tile_state, unsigned int* __restrict__ ticket, unsigned long long epoch,
@@ -1020,7 +1180,10 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     const int mul = (mask || col_stride > 0) ? 1 : S8;
     const float cond = mask ? 0.5f : sg.cond;
     unsigned short slot[kFusedItems];
-    if (sg.wide > 0) {                                   // a feature with more than 256 slots: its uint16 column
+    if (sparse.row_ptr && !mask) {                       // sparse rows: look the feature up in the row
+#pragma unroll
+        for (int k = 0; k < kFusedItems; k++) slot[k] = (unsigned short)sparse_slot(sparse, rid[k], sg.fid);
+    } else if (sg.wide > 0) {                            // a feature with more than 256 slots: its uint16 column
         const uint16_t* __restrict__ wb = wide.data + (long long)(sg.wide - 1) * wide.stride;
 #pragma unroll
         for (int k = 0; k < kFusedItems; k++) slot[k] = wb[rid[k]];
@@ -1113,11 +1276,11 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
 cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
                                    const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                                    unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
-                                   PartitionCounts* counts, cudaStream_t st) {
+                                   PartitionCounts* counts, cudaStream_t st, SparseRows sparse) {
     if (n_segs <= 0) return cudaSuccess;
     if (n_tiles <= 0) return cudaMemsetAsync(counts, 0, (size_t)n_segs * sizeof(PartitionCounts), st);
-    return launch_chain(partition_fused_k, dim3(n_tiles), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, rowidx0,
-                        rowidx1, segs, n_segs, tile_seg, n_tiles, (const int*)nullptr, tile_state, ticket, epoch, counts);
+    return launch_chain(partition_fused_k, dim3(n_tiles), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
+                        rowidx0, rowidx1, segs, n_segs, tile_seg, n_tiles, (const int*)nullptr, tile_state, ticket, epoch, counts);
 }
 
 // ------------------------------------------------------------------------------------
@@ -1224,12 +1387,13 @@ cudaError_t launch_partition_planned_root(const uint8_t* src, int32_t S8, int64_
                                           int32_t* rowidx1, long long begin, long long end, int buf, const ytk_split* rec,
                                           double min_split_loss, SplitSeg* out_segs, int* out_tile_seg, int* n_tiles_dev,
                                           int grid_bound, unsigned long long* tile_state, unsigned int* ticket,
-                                          unsigned long long epoch, PartitionCounts* next_counts, cudaStream_t st) {
+                                          unsigned long long epoch, PartitionCounts* next_counts, cudaStream_t st,
+                                          SparseRows sparse) {
     cudaError_t e = launch_chain(plan_root_partition_k, dim3(1), dim3(256), 0, st, begin, end, buf, rec, min_split_loss,
                                  wide.index, out_segs, out_tile_seg, n_tiles_dev, ticket, next_counts);
     if (e != cudaSuccess || grid_bound <= 0) return e;
-    return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, rowidx0,
-                        rowidx1, (const SplitSeg*)out_segs, 1, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
+    return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
+                        rowidx0, rowidx1, (const SplitSeg*)out_segs, 1, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
                         tile_state, ticket, epoch, next_counts);
 }
 
@@ -1239,22 +1403,22 @@ cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col
                                      const ytk_split* recs, double min_split_loss,
                                      SplitSeg* out_segs, int* out_tile_seg, int* n_tiles_dev, int grid_bound,
                                      unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
-                                     PartitionCounts* next_counts, cudaStream_t st) {
+                                     PartitionCounts* next_counts, cudaStream_t st, SparseRows sparse) {
     if (m <= 0) return cudaSuccess;
     cudaError_t e = launch_chain(plan_next_partition_k, dim3(1), dim3(512), 0, st, cur_segs, cur_counts, cur_counts_global, jobs, m, recs,
                                  min_split_loss, wide.index, out_segs, out_tile_seg, n_tiles_dev, ticket, next_counts);
     if (e != cudaSuccess || grid_bound <= 0) return e;
-    return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, rowidx0,
-                        rowidx1, (const SplitSeg*)out_segs, 2 * m, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
+    return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
+                        rowidx0, rowidx1, (const SplitSeg*)out_segs, 2 * m, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
                         tile_state, ticket, epoch, next_counts);
 }
 
 cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
                              const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
-                             uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st) {
+                             uint8_t* flags, int32_t* block_cnt, PartitionCounts* counts, cudaStream_t st, SparseRows sparse) {
     if (n_segs <= 0) return cudaSuccess;
     if (n_tiles > 0)
-        partition_count_k<<<n_tiles, kPartThreads, 0, st>>>(src, S8, col_stride, wide, rowidx0, rowidx1, segs, tile_seg,
+        partition_count_k<<<n_tiles, kPartThreads, 0, st>>>(src, S8, col_stride, wide, sparse, rowidx0, rowidx1, segs, tile_seg,
                                                             flags, block_cnt);
     partition_scan_k<<<n_segs, 1024, 0, st>>>(segs, block_cnt, counts);
     if (n_tiles > 0)
@@ -1306,7 +1470,8 @@ __global__ void add_leaf_values_k(const int32_t* __restrict__ rowidx0, const int
 
 // Rows that were not sampled for the tree are in no leaf interval: walk the tree on their slots
 // with Tree.getNext's rule, slot <= cond goes left (J/data/gbdt/Tree.java:156-168).
-__global__ void walk_rows_k(const uint8_t* __restrict__ bins, int32_t S8, WideCols wide, const int32_t* __restrict__ rows,
+__global__ void walk_rows_k(const uint8_t* __restrict__ bins, int32_t S8, WideCols wide, SparseRows sparse,
+                            const int32_t* __restrict__ rows,
                             long long begin, long long end, const TreeNodeDev* __restrict__ nodes,
                             float* __restrict__ score, int32_t K, int32_t gid) {
     for (long long i = begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < end;
@@ -1316,7 +1481,8 @@ __global__ void walk_rows_k(const uint8_t* __restrict__ bins, int32_t S8, WideCo
         TreeNodeDev nd = nodes[0];
         while (nd.left != -1) {
             const int wi = wide.index ? wide.index[nd.fid] : -1;
-            const float v = wi >= 0 ? (float)wide.data[wi * wide.stride + r] : (float)bins[r * S8 + nd.fid];
+            const float v = sparse.row_ptr ? (float)sparse_slot(sparse, (int32_t)r, nd.fid)
+                            : wi >= 0 ? (float)wide.data[wi * wide.stride + r] : (float)bins[r * S8 + nd.fid];
             pid = (v <= nd.info) ? nd.left : nd.right;
             nd = nodes[pid];
         }
@@ -1441,10 +1607,11 @@ cudaError_t launch_add_leaf_values(const int32_t* rowidx0, const int32_t* rowidx
     return cudaGetLastError();
 }
 cudaError_t launch_walk_rows(const uint8_t* bins, int32_t S8, WideCols wide, const int32_t* rows, long long begin, long long end,
-                             const TreeNodeDev* nodes, float* score, int32_t K, int32_t gid, cudaStream_t st) {
+                             const TreeNodeDev* nodes, float* score, int32_t K, int32_t gid, cudaStream_t st,
+                             SparseRows sparse) {
     if (end <= begin) return cudaSuccess;
     long long b = (end - begin + 255) / 256;
-    walk_rows_k<<<(unsigned)std::min<long long>(b, kNumSMs * 8), 256, 0, st>>>(bins, S8, wide, rows, begin, end, nodes, score, K, gid);
+    walk_rows_k<<<(unsigned)std::min<long long>(b, kNumSMs * 8), 256, 0, st>>>(bins, S8, wide, sparse, rows, begin, end, nodes, score, K, gid);
     return cudaGetLastError();
 }
 cudaError_t launch_score_values(const int32_t* xbits, long long n, int32_t stride, const TreeNodeDev* nodes,

@@ -328,6 +328,13 @@ struct ytk_gbdt {
     int32_t* d_feat_zero = nullptr;    // all zeros: "everything in one flat segment"
     int64_t* d_off_inner = nullptr;    // offset of feature f inside its owner's segment
     int64_t* d_off_flat = nullptr;     // reference layout 2*start[f]
+    // sparse rows (CSR) instead of the dense matrices: ytk_gbdt_set_bins_sparse / ytk_gbdt_upload_csr
+    bool sparse = false;
+    int64_t* d_row_ptr = nullptr;          // [N+1], absolute offsets into d_nz
+    uint32_t* d_nz = nullptr;              // feature << 16 | slot, rows sorted by feature
+    int32_t* d_default_slot = nullptr;     // [F]
+    int64_t nnz_cap = 0, csr_rows_done = 0, csr_nnz_done = 0;
+    DevTable<long long> t_node_tot;        // (g,h) totals of the rows of each node of a batch
     uint32_t* d_group_mask = nullptr;
     // features with more than 256 slots: uint16 columns beside the uint8 matrices
     int n_wide = 0;
@@ -427,7 +434,7 @@ void free_all(ytk_gbdt* h) {
     auto F = [](void* p) { if (p) cudaFree(p); };
     F(h->d_bins); F(h->d_bins_col); F(h->d_gp); F(h->d_gq); F(h->d_rowidx[0]); F(h->d_rowidx[1]); F(h->d_flags); F(h->d_block_cnt); F(h->d_tile_state); F(h->d_ticket);
     F(h->d_mask); F(h->d_start); F(h->d_nbins); F(h->d_feat_owner); F(h->d_feat_zero); F(h->d_off_inner);
-    F(h->d_off_flat); F(h->d_group_mask); F(h->d_wide); F(h->d_wide_index); F(h->d_wide_fids); F(h->d_fea_sel); F(h->d_hist_flat); F(h->d_hist_flat2);
+    F(h->d_off_flat); F(h->d_group_mask); F(h->d_row_ptr); F(h->d_nz); F(h->d_default_slot); F(h->d_wide); F(h->d_wide_index); F(h->d_wide_fids); F(h->d_fea_sel); F(h->d_hist_flat); F(h->d_hist_flat2);
     F(h->d_hist_dbl); F(h->d_scale); F(h->d_scale_hook); F(h->d_absmax); F(h->d_bad); F(h->d_node_of_row);
     F(h->d_stage); F(h->d_blob); F(h->d_blob_part); F(h->d_score); F(h->d_y); F(h->d_w); F(h->d_init); F(h->d_block_loss); F(h->d_loss);
     h->t_leafval.release(); h->t_tree.release();
@@ -438,7 +445,7 @@ void free_all(ytk_gbdt* h) {
     h->t_items.release(); h->t_leaf_items.release(); h->t_segs.release(); h->t_tile_seg.release();
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
     h->t_split_local.release(); h->t_split_all.release(); h->t_parts.release(); h->t_leaf.release(); h->t_hist_local.release();
-    h->t_rs_out.release();
+    h->t_rs_out.release(); h->t_node_tot.release();
     for (int i = 0; i < 2; i++) { h->t_spec_segs[i].release(); h->t_spec_counts[i].release(); h->h_spec_counts[i].release(); }
     h->t_spec_tiles.release();
     F(h->d_spec_ntiles);
@@ -450,6 +457,10 @@ void free_all(ytk_gbdt* h) {
     for (auto e : h->evc) cudaEventDestroy(e);
     if (h->comm) ytk::nccl_api().CommDestroy(h->comm);
     if (h->st) cudaStreamDestroy(h->st);
+}
+
+ytk::SparseRows sparse_rows(const ytk_gbdt* h) {
+    return h->sparse ? ytk::SparseRows{h->d_row_ptr, h->d_nz, h->d_default_slot} : ytk::SparseRows{nullptr, nullptr, nullptr};
 }
 
 // the uint16 columns, seen from row `row0` on
@@ -678,7 +689,8 @@ int hist_plan(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, 
         int64_t mid = (lo_u + hi_u) / 2;
         if (items_at(mid * 1024) <= target) hi_u = mid; else lo_u = mid + 1;
     }
-    const int64_t rpi = lo_u * 1024;
+    // sparse rows: a work item is a CTA of 8 warps walking one row each -- many small items instead
+    const int64_t rpi = h->sparse ? 256 : lo_u * 1024;
     pl.outs_local.resize(m);
     const int64_t local_len = h->seg_max * h->world;
     const bool peer = h->world > 1 && peer_ok(h, m);
@@ -724,14 +736,29 @@ int hist_enqueue(ytk_gbdt* h, const HistPlan& pl, ytk_time_stats* T, const ytk::
         CK(cudaMemsetAsync(peer ? (void*)h->my_hist : (void*)h->t_hist_local.d, 0,
                            (size_t)m * local_len * sizeof(long long), h->st));
     }
-    CK(cudaEventRecord(e0, h->st));        // the pair brackets the hist_build_k launch only
     const long long owner_stride = h->world == 1 ? 0 : (long long)m * h->seg_max;
-    CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1],
-                              blob_ptr<ytk::RowItem>(h, pl.o_items), (int)pl.items.size(), h->F, h->d_group_mask,
-                              h->d_nbins, h->d_feat_owner, h->d_off_inner, owner_stride, d_local, cnt_local, cnt_global,
-                              h->st));
+    if (h->sparse) {
+        CK(h->t_node_tot.reserve(2 * (size_t)m));
+        CK(cudaMemsetAsync(h->t_node_tot.d, 0, 2 * (size_t)m * sizeof(long long), h->st));
+    }
+    CK(cudaEventRecord(e0, h->st));        // the pair brackets the histogram-build launch only
+    if (h->sparse) {
+        CK(ytk::launch_hist_csr(sparse_rows(h), h->d_fea_sel, h->d_gq, h->d_rowidx[0], h->d_rowidx[1],
+                                blob_ptr<ytk::RowItem>(h, pl.o_items), (int)pl.items.size(), h->d_feat_owner, h->d_off_inner,
+                                owner_stride, d_local, h->t_node_tot.d, cnt_local, cnt_global, h->st));
+    } else {
+        CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1],
+                                  blob_ptr<ytk::RowItem>(h, pl.o_items), (int)pl.items.size(), h->F, h->d_group_mask,
+                                  h->d_nbins, h->d_feat_owner, h->d_off_inner, owner_stride, d_local, cnt_local, cnt_global,
+                                  h->st));
+    }
     if (!pl.items.empty()) h->launches++;
     CK(cudaEventRecord(e1, h->st));
+    if (h->sparse) {
+        CK(ytk::launch_csr_default_fix(sparse_rows(h), h->d_fea_sel, h->F, h->d_start, h->d_feat_owner, h->d_off_inner,
+                                       owner_stride, d_local, m, h->t_node_tot.d, h->st));
+        h->launches++;
+    }
     if (!h->wide_sel.empty() && !pl.items.empty()) {
         CK(ytk::launch_hist_wide(wide_cols(h), h->d_wide_fids, (int)h->wide_sel.size(), h->d_gq, h->d_rowidx[0],
                                  h->d_rowidx[1], blob_ptr<ytk::RowItem>(h, pl.o_items), (int)pl.items.size(),
@@ -892,7 +919,7 @@ int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const
         CK(h->t_counts.reserve(2 * (size_t)m));
         CK(ytk::launch_partition_fused(src, h->S8, col_stride, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1],
                                        pl.d_segs, m, pl.d_tiles, (int)n_tiles,
-                                       h->d_tile_state, h->d_ticket, h->part_epoch, h->t_counts.d, h->st));
+                                       h->d_tile_state, h->d_ticket, h->part_epoch, h->t_counts.d, h->st, sparse_rows(h)));
         h->launches++;
     } else {
     if (n_tiles + 1 > h->block_cnt_cap) {
@@ -904,7 +931,7 @@ int partition_enqueue(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const
     CK(h->t_counts.reserve(2 * (size_t)m));
     CK(ytk::launch_partition(src, h->S8, col_stride, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1],
                              pl.d_segs, m, pl.d_tiles, (int)n_tiles,
-                             h->d_flags, h->d_block_cnt, h->t_counts.d, h->st));
+                             h->d_flags, h->d_block_cnt, h->t_counts.d, h->st, sparse_rows(h)));
     h->launches += n_tiles == 0 ? 1 : 3;
     }
     const int nc = h->world > 1 ? 2 * m : m;
@@ -1084,7 +1111,19 @@ int ytk_gbdt_destroy(ytk_gbdt* h) {
     return YTK_OK;
 }
 
+static int set_bins_impl(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_rows, const int32_t* default_slot,
+                         int64_t nnz);
 int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_rows) {
+    return set_bins_impl(h, start, F, n_rows, nullptr, 0);
+}
+int ytk_gbdt_set_bins_sparse(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_rows, const int32_t* default_slot,
+                             int64_t nnz) {
+    if (!default_slot || nnz < 0) return fail(YTK_ERR_ARG, "set_bins_sparse: bad arguments");
+    if (F > ytk::kMaxSparseFeatures) return fail(YTK_ERR_UNSUPPORTED, "set_bins_sparse: %d features, at most %d", F, ytk::kMaxSparseFeatures);
+    return set_bins_impl(h, start, F, n_rows, default_slot, nnz);
+}
+static int set_bins_impl(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_rows, const int32_t* default_slot,
+                         int64_t nnz) {
     if (!h || !start || F < 1 || n_rows < 0) return fail(YTK_ERR_ARG, "set_bins: bad arguments");
     if (h->rows_set) return fail(YTK_ERR_ARG, "set_bins: already called");
     if (n_rows > 0x7fffffffLL) return fail(YTK_ERR_ARG, "set_bins: %lld rows exceed int32 row ids", (long long)n_rows);
@@ -1123,10 +1162,23 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
 
     const int64_t N1 = std::max<int64_t>(n_rows, 1);
     const int K = h->p.class_num;
-    CK(cudaMalloc(&h->d_bins, N1 * h->S8));
-    CK(cudaMemsetAsync(h->d_bins, 0, N1 * h->S8, h->st));
-    CK(cudaMalloc(&h->d_bins_col, N1 * F));
-    CK(cudaMemsetAsync(h->d_bins_col, 0, N1 * F, h->st));
+    h->sparse = default_slot != nullptr;
+    if (h->sparse) {
+        for (int f = 0; f < F; f++)
+            if (default_slot[f] < 0 || default_slot[f] >= h->nbins[f])
+                return fail(YTK_ERR_ARG, "set_bins_sparse: default slot %d of feature %d outside its %d bins", default_slot[f], f, h->nbins[f]);
+        h->nnz_cap = nnz;
+        CK(cudaMalloc(&h->d_row_ptr, (N1 + 1) * sizeof(int64_t)));
+        CK(cudaMemsetAsync(h->d_row_ptr, 0, (N1 + 1) * sizeof(int64_t), h->st));
+        CK(cudaMalloc(&h->d_nz, std::max<int64_t>(nnz, 1) * sizeof(uint32_t)));
+        CK(cudaMalloc(&h->d_default_slot, F * sizeof(int32_t)));
+        CK(cudaMemcpyAsync(h->d_default_slot, default_slot, F * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+    } else {
+        CK(cudaMalloc(&h->d_bins, N1 * h->S8));
+        CK(cudaMemsetAsync(h->d_bins, 0, N1 * h->S8, h->st));
+        CK(cudaMalloc(&h->d_bins_col, N1 * F));
+        CK(cudaMemsetAsync(h->d_bins_col, 0, N1 * F, h->st));
+    }
     CK(cudaMalloc(&h->d_gp, N1 * K * 2 * sizeof(float)));
     CK(cudaMalloc(&h->d_gq, N1 * sizeof(int2)));
     CK(cudaMalloc(&h->d_rowidx[0], N1 * sizeof(int32_t)));
@@ -1143,6 +1195,10 @@ int ytk_gbdt_set_bins(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n_ro
     h->wide_index.assign(F, -1);
     h->n_wide = 0;
     for (int f = 0; f < F; f++) if (h->nbins[f] > ytk::kMaxBins) h->wide_index[f] = h->n_wide++;
+    if (h->sparse) {                        // slots live in the CSR entries (16 bits each): no uint16 columns
+        h->wide_index.assign(F, -1);
+        h->n_wide = 0;
+    }
     if (h->n_wide > 0) {
         CK(cudaMalloc(&h->d_wide, (size_t)h->n_wide * N1 * sizeof(uint16_t)));
         CK(cudaMemsetAsync(h->d_wide, 0, (size_t)h->n_wide * N1 * sizeof(uint16_t), h->st));
@@ -1210,6 +1266,7 @@ static int check_rows(ytk_gbdt* h, const void* p, int64_t row0, int64_t nrows, c
 
 int ytk_gbdt_upload_rows(ytk_gbdt* h, const int32_t* x_chunk, int64_t row0, int64_t nrows, int32_t stride) {
     RET(check_rows(h, x_chunk, row0, nrows, "upload_rows"));
+    if (h->sparse) return fail(YTK_ERR_ARG, "upload_rows: this handle holds sparse rows (ytk_gbdt_upload_csr)");
     if (stride < h->F) return fail(YTK_ERR_ARG, "upload_rows: stride %d < feature dim %d", stride, h->F);
     if (nrows == 0) return YTK_OK;
     CK(cudaSetDevice(h->device));
@@ -1236,6 +1293,7 @@ int ytk_gbdt_upload_rows(ytk_gbdt* h, const int32_t* x_chunk, int64_t row0, int6
 int ytk_gbdt_quantize_rows(ytk_gbdt* h, const int32_t* xbits_chunk, int64_t row0, int64_t nrows, int32_t stride,
                            const float* cuts) {
     RET(check_rows(h, xbits_chunk, row0, nrows, "quantize_rows"));
+    if (h->sparse) return fail(YTK_ERR_ARG, "quantize_rows: this handle holds sparse rows (ytk_gbdt_upload_csr)");
     if (!cuts) return fail(YTK_ERR_ARG, "quantize_rows: null cuts");
     if (stride < h->F) return fail(YTK_ERR_ARG, "quantize_rows: stride %d < feature dim %d", stride, h->F);
     if (nrows == 0) return YTK_OK;
@@ -1260,6 +1318,45 @@ int ytk_gbdt_quantize_rows(ytk_gbdt* h, const int32_t* xbits_chunk, int64_t row0
     return YTK_OK;
 }
 
+int ytk_gbdt_upload_csr(ytk_gbdt* h, const int64_t* row_ptr, const int32_t* fids, const int32_t* slots, int64_t row0,
+                        int64_t nrows) {
+    RET(check_rows(h, row_ptr, row0, nrows, "upload_csr"));
+    if (!h->sparse) return fail(YTK_ERR_ARG, "upload_csr: call ytk_gbdt_set_bins_sparse first");
+    if (row0 != h->csr_rows_done) return fail(YTK_ERR_ARG, "upload_csr: chunks go in row order (expected row %lld, got %lld)",
+                                              (long long)h->csr_rows_done, (long long)row0);
+    if (nrows == 0) return YTK_OK;
+    const int64_t nnz = row_ptr[nrows] - row_ptr[0];
+    for (int64_t r = 0; r < nrows; r++)
+        if (row_ptr[r + 1] < row_ptr[r]) return fail(YTK_ERR_ARG, "upload_csr: row_ptr decreases at row %lld", (long long)(row0 + r));
+    if (nnz > 0 && (!fids || !slots)) return fail(YTK_ERR_ARG, "upload_csr: null entry arrays");
+    if (h->csr_nnz_done + nnz > h->nnz_cap)
+        return fail(YTK_ERR_CAPACITY, "upload_csr: %lld entries exceed the %lld announced to set_bins_sparse",
+                    (long long)(h->csr_nnz_done + nnz), (long long)h->nnz_cap);
+    CK(cudaSetDevice(h->device));
+    // absolute row offsets
+    std::vector<int64_t> abs_ptr(nrows + 1);
+    for (int64_t r = 0; r <= nrows; r++) abs_ptr[r] = h->csr_nnz_done + (row_ptr[r] - row_ptr[0]);
+    CK(cudaMemcpyAsync(h->d_row_ptr + row0, abs_ptr.data(), (nrows + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, h->st));
+    if (nnz > 0) {
+        RET(ensure_stage(h, (size_t)nnz * 2 * sizeof(int32_t)));
+        int32_t* d_f = (int32_t*)h->d_stage;
+        int32_t* d_s = d_f + nnz;
+        CK(cudaMemcpyAsync(d_f, fids + row_ptr[0], nnz * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+        CK(cudaMemcpyAsync(d_s, slots + row_ptr[0], nnz * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
+        CK(ytk::launch_csr_pack(h->d_row_ptr + row0, d_f, d_s, nrows, h->F, h->d_nbins, h->d_nz + h->csr_nnz_done, h->d_bad, h->st));
+    }
+    CK(cudaStreamSynchronize(h->st));
+    int bad = 0;
+    CK(cudaMemcpy(&bad, h->d_bad, sizeof(int), cudaMemcpyDeviceToHost));
+    if (bad) {
+        CK(cudaMemset(h->d_bad, 0, sizeof(int)));
+        return fail(YTK_ERR_ARG, "upload_csr: an entry has a feature or slot out of range, or a row is not sorted by feature");
+    }
+    h->csr_rows_done += nrows;
+    h->csr_nnz_done += nnz;
+    return YTK_OK;
+}
+
 int ytk_gbdt_download_rows(ytk_gbdt* h, int32_t* out, int64_t row0, int64_t nrows) {
     RET(check_rows(h, out, row0, nrows, "download_rows"));
     if (nrows == 0) return YTK_OK;
@@ -1269,6 +1366,8 @@ int ytk_gbdt_download_rows(ytk_gbdt* h, int32_t* out, int64_t row0, int64_t nrow
         int64_t n = std::min(step, nrows - r);
         size_t bytes = (size_t)n * h->F * sizeof(int32_t);
         RET(ensure_stage(h, bytes));
+        if (h->sparse) CK(ytk::launch_csr_to_dense(sparse_rows(h), row0 + r, n, h->F, (int32_t*)h->d_stage, h->st));
+        else
         CK(ytk::launch_unpack_rows(h->d_bins + (row0 + r) * h->S8, h->S8, n, h->F, wide_cols(h, row0 + r),
                                    (int32_t*)h->d_stage, h->st));
         CK(cudaMemcpyAsync(out + r * h->F, h->d_stage, bytes, cudaMemcpyDeviceToHost, h->st));
@@ -1447,7 +1546,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
                                                   root.b, root.e, root.buf, h->world > 1 ? h->t_split_all.d : h->h_split.h,
                                                   p.min_split_loss, h->t_spec_segs[0].d, h->t_spec_tiles.d,
                                                   h->d_spec_ntiles, (int)grid_bound, h->d_tile_state, h->d_ticket + 1,
-                                                  h->part_epoch, h->t_spec_counts[0].d, h->st));
+                                                  h->part_epoch, h->t_spec_counts[0].d, h->st, sparse_rows(h)));
             if (h->world > 1) {
                 RET(comm_mark(h));
                 const unsigned long long ep = ++h->epoch[0];
@@ -1842,7 +1941,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
                                              d_cur_segs, d_cl, d_cg, blob_ptr<ytk::SpecJob>(h, o_spec), m,
                                              h->world > 1 ? h->t_split_all.d : h->h_split.h, p.min_split_loss, h->t_spec_segs[np].d, h->t_spec_tiles.d, h->d_spec_ntiles,
                                              (int)grid_bound, h->d_tile_state, h->d_ticket + 1, h->part_epoch,
-                                             h->t_spec_counts[np].d, h->st));
+                                             h->t_spec_counts[np].d, h->st, sparse_rows(h)));
             if (h->world > 1) {   // allreduceArray(long[2], SUM) (:538) of the planned partition's counts
                 RET(comm_mark(h));
                 const unsigned long long ep = ++h->epoch[0];
@@ -2052,7 +2151,7 @@ int ytk_gbdt_update_scores(ytk_gbdt* h, int32_t gid) {
         // the row-mask compaction left the excluded rows behind the sampled ones in buffer 0, and
         // later partitions only ever rewrite the sampled range
         CK(ytk::launch_walk_rows(h->d_bins, h->S8, wide_cols(h), h->d_rowidx[0], h->unsampled_begin, h->N, h->t_tree.d, h->d_score,
-                                 h->p.class_num, gid, h->st));
+                                 h->p.class_num, gid, h->st, sparse_rows(h)));
     }
     CK(cudaStreamSynchronize(h->st));
     h->arena.rewind();
@@ -2168,6 +2267,15 @@ int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n
     std::vector<long long*> outs(1, h->d_hist_flat);
     CK(h->t_items.upload(items, h->st, h->arena));
     CK(h->t_seg_out.upload(outs, h->st, h->arena));
+    if (h->sparse) {
+        CK(h->t_node_tot.reserve(2));
+        CK(cudaMemsetAsync(h->t_node_tot.d, 0, 2 * sizeof(long long), h->st));
+        CK(ytk::launch_hist_csr(sparse_rows(h), h->d_fea_sel, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_items.d,
+                                (int)items.size(), h->d_feat_zero, h->d_off_flat, 0, h->t_seg_out.d, h->t_node_tot.d,
+                                nullptr, nullptr, h->st));
+        CK(ytk::launch_csr_default_fix(sparse_rows(h), h->d_fea_sel, h->F, h->d_start, h->d_feat_zero, h->d_off_flat, 0,
+                                       h->t_seg_out.d, 1, h->t_node_tot.d, h->st));
+    } else
     CK(ytk::launch_hist_build(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], h->t_items.d,
                               (int)items.size(), h->F, h->d_group_mask, h->d_nbins, h->d_feat_zero, h->d_off_flat, 0,
                               h->t_seg_out.d, nullptr, nullptr, h->st));

@@ -36,7 +36,9 @@ def make_params(max_depth=6, max_leaf_cnt=-1, min_split_samples=-1, grow_policy=
 class GpuTreeMaker:
     """One instance per GPU / row shard (the reference: one per worker thread)."""
 
-    def __init__(self, params, start, n_rows, device=0, rank=0, world=1, nccl_id=None):
+    def __init__(self, params, start, n_rows, device=0, rank=0, world=1, nccl_id=None, sparse_default=None, nnz=0):
+        """sparse_default (int32 [F]) switches the handle to sparse rows (upload_csr): the slot of a
+        feature a row does not store; nnz = number of stored entries of this shard."""
         self._h = C.c_void_p()
         self.params = params
         self.start = np.ascontiguousarray(start, dtype=np.int32)
@@ -49,7 +51,11 @@ class GpuTreeMaker:
         self._nccl_id = nccl_id
         B.check(B.lib().ytk_gbdt_create(C.addressof(params), int(device), int(rank), int(world), idp,
                                         C.addressof(self._h)))
-        B.check(B.lib().ytk_gbdt_set_bins(self._h, B.ptr(self.start), self.F, self.N))
+        if sparse_default is None:
+            B.check(B.lib().ytk_gbdt_set_bins(self._h, B.ptr(self.start), self.F, self.N))
+        else:
+            d = np.ascontiguousarray(sparse_default, dtype=np.int32)
+            B.check(B.lib().ytk_gbdt_set_bins_sparse(self._h, B.ptr(self.start), self.F, self.N, B.ptr(d), int(nnz)))
 
     def close(self):
         if self._h:
@@ -63,6 +69,13 @@ class GpuTreeMaker:
             pass
 
     # ---- data in -------------------------------------------------------------------
+    def upload_csr(self, row_ptr, fids, slots, row0=0):
+        """One CSR chunk (rows in order, entries of a row sorted by feature)."""
+        rp = np.ascontiguousarray(row_ptr, dtype=np.int64)
+        f = np.ascontiguousarray(fids, dtype=np.int32)
+        sl = np.ascontiguousarray(slots, dtype=np.int32)
+        B.check(B.lib().ytk_gbdt_upload_csr(self._h, B.ptr(rp), B.ptr(f), B.ptr(sl), int(row0), len(rp) - 1))
+
     def upload_rows(self, x, row0=0):
         """x: int32 slots [n, stride] (a GBDTCoreData.x chunk after binning)."""
         x = np.ascontiguousarray(x, dtype=np.int32)
