@@ -132,6 +132,7 @@ cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t*
                               const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
                               const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
                               SplitPart* parts /* n_nodes * split_scan_slices() scratch */, ytk_split* out,
+                              ytk_split* mirror /* nullable: a second copy of the records (pinned host memory) */,
                               cudaStream_t st);
 int split_scan_slices(int32_t f_from, int32_t f_to);
 

@@ -731,8 +731,10 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
 }
 
 // folds the slices of every node (increasing feature ids: strict > = smallest fid wins ties)
+// (mirror: the finished record is also stored there -- pinned host memory on one GPU, so that the host
+// reads it without a copy while device-side consumers keep reading `outs`)
 __global__ void split_merge_k(const SplitPart* __restrict__ parts, int n_nodes, int n_slices,
-                              ytk_split* __restrict__ outs) {
+                              ytk_split* __restrict__ outs, ytk_split* __restrict__ mirror) {
     pdl_sync();
     int node = blockIdx.x * blockDim.x + threadIdx.x;
     if (node >= n_nodes) return;
@@ -741,7 +743,10 @@ __global__ void split_merge_k(const SplitPart* __restrict__ parts, int n_nodes, 
         SplitPart p = parts[(size_t)node * n_slices + s];
         if (p.fid >= 0 && p.lc > best.lc) best = p;
     }
-    outs[node].loss_chg = best.lc; outs[node].fid = best.fid; outs[node].lo = best.lo; outs[node].hi = best.hi;
+    ytk_split r = outs[node];            // totals, root gain and node value were written by the scan
+    r.loss_chg = best.lc; r.fid = best.fid; r.lo = best.lo; r.hi = best.hi;
+    outs[node] = r;
+    if (mirror) mirror[node] = r;
 }
 
 // ------------------------------------------------------------------------------------
@@ -1091,7 +1096,7 @@ int split_scan_slices(int32_t f_from, int32_t f_to) {
 cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t* start, const int64_t* feat_off,
                               const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
                               const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
-                              SplitPart* parts, ytk_split* out, cudaStream_t st) {
+                              SplitPart* parts, ytk_split* out, ytk_split* mirror, cudaStream_t st) {
     if (n_nodes <= 0) return cudaSuccess;
     const int slices = split_scan_slices(f_from, f_to);
     dim3 grid((unsigned)n_nodes, (unsigned)slices);
@@ -1099,7 +1104,7 @@ cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t*
                                  f_to, first_fea, scale, gp, cnt_global, parts, out);
     if (e != cudaSuccess) return e;
     return launch_chain(split_merge_k, dim3((n_nodes + 127) / 128), dim3(128), 0, st, (const SplitPart*)parts, n_nodes, slices,
-                        out);
+                        out, mirror);
 }
 
 // Single-pass variant used inside make(): one kernel reads every row id once, gathers its slot,
@@ -1352,7 +1357,11 @@ plan_next_partition_k(const SplitSeg* __restrict__ cur_segs, const PartitionCoun
             // not split: marked; split but without rows on this GPU: counted here, no tile will
             if (!split) next_counts[s] = {-1, -1};
             else if (sg.ntiles == 0) next_counts[s] = {0, 0};
-            for (int t = 0; t < sg.ntiles; t++) out_tile_seg[sg.tile0 + t] = s;
+        }
+        // tile -> slot table: the lanes of a warp fill the tiles of the warp's 32 slots, one slot after the other
+        for (int j = 0; j < 32; j++) {
+            const int t0 = __shfl_sync(0xffffffffu, sg.tile0, j), nt = __shfl_sync(0xffffffffu, sg.ntiles, j);
+            for (int t = lane; t < nt; t += 32) out_tile_seg[t0 + t] = s0 + warp * 32 + j;
         }
         __syncthreads();
         if (threadIdx.x == 0) s_carry += total;

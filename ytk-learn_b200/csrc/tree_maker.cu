@@ -802,11 +802,11 @@ int search_enqueue(ytk_gbdt* h, const ytk::ScanNode* d_nodes, int m, int first_o
     CK(h->t_split_local.reserve(m));
     CK(h->t_parts.reserve((size_t)m * ytk::split_scan_slices(h->f_from, h->f_to)));
     CK(h->h_split.reserve((size_t)m * h->world));
-    // one GPU: the records are written straight into pinned host memory (nothing on the device reads
-    // them back); several GPUs: into device memory for the allgather
-    ytk_split* rec_out = h->world == 1 ? h->h_split.h : h->t_split_local.d;
+    // the records stay in device memory (the planner of the next partition and the exchange read them
+    // there); on one GPU the merge kernel also stores them in pinned host memory, so the host needs no copy
     CK(ytk::launch_split_scan(d_nodes, m, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to,
-                              first_owned, h->d_scale, gain_params(h->p), cnt_global, h->t_parts.d, rec_out, h->st));
+                              first_owned, h->d_scale, gain_params(h->p), cnt_global, h->t_parts.d, h->t_split_local.d,
+                              h->world == 1 ? h->h_split.h : nullptr, h->st));
     h->launches += 2;
     if (h->world > 1) {
         // "split allgather": every rank's record for each node, merged on the host with the
@@ -1543,7 +1543,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             RET(next_partition_epoch(h, (size_t)std::max<long long>(1, grid_bound)));
             CK(cudaEventRecord(h->ev_level, h->st));
             CK(ytk::launch_partition_planned_root(h->d_bins_col, h->S8, h->N, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1],
-                                                  root.b, root.e, root.buf, h->world > 1 ? h->t_split_all.d : h->h_split.h,
+                                                  root.b, root.e, root.buf, h->world > 1 ? h->t_split_all.d : h->t_split_local.d,
                                                   p.min_split_loss, h->t_spec_segs[0].d, h->t_spec_tiles.d,
                                                   h->d_spec_ntiles, (int)grid_bound, h->d_tile_state, h->d_ticket + 1,
                                                   h->part_epoch, h->t_spec_counts[0].d, h->st, sparse_rows(h)));
@@ -1939,7 +1939,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
             CK(cudaEventRecord(h->ev_level, h->st));
             CK(ytk::launch_partition_planned(h->d_bins_col, h->S8, h->N, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1],
                                              d_cur_segs, d_cl, d_cg, blob_ptr<ytk::SpecJob>(h, o_spec), m,
-                                             h->world > 1 ? h->t_split_all.d : h->h_split.h, p.min_split_loss, h->t_spec_segs[np].d, h->t_spec_tiles.d, h->d_spec_ntiles,
+                                             h->world > 1 ? h->t_split_all.d : h->t_split_local.d, p.min_split_loss, h->t_spec_segs[np].d, h->t_spec_tiles.d, h->d_spec_ntiles,
                                              (int)grid_bound, h->d_tile_state, h->d_ticket + 1, h->part_epoch,
                                              h->t_spec_counts[np].d, h->st, sparse_rows(h)));
             if (h->world > 1) {   // allreduceArray(long[2], SUM) (:538) of the planned partition's counts
@@ -2358,7 +2358,7 @@ int ytk_gbdt_find_split(ytk_gbdt* h, const double* hist, int64_t sample_cnt, con
     CK(h->h_split.reserve(1));
     CK(h->t_parts.reserve((size_t)ytk::split_scan_slices(0, h->F)));
     CK(ytk::launch_split_scan(h->t_scan.d, 1, h->d_start, h->d_off_flat, h->d_fea_sel, 0, h->F, first,
-                              h->d_scale_hook, gain_params(h->p), nullptr, h->t_parts.d, h->t_split_local.d, h->st));
+                              h->d_scale_hook, gain_params(h->p), nullptr, h->t_parts.d, h->t_split_local.d, nullptr, h->st));
     CK(cudaMemcpyAsync(h->h_split.h, h->t_split_local.d, sizeof(ytk_split), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
     *out = h->h_split.h[0];
