@@ -74,7 +74,7 @@ struct PosItem { long long begin, end; int buf; int nid; };
 struct LeafItem { long long begin, end; int buf; float value; };      // rows of one leaf and its value
 struct TreeNodeDev { int left, right, fid; float info; };             // device copy of a tree for row walks
 
-// ---- launchers (kernels.cu); all asynchronous on `st`, return cudaGetLastError() ----
+// ---- launchers (rows.cu, hist.cu, split.cu, partition.cu); all asynchronous on `st`, return cudaGetLastError() ----
 
 // both also write the feature-major copy col[f * col_stride + row] the partition gathers from
 // (`wide.data` is passed already advanced to the chunk's first row, like `bins` and `col`)
@@ -190,7 +190,7 @@ cudaError_t launch_fill_i32(int32_t* p, int64_t n, int32_t v, cudaStream_t st);
 cudaError_t launch_zero_segments(long long* const* dst, int n, int64_t len, cudaStream_t st);
 cudaError_t launch_copy_segments(const long long* src, long long* const* dst, int n, int64_t len, cudaStream_t st);
 
-// ---- collectives over NVLink peer memory (kernels.cu, last section) ----
+// ---- collectives over NVLink peer memory (peer.cu) ----
 constexpr int kMaxPeers = 64;
 constexpr int kPeerFlagSets = 4;                   // counts, histogram staging, split records, leaf sums
 constexpr size_t kPeerFlagBytes = kPeerFlagSets * kMaxPeers * 8;

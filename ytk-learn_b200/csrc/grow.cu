@@ -1,6 +1,6 @@
 // ytk_gbdt_make_tree: the control flow of DataParallelTreeMaker.make
 // (J/optimizer/gbdt/DataParallelTreeMaker.java:229-295) -- expansion queue, stop rules, smaller-child /
-// subtraction trick, HistogramPool policy -- driving the kernels of kernels.cu in batches.
+// subtraction trick, HistogramPool policy -- driving the kernels (hist.cu, split.cu, partition.cu) in batches.
 // J/ = /root/reference/src/main/java/com/fenbi/ytklearn/.
 #include "host.cuh"
 
@@ -113,6 +113,16 @@ private:
     int planned_slots = 0;
 
     // ---- small helpers -----------------------------------------------------------------
+    // The host wait of a batch: polled from user space (the wake-up through cudaEventSynchronize costs
+    // several microseconds more, once per level)
+    int wait_event(cudaEvent_t ev) {
+        if (!h->spin_wait) { CK(cudaEventSynchronize(ev)); return YTK_OK; }
+        for (;;) {
+            cudaError_t e = cudaEventQuery(ev);
+            if (e == cudaSuccess) return YTK_OK;
+            if (e != cudaErrorNotReady) CK(e);
+        }
+    }
     int new_handle() {
         iv.emplace_back(); ns.emplace_back(); exps.emplace_back(); nid_of.push_back(-1);
         return (int)iv.size() - 1;
@@ -277,7 +287,7 @@ private:
                                                   h->d_tile_state, h->d_ticket + 1, h->part_epoch, h->t_spec_counts[0].d,
                                                   h->st, sparse_rows(h)));
             RET(finish_planned(0, 1));
-            CK(cudaEventSynchronize(h->ev_level));
+            RET(wait_event(h->ev_level));
         } else {
             CK(cudaStreamSynchronize(h->st));
         }
@@ -446,7 +456,7 @@ private:
         if (b.plan_now) {
             RET(plan_next_level(b));             // everything the host waits for is in front of its event
             b.tr.t_queued = now_ms();
-            CK(cudaEventSynchronize(h->ev_level));   // the one host wait of the batch
+            RET(wait_event(h->ev_level));   // the one host wait of the batch
         } else {
             b.tr.t_queued = now_ms();
             CK(cudaStreamSynchronize(h->st));        // the one host wait of the batch

@@ -1,0 +1,485 @@
+// Histograms: gradient fixed point, the per-node (g,h) histogram kernels, subtraction.
+// Part of the CUDA side of libytkgbdt.so (sm_100a).  Nothing here is a dense contraction: the work is
+// HBM-/shared-memory-bound byte and integer traffic, so there are no tensor cores; what matters is
+// sector-aligned row reads, conflict-free shared-memory atomics and grids sized to the 148 SMs.
+// Reference semantics restated by each kernel are cited as J/... =
+// /root/reference/src/main/java/com/fenbi/ytklearn/...
+#include "common.cuh"
+#include "device_util.cuh"
+
+#include <math_constants.h>
+
+#include <algorithm>
+#include <cstdlib>
+
+namespace ytk {
+
+// ------------------------------------------------------------------------------------
+// Gradient fixed point.  The reference adds float (g,h) into double bins
+// (J/data/gbdt/HistogramBuilder.java:87-88).  Shared memory only has native 32-bit
+// integer atomics (a float or 64-bit atomicAdd is a CAS loop, measured 2.9x slower:
+// profiles/r01_microbench_smem.txt), so each tree's gradients are scaled by a power of
+// two chosen from max|g| (resp. max|h|) to signed integers below 2^bits and every sum
+// downstream is an exact 64-bit integer: histograms do not depend on row order, sharding
+// or pool hits, and parent - child equals the sibling bit for bit.  Per-row rounding is
+// at most 2^-(bits+1) of max|g| (bits = 30 by default).
+// A non-zero value never rounds to zero, so "bin has samples" (hasSample,
+// J/optimizer/gbdt/DataParallelTreeMaker.java:657-663) is preserved exactly.
+// ------------------------------------------------------------------------------------
+__global__ void grad_absmax_k(const float* __restrict__ gp, int64_t n, int32_t K, int32_t gid,
+                              unsigned* __restrict__ absmax_bits) {
+    float mg = 0.f, mh = 0.f;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        float2 v = *reinterpret_cast<const float2*>(gp + (i * K + gid) * 2);
+        mg = fmaxf(mg, fabsf(v.x));
+        mh = fmaxf(mh, fabsf(v.y));
+    }
+    for (int d = 16; d > 0; d >>= 1) {
+        mg = fmaxf(mg, __shfl_xor_sync(0xffffffffu, mg, d));
+        mh = fmaxf(mh, __shfl_xor_sync(0xffffffffu, mh, d));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMax(absmax_bits, __float_as_uint(mg));
+        atomicMax(absmax_bits + 1, __float_as_uint(mh));
+    }
+}
+
+__device__ __forceinline__ int scale_exponent(float mx, int bits) {
+    if (!(mx > 0.f)) return 0;
+    int e;
+    frexpf(mx, &e);          // mx = m * 2^e, m in [0.5,1)  =>  mx * 2^(bits-e) < 2^bits
+    return bits - e;
+}
+
+__device__ __forceinline__ int32_t to_fixed(float v, double mul) {
+    long long q = __double2ll_rn((double)v * mul);
+    if (q == 0 && v != 0.f) q = v > 0.f ? 1 : -1;
+    return (int32_t)q;
+}
+
+__global__ void grad_quantize_k(const float* __restrict__ gp, int64_t n, int32_t K, int32_t gid,
+                                int2* __restrict__ gq, const unsigned* __restrict__ absmax_bits,
+                                GradScale* __restrict__ scale, int bits) {
+    int kg = scale_exponent(__uint_as_float(absmax_bits[0]), bits);
+    int kh = scale_exponent(__uint_as_float(absmax_bits[1]), bits);
+    double mg = ldexp(1.0, kg), mh = ldexp(1.0, kh);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        scale->mul_g = mg; scale->mul_h = mh;
+        scale->inv_g = ldexp(1.0, -kg); scale->inv_h = ldexp(1.0, -kh);
+    }
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        float2 v = *reinterpret_cast<const float2*>(gp + (i * K + gid) * 2);
+        gq[i] = make_int2(to_fixed(v.x, mg), to_fixed(v.y, mh));
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// K2: per-node (g,h) histogram -- HistogramBuilder.buildHist's accumulation loop
+//     (J/data/gbdt/HistogramBuilder.java:69-90).
+//
+// What bounds this kernel on B200 is not HBM but the shared-memory atomic pipe
+// (profiles/r01_microbench_smem.txt), so it is built to issue little else:
+//   * rows are uint8, row-major, one 32 B sector per 32-feature group, so a row reached
+//     through the row-id list costs exactly one sector; a warp fetches 32 rows with two
+//     128-bit loads, adjacent lanes taking the two 16-feature halves of a row, plus that
+//     row's fixed-point (g,h) -- no staging, no per-row broadcast;
+//   * lane L works on row L>>1 and half L&1: at step k (0..15) it updates feature
+//     16*(L&1) + (k ^ (L>>1)).  The 32 lanes therefore always touch 32 different
+//     features, and the shared histogram is laid out
+//     [bin][component][feature], i.e. bank = feature: the 32 atomics of a warp
+//     instruction hit 32 different banks whatever the bins are (skewed or binary
+//     features cannot serialise it); the address is one PRMT (bin*256 from the data
+//     word) and one LOP3 ((bin256 | lane*4) ^ k*4);
+//   * exact 64-bit sums WITHOUT carries: each fixed-point value (|v| < 2^30) is split into
+//     its low 16 bits (unsigned) and its high part (signed, |.| <= 2^14), and the two
+//     limbs are accumulated in separate 32-bit words by fire-and-forget atomics
+//     (RED).  A work item covers at most 65536 rows, so neither limb sum can leave 32
+//     bits; the flush recombines hi*65536 + lo in 64-bit.  Detecting carries of a single
+//     64-bit accumulator instead costs more than the atomics themselves (7.5 vs 4.6
+//     SM-cycles per row, same file).
+// One CTA (32 warps, 128 KB of shared memory, 1 per SM) handles one work item: a run of
+// rows of one node and one feature group; it flushes non-empty bins with 64-bit global
+// reductions into that node's histogram.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kHistThreads, 1)
+hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict__ gq,
+             const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1,
+             const RowItem* __restrict__ items, int32_t F, const uint32_t* __restrict__ group_mask,
+             const int32_t* __restrict__ nbins, const int32_t* __restrict__ feat_owner,
+             const int64_t* __restrict__ feat_inner, long long owner_stride,
+             long long* const* __restrict__ seg_out, const PartitionCounts* __restrict__ cnt_local,
+             const PartitionCounts* __restrict__ cnt_global) {
+    pdl_sync();
+    // g limbs [bin][{lo,hi}][feature] (64 KB), then the h limbs in the same layout (64 KB)
+    extern __shared__ __align__(128) uint32_t sh[];
+    constexpr uint32_t kHOff = kMaxBins * 2 * kGroup * 4;        // bytes
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int fg = blockIdx.y;
+    const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
+    if (it.begin >= it.end) return;          // a deferred chunk beyond the end of its child
+    const int32_t* __restrict__ ridx = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
+
+    {
+        uint4* z = reinterpret_cast<uint4*>(sh);
+        for (int i = tid; i < kMaxBins * 4 * kGroup / 4; i += kHistThreads) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncthreads();
+
+    const uint32_t gmask = group_mask[fg];
+    // Lane L works on row (L >> 1) of a 16-row block and on the 16 features of half (L & 1) of the
+    // group: at step k (0..15) it updates feature 16*(L&1) + (k ^ (L>>1)).  The 32 lanes of a warp
+    // instruction therefore always touch 32 different features = 32 different banks.
+    const int half = lane & 1, r16 = lane >> 1;
+    const int m = r16 >> 2, bsel = r16 & 3;
+    // PRMT selectors: byte (kk ^ bsel) of a data word moved to byte 1, i.e. bin * 256 = the byte
+    // offset of that bin's 256 B row of limbs
+    uint32_t selk[4];
+#pragma unroll
+    for (int kk = 0; kk < 4; kk++) selk[kk] = 0x4404u | ((uint32_t)(kk ^ bsel) << 4);
+    // byte offset of feature 16*half + r16 inside a bin row; feature 16*half + (k ^ r16) is reached
+    // by XOR-ing k*4 into it: (bin256 | lane_off) ^ k4 is one LOP3
+    uint32_t lane_off = (uint32_t)(half * 16 + r16) << 2;
+    asm volatile("" : "+r"(lane_off));
+    const uint8_t* __restrict__ gbase = bins + fg * kGroup + (half << 4);
+    char* const shb = reinterpret_cast<char*>(sh);
+
+    // Three-stage software pipeline per warp: row ids of block t+2, row data of block t+1 and the
+    // atomics of block t are in flight together, so no load waits on another load of the same
+    // iteration (loads share the LSU queue with thousands of cycles of queued atomics).
+    // A block is 32 rows = two 128-bit loads: adjacent lanes fetch the two halves of a row, so every
+    // 32 B sector is requested once; for contiguous rows the warp reads 1 KB in 8 fully used lines.
+    struct Fetch { uint4 a, b; int2 qa, qb; };
+    auto fetch_rid = [&](long long base) -> int32_t {
+        const long long i = base + lane;
+        return i < it.end ? (ridx ? ridx[i] : (int32_t)i) : -1;
+    };
+    auto fetch = [&](int32_t rid, Fetch& f) {
+        const int32_t ra = __shfl_sync(0xffffffffu, rid, r16);
+        const int32_t rb = __shfl_sync(0xffffffffu, rid, 16 + r16);
+        // past the end of the run: zeros, i.e. "add zero to bin 0", which changes nothing
+        f.a = make_uint4(0, 0, 0, 0); f.b = f.a;
+        f.qa = make_int2(0, 0); f.qb = f.qa;
+        if (ra >= 0) { f.a = *reinterpret_cast<const uint4*>(gbase + (long long)ra * S8); f.qa = gq[ra]; }
+        if (rb >= 0) { f.b = *reinterpret_cast<const uint4*>(gbase + (long long)rb * S8); f.qb = gq[rb]; }
+    };
+
+    // 16 steps on one 16-row half block.  Register j must hold data word j ^ m (m = r16 >> 2), the
+    // word with the features this lane visits at steps 4j..4j+3: two conditional swaps.
+    // Unsampled features and padding lanes are accumulated too (the instruction is issued for the
+    // whole warp anyway) and dropped at flush time.
+    auto accumulate16 = [&](const uint4 d, const int2 q) {
+        uint32_t w[4] = {d.x, d.y, d.z, d.w};
+        {
+            const bool c0 = m & 1, c1 = m & 2;
+            uint32_t t;
+            t = c0 ? w[1] : w[0]; w[1] = c0 ? w[0] : w[1]; w[0] = t;
+            t = c0 ? w[3] : w[2]; w[3] = c0 ? w[2] : w[3]; w[2] = t;
+            t = c1 ? w[2] : w[0]; w[2] = c1 ? w[0] : w[2]; w[0] = t;
+            t = c1 ? w[3] : w[1]; w[3] = c1 ? w[1] : w[3]; w[1] = t;
+        }
+        const uint32_t g_lo = (uint32_t)q.x & 0xffffu, h_lo = (uint32_t)q.y & 0xffffu;
+        const int32_t g_hi = q.x >> 16, h_hi = q.y >> 16;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint32_t word = w[j];
+#pragma unroll
+            for (int kk = 0; kk < 4; kk++) {
+                const uint32_t off = (__byte_perm(word, 0u, selk[kk]) | lane_off) ^ (uint32_t)((4 * j + kk) << 2);
+                uint32_t* p = reinterpret_cast<uint32_t*>(shb + off);
+                atomicAdd(p, g_lo);
+                atomicAdd(reinterpret_cast<int32_t*>(p + kGroup), g_hi);
+                atomicAdd(p + kHOff / 4, h_lo);
+                atomicAdd(reinterpret_cast<int32_t*>(p + kHOff / 4 + kGroup), h_hi);
+            }
+        }
+    };
+
+    // (two register sets in explicit ping-pong: a copy `cur = nxt` would be scheduled right behind
+    // the loads and stall the warp on them)
+    long long base = it.begin + warp * 32;
+    Fetch fa, fb;
+    int32_t r1 = fetch_rid(base + kHistThreads);
+    fetch(fetch_rid(base), fa);
+    while (base < it.end) {
+        const int32_t r2 = fetch_rid(base + 2 * kHistThreads);
+        fetch(r1, fb);
+        accumulate16(fa.a, fa.qa);
+        accumulate16(fa.b, fa.qb);
+        base += kHistThreads;
+        if (base >= it.end) break;
+        r1 = fetch_rid(base + 2 * kHistThreads);
+        fetch(r2, fa);
+        accumulate16(fb.a, fb.qa);
+        accumulate16(fb.b, fb.qb);
+        base += kHistThreads;
+    }
+    __syncthreads();
+
+    // flush: recombine the limbs, one 64-bit global reduction per non-empty (feature, bin, component)
+    long long* __restrict__ out = seg_out[it.seg];
+    for (int i = tid; i < kMaxBins * kGroup; i += kHistThreads) {
+        int bin = i >> 5, ln = i & 31;
+        int ff = fg * kGroup + ln;
+        if (ff >= F || !((gmask >> ln) & 1u) || bin >= nbins[ff]) continue;
+        const uint32_t* pg = sh + bin * (2 * kGroup) + ln;
+        const uint32_t* ph = pg + kHOff / 4;
+        long long g = (long long)(int32_t)pg[kGroup] * 65536ll + (long long)pg[0];
+        long long h = (long long)(int32_t)ph[kGroup] * 65536ll + (long long)ph[0];
+        long long* dst = out + feat_owner[ff] * owner_stride + feat_inner[ff] + 2 * bin;
+        if (g != 0) atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)g);
+        if (h != 0) atomicAdd(reinterpret_cast<unsigned long long*>(dst + 1), (unsigned long long)h);
+    }
+}
+
+// ------------------------------------------------------------------------------------
+// Sparse rows (BASELINE config 4: 10 000 features at ~1 % density).  The reference's matrix is dense
+// (J/dataflow/GBDTCoreData.java:164-168) and cannot hold that shape; here the rows are CSR, an
+// absent feature has its default slot, and the histogram is what the dense path would produce.
+// ------------------------------------------------------------------------------------
+// One CTA per work item (same items as hist_build_k), one warp per row at a time, lanes over the
+// row's stored entries.  Thousands of bins per node: global 64-bit reductions, little contention.
+__global__ void __launch_bounds__(256)
+hist_csr_k(SparseRows sp, const uint8_t* __restrict__ fea_selected, const int2* __restrict__ gq,
+           const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1, const RowItem* __restrict__ items,
+           const int32_t* __restrict__ feat_owner, const int64_t* __restrict__ feat_inner, long long owner_stride,
+           long long* const* __restrict__ seg_out, long long* __restrict__ tot,
+           const PartitionCounts* __restrict__ cnt_local, const PartitionCounts* __restrict__ cnt_global) {
+    pdl_sync();
+    const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
+    const int32_t* __restrict__ rows = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
+    long long* const base = seg_out[it.seg];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    long long tg = 0, th = 0;
+    // a warp walks its rows one after the other; the next row's id, extent and (g,h) are fetched while
+    // the current row's entries are being added, so the dependent loads of a row overlap the previous row
+    long long i = it.begin + warp;
+    int32_t rid = 0;
+    long long p0 = 0, p1 = 0;
+    int2 q = make_int2(0, 0);
+    if (i < it.end) {
+        rid = rows ? rows[i] : (int32_t)i;
+        p0 = sp.row_ptr[rid]; p1 = sp.row_ptr[rid + 1];
+        q = gq[rid];
+    }
+    while (i < it.end) {
+        const long long ni = i + nwarps;
+        int32_t nrid = 0;
+        long long np0 = 0, np1 = 0;
+        int2 nq = make_int2(0, 0);
+        if (ni < it.end) {
+            nrid = rows ? rows[ni] : (int32_t)ni;
+            np0 = sp.row_ptr[nrid]; np1 = sp.row_ptr[nrid + 1];
+            nq = gq[nrid];
+        }
+        tg += q.x; th += q.y;
+        for (long long p = p0 + lane; p < p1; p += 32) {
+            const unsigned e = sp.nz[p];
+            const int f = (int)(e >> 16), slot = (int)(e & 0xffffu);
+            if (fea_selected[f]) {
+                unsigned long long* out = reinterpret_cast<unsigned long long*>(base + feat_owner[f] * owner_stride + feat_inner[f]) + 2 * slot;
+                atomicAdd(out, (unsigned long long)(long long)q.x);
+                atomicAdd(out + 1, (unsigned long long)(long long)q.y);
+            }
+        }
+        i = ni; rid = nrid; p0 = np0; p1 = np1; q = nq;
+    }
+    if (lane == 0 && (tg | th) != 0) {
+        atomicAdd(reinterpret_cast<unsigned long long*>(tot + 2 * it.seg), (unsigned long long)tg);
+        atomicAdd(reinterpret_cast<unsigned long long*>(tot + 2 * it.seg + 1), (unsigned long long)th);
+    }
+}
+
+// "Fill-value bin by subtraction": per node and selected feature, default slot += node totals - (sum of
+// what the stored entries put into the feature's bins).  Exact (integers); linear, so with several
+// GPUs it is applied to the local sums before the reduce-scatter.  grid (feature blocks, nodes), one
+// warp per feature.
+__global__ void __launch_bounds__(256)
+csr_default_fix_k(SparseRows sp, const uint8_t* __restrict__ fea_selected, int32_t F, const int32_t* __restrict__ start,
+                  const int32_t* __restrict__ feat_owner, const int64_t* __restrict__ feat_inner, long long owner_stride,
+                  long long* const* __restrict__ seg_out, const long long* __restrict__ tot) {
+    pdl_sync();
+    const int lane = threadIdx.x & 31;
+    const int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (f >= F || !fea_selected[f]) return;
+    const int seg = blockIdx.y;
+    long long* hp = seg_out[seg] + feat_owner[f] * owner_stride + feat_inner[f];
+    const int nb = start[f + 1] - start[f];
+    long long g = 0, h = 0;
+    for (int j = lane; j < nb; j += 32) {
+        const longlong2 v = *reinterpret_cast<const longlong2*>(hp + 2 * j);
+        g += v.x; h += v.y;
+    }
+    for (int d = 16; d > 0; d >>= 1) {
+        g += __shfl_xor_sync(0xffffffffu, g, d);
+        h += __shfl_xor_sync(0xffffffffu, h, d);
+    }
+    if (lane == 0) {
+        const int dslot = sp.default_slot[f];
+        hp[2 * dslot] += tot[2 * seg] - g;
+        hp[2 * dslot + 1] += tot[2 * seg + 1] - h;
+    }
+}
+
+// Features with more than 256 slots ("wide", e.g. un-sampled continuous columns) do not fit the
+// shared-memory layout above; their (g,h) go straight into the node's histogram with 64-bit global
+// reductions -- thousands of bins, so little contention.  Same work items as hist_build_k; one
+// CTA per (item, wide feature).
+__global__ void __launch_bounds__(256)
+hist_wide_k(WideCols wide, const int32_t* __restrict__ wide_fids, const int2* __restrict__ gq,
+            const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1,
+            const RowItem* __restrict__ items, const int32_t* __restrict__ feat_owner,
+            const int64_t* __restrict__ feat_inner, long long owner_stride, long long* const* __restrict__ seg_out,
+            const PartitionCounts* __restrict__ cnt_local, const PartitionCounts* __restrict__ cnt_global) {
+    pdl_sync();
+    const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
+    const int f = wide_fids[blockIdx.y];
+    const uint16_t* __restrict__ colp = wide.data + (long long)wide.index[f] * wide.stride;
+    const int32_t* __restrict__ rows = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
+    unsigned long long* out = reinterpret_cast<unsigned long long*>(seg_out[it.seg] + feat_owner[f] * owner_stride + feat_inner[f]);
+    for (long long i = it.begin + threadIdx.x; i < it.end; i += blockDim.x) {
+        const int32_t rid = rows ? rows[i] : (int32_t)i;
+        const int2 q = gq[rid];
+        const int slot = colp[rid];
+        atomicAdd(out + 2 * slot, (unsigned long long)(long long)q.x);
+        atomicAdd(out + 2 * slot + 1, (unsigned long long)(long long)q.y);
+    }
+}
+
+// K3: sibling = parent - smaller child (HistogramBuilder.substract,
+//     J/data/gbdt/HistogramBuilder.java:101-107), exact in the integer domain.
+__global__ void hist_subtract_k(const SubItem* __restrict__ items, int64_t len) {
+    pdl_sync();
+    const SubItem it = items[blockIdx.y];
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
+         i += (int64_t)gridDim.x * blockDim.x)
+        it.out[i] = it.parent[i] - it.small[i];
+}
+
+__global__ void hist_to_double_k(const long long* __restrict__ hist, int64_t len,
+                                 const GradScale* __restrict__ scale, double* __restrict__ out) {
+    double ig = scale->inv_g, ih = scale->inv_h;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
+         i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = (double)hist[i] * ((i & 1) ? ih : ig);
+}
+
+__global__ void hist_from_double_k(const double* __restrict__ in, int64_t len,
+                                   const GradScale* __restrict__ scale, long long* __restrict__ hist) {
+    double mg = scale->mul_g, mh = scale->mul_h;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
+         i += (int64_t)gridDim.x * blockDim.x)
+        hist[i] = __double2ll_rn(in[i] * ((i & 1) ? mh : mg));
+}
+
+__global__ void zero_segments_k(long long* const* __restrict__ dst, int64_t len) {
+    pdl_sync();
+    long long* d = dst[blockIdx.y];
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
+         i += (int64_t)gridDim.x * blockDim.x)
+        d[i] = 0;
+}
+
+__global__ void copy_segments_k(const long long* __restrict__ src, long long* const* __restrict__ dst, int64_t len) {
+    const long long* s = src + blockIdx.y * len;
+    long long* d = dst[blockIdx.y];
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
+         i += (int64_t)gridDim.x * blockDim.x)
+        d[i] = s[i];
+}
+
+cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t gid, int2* gq,
+                                 unsigned* absmax_bits, GradScale* scale, int bits, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(absmax_bits, 0, 2 * sizeof(unsigned), st);
+    if (e != cudaSuccess) return e;
+    int g = grid_for(n, 256, kNumSMs * 8);
+    grad_absmax_k<<<g, 256, 0, st>>>(gp, n, K, gid, absmax_bits);
+    grad_quantize_k<<<g, 256, 0, st>>>(gp, n, K, gid, gq, absmax_bits, scale, bits);
+    return cudaGetLastError();
+}
+
+int64_t hist_rows_per_item(int64_t total_rows, int groups) {
+    // one CTA per SM (128 KB of shared memory); aim at about two waves over all feature groups,
+    // never less than 4 sweeps of the CTA (4096 rows) per item so zeroing + flushing stays small
+    int64_t items = std::max<int64_t>(1, (2 * kNumSMs) / std::max(1, groups));
+    int64_t rows = (total_rows + items - 1) / items;
+    rows = std::max<int64_t>(rows, 4 * kHistThreads);
+    rows = (rows + kHistThreads - 1) / kHistThreads * kHistThreads;
+    return std::min<int64_t>(rows, kHistMaxRowsPerItem);    // the 16-bit limb sums must stay inside 32 bits
+}
+
+cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx0,
+                              const int32_t* rowidx1, const RowItem* items, int n_items, int32_t F,
+                              const uint32_t* group_mask, const int32_t* nbins, const int32_t* feat_owner,
+                              const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
+                              const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st) {
+    if (n_items <= 0) return cudaSuccess;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(hist_build_k, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             kHistSmemBytes);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    dim3 grid((unsigned)n_items, (unsigned)(S8 / kGroup));
+    return launch_chain(hist_build_k, grid, dim3(kHistThreads), kHistSmemBytes, st, bins, S8, gq, rowidx0, rowidx1, items, F, group_mask,
+                                                             nbins, feat_owner, feat_inner, owner_stride, seg_out,
+                                                             cnt_local, cnt_global);
+}
+
+cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide, const int2* gq, const int32_t* rowidx0,
+                             const int32_t* rowidx1, const RowItem* items, int n_items, const int32_t* feat_owner,
+                             const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
+                             const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st) {
+    if (n_items <= 0 || n_wide <= 0) return cudaSuccess;
+    dim3 grid((unsigned)n_items, (unsigned)n_wide);
+    return launch_chain(hist_wide_k, grid, dim3(256), 0, st, wide, wide_fids, gq, rowidx0, rowidx1, items, feat_owner, feat_inner, owner_stride,
+                                      seg_out, cnt_local, cnt_global);
+}
+
+cudaError_t launch_hist_csr(SparseRows sparse, const uint8_t* fea_selected, const int2* gq, const int32_t* rowidx0,
+                            const int32_t* rowidx1, const RowItem* items, int n_items, const int32_t* feat_owner,
+                            const int64_t* feat_inner, long long owner_stride, long long* const* seg_out, long long* tot,
+                            const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st) {
+    if (n_items <= 0) return cudaSuccess;
+    return launch_chain(hist_csr_k, dim3(n_items), dim3(256), 0, st, sparse, fea_selected, gq, rowidx0, rowidx1, items,
+                        feat_owner, feat_inner, owner_stride, seg_out, tot, cnt_local, cnt_global);
+}
+cudaError_t launch_csr_default_fix(SparseRows sparse, const uint8_t* fea_selected, int32_t F, const int32_t* start,
+                                   const int32_t* feat_owner, const int64_t* feat_inner, long long owner_stride,
+                                   long long* const* seg_out, int n_segs, const long long* tot, cudaStream_t st) {
+    if (n_segs <= 0) return cudaSuccess;
+    dim3 grid((unsigned)((F + 7) / 8), (unsigned)n_segs);
+    return launch_chain(csr_default_fix_k, grid, dim3(256), 0, st, sparse, fea_selected, F, start, feat_owner, feat_inner,
+                        owner_stride, seg_out, tot);
+}
+
+cudaError_t launch_hist_subtract(const SubItem* items, int n_items, int64_t len, cudaStream_t st) {
+    if (n_items <= 0) return cudaSuccess;
+    dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n_items);
+    return launch_chain(hist_subtract_k, grid, dim3(256), 0, st, items, len);
+}
+cudaError_t launch_hist_to_double(const long long* hist, int64_t len, const GradScale* scale, double* out,
+                                  cudaStream_t st) {
+    hist_to_double_k<<<grid_for(len, 256), 256, 0, st>>>(hist, len, scale, out);
+    return cudaGetLastError();
+}
+cudaError_t launch_hist_from_double(const double* in, int64_t len, const GradScale* scale, long long* hist,
+                                    cudaStream_t st) {
+    hist_from_double_k<<<grid_for(len, 256), 256, 0, st>>>(in, len, scale, hist);
+    return cudaGetLastError();
+}
+cudaError_t launch_zero_segments(long long* const* dst, int n, int64_t len, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n);
+    return launch_chain(zero_segments_k, grid, dim3(256), 0, st, dst, len);
+}
+cudaError_t launch_copy_segments(const long long* src, long long* const* dst, int n, int64_t len, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n);
+    copy_segments_k<<<grid, 256, 0, st>>>(src, dst, len);
+    return cudaGetLastError();
+}
+
+}  // namespace ytk

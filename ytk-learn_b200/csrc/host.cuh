@@ -246,6 +246,7 @@ struct ytk_gbdt {
     unsigned long long part_epoch = 0;
     // level-wise growth on one GPU: the next level's partition planned and started by the device
     bool plan_ahead = true;                 // YTK_GBDT_NO_PLAN_AHEAD=1 turns it off
+    bool spin_wait = true;                  // YTK_GBDT_NO_SPIN=1: block in cudaEventSynchronize instead of polling
     bool recs_merged = false;               // the last split exchange merged the records on the device
     DevTable<ytk::SplitSeg> t_spec_segs[2];
     DevTable<ytk::PartitionCounts> t_spec_counts[2];
@@ -327,7 +328,7 @@ struct ytk_gbdt {
     char* d_blob = nullptr;  size_t blob_cap = 0;     // device side of Blob
     char* d_blob_part = nullptr;  size_t blob_part_cap = 0;     // ... of the partition tables, which go up (and start work) first
 
-    // collectives over NVLink peer memory (world > 1, one node): see kernels.cu, last section
+    // collectives over NVLink peer memory (world > 1, one node): see peer.cu
     bool peer_mode = false;
     ytk::PeerTable pt{};
     char* my_xchg = nullptr; char* my_hist = nullptr;

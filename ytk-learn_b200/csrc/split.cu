@@ -1,0 +1,225 @@
+// Best-split search over the histograms.
+// Part of the CUDA side of libytkgbdt.so (sm_100a).  Nothing here is a dense contraction: the work is
+// HBM-/shared-memory-bound byte and integer traffic, so there are no tensor cores; what matters is
+// sector-aligned row reads, conflict-free shared-memory atomics and grids sized to the 148 SMs.
+// Reference semantics restated by each kernel are cited as J/... =
+// /root/reference/src/main/java/com/fenbi/ytklearn/...
+#include "common.cuh"
+#include "device_util.cuh"
+
+#include <math_constants.h>
+
+#include <algorithm>
+#include <cstdlib>
+
+namespace ytk {
+
+// ------------------------------------------------------------------------------------
+// K4/K5: node totals, split scan and arg-max.
+//   updateTreeMakerNodeStats (J/optimizer/gbdt/DataParallelTreeMaker.java:543-573),
+//   enumerateSplit (:598-637), SplitInfo.needReplace (J/data/gbdt/SplitInfo.java:99-104),
+//   UpdateStrategy.calcGain / calcNodeValue (J/optimizer/gbdt/UpdateStrategy.java:55-100).
+// One CTA per node, one warp per feature: a segmented inclusive scan over the feature's
+// bins in exact 64-bit integers (so the prefix does not depend on scan order), gains in
+// IEEE double with explicit _rn intrinsics (never fused), loss change rounded to float
+// as the reference does.
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ double threshold_l1(double w, double lambda) {
+    if (w > lambda) return __dsub_rn(w, lambda);
+    if (w < -lambda) return __dadd_rn(w, lambda);
+    return 0.0;
+}
+
+__device__ __forceinline__ double calc_node_value(const GainParams& p, double G, double H) {
+    if (H < p.min_child_weight) return 0.0;
+    double val;
+    if (p.l1 == 0.0) val = __ddiv_rn(-G, __dadd_rn(H, p.l2));
+    else val = __ddiv_rn(-threshold_l1(G, p.l1), __dadd_rn(H, p.l2));
+    if (p.max_abs_leaf_val > 0) {
+        if (val > p.max_abs_leaf_val) val = p.max_abs_leaf_val;
+        else if (val < -p.max_abs_leaf_val) val = -p.max_abs_leaf_val;
+    }
+    return val;
+}
+
+__device__ __forceinline__ double calc_gain(const GainParams& p, double G, double H) {
+    if (H < p.min_child_weight) return 0.0;
+    if (p.max_abs_leaf_val <= 0) {
+        double t = (p.l1 == 0.0) ? G : threshold_l1(G, p.l1);
+        return __ddiv_rn(__dmul_rn(t, t), __dadd_rn(H, p.l2));
+    }
+    double v = calc_node_value(p, G, H);
+    // -2 * (G*v + 0.5*(H+l2)*v^2 + l1*|v|), evaluated left to right as Java does
+    double a = __dmul_rn(G, v);
+    double b = __dmul_rn(__dmul_rn(0.5, __dadd_rn(H, p.l2)), __dmul_rn(v, v));
+    double c = __dmul_rn(p.l1, fabs(v));
+    return __dmul_rn(-2.0, __dadd_rn(__dadd_rn(a, b), c));
+}
+
+constexpr int kScanWarps = 4;     // features per CTA; a node's features are spread over several CTAs (slices)
+
+__global__ void __launch_bounds__(kScanWarps * 32)
+split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ start,
+             const int64_t* __restrict__ feat_off, const uint8_t* __restrict__ fea_selected,
+             int32_t f_from, int32_t f_to, int32_t first_fea, const GradScale* __restrict__ scale,
+             GainParams gp, const PartitionCounts* __restrict__ cnt_global, SplitPart* __restrict__ parts,
+             ytk_split* __restrict__ outs) {
+    pdl_sync();
+    __shared__ double s_tot[2];
+    __shared__ float s_lc[kScanWarps];
+    __shared__ int s_fid[kScanWarps], s_lo[kScanWarps], s_hi[kScanWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int node = blockIdx.x, slice = blockIdx.y;
+    const double ig = scale->inv_g, ih = scale->inv_h;
+    const long long* __restrict__ hist = nodes[node].hist;
+    long long sample_cnt = nodes[node].sample_cnt;
+    if (nodes[node].cseg >= 0) {
+        const PartitionCounts g = cnt_global[nodes[node].cseg];
+        const long long small = g.left < g.right ? g.left : g.right;
+        sample_cnt = nodes[node].which == 0 ? small : (g.left + g.right - small);
+    }
+
+    if (warp == 0) {
+        double G, H;
+        if (first_fea >= 0) {
+            long long g = 0, h = 0;
+            const long long* hp = hist + feat_off[first_fea];
+            int nb = start[first_fea + 1] - start[first_fea];
+            for (int j = lane; j < nb; j += 32) {
+                longlong2 gh = *reinterpret_cast<const longlong2*>(hp + 2 * j);
+                g += gh.x; h += gh.y;
+            }
+            for (int d = 16; d > 0; d >>= 1) {
+                g += __shfl_xor_sync(0xffffffffu, g, d);
+                h += __shfl_xor_sync(0xffffffffu, h, d);
+            }
+            G = (double)g * ig; H = (double)h * ih;
+        } else {
+            G = -CUDART_INF; H = -CUDART_INF;   // no feature here: neutral for the MAX allreduce (:549)
+        }
+        if (lane == 0) { s_tot[0] = G; s_tot[1] = H; }
+    }
+    __syncthreads();
+    const double totG = s_tot[0], totH = s_tot[1];
+    const float root_gain = (float)calc_gain(gp, totG, totH);
+    // UpdateStrategy.canSplit (:50-53)
+    const bool can_split = (totH >= __dmul_rn(gp.min_child_weight, 2.0)) && (sample_cnt >= gp.min_split_samples);
+
+    float w_lc = -CUDART_INF_F;
+    int w_fid = -1, w_lo = -1, w_hi = -1;
+    const int f = f_from + slice * kScanWarps + warp;       // one feature per warp
+    if (can_split && f < f_to && fea_selected[f]) {
+        const long long* hp = hist + feat_off[f];
+        const int nb = start[f + 1] - start[f];
+        long long carryG = 0, carryH = 0;
+        int carry_last = -1;
+        float b_lc = -CUDART_INF_F;
+        int b_lo = -1, b_hi = 0x7fffffff;
+        // 256 bins at a time (one pass for a feature with uint8 slots) are fetched up front -- 8 loads
+        // in flight instead of one dependent memory round trip per 32-bin chunk
+        for (int blk = 0; blk < nb; blk += kMaxBins) {
+        longlong2 pre[kMaxBins / 32];
+#pragma unroll
+        for (int c = 0; c < kMaxBins / 32; c++) {
+            const int j = blk + c * 32 + lane;
+            pre[c] = make_longlong2(0, 0);
+            if (j < nb) pre[c] = *reinterpret_cast<const longlong2*>(hp + 2 * j);
+        }
+#pragma unroll
+        for (int c = 0; c < kMaxBins / 32; c++) {
+            const int c0 = blk + c * 32;
+            if (c0 >= nb) break;
+            int j = c0 + lane;
+            long long g = pre[c].x, h = pre[c].y;
+            bool ne = (g | h) != 0;                                   // hasSample
+            long long pg = g, ph = h;
+            for (int d = 1; d < 32; d <<= 1) {
+                long long tg = __shfl_up_sync(0xffffffffu, pg, d);
+                long long th = __shfl_up_sync(0xffffffffu, ph, d);
+                if (lane >= d) { pg += tg; ph += th; }
+            }
+            long long exG = carryG + pg - g, exH = carryH + ph - h;   // left branch before bin j
+            unsigned m = __ballot_sync(0xffffffffu, ne);
+            unsigned lower = m & ((1u << lane) - 1u);
+            int prev = lower ? (c0 + 31 - __clz(lower)) : carry_last; // lastFeaValue
+            if (ne && exH != 0) {                                      // !leftBranchGradStats.empty()
+                double lG = (double)exG * ig, lH = (double)exH * ih;
+                if (lH >= gp.min_child_weight) {
+                    double rG = __dsub_rn(totG, lG), rH = __dsub_rn(totH, lH);
+                    if (rH >= gp.min_child_weight) {
+                        float lc = (float)__dsub_rn(__dadd_rn(calc_gain(gp, lG, lH), calc_gain(gp, rG, rH)),
+                                                    (double)root_gain);
+                        if (lc > b_lc) { b_lc = lc; b_lo = prev; b_hi = j; }
+                    }
+                }
+            }
+            carryG += __shfl_sync(0xffffffffu, pg, 31);
+            carryH += __shfl_sync(0xffffffffu, ph, 31);
+            if (m) carry_last = c0 + 31 - __clz(m);
+        }
+        }
+        // first (lowest bin) maximum inside the feature
+        for (int d = 16; d > 0; d >>= 1) {
+            float o_lc = __shfl_xor_sync(0xffffffffu, b_lc, d);
+            int o_lo = __shfl_xor_sync(0xffffffffu, b_lo, d);
+            int o_hi = __shfl_xor_sync(0xffffffffu, b_hi, d);
+            if (o_lc > b_lc || (o_lc == b_lc && o_hi < b_hi)) { b_lc = o_lc; b_lo = o_lo; b_hi = o_hi; }
+        }
+        if (b_lc > w_lc) { w_lc = b_lc; w_fid = f; w_lo = b_lo; w_hi = b_hi; }
+    }
+    if (lane == 0) { s_lc[warp] = w_lc; s_fid[warp] = w_fid; s_lo[warp] = w_lo; s_hi[warp] = w_hi; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // warps hold increasing feature ids: strict > keeps the smaller fid on ties
+        SplitPart best = {-CUDART_INF_F, -1, -1, -1};
+        for (int w = 0; w < kScanWarps; w++)
+            if (s_fid[w] >= 0 && s_lc[w] > best.lc) best = {s_lc[w], s_fid[w], s_lo[w], s_hi[w]};
+        parts[(size_t)node * gridDim.y + slice] = best;
+        if (slice == 0) {
+            ytk_split* out = outs + node;
+            out->sum_grad = totG; out->sum_hess = totH;
+            out->root_gain = root_gain;
+            out->node_value = (float)calc_node_value(gp, totG, totH);
+        }
+    }
+}
+
+// folds the slices of every node (increasing feature ids: strict > = smallest fid wins ties)
+// (mirror: the finished record is also stored there -- pinned host memory on one GPU, so that the host
+// reads it without a copy while device-side consumers keep reading `outs`)
+__global__ void split_merge_k(const SplitPart* __restrict__ parts, int n_nodes, int n_slices,
+                              ytk_split* __restrict__ outs, ytk_split* __restrict__ mirror) {
+    pdl_sync();
+    int node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node >= n_nodes) return;
+    SplitPart best = {-CUDART_INF_F, -1, -1, -1};
+    for (int s = 0; s < n_slices; s++) {
+        SplitPart p = parts[(size_t)node * n_slices + s];
+        if (p.fid >= 0 && p.lc > best.lc) best = p;
+    }
+    ytk_split r = outs[node];            // totals, root gain and node value were written by the scan
+    r.loss_chg = best.lc; r.fid = best.fid; r.lo = best.lo; r.hi = best.hi;
+    outs[node] = r;
+    if (mirror) mirror[node] = r;
+}
+
+int split_scan_slices(int32_t f_from, int32_t f_to) {
+    int n = f_to - f_from;
+    return n <= 0 ? 1 : (n + kScanWarps - 1) / kScanWarps;
+}
+
+cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t* start, const int64_t* feat_off,
+                              const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
+                              const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
+                              SplitPart* parts, ytk_split* out, ytk_split* mirror, cudaStream_t st) {
+    if (n_nodes <= 0) return cudaSuccess;
+    const int slices = split_scan_slices(f_from, f_to);
+    dim3 grid((unsigned)n_nodes, (unsigned)slices);
+    cudaError_t e = launch_chain(split_scan_k, grid, dim3(kScanWarps * 32), 0, st, nodes, start, feat_off, fea_selected, f_from,
+                                 f_to, first_fea, scale, gp, cnt_global, parts, out);
+    if (e != cudaSuccess) return e;
+    return launch_chain(split_merge_k, dim3((n_nodes + 127) / 128), dim3(128), 0, st, (const SplitPart*)parts, n_nodes, slices,
+                        out, mirror);
+}
+
+}  // namespace ytk

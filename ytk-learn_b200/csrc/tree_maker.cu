@@ -1,8 +1,7 @@
-// Host side of libytkgbdt.so: the tree maker behind the reference's ITreeMaker seam.
-// Restates the control flow of DataParallelTreeMaker.make
-// (J/optimizer/gbdt/DataParallelTreeMaker.java:229-295) -- expansion queue, stop rules,
-// smaller-child / subtraction trick, HistogramPool policy -- and drives the kernels of
-// kernels.cu.  J/ = /root/reference/src/main/java/com/fenbi/ytklearn/.
+// Host side of libytkgbdt.so: the handle behind the reference's ITreeMaker seam -- creation, bin layout,
+// row and gradient uploads -- and the helpers that turn batches of nodes into table-driven launches
+// (histogram plan/enqueue, split search, partition, peer-memory set-up).  The growth loop itself
+// (DataParallelTreeMaker.make) is in grow.cu.  J/ = /root/reference/src/main/java/com/fenbi/ytklearn/.
 #include "host.cuh"
 
 namespace ytkh {
@@ -712,6 +711,7 @@ int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank,
     if (const char* s = getenv("YTK_GBDT_SEQUENTIAL")) h->force_sequential = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_STABLE_PARTITION")) h->single_pass_partition = atoi(s) == 0;
     if (const char* s = getenv("YTK_GBDT_NO_PLAN_AHEAD")) h->plan_ahead = atoi(s) == 0;
+    if (const char* s = getenv("YTK_GBDT_NO_SPIN")) h->spin_wait = atoi(s) == 0;
     if (const char* s = getenv("YTK_GBDT_TRACE")) h->trace = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_LOOKAHEAD")) h->lookahead = std::max(1, std::min(1024, atoi(s)));
     auto bail = [&](int code) { free_all(h); delete h; return code; };
