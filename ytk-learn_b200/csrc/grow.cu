@@ -113,8 +113,7 @@ private:
     int planned_slots = 0;
 
     // ---- small helpers -----------------------------------------------------------------
-    // The host wait of a batch: polled from user space (the wake-up through cudaEventSynchronize costs
-    // several microseconds more, once per level)
+    // The host wait of a batch (optionally polled from user space; cudaEventSynchronize measured the same)
     int wait_event(cudaEvent_t ev) {
         if (!h->spin_wait) { CK(cudaEventSynchronize(ev)); return YTK_OK; }
         for (;;) {

@@ -711,7 +711,7 @@ int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank,
     if (const char* s = getenv("YTK_GBDT_SEQUENTIAL")) h->force_sequential = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_STABLE_PARTITION")) h->single_pass_partition = atoi(s) == 0;
     if (const char* s = getenv("YTK_GBDT_NO_PLAN_AHEAD")) h->plan_ahead = atoi(s) == 0;
-    if (const char* s = getenv("YTK_GBDT_NO_SPIN")) h->spin_wait = atoi(s) == 0;
+    if (const char* s = getenv("YTK_GBDT_SPIN")) h->spin_wait = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_TRACE")) h->trace = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_LOOKAHEAD")) h->lookahead = std::max(1, std::min(1024, atoi(s)));
     auto bail = [&](int code) { free_all(h); delete h; return code; };
