@@ -151,6 +151,13 @@ int ytk_gbdt_set_bins_sparse(ytk_gbdt *h, const int32_t *start, int32_t F, int64
 int ytk_gbdt_upload_csr(ytk_gbdt *h, const int64_t *row_ptr, const int32_t *fids, const int32_t *slots,
                         int64_t row0, int64_t nrows);
 
+/* The same with original values instead of slots (float bits, as GBDTCoreData.x holds them before
+ * binning): each stored value is binned on the device with the rule of
+ * FeatureApprData.convertFeaVal2ApprFeaIndex (A1, J/data/gbdt/FeatureApprData.java:179-205) against
+ * cuts[start[f] .. start[f+1]).  default_slot stays what the caller computed for the fill value. */
+int ytk_gbdt_quantize_csr(ytk_gbdt *h, const int64_t *row_ptr, const int32_t *fids, const int32_t *value_bits,
+                          int64_t row0, int64_t nrows, const float *cuts);
+
 /* One chunk of GBDTCoreData.x after binning (J/dataflow/GBDTCoreData.java:164-168,
  * FeatureApprData.java:202): int32 slot indices, row-major with stride S = maxFeatureDim.
  * The device keeps them as uint8, row-major, padded to 32 features (uint16 columns for the

@@ -136,3 +136,24 @@ def test_sparse_device_boosting_rounds():
             tm.update_scores(0)
         assert sp.compute_grads() == dn.compute_grads()
         assert np.array_equal(sp.get_scores(), dn.get_scores())
+
+
+def test_sparse_values_binned_on_the_device():
+    """ytk_gbdt_quantize_csr: stored original values -> slots with the A1 rule, as the dense quantize_rows does"""
+    rng = np.random.default_rng(12)
+    n, F = 4000, 60
+    nbs = rng.integers(1, 300, size=F)
+    start = np.concatenate([[0], np.cumsum(nbs)]).astype(np.int32)
+    cuts = np.concatenate([np.sort(rng.normal(size=nb)).astype(np.float32) for nb in nbs])
+    stored = rng.random((n, F)) < 0.1
+    vals = rng.normal(size=(n, F)).astype(np.float32).round(2)
+    fill = np.zeros(F, np.float32)                                    # missing entries are filled with 0.0
+    dense_vals = np.where(stored, vals, fill[None, :]).astype(np.float32)
+    want = ob.find_bins(dense_vals, cuts, start)
+    default = ob.find_bins(fill[None, :], cuts, start)[0].astype(np.int32)
+    r, f = np.nonzero(stored)
+    row_ptr = np.concatenate([[0], np.cumsum(stored.sum(axis=1))]).astype(np.int64)
+    tm = yb.GpuTreeMaker(yb.make_params(**KW), start, n, sparse_default=default, nnz=len(r))
+    tm.quantize_csr(row_ptr[:2001], f.astype(np.int32), vals[r, f], cuts, row0=0)
+    tm.quantize_csr(row_ptr[2000:], f.astype(np.int32), vals[r, f], cuts, row0=2000)
+    assert np.array_equal(tm.download_rows(), want)

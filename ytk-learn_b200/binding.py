@@ -112,6 +112,7 @@ _SIGS = {
     "ytk_gbdt_get_grads": (C.c_int, [C.c_void_p, C.c_void_p]),
     "ytk_gbdt_set_bins_sparse": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int64]),
     "ytk_gbdt_upload_csr": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]),
+    "ytk_gbdt_quantize_csr": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "ytk_gbdt_score_values": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_int32, C.c_int32, C.c_void_p]),
     "ytk_gbdt_partition_rows_static": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_float,

@@ -114,9 +114,11 @@ cudaError_t launch_hist_csr(SparseRows sparse, const uint8_t* fea_selected, cons
 cudaError_t launch_csr_default_fix(SparseRows sparse, const uint8_t* fea_selected, int32_t F, const int32_t* start,
                                    const int32_t* feat_owner, const int64_t* feat_inner, long long owner_stride,
                                    long long* const* seg_out, int n_segs, const long long* tot, cudaStream_t st);
-// checks one uploaded chunk (entries sorted by feature inside a row, features / slots in range) and packs it
+// checks one uploaded chunk (entries sorted by feature inside a row, features / slots in range) and packs it;
+// cuts != null: `slots` are float bits of original values, binned with the A1 rule first
 cudaError_t launch_csr_pack(const int64_t* row_ptr, const int32_t* fids, const int32_t* slots, int64_t nrows, int32_t F,
-                            const int32_t* nbins, uint32_t* nz_out, int* bad_flag, cudaStream_t st);
+                            const int32_t* nbins, const float* cuts, const int32_t* start, uint32_t* nz_out, int* bad_flag,
+                            cudaStream_t st);
 cudaError_t launch_csr_to_dense(SparseRows sparse, int64_t row0, int64_t nrows, int32_t F, int32_t* out, cudaStream_t st);
 // rows one hist work item should cover so that `total_rows` split into about two waves of CTAs
 int64_t hist_rows_per_item(int64_t total_rows, int groups);

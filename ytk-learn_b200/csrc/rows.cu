@@ -109,15 +109,19 @@ __global__ void unpack_rows_k(const uint8_t* __restrict__ bins, int32_t S8, int6
 }
 
 // upload: range and order checks, (feature, slot) packed into one word
+// (cuts != null: `slots` holds float bits of original values, binned here with find_bin -- A1 for sparse input)
 __global__ void csr_pack_k(const int64_t* __restrict__ row_ptr, const int32_t* __restrict__ fids,
                            const int32_t* __restrict__ slots, int64_t nrows, int32_t F, const int32_t* __restrict__ nbins,
+                           const float* __restrict__ cuts, const int32_t* __restrict__ start,
                            uint32_t* __restrict__ nz_out, int* bad_flag) {
     for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < nrows; r += (int64_t)gridDim.x * blockDim.x) {
         const int64_t p0 = row_ptr[r] - row_ptr[0], p1 = row_ptr[r + 1] - row_ptr[0];
         int prev = -1;
         for (int64_t p = p0; p < p1; p++) {
-            const int f = fids[p], sl = slots[p];
-            if (f <= prev || f >= F || sl < 0 || sl >= (f >= 0 && f < F ? nbins[f] : 0)) { *bad_flag = 1; nz_out[p] = 0; continue; }
+            const int f = fids[p];
+            if (f <= prev || f >= F) { *bad_flag = 1; nz_out[p] = 0; continue; }
+            const int sl = cuts ? find_bin(cuts + start[f], nbins[f], __int_as_float(slots[p])) : slots[p];
+            if (sl < 0 || sl >= nbins[f]) { *bad_flag = 1; nz_out[p] = 0; continue; }
             prev = f;
             nz_out[p] = ((unsigned)f << 16) | (unsigned)sl;
         }
@@ -156,9 +160,10 @@ cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, i
     return cudaGetLastError();
 }
 cudaError_t launch_csr_pack(const int64_t* row_ptr, const int32_t* fids, const int32_t* slots, int64_t nrows, int32_t F,
-                            const int32_t* nbins, uint32_t* nz_out, int* bad_flag, cudaStream_t st) {
+                            const int32_t* nbins, const float* cuts, const int32_t* start, uint32_t* nz_out, int* bad_flag,
+                            cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    csr_pack_k<<<grid_for(nrows, 128), 128, 0, st>>>(row_ptr, fids, slots, nrows, F, nbins, nz_out, bad_flag);
+    csr_pack_k<<<grid_for(nrows, 128), 128, 0, st>>>(row_ptr, fids, slots, nrows, F, nbins, cuts, start, nz_out, bad_flag);
     return cudaGetLastError();
 }
 cudaError_t launch_csr_to_dense(SparseRows sparse, int64_t row0, int64_t nrows, int32_t F, int32_t* out, cudaStream_t st) {

@@ -945,8 +945,8 @@ int ytk_gbdt_quantize_rows(ytk_gbdt* h, const int32_t* xbits_chunk, int64_t row0
     return YTK_OK;
 }
 
-int ytk_gbdt_upload_csr(ytk_gbdt* h, const int64_t* row_ptr, const int32_t* fids, const int32_t* slots, int64_t row0,
-                        int64_t nrows) {
+static int upload_csr_impl(ytk_gbdt* h, const int64_t* row_ptr, const int32_t* fids, const int32_t* slots, int64_t row0,
+                           int64_t nrows, const float* cuts) {
     RET(check_rows(h, row_ptr, row0, nrows, "upload_csr"));
     if (!h->sparse) return fail(YTK_ERR_ARG, "upload_csr: call ytk_gbdt_set_bins_sparse first");
     if (row0 != h->csr_rows_done) return fail(YTK_ERR_ARG, "upload_csr: chunks go in row order (expected row %lld, got %lld)",
@@ -970,7 +970,17 @@ int ytk_gbdt_upload_csr(ytk_gbdt* h, const int64_t* row_ptr, const int32_t* fids
         int32_t* d_s = d_f + nnz;
         CK(cudaMemcpyAsync(d_f, fids + row_ptr[0], nnz * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
         CK(cudaMemcpyAsync(d_s, slots + row_ptr[0], nnz * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
-        CK(ytk::launch_csr_pack(h->d_row_ptr + row0, d_f, d_s, nrows, h->F, h->d_nbins, h->d_nz + h->csr_nnz_done, h->d_bad, h->st));
+        float* d_cuts = nullptr;
+        if (cuts) {
+            CK(cudaMalloc(&d_cuts, (size_t)h->B * sizeof(float)));
+            cudaError_t e = cudaMemcpyAsync(d_cuts, cuts, (size_t)h->B * sizeof(float), cudaMemcpyHostToDevice, h->st);
+            if (e != cudaSuccess) { cudaFree(d_cuts); CK(e); }
+        }
+        cudaError_t e = ytk::launch_csr_pack(h->d_row_ptr + row0, d_f, d_s, nrows, h->F, h->d_nbins, d_cuts, h->d_start,
+                                             h->d_nz + h->csr_nnz_done, h->d_bad, h->st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->st);
+        if (d_cuts) cudaFree(d_cuts);
+        CK(e);
     }
     CK(cudaStreamSynchronize(h->st));
     int bad = 0;
@@ -982,6 +992,17 @@ int ytk_gbdt_upload_csr(ytk_gbdt* h, const int64_t* row_ptr, const int32_t* fids
     h->csr_rows_done += nrows;
     h->csr_nnz_done += nnz;
     return YTK_OK;
+}
+
+int ytk_gbdt_upload_csr(ytk_gbdt* h, const int64_t* row_ptr, const int32_t* fids, const int32_t* slots, int64_t row0,
+                        int64_t nrows) {
+    return upload_csr_impl(h, row_ptr, fids, slots, row0, nrows, nullptr);
+}
+
+int ytk_gbdt_quantize_csr(ytk_gbdt* h, const int64_t* row_ptr, const int32_t* fids, const int32_t* value_bits, int64_t row0,
+                          int64_t nrows, const float* cuts) {
+    if (!cuts) return fail(YTK_ERR_ARG, "quantize_csr: null cuts");
+    return upload_csr_impl(h, row_ptr, fids, value_bits, row0, nrows, cuts);
 }
 
 int ytk_gbdt_download_rows(ytk_gbdt* h, int32_t* out, int64_t row0, int64_t nrows) {

@@ -76,6 +76,15 @@ class GpuTreeMaker:
         sl = np.ascontiguousarray(slots, dtype=np.int32)
         B.check(B.lib().ytk_gbdt_upload_csr(self._h, B.ptr(rp), B.ptr(f), B.ptr(sl), int(row0), len(rp) - 1))
 
+    def quantize_csr(self, row_ptr, fids, values, cuts, row0=0):
+        """CSR chunk of original float values, binned on the device (A1) against `cuts`."""
+        rp = np.ascontiguousarray(row_ptr, dtype=np.int64)
+        f = np.ascontiguousarray(fids, dtype=np.int32)
+        v = np.ascontiguousarray(values, dtype=np.float32)
+        c = np.ascontiguousarray(cuts, dtype=np.float32)
+        B.check(B.lib().ytk_gbdt_quantize_csr(self._h, B.ptr(rp), B.ptr(f), B.ptr(v.view(np.int32)), int(row0), len(rp) - 1,
+                                              B.ptr(c)))
+
     def upload_rows(self, x, row0=0):
         """x: int32 slots [n, stride] (a GBDTCoreData.x chunk after binning)."""
         x = np.ascontiguousarray(x, dtype=np.int32)
