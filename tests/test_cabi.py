@@ -80,3 +80,33 @@ def test_no_cpu_fallback():
         yb.GpuTreeMaker(yb.make_params(), [0, 3, 5], 10)
     assert ei.value.code == -2
     assert "no CPU path" in str(ei.value)
+
+
+def _header_struct(name):
+    """(field, C type) pairs of `typedef struct { ... } name;` in include/ytk_gbdt.h"""
+    src = open(os.path.join(ROOT, "include", "ytk_gbdt.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    body = re.search(r"typedef struct\s*\{([^}]*)\}\s*%s\s*;" % name, src).group(1)
+    out = []
+    for decl in body.split(";"):
+        decl = " ".join(decl.split())
+        if not decl:
+            continue
+        ctype, names = decl.rsplit(" ", 1) if "," not in decl else (decl.split(" ", 1)[0], decl.split(" ", 1)[1])
+        for nm in names.split(","):
+            nm = nm.strip()
+            ptr = nm.startswith("*") or ctype.endswith("*")
+            out.append((nm.lstrip("*"), ctype.rstrip("* ").strip() + ("*" if ptr else "")))
+    return out
+
+
+@pytest.mark.parametrize("cname,pyname", [("ytk_gbdt_params", "Params"), ("ytk_tree_out", "TreeOut"),
+                                          ("ytk_time_stats", "TimeStats"), ("ytk_split", "Split")])
+def test_ctypes_structs_mirror_the_header(cname, pyname):
+    """The ctypes mirror used by the tests and bench.py has the header's fields, in order, with the same types."""
+    ctypes_of = {"int32_t": C.c_int32, "int64_t": C.c_int64, "double": C.c_double, "float": C.c_float}
+    want = _header_struct(cname)
+    got = getattr(yb.binding if hasattr(yb, "binding") else yb, pyname)._fields_
+    assert [n for n, _ in want] == [n for n, _ in got]
+    for (n, ct), (_, pt) in zip(want, got):
+        assert pt is (C.c_void_p if ct.endswith("*") else ctypes_of[ct]), (n, ct, pt)
