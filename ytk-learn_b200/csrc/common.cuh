@@ -160,7 +160,7 @@ cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_s
                                    PartitionCounts* counts, cudaStream_t st,
                                    SparseRows sparse = SparseRows{nullptr, nullptr, nullptr});
 
-// The next level's partition planned on the device (level-wise growth, one GPU): slot 2k / 2k+1 =
+// The next level's partition planned on the device (level-wise growth): slot 2k / 2k+1 =
 // left / right child of this level's job k.  jobs[k]: which of the current segments / count
 // entries the job is, the index of its children's record pair (-1: leaves), the children's buffer.
 struct SpecJob { int seg; int cseg; int scan; int child_buf; };

@@ -244,7 +244,7 @@ struct ytk_gbdt {
     size_t tile_state_cap = 0;
     unsigned int* d_ticket = nullptr;
     unsigned long long part_epoch = 0;
-    // level-wise growth on one GPU: the next level's partition planned and started by the device
+    // level-wise growth: the next level's partition planned and started by the device
     bool plan_ahead = true;                 // YTK_GBDT_NO_PLAN_AHEAD=1 turns it off
     bool spin_wait = false;                 // YTK_GBDT_SPIN=1: poll the level's event from user space (measured: no gain)
     bool recs_merged = false;               // the last split exchange merged the records on the device
