@@ -455,9 +455,13 @@ cudaError_t launch_csr_default_fix(SparseRows sparse, const uint8_t* fea_selecte
                         owner_stride, seg_out, tot);
 }
 
+// CTAs per segment for the streaming kernels over histogram segments: 64 is plenty for a 114 KB
+// histogram; a few nodes with 20 MB histograms (sparse rows) need the whole GPU
+static inline int seg_blocks(int n_segments) { return std::max(64, kNumSMs * 8 / std::max(1, n_segments)); }
+
 cudaError_t launch_hist_subtract(const SubItem* items, int n_items, int64_t len, cudaStream_t st) {
     if (n_items <= 0) return cudaSuccess;
-    dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n_items);
+    dim3 grid((unsigned)grid_for(len, 256, seg_blocks(n_items)), (unsigned)n_items);
     return launch_chain(hist_subtract_k, grid, dim3(256), 0, st, items, len);
 }
 cudaError_t launch_hist_to_double(const long long* hist, int64_t len, const GradScale* scale, double* out,
@@ -472,12 +476,12 @@ cudaError_t launch_hist_from_double(const double* in, int64_t len, const GradSca
 }
 cudaError_t launch_zero_segments(long long* const* dst, int n, int64_t len, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
-    dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n);
+    dim3 grid((unsigned)grid_for(len, 256, seg_blocks(n)), (unsigned)n);
     return launch_chain(zero_segments_k, grid, dim3(256), 0, st, dst, len);
 }
 cudaError_t launch_copy_segments(const long long* src, long long* const* dst, int n, int64_t len, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;
-    dim3 grid((unsigned)grid_for(len, 256, 64), (unsigned)n);
+    dim3 grid((unsigned)grid_for(len, 256, seg_blocks(n)), (unsigned)n);
     copy_segments_k<<<grid, 256, 0, st>>>(src, dst, len);
     return cudaGetLastError();
 }
