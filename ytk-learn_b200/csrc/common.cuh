@@ -135,7 +135,7 @@ cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t*
                               const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
                               SplitPart* parts /* n_nodes * split_scan_slices() scratch */, ytk_split* out,
                               ytk_split* mirror /* nullable: a second copy of the records (pinned host memory) */,
-                              cudaStream_t st);
+                              unsigned int* done /* n_nodes zero-initialised counters; left zero */, cudaStream_t st);
 int split_scan_slices(int32_t f_from, int32_t f_to);
 
 // K6: stable partition of every segment by (float)bin(row,fid) < cond (or by a byte mask)

@@ -121,8 +121,10 @@ int ytk_gbdt_find_split(ytk_gbdt* h, const double* hist, int64_t sample_cnt, con
     CK(h->t_split_local.reserve(1));
     CK(h->h_split.reserve(1));
     CK(h->t_parts.reserve((size_t)ytk::split_scan_slices(0, h->F)));
+    RET(scan_done_counters(h, 1));
     CK(ytk::launch_split_scan(h->t_scan.d, 1, h->d_start, h->d_off_flat, h->d_fea_sel, 0, h->F, first,
-                              h->d_scale_hook, gain_params(h->p), nullptr, h->t_parts.d, h->t_split_local.d, nullptr, h->st));
+                              h->d_scale_hook, gain_params(h->p), nullptr, h->t_parts.d, h->t_split_local.d, nullptr,
+                              h->t_scan_done.d, h->st));
     CK(cudaMemcpyAsync(h->h_split.h, h->t_split_local.d, sizeof(ytk_split), cudaMemcpyDeviceToHost, h->st));
     CK(cudaStreamSynchronize(h->st));
     *out = h->h_split.h[0];

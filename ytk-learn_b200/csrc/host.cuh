@@ -289,6 +289,7 @@ struct ytk_gbdt {
     int32_t* d_default_slot = nullptr;     // [F]
     int64_t nnz_cap = 0, csr_rows_done = 0, csr_nnz_done = 0;
     DevTable<long long> t_node_tot;        // (g,h) totals of the rows of each node of a batch
+    DevTable<unsigned int> t_scan_done;    // per node: slices of the split scan that have finished (kept at zero)
     uint32_t* d_group_mask = nullptr;
     // features with more than 256 slots: uint16 columns beside the uint8 matrices
     int n_wide = 0;
@@ -422,6 +423,8 @@ int hist_enqueue(ytk_gbdt* h, const HistPlan& pl, ytk_time_stats* T, const ytk::
                  const ytk::PartitionCounts* cnt_global);
 int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T, int n_sel,
                 const ytk::PartitionCounts* cnt_local, const ytk::PartitionCounts* cnt_global);
+// at least m zeroed counters in h->t_scan_done
+int scan_done_counters(ytk_gbdt* h, int m);
 int search_enqueue(ytk_gbdt* h, const ytk::ScanNode* d_nodes, int m, int first_owned,
                    const ytk::PartitionCounts* cnt_global);
 void search_collect(ytk_gbdt* h, int m, std::vector<ytk_split>& recs);

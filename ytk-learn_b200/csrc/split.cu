@@ -63,11 +63,12 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
              const int64_t* __restrict__ feat_off, const uint8_t* __restrict__ fea_selected,
              int32_t f_from, int32_t f_to, int32_t first_fea, const GradScale* __restrict__ scale,
              GainParams gp, const PartitionCounts* __restrict__ cnt_global, SplitPart* __restrict__ parts,
-             ytk_split* __restrict__ outs) {
+             ytk_split* __restrict__ outs, ytk_split* __restrict__ mirror, unsigned int* __restrict__ done) {
     pdl_sync();
     __shared__ double s_tot[2];
     __shared__ float s_lc[kScanWarps];
-    __shared__ int s_fid[kScanWarps], s_lo[kScanWarps], s_hi[kScanWarps];
+    __shared__ int s_fid[kScanWarps], s_lo[kScanWarps], s_hi[kScanWarps], s_slice[kScanWarps];
+    __shared__ int s_last;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int node = blockIdx.x, slice = blockIdx.y;
     const double ig = scale->inv_g, ih = scale->inv_h;
@@ -181,26 +182,42 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
             out->root_gain = root_gain;
             out->node_value = (float)calc_node_value(gp, totG, totH);
         }
+        // the last CTA of a node to get here folds the node's slices (no separate merge launch)
+        __threadfence();
+        s_last = atomicAdd(done + node, 1u) == gridDim.y - 1;
     }
-}
-
-// folds the slices of every node (increasing feature ids: strict > = smallest fid wins ties)
-// (mirror: the finished record is also stored there -- pinned host memory on one GPU, so that the host
-// reads it without a copy while device-side consumers keep reading `outs`)
-__global__ void split_merge_k(const SplitPart* __restrict__ parts, int n_nodes, int n_slices,
-                              ytk_split* __restrict__ outs, ytk_split* __restrict__ mirror) {
-    pdl_sync();
-    int node = blockIdx.x * blockDim.x + threadIdx.x;
-    if (node >= n_nodes) return;
-    SplitPart best = {-CUDART_INF_F, -1, -1, -1};
-    for (int s = 0; s < n_slices; s++) {
-        SplitPart p = parts[(size_t)node * n_slices + s];
-        if (p.fid >= 0 && p.lc > best.lc) best = p;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // slices hold increasing feature ids: the maximum, ties to the lowest slice = smallest fid
+    SplitPart bp = {-CUDART_INF_F, -1, -1, -1};
+    int bs = 0x7fffffff;
+    for (int s = threadIdx.x; s < (int)gridDim.y; s += blockDim.x) {
+        const int4 v = __ldcg(reinterpret_cast<const int4*>(parts + (size_t)node * gridDim.y + s));
+        const float lc = __int_as_float(v.x);
+        if (v.y >= 0 && lc > bp.lc) { bp = {lc, v.y, v.z, v.w}; bs = s; }
     }
-    ytk_split r = outs[node];            // totals, root gain and node value were written by the scan
-    r.loss_chg = best.lc; r.fid = best.fid; r.lo = best.lo; r.hi = best.hi;
-    outs[node] = r;
-    if (mirror) mirror[node] = r;
+    for (int d = 16; d > 0; d >>= 1) {
+        const float olc = __shfl_xor_sync(0xffffffffu, bp.lc, d);
+        const int ofid = __shfl_xor_sync(0xffffffffu, bp.fid, d), olo = __shfl_xor_sync(0xffffffffu, bp.lo, d);
+        const int ohi = __shfl_xor_sync(0xffffffffu, bp.hi, d), os = __shfl_xor_sync(0xffffffffu, bs, d);
+        if (ofid >= 0 && (olc > bp.lc || (olc == bp.lc && os < bs))) { bp = {olc, ofid, olo, ohi}; bs = os; }
+    }
+    if (lane == 0) { s_lc[warp] = bp.lc; s_fid[warp] = bp.fid; s_lo[warp] = bp.lo; s_hi[warp] = bp.hi; s_slice[warp] = bs; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < kScanWarps; w++)
+            if (s_fid[w] >= 0 && (s_lc[w] > bp.lc || (s_lc[w] == bp.lc && s_slice[w] < bs))) {
+                bp = {s_lc[w], s_fid[w], s_lo[w], s_hi[w]}; bs = s_slice[w];
+            }
+        ytk_split r;                       // totals, root gain and node value: written by the node's slice 0
+        r.sum_grad = __ldcg(&outs[node].sum_grad); r.sum_hess = __ldcg(&outs[node].sum_hess);
+        r.root_gain = __ldcg(&outs[node].root_gain); r.node_value = __ldcg(&outs[node].node_value);
+        r.loss_chg = bp.lc; r.fid = bp.fid; r.lo = bp.lo; r.hi = bp.hi;
+        outs[node] = r;
+        if (mirror) mirror[node] = r;      // pinned host memory on one GPU: the host reads it without a copy
+        done[node] = 0;                    // ready for the next launch
+    }
 }
 
 int split_scan_slices(int32_t f_from, int32_t f_to) {
@@ -211,15 +228,12 @@ int split_scan_slices(int32_t f_from, int32_t f_to) {
 cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t* start, const int64_t* feat_off,
                               const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
                               const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
-                              SplitPart* parts, ytk_split* out, ytk_split* mirror, cudaStream_t st) {
+                              SplitPart* parts, ytk_split* out, ytk_split* mirror, unsigned int* done, cudaStream_t st) {
     if (n_nodes <= 0) return cudaSuccess;
     const int slices = split_scan_slices(f_from, f_to);
     dim3 grid((unsigned)n_nodes, (unsigned)slices);
-    cudaError_t e = launch_chain(split_scan_k, grid, dim3(kScanWarps * 32), 0, st, nodes, start, feat_off, fea_selected, f_from,
-                                 f_to, first_fea, scale, gp, cnt_global, parts, out);
-    if (e != cudaSuccess) return e;
-    return launch_chain(split_merge_k, dim3((n_nodes + 127) / 128), dim3(128), 0, st, (const SplitPart*)parts, n_nodes, slices,
-                        out, mirror);
+    return launch_chain(split_scan_k, grid, dim3(kScanWarps * 32), 0, st, nodes, start, feat_off, fea_selected, f_from,
+                        f_to, first_fea, scale, gp, cnt_global, parts, out, mirror, done);
 }
 
 }  // namespace ytk

@@ -104,7 +104,7 @@ void free_all(ytk_gbdt* h) {
     h->t_items.release(); h->t_leaf_items.release(); h->t_segs.release(); h->t_tile_seg.release();
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
     h->t_split_local.release(); h->t_split_all.release(); h->t_parts.release(); h->t_leaf.release(); h->t_hist_local.release();
-    h->t_rs_out.release(); h->t_node_tot.release();
+    h->t_rs_out.release(); h->t_node_tot.release(); h->t_scan_done.release();
     for (int i = 0; i < 2; i++) { h->t_spec_segs[i].release(); h->t_spec_counts[i].release(); h->h_spec_counts[i].release(); }
     h->t_spec_tiles.release();
     F(h->d_spec_ntiles);
@@ -444,6 +444,14 @@ int build_hists(ytk_gbdt* h, const std::vector<HistJob>& jobs, ytk_time_stats* T
 // ---- split search: enqueue / collect ---------------------------------------------------------------
 // updateTreeMakerNodeStats + findBestSplit(nid, hist) + syncBestSplit (:543-595, :640-653) for a
 // batch of nodes; after the stream has been synchronised the merged record of node k is recs[k].
+int scan_done_counters(ytk_gbdt* h, int m) {
+    const size_t before = h->t_scan_done.cap;
+    CK(h->t_scan_done.reserve((size_t)std::max(m, 256)));
+    if (h->t_scan_done.cap != before)       // a new array: the kernels leave the counters at zero afterwards
+        CK(cudaMemsetAsync(h->t_scan_done.d, 0, h->t_scan_done.cap * sizeof(unsigned int), h->st));
+    return YTK_OK;
+}
+
 int search_enqueue(ytk_gbdt* h, const ytk::ScanNode* d_nodes, int m, int first_owned,
                    const ytk::PartitionCounts* cnt_global) {
     if (m == 0) return YTK_OK;
@@ -451,11 +459,12 @@ int search_enqueue(ytk_gbdt* h, const ytk::ScanNode* d_nodes, int m, int first_o
     CK(h->t_parts.reserve((size_t)m * ytk::split_scan_slices(h->f_from, h->f_to)));
     CK(h->h_split.reserve((size_t)m * h->world));
     // the records stay in device memory (the planner of the next partition and the exchange read them
-    // there); on one GPU the merge kernel also stores them in pinned host memory, so the host needs no copy
+    // there); on one GPU the scan also stores them in pinned host memory, so the host needs no copy
+    RET(scan_done_counters(h, m));
     CK(ytk::launch_split_scan(d_nodes, m, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to,
                               first_owned, h->d_scale, gain_params(h->p), cnt_global, h->t_parts.d, h->t_split_local.d,
-                              h->world == 1 ? h->h_split.h : nullptr, h->st));
-    h->launches += 2;
+                              h->world == 1 ? h->h_split.h : nullptr, h->t_scan_done.d, h->st));
+    h->launches++;
     if (h->world > 1) {
         // "split allgather": every rank's record for each node, merged on the host with the
         // needReplace rule -- replaces allreduceRpc(SplitInfo) and allreduceArrayRpc(MAX)
