@@ -523,3 +523,27 @@ def test_fixed_point_width(bits, monkeypatch):
         assert_same_tree(t, o)
     else:
         np.testing.assert_allclose(got, want, rtol=0, atol=1e-3 * np.abs(want).max())
+
+
+# ---------------------------------------------------------------- degenerate sizes
+@pytest.mark.parametrize("n", [1, 2, 33])
+@pytest.mark.parametrize("policy", ["level", "loss"])
+def test_handful_of_rows(n, policy):
+    kw = dict(KW, grow_policy=policy, max_depth=4 if policy == "level" else -1, max_leaf_cnt=-1 if policy == "level" else 8,
+              min_child_hessian_sum=0.0)
+    x, start, gp = synth(n, 5, 16, 3)
+    tm = maker(kw, x, start, gp)
+    t = tm.make(0)
+    o, opos, _ = ob.make_tree(ob.make_params(**kw), x, gp, 0, start)
+    assert_same_tree(t, o)
+    assert np.array_equal(tm.get_positions(), opos)
+
+
+def test_empty_shard_gives_a_single_leaf():
+    """A worker without rows (possible with several ranks) must not crash: one node, no samples."""
+    start = np.array([0, 4, 9], np.int32)
+    tm = yb.GpuTreeMaker(yb.make_params(**KW), start, 0)
+    tm.set_grads(np.zeros(0, np.float32))
+    t = tm.make(0)
+    assert t.n_nodes == 1 and t.left[0] == -1 and t.sample_cnt[0] == 0
+    assert tm.get_positions().size == 0
