@@ -16,6 +16,8 @@ KW = dict(max_depth=6, max_leaf_cnt=-1, grow_policy="level", min_child_hessian_s
 CASES = {"level": KW, "loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=24),
          "few_features": dict(KW, max_depth=4), "wide_features": dict(KW, max_depth=5),
          "sparse_rows": dict(KW, max_depth=5),
+         "empty_rank": dict(KW, max_depth=3, min_child_hessian_sum=0.0),
+         "uneven_gradients": dict(KW, max_depth=5, min_child_hessian_sum=0.01),
          "sorted_shards": dict(KW, max_depth=7), "sorted_shards_loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=40)}
 
 
@@ -25,6 +27,13 @@ def _data(case):
         return synth(20000, 3, [17, 255, 4], 5)
     if case == "wide_features":                     # features with more than 256 bins (uint16 slots)
         return synth(40000, 7, [300, 5, 1000, 256, 257, 4000, 40], 13, skew=True)
+    if case == "uneven_gradients":                  # the ranks' largest |g|, |h| differ by orders of magnitude:
+        x, start, gp = synth(30000, 12, 64, 37)     # the fixed-point scales must still be common to all ranks
+        g2 = gp.reshape(-1, 2).copy()
+        g2[15000:] *= np.float32(0.013)
+        return x, start, g2.reshape(-1)
+    if case == "empty_rank":                        # 3 rows over 2 ranks, and the first split leaves rank 0 one side only
+        return synth(3, 4, 8, 31)
     if case == "sparse_rows":                       # mostly slot 0
         x, start, gp = synth(30000, 60, 40, 29)
         x = x * (np.random.default_rng(3).random(x.shape) < 0.05)

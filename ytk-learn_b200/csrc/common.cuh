@@ -87,10 +87,12 @@ cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t st
 cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, int32_t F, WideCols wide, int32_t* out,
                                cudaStream_t st);
 
-// (g,h) float pairs of class gid -> fixed-point int2 (|value| < 2^bits) + scales
+// (g,h) float pairs of class gid -> fixed-point int2 (|value| < 2^bits) + scales, in two steps: the
+// largest |g| and |h| of the shard as float bits in absmax_bits[2] (with several GPUs the host takes
+// the maximum over the ranks in between: all ranks must use the same scales), then the conversion
+cudaError_t launch_grad_absmax(const float* gp, int64_t n, int32_t K, int32_t gid, unsigned* absmax_bits, cudaStream_t st);
 cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t gid, int2* gq,
-                                 unsigned* absmax_bits /*2, scratch*/, GradScale* scale, int bits,
-                                 cudaStream_t st);
+                                 const unsigned* absmax_bits, GradScale* scale, int bits, cudaStream_t st);
 
 // K2: histograms of n_items row runs; item -> segment -> seg_out[seg] (int64, pre-zeroed); feature f's
 // bins at seg_out[seg] + feat_owner[f]*owner_stride + feat_inner[f] + 2*bin + {0,1}.

@@ -197,9 +197,7 @@ private:
     int begin_tree(int gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask) {
         RET(set_features(h, fea_index, n_fea, &first_owned, &n_sel));
         h->pool.clear();
-        CK(ytk::launch_grad_quantize(h->d_gp, h->N, p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->fixed_bits,
-                                     h->st));
-        h->launches += 2;
+        RET(quantize_grads(h, gid));
         CK(cudaMemcpyAsync(h->h_scale.h, h->d_scale, sizeof(ytk::GradScale), cudaMemcpyDeviceToHost, h->st));
         if (row_mask) {
             if (!h->d_mask) CK(cudaMalloc(&h->d_mask, std::max<int64_t>(h->N, 1)));

@@ -389,13 +389,15 @@ __global__ void copy_segments_k(const long long* __restrict__ src, long long* co
         d[i] = s[i];
 }
 
-cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t gid, int2* gq,
-                                 unsigned* absmax_bits, GradScale* scale, int bits, cudaStream_t st) {
+cudaError_t launch_grad_absmax(const float* gp, int64_t n, int32_t K, int32_t gid, unsigned* absmax_bits, cudaStream_t st) {
     cudaError_t e = cudaMemsetAsync(absmax_bits, 0, 2 * sizeof(unsigned), st);
     if (e != cudaSuccess) return e;
-    int g = grid_for(n, 256, kNumSMs * 8);
-    grad_absmax_k<<<g, 256, 0, st>>>(gp, n, K, gid, absmax_bits);
-    grad_quantize_k<<<g, 256, 0, st>>>(gp, n, K, gid, gq, absmax_bits, scale, bits);
+    grad_absmax_k<<<grid_for(n, 256, kNumSMs * 8), 256, 0, st>>>(gp, n, K, gid, absmax_bits);
+    return cudaGetLastError();
+}
+cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t gid, int2* gq,
+                                 const unsigned* absmax_bits, GradScale* scale, int bits, cudaStream_t st) {
+    grad_quantize_k<<<grid_for(n, 256, kNumSMs * 8), 256, 0, st>>>(gp, n, K, gid, gq, absmax_bits, scale, bits);
     return cudaGetLastError();
 }
 

@@ -15,8 +15,7 @@ int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n
     CK(cudaSetDevice(h->device));
     int first_owned;
     RET(set_features(h, fea_index, n_fea, &first_owned, nullptr));
-    CK(ytk::launch_grad_quantize(h->d_gp, h->N, h->p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->fixed_bits,
-                                 h->st));
+    RET(quantize_grads(h, gid));
     int64_t n = rows ? n_rows : h->N;
     if (rows && n > 0) {
         for (int64_t i = 0; i < n; i++)

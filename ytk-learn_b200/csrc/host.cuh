@@ -409,6 +409,8 @@ void free_all(ytk_gbdt* h);
 ytk::SparseRows sparse_rows(const ytk_gbdt* h);
 ytk::WideCols wide_cols(const ytk_gbdt* h, int64_t row0 = 0);
 int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* first_owned, int* n_sel);
+// fixed-point copies of class gid's gradient pairs, with scales common to all ranks
+int quantize_grads(ytk_gbdt* h, int gid);
 int hist_events(ytk_gbdt* h, cudaEvent_t* a, cudaEvent_t* b);
 int comm_mark(ytk_gbdt* h);
 void add_row_items(std::vector<ytk::RowItem>& items, const Interval& v, int seg, int64_t rows_per_item);

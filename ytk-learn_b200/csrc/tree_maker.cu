@@ -168,6 +168,17 @@ int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* firs
     return YTK_OK;
 }
 
+int quantize_grads(ytk_gbdt* h, int gid) {
+    CK(ytk::launch_grad_absmax(h->d_gp, h->N, h->p.class_num, gid, h->d_absmax, h->st));
+    // The scales are powers of two chosen from max|g| and max|h|: of ALL rows, or the integer sums of
+    // different ranks would be in different units (float bits of non-negative values order like integers)
+    if (h->world > 1)
+        NK(ytk::nccl_api().AllReduce(h->d_absmax, h->d_absmax, 2, ncclUint32, ncclMax, h->comm, h->st));
+    CK(ytk::launch_grad_quantize(h->d_gp, h->N, h->p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->fixed_bits, h->st));
+    h->launches += 2;
+    return YTK_OK;
+}
+
 int hist_events(ytk_gbdt* h, cudaEvent_t* a, cudaEvent_t* b) {
     if (h->ev_used + 2 > (int)h->ev.size()) {
         for (int i = 0; i < 2; i++) {
