@@ -18,6 +18,7 @@ CASES = {"level": KW, "loss": dict(KW, grow_policy="loss", max_depth=-1, max_lea
          "sparse_rows": dict(KW, max_depth=5),
          "empty_rank": dict(KW, max_depth=3, min_child_hessian_sum=0.0),
          "uneven_gradients": dict(KW, max_depth=5, min_child_hessian_sum=0.01),
+         "zero_rows_rank": dict(KW, max_depth=3, min_child_hessian_sum=0.0),
          "sorted_shards": dict(KW, max_depth=7), "sorted_shards_loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=40)}
 
 
@@ -32,6 +33,8 @@ def _data(case):
         g2 = gp.reshape(-1, 2).copy()
         g2[15000:] *= np.float32(0.013)
         return x, start, g2.reshape(-1)
+    if case == "zero_rows_rank":                    # one row in all: rank 0 holds nothing
+        return synth(1, 4, 8, 33)
     if case == "empty_rank":                        # 3 rows over 2 ranks, and the first split leaves rank 0 one side only
         return synth(3, 4, 8, 31)
     if case == "sparse_rows":                       # mostly slot 0
