@@ -19,7 +19,17 @@ CASES = {"level": KW, "loss": dict(KW, grow_policy="loss", max_depth=-1, max_lea
          "empty_rank": dict(KW, max_depth=3, min_child_hessian_sum=0.0),
          "uneven_gradients": dict(KW, max_depth=5, min_child_hessian_sum=0.01),
          "zero_rows_rank": dict(KW, max_depth=3, min_child_hessian_sum=0.0),
+         "sampling_unowned": dict(KW, max_depth=5),
          "sorted_shards": dict(KW, max_depth=7), "sorted_shards_loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=40)}
+
+
+def _sampling(case, n, F):
+    """(fea_index, row_mask) of the make() call: none, except for the case where the sampled features all
+    belong to rank 0's range (rank 1 has no feature to take node totals from) and rows are sampled too."""
+    if case != "sampling_unowned":
+        return None, None
+    mask = (np.random.default_rng(9).random(n) < 0.7).astype(np.uint8)
+    return np.array([0, 2, 5], np.int32), mask
 
 
 def _data(case):
@@ -68,7 +78,8 @@ def _rank(rank, world, nccl_id, case, ret):
         tm = yb.GpuTreeMaker(p, start, hi - lo, device=rank, rank=rank, world=world, nccl_id=nccl_id)
         tm.upload_rows(x[lo:hi])
     tm.set_grads(gp.reshape(n, 2)[lo:hi].reshape(-1))
-    tree = tm.make(0)
+    fea, mask = _sampling(case, n, x.shape[1])
+    tree = tm.make(0, fea_index=fea, row_mask=None if mask is None else mask[lo:hi])
     pos = tm.get_positions()
     hist = tm.build_hist(0)                         # reduced over ranks: the global root histogram
     ret[rank] = ({name: getattr(tree, name) for name, _ in yb.Tree.FIELDS}, pos, hist)
@@ -87,7 +98,8 @@ def test_two_gpus_equal_one_gpu_and_oracle(case):
     x, start, gp = _data(case)
     n = x.shape[0]
     one = maker(CASES[case], x, start, gp)
-    t1 = one.make(0)
+    fea, mask = _sampling(case, n, x.shape[1])
+    t1 = one.make(0, fea_index=fea, row_mask=mask)
     p1 = one.get_positions()
     h1 = one.build_hist(0)
     ctx = mp.get_context("spawn")
@@ -109,6 +121,6 @@ def test_two_gpus_equal_one_gpu_and_oracle(case):
             assert np.array_equal(ret[r][0][name], getattr(t1, name), equal_nan=True), (r, name)
         assert np.array_equal(ret[r][2], h1)
     assert np.array_equal(pos, p1)
-    o, opos, _ = ob.make_tree(ob.make_params(**CASES[case]), x, gp, 0, start, W=world)
+    o, opos, _ = ob.make_tree(ob.make_params(**CASES[case]), x, gp, 0, start, W=world, fea_index=fea, row_mask=mask)
     assert_same_tree(t1, o)
     assert np.array_equal(p1, opos)
