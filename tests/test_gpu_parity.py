@@ -316,6 +316,10 @@ CASES = [
     ("multiclass", dict(KW, max_depth=4), 12000, 33, 63, 4, False),
     ("stump_depth0", dict(KW, max_depth=0, max_leaf_cnt=4), 3000, 5, 10, 1, False),
     ("tiny", dict(KW, max_depth=3, min_child_hessian_sum=0.0), 9, 3, 4, 1, False),
+    ("loss_small_pool", dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=24, histogram_pool_capacity=0.3), 20000, 12, 100, 1, False),
+    ("loss_multiclass", dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=20), 15000, 20, 63, 3, True),
+    ("loss_l1_capped", dict(KW, grow_policy="loss", max_depth=6, max_leaf_cnt=30, l1=0.4, max_abs_leaf_val=0.5), 20000, 12, 100, 1, False),
+    ("loss_min_split_samples", dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=30, min_split_samples=700, min_child_hessian_sum=0.0), 20000, 10, 32, 1, False),
 ]
 
 
@@ -547,3 +551,24 @@ def test_empty_shard_gives_a_single_leaf():
     t = tm.make(0)
     assert t.n_nodes == 1 and t.left[0] == -1 and t.sample_cnt[0] == 0
     assert tm.get_positions().size == 0
+
+
+def test_constant_features_and_extreme_gradient_magnitudes():
+    """No feature can separate anything -> a single leaf; gradients of 1e-20 and 1e+20 -> the power-of-two
+    scale adapts and the tree equals the oracle's."""
+    n, F = 5000, 6
+    x, start, gp = synth(n, F, 16, 5)
+    xc = np.tile(x[:1], (n, 1))
+    tm = maker(KW, xc, start, gp)
+    t = tm.make(0)
+    o, opos, _ = ob.make_tree(ob.make_params(**KW), xc, gp, 0, start)
+    assert t.n_nodes == 1
+    assert_same_tree(t, o)
+    for scale in (1e-20, 1e20):
+        g2 = (gp.astype(np.float64) * scale).astype(np.float32)
+        kw = dict(KW, min_child_hessian_sum=0.0, l2=0.0)
+        tm = maker(kw, x, start, g2)
+        t = tm.make(0)
+        o, opos, _ = ob.make_tree(ob.make_params(**kw), x, g2, 0, start)
+        assert_same_tree(t, o)
+        assert np.array_equal(tm.get_positions(), opos)
