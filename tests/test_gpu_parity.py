@@ -572,3 +572,27 @@ def test_constant_features_and_extreme_gradient_magnitudes():
         o, opos, _ = ob.make_tree(ob.make_params(**kw), x, g2, 0, start)
         assert_same_tree(t, o)
         assert np.array_equal(tm.get_positions(), opos)
+
+
+@pytest.mark.parametrize("policy", ["level", "loss"])
+def test_consecutive_trees_with_changing_sampling_and_gradients(policy):
+    """One handle, several make() calls as in boosting rounds: different feature subsets, row masks and
+    gradients each time -- nothing may leak from one tree into the next (pool slots, planned partitions,
+    expansions computed ahead, leaf ranges)."""
+    kw = dict(KW, grow_policy=policy, max_depth=6 if policy == "level" else -1, max_leaf_cnt=-1 if policy == "level" else 40)
+    n, F = 40000, 30
+    x, start, gp = synth(n, F, 200, 41, skew=True)
+    rng = np.random.default_rng(6)
+    tm = maker(kw, x, start, gp)
+    p = ob.make_params(**kw)
+    for it in range(5):
+        fea = None if it % 2 == 0 else np.sort(rng.permutation(F)[: 5 + 4 * it]).astype(np.int32)
+        mask = None if it in (0, 3) else (rng.random(n) < 0.4 + 0.1 * it).astype(np.uint8)
+        g = (gp.reshape(-1, 2) * np.float32(1.0 + 0.7 * it)).astype(np.float32)
+        g[:, 0] += rng.normal(size=n).astype(np.float32) * np.float32(0.05 * it)
+        g = g.reshape(-1)
+        tm.set_grads(g)
+        t = tm.make(0, fea_index=fea, row_mask=mask)
+        o, opos, _ = ob.make_tree(p, x, g, 0, start, fea_index=fea, row_mask=mask)
+        assert_same_tree(t, o)
+        assert np.array_equal(tm.get_positions(), opos), it
