@@ -596,3 +596,19 @@ def test_consecutive_trees_with_changing_sampling_and_gradients(policy):
         o, opos, _ = ob.make_tree(p, x, g, 0, start, fea_index=fea, row_mask=mask)
         assert_same_tree(t, o)
         assert np.array_equal(tm.get_positions(), opos), it
+
+
+def test_feature_sampling_that_leaves_whole_feature_groups_out():
+    """100 features = 4 groups of 32; the sampled ones sit in groups 0 and 3 only."""
+    n, F = 30000, 100
+    x, start, gp = synth(n, F, 64, 43)
+    fea = np.array([1, 5, 30, 96, 97, 99], np.int32)
+    for kw in (dict(KW, max_depth=5), dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=20)):
+        tm = maker(kw, x, start, gp)
+        t = tm.make(0, fea_index=fea)
+        o, opos, _ = ob.make_tree(ob.make_params(**kw), x, gp, 0, start, fea_index=fea)
+        assert_same_tree(t, o)
+        assert np.array_equal(tm.get_positions(), opos)
+        got = tm.build_hist(0, fea_index=fea)
+        want = ob.build_hist(x, gp, 1, 0, np.arange(n), fea, start)
+        assert_hist_close(got, want, gp)
