@@ -146,3 +146,32 @@ def test_score_values_matches_oracle_with_missing_values():
     assert np.array_equal(g2, w2)
     with pytest.raises(yb.YtkError):                          # a default child that is not a child
         tm.score_values(t, thr, full, g2, default_child=np.full(t.n_nodes, t.n_nodes + 5, np.int32))
+
+
+def test_loss_wise_rounds_score_update_with_splits_computed_ahead():
+    """Loss-wise trees: leaves whose split was computed ahead but never applied keep their rows in several
+    ranges; the score update (and rows left out by the row mask, which walk the tree) must still be exact."""
+    kw = dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=25)
+    n, F = 40000, 16
+    x, start, _ = synth(n, F, 64, 19, skew=True)
+    rng = np.random.default_rng(4)
+    y = (rng.random(n) < 0.45).astype(np.float32)
+    w = np.ones(n, np.float32)
+    init = np.zeros(n, np.float32)
+    tm = yb.GpuTreeMaker(yb.make_params(**kw), start, n)
+    tm.upload_rows(x)
+    tm.set_targets("sigmoid", y, w, init)
+    score = np.zeros(n, np.float32)
+    _, gp = ob.loss_grad_scalar("sigmoid", score, init, y, w)
+    tm.compute_grads()
+    p = ob.make_params(**kw)
+    for it in range(3):
+        mask = None if it == 0 else (rng.random(n) < 0.6).astype(np.uint8)
+        t = tm.make(0, row_mask=mask)
+        tm.update_scores(0)
+        o, opos, _ = ob.make_tree(p, x, gp, 0, start, row_mask=mask)
+        assert t.n_nodes == o.n_nodes and np.array_equal(t.fid, o.fid)
+        ob.score_slots(o, x, score)
+        _close(tm.get_scores(), score, "scores")
+        tm.compute_grads()
+        gp = tm.get_grads()
