@@ -46,7 +46,7 @@ def main():
                                                                              h["dram_write_mb"]))
     # kernels launched inside ytk_gbdt_make_tree (the timed step); the rest of a bench.py run is the one-off
     # row upload, get_positions and the device-gradient rounds
-    in_make = ("hist_build_k", "partition_", "split_", "leaf_sums_k", "hist_subtract_k", "zero_segments_k",
+    in_make = ("hist_", "csr_default_fix_k", "partition_", "plan_", "split_", "leaf_sums_k", "zero_segments_k",
                "grad_absmax_k", "grad_quantize_k", "copy_segments_k", "peer_")
     make_tot = sum(a[1] for n, a in agg.items() if n.startswith(in_make))
     print("kernels of make(): %.1f us; hist_build_k share of them: %.3f" % (make_tot, agg.get("hist_build_k", [0, 0])[1] / make_tot if make_tot else 0))
