@@ -205,8 +205,6 @@ struct PeerTable {
 };
 cudaError_t launch_peer_allreduce(const PeerTable& pt, const void* src, size_t area_off, size_t slot_bytes, size_t words,
                                   int flag_set, unsigned long long epoch, long long* out, int* err, cudaStream_t st);
-cudaError_t launch_peer_allgather(const PeerTable& pt, const void* src, size_t area_off, size_t slot_bytes, size_t bytes,
-                                  int flag_set, unsigned long long epoch, int* err, cudaStream_t st);
 // raises this rank's "staging complete" flag, waits for everybody's, sums the owned segments out of all staging buffers
 // all-gather + the needReplace / MAX merge of the split records: merged record k -> out_dev[k], out_host[k]
 cudaError_t launch_peer_allgather_merge(const PeerTable& pt, const ytk_split* src, size_t area_off, size_t slot_bytes, int m,

@@ -310,9 +310,7 @@ struct ytk_gbdt {
     void* d_stage = nullptr;  size_t stage_bytes = 0;   // upload staging
 
     // per-batch work tables and result buffers
-    DevTable<ytk::RowItem> t_items, t_leaf_items;
-    DevTable<ytk::SplitSeg> t_segs;
-    DevTable<int> t_tile_seg;
+    DevTable<ytk::RowItem> t_items;        // work items of the build_hist hook
     DevTable<ytk::ScanNode> t_scan;
     DevTable<ytk::SubItem> t_sub;
     DevTable<ytk::PosItem> t_pos;

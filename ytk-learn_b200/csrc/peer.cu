@@ -74,14 +74,8 @@ __global__ void peer_allreduce_k(PeerTable pt, const unsigned long long* __restr
     }
 }
 
-// All-gather of a small record block in one kernel: afterwards slot [r] of this rank's area holds rank r's.
-__global__ void peer_allgather_k(PeerTable pt, const unsigned long long* __restrict__ src, size_t area_off, size_t slot_bytes,
-                                 size_t bytes, int flag_set, unsigned long long epoch, int* err) {
-    peer_push(pt, src, area_off, slot_bytes, bytes, flag_set, epoch);
-    peer_wait(pt, flag_set, epoch, err);
-}
-
-// The same all-gather for the split records, followed by the merge every rank would otherwise do on
+// All-gather of the split records (every rank pushes its block into slot [rank] of every peer's area),
+// followed by the merge every rank would otherwise do on
 // its host (ytk_gbdt_merge_splits: needReplace in rank order, element-wise MAX of the node totals,
 // DataParallelTreeMaker.java:560,640-653): merged record k -> out_dev[k] and out_host[k] (pinned).
 __global__ void peer_allgather_merge_k(PeerTable pt, const ytk_split* __restrict__ src, size_t area_off, size_t slot_bytes,
@@ -145,12 +139,6 @@ cudaError_t launch_peer_allreduce(const PeerTable& pt, const void* src, size_t a
                                   int flag_set, unsigned long long epoch, long long* out, int* err, cudaStream_t st) {
     peer_allreduce_k<<<1, 256, 0, st>>>(pt, static_cast<const unsigned long long*>(src), area_off, slot_bytes, words, flag_set,
                                         epoch, out, err);
-    return cudaGetLastError();
-}
-cudaError_t launch_peer_allgather(const PeerTable& pt, const void* src, size_t area_off, size_t slot_bytes, size_t bytes,
-                                  int flag_set, unsigned long long epoch, int* err, cudaStream_t st) {
-    peer_allgather_k<<<1, 256, 0, st>>>(pt, static_cast<const unsigned long long*>(src), area_off, slot_bytes, bytes, flag_set,
-                                        epoch, err);
     return cudaGetLastError();
 }
 cudaError_t launch_peer_allgather_merge(const PeerTable& pt, const ytk_split* src, size_t area_off, size_t slot_bytes, int m,

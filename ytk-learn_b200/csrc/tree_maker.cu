@@ -101,7 +101,7 @@ void free_all(ytk_gbdt* h) {
         for (int r = 0; r < h->world; r++)
             if (r != h->rank) { cudaIpcCloseMemHandle(h->pt.xchg[r]); cudaIpcCloseMemHandle(h->pt.hist[r]); }
     F(h->my_xchg); F(h->my_hist); F(h->d_peer_err);
-    h->t_items.release(); h->t_leaf_items.release(); h->t_segs.release(); h->t_tile_seg.release();
+    h->t_items.release();
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
     h->t_split_local.release(); h->t_split_all.release(); h->t_parts.release(); h->t_leaf.release(); h->t_hist_local.release();
     h->t_rs_out.release(); h->t_node_tot.release(); h->t_scan_done.release();
