@@ -271,7 +271,9 @@ int ytk_gbdt_score_values(ytk_gbdt *h, const int32_t *xbits, int64_t nrows, int3
  *   - the array is shared by all calls in the process: two calls that can run on the same GPU at
  *     the same time (different streams or threads) race on it -- keep them ordered;
  *   - the first call on each GPU also looks up the array's device address (the device that is
- *     current at the call); make that first call before any stream capture. */
+ *     current at the call); make that first call before any stream capture;
+ *   - `cuda_stream` must belong to the device that is current at the call (the array used is that
+ *     device's), and d_rows_in / d_rows_out must not overlap (refused with YTK_ERR_ARG). */
 int ytk_gbdt_partition_rows_static(const uint8_t *d_bins, int32_t stride, const int32_t *d_rows_in,
                                    int64_t n_rows, int32_t fid, float cond, int32_t *d_rows_out,
                                    int64_t *d_left_cnt, void *cuda_stream);

@@ -122,6 +122,8 @@ cudaError_t launch_csr_pack(const int64_t* row_ptr, const int32_t* fids, const i
                             const int32_t* nbins, const float* cuts, const int32_t* start, uint32_t* nz_out, int* bad_flag,
                             cudaStream_t st);
 cudaError_t launch_csr_to_dense(SparseRows sparse, int64_t row0, int64_t nrows, int32_t F, int32_t* out, cudaStream_t st);
+// per-device opt-ins of the histogram kernels (call with the device current, once per handle)
+cudaError_t hist_kernels_init();
 // rows one hist work item should cover so that `total_rows` split into about two waves of CTAs
 int64_t hist_rows_per_item(int64_t total_rows, int groups);
 
@@ -200,6 +202,7 @@ constexpr int kPeerFlagSets = 4;                   // counts, histogram staging,
 constexpr size_t kPeerFlagBytes = kPeerFlagSets * kMaxPeers * 8;
 struct PeerTable {
     int rank, world;
+    long long timeout_cycles;   // a wait for a peer gives up after this many SM clocks (YTK_GBDT_PEER_TIMEOUT_MS)
     char* xchg[16];        // every rank's exchange buffer: flags, then the slot areas
     char* hist[16];        // every rank's histogram staging buffer
 };

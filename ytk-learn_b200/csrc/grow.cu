@@ -115,12 +115,16 @@ private:
     // ---- small helpers -----------------------------------------------------------------
     // The host wait of a batch (optionally polled from user space; cudaEventSynchronize measured the same)
     int wait_event(cudaEvent_t ev) {
-        if (!h->spin_wait) { CK(cudaEventSynchronize(ev)); return YTK_OK; }
+        if (!h->spin_wait) { CK(cudaEventSynchronize(ev)); return peer_check(h, "make_tree"); }
         for (;;) {
             cudaError_t e = cudaEventQuery(ev);
-            if (e == cudaSuccess) return YTK_OK;
+            if (e == cudaSuccess) return peer_check(h, "make_tree");
             if (e != cudaErrorNotReady) CK(e);
         }
+    }
+    int wait_stream() {
+        CK(cudaStreamSynchronize(h->st));
+        return peer_check(h, "make_tree");
     }
     int new_handle() {
         iv.emplace_back(); ns.emplace_back(); exps.emplace_back(); nid_of.push_back(-1);
@@ -286,7 +290,7 @@ private:
             RET(finish_planned(0, 1));
             RET(wait_event(h->ev_level));
         } else {
-            CK(cudaStreamSynchronize(h->st));
+            RET(wait_stream());
         }
         h->arena.rewind();
         search_collect(h, 1, recs);
@@ -456,7 +460,7 @@ private:
             RET(wait_event(h->ev_level));   // the one host wait of the batch
         } else {
             b.tr.t_queued = now_ms();
-            CK(cudaStreamSynchronize(h->st));        // the one host wait of the batch
+            RET(wait_stream());                      // the one host wait of the batch
         }
         b.tr.t_done = now_ms();
         T->max_batch_ms = std::max(T->max_batch_ms, b.tr.t_done - b.tr.t_pop);
@@ -502,7 +506,7 @@ private:
         }
         b.tr.t_part = now_ms();
         if (!deferred) {                        // the host needs the counts before it can go on
-            CK(cudaStreamSynchronize(h->st));
+            RET(wait_stream());
             h->arena.rewind();
             partition_collect(h, m, cl, cg);
             for (int k = 0; k < m; k++) {
@@ -749,10 +753,8 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     RET(grower.grow(gid, fea_index, n_fea, row_mask));
 
     if (h->peer_mode) {
-        int perr = 0;
-        CK(cudaMemcpyAsync(&perr, h->d_peer_err, sizeof(int), cudaMemcpyDeviceToHost, h->st));
         CK(cudaStreamSynchronize(h->st));
-        if (perr) return fail(YTK_ERR_NCCL, "make_tree: a peer GPU did not reach a collective within 3 s");
+        RET(peer_check(h, "make_tree"));
     }
     if (h->trace) {
         double prev_done = 0;

@@ -401,6 +401,12 @@ cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t 
     return cudaGetLastError();
 }
 
+// The 128 KB of dynamic shared memory are an opt-in PER DEVICE: called by set_bins with the handle's
+// device current (one process may drive several GPUs, one thread each).
+cudaError_t hist_kernels_init() {
+    return cudaFuncSetAttribute(hist_build_k, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemBytes);
+}
+
 int64_t hist_rows_per_item(int64_t total_rows, int groups) {
     // one CTA per SM (128 KB of shared memory); aim at about two waves over all feature groups,
     // never less than 4 sweeps of the CTA (4096 rows) per item so zeroing + flushing stays small
@@ -417,13 +423,6 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
                               const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
                               const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st) {
     if (n_items <= 0) return cudaSuccess;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(hist_build_k, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             kHistSmemBytes);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
     dim3 grid((unsigned)n_items, (unsigned)(S8 / kGroup));
     return launch_chain(hist_build_k, grid, dim3(kHistThreads), kHistSmemBytes, st, bins, S8, gq, rowidx0, rowidx1, items, F, group_mask,
                                                              nbins, feat_owner, feat_inner, owner_stride, seg_out,

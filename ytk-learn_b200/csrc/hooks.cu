@@ -17,6 +17,9 @@ int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n
     RET(set_features(h, fea_index, n_fea, &first_owned, nullptr));
     RET(quantize_grads(h, gid));
     int64_t n = rows ? n_rows : h->N;
+    // this hook overwrites the fixed-point gradients (and, with a row list, the row-id buffers) the last
+    // tree's partition lives in: get_positions / update_scores must not use them afterwards
+    h->tree_made = false; h->leaf_ranges.clear(); h->last_tree.clear(); h->last_gid = -1;
     if (rows && n > 0) {
         for (int64_t i = 0; i < n; i++)
             if (rows[i] < 0 || rows[i] >= h->N) return fail(YTK_ERR_ARG, "build_hist: row %d out of range", rows[i]);
@@ -140,6 +143,7 @@ int ytk_gbdt_partition_rows(ytk_gbdt* h, const int32_t* rows, int64_t n_rows, in
     for (int64_t i = 0; i < n_rows; i++)
         if (rows[i] < 0 || rows[i] >= h->N) return fail(YTK_ERR_ARG, "partition_rows: row %d out of range", rows[i]);
     CK(cudaSetDevice(h->device));
+    h->tree_made = false; h->leaf_ranges.clear(); h->last_tree.clear(); h->last_gid = -1;      // the row-id buffers are overwritten
     if (n_rows > 0) CK(cudaMemcpyAsync(h->d_rowidx[0], rows, n_rows * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
     std::vector<ytk::SplitSeg> sg(1);
     sg[0] = {0, (long long)n_rows, 0, fid, cond, 0, 0, h->wide_index[fid] + 1};

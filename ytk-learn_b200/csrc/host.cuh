@@ -335,7 +335,8 @@ struct ytk_gbdt {
     int peer_cap_nodes = 0;                  // nodes per batch the exchange slots can hold
     size_t off_counts = 0, off_recs = 0, off_leaf = 0, slot_counts = 0, slot_recs = 0, slot_leaf = 0;
     unsigned long long epoch[ytk::kPeerFlagSets] = {0, 0, 0, 0};
-    int* d_peer_err = nullptr;
+    int* d_peer_err = nullptr;               // mapped host memory: set by a peer kernel that gave up waiting
+    double peer_timeout_ms = 10000.0;        // YTK_GBDT_PEER_TIMEOUT_MS
 
     // §8(f) row 1 state
     float* d_score = nullptr; float* d_y = nullptr; float* d_w = nullptr; float* d_init = nullptr;
@@ -415,6 +416,8 @@ void add_row_items(std::vector<ytk::RowItem>& items, const Interval& v, int seg,
 void add_deferred_items(std::vector<ytk::RowItem>& items, const Interval& parent, int child_buf, int seg, int cseg,
                         int64_t rows_per_item, int world);
 int peer_setup(ytk_gbdt* h);
+// after a host wait: did a peer kernel give up?  Reports (and clears) the flag, so the handle stays usable.
+int peer_check(ytk_gbdt* h, const char* where);
 bool peer_ok(const ytk_gbdt* h, int m);
 int blob_commit_to(ytk_gbdt* h, const Blob& bl, char** d_buf, size_t* cap);
 int blob_commit(ytk_gbdt* h, const Blob& bl);

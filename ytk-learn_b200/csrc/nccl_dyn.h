@@ -6,6 +6,8 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <mutex>
+
 namespace ytk {
 
 struct NcclApi {
@@ -20,17 +22,22 @@ struct NcclApi {
                               cudaStream_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
 
+    // Several threads create their handles at the same time (ncclCommInitRank blocks until every rank
+    // has joined), so loading is serialised and `lib` is published only once every symbol is bound.
+    std::mutex mu;
     bool load(const char** why) {
+        std::lock_guard<std::mutex> lk(mu);
         if (lib) return true;
+        void* l = nullptr;
         const char* names[] = {"libnccl.so.2", "libnccl.so"};
         for (const char* n : names) {
-            lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
-            if (lib) break;
+            l = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+            if (l) break;
         }
-        if (!lib) { *why = "libnccl.so.2 not found"; return false; }
+        if (!l) { *why = "libnccl.so.2 not found"; return false; }
 #define YTK_NCCL_SYM(field, sym)                                              \
-    field = reinterpret_cast<decltype(field)>(dlsym(lib, sym));               \
-    if (!field) { *why = "missing NCCL symbol " sym; lib = nullptr; return false; }
+    field = reinterpret_cast<decltype(field)>(dlsym(l, sym));                 \
+    if (!field) { *why = "missing NCCL symbol " sym; return false; }
         YTK_NCCL_SYM(GetUniqueId, "ncclGetUniqueId")
         YTK_NCCL_SYM(CommInitRank, "ncclCommInitRank")
         YTK_NCCL_SYM(CommDestroy, "ncclCommDestroy")
@@ -39,6 +46,7 @@ struct NcclApi {
         YTK_NCCL_SYM(AllReduce, "ncclAllReduce")
         YTK_NCCL_SYM(GetErrorString, "ncclGetErrorString")
 #undef YTK_NCCL_SYM
+        lib = l;
         return true;
     }
 };

@@ -21,7 +21,7 @@ namespace ytk { void set_last_error(const char* msg); }
 
 namespace {
 
-// ---- the work space: 4 MiB + 16.5 KiB, resident on every GPU that loads the library, until exit ----
+// ---- the work space: 4 MiB + 17 KiB, resident on every GPU that loads the library, until exit ----
 constexpr long long kStaticMaxRows = 1LL << 22;                                   // 4,194,304 rows
 constexpr int kStaticMaxTiles = (int)(kStaticMaxRows / ytk::kPartTile);           // 2048 tiles
 constexpr size_t kOffFlags = 0;                                                    // one byte per row
@@ -68,6 +68,9 @@ extern "C" int ytk_gbdt_partition_rows_static(const uint8_t* d_bins, int32_t str
                     (long long)n_rows, kStaticMaxRows);
     if (stride < 1 || fid < 0 || fid >= stride)
         return fail(YTK_ERR_ARG, "partition_rows_static: fid %d not in [0, stride %d)", fid, stride);
+    // the scatter reads the input list while other CTAs already write the output list
+    if (n_rows > 0 && d_rows_in < d_rows_out + n_rows && d_rows_out < d_rows_in + n_rows)
+        return fail(YTK_ERR_ARG, "partition_rows_static: the input and output row lists overlap");
 
     int dev = -1;
     cudaError_t e = cudaGetDevice(&dev);
@@ -106,6 +109,8 @@ extern "C" int ytk_gbdt_partition_rows_static(const uint8_t* d_bins, int32_t str
     ytk::SplitSeg v;
     v.begin = 0; v.end = n_rows; v.buf = 0; v.fid = fid; v.cond = cond; v.tile0 = 0; v.ntiles = n_tiles; v.wide = 0;
     static_begin_k<<<1, 1, 0, st>>>(seg, v);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(YTK_ERR_CUDA, "partition_rows_static: launch: %s", cudaGetErrorString(e));
     // buffer 0 is the caller's input list (only read when the segment's source is buffer 0),
     // buffer 1 its output list
     e = ytk::launch_partition(d_bins, stride, /*row-major*/ 0, ytk::WideCols{nullptr, 0, nullptr}, const_cast<int32_t*>(d_rows_in), d_rows_out, seg, 1, tile_seg, n_tiles,

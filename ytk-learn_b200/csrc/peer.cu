@@ -52,7 +52,11 @@ __device__ __forceinline__ bool peer_wait(const PeerTable& pt, int flag_set, uns
         const unsigned long long* f = reinterpret_cast<const unsigned long long*>(pt.xchg[pt.rank]) + flag_set * kMaxPeers + threadIdx.x;
         const long long t0 = clock64();
         while (ld_acquire_sys(f) < epoch) {
-            if (clock64() - t0 > 6000000000ll) { s_ok = 0; *err = 1; break; }     // ~3 s: a peer died
+            if (clock64() - t0 > pt.timeout_cycles) {                              // a peer died or hangs
+                s_ok = 0;
+                *reinterpret_cast<volatile int*>(err) = 1;                         // (mapped host memory: the host reads it at its next wait)
+                break;
+            }
             __nanosleep(100);
         }
     }

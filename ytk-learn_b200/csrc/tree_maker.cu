@@ -100,7 +100,8 @@ void free_all(ytk_gbdt* h) {
     if (h->peer_mode)
         for (int r = 0; r < h->world; r++)
             if (r != h->rank) { cudaIpcCloseMemHandle(h->pt.xchg[r]); cudaIpcCloseMemHandle(h->pt.hist[r]); }
-    F(h->my_xchg); F(h->my_hist); F(h->d_peer_err);
+    F(h->my_xchg); F(h->my_hist);
+    if (h->d_peer_err) cudaFreeHost(h->d_peer_err);
     h->t_items.release();
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
     h->t_split_local.release(); h->t_split_all.release(); h->t_parts.release(); h->t_leaf.release(); h->t_hist_local.release();
@@ -231,6 +232,7 @@ int peer_setup(ytk_gbdt* h) {
     h->peer_mode = false;
     if (h->world < 2 || h->world > 16) return YTK_OK;
     if (const char* e = getenv("YTK_GBDT_NO_PEER")) if (atoi(e) != 0) return YTK_OK;
+    if (const char* e = getenv("YTK_GBDT_PEER_TIMEOUT_MS")) h->peer_timeout_ms = std::max(1.0, atof(e));
     const int cap = 4096;
     h->peer_cap_nodes = cap;
     h->slot_counts = (size_t)cap * sizeof(ytk::PartitionCounts);
@@ -243,33 +245,41 @@ int peer_setup(ytk_gbdt* h) {
     const size_t local_len = (size_t)h->seg_max * h->world;
     size_t hist_words = std::max<size_t>(local_len * 256, (size_t(128) << 20) / 8);      // >= 256 nodes, >= 128 MB
     hist_words = std::min<size_t>(hist_words, std::max<size_t>(local_len * 2, (size_t(1) << 30) / 8));
+    // Every rank goes through BOTH agreements below whatever fails locally: a rank that returned early
+    // would leave the others hanging in the collective.  Local failures only clear `ok`.
     int ok = 1;
     cudaIpcMemHandle_t mine[2];
+    memset(mine, 0, sizeof(mine));
     if (cudaMalloc(&h->my_xchg, xchg_bytes) != cudaSuccess || cudaMalloc(&h->my_hist, hist_words * 8) != cudaSuccess ||
-        cudaMalloc(&h->d_peer_err, sizeof(int)) != cudaSuccess)
+        cudaHostAlloc((void**)&h->d_peer_err, sizeof(int), cudaHostAllocMapped) != cudaSuccess)
         ok = 0;
     if (ok) {
-        cudaMemset(h->my_xchg, 0, xchg_bytes);
-        cudaMemset(h->d_peer_err, 0, sizeof(int));
-        if (cudaIpcGetMemHandle(&mine[0], h->my_xchg) != cudaSuccess || cudaIpcGetMemHandle(&mine[1], h->my_hist) != cudaSuccess)
+        *h->d_peer_err = 0;
+        if (cudaMemset(h->my_xchg, 0, xchg_bytes) != cudaSuccess ||
+            cudaIpcGetMemHandle(&mine[0], h->my_xchg) != cudaSuccess || cudaIpcGetMemHandle(&mine[1], h->my_hist) != cudaSuccess)
             ok = 0;
     }
     cudaGetLastError();
     // exchange the handles (and learn whether everybody got this far) over NCCL, once
     const size_t rec = sizeof(mine) + 8;
     char* d_send = nullptr; char* d_recv = nullptr;
-    CK(cudaMalloc(&d_send, rec));
-    CK(cudaMalloc(&d_recv, rec * h->world));
-    std::vector<char> send(rec, 0), recv(rec * h->world);
+    std::vector<char> send(rec, 0), recv(rec * h->world, 0);
     if (ok) memcpy(send.data(), mine, sizeof(mine));
     long long okv = ok;
     memcpy(send.data() + sizeof(mine), &okv, 8);
-    CK(cudaMemcpy(d_send, send.data(), rec, cudaMemcpyHostToDevice));
-    NK(ytk::nccl_api().AllGather(d_send, d_recv, rec, ncclChar, h->comm, h->st));
-    CK(cudaStreamSynchronize(h->st));
-    CK(cudaMemcpy(recv.data(), d_recv, rec * h->world, cudaMemcpyDeviceToHost));
+    // (these two small allocations are needed for the agreement itself: without them nothing can be agreed)
+    CK(cudaMalloc(&d_send, rec));
+    CK(cudaMalloc(&d_recv, rec * h->world));
+    cudaError_t ce = cudaMemcpy(d_send, send.data(), rec, cudaMemcpyHostToDevice);
+    ncclResult_t nr = ytk::nccl_api().AllGather(d_send, d_recv, rec, ncclChar, h->comm, h->st);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(h->st);
+    if (ce == cudaSuccess) ce = cudaMemcpy(recv.data(), d_recv, rec * h->world, cudaMemcpyDeviceToHost);
+    if (ce != cudaSuccess || nr != ncclSuccess) ok = 0;
     for (int r = 0; r < h->world; r++) { long long v; memcpy(&v, recv.data() + r * rec + sizeof(mine), 8); if (!v) ok = 0; }
     h->pt.rank = h->rank; h->pt.world = h->world;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, h->device);
+    h->pt.timeout_cycles = (long long)(h->peer_timeout_ms * (khz > 0 ? khz : 2000000));
     int opened = 0;
     for (int r = 0; r < h->world && ok; r++) {
         if (r == h->rank) { h->pt.xchg[r] = h->my_xchg; h->pt.hist[r] = h->my_hist; continue; }
@@ -287,11 +297,13 @@ int peer_setup(ytk_gbdt* h) {
     }
     // second agreement: did every rank manage to open every peer?
     okv = ok;
-    CK(cudaMemcpy(d_send, &okv, 8, cudaMemcpyHostToDevice));
-    NK(ytk::nccl_api().AllReduce(d_send, d_send, 1, ncclInt64, ncclMin, h->comm, h->st));
-    CK(cudaStreamSynchronize(h->st));
-    CK(cudaMemcpy(&okv, d_send, 8, cudaMemcpyDeviceToHost));
+    ce = cudaMemcpy(d_send, &okv, 8, cudaMemcpyHostToDevice);
+    nr = ytk::nccl_api().AllReduce(d_send, d_send, 1, ncclInt64, ncclMin, h->comm, h->st);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(h->st);
+    if (ce == cudaSuccess) ce = cudaMemcpy(&okv, d_send, 8, cudaMemcpyDeviceToHost);
     cudaFree(d_send); cudaFree(d_recv);
+    if (nr != ncclSuccess) return fail(YTK_ERR_NCCL, "peer set-up: %s", ytk::nccl_api().GetErrorString(nr));
+    CK(ce);
     if (getenv("YTK_GBDT_VERBOSE"))
         fprintf(stderr, "ytk_gbdt[rank %d]: peer-memory collectives %s (local setup %s)\n", h->rank, okv ? "on" : "off", ok ? "ok" : "failed");
     if (!okv) {
@@ -302,6 +314,12 @@ int peer_setup(ytk_gbdt* h) {
     h->hist_cap_words = hist_words;
     h->peer_mode = true;
     return YTK_OK;
+}
+int peer_check(ytk_gbdt* h, const char* where) {
+    if (!h->peer_mode || !h->d_peer_err || !*reinterpret_cast<volatile int*>(h->d_peer_err)) return YTK_OK;
+    *reinterpret_cast<volatile int*>(h->d_peer_err) = 0;
+    return fail(YTK_ERR_NCCL, "%s: a peer GPU did not reach a collective within %.0f ms; this tree is abandoned", where,
+                h->peer_timeout_ms);
 }
 // may this batch of m nodes use the peer-memory collectives? (same answer on every rank)
 bool peer_ok(const ytk_gbdt* h, int m) {
@@ -632,6 +650,7 @@ int partition_nodes(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const s
                     std::vector<ytk::PartitionCounts>& local, std::vector<ytk::PartitionCounts>& global) {
     RET(partition_launch(h, src, col_stride, segs_in));
     CK(cudaStreamSynchronize(h->st));
+    RET(peer_check(h, "partition"));
     h->arena.rewind();
     partition_collect(h, (int)segs_in.size(), local, global);
     return YTK_OK;
@@ -775,6 +794,7 @@ static int set_bins_impl(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n
     if (h->rows_set) return fail(YTK_ERR_ARG, "set_bins: already called");
     if (n_rows > 0x7fffffffLL) return fail(YTK_ERR_ARG, "set_bins: %lld rows exceed int32 row ids", (long long)n_rows);
     CK(cudaSetDevice(h->device));
+    CK(ytk::hist_kernels_init());
     h->F = F; h->N = n_rows;
     h->start.assign(start, start + F + 1);
     h->nbins.resize(F);
