@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--cpu-rows", type=int, default=2_000_000, help="rows of the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-loss-wise", action="store_true", help="skip the extra loss-wise 255-leaf measurement")
+    ap.add_argument("--no-parity-check", action="store_true", help="skip the self-check after the timed region")
     ap.add_argument("--uniform-bins", action="store_true", help="experiment: every feature uniform over its bins")
     return ap.parse_args()
 
@@ -57,31 +58,10 @@ def tree_kwargs(a):
                 min_split_loss=0.0, l1=0.0, l2=0.0, learning_rate=0.1, min_split_samples=-1)
 
 
-def synth_bins(n, F, nb, seed, uniform=False):
-    """half the features uniform over the bins, half skewed (geometric),
-    generated directly as uint8 bins; labels depend on a few features so that trees have
-    real structure."""
-    rng = np.random.default_rng(seed)
-    x = np.empty((n, F), dtype=np.uint8)
-    for f in range(F):
-        if f % 2 == 0 or uniform:
-            x[:, f] = rng.integers(0, nb, size=n, dtype=np.uint8)
-        else:
-            x[:, f] = np.minimum(rng.geometric(0.04, size=n) - 1, nb - 1).astype(np.uint8)
-    z = np.zeros(n, dtype=np.float32)
-    for f in range(0, min(F, 12)):
-        z += (x[:, f].astype(np.float32) / nb - 0.5) * np.float32(((-1) ** f) * (1.0 + 0.3 * f))
-    z += (x[:, 1] > 20) * np.float32(0.8) - (x[:, 3] < 3) * np.float32(0.5)
-    p = 1.0 / (1.0 + np.exp(-z))
-    y = (rng.random(n, dtype=np.float32) < p).astype(np.float32)
-    return x, y
+import workloads as wl          # tests/workloads.py: the synthetic inputs of the BASELINE shapes
 
-
-def sigmoid_grads(score, y, out):
-    """SigmoidFunction (J/loss/SigmoidFunction.java:63-80) with the reference's float casts."""
-    p = (1.0 / (1.0 + np.exp(-score.astype(np.float64)))).astype(np.float32).astype(np.float64)
-    out[0::2] = (p - y).astype(np.float32)
-    out[1::2] = (p * (1.0 - p)).astype(np.float32)
+synth_bins = wl.c2_higgs        # (n, F, nb, seed, uniform=False) -> uint8 slots [n,F], labels
+sigmoid_grads = wl.sigmoid_grads
 
 
 class ClockSampler:
@@ -181,6 +161,101 @@ def cpu_baseline(a, xs, ys, steps=1, threads=None):
             "sample": "%d trees on the first %d of %d rows x %d features, W=%d emulated workers"
                       % (steps, n, xs.shape[0], a.features, cores),
             "seconds_per_tree_on_sample": secs / steps, "nodes": nodes}
+
+
+def _tree_digest(tree, fields):
+    import hashlib
+    hd = hashlib.sha256()
+    hd.update(np.int64(tree.n_nodes).tobytes())
+    for name, _ in fields:
+        hd.update(np.ascontiguousarray(getattr(tree, name)).tobytes())
+    return np.frombuffer(hd.digest(), dtype=np.uint8).copy()
+
+
+def parity_check(a, yb, torch, dist, world, rank, local, fresh_nccl_id, last_tree, rows_small=1_000_000):
+    """Outside every timer.  (1) every rank holds the same tree (all fields, byte for byte) and its root
+    counts the global rows; (2) on a second, small tree maker (rows_small rows per rank, same generator):
+    the N-rank tree and the concatenated per-row leaves equal the tree ONE GPU builds on the concatenated
+    rows (a world = 1 handle on rank 0), bit for bit, level-wise depth 8 and loss-wise 255 leaves; and
+    that tree equals the CPU oracle's (W = N emulated workers): structure, split features / intervals,
+    counts and per-row leaves exactly, values to 1e-5.  Returns a dict; "ok" False makes bench.py exit 1."""
+    res = {"ok": True, "checks": [], "rows_per_rank_small": rows_small}
+
+    def note(name, ok, detail=None):
+        res["checks"].append({"name": name, "ok": bool(ok), **({"detail": detail} if detail else {})})
+        res["ok"] = res["ok"] and bool(ok)
+
+    def all_ok(flag):                       # every rank learns whether any rank failed
+        if world == 1:
+            return flag
+        t = torch.tensor([1 if flag else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return bool(t.item())
+
+    # (1) the timed workload's last tree
+    dig = torch.from_numpy(_tree_digest(last_tree, yb.Tree.FIELDS)).cuda()
+    if world > 1:
+        allg = [torch.empty_like(dig) for _ in range(world)]
+        dist.all_gather(allg, dig)
+        same = all(bool(torch.equal(g, allg[0])) for g in allg)
+    else:
+        same = True
+    if rank == 0:
+        note("all_ranks_hold_the_same_tree", same)
+        note("root_counts_global_rows", int(last_tree.sample_cnt[0]) == a.rows * world,
+             "%d vs %d" % (int(last_tree.sample_cnt[0]), a.rows * world))
+
+    # (2) small second tree maker
+    n, F = rows_small, a.features
+    start = (np.arange(F + 1) * a.bins).astype(np.int32)
+    xs, ys = synth_bins(n, F, a.bins, 4321 + rank)
+    gp = np.empty(2 * n, np.float32)
+    sigmoid_grads(np.zeros(n, np.float32), ys, gp)
+    settings = {"level_depth8": dict(tree_kwargs(a), grow_policy="level", max_depth=8, max_leaf_cnt=-1),
+                "loss_255": dict(tree_kwargs(a), grow_policy="loss", max_depth=-1, max_leaf_cnt=255)}
+    for name, kw in settings.items():
+        tm = yb.GpuTreeMaker(yb.make_params(**kw), start, n, device=local, rank=rank, world=world,
+                             nccl_id=fresh_nccl_id())
+        tm.upload_rows(xs.astype(np.int32))
+        tm.set_grads(gp)
+        tree = tm.make(0)
+        pos = tm.get_positions()
+        tm.close()
+        if world > 1:
+            pos_t = torch.from_numpy(pos).cuda()
+            gathered = [torch.empty_like(pos_t) for _ in range(world)] if rank == 0 else None
+            dist.gather(pos_t, gathered, dst=0)
+        if rank == 0:
+            # the same rows on ONE GPU, and through the CPU oracle
+            xa = [xs] + [synth_bins(n, F, a.bins, 4321 + r)[0] for r in range(1, world)]
+            ya = [ys] + [synth_bins(n, F, a.bins, 4321 + r)[1] for r in range(1, world)]
+            x_all = np.concatenate(xa).astype(np.int32)
+            gp_all = np.empty(2 * n * world, np.float32)
+            sigmoid_grads(np.zeros(n * world, np.float32), np.concatenate(ya), gp_all)
+            pos_all = pos if world == 1 else np.concatenate([g.cpu().numpy() for g in gathered])
+            if world > 1:
+                one = yb.GpuTreeMaker(yb.make_params(**kw), start, n * world, device=local)
+                one.upload_rows(x_all)
+                one.set_grads(gp_all)
+                t1 = one.make(0)
+                p1 = one.get_positions()
+                one.close()
+                eq = t1.n_nodes == tree.n_nodes and all(
+                    np.array_equal(getattr(t1, f), getattr(tree, f), equal_nan=True) for f, _ in yb.Tree.FIELDS)
+                note(name + ":%d_ranks_equal_one_gpu_bit_for_bit" % world, eq and np.array_equal(p1, pos_all))
+            import oracle_binding as ob
+            from gpu_common import assert_same_tree
+            o, opos, _ = ob.make_tree(ob.make_params(**kw), x_all, gp_all, 0, start, W=max(world, 1),
+                                      threads=os.cpu_count() or 1)
+            try:
+                assert_same_tree(tree, o)
+                ok, why = np.array_equal(pos_all, opos), "per-row leaves"
+            except AssertionError as e:
+                ok, why = False, str(e)[:200]
+            note(name + ":equals_cpu_oracle_W%d" % world, ok, None if ok else why)
+            res.setdefault("nodes", {})[name] = int(tree.n_nodes)
+    res["ok"] = all_ok(res["ok"])
+    return res
 
 
 def config(a, world):
@@ -294,6 +369,7 @@ def main():
             agg["ts_build"] += ts.build_hist; agg["ts_split"] += ts.find_best_split
             agg["ts_part"] += ts.partition; agg["ts_total"] += ts.total; agg["ts_comm"] += ts.communicate_hist
             agg["d2h"] = sum(getattr(tree, nme).nbytes for nme, _ in yb.Tree.FIELDS)
+            last_tree = tree
     barrier()
     clocks = sampler.stop()
 
@@ -335,6 +411,11 @@ def main():
         loss_wise = {"ms_per_tree": t_lw / a.steps * 1e3, "nodes_per_tree": int(tree.n_nodes),
                      "host_waits_per_tree": tm.last_stats.batches + 1,
                      "what": "loss-wise growth, 255 leaves (the reference's experiment/higgs conf), same rows"}
+
+    pc = None
+    if not a.no_parity_check:
+        tm.close()
+        pc = parity_check(a, yb, torch, dist, world, rank, local, fresh_nccl_id, last_tree)
 
     vals = torch.tensor([agg["t_tree"], agg["t_e2e"], dev_round], dtype=torch.float64, device="cuda")
     sums = torch.tensor([agg["cells"]], dtype=torch.float64, device="cuda")
@@ -378,6 +459,7 @@ def main():
                          "launches_per_step": agg["hist_launches"] / a.steps,
                          "nodes_built_per_step": agg["built"] / a.steps},
             "clocks": clocks,
+            "parity_check": pc,
         }
         if not a.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(a, xs, ys, steps=1)
@@ -387,6 +469,8 @@ def main():
     tm.close()
     if world > 1:
         dist.destroy_process_group()
+    if pc is not None and not pc["ok"]:
+        sys.exit(1)
 
 
 if __name__ == "__main__":

@@ -126,25 +126,67 @@ double orc_calc_gain(const orc_params *p, double G, double H) {
 
 /* ------------------------------------------------------------------ A2 */
 
-/* Accumulation loop of HistogramBuilder.buildHist (J/data/gbdt/HistogramBuilder.java:69-90). */
-void orc_build_hist(const int32_t *x, int32_t S, const float *gp, int32_t K, int32_t gid,
-                    const int32_t *pos_idx, int64_t v1, int64_t v2,
-                    const int32_t *fea_index, int32_t n_fea, const int32_t *start,
-                    int32_t B, double *hist) {
+/* A "virtual" dense matrix for shapes whose dense int32 form does not fit in memory (BASELINE config 4:
+ * 10 000 features at 1 % density): rows are held as CSR (entries of a row sorted by feature) plus one
+ * default slot per feature, and x[row][fid] is looked up on the fly.  The loops below are still the
+ * reference's dense loops (every row visits every sampled feature); only the storage of x differs.
+ * Set once before orc_make_tree(x = NULL); read-only afterwards. */
+static struct { const int64_t *row_ptr; const int32_t *fids; const int32_t *slots; const int32_t *default_slot; } g_csr;
+void orc_set_virtual_csr(const int64_t *row_ptr, const int32_t *fids, const int32_t *slots, const int32_t *default_slot) {
+    g_csr.row_ptr = row_ptr; g_csr.fids = fids; g_csr.slots = slots; g_csr.default_slot = default_slot;
+}
+static int32_t csr_slot(int64_t row, int32_t fid) {
+    int64_t lo = g_csr.row_ptr[row], hi = g_csr.row_ptr[row + 1];
+    const int64_t end = hi;
+    while (lo < hi) {
+        int64_t mid = (lo + hi) >> 1;
+        if (g_csr.fids[mid] < fid) lo = mid + 1; else hi = mid;
+    }
+    return (lo < end && g_csr.fids[lo] == fid) ? g_csr.slots[lo] : g_csr.default_slot[fid];
+}
+
+/* Accumulation loop of HistogramBuilder.buildHist (J/data/gbdt/HistogramBuilder.java:69-90).
+ * x == NULL: the virtual matrix above, rows offset by row_base. */
+static void build_hist_rows(const int32_t *x, int32_t S, int64_t row_base, const float *gp, int32_t K, int32_t gid,
+                            const int32_t *pos_idx, int64_t v1, int64_t v2,
+                            const int32_t *fea_index, int32_t n_fea, const int32_t *start,
+                            int32_t B, double *hist) {
     for (int64_t i = 0; i < 2 * (int64_t)B; i++) hist[i] = 0;
     for (int64_t i = v1; i < v2; i++) {
         if (pos_idx[2 * i] < 0) continue;                       /* not sampled */
         int64_t row = pos_idx[2 * i + 1];
-        const int32_t *xr = x + row * S;
         int64_t gi = (row * K + gid) * 2;
         float g = gp[gi], h = gp[gi + 1];
-        for (int32_t k = 0; k < n_fea; k++) {
-            int32_t fid = fea_index[k];
-            int64_t b = ((int64_t)start[fid] + xr[fid]) * 2;
-            hist[b] += g;                                       /* float widened to double */
-            hist[b + 1] += h;
+        if (x) {
+            const int32_t *xr = x + row * S;
+            for (int32_t k = 0; k < n_fea; k++) {
+                int32_t fid = fea_index[k];
+                int64_t b = ((int64_t)start[fid] + xr[fid]) * 2;
+                hist[b] += g;                                   /* float widened to double */
+                hist[b + 1] += h;
+            }
+        } else {
+            const int64_t p0 = g_csr.row_ptr[row_base + row], p1 = g_csr.row_ptr[row_base + row + 1];
+            int64_t q = p0;
+            int32_t prev = -1;
+            for (int32_t k = 0; k < n_fea; k++) {
+                int32_t fid = fea_index[k];
+                if (fid < prev) q = p0;                         /* feaIndex is sorted in the reference (:449) */
+                prev = fid;
+                while (q < p1 && g_csr.fids[q] < fid) q++;
+                int32_t slot = (q < p1 && g_csr.fids[q] == fid) ? g_csr.slots[q] : g_csr.default_slot[fid];
+                int64_t b = ((int64_t)start[fid] + slot) * 2;
+                hist[b] += g;
+                hist[b + 1] += h;
+            }
         }
     }
+}
+void orc_build_hist(const int32_t *x, int32_t S, const float *gp, int32_t K, int32_t gid,
+                    const int32_t *pos_idx, int64_t v1, int64_t v2,
+                    const int32_t *fea_index, int32_t n_fea, const int32_t *start,
+                    int32_t B, double *hist) {
+    build_hist_rows(x, S, 0, gp, K, gid, pos_idx, v1, v2, fea_index, n_fea, start, B, hist);
 }
 
 /* ------------------------------------------------------------------ A5/A6 */
@@ -207,14 +249,19 @@ static int64_t sort_by_node_index(int32_t *pi, int64_t v1, int64_t v2, int32_t l
 
 /* SamplePositionData.resetPosition(trainData, nid, tree) (:115-133): strict `<` on a
  * float cond against an int slot. */
-int64_t orc_reset_position(int32_t *pos_idx, int64_t v1, int64_t v2, const int32_t *x,
-                           int32_t S, int32_t fid, float cond, int32_t left, int32_t right) {
+static int64_t reset_position_rows(int32_t *pos_idx, int64_t v1, int64_t v2, const int32_t *x,
+                                   int32_t S, int64_t row_base, int32_t fid, float cond, int32_t left, int32_t right) {
     for (int64_t i = v1; i < v2; i++) {
         int64_t row = pos_idx[2 * i + 1];
-        if ((float)x[row * S + fid] < cond) pos_idx[2 * i] = left;
+        int32_t slot = x ? x[row * S + fid] : csr_slot(row_base + row, fid);
+        if ((float)slot < cond) pos_idx[2 * i] = left;
         else pos_idx[2 * i] = right;
     }
     return sort_by_node_index(pos_idx, v1, v2, left, right);
+}
+int64_t orc_reset_position(int32_t *pos_idx, int64_t v1, int64_t v2, const int32_t *x,
+                           int32_t S, int32_t fid, float cond, int32_t left, int32_t right) {
+    return reset_position_rows(pos_idx, v1, v2, x, S, 0, fid, cond, left, right);
 }
 
 /* ------------------------------------------------------------------ A3' pool */
@@ -355,8 +402,8 @@ static double *sync_global_grad_sum(maker *m, int32_t nid, double *scratch) {
 #pragma omp parallel for num_threads(m->threads) if (m->threads > 1) schedule(static, 1)
     for (int32_t w = 0; w < m->W; w++) {
         int64_t v1 = m->iv[((int64_t)nid * m->W + w) * 2], v2 = m->iv[((int64_t)nid * m->W + w) * 2 + 1];
-        orc_build_hist(m->x + m->row_off[w] * m->S, m->S, m->gp + m->row_off[w] * m->K * 2, m->K, m->gid,
-                       m->pos[w], v1, v2, m->fea_index, m->n_fea, m->start, m->B, m->local[w]);
+        build_hist_rows(m->x ? m->x + m->row_off[w] * m->S : NULL, m->S, m->row_off[w], m->gp + m->row_off[w] * m->K * 2,
+                        m->K, m->gid, m->pos[w], v1, v2, m->fea_index, m->n_fea, m->start, m->B, m->local[w]);
     }
     for (int32_t w = 0; w < m->W; w++)
         rows += m->iv[((int64_t)nid * m->W + w) * 2 + 1] - m->iv[((int64_t)nid * m->W + w) * 2];
@@ -531,8 +578,8 @@ int orc_make_tree(const orc_params *p, int32_t W, const int64_t *row_off,
 #pragma omp parallel for num_threads(m.threads) if (m.threads > 1) schedule(static, 1)
         for (int32_t w = 0; w < W; w++) {
             int64_t v1 = m.iv[((int64_t)nid * W + w) * 2], v2 = m.iv[((int64_t)nid * W + w) * 2 + 1];
-            int64_t lc = orc_reset_position(m.pos[w], v1, v2, x + row_off[w] * S, S, out->fid[nid],
-                                            out->node_info[nid], l, r);
+            int64_t lc = reset_position_rows(m.pos[w], v1, v2, x ? x + row_off[w] * S : NULL, S, row_off[w], out->fid[nid],
+                                             out->node_info[nid], l, r);
             m.iv[((int64_t)l * W + w) * 2] = v1; m.iv[((int64_t)l * W + w) * 2 + 1] = v1 + lc;
             m.iv[((int64_t)r * W + w) * 2] = v1 + lc; m.iv[((int64_t)r * W + w) * 2 + 1] = v2;
         }

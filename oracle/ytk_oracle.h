@@ -89,6 +89,12 @@ void orc_enumerate_split(const orc_params *p, const double *hist, const int32_t 
                          int32_t fid, double sumG, double sumH, float root_gain,
                          orc_split *best);
 
+/* Shapes whose dense int32 matrix does not fit in memory (10 000 features at 1 % density): hold the rows
+ * as CSR (entries sorted by feature inside a row) + one default slot per feature and call
+ * orc_make_tree with x = NULL; x[row][fid] is then looked up on the fly by the same dense loops.
+ * Pass NULLs to clear.  Not thread-safe against a concurrent orc_make_tree. */
+void orc_set_virtual_csr(const int64_t *row_ptr, const int32_t *fids, const int32_t *slots, const int32_t *default_slot);
+
 /* SamplePositionData.resetPosition + sortByNodeIndex
  * (J/data/gbdt/SamplePositionData.java:115-165): returns leftCnt. */
 int64_t orc_reset_position(int32_t *pos_idx, int64_t v1, int64_t v2, const int32_t *x,

@@ -31,6 +31,10 @@ KAT2_PARAMS = dict(max_depth=6, max_leaf_cnt=128, min_split_samples=-1, grow_pol
                    l1=0.0, l2=1.0, histogram_pool_capacity=-1.0, learning_rate=0.1, class_num=6)
 
 
+KAT2_TREE_SIZES = [[7, 17, 5, 21, 3, 3], [5, 17, 5, 15, 3, 3], [9, 19, 5, 15, 5, 3], [7, 17, 5, 17, 5, 3], [5, 21, 5, 17, 5, 3]]
+KAT2_ROWS = [0, 14, 23, 50, 52, 69]      # 0-based rows of dermatology.test.ytklearn that yield KAT2_PRED
+
+
 def load_kat1():
     """Agaricus demo inputs: from the committed fixture (made by tests/golden/make_golden.py),
     or straight from the reference's demo data when it is mounted."""

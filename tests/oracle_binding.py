@@ -69,6 +69,8 @@ def lib():
         _lib.orc_normalize_max_leaf_cnt.restype = C.c_int32
         _lib.orc_split_need_replace.restype = C.c_int
         _lib.orc_split_need_replace.argtypes = [C.c_void_p, C.c_float, C.c_int32]
+        _lib.orc_set_virtual_csr.restype = None
+        _lib.orc_set_virtual_csr.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib.orc_enumerate_split.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                              C.c_double, C.c_double, C.c_float, C.c_void_p]
     return _lib
@@ -202,10 +204,19 @@ def reset_position(pos_idx, v1, v2, x, fid, cond, left, right):
 
 
 def make_tree(p, x, gp, gid, start, fea_index=None, W=1, row_off=None, row_mask=None,
-              threads=1, want_positions=True):
-    """DataParallelTreeMaker.make with W emulated workers. Returns (Tree, node_of_row, info)."""
-    x = np.ascontiguousarray(x, dtype=np.int32)
-    n, S = x.shape
+              threads=1, want_positions=True, csr=None):
+    """DataParallelTreeMaker.make with W emulated workers. Returns (Tree, node_of_row, info).
+    csr = (row_ptr int64, fids int32, slots int32, default_slot int32) with x = None: the rows are
+    looked up in CSR storage by the same dense loops (oracle/ytk_oracle.h: orc_set_virtual_csr)."""
+    if csr is not None:
+        assert x is None
+        rp, cf, cs, dflt = (np.ascontiguousarray(csr[0], np.int64), np.ascontiguousarray(csr[1], np.int32),
+                            np.ascontiguousarray(csr[2], np.int32), np.ascontiguousarray(csr[3], np.int32))
+        lib().orc_set_virtual_csr(_p(rp), _p(cf), _p(cs), _p(dflt))
+        n, S = len(rp) - 1, len(dflt)
+    else:
+        x = np.ascontiguousarray(x, dtype=np.int32)
+        n, S = x.shape
     gp = np.ascontiguousarray(gp, dtype=np.float32)
     start = np.ascontiguousarray(start, dtype=np.int32)
     F = len(start) - 1
@@ -224,11 +235,13 @@ def make_tree(p, x, gp, gid, start, fea_index=None, W=1, row_off=None, row_mask=
     miss = C.c_int32(0)
     ts = np.zeros(4, dtype=np.float64)
     cells = C.c_double(0)
-    rc = lib().orc_make_tree(C.byref(cp), C.c_int32(W), _p(row_off), _p(x), C.c_int32(S),
+    rc = lib().orc_make_tree(C.byref(cp), C.c_int32(W), _p(row_off), _p(x) if csr is None else None, C.c_int32(S),
                              C.c_int32(F), _p(gp), C.c_int32(gid), _p(start), _p(fea_index),
                              C.c_int32(len(fea_index)), _p(row_mask), C.byref(ot),
                              _p(node_of_row), C.byref(miss), C.c_int32(threads), _p(ts),
                              C.byref(cells))
+    if csr is not None:
+        lib().orc_set_virtual_csr(None, None, None, None)
     if rc != 0:
         raise RuntimeError("orc_make_tree failed rc=%d" % rc)
     t.n_nodes = ot.n_nodes

@@ -254,6 +254,53 @@ def test_a456_find_split_random_hist(seed):
     np.testing.assert_allclose(got.root_gain, rg, rtol=REL)
 
 
+@pytest.mark.parametrize("lead", [1, 3, 40])
+def test_a5_bins_with_gradient_but_zero_hessian_before_the_first_real_bin(lead):
+    """enumerateSplit tests "left is initialised" with GradStats.empty() = (H == 0)
+    (J/optimizer/gbdt/DataParallelTreeMaker.java:598-637, J/data/gbdt/GradStats.java:73-75): while the
+    accumulated left hessian is still exactly 0 -- leading bins with g != 0 and h == 0 -- bins keep being
+    added and `last` advances without any candidate being evaluated; the first candidate comes at the
+    second bin whose prefix has H != 0.  Features: (0) `lead` degenerate bins first, (1) degenerate bins
+    in the middle (prefix H already > 0: ordinary candidates), (2) only degenerate bins, (3) a degenerate
+    bin whose g cancels a later one."""
+    rng = np.random.default_rng(lead)
+    nb = 64
+    F = 4
+    start = (np.arange(F + 1) * nb).astype(np.int32)
+    hist = np.zeros((F, nb, 2))
+    # feature 0: degenerate lead, then real bins (some empty in between)
+    hist[0, :lead, 0] = rng.normal(size=lead) + 3.0
+    real = np.arange(lead, nb)[rng.random(nb - lead) < 0.6]
+    hist[0, real, 0] = rng.normal(size=len(real))
+    hist[0, real, 1] = rng.random(len(real)) + 0.1
+    # feature 1: real bins with a few (g != 0, h == 0) bins in the middle
+    hist[1, :, 0] = rng.normal(size=nb)
+    hist[1, :, 1] = rng.random(nb) + 0.1
+    hist[1, 10:14, 1] = 0.0
+    hist[1, 30, :] = 0.0
+    # feature 2: nothing but degenerate bins
+    hist[2, ::3, 0] = rng.normal(size=len(range(0, nb, 3)))
+    # feature 3: +g, h == 0 first; -g later inside a real bin
+    hist[3, 0] = (5.0, 0.0)
+    hist[3, 5] = (-5.0, 1.0)
+    hist[3, 9] = (1.0, 2.0)
+    hist[3, 20] = (-2.0, 1.5)
+    hist = hist.reshape(-1)
+    for kw in (dict(KW, min_child_hessian_sum=0.0, l2=0.0), dict(KW, min_child_hessian_sum=0.5, l2=1.0)):
+        tm = yb.GpuTreeMaker(yb.make_params(**kw), start, 8)
+        p = ob.make_params(**kw)
+        for fea in ([0], [1], [2], [3], [0, 1, 2, 3], [2, 3]):
+            fea = np.array(fea, np.int32)
+            got = tm.find_split(hist, 1000, fea_index=fea)
+            want, G, H, rg = _oracle_split(p, hist, start, 1000, fea)
+            assert (got.fid, got.lo, got.hi) == (want[1], want[2], want[3]), (list(fea), got.as_tuple(), want)
+            if np.isfinite(want[0]):
+                assert abs(got.loss_chg - want[0]) <= REL * max(1.0, abs(want[0]))
+            else:
+                assert got.loss_chg == want[0]
+        tm.close()
+
+
 def test_a6_tie_rule_smallest_feature_then_lowest_bin():
     # three identical features: every candidate ties across features -> fid 0, first best bin
     nb = 6
@@ -409,8 +456,10 @@ def test_kat2_dermatology_prediction_on_gpu():
     d = kat.load_kat2()
     pred, trees = kat.run_kat2(_gpu_maker(d, kat.KAT2_PARAMS), d)
     err = np.abs(pred - np.array(kat.KAT2_PRED)[None, :]).max(axis=1)
-    assert err.min() < 1e-9, err.min()   # 30-bit fixed-point gradients; north_star bar is 1e-5 relative
-    assert [[t.n_nodes for t in g] for g in trees][0] == [7, 17, 5, 21, 3, 3]
+    # 30-bit fixed-point gradients; north_star bar is 1e-5 relative.  All six rows the README line belongs
+    # to, and the tree sizes of all five rounds.
+    assert list(np.where(err < 1e-9)[0]) == kat.KAT2_ROWS, (np.where(err < 1e-9)[0], err.min())
+    assert [[t.n_nodes for t in g] for g in trees] == kat.KAT2_TREE_SIZES
 
 
 # ---------------------------------------------------------------- batching and fixed-point width
