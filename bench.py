@@ -339,7 +339,8 @@ def main():
     score = np.zeros(n, np.float32)
     h2d = gp.nbytes
     agg = dict(t_tree=0.0, t_e2e=0.0, cells=0.0, rows=0.0, rows_idx=0.0, built=0, gpu_hist_ms=0.0, launches=0,
-               d2h=0, nodes=0, ts_build=0.0, ts_split=0.0, ts_part=0.0, ts_total=0.0, hist_launches=0, ts_comm=0.0)
+               d2h=0, nodes=0, ts_build=0.0, ts_split=0.0, ts_part=0.0, ts_total=0.0, hist_launches=0, ts_comm=0.0,
+               ts_init=0.0, ts_sync=0.0, ts_enq=0.0, ts_wait=0.0, ts_gpu=0)
     sampler = ClockSampler(local)                         # started now, used from the first timed step on
     for step in range(a.warmup + a.steps):
         sigmoid_grads(score, ys, gp)                      # the Java side's job, outside the hot path
@@ -368,6 +369,8 @@ def main():
             agg["slow_steps"] = agg.get("slow_steps", []) + [round((t2 - t1) * 1e3, 2)]
             agg["ts_build"] += ts.build_hist; agg["ts_split"] += ts.find_best_split
             agg["ts_part"] += ts.partition; agg["ts_total"] += ts.total; agg["ts_comm"] += ts.communicate_hist
+            agg["ts_init"] += ts.init_stats; agg["ts_sync"] += ts.sync_best_split
+            agg["ts_enq"] += ts.enqueue_ms; agg["ts_wait"] += ts.host_wait_ms; agg["ts_gpu"] = ts.stage_times_from_gpu
             agg["d2h"] = sum(getattr(tree, nme).nbytes for nme, _ in yb.Tree.FIELDS)
             last_tree = tree
     barrier()
@@ -445,6 +448,9 @@ def main():
             "gpu_launches": agg["launches"], "peer_memory_collectives": used_peer,
             "time_stats_ms_per_tree": {"build_hist": agg["ts_build"] / a.steps, "find_best_split": agg["ts_split"] / a.steps,
                                        "partition": agg["ts_part"] / a.steps, "total": agg["ts_total"] / a.steps,
+                                       "init_stats": agg["ts_init"] / a.steps, "sync_best_split": agg["ts_sync"] / a.steps,
+                                       "stage_times_are_cuda_event_times": bool(agg["ts_gpu"]),
+                                       "host_enqueue": agg["ts_enq"] / a.steps, "host_wait": agg["ts_wait"] / a.steps,
                                        "collectives_gpu": agg["ts_comm"] / a.steps,
                                        "host_waits": host_waits, "device_allocs_in_timed_steps": agg.get("allocs", 0),
                                        "longest_batch_ms": agg.get("max_batch", 0.0),

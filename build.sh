@@ -1,9 +1,24 @@
 #!/bin/bash
-# Builds libytkgbdt.so (CUDA kernels + C ABI) for sm_100a, in-tree.
+# Builds libytkgbdt.so (CUDA kernels + C ABI) for sm_100a, in-tree.  Objects are compiled in parallel into
+# build/ and only when a source or header is newer (FORCE=1 rebuilds everything).
 set -e
 cd "$(dirname "$0")"
 OUT=ytk-learn_b200/libytkgbdt.so
-nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 \
-     -Xcompiler -fPIC,-ffp-contract=off,-Wall -shared -I include -I ytk-learn_b200/csrc \
-     ${YTK_NVCC_EXTRA} -o "$OUT" ytk-learn_b200/csrc/rows.cu ytk-learn_b200/csrc/hist.cu ytk-learn_b200/csrc/split.cu ytk-learn_b200/csrc/partition.cu ytk-learn_b200/csrc/boost_kernels.cu ytk-learn_b200/csrc/peer.cu ytk-learn_b200/csrc/tree_maker.cu ytk-learn_b200/csrc/grow.cu ytk-learn_b200/csrc/boost.cu ytk-learn_b200/csrc/hooks.cu ytk-learn_b200/csrc/no_alloc.cu -ldl
+SRC=ytk-learn_b200/csrc
+FILES="rows hist split partition level boost_kernels peer tree_maker grow engine boost hooks no_alloc"
+FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-ffp-contract=off,-Wall -I include -I $SRC ${YTK_NVCC_EXTRA}"
+mkdir -p build
+newest_hdr=$(ls -t $SRC/*.cuh $SRC/*.h include/*.h build.sh | head -1)
+pids=()
+for f in $FILES; do
+  o=build/$f.o
+  if [ -n "$FORCE" ] || [ ! -f $o ] || [ $SRC/$f.cu -nt $o ] || [ $newest_hdr -nt $o ]; then
+    nvcc $FLAGS -c $SRC/$f.cu -o $o &
+    pids+=($!)
+  fi
+done
+for p in "${pids[@]}"; do wait $p; done
+objs=""
+for f in $FILES; do objs="$objs build/$f.o"; done
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -o "$OUT" $objs -ldl
 echo "built $OUT"

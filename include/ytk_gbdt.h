@@ -91,6 +91,11 @@ typedef struct {
     int32_t batches;          /* batches of launches = host waits after the root (a level, a node, or a look-ahead set) */
     int32_t device_allocs;    /* cudaMalloc calls made by this call (histogram slots, grown tables): 0 once warmed up */
     double  max_batch_ms;     /* longest single batch, enqueue to host wake-up (a stall shows up here) */
+    double  enqueue_ms;       /* device-driven level loop: host time to queue the whole tree ...       */
+    double  host_wait_ms;     /* ... and its one wait for the device                                    */
+    int32_t stage_times_from_gpu; /* 1: build_hist .. partition above are CUDA-event times of the stages on the
+                                     device (they add up to the tree's device time); 0: host wall-clock per stage */
+    int32_t reserved;
 } ytk_time_stats;
 
 /* One best split: SplitInfo (J/data/gbdt/SplitInfo.java:36-70) plus the node totals the

@@ -68,7 +68,7 @@ constexpr int kMaxSparseFeatures = 65536;
 // cseg >= 0: sample_cnt is the global row count of the smaller (which = 0) / larger (which = 1)
 // child of split segment cseg, read from the device counts
 struct ScanNode { const long long* hist; long long sample_cnt; int cseg; int which; };
-struct SplitPart { float lc; int fid, lo, hi; };     // best split of one slice of a node's features
+struct alignas(16) SplitPart { float lc; int fid, lo, hi; long long lh; long long pad; };   // best split of one slice of a node's features (lh: hessian left of it, fixed point)
 struct SubItem { const long long* parent; const long long* small; long long* out; };
 struct PosItem { long long begin, end; int buf; int nid; };
 struct LeafItem { long long begin, end; int buf; float value; };      // rows of one leaf and its value
@@ -101,6 +101,14 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
                               const uint32_t* group_mask, const int32_t* nbins, const int32_t* feat_owner,
                               const int64_t* feat_inner, long long owner_stride, long long* const* seg_out,
                               const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st);
+// Level planned on the device (level.cu): the build nodes of a level with a running cost prefix
+// (cost of a node = its rows + kHistFlushCost), walked by hist_span_k in spans of equal cost.
+constexpr long long kHistFlushCost = 512;       // a flush of the shared histogram, in rows' worth of time
+struct BuildNode { long long begin, end; long long cost_end; int buf; int seg; };
+cudaError_t launch_hist_span(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1,
+                             const BuildNode* nodes, const int* n_nodes_dev, int groups, int32_t F, const uint32_t* group_mask,
+                             const int32_t* nbins, const int32_t* feat_owner, const int64_t* feat_inner, long long owner_stride,
+                             long long* const* seg_out, cudaStream_t st);
 // the wide features' share of the same work items: 64-bit global reductions, one CTA per (item, feature)
 cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide, const int2* gq, const int32_t* rowidx0,
                              const int32_t* rowidx1, const RowItem* items, int n_items, const int32_t* feat_owner,
@@ -139,7 +147,8 @@ cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t*
                               const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
                               SplitPart* parts /* n_nodes * split_scan_slices() scratch */, ytk_split* out,
                               ytk_split* mirror /* nullable: a second copy of the records (pinned host memory) */,
-                              unsigned int* done /* n_nodes zero-initialised counters; left zero */, cudaStream_t st);
+                              unsigned int* done /* n_nodes zero-initialised counters; left zero */, cudaStream_t st,
+                              long long* lh_out = nullptr /* [n_nodes][2]: hessian left of the best split, of the node (fixed point) */);
 int split_scan_slices(int32_t f_from, int32_t f_to);
 
 // K6: stable partition of every segment by (float)bin(row,fid) < cond (or by a byte mask)

@@ -1,0 +1,368 @@
+// Level-wise growth with the host out of the loop: DataParallelTreeMaker.make
+// (J/optimizer/gbdt/DataParallelTreeMaker.java:229-295) for grow policy "level" as ONE enqueue and ONE
+// host wait per tree.  Every table a level's kernels need is planned on the device from the split records
+// and child counts it already holds (level.cu); the host queues root + max_depth levels of kernels with
+// grids that are upper bounds, waits once, reads the records back and assembles the Tree in the
+// reference's node order (Tree.addChilds order = polling order, :246-258).  The host-planned path
+// (grow.cu) remains for everything this one does not take: loss-wise growth, a bounded histogram pool,
+// the row-count stop rule, a leaf budget that can bind, sparse rows, features with more than 256 bins.
+// J/ = /root/reference/src/main/java/com/fenbi/ytklearn/.
+#include "host.cuh"
+#include "level.cuh"
+
+namespace ytkh {
+
+namespace {
+
+size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
+
+// buffer the rows of level d live in: the root's (-1 identity / 0 after a row mask), then alternating
+int level_buf(int root_buf, int d) {
+    int b = root_buf;
+    for (int i = 0; i < d; i++) b = (b == 0) ? 1 : 0;
+    return b;
+}
+
+}  // namespace
+
+bool engine_applicable(const ytk_gbdt* h) {
+    const ytk_gbdt_params& p = h->p;
+    if (!h->use_engine || h->force_sequential || !h->single_pass_partition || !h->plan_ahead) return false;
+    if (p.grow_policy != 0 || p.max_depth < 1 || p.max_depth > 14) return false;
+    if (p.min_split_samples > 0 || p.histogram_pool_capacity > 0) return false;
+    if (p.max_leaf_cnt > 0 && (long long)p.max_leaf_cnt < (1LL << p.max_depth)) return false;      // the leaf budget could bind
+    if (h->sparse || h->n_wide > 0) return false;
+    if (h->world > 1) return false;
+    if ((size_t)(1u << (p.max_depth - 1)) > h->pool_chunk_slots) return false;
+    return true;
+}
+
+// Device tables and their pinned mirrors for trees of depth D (kept across trees).
+static int engine_reserve(ytk_gbdt* h, int D) {
+    EngineBuffers& e = h->eng;
+    const size_t heap = (size_t(1) << (D + 1)) - 1, slots = size_t(1) << (D - 1);
+    const size_t tiles = (size_t)(h->N / ytk::kFusedTile) + (size_t(1) << D) + 2;
+    if (e.depth == D && e.tile_cap >= tiles) return YTK_OK;
+    if (e.dev) CK(cudaFree(e.dev));
+    if (e.host) CK(cudaFreeHost(e.host));
+    e = EngineBuffers();
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align256(off + bytes); return o; };
+    const size_t o_nodes = take(heap * sizeof(ytk::LvNode)), o_recs = take(heap * sizeof(ytk_split)),
+                 o_lh = take(heap * 2 * sizeof(long long)), o_leaf = take(heap * 2 * sizeof(long long));
+    const size_t mirror_bytes = off;                     // everything up to here is copied back after the tree
+    const size_t o_segs = take(slots * sizeof(ytk::SplitSeg)), o_tiles = take(tiles * sizeof(int)), o_ntiles = take(sizeof(int)),
+                 o_counts = take(slots * sizeof(ytk::PartitionCounts)), o_gcounts = take(slots * sizeof(ytk::PartitionCounts)),
+                 o_build = take(2 * slots * sizeof(ytk::BuildNode)), o_nbuild = take(sizeof(int)),
+                 o_subs = take(slots * sizeof(ytk::SubItem)), o_scans = take(2 * slots * sizeof(ytk::ScanNode)),
+                 o_segout = take(2 * slots * sizeof(long long*));
+    CK(cudaMalloc(&e.dev, off));
+    CK(cudaMemsetAsync(e.dev, 0, off, h->st));
+    CK(cudaHostAlloc((void**)&e.host, mirror_bytes, cudaHostAllocDefault));
+    e.depth = D; e.tile_cap = tiles; e.mirror_bytes = mirror_bytes; e.heap = heap;
+    ytk::LvTables& t = e.t;
+    t.nodes = reinterpret_cast<ytk::LvNode*>(e.dev + o_nodes);
+    t.recs = reinterpret_cast<ytk_split*>(e.dev + o_recs);
+    t.left_h = reinterpret_cast<long long*>(e.dev + o_lh);
+    t.leaf = reinterpret_cast<long long*>(e.dev + o_leaf);
+    t.segs = reinterpret_cast<ytk::SplitSeg*>(e.dev + o_segs);
+    t.tile_seg = reinterpret_cast<int*>(e.dev + o_tiles);
+    t.n_tiles = reinterpret_cast<int*>(e.dev + o_ntiles);
+    t.counts = reinterpret_cast<ytk::PartitionCounts*>(e.dev + o_counts);
+    t.gcounts = reinterpret_cast<ytk::PartitionCounts*>(e.dev + o_gcounts);
+    t.build = reinterpret_cast<ytk::BuildNode*>(e.dev + o_build);
+    t.n_build = reinterpret_cast<int*>(e.dev + o_nbuild);
+    t.subs = reinterpret_cast<ytk::SubItem*>(e.dev + o_subs);
+    t.scans = reinterpret_cast<ytk::ScanNode*>(e.dev + o_scans);
+    t.seg_out = reinterpret_cast<long long**>(e.dev + o_segout);
+    e.h_nodes = reinterpret_cast<ytk::LvNode*>(e.host + o_nodes);
+    e.h_recs = reinterpret_cast<ytk_split*>(e.host + o_recs);
+    e.h_leaf = reinterpret_cast<long long*>(e.host + o_leaf);
+    e.clear_bytes = o_segs;                              // nodes, records, left hessians, leaf sums: cleared per tree
+    return YTK_OK;
+}
+
+namespace {
+
+class LevelEngine {
+public:
+    LevelEngine(ytk_gbdt* handle, ytk_tree_out* tree, ytk_time_stats* stats)
+        : h(handle), p(handle->p), out(tree), T(stats), D(handle->p.max_depth) {}
+
+    int run(int gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask) {
+        const double t0 = now_ms();
+        RET(begin(gid, fea_index, n_fea, row_mask));
+        RET(enqueue_root());
+        for (int d = 0; d < D; d++) RET(enqueue_level(d));
+        RET(finish_enqueue());
+        const double t1 = now_ms();
+        CK(cudaStreamSynchronize(h->st));                 // the one host wait of the tree
+        const double t2 = now_ms();
+        T->batches = 0;
+        T->max_batch_ms = t2 - t0;
+        h->arena.rewind();
+        RET(assemble(row_mask != nullptr));
+        RET(stage_times());
+        T->enqueue_ms = t1 - t0;
+        T->host_wait_ms = t2 - t1;
+        return YTK_OK;
+    }
+
+private:
+    ytk_gbdt* h;
+    const ytk_gbdt_params& p;
+    ytk_tree_out* out;
+    ytk_time_stats* T;
+    const int D;
+    int first_owned = -1, n_sel = 0;
+    int root_buf = -1;
+    long long root_rows_bound = 0;
+    ytk::LvTables t{};
+    // CUDA events at the stage boundaries of the tree (TimeStats.getStats, J/data/gbdt/TimeStats.java:69-78)
+    enum Stage { kInit = 0, kHist, kComm, kSplit, kSync, kPart, kStages };
+    std::vector<int> marks;              // stage that ENDS at event i + 1
+
+    int mark(Stage s) {
+        if (h->ev_stage_used >= (int)h->ev_stage.size()) {
+            cudaEvent_t e;
+            CK(cudaEventCreate(&e));
+            h->ev_stage.push_back(e);
+        }
+        CK(cudaEventRecord(h->ev_stage[h->ev_stage_used++], h->st));
+        marks.push_back((int)s);
+        return YTK_OK;
+    }
+
+    int begin(int gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask) {
+        RET(engine_reserve(h, D));
+        t = h->eng.t;
+        t.pool = h->d_pool_chunk;
+        t.staging = nullptr;
+        t.seg_max = h->seg_max;
+        t.world = h->world;
+        t.ticket = h->d_ticket ? h->d_ticket + 1 : nullptr;
+        RET(set_features(h, fea_index, n_fea, &first_owned, &n_sel));
+        h->pool.clear();
+        h->ev_stage_used = 0;
+        RET(mark(kInit));                                 // (event 0: the start; its stage label is unused)
+        RET(quantize_grads(h, gid));
+        CK(cudaMemcpyAsync(h->h_scale.h, h->d_scale, sizeof(ytk::GradScale), cudaMemcpyDeviceToHost, h->st));
+        CK(cudaMemsetAsync(h->eng.dev, 0, h->eng.clear_bytes, h->st));
+        root_buf = -1;
+        root_rows_bound = h->N;
+        const ytk::PartitionCounts* mask_counts = nullptr;
+        if (row_mask) {
+            // resetPositionAfterSample (SamplePositionData.java:84-87): the sampled rows first, in buffer 0
+            if (!h->d_mask) CK(cudaMalloc(&h->d_mask, std::max<int64_t>(h->N, 1)));
+            void* stage = h->arena.take((size_t)h->N, h->st);
+            if (!stage) return fail(YTK_ERR_CUDA, "pinned staging allocation failed");
+            memcpy(stage, row_mask, (size_t)h->N);
+            CK(cudaMemcpyAsync(h->d_mask, stage, h->N, cudaMemcpyHostToDevice, h->st));
+            std::vector<ytk::SplitSeg> sg(1);
+            sg[0] = {0, (long long)h->N, -1, -1, 0.f, 0, 0, 0};
+            RET(partition_launch(h, h->d_mask, 0, sg));   // queued, not waited for: the count stays on the device
+            mask_counts = h->t_counts.d;
+            root_buf = 0;
+        }
+        // the partition's chained-scan state for the largest level
+        RET(next_partition_epoch(h, h->eng.tile_cap));
+        t.ticket = h->d_ticket + 1;
+        CK(ytk::launch_lv_root(t, 0, h->N, root_buf, mask_counts, h->st));
+        h->launches++;
+        RET(mark(kInit));
+        return YTK_OK;
+    }
+
+    int hist_launch() {
+        cudaEvent_t e0, e1;
+        RET(hist_events(h, &e0, &e1));
+        CK(cudaEventRecord(e0, h->st));
+        CK(ytk::launch_hist_span(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], t.build, t.n_build, h->groups, h->F,
+                                 h->d_group_mask, h->d_nbins, h->d_feat_owner, h->d_off_inner, 0, t.seg_out, h->st));
+        CK(cudaEventRecord(e1, h->st));
+        h->launches++;
+        return YTK_OK;
+    }
+
+    int scan_launch(const ytk::ScanNode* nodes, int n, size_t first_heap) {
+        CK(h->t_parts.reserve((size_t)n * ytk::split_scan_slices(h->f_from, h->f_to)));
+        RET(scan_done_counters(h, n));
+        CK(ytk::launch_split_scan(nodes, n, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to, first_owned,
+                                  h->d_scale, gain_params(p), nullptr, h->t_parts.d, t.recs + first_heap, nullptr,
+                                  h->t_scan_done.d, h->st, t.left_h + 2 * first_heap));
+        h->launches++;
+        return YTK_OK;
+    }
+
+    // findBestSplit(root) (:302-318)
+    int enqueue_root() {
+        CK(cudaMemsetAsync(t.pool, 0, (size_t)h->seg_max * sizeof(long long), h->st));
+        RET(hist_launch());
+        RET(mark(kHist));
+        RET(scan_launch(t.scans, 1, 0));
+        RET(mark(kSplit));
+        return YTK_OK;
+    }
+
+    // One level of the loop (:244-281) for all its nodes at once.
+    int enqueue_level(int d) {
+        const int m = 1 << d;
+        const int buf = level_buf(root_buf, d), child_buf = buf == 0 ? 1 : 0;
+        const bool leaf = d == D - 1;                     // the children are leaves (:266)
+        CK(ytk::launch_lv_plan_split(t, d, buf, p.min_split_loss, nullptr, ytk::kFusedTile, h->st));
+        const long long grid_bound = root_rows_bound / ytk::kFusedTile + m + 1;
+        RET(next_partition_epoch(h, (size_t)grid_bound));
+        CK(ytk::launch_partition_fused_planned(h->d_bins_col, h->S8, h->N, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1], t.segs, m,
+                                               t.tile_seg, t.n_tiles, (int)grid_bound, h->d_tile_state, t.ticket, h->part_epoch,
+                                               t.counts, h->st));
+        RET(mark(kPart));
+        CK(ytk::launch_lv_plan_build(t, d, child_buf, leaf, h->st));
+        h->launches += 3;
+        if (leaf) {
+            CK(ytk::launch_lv_leaf_sums(t, d, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], ytk::kNumSMs * 4, h->st));
+            h->launches++;
+            RET(mark(kInit));
+            return YTK_OK;
+        }
+        // the level's fresh slots (smaller children) start at zero; the larger children overwrite their parents
+        CK(cudaMemsetAsync(t.pool + (size_t)m * h->seg_max, 0, (size_t)m * h->seg_max * sizeof(long long), h->st));
+        RET(hist_launch());
+        RET(mark(kHist));
+        CK(ytk::launch_hist_subtract(t.subs, m, h->seg_max, h->st));
+        h->launches++;
+        RET(scan_launch(t.scans, 2 * m, (size_t)2 * m - 1));
+        RET(mark(kSplit));
+        return YTK_OK;
+    }
+
+    int finish_enqueue() {
+        CK(cudaMemcpyAsync(h->eng.host, h->eng.dev, h->eng.mirror_bytes, cudaMemcpyDeviceToHost, h->st));
+        return YTK_OK;
+    }
+
+    // ---- after the wait: the Tree, in the reference's order ---------------------------------------------------
+    int alloc_node(int parent) {        // Tree.AllocTreeNode (J/data/gbdt/Tree.java:58-64)
+        if (out->n_nodes >= out->capacity) return -1;
+        int nid = out->n_nodes++;
+        out->parent[nid] = parent; out->left[nid] = -1; out->right[nid] = -1;
+        out->fid[nid] = 0; out->lo[nid] = 0; out->hi[nid] = 0; out->node_info[nid] = 0.f;
+        out->loss_chg[nid] = -std::numeric_limits<float>::infinity(); out->hess_sum[nid] = 0.f; out->sample_cnt[nid] = 0;
+        return nid;
+    }
+
+    int assemble(bool masked) {
+        const ytk::LvNode* nodes = h->eng.h_nodes;
+        const ytk_split* recs = h->eng.h_recs;
+        const long long* leaf = h->eng.h_leaf;
+        const float lr = p.learning_rate;
+        const ytk::GradScale sc = *h->h_scale.h;
+        out->n_nodes = 0;
+        h->leaf_ranges.clear();
+        struct Polled { int heap, nid; };
+        std::vector<Polled> cur, next;
+        if (!(nodes[0].flags & ytk::kLvActive)) return fail(YTK_ERR_ARG, "internal: the device built no root");
+        const int root_nid = alloc_node(-1);
+        if (root_nid < 0) return fail(YTK_ERR_CAPACITY, "make_tree: tree capacity %d", out->capacity);
+        cur.push_back({0, root_nid});
+        auto searched = [&](int heap, int nid) {            // updateTreeNodeStat (:387-393) of a searched node + setSplit
+            const ytk_split& r = recs[heap];
+            out->loss_chg[nid] = r.loss_chg;
+            out->hess_sum[nid] = (float)r.sum_hess;
+            out->sample_cnt[nid] = nodes[heap].sample_cnt;
+            if ((double)r.loss_chg > p.min_split_loss) {         // findBestSplit tail (:587-592)
+                out->fid[nid] = r.fid; out->lo[nid] = r.lo; out->hi[nid] = r.hi;
+                out->node_info[nid] = 0.5f * (float)(r.lo + r.hi);
+            }
+        };
+        auto range_of = [&](int heap, int depth, int nid) {
+            if (nodes[heap].end > nodes[heap].begin) {
+                Interval v; v.b = nodes[heap].begin; v.e = nodes[heap].end; v.buf = level_buf(root_buf, depth);
+                h->leaf_ranges.push_back({nid, v});
+            }
+        };
+        searched(0, root_nid);
+        T->hist_built = 1;
+        double rows_root = (double)(nodes[0].end - nodes[0].begin);
+        T->hist_rows = rows_root; T->hist_cells = rows_root * n_sel;
+        T->hist_rows_indexed = root_buf >= 0 ? rows_root : 0.0;
+        for (int d = 0; d <= D && !cur.empty(); d++) {
+            next.clear();
+            for (const Polled& e : cur) {
+                const ytk_split& r = recs[e.heap];
+                const bool is_leaf = (double)r.loss_chg <= p.min_split_loss || d == D;      // (:249-250)
+                const bool dev_split = (nodes[e.heap].flags & ytk::kLvSplit) != 0;
+                if (is_leaf == dev_split)
+                    return fail(YTK_ERR_ARG, "internal: the device split a different set of nodes than the host (heap node %d)", e.heap);
+                if (is_leaf) {                               // (:253)
+                    out->node_info[e.nid] = r.node_value * lr;
+                    range_of(e.heap, d, e.nid);
+                    continue;
+                }
+                const int l = alloc_node(e.nid), rr = alloc_node(e.nid);      // tree.addChilds (:256)
+                if (l < 0 || rr < 0) return fail(YTK_ERR_CAPACITY, "make_tree: tree needs more than %d nodes", out->capacity);
+                out->left[e.nid] = l; out->right[e.nid] = rr;
+                const int hl = 2 * e.heap + 1, hr = 2 * e.heap + 2;
+                const ytk::LvNode& pn = nodes[e.heap];
+                const bool small_left_dev = (pn.flags & ytk::kLvSmallLeft) != 0;
+                const double rows_small = (double)(small_left_dev ? pn.cnt_l : pn.cnt_r);
+                if (d + 1 == D) {
+                    // computeLeafStats (:341-385): the smaller child's sums, the larger one by subtraction
+                    const bool small_left = pn.gcnt_l < pn.gcnt_r;          // (:344-350)
+                    if (small_left != small_left_dev)
+                        return fail(YTK_ERR_ARG, "internal: leaf sums were taken over the other child (heap node %d)", e.heap);
+                    const int hs = small_left ? hl : hr;
+                    const double sG = (double)leaf[2 * hs] * sc.inv_g, sH = (double)leaf[2 * hs + 1] * sc.inv_h;
+                    const double lG = r.sum_grad - sG, lH = r.sum_hess - sH;                 // setSubstract (:382)
+                    const int nid_s = small_left ? l : rr, nid_l = small_left ? rr : l;
+                    float rg, nv;
+                    ytk_host_node_value(&p, sG, sH, &rg, &nv);
+                    out->node_info[nid_s] = nv * lr; out->hess_sum[nid_s] = (float)sH;
+                    ytk_host_node_value(&p, lG, lH, &rg, &nv);
+                    out->node_info[nid_l] = nv * lr; out->hess_sum[nid_l] = (float)lH;
+                    out->sample_cnt[l] = pn.gcnt_l; out->sample_cnt[rr] = pn.gcnt_r;
+                    range_of(hl, d + 1, l);
+                    range_of(hr, d + 1, rr);
+                } else {
+                    searched(hl, l);
+                    searched(hr, rr);
+                    next.push_back({hl, l});
+                    next.push_back({hr, rr});
+                    T->hist_built++;
+                    T->hist_rows += rows_small; T->hist_cells += rows_small * n_sel; T->hist_rows_indexed += rows_small;
+                }
+            }
+            cur.swap(next);
+        }
+        h->tree_made = true;
+        h->unsampled_begin = masked ? nodes[0].end : -1;
+        return YTK_OK;
+    }
+
+    int stage_times() {
+        double acc[kStages] = {0, 0, 0, 0, 0, 0};
+        for (int i = 0; i + 1 < h->ev_stage_used; i++) {
+            float ms = 0.f;
+            CK(cudaEventElapsedTime(&ms, h->ev_stage[i], h->ev_stage[i + 1]));
+            acc[marks[i + 1]] += ms;
+        }
+        T->init_stats = acc[kInit];
+        T->compute_hist = acc[kHist];
+        T->communicate_hist = acc[kComm];
+        T->build_hist = acc[kHist] + acc[kComm];
+        T->find_best_split = acc[kSplit];
+        T->sync_best_split = acc[kSync];
+        T->partition = acc[kPart];
+        T->stage_times_from_gpu = 1;
+        return YTK_OK;
+    }
+};
+
+}  // namespace
+
+int engine_make_tree(ytk_gbdt* h, int gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask, ytk_tree_out* out,
+                     ytk_time_stats* T) {
+    LevelEngine e(h, out, T);
+    return e.run(gid, fea_index, n_fea, row_mask);
+}
+
+}  // namespace ytkh

@@ -749,8 +749,12 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     h->ev_used = 0;
     h->evc_used = 0;
 
-    TreeGrower grower(h, out, T);
-    RET(grower.grow(gid, fea_index, n_fea, row_mask));
+    if (engine_applicable(h)) {
+        RET(engine_make_tree(h, gid, fea_index, n_fea, row_mask, out, T));
+    } else {
+        TreeGrower grower(h, out, T);
+        RET(grower.grow(gid, fea_index, n_fea, row_mask));
+    }
 
     if (h->peer_mode) {
         CK(cudaStreamSynchronize(h->st));
@@ -787,9 +791,11 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         CK(cudaEventElapsedTime(&ms, h->evc[i], h->evc[i + 1]));
         comm_ms += ms;
     }
-    T->communicate_hist = comm_ms;     // CUDA-event time of the collectives (stream time, includes waiting for peers)
     T->gpu_hist_ms = gpu_ms;
-    T->compute_hist = gpu_ms;
+    if (!T->stage_times_from_gpu) {
+        T->communicate_hist = comm_ms;     // CUDA-event time of the collectives (stream time, includes waiting for peers)
+        T->compute_hist = gpu_ms;
+    }
     T->kernel_launches = h->launches;
     T->hist_launches = h->ev_used / 2;
     T->peer_collectives = h->peer_mode ? 1 : 0;

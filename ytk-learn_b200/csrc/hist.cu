@@ -103,48 +103,44 @@ __global__ void grad_quantize_k(const float* __restrict__ gp, int64_t n, int32_t
 // rows of one node and one feature group; it flushes non-empty bins with 64-bit global
 // reductions into that node's histogram.
 // ------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kHistThreads, 1)
-hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict__ gq,
-             const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1,
-             const RowItem* __restrict__ items, int32_t F, const uint32_t* __restrict__ group_mask,
-             const int32_t* __restrict__ nbins, const int32_t* __restrict__ feat_owner,
-             const int64_t* __restrict__ feat_inner, long long owner_stride,
-             long long* const* __restrict__ seg_out, const PartitionCounts* __restrict__ cnt_local,
-             const PartitionCounts* __restrict__ cnt_global) {
-    pdl_sync();
-    // g limbs [bin][{lo,hi}][feature] (64 KB), then the h limbs in the same layout (64 KB)
-    extern __shared__ __align__(128) uint32_t sh[];
-    constexpr uint32_t kHOff = kMaxBins * 2 * kGroup * 4;        // bytes
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int fg = blockIdx.y;
-    const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
-    if (it.begin >= it.end) return;          // a deferred chunk beyond the end of its child
-    const int32_t* __restrict__ ridx = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
-
-    {
-        uint4* z = reinterpret_cast<uint4*>(sh);
-        for (int i = tid; i < kMaxBins * 4 * kGroup / 4; i += kHistThreads) z[i] = make_uint4(0, 0, 0, 0);
-    }
-    __syncthreads();
-
-    const uint32_t gmask = group_mask[fg];
+// ---- the core both histogram kernels share --------------------------------------------------------
+// Per-thread constants of the lane -> (row, feature) mapping.
+struct HistLane {
+    int half, r16, m;
+    uint32_t selk[4];
+    uint32_t lane_off;
+};
+__device__ __forceinline__ HistLane hist_lane(int lane) {
+    HistLane L;
     // Lane L works on row (L >> 1) of a 16-row block and on the 16 features of half (L & 1) of the
     // group: at step k (0..15) it updates feature 16*(L&1) + (k ^ (L>>1)).  The 32 lanes of a warp
     // instruction therefore always touch 32 different features = 32 different banks.
-    const int half = lane & 1, r16 = lane >> 1;
-    const int m = r16 >> 2, bsel = r16 & 3;
+    L.half = lane & 1; L.r16 = lane >> 1;
+    L.m = L.r16 >> 2;
+    const int bsel = L.r16 & 3;
     // PRMT selectors: byte (kk ^ bsel) of a data word moved to byte 1, i.e. bin * 256 = the byte
     // offset of that bin's 256 B row of limbs
-    uint32_t selk[4];
 #pragma unroll
-    for (int kk = 0; kk < 4; kk++) selk[kk] = 0x4404u | ((uint32_t)(kk ^ bsel) << 4);
+    for (int kk = 0; kk < 4; kk++) L.selk[kk] = 0x4404u | ((uint32_t)(kk ^ bsel) << 4);
     // byte offset of feature 16*half + r16 inside a bin row; feature 16*half + (k ^ r16) is reached
     // by XOR-ing k*4 into it: (bin256 | lane_off) ^ k4 is one LOP3
-    uint32_t lane_off = (uint32_t)(half * 16 + r16) << 2;
-    asm volatile("" : "+r"(lane_off));
+    L.lane_off = (uint32_t)(L.half * 16 + L.r16) << 2;
+    asm volatile("" : "+r"(L.lane_off));
+    return L;
+}
+
+constexpr uint32_t kHOff = kMaxBins * 2 * kGroup * 4;        // bytes: the h limbs follow the g limbs
+
+// Accumulates rows [begin, end) (through ridx, or the rows themselves when ridx is null) of feature
+// group `fg` into the CTA's shared histogram `sh` (zero, or holding earlier rows of the same node;
+// at most kHistMaxRowsPerItem rows between two flushes).  Called by all threads of the CTA.
+__device__ __forceinline__ void hist_rows(uint32_t* sh, const HistLane& L, const uint8_t* __restrict__ bins, int32_t S8,
+                                          const int2* __restrict__ gq, const int32_t* __restrict__ ridx, int fg,
+                                          long long begin, long long end) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int half = L.half, r16 = L.r16, m = L.m;
     const uint8_t* __restrict__ gbase = bins + fg * kGroup + (half << 4);
     char* const shb = reinterpret_cast<char*>(sh);
-
     // Three-stage software pipeline per warp: row ids of block t+2, row data of block t+1 and the
     // atomics of block t are in flight together, so no load waits on another load of the same
     // iteration (loads share the LSU queue with thousands of cycles of queued atomics).
@@ -153,7 +149,7 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
     struct Fetch { uint4 a, b; int2 qa, qb; };
     auto fetch_rid = [&](long long base) -> int32_t {
         const long long i = base + lane;
-        return i < it.end ? (ridx ? ridx[i] : (int32_t)i) : -1;
+        return i < end ? (ridx ? ridx[i] : (int32_t)i) : -1;
     };
     auto fetch = [&](int32_t rid, Fetch& f) {
         const int32_t ra = __shfl_sync(0xffffffffu, rid, r16);
@@ -164,7 +160,6 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
         if (ra >= 0) { f.a = *reinterpret_cast<const uint4*>(gbase + (long long)ra * S8); f.qa = gq[ra]; }
         if (rb >= 0) { f.b = *reinterpret_cast<const uint4*>(gbase + (long long)rb * S8); f.qb = gq[rb]; }
     };
-
     // 16 steps on one 16-row half block.  Register j must hold data word j ^ m (m = r16 >> 2), the
     // word with the features this lane visits at steps 4j..4j+3: two conditional swaps.
     // Unsampled features and padding lanes are accumulated too (the instruction is issued for the
@@ -186,7 +181,7 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
             const uint32_t word = w[j];
 #pragma unroll
             for (int kk = 0; kk < 4; kk++) {
-                const uint32_t off = (__byte_perm(word, 0u, selk[kk]) | lane_off) ^ (uint32_t)((4 * j + kk) << 2);
+                const uint32_t off = (__byte_perm(word, 0u, L.selk[kk]) | L.lane_off) ^ (uint32_t)((4 * j + kk) << 2);
                 uint32_t* p = reinterpret_cast<uint32_t*>(shb + off);
                 atomicAdd(p, g_lo);
                 atomicAdd(reinterpret_cast<int32_t*>(p + kGroup), g_hi);
@@ -195,41 +190,133 @@ hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restric
             }
         }
     };
-
     // (two register sets in explicit ping-pong: a copy `cur = nxt` would be scheduled right behind
     // the loads and stall the warp on them)
-    long long base = it.begin + warp * 32;
+    long long base = begin + warp * 32;
     Fetch fa, fb;
     int32_t r1 = fetch_rid(base + kHistThreads);
     fetch(fetch_rid(base), fa);
-    while (base < it.end) {
+    while (base < end) {
         const int32_t r2 = fetch_rid(base + 2 * kHistThreads);
         fetch(r1, fb);
         accumulate16(fa.a, fa.qa);
         accumulate16(fa.b, fa.qb);
         base += kHistThreads;
-        if (base >= it.end) break;
+        if (base >= end) break;
         r1 = fetch_rid(base + 2 * kHistThreads);
         fetch(r2, fa);
         accumulate16(fb.a, fb.qa);
         accumulate16(fb.b, fb.qb);
         base += kHistThreads;
     }
-    __syncthreads();
+}
 
-    // flush: recombine the limbs, one 64-bit global reduction per non-empty (feature, bin, component)
-    long long* __restrict__ out = seg_out[it.seg];
-    for (int i = tid; i < kMaxBins * kGroup; i += kHistThreads) {
+// Flush: recombines the limbs, one 64-bit global reduction per non-empty (feature, bin, component) into
+// `out` (the node's histogram), and -- kRezero -- puts the words it read back to zero, so that the next
+// node's rows find a clean table without a separate zeroing pass.  (Cells of padding features and of
+// bins a feature does not have are never read here, so they may hold anything.)
+template <bool kRezero>
+__device__ __forceinline__ void hist_flush(uint32_t* sh, int fg, int32_t F, uint32_t gmask, const int32_t* __restrict__ nbins,
+                                           const int32_t* __restrict__ feat_owner, const int64_t* __restrict__ feat_inner,
+                                           long long owner_stride, long long* __restrict__ out) {
+    for (int i = threadIdx.x; i < kMaxBins * kGroup; i += kHistThreads) {
         int bin = i >> 5, ln = i & 31;
         int ff = fg * kGroup + ln;
         if (ff >= F || !((gmask >> ln) & 1u) || bin >= nbins[ff]) continue;
-        const uint32_t* pg = sh + bin * (2 * kGroup) + ln;
-        const uint32_t* ph = pg + kHOff / 4;
-        long long g = (long long)(int32_t)pg[kGroup] * 65536ll + (long long)pg[0];
-        long long h = (long long)(int32_t)ph[kGroup] * 65536ll + (long long)ph[0];
+        uint32_t* pg = sh + bin * (2 * kGroup) + ln;
+        uint32_t* ph = pg + kHOff / 4;
+        const uint32_t g0 = pg[0], g1 = pg[kGroup], h0 = ph[0], h1 = ph[kGroup];
+        if ((g0 | g1 | h0 | h1) == 0) continue;
+        if (kRezero) { pg[0] = 0; pg[kGroup] = 0; ph[0] = 0; ph[kGroup] = 0; }
+        long long g = (long long)(int32_t)g1 * 65536ll + (long long)g0;
+        long long h = (long long)(int32_t)h1 * 65536ll + (long long)h0;
         long long* dst = out + feat_owner[ff] * owner_stride + feat_inner[ff] + 2 * bin;
         if (g != 0) atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)g);
         if (h != 0) atomicAdd(reinterpret_cast<unsigned long long*>(dst + 1), (unsigned long long)h);
+    }
+}
+
+__device__ __forceinline__ void hist_zero(uint32_t* sh) {
+    uint4* z = reinterpret_cast<uint4*>(sh);
+    for (int i = threadIdx.x; i < kMaxBins * 4 * kGroup / 4; i += kHistThreads) z[i] = make_uint4(0, 0, 0, 0);
+}
+
+// One CTA (32 warps, 128 KB of shared memory, 1 per SM) per work item: a run of rows of one node and one
+// feature group -- the tables of the host-planned path (grow.cu) and the hooks.
+__global__ void __launch_bounds__(kHistThreads, 1)
+hist_build_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict__ gq,
+             const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1,
+             const RowItem* __restrict__ items, int32_t F, const uint32_t* __restrict__ group_mask,
+             const int32_t* __restrict__ nbins, const int32_t* __restrict__ feat_owner,
+             const int64_t* __restrict__ feat_inner, long long owner_stride,
+             long long* const* __restrict__ seg_out, const PartitionCounts* __restrict__ cnt_local,
+             const PartitionCounts* __restrict__ cnt_global) {
+    pdl_sync();
+    // g limbs [bin][{lo,hi}][feature] (64 KB), then the h limbs in the same layout (64 KB)
+    extern __shared__ __align__(128) uint32_t sh[];
+    const int fg = blockIdx.y;
+    const RowItem it = resolve_item(items[blockIdx.x], cnt_local, cnt_global);
+    if (it.begin >= it.end) return;          // a deferred chunk beyond the end of its child
+    const int32_t* __restrict__ ridx = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
+    hist_zero(sh);
+    __syncthreads();
+    const HistLane L = hist_lane(threadIdx.x & 31);
+    hist_rows(sh, L, bins, S8, gq, ridx, fg, it.begin, it.end);
+    __syncthreads();
+    hist_flush<false>(sh, fg, F, group_mask[fg], nbins, feat_owner, feat_inner, owner_stride, seg_out[it.seg]);
+}
+
+// ------------------------------------------------------------------------------------
+// The same histograms for a whole tree LEVEL whose work is planned on the device (level.cu): the rows
+// to be visited are the concatenation of the level's build nodes (the smaller child of every node
+// split at this level), `nodes[j]` with a running prefix of COST = rows + a flush's worth of rows.
+// Every CTA takes one contiguous span of equal cost -- no tickets, no tail, one set of dependent
+// start-up loads per CTA -- walks the nodes in it and flushes at every node boundary (and every
+// kHistMaxRowsPerItem rows), re-zeroing while it flushes.  grid = (CTAs per group, groups).
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kHistThreads, 1)
+hist_span_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict__ gq,
+            const int32_t* __restrict__ rowidx0, const int32_t* __restrict__ rowidx1,
+            const BuildNode* __restrict__ nodes, const int* __restrict__ n_nodes_dev, int32_t F,
+            const uint32_t* __restrict__ group_mask, const int32_t* __restrict__ nbins,
+            const int32_t* __restrict__ feat_owner, const int64_t* __restrict__ feat_inner, long long owner_stride,
+            long long* const* __restrict__ seg_out) {
+    pdl_sync();
+    extern __shared__ __align__(128) uint32_t sh[];
+    const int nb = *n_nodes_dev;
+    if (nb <= 0) return;
+    const int fg = blockIdx.y;
+    const long long total = nodes[nb - 1].cost_end;
+    const long long c0 = total * blockIdx.x / gridDim.x, c1 = total * (blockIdx.x + 1) / gridDim.x;
+    if (c0 >= c1) return;
+    // first node whose cost range ends beyond c0
+    int lo = 0, hi = nb - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (nodes[mid].cost_end > c0) hi = mid; else lo = mid + 1;
+    }
+    hist_zero(sh);
+    __syncthreads();
+    const HistLane L = hist_lane(threadIdx.x & 31);
+    const uint32_t gmask = group_mask[fg];
+    for (int j = lo; j < nb; j++) {
+        const BuildNode nd = nodes[j];
+        const long long n = nd.end - nd.begin;
+        const long long cost_begin = nd.cost_end - n - kHistFlushCost;
+        if (cost_begin >= c1) break;
+        long long o0 = c0 - cost_begin, o1 = c1 - cost_begin;       // my share of the node, in rows from its begin
+        o0 = o0 < 0 ? 0 : o0;
+        o1 = o1 > n ? n : o1;
+        if (o0 >= o1) continue;                                     // only (part of) its flush cost falls to me
+        const int32_t* __restrict__ ridx = nd.buf < 0 ? nullptr : (nd.buf == 0 ? rowidx0 : rowidx1);
+        long long* __restrict__ out = seg_out[nd.seg];
+        for (long long b = nd.begin + o0; b < nd.begin + o1; b += kHistMaxRowsPerItem) {
+            const long long e = min(nd.begin + o1, b + (long long)kHistMaxRowsPerItem);
+            hist_rows(sh, L, bins, S8, gq, ridx, fg, b, e);
+            __syncthreads();
+            hist_flush<true>(sh, fg, F, gmask, nbins, feat_owner, feat_inner, owner_stride, out);
+            __syncthreads();
+        }
     }
 }
 
@@ -352,6 +439,7 @@ hist_wide_k(WideCols wide, const int32_t* __restrict__ wide_fids, const int2* __
 __global__ void hist_subtract_k(const SubItem* __restrict__ items, int64_t len) {
     pdl_sync();
     const SubItem it = items[blockIdx.y];
+    if (!it.out) return;                    // an unused entry of a device-planned table
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < len;
          i += (int64_t)gridDim.x * blockDim.x)
         it.out[i] = it.parent[i] - it.small[i];
@@ -404,7 +492,9 @@ cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t 
 // The 128 KB of dynamic shared memory are an opt-in PER DEVICE: called by set_bins with the handle's
 // device current (one process may drive several GPUs, one thread each).
 cudaError_t hist_kernels_init() {
-    return cudaFuncSetAttribute(hist_build_k, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(hist_build_k, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemBytes);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(hist_span_k, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemBytes);
 }
 
 int64_t hist_rows_per_item(int64_t total_rows, int groups) {
@@ -427,6 +517,16 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
     return launch_chain(hist_build_k, grid, dim3(kHistThreads), kHistSmemBytes, st, bins, S8, gq, rowidx0, rowidx1, items, F, group_mask,
                                                              nbins, feat_owner, feat_inner, owner_stride, seg_out,
                                                              cnt_local, cnt_global);
+}
+
+cudaError_t launch_hist_span(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1,
+                             const BuildNode* nodes, const int* n_nodes_dev, int groups, int32_t F, const uint32_t* group_mask,
+                             const int32_t* nbins, const int32_t* feat_owner, const int64_t* feat_inner, long long owner_stride,
+                             long long* const* seg_out, cudaStream_t st) {
+    const int per_group = std::max(1, kNumSMs / std::max(1, groups));
+    dim3 grid((unsigned)per_group, (unsigned)groups);
+    return launch_chain(hist_span_k, grid, dim3(kHistThreads), kHistSmemBytes, st, bins, S8, gq, rowidx0, rowidx1, nodes, n_nodes_dev,
+                        F, group_mask, nbins, feat_owner, feat_inner, owner_stride, seg_out);
 }
 
 cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide, const int2* gq, const int32_t* rowidx0,

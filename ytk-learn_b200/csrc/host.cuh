@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "level.cuh"
 #include "nccl_dyn.h"
 
 namespace ytkh {
@@ -227,6 +228,18 @@ struct PinnedBuf {
 };
 
 
+// device tables (and pinned mirrors of what comes back) of the device-driven level loop (engine.cu)
+struct EngineBuffers {
+    int depth = -1;
+    size_t tile_cap = 0, mirror_bytes = 0, clear_bytes = 0, heap = 0;
+    char* dev = nullptr;
+    char* host = nullptr;
+    ytk::LvTables t{};
+    ytk::LvNode* h_nodes = nullptr;
+    ytk_split* h_recs = nullptr;
+    long long* h_leaf = nullptr;
+};
+
 }  // namespace ytkh
 
 // Host mirror of UpdateStrategy.calcGain / calcNodeValue (tree_maker.cu)
@@ -247,6 +260,11 @@ struct ytk_gbdt {
     // level-wise growth: the next level's partition planned and started by the device
     bool plan_ahead = true;                 // YTK_GBDT_NO_PLAN_AHEAD=1 turns it off
     bool spin_wait = false;                 // YTK_GBDT_SPIN=1: poll the level's event from user space (measured: no gain)
+    bool use_engine = true;                 // YTK_GBDT_NO_ENGINE=1: level-wise growth through the host-planned path too
+    EngineBuffers eng;
+    size_t pool_chunk_slots = 0;            // histogram slots in d_pool_chunk
+    std::vector<cudaEvent_t> ev_stage;      // stage boundaries of a device-driven tree
+    int ev_stage_used = 0;
     bool recs_merged = false;               // the last split exchange merged the records on the device
     DevTable<ytk::SplitSeg> t_spec_segs[2];
     DevTable<ytk::PartitionCounts> t_spec_counts[2];
@@ -441,5 +459,9 @@ void partition_collect(ytk_gbdt* h, int m, std::vector<ytk::PartitionCounts>& lo
                        std::vector<ytk::PartitionCounts>& global);
 int partition_nodes(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const std::vector<ytk::SplitSeg>& segs_in,
                     std::vector<ytk::PartitionCounts>& local, std::vector<ytk::PartitionCounts>& global);
+// ---- engine.cu: level-wise growth planned on the device --------------------------------------------
+bool engine_applicable(const ytk_gbdt* h);
+int engine_make_tree(ytk_gbdt* h, int gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask, ytk_tree_out* out,
+                     ytk_time_stats* T);
 
 }  // namespace ytkh

@@ -1,0 +1,235 @@
+// Planner kernels of the device-driven level loop (level.cuh, engine.cu): one CTA each, queued between the
+// data kernels of a level with programmatic dependent launch.  They restate, on the device, the decisions
+// DataParallelTreeMaker.make takes between two kernels of a level
+// (J/optimizer/gbdt/DataParallelTreeMaker.java:244-281): which polled nodes are split (:249-252), where
+// the children's rows are (SamplePositionData.java:128-132), which child is built from rows and which by
+// subtraction (:489-508), whose leaf statistics are summed (:341-385).
+#include "level.cuh"
+#include "device_util.cuh"
+
+namespace ytk {
+
+constexpr int kPlanThreads = 512;
+
+// exclusive scan of one value per thread over the CTA; *total = sum over the CTA.  s_warp: kPlanThreads/32 words
+template <typename T>
+__device__ __forceinline__ T block_excl_scan(T v, T* s_warp, T* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    T p = v;
+    for (int d = 1; d < 32; d <<= 1) {
+        T t = __shfl_up_sync(0xffffffffu, p, d);
+        if (lane >= d) p += t;
+    }
+    __syncthreads();                     // s_warp may still be read from an earlier call
+    if (lane == 31) s_warp[warp] = p;
+    __syncthreads();
+    T woff = 0, tot = 0;
+    for (int w = 0; w < kPlanThreads / 32; w++) {
+        if (w < warp) woff += s_warp[w];
+        tot += s_warp[w];
+    }
+    *total = tot;
+    return woff + p - v;
+}
+
+__global__ void lv_root_k(LvTables t, long long begin, long long end, int buf, const PartitionCounts* mask_counts) {
+    pdl_sync();
+    if (threadIdx.x != 0) return;
+    if (mask_counts) end = begin + mask_counts[0].left;          // rows kept by the row mask come first
+    LvNode nd = {begin, end, 0, 0, 0, 0, end - begin, kLvActive, 0};
+    t.nodes[0] = nd;
+    const long long n = end - begin;
+    t.build[0] = {begin, end, n + kHistFlushCost, buf, 0};
+    *t.n_build = n > 0 ? 1 : 0;
+    t.seg_out[0] = t.world == 1 ? t.pool : t.staging;
+    t.scans[0] = {t.pool, n, -1, 0};
+}
+
+// Which nodes of level d are split -- lossChg > min_split_loss (the depth rule is the host's: it does not
+// ask for a level beyond max_depth) -- and the partition's segment and tile tables.
+__global__ void __launch_bounds__(kPlanThreads)
+lv_plan_split_k(LvTables t, int d, int buf, double min_split_loss, const int32_t* __restrict__ wide_index, int tile_rows) {
+    pdl_sync();
+    __shared__ int s_warp[kPlanThreads / 32];
+    __shared__ int s_carry;
+    const int m = 1 << d, L0 = m - 1;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { s_carry = 0; *t.ticket = 0; }
+    __syncthreads();
+    for (int s0 = 0; s0 < m; s0 += kPlanThreads) {
+        const int s = s0 + threadIdx.x;
+        SplitSeg sg = {0, 0, 0, 0, 0.f, 0, 0, 0};
+        bool split = false;
+        if (s < m) {
+            const LvNode nd = t.nodes[L0 + s];
+            if (nd.flags & kLvActive) {
+                const ytk_split r = t.recs[L0 + s];
+                if (!((double)r.loss_chg <= min_split_loss)) {          // the negation of the leaf rule (:249)
+                    split = true;
+                    sg.begin = nd.begin; sg.end = nd.end; sg.buf = buf;
+                    sg.fid = r.fid;
+                    sg.cond = 0.5f * (float)(r.lo + r.hi);               // TreeNode.setSplit (:144-149)
+                    sg.wide = wide_index ? wide_index[r.fid] + 1 : 0;
+                    sg.ntiles = (int)((sg.end - sg.begin + tile_rows - 1) / tile_rows);
+                    t.nodes[L0 + s].flags = nd.flags | kLvSplit;
+                }
+            }
+        }
+        int total;
+        sg.tile0 = s_carry + block_excl_scan<int>(sg.ntiles, s_warp, &total);
+        if (s < m) {
+            t.segs[s] = sg;
+            if (!split) t.counts[s] = {-1, -1};
+            else if (sg.ntiles == 0) t.counts[s] = {0, 0};
+        }
+        // tile -> slot table: the lanes of a warp fill the tiles of the warp's 32 slots, one slot after the other
+        for (int j = 0; j < 32; j++) {
+            const int t0 = __shfl_sync(0xffffffffu, sg.tile0, j), nt = __shfl_sync(0xffffffffu, sg.ntiles, j);
+            for (int q = lane; q < nt; q += 32) t.tile_seg[t0 + q] = s0 + warp * 32 + j;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_carry += total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *t.n_tiles = s_carry;
+}
+
+// After the partition of level d.  The children of every split node get their row intervals; the smaller
+// child (fewer global rows, ties to the right: :344-350, :493-499 -- with several GPUs: the smaller
+// hessian sum of the parent's best split, which every GPU can evaluate without an exchange; integer
+// histograms make parent - child exact whichever child is built) goes on the level's build list.
+// leaf = false: the smaller child takes a fresh histogram slot, the larger one its parent's (sibling written
+// over its parent), and the subtraction pairs and the scan nodes of both children are laid down.
+__global__ void __launch_bounds__(kPlanThreads)
+lv_plan_build_k(LvTables t, int d, int child_buf, int leaf) {
+    pdl_sync();
+    __shared__ long long s_warp_ll[kPlanThreads / 32];
+    __shared__ int s_warp_i[kPlanThreads / 32];
+    __shared__ long long s_cost;
+    __shared__ int s_cnt;
+    const int m = 1 << d, L0 = m - 1;
+    if (threadIdx.x == 0) { s_cost = 0; s_cnt = 0; }
+    __syncthreads();
+    for (int s0 = 0; s0 < m; s0 += kPlanThreads) {
+        const int s = s0 + threadIdx.x;
+        bool add = false;
+        BuildNode bn = {0, 0, 0, 0, 0};
+        if (s < m) {
+            const int p = L0 + s;
+            LvNode nd = t.nodes[p];
+            SubItem sub = {nullptr, nullptr, nullptr};
+            ScanNode sc_l = {nullptr, 0, -1, 0}, sc_r = sc_l;
+            if (nd.flags & kLvSplit) {
+                const PartitionCounts c = t.counts[s];
+                const PartitionCounts gc = t.world == 1 ? c : t.gcounts[s];
+                bool small_left;
+                if (t.world == 1) small_left = gc.left < gc.right;
+                else {
+                    const long long lh = t.left_h[2 * p], th = t.left_h[2 * p + 1];
+                    small_left = lh < th - lh;
+                }
+                nd.cnt_l = c.left; nd.cnt_r = c.right;
+                nd.gcnt_l = gc.left; nd.gcnt_r = gc.right;
+                if (small_left) nd.flags |= kLvSmallLeft;
+                const int slot_small = leaf ? -1 : m + s, slot_large = leaf ? -1 : nd.slot;
+                LvNode cl = {nd.begin, nd.begin + c.left, 0, 0, 0, 0, gc.left, kLvActive, small_left ? slot_small : slot_large};
+                LvNode cr = {nd.begin + c.left, nd.end, 0, 0, 0, 0, gc.right, kLvActive, small_left ? slot_large : slot_small};
+                t.nodes[2 * p + 1] = cl;
+                t.nodes[2 * p + 2] = cr;
+                t.nodes[p] = nd;
+                bn.begin = small_left ? cl.begin : cr.begin;
+                bn.end = small_left ? cl.end : cr.end;
+                bn.buf = child_buf;
+                bn.seg = leaf ? 2 * s + (small_left ? 0 : 1) : s;     // leaf sums are kept per child, histograms per parent slot
+                add = bn.end > bn.begin;
+                if (!leaf) {
+                    long long* parent_h = t.pool + (long long)nd.slot * t.seg_max;
+                    long long* small_h = t.pool + (long long)slot_small * t.seg_max;
+                    sub = {parent_h, small_h, parent_h};                   // substract (:101-107), in place
+                    sc_l.hist = small_left ? small_h : parent_h;
+                    sc_r.hist = small_left ? parent_h : small_h;
+                    sc_l.sample_cnt = gc.left; sc_r.sample_cnt = gc.right;
+                    t.seg_out[s] = t.world == 1 ? small_h : t.staging + (long long)s * t.seg_max;
+                }
+            }
+            if (!leaf) { t.subs[s] = sub; t.scans[2 * s] = sc_l; t.scans[2 * s + 1] = sc_r; }
+        }
+        int n_add;
+        const int j = s_cnt + block_excl_scan<int>(add ? 1 : 0, s_warp_i, &n_add);
+        long long cost_add;
+        const long long mine = add ? (bn.end - bn.begin) + kHistFlushCost : 0;
+        const long long before = s_cost + block_excl_scan<long long>(mine, s_warp_ll, &cost_add);
+        if (add) { bn.cost_end = before + mine; t.build[j] = bn; }
+        __syncthreads();
+        if (threadIdx.x == 0) { s_cnt += n_add; s_cost += cost_add; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *t.n_build = s_cnt;
+}
+
+// computeLeafStats (:352-372) for the last level: exact fixed-point (g,h) sums over the rows of the level's
+// build nodes (the smaller child of every node split there), walked in spans of equal cost like
+// hist_span_k; build node `seg` = its position in level d + 1 adds into leaf[2 * (2^(d+1) - 1 + seg)].
+__global__ void __launch_bounds__(256)
+lv_leaf_sums_k(LvTables t, int d, const int2* __restrict__ gq, const int32_t* __restrict__ rowidx0,
+               const int32_t* __restrict__ rowidx1) {
+    pdl_sync();
+    __shared__ long long s_g[8], s_h[8];
+    const int nb = *t.n_build;
+    if (nb <= 0) return;
+    const int L0 = (2 << d) - 1;             // first heap node of the children's level
+    const long long total = t.build[nb - 1].cost_end;
+    const long long c0 = total * blockIdx.x / gridDim.x, c1 = total * (blockIdx.x + 1) / gridDim.x;
+    if (c0 >= c1) return;
+    int lo = 0, hi = nb - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (t.build[mid].cost_end > c0) hi = mid; else lo = mid + 1;
+    }
+    for (int j = lo; j < nb; j++) {
+        const BuildNode nd = t.build[j];
+        const long long n = nd.end - nd.begin;
+        const long long cost_begin = nd.cost_end - n - kHistFlushCost;
+        if (cost_begin >= c1) break;
+        long long o0 = c0 - cost_begin, o1 = c1 - cost_begin;
+        o0 = o0 < 0 ? 0 : o0;
+        o1 = o1 > n ? n : o1;
+        if (o0 >= o1) continue;
+        const int32_t* __restrict__ ridx = nd.buf < 0 ? nullptr : (nd.buf == 0 ? rowidx0 : rowidx1);
+        long long g = 0, h = 0;
+        for (long long i = nd.begin + o0 + threadIdx.x; i < nd.begin + o1; i += blockDim.x) {
+            const int2 q = gq[ridx ? ridx[i] : (int32_t)i];
+            g += q.x; h += q.y;
+        }
+        for (int k = 16; k > 0; k >>= 1) {
+            g += __shfl_xor_sync(0xffffffffu, g, k);
+            h += __shfl_xor_sync(0xffffffffu, h, k);
+        }
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) { s_g[threadIdx.x >> 5] = g; s_h[threadIdx.x >> 5] = h; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int w = 1; w < 8; w++) { g += s_g[w]; h += s_h[w]; }
+            long long* out = t.leaf + 2 * (long long)(L0 + nd.seg);
+            if (g) atomicAdd(reinterpret_cast<unsigned long long*>(out), (unsigned long long)g);
+            if (h) atomicAdd(reinterpret_cast<unsigned long long*>(out + 1), (unsigned long long)h);
+        }
+    }
+}
+
+cudaError_t launch_lv_root(LvTables t, long long begin, long long end, int buf, const PartitionCounts* mask_counts, cudaStream_t st) {
+    return launch_chain(lv_root_k, dim3(1), dim3(32), 0, st, t, begin, end, buf, mask_counts);
+}
+cudaError_t launch_lv_plan_split(LvTables t, int d, int buf, double min_split_loss, const int32_t* wide_index, int tile_rows,
+                                 cudaStream_t st) {
+    return launch_chain(lv_plan_split_k, dim3(1), dim3(kPlanThreads), 0, st, t, d, buf, min_split_loss, wide_index, tile_rows);
+}
+cudaError_t launch_lv_plan_build(LvTables t, int d, int child_buf, bool leaf, cudaStream_t st) {
+    return launch_chain(lv_plan_build_k, dim3(1), dim3(kPlanThreads), 0, st, t, d, child_buf, leaf ? 1 : 0);
+}
+cudaError_t launch_lv_leaf_sums(LvTables t, int d, const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1, int grid,
+                                cudaStream_t st) {
+    return launch_chain(lv_leaf_sums_k, dim3(grid), dim3(256), 0, st, t, d, gq, rowidx0, rowidx1);
+}
+
+}  // namespace ytk

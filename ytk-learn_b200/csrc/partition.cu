@@ -6,6 +6,7 @@
 // /root/reference/src/main/java/com/fenbi/ytklearn/...
 #include "common.cuh"
 #include "device_util.cuh"
+#include "level.cuh"
 
 #include <math_constants.h>
 
@@ -525,6 +526,16 @@ cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col
     return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
                         rowidx0, rowidx1, (const SplitSeg*)out_segs, 2 * m, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
                         tile_state, ticket, epoch, next_counts);
+}
+
+cudaError_t launch_partition_fused_planned(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
+                                           int32_t* rowidx1, const SplitSeg* segs, int n_segs, const int* tile_seg,
+                                           const int* n_tiles_dev, int grid_bound, unsigned long long* tile_state,
+                                           unsigned int* ticket, unsigned long long epoch, PartitionCounts* counts,
+                                           cudaStream_t st, SparseRows sparse) {
+    if (grid_bound <= 0) return cudaSuccess;
+    return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
+                        rowidx0, rowidx1, segs, n_segs, tile_seg, 0, n_tiles_dev, tile_state, ticket, epoch, counts);
 }
 
 cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,

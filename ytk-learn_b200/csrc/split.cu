@@ -63,9 +63,11 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
              const int64_t* __restrict__ feat_off, const uint8_t* __restrict__ fea_selected,
              int32_t f_from, int32_t f_to, int32_t first_fea, const GradScale* __restrict__ scale,
              GainParams gp, const PartitionCounts* __restrict__ cnt_global, SplitPart* __restrict__ parts,
-             ytk_split* __restrict__ outs, ytk_split* __restrict__ mirror, unsigned int* __restrict__ done) {
+             ytk_split* __restrict__ outs, ytk_split* __restrict__ mirror, unsigned int* __restrict__ done,
+             long long* __restrict__ lh_out) {
     pdl_sync();
     __shared__ double s_tot[2];
+    __shared__ long long s_toth, s_lh[kScanWarps];
     __shared__ float s_lc[kScanWarps];
     __shared__ int s_fid[kScanWarps], s_lo[kScanWarps], s_hi[kScanWarps], s_slice[kScanWarps];
     __shared__ int s_last;
@@ -73,6 +75,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
     const int node = blockIdx.x, slice = blockIdx.y;
     const double ig = scale->inv_g, ih = scale->inv_h;
     const long long* __restrict__ hist = nodes[node].hist;
+    if (!hist) return;                      // an unused entry of a device-planned table (the whole CTA leaves)
     long long sample_cnt = nodes[node].sample_cnt;
     if (nodes[node].cseg >= 0) {
         const PartitionCounts g = cnt_global[nodes[node].cseg];
@@ -95,8 +98,10 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
                 h += __shfl_xor_sync(0xffffffffu, h, d);
             }
             G = (double)g * ig; H = (double)h * ih;
+            if (lane == 0) s_toth = h;
         } else {
             G = -CUDART_INF; H = -CUDART_INF;   // no feature here: neutral for the MAX allreduce (:549)
+            if (lane == 0) s_toth = 0;
         }
         if (lane == 0) { s_tot[0] = G; s_tot[1] = H; }
     }
@@ -108,6 +113,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
 
     float w_lc = -CUDART_INF_F;
     int w_fid = -1, w_lo = -1, w_hi = -1;
+    long long w_lh = 0;                     // fixed-point hessian left of the best split (exact)
     const int f = f_from + slice * kScanWarps + warp;       // one feature per warp
     if (can_split && f < f_to && fea_selected[f]) {
         const long long* hp = hist + feat_off[f];
@@ -116,6 +122,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
         int carry_last = -1;
         float b_lc = -CUDART_INF_F;
         int b_lo = -1, b_hi = 0x7fffffff;
+        long long b_lh = 0;
         // 256 bins at a time (one pass for a feature with uint8 slots) are fetched up front -- 8 loads
         // in flight instead of one dependent memory round trip per 32-bin chunk
         for (int blk = 0; blk < nb; blk += kMaxBins) {
@@ -150,7 +157,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
                     if (rH >= gp.min_child_weight) {
                         float lc = (float)__dsub_rn(__dadd_rn(calc_gain(gp, lG, lH), calc_gain(gp, rG, rH)),
                                                     (double)root_gain);
-                        if (lc > b_lc) { b_lc = lc; b_lo = prev; b_hi = j; }
+                        if (lc > b_lc) { b_lc = lc; b_lo = prev; b_hi = j; b_lh = exH; }
                     }
                 }
             }
@@ -164,18 +171,20 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
             float o_lc = __shfl_xor_sync(0xffffffffu, b_lc, d);
             int o_lo = __shfl_xor_sync(0xffffffffu, b_lo, d);
             int o_hi = __shfl_xor_sync(0xffffffffu, b_hi, d);
-            if (o_lc > b_lc || (o_lc == b_lc && o_hi < b_hi)) { b_lc = o_lc; b_lo = o_lo; b_hi = o_hi; }
+            long long o_lh = __shfl_xor_sync(0xffffffffu, b_lh, d);
+            if (o_lc > b_lc || (o_lc == b_lc && o_hi < b_hi)) { b_lc = o_lc; b_lo = o_lo; b_hi = o_hi; b_lh = o_lh; }
         }
-        if (b_lc > w_lc) { w_lc = b_lc; w_fid = f; w_lo = b_lo; w_hi = b_hi; }
+        if (b_lc > w_lc) { w_lc = b_lc; w_fid = f; w_lo = b_lo; w_hi = b_hi; w_lh = b_lh; }
     }
-    if (lane == 0) { s_lc[warp] = w_lc; s_fid[warp] = w_fid; s_lo[warp] = w_lo; s_hi[warp] = w_hi; }
+    if (lane == 0) { s_lc[warp] = w_lc; s_fid[warp] = w_fid; s_lo[warp] = w_lo; s_hi[warp] = w_hi; s_lh[warp] = w_lh; }
     __syncthreads();
     if (threadIdx.x == 0) {
         // warps hold increasing feature ids: strict > keeps the smaller fid on ties
-        SplitPart best = {-CUDART_INF_F, -1, -1, -1};
+        SplitPart best = {-CUDART_INF_F, -1, -1, -1, 0, 0};
         for (int w = 0; w < kScanWarps; w++)
-            if (s_fid[w] >= 0 && s_lc[w] > best.lc) best = {s_lc[w], s_fid[w], s_lo[w], s_hi[w]};
+            if (s_fid[w] >= 0 && s_lc[w] > best.lc) best = {s_lc[w], s_fid[w], s_lo[w], s_hi[w], s_lh[w], 0};
         parts[(size_t)node * gridDim.y + slice] = best;
+        if (slice == 0 && lh_out) lh_out[2 * node + 1] = s_toth;
         if (slice == 0) {
             ytk_split* out = outs + node;
             out->sum_grad = totG; out->sum_hess = totH;
@@ -190,26 +199,29 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
     if (!s_last) return;
     __threadfence();
     // slices hold increasing feature ids: the maximum, ties to the lowest slice = smallest fid
-    SplitPart bp = {-CUDART_INF_F, -1, -1, -1};
+    SplitPart bp = {-CUDART_INF_F, -1, -1, -1, 0, 0};
     int bs = 0x7fffffff;
     for (int s = threadIdx.x; s < (int)gridDim.y; s += blockDim.x) {
-        const int4 v = __ldcg(reinterpret_cast<const int4*>(parts + (size_t)node * gridDim.y + s));
+        const SplitPart* pp = parts + (size_t)node * gridDim.y + s;
+        const int4 v = __ldcg(reinterpret_cast<const int4*>(pp));
         const float lc = __int_as_float(v.x);
-        if (v.y >= 0 && lc > bp.lc) { bp = {lc, v.y, v.z, v.w}; bs = s; }
+        if (v.y >= 0 && lc > bp.lc) { bp = {lc, v.y, v.z, v.w, __ldcg(&pp->lh), 0}; bs = s; }
     }
     for (int d = 16; d > 0; d >>= 1) {
         const float olc = __shfl_xor_sync(0xffffffffu, bp.lc, d);
         const int ofid = __shfl_xor_sync(0xffffffffu, bp.fid, d), olo = __shfl_xor_sync(0xffffffffu, bp.lo, d);
         const int ohi = __shfl_xor_sync(0xffffffffu, bp.hi, d), os = __shfl_xor_sync(0xffffffffu, bs, d);
-        if (ofid >= 0 && (olc > bp.lc || (olc == bp.lc && os < bs))) { bp = {olc, ofid, olo, ohi}; bs = os; }
+        const long long olh = __shfl_xor_sync(0xffffffffu, bp.lh, d);
+        if (ofid >= 0 && (olc > bp.lc || (olc == bp.lc && os < bs))) { bp = {olc, ofid, olo, ohi, olh, 0}; bs = os; }
     }
-    if (lane == 0) { s_lc[warp] = bp.lc; s_fid[warp] = bp.fid; s_lo[warp] = bp.lo; s_hi[warp] = bp.hi; s_slice[warp] = bs; }
+    if (lane == 0) { s_lc[warp] = bp.lc; s_fid[warp] = bp.fid; s_lo[warp] = bp.lo; s_hi[warp] = bp.hi; s_slice[warp] = bs; s_lh[warp] = bp.lh; }
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int w = 1; w < kScanWarps; w++)
             if (s_fid[w] >= 0 && (s_lc[w] > bp.lc || (s_lc[w] == bp.lc && s_slice[w] < bs))) {
-                bp = {s_lc[w], s_fid[w], s_lo[w], s_hi[w]}; bs = s_slice[w];
+                bp = {s_lc[w], s_fid[w], s_lo[w], s_hi[w], s_lh[w], 0}; bs = s_slice[w];
             }
+        if (lh_out) lh_out[2 * node] = bp.lh;
         ytk_split r;                       // totals, root gain and node value: written by the node's slice 0
         r.sum_grad = __ldcg(&outs[node].sum_grad); r.sum_hess = __ldcg(&outs[node].sum_hess);
         r.root_gain = __ldcg(&outs[node].root_gain); r.node_value = __ldcg(&outs[node].node_value);
@@ -228,12 +240,13 @@ int split_scan_slices(int32_t f_from, int32_t f_to) {
 cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t* start, const int64_t* feat_off,
                               const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
                               const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
-                              SplitPart* parts, ytk_split* out, ytk_split* mirror, unsigned int* done, cudaStream_t st) {
+                              SplitPart* parts, ytk_split* out, ytk_split* mirror, unsigned int* done, cudaStream_t st,
+                              long long* lh_out) {
     if (n_nodes <= 0) return cudaSuccess;
     const int slices = split_scan_slices(f_from, f_to);
     dim3 grid((unsigned)n_nodes, (unsigned)slices);
     return launch_chain(split_scan_k, grid, dim3(kScanWarps * 32), 0, st, nodes, start, feat_off, fea_selected, f_from,
-                        f_to, first_fea, scale, gp, cnt_global, parts, out, mirror, done);
+                        f_to, first_fea, scale, gp, cnt_global, parts, out, mirror, done, lh_out);
 }
 
 }  // namespace ytk

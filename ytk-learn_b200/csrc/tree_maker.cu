@@ -113,6 +113,9 @@ void free_all(ytk_gbdt* h) {
     h->h_counts.release(); h->h_split.release(); h->h_leaf.release(); h->h_scale.release(); h->arena.release();
     for (auto* it : h->pool.all) { if (it->own_buf) F(it->buf); delete it; }
     F(h->d_pool_chunk);
+    F(h->eng.dev);
+    if (h->eng.host) cudaFreeHost(h->eng.host);
+    for (auto e : h->ev_stage) cudaEventDestroy(e);
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto e : h->evc) cudaEventDestroy(e);
     if (h->comm) ytk::nccl_api().CommDestroy(h->comm);
@@ -751,6 +754,7 @@ int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank,
     if (const char* s = getenv("YTK_GBDT_STABLE_PARTITION")) h->single_pass_partition = atoi(s) == 0;
     if (const char* s = getenv("YTK_GBDT_NO_PLAN_AHEAD")) h->plan_ahead = atoi(s) == 0;
     if (const char* s = getenv("YTK_GBDT_SPIN")) h->spin_wait = atoi(s) != 0;
+    if (const char* s = getenv("YTK_GBDT_NO_ENGINE")) h->use_engine = atoi(s) == 0;
     if (const char* s = getenv("YTK_GBDT_TRACE")) h->trace = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_LOOKAHEAD")) h->lookahead = std::max(1, std::min(1024, atoi(s)));
     auto bail = [&](int code) { free_all(h); delete h; return code; };
@@ -908,9 +912,10 @@ static int set_bins_impl(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n
         // beyond that (or beyond 1 GiB here) is still allocated on demand.
         const size_t slot_bytes = (size_t)h->seg_max * sizeof(long long);
         size_t n_pre = 2 * (size_t)capacity + 2;
-        n_pre = std::min(n_pre, std::max<size_t>(2, (size_t(1) << 30) / slot_bytes));
+        n_pre = std::min(n_pre, std::max<size_t>(2, (size_t(8) << 30) / slot_bytes));
         if (h->p.histogram_pool_capacity > 0) n_pre = (size_t)capacity;      // a bounded pool never holds more
         CK(cudaMalloc(&h->d_pool_chunk, n_pre * slot_bytes));
+        h->pool_chunk_slots = n_pre;
         for (size_t i = 0; i < n_pre; i++) {
             HistPool::Item* it = new HistPool::Item{-1, h->d_pool_chunk + i * (size_t)h->seg_max, false};
             h->pool.all.push_back(it);
