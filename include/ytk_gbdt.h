@@ -193,6 +193,20 @@ int ytk_gbdt_set_grads(ytk_gbdt *h, const float *gp_chunk, int64_t row0, int64_t
 int ytk_gbdt_make_tree(ytk_gbdt *h, int32_t gid, const int32_t *fea_index, int32_t n_fea,
                        const uint8_t *row_mask, ytk_tree_out *out, ytk_time_stats *ts);
 
+/* The same trainer with its `world` row shards on ONE device: `world` handles that share a stream; every
+ * collective of the data-parallel scheme (J/data/gbdt/HistogramBuilder.java:95,
+ * J/optimizer/gbdt/DataParallelTreeMaker.java:538,560,640-653) becomes a plain kernel over the members'
+ * buffers, the ranks' kernels running one after the other.  Same kernels, same [owner][node][segment]
+ * staging layout, feature ownership and record merge as one process per GPU -- for hosts with fewer GPUs
+ * than shards, and for testing the multi-rank path on one GPU.  Every member gets set_bins / upload_rows /
+ * set_grads like any handle; ytk_gbdt_make_tree_clique replaces the `world` concurrent ITreeMaker.make
+ * calls (row_masks: NULL or one mask pointer per rank, each NULL or n_rows of that rank; outs/ts: one per
+ * rank, ts may be NULL).  Takes what the device-planned level loop takes (level-wise growth, max_depth
+ * 1..12, no bounded pool, no row-count stop rule, dense rows); anything else: YTK_ERR_UNSUPPORTED. */
+int ytk_gbdt_create_clique(const ytk_gbdt_params *params, int32_t device, int32_t world, ytk_gbdt **out /* [world] */);
+int ytk_gbdt_make_tree_clique(ytk_gbdt **members, int32_t world, int32_t gid, const int32_t *fea_index, int32_t n_fea,
+                              const uint8_t *const *row_masks, ytk_tree_out *outs, ytk_time_stats *ts);
+
 /* Final partition of the last make(): node id of every local row, -1 if not sampled
  * (SamplePositionData.getPosAndSampleIndex, J/data/gbdt/SamplePositionData.java:64-74;
  * consumed by TreeRefiner, J/optimizer/gbdt/TreeRefiner.java:104-123). */

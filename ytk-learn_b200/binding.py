@@ -96,6 +96,9 @@ _SIGS = {
     "ytk_gbdt_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "ytk_gbdt_create": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "ytk_gbdt_destroy": (C.c_int, [C.c_void_p]),
+    "ytk_gbdt_create_clique": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "ytk_gbdt_make_tree_clique": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                            C.c_void_p]),
     "ytk_gbdt_set_bins": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64]),
     "ytk_gbdt_upload_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32]),
     "ytk_gbdt_quantize_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]),

@@ -32,8 +32,15 @@ bool engine_applicable(const ytk_gbdt* h) {
     if (p.min_split_samples > 0 || p.histogram_pool_capacity > 0) return false;
     if (p.max_leaf_cnt > 0 && (long long)p.max_leaf_cnt < (1LL << p.max_depth)) return false;      // the leaf budget could bind
     if (h->sparse || h->n_wide > 0) return false;
-    if (h->world > 1) return false;
     if ((size_t)(1u << (p.max_depth - 1)) > h->pool_chunk_slots) return false;
+    if (h->world > 1) {
+        // exchanges over peer memory (one process per GPU), or a clique of handles on one device
+        if (!h->peer_mode && !h->clique) return false;
+        if (p.max_depth > 12) return false;
+        const size_t slots = size_t(1) << (p.max_depth - 1);
+        if ((int)slots > h->peer_cap_nodes / 2) return false;
+        if (slots * (size_t)h->seg_max * h->world > h->hist_cap_words) return false;
+    }
     return true;
 }
 
@@ -55,7 +62,8 @@ static int engine_reserve(ytk_gbdt* h, int D) {
                  o_counts = take(slots * sizeof(ytk::PartitionCounts)), o_gcounts = take(slots * sizeof(ytk::PartitionCounts)),
                  o_build = take(2 * slots * sizeof(ytk::BuildNode)), o_nbuild = take(sizeof(int)),
                  o_subs = take(slots * sizeof(ytk::SubItem)), o_scans = take(2 * slots * sizeof(ytk::ScanNode)),
-                 o_segout = take(2 * slots * sizeof(long long*));
+                 o_segout = take(2 * slots * sizeof(long long*)), o_segfinal = take(2 * slots * sizeof(long long*)),
+                 o_recs_local = take(2 * slots * sizeof(ytk_split)), o_lh_local = take(4 * slots * sizeof(long long));
     CK(cudaMalloc(&e.dev, off));
     CK(cudaMemsetAsync(e.dev, 0, off, h->st));
     CK(cudaHostAlloc((void**)&e.host, mirror_bytes, cudaHostAllocDefault));
@@ -75,6 +83,9 @@ static int engine_reserve(ytk_gbdt* h, int D) {
     t.subs = reinterpret_cast<ytk::SubItem*>(e.dev + o_subs);
     t.scans = reinterpret_cast<ytk::ScanNode*>(e.dev + o_scans);
     t.seg_out = reinterpret_cast<long long**>(e.dev + o_segout);
+    t.seg_final = reinterpret_cast<long long**>(e.dev + o_segfinal);
+    t.recs_local = reinterpret_cast<ytk_split*>(e.dev + o_recs_local);
+    t.lh_local = reinterpret_cast<long long*>(e.dev + o_lh_local);
     e.h_nodes = reinterpret_cast<ytk::LvNode*>(e.host + o_nodes);
     e.h_recs = reinterpret_cast<ytk_split*>(e.host + o_recs);
     e.h_leaf = reinterpret_cast<long long*>(e.host + o_leaf);
@@ -89,26 +100,50 @@ public:
     LevelEngine(ytk_gbdt* handle, ytk_tree_out* tree, ytk_time_stats* stats)
         : h(handle), p(handle->p), out(tree), T(stats), D(handle->p.max_depth) {}
 
+    // One rank on its own (one GPU, or one process per GPU with exchanges over peer memory).
     int run(int gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask) {
         const double t0 = now_ms();
-        RET(begin(gid, fea_index, n_fea, row_mask));
-        RET(enqueue_root());
-        for (int d = 0; d < D; d++) RET(enqueue_level(d));
+        const int x = h->world > 1 ? ytk::kXAll : 0;
+        RET(begin_scale(gid, fea_index, n_fea));
+        if (x) RET(x_max(x));
+        RET(begin_root(gid, row_mask));
+        RET(root_hist());
+        if (x) RET(x_hist(-1, x));
+        RET(root_scan());
+        if (x) RET(x_recs(-1, x));
+        for (int d = 0; d < D; d++) {
+            RET(level_partition(d));
+            if (d == D - 1) {
+                RET(level_leaf(d));
+                if (x) RET(x_leaf(d, x));
+            } else {
+                RET(level_hist(d));
+                if (x) RET(x_hist(d, x));
+                RET(level_scan(d));
+                if (x) RET(x_recs(d, x));
+            }
+        }
         RET(finish_enqueue());
         const double t1 = now_ms();
         CK(cudaStreamSynchronize(h->st));                 // the one host wait of the tree
+        RET(peer_check(h, "make_tree"));
         const double t2 = now_ms();
+        RET(after_wait(row_mask != nullptr, t0, t1, t2));
+        return YTK_OK;
+    }
+
+    // ---- the phases, also driven rank by rank for a clique of handles on one device (engine_make_tree_clique) ----
+    int after_wait(bool masked, double t0, double t1, double t2) {
         T->batches = 0;
         T->max_batch_ms = t2 - t0;
         h->arena.rewind();
-        RET(assemble(row_mask != nullptr));
+        RET(assemble(masked));
         RET(stage_times());
         T->enqueue_ms = t1 - t0;
         T->host_wait_ms = t2 - t1;
         return YTK_OK;
     }
 
-private:
     ytk_gbdt* h;
     const ytk_gbdt_params& p;
     ytk_tree_out* out;
@@ -133,19 +168,25 @@ private:
         return YTK_OK;
     }
 
-    int begin(int gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask) {
+    int begin_scale(int gid, const int32_t* fea_index, int32_t n_fea) {
         RET(engine_reserve(h, D));
         t = h->eng.t;
         t.pool = h->d_pool_chunk;
-        t.staging = nullptr;
+        t.staging = h->world > 1 ? reinterpret_cast<long long*>(h->my_hist) : nullptr;
         t.seg_max = h->seg_max;
         t.world = h->world;
-        t.ticket = h->d_ticket ? h->d_ticket + 1 : nullptr;
         RET(set_features(h, fea_index, n_fea, &first_owned, &n_sel));
         h->pool.clear();
         h->ev_stage_used = 0;
         RET(mark(kInit));                                 // (event 0: the start; its stage label is unused)
-        RET(quantize_grads(h, gid));
+        CK(ytk::launch_grad_absmax(h->d_gp, h->N, p.class_num, gid, h->d_absmax, h->st));
+        h->launches++;
+        return YTK_OK;
+    }
+
+    int begin_root(int gid, const uint8_t* row_mask) {
+        CK(ytk::launch_grad_quantize(h->d_gp, h->N, p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->fixed_bits, h->st));
+        h->launches++;
         CK(cudaMemcpyAsync(h->h_scale.h, h->d_scale, sizeof(ytk::GradScale), cudaMemcpyDeviceToHost, h->st));
         CK(cudaMemsetAsync(h->eng.dev, 0, h->eng.clear_bytes, h->st));
         root_buf = -1;
@@ -154,13 +195,17 @@ private:
         if (row_mask) {
             // resetPositionAfterSample (SamplePositionData.java:84-87): the sampled rows first, in buffer 0
             if (!h->d_mask) CK(cudaMalloc(&h->d_mask, std::max<int64_t>(h->N, 1)));
-            void* stage = h->arena.take((size_t)h->N, h->st);
+            void* stage = h->arena.take((size_t)std::max<int64_t>(h->N, 1), h->st);
             if (!stage) return fail(YTK_ERR_CUDA, "pinned staging allocation failed");
             memcpy(stage, row_mask, (size_t)h->N);
             CK(cudaMemcpyAsync(h->d_mask, stage, h->N, cudaMemcpyHostToDevice, h->st));
             std::vector<ytk::SplitSeg> sg(1);
             sg[0] = {0, (long long)h->N, -1, -1, 0.f, 0, 0, 0};
-            RET(partition_launch(h, h->d_mask, 0, sg));   // queued, not waited for: the count stays on the device
+            const int world = h->world;
+            h->world = 1;                                 // a local operation: the count stays on the device, no exchange
+            const int rc = partition_launch(h, h->d_mask, 0, sg);
+            h->world = world;
+            RET(rc);
             mask_counts = h->t_counts.d;
             root_buf = 0;
         }
@@ -173,12 +218,47 @@ private:
         return YTK_OK;
     }
 
-    int hist_launch() {
+    // ---- exchanges (world > 1) ------------------------------------------------------------------------------
+    int x_max(int phase) {
+        if (phase != ytk::kXReduce) ++h->epoch[0];
+        CK(ytk::launch_lv_xmax(h->pt, h->d_absmax, h->off_max, h->slot_max, 0, h->epoch[0], phase, h->d_peer_err, h->st));
+        h->launches++;
+        return YTK_OK;
+    }
+    int x_hist(int d, int phase) {
+        if (phase != ytk::kXReduce) ++h->epoch[1];
+        CK(ytk::launch_lv_xhist(h->pt, t, d, d < 0 ? 1 : (1 << d), h->off_counts, h->slot_counts, 1, h->epoch[1], phase,
+                                h->d_peer_err, h->st));
+        h->launches++;
+        if (phase != ytk::kXPush) RET(mark(kComm));
+        return YTK_OK;
+    }
+    int x_recs(int d, int phase) {
+        if (phase != ytk::kXReduce) ++h->epoch[2];
+        const int n = d < 0 ? 1 : (2 << d);
+        const long long first = d < 0 ? 0 : (2ll << d) - 1;
+        CK(ytk::launch_lv_xrecs(h->pt, t, n, first, h->off_recs, h->slot_recs, h->off_lh, h->slot_lh, 2, h->epoch[2], phase,
+                                h->d_peer_err, h->st));
+        h->launches++;
+        if (phase != ytk::kXPush) RET(mark(kSync));
+        return YTK_OK;
+    }
+    int x_leaf(int d, int phase) {
+        if (phase != ytk::kXReduce) ++h->epoch[3];
+        CK(ytk::launch_lv_xleaf(h->pt, t, d, h->off_leaf, h->slot_leaf, h->off_counts, h->slot_counts, 3, h->epoch[3], phase,
+                                h->d_peer_err, h->st));
+        h->launches++;
+        if (phase != ytk::kXPush) RET(mark(kComm));
+        return YTK_OK;
+    }
+
+    int hist_launch(int m_slots) {
         cudaEvent_t e0, e1;
         RET(hist_events(h, &e0, &e1));
         CK(cudaEventRecord(e0, h->st));
         CK(ytk::launch_hist_span(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], t.build, t.n_build, h->groups, h->F,
-                                 h->d_group_mask, h->d_nbins, h->d_feat_owner, h->d_off_inner, 0, t.seg_out, h->st));
+                                 h->d_group_mask, h->d_nbins, h->d_feat_owner, h->d_off_inner,
+                                 h->world == 1 ? 0 : (long long)m_slots * h->seg_max, t.seg_out, h->st));
         CK(cudaEventRecord(e1, h->st));
         h->launches++;
         return YTK_OK;
@@ -187,25 +267,39 @@ private:
     int scan_launch(const ytk::ScanNode* nodes, int n, size_t first_heap) {
         CK(h->t_parts.reserve((size_t)n * ytk::split_scan_slices(h->f_from, h->f_to)));
         RET(scan_done_counters(h, n));
+        // several GPUs: this rank's records first, the merged ones go to the heap arrays (x_recs)
         CK(ytk::launch_split_scan(nodes, n, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to, first_owned,
-                                  h->d_scale, gain_params(p), nullptr, h->t_parts.d, t.recs + first_heap, nullptr,
-                                  h->t_scan_done.d, h->st, t.left_h + 2 * first_heap));
+                                  h->d_scale, gain_params(p), nullptr, h->t_parts.d,
+                                  h->world == 1 ? t.recs + first_heap : t.recs_local, nullptr, h->t_scan_done.d, h->st,
+                                  h->world == 1 ? t.left_h + 2 * first_heap : t.lh_local));
         h->launches++;
         return YTK_OK;
     }
 
+    // histogram slots that receive atomics start at zero: the slots themselves on one GPU, else the staging buffer
+    int zero_build_targets(int first_slot, int m_slots) {
+        if (h->world == 1)
+            CK(cudaMemsetAsync(t.pool + (size_t)first_slot * h->seg_max, 0, (size_t)m_slots * h->seg_max * sizeof(long long), h->st));
+        else
+            CK(cudaMemsetAsync(t.staging, 0, (size_t)m_slots * h->seg_max * h->world * sizeof(long long), h->st));
+        return YTK_OK;
+    }
+
     // findBestSplit(root) (:302-318)
-    int enqueue_root() {
-        CK(cudaMemsetAsync(t.pool, 0, (size_t)h->seg_max * sizeof(long long), h->st));
-        RET(hist_launch());
+    int root_hist() {
+        RET(zero_build_targets(0, 1));
+        RET(hist_launch(1));
         RET(mark(kHist));
+        return YTK_OK;
+    }
+    int root_scan() {
         RET(scan_launch(t.scans, 1, 0));
         RET(mark(kSplit));
         return YTK_OK;
     }
 
-    // One level of the loop (:244-281) for all its nodes at once.
-    int enqueue_level(int d) {
+    // One level of the loop (:244-281) for all its nodes at once: position.resetPosition (:260) ...
+    int level_partition(int d) {
         const int m = 1 << d;
         const int buf = level_buf(root_buf, d), child_buf = buf == 0 ? 1 : 0;
         const bool leaf = d == D - 1;                     // the children are leaves (:266)
@@ -218,16 +312,26 @@ private:
         RET(mark(kPart));
         CK(ytk::launch_lv_plan_build(t, d, child_buf, leaf, h->st));
         h->launches += 3;
-        if (leaf) {
-            CK(ytk::launch_lv_leaf_sums(t, d, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], ytk::kNumSMs * 4, h->st));
-            h->launches++;
-            RET(mark(kInit));
-            return YTK_OK;
-        }
-        // the level's fresh slots (smaller children) start at zero; the larger children overwrite their parents
-        CK(cudaMemsetAsync(t.pool + (size_t)m * h->seg_max, 0, (size_t)m * h->seg_max * sizeof(long long), h->st));
-        RET(hist_launch());
+        return YTK_OK;
+    }
+    // ... computeLeafStats (:341-385) when the children are leaves ...
+    int level_leaf(int d) {
+        CK(ytk::launch_lv_leaf_sums(t, d, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], ytk::kNumSMs * 4, h->st));
+        h->launches++;
+        RET(mark(kInit));
+        return YTK_OK;
+    }
+    // ... else buildHist(parent, l, r) (:489-508): the smaller children from rows ...
+    int level_hist(int d) {
+        const int m = 1 << d;
+        RET(zero_build_targets(m, m));
+        RET(hist_launch(m));
         RET(mark(kHist));
+        return YTK_OK;
+    }
+    // ... the larger ones by subtraction, and findBestSplit of both
+    int level_scan(int d) {
+        const int m = 1 << d;
         CK(ytk::launch_hist_subtract(t.subs, m, h->seg_max, h->st));
         h->launches++;
         RET(scan_launch(t.scans, 2 * m, (size_t)2 * m - 1));
@@ -308,7 +412,7 @@ private:
                 if (d + 1 == D) {
                     // computeLeafStats (:341-385): the smaller child's sums, the larger one by subtraction
                     const bool small_left = pn.gcnt_l < pn.gcnt_r;          // (:344-350)
-                    if (small_left != small_left_dev)
+                    if (h->world == 1 && small_left != small_left_dev)    // (several GPUs: both children were summed)
                         return fail(YTK_ERR_ARG, "internal: leaf sums were taken over the other child (heap node %d)", e.heap);
                     const int hs = small_left ? hl : hr;
                     const double sG = (double)leaf[2 * hs] * sc.inv_g, sH = (double)leaf[2 * hs + 1] * sc.inv_h;
@@ -363,6 +467,47 @@ int engine_make_tree(ytk_gbdt* h, int gid, const int32_t* fea_index, int32_t n_f
                      ytk_time_stats* T) {
     LevelEngine e(h, out, T);
     return e.run(gid, fea_index, n_fea, row_mask);
+}
+
+// The ranks of a clique of handles on ONE device, phase by phase on their shared stream: every rank's
+// kernels of a phase, then the exchange as "push" for every rank and "reduce" for every rank.  The same
+// kernels, tables and staging layout as one process per GPU; only the flags between GPUs are not needed.
+int engine_make_tree_clique(ytk_gbdt** hs, int world, int gid, const int32_t* fea_index, int32_t n_fea,
+                            const uint8_t* const* row_masks, ytk_tree_out* outs, ytk_time_stats* Ts) {
+    std::vector<LevelEngine> eng;
+    eng.reserve(world);
+    for (int r = 0; r < world; r++) eng.emplace_back(hs[r], &outs[r], &Ts[r]);
+    const int D = hs[0]->p.max_depth;
+    const double t0 = now_ms();
+#define EACH(call) for (int r = 0; r < world; r++) RET(eng[r].call)
+#define XCHG(fn, d) do { EACH(fn(d, ytk::kXPush)); EACH(fn(d, ytk::kXReduce)); } while (0)
+    EACH(begin_scale(gid, fea_index, n_fea));
+    EACH(x_max(ytk::kXPush)); EACH(x_max(ytk::kXReduce));
+    for (int r = 0; r < world; r++) RET(eng[r].begin_root(gid, row_masks ? row_masks[r] : nullptr));
+    EACH(root_hist());
+    XCHG(x_hist, -1);
+    EACH(root_scan());
+    XCHG(x_recs, -1);
+    for (int d = 0; d < D; d++) {
+        EACH(level_partition(d));
+        if (d == D - 1) {
+            EACH(level_leaf(d));
+            XCHG(x_leaf, d);
+        } else {
+            EACH(level_hist(d));
+            XCHG(x_hist, d);
+            EACH(level_scan(d));
+            XCHG(x_recs, d);
+        }
+    }
+    EACH(finish_enqueue());
+#undef XCHG
+#undef EACH
+    const double t1 = now_ms();
+    CK(cudaStreamSynchronize(hs[0]->st));
+    const double t2 = now_ms();
+    for (int r = 0; r < world; r++) RET(eng[r].after_wait(row_masks && row_masks[r], t0, t1, t2));
+    return YTK_OK;
 }
 
 }  // namespace ytkh

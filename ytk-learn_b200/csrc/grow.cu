@@ -740,6 +740,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     if (!h->rows_set || !h->grads_set) return fail(YTK_ERR_ARG, "make_tree: set_bins/upload_rows/set_grads first");
     if (gid < 0 || gid >= h->p.class_num) return fail(YTK_ERR_ARG, "make_tree: groupId %d not in [0,%d)", gid, h->p.class_num);
     if (out->capacity < 1) return fail(YTK_ERR_CAPACITY, "make_tree: tree capacity %d", out->capacity);
+    if (h->clique) return fail(YTK_ERR_ARG, "make_tree: this handle is a member of a clique (ytk_gbdt_make_tree_clique)");
     CK(cudaSetDevice(h->device));
     const double t_start = now_ms();
     ytk_time_stats local_ts;
@@ -801,6 +802,45 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     T->peer_collectives = h->peer_mode ? 1 : 0;
     T->total = now_ms() - t_start;
     if (ts) *ts = *T;
+    return YTK_OK;
+}
+
+int ytk_gbdt_make_tree_clique(ytk_gbdt** hs, int32_t world, int32_t gid, const int32_t* fea_index, int32_t n_fea,
+                              const uint8_t* const* row_masks, ytk_tree_out* outs, ytk_time_stats* ts) {
+    if (!hs || !outs || world < 2) return fail(YTK_ERR_ARG, "make_tree_clique: bad arguments");
+    for (int r = 0; r < world; r++) {
+        ytk_gbdt* h = hs[r];
+        if (!h || !h->clique || h->world != world || h->rank != r || h->clique_members != hs[0]->clique_members)
+            return fail(YTK_ERR_ARG, "make_tree_clique: handle %d is not rank %d of one clique of %d", r, r, world);
+        if (!h->rows_set || !h->grads_set) return fail(YTK_ERR_ARG, "make_tree_clique: set_bins/upload_rows/set_grads first (rank %d)", r);
+        if (gid < 0 || gid >= h->p.class_num) return fail(YTK_ERR_ARG, "make_tree_clique: groupId %d", gid);
+        if (h->F != hs[0]->F || h->B != hs[0]->B) return fail(YTK_ERR_ARG, "make_tree_clique: the ranks' bin layouts differ");
+        if (outs[r].capacity < 1) return fail(YTK_ERR_CAPACITY, "make_tree_clique: tree capacity %d", outs[r].capacity);
+    }
+    CK(cudaSetDevice(hs[0]->device));
+    if (!hs[0]->clique_linked) {           // every member sees every member's exchange and staging buffers
+        for (int r = 0; r < world; r++)
+            for (int q = 0; q < world; q++) { hs[r]->pt.xchg[q] = hs[q]->my_xchg; hs[r]->pt.hist[q] = hs[q]->my_hist; }
+        for (int r = 0; r < world; r++) hs[r]->clique_linked = true;
+    }
+    if (!engine_applicable(hs[0]))
+        return fail(YTK_ERR_UNSUPPORTED, "make_tree_clique: only what the device-planned level loop takes (level-wise growth, "
+                                         "max_depth 1..12, unbounded pool, no row-count rule, dense rows of at most 256 bins)");
+    const double t_start = now_ms();
+    std::vector<ytk_time_stats> T(world);
+    memset(T.data(), 0, sizeof(ytk_time_stats) * world);
+    for (int r = 0; r < world; r++) { hs[r]->launches = 0; hs[r]->ev_used = 0; hs[r]->evc_used = 0; }
+    RET(engine_make_tree_clique(hs, world, gid, fea_index, n_fea, row_masks, outs, T.data()));
+    for (int r = 0; r < world; r++) {
+        ytk_gbdt* h = hs[r];
+        h->last_tree.resize(outs[r].n_nodes);
+        for (int nid = 0; nid < outs[r].n_nodes; nid++)
+            h->last_tree[nid] = {outs[r].left[nid], outs[r].right[nid], outs[r].fid[nid], outs[r].node_info[nid]};
+        h->last_gid = gid;
+        T[r].kernel_launches = h->launches;
+        T[r].total = now_ms() - t_start;
+        if (ts) ts[r] = T[r];
+    }
     return YTK_OK;
 }
 

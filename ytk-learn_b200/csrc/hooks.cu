@@ -49,7 +49,7 @@ int ytk_gbdt_build_hist(ytk_gbdt* h, int32_t gid, const int32_t* rows, int64_t n
         CK(ytk::launch_hist_wide(wide_cols(h), h->d_wide_fids, (int)h->wide_sel.size(), h->d_gq, h->d_rowidx[0],
                                  h->d_rowidx[1], h->t_items.d, (int)items.size(), h->d_feat_zero, h->d_off_flat, 0,
                                  h->t_seg_out.d, nullptr, nullptr, h->st));
-    if (h->world > 1)
+    if (h->world > 1 && h->comm)           // (a clique member has no communicator: its hook returns the local histogram)
         NK(ytk::nccl_api().AllReduce(h->d_hist_flat, h->d_hist_flat, (size_t)len, ncclInt64, ncclSum, h->comm, h->st));
     CK(ytk::launch_hist_to_double(h->d_hist_flat, len, h->d_scale, h->d_hist_dbl, h->st));
     CK(cudaMemcpyAsync(out, h->d_hist_dbl, len * sizeof(double), cudaMemcpyDeviceToHost, h->st));

@@ -352,6 +352,12 @@ struct ytk_gbdt {
     size_t hist_cap_words = 0;               // capacity of my_hist in int64 words
     int peer_cap_nodes = 0;                  // nodes per batch the exchange slots can hold
     size_t off_counts = 0, off_recs = 0, off_leaf = 0, slot_counts = 0, slot_recs = 0, slot_leaf = 0;
+    size_t off_lh = 0, slot_lh = 0, off_max = 0, slot_max = 0;
+    // a clique of `world` handles on ONE device sharing one stream (ytk_gbdt_create_clique): the ranks' kernels run one
+    // after the other, the exchanges read the other handles' buffers directly
+    bool clique = false;
+    bool clique_linked = false;
+    ytk_gbdt** clique_members = nullptr;     // [world], owned by rank 0
     unsigned long long epoch[ytk::kPeerFlagSets] = {0, 0, 0, 0};
     int* d_peer_err = nullptr;               // mapped host memory: set by a peer kernel that gave up waiting
     double peer_timeout_ms = 10000.0;        // YTK_GBDT_PEER_TIMEOUT_MS
@@ -463,5 +469,9 @@ int partition_nodes(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const s
 bool engine_applicable(const ytk_gbdt* h);
 int engine_make_tree(ytk_gbdt* h, int gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask, ytk_tree_out* out,
                      ytk_time_stats* T);
+int engine_make_tree_clique(ytk_gbdt** hs, int world, int gid, const int32_t* fea_index, int32_t n_fea,
+                            const uint8_t* const* row_masks, ytk_tree_out* outs, ytk_time_stats* Ts);
+// sizes and offsets of the exchange areas (equal on every rank); returns the bytes of an exchange buffer
+size_t peer_layout(ytk_gbdt* h, size_t* hist_words);
 
 }  // namespace ytkh

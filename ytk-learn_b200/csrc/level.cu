@@ -42,6 +42,10 @@ __global__ void lv_root_k(LvTables t, long long begin, long long end, int buf, c
     t.build[0] = {begin, end, n + kHistFlushCost, buf, 0};
     *t.n_build = n > 0 ? 1 : 0;
     t.seg_out[0] = t.world == 1 ? t.pool : t.staging;
+    if (t.world > 1) {
+        t.seg_final[0] = t.pool;
+        t.counts[0] = {n, 0};                                    // summed over the ranks beside the root histogram
+    }
     t.scans[0] = {t.pool, n, -1, 0};
 }
 
@@ -112,8 +116,8 @@ lv_plan_build_k(LvTables t, int d, int child_buf, int leaf) {
     __syncthreads();
     for (int s0 = 0; s0 < m; s0 += kPlanThreads) {
         const int s = s0 + threadIdx.x;
-        bool add = false;
-        BuildNode bn = {0, 0, 0, 0, 0};
+        bool add = false, add2 = false;      // add2: several GPUs, last level: the larger child's sums are taken too
+        BuildNode bn = {0, 0, 0, 0, 0}, bn2 = bn;
         if (s < m) {
             const int p = L0 + s;
             LvNode nd = t.nodes[p];
@@ -142,6 +146,15 @@ lv_plan_build_k(LvTables t, int d, int child_buf, int leaf) {
                 bn.buf = child_buf;
                 bn.seg = leaf ? 2 * s + (small_left ? 0 : 1) : s;     // leaf sums are kept per child, histograms per parent slot
                 add = bn.end > bn.begin;
+                if (leaf && t.world > 1) {
+                    // which child is the smaller one follows from the GLOBAL counts, which are only summed beside
+                    // the leaf sums themselves: both children are summed and the host takes its pick (:344-350)
+                    bn2.begin = small_left ? cr.begin : cl.begin;
+                    bn2.end = small_left ? cr.end : cl.end;
+                    bn2.buf = child_buf;
+                    bn2.seg = 2 * s + (small_left ? 1 : 0);
+                    add2 = bn2.end > bn2.begin;
+                }
                 if (!leaf) {
                     long long* parent_h = t.pool + (long long)nd.slot * t.seg_max;
                     long long* small_h = t.pool + (long long)slot_small * t.seg_max;
@@ -150,16 +163,20 @@ lv_plan_build_k(LvTables t, int d, int child_buf, int leaf) {
                     sc_r.hist = small_left ? parent_h : small_h;
                     sc_l.sample_cnt = gc.left; sc_r.sample_cnt = gc.right;
                     t.seg_out[s] = t.world == 1 ? small_h : t.staging + (long long)s * t.seg_max;
+                    if (t.world > 1) t.seg_final[s] = small_h;
                 }
+            } else if (!leaf && t.world > 1) {
+                t.seg_final[s] = nullptr;
             }
             if (!leaf) { t.subs[s] = sub; t.scans[2 * s] = sc_l; t.scans[2 * s + 1] = sc_r; }
         }
         int n_add;
-        const int j = s_cnt + block_excl_scan<int>(add ? 1 : 0, s_warp_i, &n_add);
+        int j = s_cnt + block_excl_scan<int>((add ? 1 : 0) + (add2 ? 1 : 0), s_warp_i, &n_add);
         long long cost_add;
-        const long long mine = add ? (bn.end - bn.begin) + kHistFlushCost : 0;
-        const long long before = s_cost + block_excl_scan<long long>(mine, s_warp_ll, &cost_add);
-        if (add) { bn.cost_end = before + mine; t.build[j] = bn; }
+        const long long c1 = add ? (bn.end - bn.begin) + kHistFlushCost : 0, c2 = add2 ? (bn2.end - bn2.begin) + kHistFlushCost : 0;
+        const long long before = s_cost + block_excl_scan<long long>(c1 + c2, s_warp_ll, &cost_add);
+        if (add) { bn.cost_end = before + c1; t.build[j++] = bn; }
+        if (add2) { bn2.cost_end = before + c1 + c2; t.build[j] = bn2; }
         __syncthreads();
         if (threadIdx.x == 0) { s_cnt += n_add; s_cost += cost_add; }
         __syncthreads();

@@ -43,11 +43,42 @@ struct LvTables {
     SubItem* subs;                  // [slots]
     ScanNode* scans;                // [2 * slots]
     long long** seg_out;            // [slots] where hist_span_k accumulates node `seg`
+    long long** seg_final;          // [slots] world > 1: the slot the reduced histogram of node `seg` goes to (null: none)
+    ytk_split* recs_local;          // [2 * slots] world > 1: this rank's records of the level's children, before the merge
+    long long* lh_local;            // [2 * slots][2]
     long long* pool;                // histogram slots, seg_max words each
     long long* staging;             // world > 1: [owner][slot][seg_max]
     long long seg_max;
     int world;
 };
+
+// ---- exchanges of the device-driven level loop over peer memory (peer.cu) ----------------------------
+// `phase`: kXAll = one kernel per exchange with flags between GPUs (one process per GPU); a clique of
+// handles on ONE device (tests: the ranks' kernels run one after the other on one stream) runs
+// kXPush for every rank, then kXReduce for every rank, and needs no flags.
+constexpr int kXPush = 1, kXWait = 2, kXReduce = 4, kXAll = 7;
+// largest |g|, |h| of all ranks (float bits): absmax[2] in place
+cudaError_t launch_lv_xmax(const PeerTable& pt, unsigned* absmax, size_t area_off, size_t slot_bytes, int flag_set,
+                           unsigned long long epoch, int phase, int* err, cudaStream_t st);
+// histogram reduce-scatter of the `m` slots of a level (m = 1, d = -1: the root) + the global child counts
+cudaError_t launch_lv_xhist(const PeerTable& pt, LvTables t, int d, int m, size_t area_off, size_t slot_bytes, int flag_set,
+                            unsigned long long epoch, int phase, int* err, cudaStream_t st);
+// split records of `n` searched nodes whose first heap node is `first_heap`: all-gather + needReplace / MAX merge
+cudaError_t launch_lv_xrecs(const PeerTable& pt, LvTables t, int n, long long first_heap, size_t area_off, size_t slot_bytes,
+                            size_t lh_off, size_t lh_slot_bytes, int flag_set, unsigned long long epoch, int phase, int* err,
+                            cudaStream_t st);
+// leaf sums of the 2m children of the last level (summed over ranks, in place) + the global child counts
+cudaError_t launch_lv_xleaf(const PeerTable& pt, LvTables t, int d, size_t area_off, size_t slot_bytes, size_t cnt_off,
+                            size_t cnt_slot_bytes, int flag_set, unsigned long long epoch, int phase, int* err, cudaStream_t st);
+
+// global child counts of split slot s of level d (d = -1: the root's own row count, in gc.left) into the nodes
+__device__ __forceinline__ void lv_apply_gcounts(const LvTables& t, int d, int s, PartitionCounts gc) {
+    if (d < 0) { t.nodes[0].sample_cnt = gc.left; return; }
+    const int p = (1 << d) - 1 + s;
+    t.nodes[p].gcnt_l = gc.left; t.nodes[p].gcnt_r = gc.right;
+    t.nodes[2 * p + 1].sample_cnt = gc.left;
+    t.nodes[2 * p + 2].sample_cnt = gc.right;
+}
 
 cudaError_t launch_lv_root(LvTables t, long long begin, long long end, int buf, const PartitionCounts* mask_counts, cudaStream_t st);
 // plans the partition of level d (slots = 2^d): which nodes split, their segments and tiles

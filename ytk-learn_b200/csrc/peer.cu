@@ -9,6 +9,7 @@
 // ====================================================================================
 #include "common.cuh"
 #include "device_util.cuh"
+#include "level.cuh"
 
 #include <math_constants.h>
 
@@ -137,6 +138,194 @@ __global__ void peer_pull_reduce_k(PeerTable pt, int m, long long seg_max, int f
         }
         *reinterpret_cast<longlong2*>(out + i) = s;
     }
+}
+
+// ====================================================================================
+// Exchanges of the device-driven level loop (engine.cu).  Same transport as above -- plain stores into the
+// peers' exchange areas, a release flag per (exchange kind, rank), acquire-polling of one's own flags --
+// but every kernel can also run its three steps separately (phase bits kXPush / kXWait / kXReduce): a
+// clique of handles on ONE device runs "push" for every rank and then "reduce" for every rank on one
+// stream, where kernels must not wait for one another (nothing guarantees they are co-scheduled).
+// ====================================================================================
+__device__ __forceinline__ void lv_push_words(const PeerTable& pt, const unsigned long long* __restrict__ src, size_t area_off,
+                                              size_t slot_bytes, size_t words) {
+    for (int r = 0; r < pt.world; r++) {
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(pt.xchg[r] + area_off + (size_t)pt.rank * slot_bytes);
+        for (size_t i = threadIdx.x; i < words; i += blockDim.x) dst[i] = src[i];
+    }
+}
+__device__ __forceinline__ void lv_raise(const PeerTable& pt, int flag_set, unsigned long long epoch) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < pt.world) {
+        unsigned long long* f = reinterpret_cast<unsigned long long*>(pt.xchg[threadIdx.x]) + flag_set * kMaxPeers + pt.rank;
+        st_release_sys(f, epoch);
+    }
+}
+
+__global__ void lv_xmax_k(PeerTable pt, unsigned* __restrict__ absmax, size_t area_off, size_t slot_bytes, int flag_set,
+                          unsigned long long epoch, int phase, int* err) {
+    __shared__ unsigned long long s_v;
+    if (phase & kXPush) {
+        if (threadIdx.x == 0) s_v = (unsigned long long)absmax[0] | ((unsigned long long)absmax[1] << 32);
+        __syncthreads();
+        lv_push_words(pt, &s_v, area_off, slot_bytes, 1);
+        if (phase & kXWait) lv_raise(pt, flag_set, epoch);
+    }
+    if ((phase & kXWait) && !peer_wait(pt, flag_set, epoch, err)) return;
+    if ((phase & kXReduce) && threadIdx.x == 0) {
+        // float bits of non-negative values order like unsigned integers
+        unsigned g = 0, h = 0;
+        for (int r = 0; r < pt.world; r++) {
+            const unsigned long long v = *reinterpret_cast<const unsigned long long*>(pt.xchg[pt.rank] + area_off + (size_t)r * slot_bytes);
+            g = max(g, (unsigned)v); h = max(h, (unsigned)(v >> 32));
+        }
+        absmax[0] = g; absmax[1] = h;
+    }
+}
+
+// grid (chunks, m).  Raises "my staging buffer is complete" (the histogram kernel ahead in the stream has
+// finished), waits for everybody's, and sums the segment this rank owns of every slot that is being built
+// straight out of all staging buffers into the slot's histogram.  Block (0,0) also exchanges the child
+// counts of the level's partition (d < 0: the root's row count).
+__global__ void lv_xhist_k(PeerTable pt, LvTables t, int d, int m, size_t area_off, size_t slot_bytes, int flag_set,
+                           unsigned long long epoch, int phase, int* err) {
+    const bool lead = blockIdx.x == 0 && blockIdx.y == 0;
+    if ((phase & kXPush) && lead) {
+        lv_push_words(pt, reinterpret_cast<const unsigned long long*>(t.counts), area_off, slot_bytes, 2 * (size_t)m);
+        if (phase & kXWait) lv_raise(pt, flag_set, epoch);
+    }
+    if ((phase & kXWait) && !peer_wait(pt, flag_set, epoch, err)) return;
+    if (!(phase & kXReduce)) return;
+    if (lead) {
+        const char* base = pt.xchg[pt.rank] + area_off;
+        for (int s = threadIdx.x; s < m; s += blockDim.x) {
+            PartitionCounts g = {0, 0};
+            bool unused = false;
+            for (int r = 0; r < pt.world; r++) {
+                const PartitionCounts c = reinterpret_cast<const PartitionCounts*>(base + (size_t)r * slot_bytes)[s];
+                if (c.left < 0) unused = true;          // the slot is not split (every rank says so)
+                g.left += c.left; g.right += c.right;
+            }
+            if (unused) continue;
+            t.gcounts[s] = g;
+            lv_apply_gcounts(t, d, s, g);
+        }
+    }
+    const int slot = blockIdx.y;
+    long long* __restrict__ out = t.seg_final[slot];
+    if (!out) return;
+    const size_t off = ((size_t)pt.rank * m + slot) * (size_t)t.seg_max;
+    for (long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 2; i < t.seg_max;
+         i += (long long)gridDim.x * blockDim.x * 2) {
+        longlong2 s2 = make_longlong2(0, 0);
+        for (int r = 0; r < pt.world; r++) {
+            const longlong2 v = *reinterpret_cast<const longlong2*>(reinterpret_cast<const long long*>(pt.hist[r]) + off + i);
+            s2.x += v.x; s2.y += v.y;
+        }
+        *reinterpret_cast<longlong2*>(out + i) = s2;
+    }
+}
+
+// One CTA.  Every rank's records (and left / total hessians) of the n searched nodes go to everybody; merged
+// as every rank's host would (ytk_gbdt_merge_splits: needReplace in rank order, element-wise MAX of the node
+// totals, DataParallelTreeMaker.java:560,640-653) into the heap arrays.
+__global__ void lv_xrecs_k(PeerTable pt, LvTables t, int n, long long first_heap, size_t area_off, size_t slot_bytes, size_t lh_off,
+                           size_t lh_slot_bytes, int flag_set, unsigned long long epoch, int phase, int* err) {
+    if (phase & kXPush) {
+        lv_push_words(pt, reinterpret_cast<const unsigned long long*>(t.recs_local), area_off, slot_bytes,
+                      (size_t)n * sizeof(ytk_split) / 8);
+        lv_push_words(pt, reinterpret_cast<const unsigned long long*>(t.lh_local), lh_off, lh_slot_bytes, 2 * (size_t)n);
+        if (phase & kXWait) lv_raise(pt, flag_set, epoch);
+    }
+    if ((phase & kXWait) && !peer_wait(pt, flag_set, epoch, err)) return;
+    if (!(phase & kXReduce)) return;
+    const char* base = pt.xchg[pt.rank] + area_off;
+    const char* lbase = pt.xchg[pt.rank] + lh_off;
+    for (int k = threadIdx.x; k < n; k += blockDim.x) {
+        if (!t.scans[k].hist) continue;                 // not searched (same on every rank)
+        ytk_split best = reinterpret_cast<const ytk_split*>(base)[k];
+        int best_r = 0;
+        double G = best.sum_grad, H = best.sum_hess;
+        for (int r = 1; r < pt.world; r++) {
+            const ytk_split t2 = reinterpret_cast<const ytk_split*>(base + (size_t)r * slot_bytes)[k];
+            const bool rep = (best.fid <= t2.fid) ? (t2.loss_chg > best.loss_chg) : (t2.loss_chg >= best.loss_chg);
+            if (rep) { best = t2; best_r = r; }
+            if (t2.sum_grad > G) G = t2.sum_grad;
+            if (t2.sum_hess > H) H = t2.sum_hess;
+        }
+        long long tot_h = 0;
+        for (int r = 0; r < pt.world; r++) {            // root_gain / node_value / total hessian: from the first rank that had the totals
+            const ytk_split t2 = reinterpret_cast<const ytk_split*>(base + (size_t)r * slot_bytes)[k];
+            if (t2.sum_grad == G && t2.sum_hess == H) {
+                best.root_gain = t2.root_gain; best.node_value = t2.node_value;
+                tot_h = reinterpret_cast<const long long*>(lbase + (size_t)r * lh_slot_bytes)[2 * k + 1];
+                break;
+            }
+        }
+        best.sum_grad = G; best.sum_hess = H;
+        t.recs[first_heap + k] = best;
+        t.left_h[2 * (first_heap + k)] = reinterpret_cast<const long long*>(lbase + (size_t)best_r * lh_slot_bytes)[2 * k];
+        t.left_h[2 * (first_heap + k) + 1] = tot_h;
+    }
+}
+
+// One CTA.  allreduceArray(double[2], SUM) of computeLeafStats (:375) for the 2m children of the last
+// level, exact in the integer domain, and the global child counts of the level's partition.
+__global__ void lv_xleaf_k(PeerTable pt, LvTables t, int d, size_t area_off, size_t slot_bytes, size_t cnt_off, size_t cnt_slot_bytes,
+                           int flag_set, unsigned long long epoch, int phase, int* err) {
+    const int m = 1 << d;
+    const long long C0 = 2ll * m - 1;
+    if (phase & kXPush) {
+        lv_push_words(pt, reinterpret_cast<const unsigned long long*>(t.leaf + 2 * C0), area_off, slot_bytes, 4 * (size_t)m);
+        lv_push_words(pt, reinterpret_cast<const unsigned long long*>(t.counts), cnt_off, cnt_slot_bytes, 2 * (size_t)m);
+        if (phase & kXWait) lv_raise(pt, flag_set, epoch);
+    }
+    if ((phase & kXWait) && !peer_wait(pt, flag_set, epoch, err)) return;
+    if (!(phase & kXReduce)) return;
+    const char* base = pt.xchg[pt.rank] + area_off;
+    for (int i = threadIdx.x; i < 4 * m; i += blockDim.x) {
+        long long sum = 0;
+        for (int r = 0; r < pt.world; r++) sum += reinterpret_cast<const long long*>(base + (size_t)r * slot_bytes)[i];
+        t.leaf[2 * C0 + i] = sum;
+    }
+    const char* cbase = pt.xchg[pt.rank] + cnt_off;
+    for (int s = threadIdx.x; s < m; s += blockDim.x) {
+        PartitionCounts g = {0, 0};
+        bool unused = false;
+        for (int r = 0; r < pt.world; r++) {
+            const PartitionCounts c = reinterpret_cast<const PartitionCounts*>(cbase + (size_t)r * cnt_slot_bytes)[s];
+            if (c.left < 0) unused = true;
+            g.left += c.left; g.right += c.right;
+        }
+        if (unused) continue;
+        t.gcounts[s] = g;
+        lv_apply_gcounts(t, d, s, g);
+    }
+}
+
+cudaError_t launch_lv_xmax(const PeerTable& pt, unsigned* absmax, size_t area_off, size_t slot_bytes, int flag_set,
+                           unsigned long long epoch, int phase, int* err, cudaStream_t st) {
+    lv_xmax_k<<<1, 64, 0, st>>>(pt, absmax, area_off, slot_bytes, flag_set, epoch, phase, err);
+    return cudaGetLastError();
+}
+cudaError_t launch_lv_xhist(const PeerTable& pt, LvTables t, int d, int m, size_t area_off, size_t slot_bytes, int flag_set,
+                            unsigned long long epoch, int phase, int* err, cudaStream_t st) {
+    dim3 grid((unsigned)std::max<long long>(1, std::min<long long>(16, (t.seg_max / 2 + 255) / 256)), (unsigned)m);
+    if (phase == kXPush) grid = dim3(1, 1);
+    lv_xhist_k<<<grid, 256, 0, st>>>(pt, t, d, m, area_off, slot_bytes, flag_set, epoch, phase, err);
+    return cudaGetLastError();
+}
+cudaError_t launch_lv_xrecs(const PeerTable& pt, LvTables t, int n, long long first_heap, size_t area_off, size_t slot_bytes,
+                            size_t lh_off, size_t lh_slot_bytes, int flag_set, unsigned long long epoch, int phase, int* err,
+                            cudaStream_t st) {
+    lv_xrecs_k<<<1, 256, 0, st>>>(pt, t, n, first_heap, area_off, slot_bytes, lh_off, lh_slot_bytes, flag_set, epoch, phase, err);
+    return cudaGetLastError();
+}
+cudaError_t launch_lv_xleaf(const PeerTable& pt, LvTables t, int d, size_t area_off, size_t slot_bytes, size_t cnt_off,
+                            size_t cnt_slot_bytes, int flag_set, unsigned long long epoch, int phase, int* err, cudaStream_t st) {
+    lv_xleaf_k<<<1, 256, 0, st>>>(pt, t, d, area_off, slot_bytes, cnt_off, cnt_slot_bytes, flag_set, epoch, phase, err);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_peer_allreduce(const PeerTable& pt, const void* src, size_t area_off, size_t slot_bytes, size_t words,

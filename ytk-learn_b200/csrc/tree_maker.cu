@@ -119,7 +119,8 @@ void free_all(ytk_gbdt* h) {
     for (auto e : h->ev) cudaEventDestroy(e);
     for (auto e : h->evc) cudaEventDestroy(e);
     if (h->comm) ytk::nccl_api().CommDestroy(h->comm);
-    if (h->st) cudaStreamDestroy(h->st);
+    if (h->st && (!h->clique || h->rank == 0)) cudaStreamDestroy(h->st);      // a clique shares rank 0's stream
+    if (h->clique && h->rank == 0) delete[] h->clique_members;
 }
 
 ytk::SparseRows sparse_rows(const ytk_gbdt* h) {
@@ -176,7 +177,7 @@ int quantize_grads(ytk_gbdt* h, int gid) {
     CK(ytk::launch_grad_absmax(h->d_gp, h->N, h->p.class_num, gid, h->d_absmax, h->st));
     // The scales are powers of two chosen from max|g| and max|h|: of ALL rows, or the integer sums of
     // different ranks would be in different units (float bits of non-negative values order like integers)
-    if (h->world > 1)
+    if (h->world > 1 && h->comm)
         NK(ytk::nccl_api().AllReduce(h->d_absmax, h->d_absmax, 2, ncclUint32, ncclMax, h->comm, h->st));
     CK(ytk::launch_grad_quantize(h->d_gp, h->N, h->p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->fixed_bits, h->st));
     h->launches += 2;
@@ -231,23 +232,47 @@ void add_deferred_items(std::vector<ytk::RowItem>& items, const Interval& parent
 // Maps every rank's exchange and histogram staging buffers into this process (CUDA IPC) so that the
 // per-level collectives can run as plain kernels over NVLink.  All ranks must be processes on one node;
 // if any rank cannot set this up, all of them stay on NCCL (the decision itself is an NCCL allreduce).
-int peer_setup(ytk_gbdt* h) {
-    h->peer_mode = false;
-    if (h->world < 2 || h->world > 16) return YTK_OK;
-    if (const char* e = getenv("YTK_GBDT_NO_PEER")) if (atoi(e) != 0) return YTK_OK;
-    if (const char* e = getenv("YTK_GBDT_PEER_TIMEOUT_MS")) h->peer_timeout_ms = std::max(1.0, atof(e));
+size_t peer_layout(ytk_gbdt* h, size_t* hist_words) {
     const int cap = 4096;
     h->peer_cap_nodes = cap;
     h->slot_counts = (size_t)cap * sizeof(ytk::PartitionCounts);
     h->slot_recs = (size_t)2 * cap * sizeof(ytk_split);
     h->slot_leaf = (size_t)2 * cap * sizeof(long long);
+    h->slot_lh = (size_t)2 * cap * 2 * sizeof(long long);
+    h->slot_max = 64;
     h->off_counts = ytk::kPeerFlagBytes;
     h->off_recs = h->off_counts + h->slot_counts * h->world;
     h->off_leaf = h->off_recs + h->slot_recs * h->world;
-    const size_t xchg_bytes = h->off_leaf + h->slot_leaf * h->world;
+    h->off_lh = h->off_leaf + h->slot_leaf * h->world;
+    h->off_max = h->off_lh + h->slot_lh * h->world;
     const size_t local_len = (size_t)h->seg_max * h->world;
-    size_t hist_words = std::max<size_t>(local_len * 256, (size_t(128) << 20) / 8);      // >= 256 nodes, >= 128 MB
-    hist_words = std::min<size_t>(hist_words, std::max<size_t>(local_len * 2, (size_t(1) << 30) / 8));
+    size_t words = std::max<size_t>(local_len * 256, (size_t(128) << 20) / 8);      // >= 256 nodes, >= 128 MB
+    words = std::min<size_t>(words, std::max<size_t>(local_len * 2, (size_t(1) << 30) / 8));
+    *hist_words = words;
+    return h->off_max + h->slot_max * h->world;
+}
+
+// A clique member's own buffers; the members are linked (PeerTable) at the first ytk_gbdt_make_tree_clique.
+static int clique_buffers(ytk_gbdt* h) {
+    size_t hist_words = 0;
+    const size_t xchg_bytes = peer_layout(h, &hist_words);
+    CK(cudaMalloc(&h->my_xchg, xchg_bytes));
+    CK(cudaMemsetAsync(h->my_xchg, 0, xchg_bytes, h->st));
+    CK(cudaMalloc(&h->my_hist, hist_words * 8));
+    CK(cudaHostAlloc((void**)&h->d_peer_err, sizeof(int), cudaHostAllocMapped));
+    *h->d_peer_err = 0;
+    h->hist_cap_words = hist_words;
+    h->pt.rank = h->rank; h->pt.world = h->world; h->pt.timeout_cycles = 0;
+    return YTK_OK;
+}
+
+int peer_setup(ytk_gbdt* h) {
+    h->peer_mode = false;
+    if (h->world < 2 || h->world > 16) return YTK_OK;
+    if (const char* e = getenv("YTK_GBDT_NO_PEER")) if (atoi(e) != 0) return YTK_OK;
+    if (const char* e = getenv("YTK_GBDT_PEER_TIMEOUT_MS")) h->peer_timeout_ms = std::max(1.0, atof(e));
+    size_t hist_words = 0;
+    const size_t xchg_bytes = peer_layout(h, &hist_words);
     // Every rank goes through BOTH agreements below whatever fails locally: a rank that returned early
     // would leave the others hanging in the collective.  Local failures only clear `ok`.
     int ok = 1;
@@ -774,6 +799,28 @@ int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank,
     return YTK_OK;
 }
 
+int ytk_gbdt_create_clique(const ytk_gbdt_params* params, int32_t device, int32_t world, ytk_gbdt** out) {
+    if (!params || !out) return fail(YTK_ERR_ARG, "create_clique: null argument");
+    if (world < 2 || world > 16) return fail(YTK_ERR_ARG, "create_clique: world %d not in [2,16]", world);
+    ytk_gbdt** members = new ytk_gbdt*[world];
+    for (int r = 0; r < world; r++) members[r] = nullptr;
+    for (int r = 0; r < world; r++) {
+        ytk_gbdt* h = nullptr;
+        int rc = ytk_gbdt_create(params, device, 0, 1, nullptr, &h);      // (as a world of one: no NCCL)
+        if (rc != YTK_OK) {
+            for (int q = 0; q < r; q++) { members[q]->clique = false; ytk_gbdt_destroy(members[q]); }
+            delete[] members;
+            return rc;
+        }
+        h->rank = r; h->world = world; h->clique = true;
+        if (r > 0) { cudaStreamDestroy(h->st); h->st = members[0]->st; }
+        h->clique_members = members;
+        members[r] = h;
+    }
+    for (int r = 0; r < world; r++) out[r] = members[r];
+    return YTK_OK;
+}
+
 int ytk_gbdt_destroy(ytk_gbdt* h) {
     if (!h) return YTK_OK;
     free_all(h);
@@ -922,7 +969,8 @@ static int set_bins_impl(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n
             h->pool.avail.push_back(it);
         }
     }
-    if (h->world > 1) RET(peer_setup(h));
+    if (h->clique) RET(clique_buffers(h));
+    else if (h->world > 1) RET(peer_setup(h));
     h->rows_set = true;
     return YTK_OK;
 }

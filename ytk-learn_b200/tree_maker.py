@@ -57,6 +57,50 @@ class GpuTreeMaker:
             d = np.ascontiguousarray(sparse_default, dtype=np.int32)
             B.check(B.lib().ytk_gbdt_set_bins_sparse(self._h, B.ptr(self.start), self.F, self.N, B.ptr(d), int(nnz)))
 
+    @classmethod
+    def clique(cls, params, start, n_rows_per_rank, device=0):
+        """`len(n_rows_per_rank)` tree makers on ONE device that behave as the ranks of a multi-GPU run
+        (ytk_gbdt_create_clique); build their trees together with `make_clique`."""
+        world = len(n_rows_per_rank)
+        hs = (C.c_void_p * world)()
+        B.check(B.lib().ytk_gbdt_create_clique(C.addressof(params), int(device), world, C.addressof(hs)))
+        members = []
+        for r in range(world):
+            m = cls.__new__(cls)
+            m._h = C.c_void_p(hs[r])
+            m.params = params
+            m.start = np.ascontiguousarray(start, dtype=np.int32)
+            m.F = len(m.start) - 1
+            m.B = int(m.start[-1])
+            m.N = int(n_rows_per_rank[r])
+            m.K = params.class_num
+            m.last_stats = None
+            m._nccl_id = None
+            B.check(B.lib().ytk_gbdt_set_bins(m._h, B.ptr(m.start), m.F, m.N))
+            members.append(m)
+        return members
+
+    @staticmethod
+    def make_clique(members, group_id=0, fea_index=None, row_masks=None):
+        """ITreeMaker.make of every rank of a clique at once; returns the ranks' trees."""
+        world = len(members)
+        p = members[0].params
+        cap = 2 * p.max_leaf_cnt - 1 if p.max_leaf_cnt > 0 else 2 ** (p.max_depth + 1) - 1
+        trees = [B.Tree(cap) for _ in range(world)]
+        outs = (B.TreeOut * world)(*[t._as_c() for t in trees])
+        ts = (B.TimeStats * world)()
+        hs = (C.c_void_p * world)(*[m._h for m in members])
+        fi = None if fea_index is None else np.ascontiguousarray(fea_index, dtype=np.int32)
+        masks, mp = None, None
+        if row_masks is not None:
+            masks = [None if m is None else np.ascontiguousarray(m, dtype=np.uint8) for m in row_masks]
+            mp = (C.c_void_p * world)(*[None if m is None else m.ctypes.data for m in masks])
+        B.check(B.lib().ytk_gbdt_make_tree_clique(C.addressof(hs), world, int(group_id), B.ptr(fi), 0 if fi is None else len(fi),
+                                                  None if mp is None else C.addressof(mp), C.addressof(outs), C.addressof(ts)))
+        for r, m in enumerate(members):
+            m.last_stats = B.TimeStats.from_buffer_copy(ts[r])
+        return [t._trim(outs[r].n_nodes) for r, t in enumerate(trees)]
+
     def close(self):
         if self._h:
             B.lib().ytk_gbdt_destroy(self._h)
