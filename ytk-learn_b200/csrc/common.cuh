@@ -103,8 +103,10 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
                               const PartitionCounts* cnt_local, const PartitionCounts* cnt_global, cudaStream_t st);
 // Level planned on the device (level.cu): the build nodes of a level with a running cost prefix
 // (cost of a node = its rows + kHistFlushCost), walked by hist_span_k in spans of equal cost.
-constexpr long long kHistFlushCost = 512;       // a flush of the shared histogram, in rows' worth of time
-struct BuildNode { long long begin, end; long long cost_end; int buf; int seg; };
+// cost of a node = its rows + flush_cost: what a node boundary inside a span costs (flush + re-zero of the shared
+// histogram, the dependent loads that start the next node's rows, two barriers), in rows' worth of time
+constexpr long long kHistFlushCost = 6144;     // measured on the Higgs shape: 512 -> 1.09 ms of histogram time per tree, 1536 -> 1.05, 3000 -> 1.01, 6000 and 12000 -> 0.97
+struct BuildNode { long long begin, end; long long cost_end; long long cost; int buf; int seg; };
 cudaError_t launch_hist_span(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1,
                              const BuildNode* nodes, const int* n_nodes_dev, int groups, int32_t F, const uint32_t* group_mask,
                              const int32_t* nbins, const int32_t* feat_owner, const int64_t* feat_inner, long long owner_stride,
@@ -132,6 +134,7 @@ cudaError_t launch_csr_pack(const int64_t* row_ptr, const int32_t* fids, const i
 cudaError_t launch_csr_to_dense(SparseRows sparse, int64_t row0, int64_t nrows, int32_t F, int32_t* out, cudaStream_t st);
 // per-device opt-ins of the histogram kernels (call with the device current, once per handle)
 cudaError_t hist_kernels_init();
+cudaError_t partition_kernels_init();
 // rows one hist work item should cover so that `total_rows` split into about two waves of CTAs
 int64_t hist_rows_per_item(int64_t total_rows, int groups);
 

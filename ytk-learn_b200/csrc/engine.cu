@@ -175,6 +175,8 @@ public:
         t.staging = h->world > 1 ? reinterpret_cast<long long*>(h->my_hist) : nullptr;
         t.seg_max = h->seg_max;
         t.world = h->world;
+        static const long long flush_cost = [] { const char* e = getenv("YTK_GBDT_FLUSH_COST"); return e ? std::max(0, atoi(e)) : (int)ytk::kHistFlushCost; }();
+        t.flush_cost = flush_cost;
         RET(set_features(h, fea_index, n_fea, &first_owned, &n_sel));
         h->pool.clear();
         h->ev_stage_used = 0;

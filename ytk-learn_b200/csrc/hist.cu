@@ -302,7 +302,7 @@ hist_span_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict
     for (int j = lo; j < nb; j++) {
         const BuildNode nd = nodes[j];
         const long long n = nd.end - nd.begin;
-        const long long cost_begin = nd.cost_end - n - kHistFlushCost;
+        const long long cost_begin = nd.cost_end - n - nd.cost;
         if (cost_begin >= c1) break;
         long long o0 = c0 - cost_begin, o1 = c1 - cost_begin;       // my share of the node, in rows from its begin
         o0 = o0 < 0 ? 0 : o0;

@@ -39,7 +39,7 @@ __global__ void lv_root_k(LvTables t, long long begin, long long end, int buf, c
     LvNode nd = {begin, end, 0, 0, 0, 0, end - begin, kLvActive, 0};
     t.nodes[0] = nd;
     const long long n = end - begin;
-    t.build[0] = {begin, end, n + kHistFlushCost, buf, 0};
+    t.build[0] = {begin, end, n + t.flush_cost, t.flush_cost, buf, 0};
     *t.n_build = n > 0 ? 1 : 0;
     t.seg_out[0] = t.world == 1 ? t.pool : t.staging;
     if (t.world > 1) {
@@ -117,7 +117,7 @@ lv_plan_build_k(LvTables t, int d, int child_buf, int leaf) {
     for (int s0 = 0; s0 < m; s0 += kPlanThreads) {
         const int s = s0 + threadIdx.x;
         bool add = false, add2 = false;      // add2: several GPUs, last level: the larger child's sums are taken too
-        BuildNode bn = {0, 0, 0, 0, 0}, bn2 = bn;
+        BuildNode bn = {0, 0, 0, 0, 0, 0}, bn2 = bn;
         if (s < m) {
             const int p = L0 + s;
             LvNode nd = t.nodes[p];
@@ -173,7 +173,8 @@ lv_plan_build_k(LvTables t, int d, int child_buf, int leaf) {
         int n_add;
         int j = s_cnt + block_excl_scan<int>((add ? 1 : 0) + (add2 ? 1 : 0), s_warp_i, &n_add);
         long long cost_add;
-        const long long c1 = add ? (bn.end - bn.begin) + kHistFlushCost : 0, c2 = add2 ? (bn2.end - bn2.begin) + kHistFlushCost : 0;
+        const long long c1 = add ? (bn.end - bn.begin) + t.flush_cost : 0, c2 = add2 ? (bn2.end - bn2.begin) + t.flush_cost : 0;
+        bn.cost = bn2.cost = t.flush_cost;
         const long long before = s_cost + block_excl_scan<long long>(c1 + c2, s_warp_ll, &cost_add);
         if (add) { bn.cost_end = before + c1; t.build[j++] = bn; }
         if (add2) { bn2.cost_end = before + c1 + c2; t.build[j] = bn2; }
@@ -206,7 +207,7 @@ lv_leaf_sums_k(LvTables t, int d, const int2* __restrict__ gq, const int32_t* __
     for (int j = lo; j < nb; j++) {
         const BuildNode nd = t.build[j];
         const long long n = nd.end - nd.begin;
-        const long long cost_begin = nd.cost_end - n - kHistFlushCost;
+        const long long cost_begin = nd.cost_end - n - nd.cost;
         if (cost_begin >= c1) break;
         long long o0 = c0 - cost_begin, o1 = c1 - cost_begin;
         o0 = o0 < 0 ? 0 : o0;

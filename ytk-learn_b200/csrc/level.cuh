@@ -49,6 +49,7 @@ struct LvTables {
     long long* pool;                // histogram slots, seg_max words each
     long long* staging;             // world > 1: [owner][slot][seg_max]
     long long seg_max;
+    long long flush_cost;           // cost of a node boundary in a span, in rows (kHistFlushCost; YTK_GBDT_FLUSH_COST)
     int world;
 };
 

@@ -13,6 +13,9 @@
 #include <algorithm>
 #include <cstdlib>
 
+#ifndef YTK_PART_MIN_BLOCKS
+#define YTK_PART_MIN_BLOCKS 3
+#endif
 namespace ytk {
 
 // ------------------------------------------------------------------------------------
@@ -231,7 +234,7 @@ __device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned 
     asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(kFusedThreads)
+__global__ void __launch_bounds__(kFusedThreads, YTK_PART_MIN_BLOCKS)
 partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, WideCols wide, SparseRows sparse,
                   int32_t* __restrict__ rowidx0,
                   int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs, int n_segs,
@@ -526,6 +529,15 @@ cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col
     return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
                         rowidx0, rowidx1, (const SplitSeg*)out_segs, 2 * m, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
                         tile_state, ticket, epoch, next_counts);
+}
+
+// The shared-memory carve-out of the partition is left to the driver unless YTK_GBDT_PART_CARVEOUT (percent) says
+// otherwise: its one-byte gathers live on L1 hits (a sector is asked for 16 times), and a maximal carve-out,
+// which would allow more CTAs per SM, takes that cache away (measured: 0.64 -> 1.0 ms per tree).
+cudaError_t partition_kernels_init() {
+    if (const char* e = getenv("YTK_GBDT_PART_CARVEOUT"))
+        return cudaFuncSetAttribute(partition_fused_k, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
+    return cudaSuccess;
 }
 
 cudaError_t launch_partition_fused_planned(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,

@@ -846,6 +846,7 @@ static int set_bins_impl(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n
     if (n_rows > 0x7fffffffLL) return fail(YTK_ERR_ARG, "set_bins: %lld rows exceed int32 row ids", (long long)n_rows);
     CK(cudaSetDevice(h->device));
     CK(ytk::hist_kernels_init());
+    CK(ytk::partition_kernels_init());
     h->F = F; h->N = n_rows;
     h->start.assign(start, start + F + 1);
     h->nbins.resize(F);
