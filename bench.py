@@ -49,6 +49,10 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-loss-wise", action="store_true", help="skip the extra loss-wise 255-leaf measurement")
     ap.add_argument("--no-parity-check", action="store_true", help="skip the self-check after the timed region")
+    ap.add_argument("--no-other-configs", action="store_true", help="skip BASELINE configs[2..4] (other_configs)")
+    ap.add_argument("--c3-rows", type=int, default=12_500_000, help="rows per GPU of configs[2]")
+    ap.add_argument("--c5-rows", type=int, default=20_000_000, help="rows per GPU of configs[4]")
+    ap.add_argument("--c4-rows", type=int, default=6_250_000, help="rows per GPU of configs[3]")
     ap.add_argument("--uniform-bins", action="store_true", help="experiment: every feature uniform over its bins")
     return ap.parse_args()
 
@@ -258,6 +262,152 @@ def parity_check(a, yb, torch, dist, world, rank, local, fresh_nccl_id, last_tre
     return res
 
 
+def _gen_c3(torch, n, F, nb, seed):
+    """configs[2] shape on the device: uniform slots, y = sum_j a_j slot_j + N(0,1), l2 gradients at score 0."""
+    g = torch.Generator(device="cuda"); g.manual_seed(seed)
+    x = torch.randint(0, nb, (n, F), dtype=torch.uint8, device="cuda", generator=g)
+    a = torch.randn(F, device="cuda", generator=g) * (torch.rand(F, device="cuda", generator=g) < 0.25) / nb
+    y = torch.zeros(n, device="cuda")
+    for f in torch.nonzero(a).flatten().tolist():
+        y += x[:, f].float() * a[f]
+    y += torch.randn(n, device="cuda", generator=g)
+    gp = torch.stack([-y, torch.ones_like(y)], 1).reshape(-1)
+    return x.cpu().numpy(), gp.cpu().numpy()
+
+
+def _gen_c5(torch, n, F, nb, K, seed):
+    """configs[4] shape on the device: uniform slots, K classes, softmax gradients at score 0."""
+    g = torch.Generator(device="cuda"); g.manual_seed(seed)
+    x = torch.randint(0, nb, (n, F), dtype=torch.uint8, device="cuda", generator=g)
+    w = torch.randn(8, K, device="cuda", generator=g) * 3
+    z = (x[:, :8].float() / nb - 0.5) @ w
+    z += -torch.log(-torch.log(torch.rand(n, K, device="cuda", generator=g).clamp_min(1e-9)))
+    label = z.argmax(1)
+    p = 1.0 / K
+    gp = torch.empty(n, K, 2, device="cuda")
+    gp[:, :, 0] = p
+    gp[torch.arange(n, device="cuda"), label, 0] = p - 1.0
+    gp[:, :, 1] = 2.0 * p * (1.0 - p)
+    return x.cpu().numpy(), gp.reshape(-1).cpu().numpy()
+
+
+def _gen_c4(torch, n, F, density, seed):
+    """configs[3] shape on the device: k = F*density stored entries per row, one per stratum of F/k features,
+    slots 1..b_f-1 with b_f in [2,255], default slot 0; sigmoid gradients at score 0 from labels that
+    depend on a few features."""
+    g = torch.Generator(device="cuda"); g.manual_seed(seed)
+    k = max(1, int(round(F * density)))
+    width = F // k
+    nbs = torch.randint(2, 256, (F,), device="cuda", generator=g)
+    fids = torch.arange(k, device="cuda")[None, :] * width + torch.randint(0, width, (n, k), device="cuda", generator=g)
+    nbf = nbs[fids]
+    slots = 1 + (torch.rand(n, k, device="cuda", generator=g) * (nbf - 1)).long().clamp_max(253)
+    slots = torch.minimum(slots, nbf - 1)
+    w = torch.randn(F, device="cuda", generator=g) * (torch.rand(F, device="cuda", generator=g) < 0.05)
+    z = (w[fids] * (slots.float() / nbf.float())).sum(1)
+    y = (torch.rand(n, device="cuda", generator=g) < torch.sigmoid(3 * z)).float()
+    gp = torch.stack([0.5 - y, torch.full_like(y, 0.25)], 1).reshape(-1)
+    start = np.concatenate([[0], np.cumsum(nbs.cpu().numpy())]).astype(np.int32)
+    row_ptr = np.arange(n + 1, dtype=np.int64) * k
+    return start, row_ptr, fids.reshape(-1).int().cpu().numpy(), slots.reshape(-1).int().cpu().numpy(), gp.cpu().numpy()
+
+
+def other_configs(a, yb, torch, dist, world, rank, local, fresh_nccl_id, barrier, peak):
+    """BASELINE.json configs[2..4] on this run's GPUs (north_star: "throughput on synthetic data of the named
+    shapes at 1, 2, 4 and 8 GPUs"): per-GPU shard of each shape generated on the device, a few trees timed
+    like the headline workload (gradients resident in HBM, max over ranks), each with the roofline of its
+    own dominant kernel.  Parity for these shapes: tests/test_gpu_fullsize.py (2 M / 1 M / 1 M rows)."""
+    out = {}
+
+    def timed(tm, gids, warm, steps):
+        cells = rows = rows_idx = built = hist_ms = t_sum = 0.0
+        nodes = 0
+        for i in range(warm + steps):
+            barrier()
+            t0 = time.perf_counter()
+            tree = tm.make(gids[i % len(gids)])
+            dt = time.perf_counter() - t0
+            if i >= warm:
+                ts = tm.last_stats
+                t_sum += dt; cells += ts.hist_cells; rows += ts.hist_rows; rows_idx += ts.hist_rows_indexed
+                built += ts.hist_built; hist_ms += ts.gpu_hist_ms; nodes = int(tree.n_nodes)
+        barrier()
+        v = torch.tensor([t_sum], dtype=torch.float64, device="cuda")
+        c = torch.tensor([cells], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(v, op=dist.ReduceOp.MAX)
+            dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        return dict(t=float(v.item()), cells_all=float(c.item()), cells=cells, rows=rows, rows_idx=rows_idx, built=built,
+                    hist_ms=hist_ms, nodes=nodes, steps=steps)
+
+    def entry(name, what, r, alg_bytes, kernel, extra=None):
+        ach = alg_bytes / (r["hist_ms"] * 1e-3) / 1e9 if r["hist_ms"] > 0 else 0.0
+        e = {"workload": what, "ms_per_tree": r["t"] / r["steps"] * 1e3, "value": r["cells_all"] / r["t"], "unit": UNIT,
+             "nodes_per_tree": r["nodes"], "trees_timed": r["steps"],
+             "roofline": {"bound": "hbm", "kernel": kernel, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                          "kernel_ms_per_tree": r["hist_ms"] / r["steps"], "algorithmic_bytes_per_tree": alg_bytes / r["steps"]}}
+        if extra:
+            e.update(extra)
+        out[name] = e
+
+    base = dict(min_child_hessian_sum=100.0, min_split_loss=0.0, l1=0.0, l2=0.0, learning_rate=0.1, min_split_samples=-1)
+    sampler = ClockSampler(local)
+    sampler.mark()
+    # ---- configs[2]: 100 M x 128 regression over 8 GPUs = 12.5 M rows per GPU, 255 bins, loss-wise 255 leaves
+    n, F, nb = a.c3_rows, 128, 255
+    x, gp = _gen_c3(torch, n, F, nb, 42 + rank)
+    start = (np.arange(F + 1) * nb).astype(np.int32)
+    tm = yb.GpuTreeMaker(yb.make_params(max_depth=-1, max_leaf_cnt=255, grow_policy="loss", **base), start, n, device=local,
+                         rank=rank, world=world, nccl_id=fresh_nccl_id())
+    for r0 in range(0, n, 1 << 20):
+        tm.upload_rows_u8(x[r0:r0 + (1 << 20)], r0)
+    tm.set_grads(gp)
+    del x
+    r = timed(tm, [0], 1, 3)
+    tm.close()
+    B = int(start[-1])
+    entry("c3", "synthetic regression: %d rows/GPU x 128 features, 255 bins, loss-wise 255 leaves (l2 loss)" % n, r,
+          r["cells"] + 8 * r["rows"] + 4 * r["rows_idx"] + 16.0 * B * r["built"], "hist_build_k")
+    # ---- configs[4]: 20 M x 256, 63 bins, 10 classes, depth 10: class-trees of one boosting round
+    n, F, nb, K = a.c5_rows, 256, 63, 10
+    x, gp = _gen_c5(torch, n, F, nb, K, 99 + rank)
+    start = (np.arange(F + 1) * nb).astype(np.int32)
+    tm = yb.GpuTreeMaker(yb.make_params(max_depth=10, max_leaf_cnt=-1, grow_policy="level", class_num=K, **base), start, n,
+                         device=local, rank=rank, world=world, nccl_id=fresh_nccl_id())
+    for r0 in range(0, n, 1 << 19):
+        tm.upload_rows_u8(x[r0:r0 + (1 << 19)], r0)
+    tm.set_grads(gp)
+    del x, gp
+    r = timed(tm, [0, 1, 2, 3], 1, 3)
+    tm.close()
+    B = int(start[-1])
+    entry("c5", "synthetic multiclass: %d rows/GPU x 256 features, 63 bins, 10 classes, level-wise depth 10 "
+                "(one tree per class and round; class-trees timed)" % n, r,
+          r["cells"] + 8 * r["rows"] + 4 * r["rows_idx"] + 16.0 * B * r["built"], "hist_span_k",
+          {"ms_per_round_of_10_class_trees": r["t"] / r["steps"] * 1e3 * K})
+    # ---- configs[3]: 50 M x 10 k sparse at 1 % over 8 GPUs = 6.25 M rows per GPU, level-wise depth 6, CSR rows
+    n, F = a.c4_rows, 10_000
+    start, row_ptr, fids, slots, gp = _gen_c4(torch, n, F, 0.01, 7 + rank)
+    nnz = len(fids)
+    tm = yb.GpuTreeMaker(yb.make_params(max_depth=6, max_leaf_cnt=-1, grow_policy="level", **base), start, n, device=local,
+                         rank=rank, world=world, nccl_id=fresh_nccl_id(), sparse_default=np.zeros(F, np.int32), nnz=nnz)
+    step = 1 << 18
+    for r0 in range(0, n, step):
+        r1 = min(n, r0 + step)
+        tm.upload_csr(row_ptr[r0:r1 + 1], fids, slots, row0=r0)
+    tm.set_grads(gp)
+    del fids, slots
+    r = timed(tm, [0], 1, 2)
+    tm.close()
+    per_row = nnz / max(1, n)
+    entry("c4", "synthetic sparse: %d rows/GPU x 10000 features at 1%% (CSR, %d stored entries), up to 255 bins, "
+                "level-wise depth 6" % (n, nnz), r, r["rows"] * (per_row * 3 + 20), "hist_csr_k",
+          {"bins_total": int(start[-1]), "histogram_mb_per_node": 16.0 * int(start[-1]) / 1e6,
+           "value_note": "rows x features counts all 10000 features of a row, stored or not (the dense path's work)"})
+    out["clocks"] = sampler.stop()
+    return out
+
+
 def config(a, world):
     return {"workload": "higgs-shape synthetic: %d rows/GPU x %d features, %d bins, %s-wise depth %d%s"
                         % (a.rows, a.features, a.bins, a.policy, a.depth,
@@ -420,6 +570,11 @@ def main():
         tm.close()
         pc = parity_check(a, yb, torch, dist, world, rank, local, fresh_nccl_id, last_tree)
 
+    oc = None
+    if not a.no_other_configs:
+        tm.close()
+        oc = other_configs(a, yb, torch, dist, world, rank, local, fresh_nccl_id, barrier, measured_peak()[0])
+
     vals = torch.tensor([agg["t_tree"], agg["t_e2e"], dev_round], dtype=torch.float64, device="cuda")
     sums = torch.tensor([agg["cells"]], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -466,6 +621,7 @@ def main():
                          "nodes_built_per_step": agg["built"] / a.steps},
             "clocks": clocks,
             "parity_check": pc,
+            "other_configs": oc,
         }
         if not a.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(a, xs, ys, steps=1)

@@ -169,6 +169,10 @@ int ytk_gbdt_quantize_csr(ytk_gbdt *h, const int64_t *row_ptr, const int32_t *fi
  * features with more than 256 bins). */
 int ytk_gbdt_upload_rows(ytk_gbdt *h, const int32_t *x_chunk, int64_t row0, int64_t nrows,
                          int32_t stride);
+/* The same rows as one byte per slot ("direct u8 upload"): for a trainer that keeps
+ * GBDTCoreData.x narrower than int32 once FeatureApprData has binned it (every feature at most 256
+ * bins) -- a quarter of the bytes over PCIe.  Same checks, same result as ytk_gbdt_upload_rows. */
+int ytk_gbdt_upload_rows_u8(ytk_gbdt *h, const uint8_t *x_chunk, int64_t row0, int64_t nrows, int32_t stride);
 
 /* Same rows, but still holding Float.floatToRawIntBits(value)
  * (GBDTCoreData.java:381): applies FeatureApprData.convertFeaVal2ApprFeaIndex

@@ -101,6 +101,7 @@ _SIGS = {
                                             C.c_void_p]),
     "ytk_gbdt_set_bins": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64]),
     "ytk_gbdt_upload_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32]),
+    "ytk_gbdt_upload_rows_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32]),
     "ytk_gbdt_quantize_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p]),
     "ytk_gbdt_download_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]),
     "ytk_gbdt_set_grads": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]),

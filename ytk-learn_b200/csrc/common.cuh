@@ -81,6 +81,9 @@ struct TreeNodeDev { int left, right, fid; float info; };             // device 
 cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, int32_t F, const int32_t* nbins,
                                uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, WideCols wide,
                                int64_t row_base, int* bad_flag, cudaStream_t st);
+cudaError_t launch_repack_rows_u8(const uint8_t* x, int64_t nrows, int32_t stride, int32_t F, const int32_t* nbins,
+                                  uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, WideCols wide,
+                                  int64_t row_base, int* bad_flag, cudaStream_t st);
 cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t stride, int32_t F,
                                  const float* cuts, const int32_t* start, uint8_t* bins, int32_t S8,
                                  uint8_t* col, int64_t col_stride, WideCols wide, int64_t row_base, cudaStream_t st);

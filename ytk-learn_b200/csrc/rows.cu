@@ -19,7 +19,8 @@ namespace ytk {
 //     -> uint8 row-major, rows padded to a multiple of 32 features (one 32 B sector per
 //     feature group and row).
 // ------------------------------------------------------------------------------------
-__global__ void repack_rows_k(const int32_t* __restrict__ x, int64_t nrows, int32_t stride, int32_t F,
+template <typename TIn>
+__global__ void repack_rows_k(const TIn* __restrict__ x, int64_t nrows, int32_t stride, int32_t F,
                               const int32_t* __restrict__ nbins, uint8_t* __restrict__ bins, int32_t S8,
                               uint8_t* __restrict__ col, int64_t col_stride, WideCols wide, int64_t row_base,
                               int* bad_flag) {
@@ -33,7 +34,7 @@ __global__ void repack_rows_k(const int32_t* __restrict__ x, int64_t nrows, int3
         // the same shared-memory word
         uint8_t b = (uint8_t)((r + row_base) * 37 + f * 11);
         if (f < F) {
-            int32_t v = x[r * stride + f];
+            int32_t v = (int32_t)x[r * stride + f];
             if (v < 0 || v >= nbins[f]) { *bad_flag = 1; v = 0; }
             const int wi = wide.index ? wide.index[f] : -1;
             if (wi >= 0) {
@@ -141,8 +142,16 @@ cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, 
                                uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, WideCols wide,
                                int64_t row_base, int* bad_flag, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    repack_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, nbins, bins, S8, col, col_stride, wide,
-                                                             row_base, bad_flag);
+    repack_rows_k<int32_t><<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, nbins, bins, S8, col, col_stride, wide,
+                                                                      row_base, bad_flag);
+    return cudaGetLastError();
+}
+cudaError_t launch_repack_rows_u8(const uint8_t* x, int64_t nrows, int32_t stride, int32_t F, const int32_t* nbins,
+                                  uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, WideCols wide,
+                                  int64_t row_base, int* bad_flag, cudaStream_t st) {
+    if (nrows <= 0) return cudaSuccess;
+    repack_rows_k<uint8_t><<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, nbins, bins, S8, col, col_stride, wide,
+                                                                      row_base, bad_flag);
     return cudaGetLastError();
 }
 cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t stride, int32_t F,

@@ -1011,6 +1011,33 @@ int ytk_gbdt_upload_rows(ytk_gbdt* h, const int32_t* x_chunk, int64_t row0, int6
     return YTK_OK;
 }
 
+int ytk_gbdt_upload_rows_u8(ytk_gbdt* h, const uint8_t* x_chunk, int64_t row0, int64_t nrows, int32_t stride) {
+    RET(check_rows(h, x_chunk, row0, nrows, "upload_rows_u8"));
+    if (h->sparse) return fail(YTK_ERR_ARG, "upload_rows_u8: this handle holds sparse rows (ytk_gbdt_upload_csr)");
+    if (stride < h->F) return fail(YTK_ERR_ARG, "upload_rows_u8: stride %d < feature dim %d", stride, h->F);
+    if (h->n_wide > 0) return fail(YTK_ERR_ARG, "upload_rows_u8: a feature has more than 256 bins; its slots need ytk_gbdt_upload_rows");
+    if (nrows == 0) return YTK_OK;
+    CK(cudaSetDevice(h->device));
+    const int64_t step = std::max<int64_t>(1, (64LL << 20) / (int64_t)stride);
+    for (int64_t r = 0; r < nrows; r += step) {
+        int64_t n = std::min(step, nrows - r);
+        size_t bytes = (size_t)n * stride;
+        RET(ensure_stage(h, bytes));
+        CK(cudaMemcpyAsync(h->d_stage, x_chunk + r * stride, bytes, cudaMemcpyHostToDevice, h->st));
+        CK(ytk::launch_repack_rows_u8((const uint8_t*)h->d_stage, n, stride, h->F, h->d_nbins, h->d_bins + (row0 + r) * h->S8,
+                                      h->S8, h->d_bins_col + (row0 + r), h->N, wide_cols(h, row0 + r), row0 + r, h->d_bad,
+                                      h->st));
+        CK(cudaStreamSynchronize(h->st));
+    }
+    int bad = 0;
+    CK(cudaMemcpy(&bad, h->d_bad, sizeof(int), cudaMemcpyDeviceToHost));
+    if (bad) {
+        CK(cudaMemset(h->d_bad, 0, sizeof(int)));
+        return fail(YTK_ERR_ARG, "upload_rows_u8: slot index outside [0, bins of its feature)");
+    }
+    return YTK_OK;
+}
+
 int ytk_gbdt_quantize_rows(ytk_gbdt* h, const int32_t* xbits_chunk, int64_t row0, int64_t nrows, int32_t stride,
                            const float* cuts) {
     RET(check_rows(h, xbits_chunk, row0, nrows, "quantize_rows"));

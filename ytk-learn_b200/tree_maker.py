@@ -134,6 +134,11 @@ class GpuTreeMaker:
         x = np.ascontiguousarray(x, dtype=np.int32)
         B.check(B.lib().ytk_gbdt_upload_rows(self._h, B.ptr(x), int(row0), x.shape[0], x.shape[1]))
 
+    def upload_rows_u8(self, x, row0=0):
+        """x: uint8 slots [n, stride] (every feature at most 256 bins)."""
+        x = np.ascontiguousarray(x, dtype=np.uint8)
+        B.check(B.lib().ytk_gbdt_upload_rows_u8(self._h, B.ptr(x), int(row0), x.shape[0], x.shape[1]))
+
     def quantize_rows(self, values, cuts, row0=0):
         """values: float32 [n, stride] raw feature values; cuts: sorted bin centres."""
         bits = np.ascontiguousarray(values, dtype=np.float32).view(np.int32)
