@@ -239,12 +239,25 @@ int ytk_gbdt_find_split(ytk_gbdt *h, const double *hist, int64_t sample_cnt,
 int ytk_gbdt_partition_rows(ytk_gbdt *h, const int32_t *rows, int64_t n_rows, int32_t fid,
                             float cond, int32_t *out_rows, int64_t *left_cnt);
 
+/* ---- TreeRefiner for loss_function = l1 --------------------------------------
+ * TreeRefiner.refine (J/optimizer/gbdt/TreeRefiner.java:209-255, exact data-parallel variant :104-123 with
+ * PreciseQuantile's weighted median, J/utils/PreciseQuantile.java:156-208): right after make(), every leaf
+ * of `tree` (the tree that make() just returned) gets the value learning_rate x weighted median of
+ * `residual` over the leaf's rows of ALL ranks -- the sampled rows when a row mask was given.
+ *   residual  label - score per local row (TreeRefiner.java:226), or NULL: y - score as
+ *             ytk_gbdt_set_targets / ytk_gbdt_update_scores hold them on the device;
+ *   weight    per local row, or NULL: GBDTCoreData.weight from set_targets when residual is NULL, else 1.
+ * The refined values also replace the leaf values ytk_gbdt_update_scores adds.  world > 1: a collective
+ * call (every rank gathers all ranks' pairs over NCCL).  The sketch variant (lad_refine_appr = true,
+ * :156-207) is not built: the exact one is what the sketch approximates. */
+int ytk_gbdt_refine_leaves(ytk_gbdt *h, const float *residual, const float *weight, ytk_tree_out *tree);
+
 /* ---- the step either side of make(), kept on the device -------------------
  * GBDTOptimizer.predictAndCalcLossGrad, train branch (J/optimizer/GBDTOptimizer.java:513-609): score
  * update from the trees just made, loss, and the next round's gradient pairs, without the (g,h) arrays
  * crossing PCIe every round.  Optional: a trainer that keeps computing gradients in Java simply keeps
  * calling ytk_gbdt_set_grads. */
-typedef enum { YTK_LOSS_SIGMOID = 0, YTK_LOSS_L2 = 1, YTK_LOSS_SOFTMAX = 2 } ytk_loss;
+typedef enum { YTK_LOSS_SIGMOID = 0, YTK_LOSS_L2 = 1, YTK_LOSS_SOFTMAX = 2, YTK_LOSS_L1 = 3 } ytk_loss;
 
 /* GBDTCoreData.y / weight / initScore (J/dataflow/GBDTCoreData.java:286-296,424-447): y has N*K floats
  * (K > 1: one-hot rows), weight N floats (NULL = 1), init_score N*K floats (NULL = 0).  Resets the

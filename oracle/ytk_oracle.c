@@ -738,6 +738,9 @@ double orc_loss_grad_scalar(int32_t loss_kind, const float *score, const float *
             else l = log(1 + exp(s)) - s * label;
             if (s >= 0.0) pred = 1.0 / (1.0 + exp(-s));
             else { double ez = exp(s); pred = ez / (1.0 + ez); }
+        } else if (loss_kind == 3) {                            /* L1Function (J/loss/L1Function.java:31-54) */
+            l = fabs(label - s);
+            pred = s;
         } else {                                                /* L2Function */
             l = 0.5 * (label - s) * (label - s);
             pred = s;
@@ -747,6 +750,7 @@ double orc_loss_grad_scalar(int32_t loss_kind, const float *score, const float *
         if (gp) {
             double p = pf, d0, d1;
             if (loss_kind == 0) { d0 = p - label; d1 = p * (1.0 - p); }   /* getDerivativeFast */
+            else if (loss_kind == 3) { d0 = p - label; d0 = d0 > 0 ? 1.0 : (d0 < 0 ? -1.0 : d0); d1 = 1.0; }   /* Math.signum */
             else { d0 = p - label; d1 = 1.0; }                  /* ILossFunction default: first/second derivative */
             gp[2 * i] = (float)(d0 * wei);
             gp[2 * i + 1] = (float)(d1 * wei);
@@ -784,4 +788,52 @@ double orc_loss_grad_softmax(const float *score, const float *init_score, const 
     }
     free(ls);
     return loss;
+}
+
+/* ------------------------------------------------------------------ TreeRefiner (l1) */
+
+typedef struct { float v, w; } vw_pair;
+static int vw_cmp(const void *a, const void *b) {
+    float x = ((const vw_pair *)a)->v, y = ((const vw_pair *)b)->v;
+    return x < y ? -1 : (x > y ? 1 : 0);
+}
+
+/* TreeRefiner.refine, exact data-parallel variant (J/optimizer/gbdt/TreeRefiner.java:104-123,209-255) with
+ * PreciseQuantile's weighted median (J/utils/PreciseQuantile.java:156-208: all workers' (value, weight)
+ * pairs of a leaf concatenated, sorted by value, weights accumulated in double in that order, the first
+ * value whose accumulated weight reaches half the total; an empty leaf gives QUANTILE_MISSGING = +inf):
+ * leaf value = median(label - score) * learningRate.  residual/weight are per row; node_of_row as
+ * orc_make_tree returns it (-1: the row was not sampled). */
+void orc_refine_leaves(orc_tree *t, const int32_t *node_of_row, const float *residual, const float *weight,
+                       int64_t n, float learning_rate) {
+    int64_t *cnt = (int64_t *)calloc((size_t)t->n_nodes + 1, sizeof(int64_t));
+    for (int64_t i = 0; i < n; i++) if (node_of_row[i] >= 0) cnt[node_of_row[i] + 1]++;
+    for (int32_t k = 0; k < t->n_nodes; k++) cnt[k + 1] += cnt[k];
+    vw_pair *buf = (vw_pair *)malloc(sizeof(vw_pair) * (size_t)(cnt[t->n_nodes] > 0 ? cnt[t->n_nodes] : 1));
+    int64_t *cur = (int64_t *)malloc(sizeof(int64_t) * ((size_t)t->n_nodes + 1));
+    memcpy(cur, cnt, sizeof(int64_t) * ((size_t)t->n_nodes + 1));
+    for (int64_t i = 0; i < n; i++) {
+        if (node_of_row[i] < 0) continue;
+        vw_pair p = {residual[i], weight ? weight[i] : 1.0f};
+        buf[cur[node_of_row[i]]++] = p;
+    }
+    for (int32_t nid = 0; nid < t->n_nodes; nid++) {
+        if (t->left[nid] != -1) continue;
+        vw_pair *seg = buf + cnt[nid];
+        int64_t m = cnt[nid + 1] - cnt[nid];
+        float med = INFINITY;
+        if (m > 0) {
+            qsort(seg, (size_t)m, sizeof(vw_pair), vw_cmp);
+            double total = 0.0;
+            for (int64_t i = 0; i < m; i++) total += seg[i].w;
+            double target = total * 0.5, acc = 0.0;
+            med = seg[m - 1].v;
+            for (int64_t i = 0; i < m; i++) {
+                acc += seg[i].w;
+                if (acc >= target) { med = seg[i].v; break; }
+            }
+        }
+        t->node_info[nid] = med * learning_rate;
+    }
+    free(buf); free(cur); free(cnt);
 }

@@ -147,6 +147,12 @@ void orc_score_value_bits(const orc_tree *t, const float *thr, const int32_t *de
 double orc_loss_grad_scalar(int32_t loss_kind, const float *score, const float *init_score,
                             const float *y, const float *w, int64_t n, float *gp);
 
+/* TreeRefiner.refine, exact data-parallel variant (J/optimizer/gbdt/TreeRefiner.java:104-123,209-255;
+ * J/utils/PreciseQuantile.java:156-208): every leaf's value becomes learning_rate * weighted median of
+ * `residual` over the leaf's rows (weight NULL: all 1).  loss_kind 3 of orc_loss_grad_scalar is L1Function. */
+void orc_refine_leaves(orc_tree *t, const int32_t *node_of_row, const float *residual, const float *weight,
+                       int64_t n, float learning_rate);
+
 /* Softmax branch (:559-607, J/loss/SoftmaxFunction.java:44-113). y one-hot [n][K]. */
 double orc_loss_grad_softmax(const float *score, const float *init_score, const float *y,
                              const float *w, int64_t n, int32_t K, float *gp, float *pred);

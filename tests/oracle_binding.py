@@ -291,9 +291,23 @@ def score_value_bits(tree, thr, def_child, xbits, score, K=1, gid=0):
 def loss_grad_scalar(kind, score, init_score, y, w, want_grad=True):
     n = len(y)
     gp = np.zeros(2 * n, dtype=np.float32) if want_grad else None
-    loss = lib().orc_loss_grad_scalar(C.c_int32(0 if kind == "sigmoid" else 1), _p(score),
+    loss = lib().orc_loss_grad_scalar(C.c_int32({"sigmoid": 0, "l2": 1, "l1": 3}[kind]), _p(score),
                                       _p(init_score), _p(y), _p(w), C.c_int64(n), _p(gp))
     return loss, gp
+
+
+def refine_leaves(tree, node_of_row, residual, weight, learning_rate):
+    """TreeRefiner.refine (exact): returns a copy of the tree with refined leaf values."""
+    t = _tree_to_orc(tree)
+    ot = t.as_orc()
+    residual = np.ascontiguousarray(residual, dtype=np.float32)
+    weight = None if weight is None else np.ascontiguousarray(weight, dtype=np.float32)
+    pos = np.ascontiguousarray(node_of_row, dtype=np.int32)
+    f = lib().orc_refine_leaves
+    f.restype = None
+    f(C.byref(ot), _p(pos), _p(residual), _p(weight) if weight is not None else None, C.c_int64(len(pos)),
+      C.c_float(learning_rate))
+    return t
 
 
 def loss_grad_softmax(score, init_score, y_onehot, w, K, want_grad=True):

@@ -20,7 +20,14 @@ CASES = {"level": KW, "loss": dict(KW, grow_policy="loss", max_depth=-1, max_lea
          "uneven_gradients": dict(KW, max_depth=5, min_child_hessian_sum=0.01),
          "zero_rows_rank": dict(KW, max_depth=3, min_child_hessian_sum=0.0),
          "sampling_unowned": dict(KW, max_depth=5),
-         "sorted_shards": dict(KW, max_depth=7), "sorted_shards_loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=40)}
+         "sorted_shards": dict(KW, max_depth=7), "sorted_shards_loss": dict(KW, grow_policy="loss", max_depth=-1, max_leaf_cnt=40),
+         "refine_l1": dict(KW, max_depth=5, learning_rate=0.3)}
+
+
+def _residuals(n):
+    """(label - score, weight) of the l1 TreeRefiner case, the same on every rank"""
+    rng = np.random.default_rng(77)
+    return np.round(rng.normal(size=n) * 4).astype(np.float32) / 4, rng.integers(1, 4, size=n).astype(np.float32)
 
 
 def _sampling(case, n, F):
@@ -81,6 +88,9 @@ def _rank(rank, world, nccl_id, case, ret):
     fea, mask = _sampling(case, n, x.shape[1])
     tree = tm.make(0, fea_index=fea, row_mask=None if mask is None else mask[lo:hi])
     pos = tm.get_positions()
+    if case == "refine_l1":                         # TreeRefiner: medians over the rows of ALL ranks
+        res, w = _residuals(n)
+        tm.refine_leaves(tree, res[lo:hi], w[lo:hi])
     hist = tm.build_hist(0)                         # reduced over ranks: the global root histogram
     ret[rank] = ({name: getattr(tree, name) for name, _ in yb.Tree.FIELDS}, pos, hist)
     tm.close()
@@ -101,6 +111,11 @@ def test_two_gpus_equal_one_gpu_and_oracle(case):
     fea, mask = _sampling(case, n, x.shape[1])
     t1 = one.make(0, fea_index=fea, row_mask=mask)
     p1 = one.get_positions()
+    if case == "refine_l1":
+        res, w = _residuals(n)
+        want = ob.refine_leaves(t1, p1, res, w, CASES[case]["learning_rate"])
+        one.refine_leaves(t1, res, w)
+        assert np.array_equal(t1.node_info, want.node_info)
     h1 = one.build_hist(0)
     ctx = mp.get_context("spawn")
     mgr = ctx.Manager()
@@ -122,5 +137,8 @@ def test_two_gpus_equal_one_gpu_and_oracle(case):
         assert np.array_equal(ret[r][2], h1)
     assert np.array_equal(pos, p1)
     o, opos, _ = ob.make_tree(ob.make_params(**CASES[case]), x, gp, 0, start, W=world, fea_index=fea, row_mask=mask)
+    if case == "refine_l1":
+        res, w = _residuals(n)
+        o = ob.refine_leaves(o, opos, res, w, CASES[case]["learning_rate"])
     assert_same_tree(t1, o)
     assert np.array_equal(p1, opos)

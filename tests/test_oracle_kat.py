@@ -80,3 +80,37 @@ def test_value_walk_with_missing_values_default_child():
     ob.score_value_bits(t, thr, None, v.view(np.int32), a)
     ob.score_values(t, thr, v, b2)
     assert np.array_equal(a, b2)
+
+
+def test_oracle_weighted_median_of_tree_refiner():
+    """orc_refine_leaves against a direct numpy restatement of PreciseQuantile.getWeightedQuantileLocal
+    (J/utils/PreciseQuantile.java:156-208) and a hand-worked case."""
+    import oracle_binding as ob
+
+    class T:
+        pass
+    t = T()
+    t.n_nodes = 3
+    for name, dt in ob.Tree.FIELDS:
+        setattr(t, name, np.zeros(3, dt))
+    t.left[:] = [1, -1, -1]
+    t.right[:] = [2, -1, -1]
+    # leaf 1: values 1,2,3,4 with weights 1,1,1,1 -> total 4, target 2 -> first acc >= 2 is value 2
+    # leaf 2: values 5,7 with weights 1,3 -> target 2 -> value 7; one unsampled row
+    pos = np.array([1, 1, 1, 1, 2, 2, -1], np.int32)
+    res = np.array([4, 1, 3, 2, 7, 5, 100], np.float32)
+    w = np.array([1, 1, 1, 1, 3, 1, 9], np.float32)
+    out = ob.refine_leaves(t, pos, res, w, 0.5)
+    assert out.node_info[1] == np.float32(2 * 0.5) and out.node_info[2] == np.float32(7 * 0.5)
+    rng = np.random.default_rng(0)
+    n = 5000
+    pos = rng.integers(1, 3, size=n).astype(np.int32)
+    res = rng.normal(size=n).astype(np.float32)
+    w = rng.random(n).astype(np.float32)
+    out = ob.refine_leaves(t, pos, res, w, 1.0)
+    for leaf in (1, 2):
+        idx = np.where(pos == leaf)[0]
+        order = idx[np.argsort(res[idx], kind="stable")]
+        acc = np.cumsum(w[order].astype(np.float64))
+        k = int(np.argmax(acc >= acc[-1] * 0.5))
+        assert out.node_info[leaf] == res[order][k]

@@ -111,6 +111,7 @@ _SIGS = {
     "ytk_gbdt_subtract_hist": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ytk_gbdt_find_split": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p]),
     "ytk_gbdt_partition_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p, C.c_void_p]),
+    "ytk_gbdt_refine_leaves": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ytk_gbdt_set_targets": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ytk_gbdt_update_scores": (C.c_int, [C.c_void_p, C.c_int32]),
     "ytk_gbdt_compute_grads": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -10,7 +10,7 @@ int ytk_gbdt_set_targets(ytk_gbdt* h, int32_t loss, const float* y, const float*
     if (!h || !y) return fail(YTK_ERR_ARG, "set_targets: null argument");
     if (!h->rows_set) return fail(YTK_ERR_ARG, "set_targets: call set_bins first");
     const int K = h->p.class_num;
-    if (loss < 0 || loss > 2) return fail(YTK_ERR_ARG, "set_targets: unknown loss %d", loss);
+    if (loss < 0 || loss > 3) return fail(YTK_ERR_ARG, "set_targets: unknown loss %d", loss);
     // GBDTOptimizationParams.checkParams: only softmax may have class_num > 1 (:222-224)
     if (loss != YTK_LOSS_SOFTMAX && K > 1)
         return fail(YTK_ERR_ARG, "[GBDT] class_num(%d) and objective(%d) inconsistent", K, loss);

@@ -99,6 +99,9 @@ __global__ void loss_grad_scalar_k(int loss_kind, const float* __restrict__ scor
                 l = __dsub_rn(log(__dadd_rn(1.0, e)), __dmul_rn(s, label));
                 pred = __ddiv_rn(e, __dadd_rn(1.0, e));
             }
+        } else if (loss_kind == 3) {                        // L1Function (J/loss/L1Function.java:31-54)
+            l = fabs(__dsub_rn(label, s));
+            pred = s;
         } else {
             const double d = __dsub_rn(label, s);
             l = __dmul_rn(__dmul_rn(0.5, d), d);
@@ -106,7 +109,8 @@ __global__ void loss_grad_scalar_k(int loss_kind, const float* __restrict__ scor
         }
         loss = __dadd_rn(loss, __dmul_rn(wei, l));
         const double p = (double)(float)pred;
-        const double d0 = __dsub_rn(p, label);
+        double d0 = __dsub_rn(p, label);
+        if (loss_kind == 3) d0 = d0 > 0.0 ? 1.0 : (d0 < 0.0 ? -1.0 : d0);      // Math.signum(score - label)
         const double d1 = loss_kind == 0 ? __dmul_rn(p, __dsub_rn(1.0, p)) : 1.0;
         *reinterpret_cast<float2*>(gp + 2 * i) = make_float2((float)__dmul_rn(d0, wei), (float)__dmul_rn(d1, wei));
     }

@@ -187,7 +187,7 @@ class GpuTreeMaker:
         return out
 
     # ---- the step either side of make(), on the device ------------------
-    LOSSES = {"sigmoid": 0, "l2": 1, "softmax": 2}
+    LOSSES = {"sigmoid": 0, "l2": 1, "softmax": 2, "l1": 3}
 
     def set_targets(self, loss, y, weight=None, init_score=None):
         """GBDTCoreData.y / weight / initScore; y is [N*K] (one-hot rows when K > 1)."""
@@ -197,6 +197,16 @@ class GpuTreeMaker:
         w = None if weight is None else np.ascontiguousarray(weight, dtype=np.float32)
         i0 = None if init_score is None else np.ascontiguousarray(init_score, dtype=np.float32).reshape(-1)
         B.check(B.lib().ytk_gbdt_set_targets(self._h, self.LOSSES[loss], B.ptr(y), B.ptr(w), B.ptr(i0)))
+
+    def refine_leaves(self, tree, residual=None, weight=None):
+        """TreeRefiner.refine (l1): leaf values of `tree` (the last make()'s) become learning_rate x the weighted
+        median of the residuals of their rows; returns the tree (modified in place)."""
+        r = None if residual is None else np.ascontiguousarray(residual, dtype=np.float32)
+        w = None if weight is None else np.ascontiguousarray(weight, dtype=np.float32)
+        ct = tree._as_c()
+        ct.n_nodes = tree.n_nodes
+        B.check(B.lib().ytk_gbdt_refine_leaves(self._h, B.ptr(r), B.ptr(w), C.addressof(ct)))
+        return tree
 
     def update_scores(self, group_id=0):
         B.check(B.lib().ytk_gbdt_update_scores(self._h, int(group_id)))
