@@ -5,7 +5,7 @@ set -e
 cd "$(dirname "$0")"
 OUT=ytk-learn_b200/libytkgbdt.so
 SRC=ytk-learn_b200/csrc
-FILES="rows hist split partition level boost_kernels peer tree_maker grow engine boost refine hooks no_alloc"
+FILES="rows hist split partition level boost_kernels peer tree_maker grow engine boost refine hooks no_alloc formats"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-ffp-contract=off,-Wall -I include -I $SRC ${YTK_NVCC_EXTRA}"
 mkdir -p build
 newest_hdr=$(ls -t $SRC/*.cuh $SRC/*.h include/*.h build.sh | head -1)

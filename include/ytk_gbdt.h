@@ -239,6 +239,38 @@ int ytk_gbdt_find_split(ytk_gbdt *h, const double *hist, int64_t sample_cnt,
 int ytk_gbdt_partition_rows(ytk_gbdt *h, const int32_t *rows, int64_t n_rows, int32_t fid,
                             float cond, int32_t *out_rows, int64_t *left_cnt);
 
+/* ---- the text formats either side of the tree maker (host only, no GPU needed) ------
+ * The model text of GBDTModel.dumpModel / loadModel (J/data/gbdt/GBDTModel.java:63-97) and Tree.dumpModel / loadModel
+ * (J/data/gbdt/Tree.java:192-291; node patterns :47-48; TreeNodeStat.print J/data/gbdt/TreeNodeStat.java:71-79),
+ * byte for byte: floats are printed as java.lang.Float.toString prints them.  A tree is its ytk_tree_out arrays
+ * (node_info = leaf values) plus per node: the real-valued threshold of an inner node (convertModel,
+ * J/optimizer/GBDTOptimizer.java:663-677), its default child (NULL: the left one) and -- optionally -- feature
+ * names indexed by fid (NULL: the decimal fid).  The dump functions return the number of bytes the text needs
+ * (without the terminating NUL) and write at most cap bytes; -1 on a malformed tree. */
+int ytk_gbdt_float_to_string(float v, char *out, int32_t cap);
+int64_t ytk_gbdt_dump_model_header(float base_prediction, int32_t class_num, const char *loss_function, int32_t tree_num,
+                                   char *out, int64_t cap);
+int64_t ytk_gbdt_dump_tree(const ytk_tree_out *tree, const float *threshold, const int32_t *default_child,
+                           const char *const *feature_names, int32_t iter, int32_t with_stats, char *out, int64_t cap);
+/* *consumed = bytes of `text` read; ytk_gbdt_load_tree fills the caller's arrays (tree->capacity nodes; fid = the
+ * feature name when it is a decimal number, else -1; names: name_stride bytes per node, may be NULL). */
+int ytk_gbdt_load_model_header(const char *text, int64_t len, float *base_prediction, int32_t *class_num,
+                               char *loss_function, int32_t loss_cap, int32_t *tree_num, int64_t *consumed);
+int ytk_gbdt_load_tree(const char *text, int64_t len, ytk_tree_out *tree, float *threshold, int32_t *default_child,
+                       char *names, int32_t name_stride, int64_t *consumed);
+/* The ytklearn training-row text (docs/data_format.md:1-40: weight x_delim labels x_delim name:value,... [x_delim init
+ * prediction]) parsed as GBDTCoreData does (J/dataflow/GBDTCoreData.java:205-249,352-404, J/dataflow/CoreData.java:
+ * 369-378) into weight[row], y[row][class_num] (a single class index becomes a one-hot row), init_score (may be NULL) and
+ * CSR rows for ytk_gbdt_quantize_csr: row_ptr[rows + 1], fids, value_bits = Float.floatToRawIntBits(value), entries
+ * sorted by feature, the last value of a repeated name kept (it is a HashMap there).  dict_sorted: the feature names in
+ * lexicographic order = their indices (J/dataflow/DataFlow.java:299-329); names not in it are skipped; NULL: the name
+ * is its own decimal index.  Delimiters are literal strings.  Stops at max_rows / max_entries or at an unterminated
+ * last line; *consumed = bytes parsed, so a caller streams a file chunk by chunk. */
+int ytk_gbdt_parse_rows(const char *text, int64_t len, const char *x_delim, const char *y_delim, const char *features_delim,
+                        const char *name_val_delim, int32_t class_num, const char *const *dict_sorted, int32_t n_dict,
+                        int64_t max_rows, int64_t max_entries, float *weight, float *y, float *init_score, int64_t *row_ptr,
+                        int32_t *fids, int32_t *value_bits, int64_t *n_rows, int64_t *n_entries, int64_t *consumed);
+
 /* ---- TreeRefiner for loss_function = l1 --------------------------------------
  * TreeRefiner.refine (J/optimizer/gbdt/TreeRefiner.java:209-255, exact data-parallel variant :104-123 with
  * PreciseQuantile's weighted median, J/utils/PreciseQuantile.java:156-208): right after make(), every leaf

@@ -31,6 +31,12 @@ def main():
     start = np.array([0, len(cuts)], np.int32)
     bins = ob.find_bins(vals.reshape(-1, 1), cuts, start).reshape(-1)
     np.savez_compressed(os.path.join(HERE, "bins_golden.npz"), cuts=cuts, vals=vals, bins=bins)
+    # the first rows of the reference's demo data, verbatim: input of the row-format parser test
+    import ytk_data as yd
+    for name, rows in (("agaricus.train.ytklearn", 25), ("dermatology.train.ytklearn", 25)):
+        with open(os.path.join(yd.REF, "demo/data/ytklearn", name)) as src, open(os.path.join(HERE, name + ".head"), "w") as dst:
+            for _ in range(rows):
+                dst.write(src.readline())
 
 
 if __name__ == "__main__":

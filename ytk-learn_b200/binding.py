@@ -111,6 +111,15 @@ _SIGS = {
     "ytk_gbdt_subtract_hist": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ytk_gbdt_find_split": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p]),
     "ytk_gbdt_partition_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_float, C.c_void_p, C.c_void_p]),
+    "ytk_gbdt_float_to_string": (C.c_int, [C.c_float, C.c_char_p, C.c_int32]),
+    "ytk_gbdt_dump_model_header": (C.c_int64, [C.c_float, C.c_int32, C.c_char_p, C.c_int32, C.c_char_p, C.c_int64]),
+    "ytk_gbdt_dump_tree": (C.c_int64, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_char_p, C.c_int64]),
+    "ytk_gbdt_load_model_header": (C.c_int, [C.c_char_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32, C.c_void_p,
+                                             C.c_void_p]),
+    "ytk_gbdt_load_tree": (C.c_int, [C.c_char_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32, C.c_void_p]),
+    "ytk_gbdt_parse_rows": (C.c_int, [C.c_char_p, C.c_int64, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int32, C.c_void_p,
+                                      C.c_int32, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ytk_gbdt_refine_leaves": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ytk_gbdt_set_targets": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ytk_gbdt_update_scores": (C.c_int, [C.c_void_p, C.c_int32]),
