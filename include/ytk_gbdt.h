@@ -95,7 +95,10 @@ typedef struct {
     double  host_wait_ms;     /* ... and its one wait for the device                                    */
     int32_t stage_times_from_gpu; /* 1: build_hist .. partition above are CUDA-event times of the stages on the
                                      device (they add up to the tree's device time); 0: host wall-clock per stage */
-    int32_t reserved;
+    int32_t graph_replayed;   /* 1: the tree's launches were replayed from a recorded CUDA graph */
+    double  device_span_ms;   /* device-driven level loop: first kernel start to last kernel end on the GPU's timer */
+    double  hist_events_ms;   /* CUDA-event time around the histogram launches when they were queued directly (0 in a replay):
+                                 gpu_hist_ms is then the kernels' own span on the GPU's timer, and the two agree */
 } ytk_time_stats;
 
 /* One best split: SplitInfo (J/data/gbdt/SplitInfo.java:36-70) plus the node totals the

@@ -93,9 +93,12 @@ cudaError_t launch_unpack_rows(const uint8_t* bins, int32_t S8, int64_t nrows, i
 // (g,h) float pairs of class gid -> fixed-point int2 (|value| < 2^bits) + scales, in two steps: the
 // largest |g| and |h| of the shard as float bits in absmax_bits[2] (with several GPUs the host takes
 // the maximum over the ranks in between: all ranks must use the same scales), then the conversion
-cudaError_t launch_grad_absmax(const float* gp, int64_t n, int32_t K, int32_t gid, unsigned* absmax_bits, cudaStream_t st);
+// gid_dev != null: the class index is read on the device (launches recorded in a CUDA graph)
+cudaError_t launch_grad_absmax(const float* gp, int64_t n, int32_t K, int32_t gid, unsigned* absmax_bits, cudaStream_t st,
+                               const int* gid_dev = nullptr);
 cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t gid, int2* gq,
-                                 const unsigned* absmax_bits, GradScale* scale, int bits, cudaStream_t st);
+                                 const unsigned* absmax_bits, GradScale* scale, int bits, cudaStream_t st,
+                                 const int* gid_dev = nullptr);
 
 // K2: histograms of n_items row runs; item -> segment -> seg_out[seg] (int64, pre-zeroed); feature f's
 // bins at seg_out[seg] + feat_owner[f]*owner_stride + feat_inner[f] + 2*bin + {0,1}.
@@ -113,7 +116,7 @@ struct BuildNode { long long begin, end; long long cost_end; long long cost; int
 cudaError_t launch_hist_span(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1,
                              const BuildNode* nodes, const int* n_nodes_dev, int groups, int32_t F, const uint32_t* group_mask,
                              const int32_t* nbins, const int32_t* feat_owner, const int64_t* feat_inner, long long owner_stride,
-                             long long* const* seg_out, cudaStream_t st);
+                             long long* const* seg_out, cudaStream_t st, unsigned long long* stamp = nullptr);
 // the wide features' share of the same work items: 64-bit global reductions, one CTA per (item, feature)
 cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide, const int2* gq, const int32_t* rowidx0,
                              const int32_t* rowidx1, const RowItem* items, int n_items, const int32_t* feat_owner,
@@ -154,7 +157,8 @@ cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t*
                               SplitPart* parts /* n_nodes * split_scan_slices() scratch */, ytk_split* out,
                               ytk_split* mirror /* nullable: a second copy of the records (pinned host memory) */,
                               unsigned int* done /* n_nodes zero-initialised counters; left zero */, cudaStream_t st,
-                              long long* lh_out = nullptr /* [n_nodes][2]: hessian left of the best split, of the node (fixed point) */);
+                              long long* lh_out = nullptr /* [n_nodes][2]: hessian left of the best split, of the node (fixed point) */,
+                              unsigned long long* stamp = nullptr /* {~start, end} on the global timer, see device_util.cuh */);
 int split_scan_slices(int32_t f_from, int32_t f_to);
 
 // K6: stable partition of every segment by (float)bin(row,fid) < cond (or by a byte mask)

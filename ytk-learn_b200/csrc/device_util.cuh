@@ -28,6 +28,22 @@ static cudaError_t launch_chain(void (*kernel)(KArgs...), dim3 grid, dim3 block,
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
+// A kernel's own account of when it ran: the first CTA's start and the last CTA's end on the GPU's global timer
+// (ns), kept as {max of ~start, max of end} so that an all-zero pair means "did not run".  Launches replayed
+// from a CUDA graph cannot be bracketed with CUDA events (cudaEventElapsedTime refuses events recorded by a
+// graph), so the device-driven level loop times its kernels this way.
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void stamp_begin(unsigned long long* s) {
+    if (s && threadIdx.x == 0) atomicMax(s, ~global_ns());
+}
+__device__ __forceinline__ void stamp_end(unsigned long long* s) {
+    if (s && threadIdx.x == 0) atomicMax(s + 1, global_ns());
+}
+
 // smaller child = strictly fewer GLOBAL rows on the left, else the right
 // (J/optimizer/gbdt/DataParallelTreeMaker.java:344-350, :493-499)
 __device__ __forceinline__ RowItem resolve_item(RowItem it, const PartitionCounts* __restrict__ cnt_local,

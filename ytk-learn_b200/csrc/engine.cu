@@ -16,6 +16,11 @@ namespace {
 
 size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 
+// kernels of a tree that report their own time span (device_util.cuh): stamp slot = kind * kStampLevels + level
+constexpr int kStampLevels = 20;
+enum StampKind { kStHist = 0, kStPart = 1, kStScan = 2, kStKinds = 3 };
+constexpr int kMaxStamps = kStKinds * kStampLevels;
+
 // buffer the rows of level d live in: the root's (-1 identity / 0 after a row mask), then alternating
 int level_buf(int root_buf, int d) {
     int b = root_buf;
@@ -44,26 +49,34 @@ bool engine_applicable(const ytk_gbdt* h) {
     return true;
 }
 
+void engine_drop_graphs(ytk_gbdt* h) {
+    for (auto& g : h->eng.graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+    h->eng.graphs.clear();
+}
+
 // Device tables and their pinned mirrors for trees of depth D (kept across trees).
 static int engine_reserve(ytk_gbdt* h, int D) {
     EngineBuffers& e = h->eng;
     const size_t heap = (size_t(1) << (D + 1)) - 1, slots = size_t(1) << (D - 1);
     const size_t tiles = (size_t)(h->N / ytk::kFusedTile) + (size_t(1) << D) + 2;
     if (e.depth == D && e.tile_cap >= tiles) return YTK_OK;
+    engine_drop_graphs(h);                               // they hold the old tables' addresses
     if (e.dev) CK(cudaFree(e.dev));
     if (e.host) CK(cudaFreeHost(e.host));
     e = EngineBuffers();
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off = align256(off + bytes); return o; };
     const size_t o_nodes = take(heap * sizeof(ytk::LvNode)), o_recs = take(heap * sizeof(ytk_split)),
-                 o_lh = take(heap * 2 * sizeof(long long)), o_leaf = take(heap * 2 * sizeof(long long));
+                 o_lh = take(heap * 2 * sizeof(long long)), o_leaf = take(heap * 2 * sizeof(long long)),
+                 o_stamps = take(2 * kMaxStamps * sizeof(unsigned long long));
     const size_t mirror_bytes = off;                     // everything up to here is copied back after the tree
     const size_t o_segs = take(slots * sizeof(ytk::SplitSeg)), o_tiles = take(tiles * sizeof(int)), o_ntiles = take(sizeof(int)),
                  o_counts = take(slots * sizeof(ytk::PartitionCounts)), o_gcounts = take(slots * sizeof(ytk::PartitionCounts)),
                  o_build = take(2 * slots * sizeof(ytk::BuildNode)), o_nbuild = take(sizeof(int)),
                  o_subs = take(slots * sizeof(ytk::SubItem)), o_scans = take(2 * slots * sizeof(ytk::ScanNode)),
                  o_segout = take(2 * slots * sizeof(long long*)), o_segfinal = take(2 * slots * sizeof(long long*)),
-                 o_recs_local = take(2 * slots * sizeof(ytk_split)), o_lh_local = take(4 * slots * sizeof(long long));
+                 o_recs_local = take(2 * slots * sizeof(ytk_split)), o_lh_local = take(4 * slots * sizeof(long long)),
+                 o_epoch = take(sizeof(unsigned long long)), o_gid = take(sizeof(int));
     CK(cudaMalloc(&e.dev, off));
     CK(cudaMemsetAsync(e.dev, 0, off, h->st));
     CK(cudaHostAlloc((void**)&e.host, mirror_bytes, cudaHostAllocDefault));
@@ -86,9 +99,13 @@ static int engine_reserve(ytk_gbdt* h, int D) {
     t.seg_final = reinterpret_cast<long long**>(e.dev + o_segfinal);
     t.recs_local = reinterpret_cast<ytk_split*>(e.dev + o_recs_local);
     t.lh_local = reinterpret_cast<long long*>(e.dev + o_lh_local);
+    t.epoch = reinterpret_cast<unsigned long long*>(e.dev + o_epoch);
+    t.gid = reinterpret_cast<int*>(e.dev + o_gid);
     e.h_nodes = reinterpret_cast<ytk::LvNode*>(e.host + o_nodes);
     e.h_recs = reinterpret_cast<ytk_split*>(e.host + o_recs);
     e.h_leaf = reinterpret_cast<long long*>(e.host + o_leaf);
+    e.d_stamps = reinterpret_cast<unsigned long long*>(e.dev + o_stamps);
+    e.h_stamps = reinterpret_cast<unsigned long long*>(e.host + o_stamps);
     e.clear_bytes = o_segs;                              // nodes, records, left hessians, leaf sums: cleared per tree
     return YTK_OK;
 }
@@ -103,10 +120,41 @@ public:
     // One rank on its own (one GPU, or one process per GPU with exchanges over peer memory).
     int run(int gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask) {
         const double t0 = now_ms();
+        RET(prepare(gid, fea_index, n_fea));
+        // On one GPU the launch sequence of a tree is the same every time (grids are upper bounds, tables and the
+        // class index live on the device): it is recorded once as a CUDA graph and replayed, which takes the
+        // per-launch gaps out of the ~60 short kernels of a tree.  (Not with a row mask: its table upload is per tree.)
+        bool launched = false;
+        if (h->use_graph && h->world == 1 && !row_mask) {
+            const unsigned long long sig = signature();
+            EngineGraph* g = nullptr;
+            for (auto& c : h->eng.graphs) if (c.sig == sig) g = &c;
+            if (!g) RET(record_graph(sig, &g));
+            if (g) {
+                CK(cudaGraphLaunch(g->exec, h->st));
+                marks = g->marks;
+                h->ev_stage_used = g->ev_stage_used; h->ev_used = g->ev_used; h->launches += g->launches;
+                root_buf = -1;
+                launched = true;
+                replayed = true;
+                T->graph_replayed = 1;
+            }
+        }
+        if (!launched) RET(enqueue_tree(row_mask));
+        const double t1 = now_ms();
+        CK(cudaStreamSynchronize(h->st));                 // the one host wait of the tree
+        RET(peer_check(h, "make_tree"));
+        const double t2 = now_ms();
+        RET(after_wait(row_mask != nullptr, t0, t1, t2));
+        return YTK_OK;
+    }
+
+    // everything a tree queues, from the gradient scales to the copy of the records back to the host
+    int enqueue_tree(const uint8_t* row_mask) {
         const int x = h->world > 1 ? ytk::kXAll : 0;
-        RET(begin_scale(gid, fea_index, n_fea));
+        RET(begin_scale());
         if (x) RET(x_max(x));
-        RET(begin_root(gid, row_mask));
+        RET(begin_root(row_mask));
         RET(root_hist());
         if (x) RET(x_hist(-1, x));
         RET(root_scan());
@@ -123,12 +171,50 @@ public:
                 if (x) RET(x_recs(d, x));
             }
         }
-        RET(finish_enqueue());
-        const double t1 = now_ms();
-        CK(cudaStreamSynchronize(h->st));                 // the one host wait of the tree
-        RET(peer_check(h, "make_tree"));
-        const double t2 = now_ms();
-        RET(after_wait(row_mask != nullptr, t0, t1, t2));
+        return finish_enqueue();
+    }
+
+    // what a recorded launch sequence depends on besides the contents of device memory
+    unsigned long long signature() const {
+        unsigned long long v = 1469598103934665603ull;
+        auto mix = [&](unsigned long long x) { v = (v ^ x) * 1099511628211ull; };
+        mix((unsigned long long)(uintptr_t)h->eng.dev); mix((unsigned long long)(uintptr_t)h->eng.host);
+        mix((unsigned long long)(uintptr_t)h->d_tile_state); mix((unsigned long long)(uintptr_t)h->d_ticket);
+        mix((unsigned long long)(uintptr_t)h->t_parts.d); mix((unsigned long long)(uintptr_t)h->t_scan_done.d);
+        mix((unsigned long long)(uintptr_t)h->h_scale.h); mix((unsigned long long)(uintptr_t)h->d_gq);
+        mix((unsigned long long)(first_owned + 7)); mix((unsigned long long)D); mix((unsigned long long)h->N);
+        mix((unsigned long long)t.flush_cost);
+        return v;
+    }
+
+    int record_graph(unsigned long long sig, EngineGraph** out) {
+        *out = nullptr;
+        cudaGraph_t graph = nullptr;
+        const int launches_before = h->launches;
+        h->ev_used = 0;
+        if (cudaStreamBeginCapture(h->st, cudaStreamCaptureModeRelaxed) != cudaSuccess) { cudaGetLastError(); h->use_graph = false; return YTK_OK; }
+        capturing = true;
+        const int rc = enqueue_tree(nullptr);
+        capturing = false;
+        const cudaError_t ce = cudaStreamEndCapture(h->st, &graph);
+        cudaGraphExec_t exec = nullptr;
+        if (rc != YTK_OK || ce != cudaSuccess || !graph || cudaGraphInstantiate(&exec, graph, 0) != cudaSuccess) {
+            // recording is an optimisation: without it the same calls are queued directly
+            cudaGetLastError();
+            if (graph) cudaGraphDestroy(graph);
+            h->use_graph = false;
+            h->launches = launches_before;
+            if (getenv("YTK_GBDT_VERBOSE")) fprintf(stderr, "ytk_gbdt: CUDA graph recording failed (%s); trees are queued launch by launch\n", cudaGetErrorString(ce));
+            return YTK_OK;
+        }
+        cudaGraphDestroy(graph);
+        if (h->eng.graphs.size() >= 32) engine_drop_graphs(h);
+        EngineGraph g;
+        g.sig = sig; g.exec = exec; g.marks = marks; g.ev_stage_used = h->ev_stage_used; g.ev_used = h->ev_used;
+        g.launches = h->launches - launches_before;
+        h->launches = launches_before;
+        h->eng.graphs.push_back(g);
+        *out = &h->eng.graphs.back();
         return YTK_OK;
     }
 
@@ -157,7 +243,9 @@ public:
     enum Stage { kInit = 0, kHist, kComm, kSplit, kSync, kPart, kStages };
     std::vector<int> marks;              // stage that ENDS at event i + 1
 
+    bool capturing = false;            // a recorded sequence carries no CUDA events (they cannot be read back from a replay)
     int mark(Stage s) {
+        if (capturing) return YTK_OK;
         if (h->ev_stage_used >= (int)h->ev_stage.size()) {
             cudaEvent_t e;
             CK(cudaEventCreate(&e));
@@ -168,7 +256,9 @@ public:
         return YTK_OK;
     }
 
-    int begin_scale(int gid, const int32_t* fea_index, int32_t n_fea) {
+    // Outside any recording: tables and scratch at their final sizes (nothing is allocated while a tree is queued),
+    // the selected features and the class index on the device.
+    int prepare(int gid, const int32_t* fea_index, int32_t n_fea) {
         RET(engine_reserve(h, D));
         t = h->eng.t;
         t.pool = h->d_pool_chunk;
@@ -179,15 +269,30 @@ public:
         t.flush_cost = flush_cost;
         RET(set_features(h, fea_index, n_fea, &first_owned, &n_sel));
         h->pool.clear();
+        RET(next_partition_epoch(h, h->eng.tile_cap));    // the partition's chained-scan state for the largest level
+        t.ticket = h->d_ticket + 1;
+        CK(h->t_parts.reserve((size_t)(2 << D) * ytk::split_scan_slices(h->f_from, h->f_to)));
+        RET(scan_done_counters(h, 2 << D));
+        while ((int)h->ev_stage.size() < 6 * D + 16) { cudaEvent_t e; CK(cudaEventCreate(&e)); h->ev_stage.push_back(e); }
+        while ((int)h->ev.size() < 2 * D + 4) { cudaEvent_t e; CK(cudaEventCreate(&e)); h->ev.push_back(e); }
+        int* stage = static_cast<int*>(h->arena.take(sizeof(int), h->st));
+        if (!stage) return fail(YTK_ERR_CUDA, "pinned staging allocation failed");
+        *stage = gid;
+        CK(cudaMemcpyAsync(t.gid, stage, sizeof(int), cudaMemcpyHostToDevice, h->st));
+        return YTK_OK;
+    }
+
+    int begin_scale() {
         h->ev_stage_used = 0;
+        marks.clear();
         RET(mark(kInit));                                 // (event 0: the start; its stage label is unused)
-        CK(ytk::launch_grad_absmax(h->d_gp, h->N, p.class_num, gid, h->d_absmax, h->st));
+        CK(ytk::launch_grad_absmax(h->d_gp, h->N, p.class_num, 0, h->d_absmax, h->st, t.gid));
         h->launches++;
         return YTK_OK;
     }
 
-    int begin_root(int gid, const uint8_t* row_mask) {
-        CK(ytk::launch_grad_quantize(h->d_gp, h->N, p.class_num, gid, h->d_gq, h->d_absmax, h->d_scale, h->fixed_bits, h->st));
+    int begin_root(const uint8_t* row_mask) {
+        CK(ytk::launch_grad_quantize(h->d_gp, h->N, p.class_num, 0, h->d_gq, h->d_absmax, h->d_scale, h->fixed_bits, h->st, t.gid));
         h->launches++;
         CK(cudaMemcpyAsync(h->h_scale.h, h->d_scale, sizeof(ytk::GradScale), cudaMemcpyDeviceToHost, h->st));
         CK(cudaMemsetAsync(h->eng.dev, 0, h->eng.clear_bytes, h->st));
@@ -211,9 +316,6 @@ public:
             mask_counts = h->t_counts.d;
             root_buf = 0;
         }
-        // the partition's chained-scan state for the largest level
-        RET(next_partition_epoch(h, h->eng.tile_cap));
-        t.ticket = h->d_ticket + 1;
         CK(ytk::launch_lv_root(t, 0, h->N, root_buf, mask_counts, h->st));
         h->launches++;
         RET(mark(kInit));
@@ -254,26 +356,28 @@ public:
         return YTK_OK;
     }
 
-    int hist_launch(int m_slots) {
-        cudaEvent_t e0, e1;
-        RET(hist_events(h, &e0, &e1));
-        CK(cudaEventRecord(e0, h->st));
+    unsigned long long* stamp(StampKind k, int level) { return h->eng.d_stamps + 2 * (k * kStampLevels + level); }
+
+    int hist_launch(int m_slots, int level) {
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (!capturing) {
+            RET(hist_events(h, &e0, &e1));
+            CK(cudaEventRecord(e0, h->st));
+        }
         CK(ytk::launch_hist_span(h->d_bins, h->S8, h->d_gq, h->d_rowidx[0], h->d_rowidx[1], t.build, t.n_build, h->groups, h->F,
                                  h->d_group_mask, h->d_nbins, h->d_feat_owner, h->d_off_inner,
-                                 h->world == 1 ? 0 : (long long)m_slots * h->seg_max, t.seg_out, h->st));
-        CK(cudaEventRecord(e1, h->st));
+                                 h->world == 1 ? 0 : (long long)m_slots * h->seg_max, t.seg_out, h->st, stamp(kStHist, level)));
+        if (!capturing) CK(cudaEventRecord(e1, h->st));
         h->launches++;
         return YTK_OK;
     }
 
-    int scan_launch(const ytk::ScanNode* nodes, int n, size_t first_heap) {
-        CK(h->t_parts.reserve((size_t)n * ytk::split_scan_slices(h->f_from, h->f_to)));
-        RET(scan_done_counters(h, n));
+    int scan_launch(const ytk::ScanNode* nodes, int n, size_t first_heap, int level) {
         // several GPUs: this rank's records first, the merged ones go to the heap arrays (x_recs)
         CK(ytk::launch_split_scan(nodes, n, h->d_start, h->d_off_inner, h->d_fea_sel, h->f_from, h->f_to, first_owned,
                                   h->d_scale, gain_params(p), nullptr, h->t_parts.d,
                                   h->world == 1 ? t.recs + first_heap : t.recs_local, nullptr, h->t_scan_done.d, h->st,
-                                  h->world == 1 ? t.left_h + 2 * first_heap : t.lh_local));
+                                  h->world == 1 ? t.left_h + 2 * first_heap : t.lh_local, stamp(kStScan, level)));
         h->launches++;
         return YTK_OK;
     }
@@ -290,12 +394,12 @@ public:
     // findBestSplit(root) (:302-318)
     int root_hist() {
         RET(zero_build_targets(0, 1));
-        RET(hist_launch(1));
+        RET(hist_launch(1, 0));
         RET(mark(kHist));
         return YTK_OK;
     }
     int root_scan() {
-        RET(scan_launch(t.scans, 1, 0));
+        RET(scan_launch(t.scans, 1, 0, 0));
         RET(mark(kSplit));
         return YTK_OK;
     }
@@ -307,10 +411,9 @@ public:
         const bool leaf = d == D - 1;                     // the children are leaves (:266)
         CK(ytk::launch_lv_plan_split(t, d, buf, p.min_split_loss, nullptr, ytk::kFusedTile, h->st));
         const long long grid_bound = root_rows_bound / ytk::kFusedTile + m + 1;
-        RET(next_partition_epoch(h, (size_t)grid_bound));
         CK(ytk::launch_partition_fused_planned(h->d_bins_col, h->S8, h->N, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1], t.segs, m,
-                                               t.tile_seg, t.n_tiles, (int)grid_bound, h->d_tile_state, t.ticket, h->part_epoch,
-                                               t.counts, h->st));
+                                               t.tile_seg, t.n_tiles, (int)grid_bound, h->d_tile_state, t.ticket, t.epoch,
+                                               t.counts, h->st, sparse_rows(h), stamp(kStPart, d)));
         RET(mark(kPart));
         CK(ytk::launch_lv_plan_build(t, d, child_buf, leaf, h->st));
         h->launches += 3;
@@ -327,7 +430,7 @@ public:
     int level_hist(int d) {
         const int m = 1 << d;
         RET(zero_build_targets(m, m));
-        RET(hist_launch(m));
+        RET(hist_launch(m, d + 1));
         RET(mark(kHist));
         return YTK_OK;
     }
@@ -336,7 +439,7 @@ public:
         const int m = 1 << d;
         CK(ytk::launch_hist_subtract(t.subs, m, h->seg_max, h->st));
         h->launches++;
-        RET(scan_launch(t.scans, 2 * m, (size_t)2 * m - 1));
+        RET(scan_launch(t.scans, 2 * m, (size_t)2 * m - 1, d + 1));
         RET(mark(kSplit));
         return YTK_OK;
     }
@@ -444,23 +547,45 @@ public:
         return YTK_OK;
     }
 
+    // TimeStats (J/data/gbdt/TimeStats.java:69-78) from the kernels' own time spans on the device: histogram build,
+    // row partition, split search; everything else on the device (gradient fixed point, planners, subtraction, leaf
+    // sums, gaps) is the remainder of the tree's device time and goes to init_stats.
     int stage_times() {
-        double acc[kStages] = {0, 0, 0, 0, 0, 0};
-        for (int i = 0; i + 1 < h->ev_stage_used; i++) {
-            float ms = 0.f;
-            CK(cudaEventElapsedTime(&ms, h->ev_stage[i], h->ev_stage[i + 1]));
-            acc[marks[i + 1]] += ms;
+        const unsigned long long* st = h->eng.h_stamps;
+        double ms[kStKinds] = {0, 0, 0};
+        unsigned long long first = ~0ull, last = 0;
+        for (int k = 0; k < kStKinds; k++)
+            for (int l = 0; l < kStampLevels; l++) {
+                const unsigned long long a = ~st[2 * (k * kStampLevels + l)], b = st[2 * (k * kStampLevels + l) + 1];
+                if (b == 0 || b < a) continue;
+                ms[k] += (double)(b - a) * 1e-6;
+                first = std::min(first, a); last = std::max(last, b);
+            }
+        T->compute_hist = ms[kStHist];
+        T->gpu_hist_ms = ms[kStHist];
+        T->hist_launches = 0;
+        for (int l = 0; l < kStampLevels; l++) T->hist_launches += st[2 * (kStHist * kStampLevels + l) + 1] != 0;
+        T->partition = ms[kStPart];
+        T->find_best_split = ms[kStScan];
+        T->communicate_hist = 0; T->sync_best_split = 0;
+        if (h->world > 1 && !replayed) {                  // exchanges: CUDA events around them (queued launch by launch)
+            double comm = 0, sync = 0;
+            for (int i = 0; i + 1 < h->ev_stage_used; i++) {
+                float e = 0.f;
+                if (marks[i + 1] != kComm && marks[i + 1] != kSync) continue;
+                CK(cudaEventElapsedTime(&e, h->ev_stage[i], h->ev_stage[i + 1]));
+                (marks[i + 1] == kComm ? comm : sync) += e;
+            }
+            T->communicate_hist = comm; T->sync_best_split = sync;
         }
-        T->init_stats = acc[kInit];
-        T->compute_hist = acc[kHist];
-        T->communicate_hist = acc[kComm];
-        T->build_hist = acc[kHist] + acc[kComm];
-        T->find_best_split = acc[kSplit];
-        T->sync_best_split = acc[kSync];
-        T->partition = acc[kPart];
+        T->build_hist = T->compute_hist + T->communicate_hist;
+        const double span = last > first ? (double)(last - first) * 1e-6 : 0.0;
+        T->device_span_ms = span;
+        T->init_stats = std::max(0.0, span - ms[kStHist] - ms[kStPart] - ms[kStScan] - T->communicate_hist - T->sync_best_split);
         T->stage_times_from_gpu = 1;
         return YTK_OK;
     }
+    bool replayed = false;
 };
 
 }  // namespace
@@ -483,9 +608,10 @@ int engine_make_tree_clique(ytk_gbdt** hs, int world, int gid, const int32_t* fe
     const double t0 = now_ms();
 #define EACH(call) for (int r = 0; r < world; r++) RET(eng[r].call)
 #define XCHG(fn, d) do { EACH(fn(d, ytk::kXPush)); EACH(fn(d, ytk::kXReduce)); } while (0)
-    EACH(begin_scale(gid, fea_index, n_fea));
+    EACH(prepare(gid, fea_index, n_fea));
+    EACH(begin_scale());
     EACH(x_max(ytk::kXPush)); EACH(x_max(ytk::kXReduce));
-    for (int r = 0; r < world; r++) RET(eng[r].begin_root(gid, row_masks ? row_masks[r] : nullptr));
+    for (int r = 0; r < world; r++) RET(eng[r].begin_root(row_masks ? row_masks[r] : nullptr));
     EACH(root_hist());
     XCHG(x_hist, -1);
     EACH(root_scan());

@@ -792,13 +792,14 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
         CK(cudaEventElapsedTime(&ms, h->evc[i], h->evc[i + 1]));
         comm_ms += ms;
     }
-    T->gpu_hist_ms = gpu_ms;
+    T->hist_events_ms = gpu_ms;            // CUDA events around the histogram launches (0 when replayed from a graph)
     if (!T->stage_times_from_gpu) {
+        T->gpu_hist_ms = gpu_ms;
+        T->hist_launches = h->ev_used / 2;
         T->communicate_hist = comm_ms;     // CUDA-event time of the collectives (stream time, includes waiting for peers)
         T->compute_hist = gpu_ms;
     }
     T->kernel_launches = h->launches;
-    T->hist_launches = h->ev_used / 2;
     T->peer_collectives = h->peer_mode ? 1 : 0;
     T->total = now_ms() - t_start;
     if (ts) *ts = *T;

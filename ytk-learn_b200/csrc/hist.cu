@@ -26,8 +26,9 @@ namespace ytk {
 // A non-zero value never rounds to zero, so "bin has samples" (hasSample,
 // J/optimizer/gbdt/DataParallelTreeMaker.java:657-663) is preserved exactly.
 // ------------------------------------------------------------------------------------
-__global__ void grad_absmax_k(const float* __restrict__ gp, int64_t n, int32_t K, int32_t gid,
+__global__ void grad_absmax_k(const float* __restrict__ gp, int64_t n, int32_t K, int32_t gid, const int* __restrict__ gid_dev,
                               unsigned* __restrict__ absmax_bits) {
+    if (gid_dev) gid = *gid_dev;
     float mg = 0.f, mh = 0.f;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
          i += (int64_t)gridDim.x * blockDim.x) {
@@ -58,9 +59,10 @@ __device__ __forceinline__ int32_t to_fixed(float v, double mul) {
     return (int32_t)q;
 }
 
-__global__ void grad_quantize_k(const float* __restrict__ gp, int64_t n, int32_t K, int32_t gid,
+__global__ void grad_quantize_k(const float* __restrict__ gp, int64_t n, int32_t K, int32_t gid, const int* __restrict__ gid_dev,
                                 int2* __restrict__ gq, const unsigned* __restrict__ absmax_bits,
                                 GradScale* __restrict__ scale, int bits) {
+    if (gid_dev) gid = *gid_dev;
     int kg = scale_exponent(__uint_as_float(absmax_bits[0]), bits);
     int kh = scale_exponent(__uint_as_float(absmax_bits[1]), bits);
     double mg = ldexp(1.0, kg), mh = ldexp(1.0, kh);
@@ -280,11 +282,12 @@ hist_span_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict
             const BuildNode* __restrict__ nodes, const int* __restrict__ n_nodes_dev, int32_t F,
             const uint32_t* __restrict__ group_mask, const int32_t* __restrict__ nbins,
             const int32_t* __restrict__ feat_owner, const int64_t* __restrict__ feat_inner, long long owner_stride,
-            long long* const* __restrict__ seg_out) {
+            long long* const* __restrict__ seg_out, unsigned long long* __restrict__ stamp) {
     pdl_sync();
     extern __shared__ __align__(128) uint32_t sh[];
     const int nb = *n_nodes_dev;
     if (nb <= 0) return;
+    stamp_begin(stamp);
     const int fg = blockIdx.y;
     const long long total = nodes[nb - 1].cost_end;
     const long long c0 = total * blockIdx.x / gridDim.x, c1 = total * (blockIdx.x + 1) / gridDim.x;
@@ -318,6 +321,7 @@ hist_span_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict
             __syncthreads();
         }
     }
+    stamp_end(stamp);
 }
 
 // ------------------------------------------------------------------------------------
@@ -477,15 +481,16 @@ __global__ void copy_segments_k(const long long* __restrict__ src, long long* co
         d[i] = s[i];
 }
 
-cudaError_t launch_grad_absmax(const float* gp, int64_t n, int32_t K, int32_t gid, unsigned* absmax_bits, cudaStream_t st) {
+cudaError_t launch_grad_absmax(const float* gp, int64_t n, int32_t K, int32_t gid, unsigned* absmax_bits, cudaStream_t st,
+                               const int* gid_dev) {
     cudaError_t e = cudaMemsetAsync(absmax_bits, 0, 2 * sizeof(unsigned), st);
     if (e != cudaSuccess) return e;
-    grad_absmax_k<<<grid_for(n, 256, kNumSMs * 8), 256, 0, st>>>(gp, n, K, gid, absmax_bits);
+    grad_absmax_k<<<grid_for(n, 256, kNumSMs * 8), 256, 0, st>>>(gp, n, K, gid, gid_dev, absmax_bits);
     return cudaGetLastError();
 }
 cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t gid, int2* gq,
-                                 const unsigned* absmax_bits, GradScale* scale, int bits, cudaStream_t st) {
-    grad_quantize_k<<<grid_for(n, 256, kNumSMs * 8), 256, 0, st>>>(gp, n, K, gid, gq, absmax_bits, scale, bits);
+                                 const unsigned* absmax_bits, GradScale* scale, int bits, cudaStream_t st, const int* gid_dev) {
+    grad_quantize_k<<<grid_for(n, 256, kNumSMs * 8), 256, 0, st>>>(gp, n, K, gid, gid_dev, gq, absmax_bits, scale, bits);
     return cudaGetLastError();
 }
 
@@ -522,11 +527,11 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
 cudaError_t launch_hist_span(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1,
                              const BuildNode* nodes, const int* n_nodes_dev, int groups, int32_t F, const uint32_t* group_mask,
                              const int32_t* nbins, const int32_t* feat_owner, const int64_t* feat_inner, long long owner_stride,
-                             long long* const* seg_out, cudaStream_t st) {
+                             long long* const* seg_out, cudaStream_t st, unsigned long long* stamp) {
     const int per_group = std::max(1, kNumSMs / std::max(1, groups));
     dim3 grid((unsigned)per_group, (unsigned)groups);
     return launch_chain(hist_span_k, grid, dim3(kHistThreads), kHistSmemBytes, st, bins, S8, gq, rowidx0, rowidx1, nodes, n_nodes_dev,
-                        F, group_mask, nbins, feat_owner, feat_inner, owner_stride, seg_out);
+                        F, group_mask, nbins, feat_owner, feat_inner, owner_stride, seg_out, stamp);
 }
 
 cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide, const int2* gq, const int32_t* rowidx0,

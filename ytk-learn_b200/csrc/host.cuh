@@ -228,8 +228,17 @@ struct PinnedBuf {
 };
 
 
+// a tree's launch sequence recorded as a CUDA graph (one GPU), and what the replay must restore on the host
+struct EngineGraph {
+    unsigned long long sig = 0;
+    cudaGraphExec_t exec = nullptr;
+    std::vector<int> marks;
+    int ev_stage_used = 0, ev_used = 0, launches = 0;
+};
+
 // device tables (and pinned mirrors of what comes back) of the device-driven level loop (engine.cu)
 struct EngineBuffers {
+    std::vector<EngineGraph> graphs;
     int depth = -1;
     size_t tile_cap = 0, mirror_bytes = 0, clear_bytes = 0, heap = 0;
     char* dev = nullptr;
@@ -238,6 +247,8 @@ struct EngineBuffers {
     ytk::LvNode* h_nodes = nullptr;
     ytk_split* h_recs = nullptr;
     long long* h_leaf = nullptr;
+    unsigned long long* d_stamps = nullptr;      // {~start, end} of the tree's main kernels on the global timer
+    unsigned long long* h_stamps = nullptr;
 };
 
 }  // namespace ytkh
@@ -261,6 +272,7 @@ struct ytk_gbdt {
     bool plan_ahead = true;                 // YTK_GBDT_NO_PLAN_AHEAD=1 turns it off
     bool spin_wait = false;                 // YTK_GBDT_SPIN=1: poll the level's event from user space (measured: no gain)
     bool use_engine = true;                 // YTK_GBDT_NO_ENGINE=1: level-wise growth through the host-planned path too
+    bool use_graph = true;                  // YTK_GBDT_NO_GRAPH=1: queue every tree launch by launch
     EngineBuffers eng;
     size_t pool_chunk_slots = 0;            // histogram slots in d_pool_chunk
     std::vector<cudaEvent_t> ev_stage;      // stage boundaries of a device-driven tree
@@ -467,6 +479,7 @@ int partition_nodes(ytk_gbdt* h, const uint8_t* src, int64_t col_stride, const s
                     std::vector<ytk::PartitionCounts>& local, std::vector<ytk::PartitionCounts>& global);
 // ---- engine.cu: level-wise growth planned on the device --------------------------------------------
 bool engine_applicable(const ytk_gbdt* h);
+void engine_drop_graphs(ytk_gbdt* h);
 int engine_make_tree(ytk_gbdt* h, int gid, const int32_t* fea_index, int32_t n_fea, const uint8_t* row_mask, ytk_tree_out* out,
                      ytk_time_stats* T);
 int engine_make_tree_clique(ytk_gbdt** hs, int world, int gid, const int32_t* fea_index, int32_t n_fea,

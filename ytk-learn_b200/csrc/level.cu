@@ -58,7 +58,14 @@ lv_plan_split_k(LvTables t, int d, int buf, double min_split_loss, const int32_t
     __shared__ int s_carry;
     const int m = 1 << d, L0 = m - 1;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) { s_carry = 0; *t.ticket = 0; }
+    if (threadIdx.x == 0) {
+        s_carry = 0; *t.ticket = 0;
+        // a fresh epoch for the partition's chained-scan state; the device's epochs live in [2^29, 2^30), the host's
+        // (tables planned there) below
+        unsigned long long e = *t.epoch + 1;
+        if (e < (1ull << 29) || e >= (1ull << 30)) e = (1ull << 29) + 1;
+        *t.epoch = e;
+    }
     __syncthreads();
     for (int s0 = 0; s0 < m; s0 += kPlanThreads) {
         const int s = s0 + threadIdx.x;

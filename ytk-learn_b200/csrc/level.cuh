@@ -36,6 +36,7 @@ struct LvTables {
     int* tile_seg;                  // partition tile -> segment
     int* n_tiles;
     unsigned int* ticket;           // of the partition kernel
+    unsigned long long* epoch;      // of its chained-scan state: bumped by the planner before every partition
     PartitionCounts* counts;        // [slots] local child counts of the level's partition
     PartitionCounts* gcounts;       // [slots] global (== counts on one GPU)
     BuildNode* build;               // [slots] histogram build nodes of the level
@@ -49,6 +50,7 @@ struct LvTables {
     long long* pool;                // histogram slots, seg_max words each
     long long* staging;             // world > 1: [owner][slot][seg_max]
     long long seg_max;
+    int* gid;                       // the class whose tree is being built (read by the gradient kernels)
     long long flush_cost;           // cost of a node boundary in a span, in rows (kHistFlushCost; YTK_GBDT_FLUSH_COST)
     int world;
 };
@@ -95,7 +97,8 @@ cudaError_t launch_lv_leaf_sums(LvTables t, int d, const int2* gq, const int32_t
 cudaError_t launch_partition_fused_planned(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
                                            int32_t* rowidx1, const SplitSeg* segs, int n_segs, const int* tile_seg,
                                            const int* n_tiles_dev, int grid_bound, unsigned long long* tile_state,
-                                           unsigned int* ticket, unsigned long long epoch, PartitionCounts* counts,
-                                           cudaStream_t st, SparseRows sparse = SparseRows{nullptr, nullptr, nullptr});
+                                           unsigned int* ticket, const unsigned long long* epoch_dev, PartitionCounts* counts,
+                                           cudaStream_t st, SparseRows sparse = SparseRows{nullptr, nullptr, nullptr},
+                                           unsigned long long* stamp = nullptr);
 
 }  // namespace ytk

@@ -240,8 +240,10 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
                   int32_t* __restrict__ rowidx1, const SplitSeg* __restrict__ segs, int n_segs,
                   const int* __restrict__ tile_seg, int n_tiles, const int* __restrict__ n_tiles_dev,
                   unsigned long long* __restrict__ tile_state, unsigned int* __restrict__ ticket, unsigned long long epoch,
-                  PartitionCounts* __restrict__ counts) {
+                  PartitionCounts* __restrict__ counts, const unsigned long long* __restrict__ epoch_dev,
+                  unsigned long long* __restrict__ stamp) {
     pdl_sync();
+    if (epoch_dev) epoch = *epoch_dev;       // kept on the device (a launch recorded in a CUDA graph cannot take a new value)
     __shared__ int s_tile, s_prefix, s_found;
     __shared__ int s_warp[kFusedThreads / 32], s_lb_sum[kFusedThreads / 32], s_lb_fp[kFusedThreads / 32];
     __shared__ int32_t s_rows[kFusedTile];      // the tile, left rows first, both sides in input order
@@ -254,6 +256,7 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     __syncthreads();
     const int tile = s_tile;
     if (tile >= n_tiles) return;
+    stamp_begin(stamp);
     if (tile == 0 && !n_tiles_dev)
         for (int k = threadIdx.x; k < n_segs; k += kFusedThreads)
             if (segs[k].ntiles == 0) counts[k] = {0, 0};
@@ -385,6 +388,7 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     const long long right_last = sg.end - 1 - ((long long)j * kFusedTile - s_prefix) + tile_left;   // minus (i - tile_left) below
     for (int i = threadIdx.x; i < tile_n; i += kFusedThreads)
         out[i < tile_left ? left_base + i : right_last - i] = s_rows[i];
+    stamp_end(stamp);
 }
 
 cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
@@ -394,7 +398,8 @@ cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_s
     if (n_segs <= 0) return cudaSuccess;
     if (n_tiles <= 0) return cudaMemsetAsync(counts, 0, (size_t)n_segs * sizeof(PartitionCounts), st);
     return launch_chain(partition_fused_k, dim3(n_tiles), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
-                        rowidx0, rowidx1, segs, n_segs, tile_seg, n_tiles, (const int*)nullptr, tile_state, ticket, epoch, counts);
+                        rowidx0, rowidx1, segs, n_segs, tile_seg, n_tiles, (const int*)nullptr, tile_state, ticket, epoch, counts,
+                        (const unsigned long long*)nullptr, (unsigned long long*)nullptr);
 }
 
 // ------------------------------------------------------------------------------------
@@ -512,7 +517,7 @@ cudaError_t launch_partition_planned_root(const uint8_t* src, int32_t S8, int64_
     if (e != cudaSuccess || grid_bound <= 0) return e;
     return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
                         rowidx0, rowidx1, (const SplitSeg*)out_segs, 1, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
-                        tile_state, ticket, epoch, next_counts);
+                        tile_state, ticket, epoch, next_counts, (const unsigned long long*)nullptr, (unsigned long long*)nullptr);
 }
 
 cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
@@ -528,7 +533,7 @@ cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col
     if (e != cudaSuccess || grid_bound <= 0) return e;
     return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
                         rowidx0, rowidx1, (const SplitSeg*)out_segs, 2 * m, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
-                        tile_state, ticket, epoch, next_counts);
+                        tile_state, ticket, epoch, next_counts, (const unsigned long long*)nullptr, (unsigned long long*)nullptr);
 }
 
 // The shared-memory carve-out of the partition is left to the driver unless YTK_GBDT_PART_CARVEOUT (percent) says
@@ -543,11 +548,11 @@ cudaError_t partition_kernels_init() {
 cudaError_t launch_partition_fused_planned(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0,
                                            int32_t* rowidx1, const SplitSeg* segs, int n_segs, const int* tile_seg,
                                            const int* n_tiles_dev, int grid_bound, unsigned long long* tile_state,
-                                           unsigned int* ticket, unsigned long long epoch, PartitionCounts* counts,
-                                           cudaStream_t st, SparseRows sparse) {
+                                           unsigned int* ticket, const unsigned long long* epoch_dev, PartitionCounts* counts,
+                                           cudaStream_t st, SparseRows sparse, unsigned long long* stamp) {
     if (grid_bound <= 0) return cudaSuccess;
     return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
-                        rowidx0, rowidx1, segs, n_segs, tile_seg, 0, n_tiles_dev, tile_state, ticket, epoch, counts);
+                        rowidx0, rowidx1, segs, n_segs, tile_seg, 0, n_tiles_dev, tile_state, ticket, 0ull, counts, epoch_dev, stamp);
 }
 
 cudaError_t launch_partition(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,

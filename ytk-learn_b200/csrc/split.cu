@@ -64,7 +64,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
              int32_t f_from, int32_t f_to, int32_t first_fea, const GradScale* __restrict__ scale,
              GainParams gp, const PartitionCounts* __restrict__ cnt_global, SplitPart* __restrict__ parts,
              ytk_split* __restrict__ outs, ytk_split* __restrict__ mirror, unsigned int* __restrict__ done,
-             long long* __restrict__ lh_out) {
+             long long* __restrict__ lh_out, unsigned long long* __restrict__ stamp) {
     pdl_sync();
     __shared__ double s_tot[2];
     __shared__ long long s_toth, s_lh[kScanWarps];
@@ -76,6 +76,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
     const double ig = scale->inv_g, ih = scale->inv_h;
     const long long* __restrict__ hist = nodes[node].hist;
     if (!hist) return;                      // an unused entry of a device-planned table (the whole CTA leaves)
+    stamp_begin(stamp);
     long long sample_cnt = nodes[node].sample_cnt;
     if (nodes[node].cseg >= 0) {
         const PartitionCounts g = cnt_global[nodes[node].cseg];
@@ -196,7 +197,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
         s_last = atomicAdd(done + node, 1u) == gridDim.y - 1;
     }
     __syncthreads();
-    if (!s_last) return;
+    if (!s_last) { stamp_end(stamp); return; }
     __threadfence();
     // slices hold increasing feature ids: the maximum, ties to the lowest slice = smallest fid
     SplitPart bp = {-CUDART_INF_F, -1, -1, -1, 0, 0};
@@ -230,6 +231,7 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
         if (mirror) mirror[node] = r;      // pinned host memory on one GPU: the host reads it without a copy
         done[node] = 0;                    // ready for the next launch
     }
+    stamp_end(stamp);
 }
 
 int split_scan_slices(int32_t f_from, int32_t f_to) {
@@ -241,12 +243,12 @@ cudaError_t launch_split_scan(const ScanNode* nodes, int n_nodes, const int32_t*
                               const uint8_t* fea_selected, int32_t f_from, int32_t f_to, int32_t first_fea,
                               const GradScale* scale, GainParams gp, const PartitionCounts* cnt_global,
                               SplitPart* parts, ytk_split* out, ytk_split* mirror, unsigned int* done, cudaStream_t st,
-                              long long* lh_out) {
+                              long long* lh_out, unsigned long long* stamp) {
     if (n_nodes <= 0) return cudaSuccess;
     const int slices = split_scan_slices(f_from, f_to);
     dim3 grid((unsigned)n_nodes, (unsigned)slices);
     return launch_chain(split_scan_k, grid, dim3(kScanWarps * 32), 0, st, nodes, start, feat_off, fea_selected, f_from,
-                        f_to, first_fea, scale, gp, cnt_global, parts, out, mirror, done, lh_out);
+                        f_to, first_fea, scale, gp, cnt_global, parts, out, mirror, done, lh_out, stamp);
 }
 
 }  // namespace ytk

@@ -113,6 +113,7 @@ void free_all(ytk_gbdt* h) {
     h->h_counts.release(); h->h_split.release(); h->h_leaf.release(); h->h_scale.release(); h->arena.release();
     for (auto* it : h->pool.all) { if (it->own_buf) F(it->buf); delete it; }
     F(h->d_pool_chunk);
+    engine_drop_graphs(h);
     F(h->eng.dev);
     if (h->eng.host) cudaFreeHost(h->eng.host);
     for (auto e : h->ev_stage) cudaEventDestroy(e);
@@ -605,7 +606,7 @@ int next_partition_epoch(ytk_gbdt* h, size_t n_tiles) {
         CK(cudaMalloc(&h->d_ticket, 2 * sizeof(unsigned int)));
         CK(cudaMemsetAsync(h->d_ticket, 0, 2 * sizeof(unsigned int), h->st));
     }
-    if (++h->part_epoch >= (1ull << 30)) {       // entries of other epochs read as "not written yet"
+    if (++h->part_epoch >= (1ull << 29)) {     // (epochs from 2^29 on belong to the device-planned level loop)       // entries of other epochs read as "not written yet"
         CK(cudaMemsetAsync(h->d_tile_state, 0, h->tile_state_cap * sizeof(unsigned long long), h->st));
         h->part_epoch = 1;
     }
@@ -780,6 +781,7 @@ int ytk_gbdt_create(const ytk_gbdt_params* params, int32_t device, int32_t rank,
     if (const char* s = getenv("YTK_GBDT_NO_PLAN_AHEAD")) h->plan_ahead = atoi(s) == 0;
     if (const char* s = getenv("YTK_GBDT_SPIN")) h->spin_wait = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_NO_ENGINE")) h->use_engine = atoi(s) == 0;
+    if (const char* s = getenv("YTK_GBDT_NO_GRAPH")) h->use_graph = atoi(s) == 0;
     if (const char* s = getenv("YTK_GBDT_TRACE")) h->trace = atoi(s) != 0;
     if (const char* s = getenv("YTK_GBDT_LOOKAHEAD")) h->lookahead = std::max(1, std::min(1024, atoi(s)));
     auto bail = [&](int code) { free_all(h); delete h; return code; };
