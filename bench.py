@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--no-loss-wise", action="store_true", help="skip the extra loss-wise 255-leaf measurement")
     ap.add_argument("--no-parity-check", action="store_true", help="skip the self-check after the timed region")
     ap.add_argument("--no-other-configs", action="store_true", help="skip BASELINE configs[2..4] (other_configs)")
+    ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the strong-scaling extra (strong_11M)")
     ap.add_argument("--c3-rows", type=int, default=12_500_000, help="rows per GPU of configs[2]")
     ap.add_argument("--c5-rows", type=int, default=20_000_000, help="rows per GPU of configs[4]")
     ap.add_argument("--c4-rows", type=int, default=6_250_000, help="rows per GPU of configs[3]")
@@ -133,12 +134,18 @@ def measured_peak():
 
 
 def ncu_traffic():
-    """DRAM bytes per hist_build_k launch from the committed ncu capture (tools/summarize_ncu.py)."""
+    """DRAM bytes per histogram-build launch from the committed ncu launch list (tools/summarize_ncu.py) -- reported
+    only while the kernels' source is byte for byte what was profiled (the summary records its hash); else null."""
     path = os.path.join(ROOT, "profiles", "hist_build_ncu.json")
     try:
-        return float(json.load(open(path))["dram_bytes_per_launch"])
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import summarize_ncu
+        d = json.load(open(path))
+        if d.get("kernel_source_sha256_16") != summarize_ncu.kernel_source_hash():
+            return None, "profiles/hist_build_ncu.json was taken from an older build of the kernel: not reported"
+        return float(d["dram_bytes_per_launch"]), "ncu launch list %s (commit %s), same kernel source" % (d.get("source"), d.get("summarised_at_commit"))
     except Exception:
-        return None
+        return None, "no capture"
 
 
 def cpu_baseline(a, xs, ys, steps=1, threads=None):
@@ -408,6 +415,28 @@ def other_configs(a, yb, torch, dist, world, rank, local, fresh_nccl_id, barrier
     return out
 
 
+def collectives_info(a, world, agg, B):
+    """What crosses NVLink per tree and how fast (north_star: the reduce-scatter as a fraction of the NVLink
+    roofline).  Every built node's histogram is reduce-scattered by feature range: a rank pulls its 1/N of the
+    16*B bytes from each of the other N-1 ranks.  The time is the stream time of the exchange kernels, which
+    includes waiting for the slowest rank to arrive -- at this shape the exchanges are latency-, not wire-bound."""
+    if world == 1:
+        return {"rendezvous_per_tree": 0, "note": "one GPU: no exchange"}
+    steps = max(1, a.steps)
+    pulled = agg["built"] / steps * 16.0 * B * (world - 1) / world
+    ms = agg["ts_comm"] / steps
+    ach = pulled / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+    return {"rendezvous_per_tree": agg.get("rendezvous", 0),
+            "exchange_ms_per_tree": ms, "split_record_merge_ms_per_tree": agg["ts_sync"] / steps,
+            "hist_reduce_scatter": {"bytes_pulled_per_gpu_per_tree": pulled, "achieved_gbs_per_gpu": ach,
+                                    "peak_gbs_per_direction": 770.0, "nominal_gbs_per_direction": 900.0,
+                                    "frac_of_measured_peer_copy": ach / 770.0,
+                                    "peak_source": "B200_PROFILING.md: measured peer copy 770 GB/s per direction (nominal 900)"},
+            "note": "latency-bound: %.0f KB per GPU and level at this shape (0.1 us of wire time); the time is "
+                    "arrival skew between the ranks at %d rendezvous per tree" % (16.0 * B * (world - 1) / world / 1e3,
+                                                                                  agg.get("rendezvous", 0))}
+
+
 def config(a, world):
     return {"workload": "higgs-shape synthetic: %d rows/GPU x %d features, %d bins, %s-wise depth %d%s"
                         % (a.rows, a.features, a.bins, a.policy, a.depth,
@@ -440,6 +469,32 @@ def run_reference(a):
     print(json.dumps(line))
 
 
+def bind_to_gpu_cpus(gpu):
+    """Pin this rank to the CPU cores next to its GPU (`nvidia-smi topo -m`, column "CPU Affinity") BEFORE the pinned
+    gradient buffer is allocated and first touched, so that the pages of the 88 MB the rank copies every step sit on
+    the GPU's own NUMA node.  Returns what was done, for the JSON line."""
+    try:
+        out = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout
+        lines = [l for l in out.splitlines() if l.strip()]
+        hdr = next(l for l in lines if "CPU Affinity" in l)
+        cols = [c.strip() for c in hdr.split("\t")]
+        idx = cols.index("CPU Affinity")
+        row = next(l for l in lines if l.startswith("GPU%d\t" % gpu) or l.startswith("GPU%d " % gpu))
+        cells = [c.strip() for c in row.split("\t")]
+        spec = cells[idx]
+        cpus = set()
+        for part in spec.split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return "nvidia-smi names cores outside this process's set (%s): unchanged" % spec
+        os.sched_setaffinity(0, cpus)
+        return "cores %s" % spec
+    except Exception as e:          # no topology information: nothing is changed
+        return "unchanged (%s)" % type(e).__name__
+
+
 def main():
     a = parse()
     if a.impl == "reference":
@@ -456,6 +511,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    cpu_binding = bind_to_gpu_cpus(local)
     def fresh_nccl_id():
         """One NCCL unique id per tree-maker clique, made on rank 0 and handed round by the host."""
         if world == 1:
@@ -521,6 +577,7 @@ def main():
             agg["ts_part"] += ts.partition; agg["ts_total"] += ts.total; agg["ts_comm"] += ts.communicate_hist
             agg["ts_init"] += ts.init_stats; agg["ts_sync"] += ts.sync_best_split
             agg["ts_enq"] += ts.enqueue_ms; agg["ts_wait"] += ts.host_wait_ms; agg["ts_gpu"] = ts.stage_times_from_gpu
+            agg["rendezvous"] = ts.rendezvous; agg["graph"] = ts.graph_replayed
             agg["d2h"] = sum(getattr(tree, nme).nbytes for nme, _ in yb.Tree.FIELDS)
             last_tree = tree
     barrier()
@@ -564,6 +621,30 @@ def main():
         loss_wise = {"ms_per_tree": t_lw / a.steps * 1e3, "nodes_per_tree": int(tree.n_nodes),
                      "host_waits_per_tree": tm.last_stats.batches + 1,
                      "what": "loss-wise growth, 255 leaves (the reference's experiment/higgs conf), same rows"}
+
+    # For information at N > 1: the same 11 M rows split over the N GPUs (strong scaling: the latency floor of a level)
+    strong = None
+    if world > 1 and not a.no_strong:
+        tm.close()
+        ns = a.rows // world
+        xs2, ys2 = synth_bins(ns, F, a.bins, 777 + rank, a.uniform_bins)
+        tm = yb.GpuTreeMaker(params, start, ns, device=local, rank=rank, world=world, nccl_id=fresh_nccl_id())
+        tm.upload_rows_u8(xs2)
+        g2 = np.empty(2 * ns, np.float32)
+        sigmoid_grads(np.zeros(ns, np.float32), ys2, g2)
+        tm.set_grads(g2)
+        t_s = 0.0
+        for step in range(3 + a.steps):
+            barrier()
+            t0 = time.perf_counter()
+            tm.make(0)
+            if step >= 3:
+                t_s += time.perf_counter() - t0
+        barrier()
+        v = torch.tensor([t_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(v, op=dist.ReduceOp.MAX)
+        strong = {"rows_total": ns * world, "rows_per_gpu": ns, "ms_per_tree": float(v.item()) / a.steps * 1e3,
+                  "what": "the headline workload's row count split over the %d GPUs (strong scaling), gradients resident" % world}
 
     pc = None
     if not a.no_parity_check:
@@ -610,8 +691,12 @@ def main():
                                        "host_waits": host_waits, "device_allocs_in_timed_steps": agg.get("allocs", 0),
                                        "longest_batch_ms": agg.get("max_batch", 0.0),
                                        "ms_of_each_step": agg.get("slow_steps", [])},
-            "roofline": {"bound": "hbm", "kernel": "hist_build_k", "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
+            "roofline": {"bound": "hbm", "kernel": "hist_span_k" if agg["ts_gpu"] else "hist_build_k", "achieved": ach, "peak": peak,
+                         "unit": "GB/s", "frac": ach / peak, "traffic": ncu_traffic()[0], "traffic_source": ncu_traffic()[1],
+                         "peak_source": peak_src,
+                         "kernel_time_source": ("the kernels' own span on the GPU's global timer (launches replayed from a CUDA "
+                                                "graph cannot be bracketed by CUDA events; tests check the two agree)"
+                                                if agg["ts_gpu"] else "CUDA events on the library's stream"),
                          "algorithmic_bytes_per_launch": alg / max(1, agg["hist_launches"]),
                          "kernel_us_per_launch": agg["gpu_hist_ms"] * 1e3 / max(1, agg["hist_launches"]),
                          "algorithmic_bytes_per_step": alg / a.steps,
@@ -619,6 +704,10 @@ def main():
                          "kernel_share_of_step": agg["gpu_hist_ms"] * 1e-3 / t_tree,
                          "launches_per_step": agg["hist_launches"] / a.steps,
                          "nodes_built_per_step": agg["built"] / a.steps},
+            "collectives": collectives_info(a, world, agg, int(start[-1])),
+            "strong_11M": strong,
+            "cuda_graph_replay": bool(agg.get("graph", 0)),
+            "cpu_binding": cpu_binding,
             "clocks": clocks,
             "parity_check": pc,
             "other_configs": oc,

@@ -99,6 +99,8 @@ typedef struct {
     double  device_span_ms;   /* device-driven level loop: first kernel start to last kernel end on the GPU's timer */
     double  hist_events_ms;   /* CUDA-event time around the histogram launches when they were queued directly (0 in a replay):
                                  gpu_hist_ms is then the kernels' own span on the GPU's timer, and the two agree */
+    int32_t rendezvous;       /* world > 1: exchanges between the GPUs in this tree (each waits for the slowest rank) */
+    int32_t reserved;
 } ytk_time_stats;
 
 /* One best split: SplitInfo (J/data/gbdt/SplitInfo.java:36-70) plus the node totals the

@@ -5,9 +5,22 @@
 Writes profiles/hist_build_ncu.json (per-launch DRAM traffic used by bench.py's roofline.traffic)."""
 import collections
 import csv
+import hashlib
 import json
 import os
+import subprocess
 import sys
+
+ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
+HIST_KERNELS = ("hist_span_k", "hist_build_k")          # device-planned level loop / host-planned path
+
+
+def kernel_source_hash():
+    """what bench.py compares before it reports the capture's DRAM traffic: the histogram kernels' source"""
+    h = hashlib.sha256()
+    for f in ("hist.cu", "common.cuh", "device_util.cuh"):
+        h.update(open(os.path.join(ROOT, "ytk-learn_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
 
 
 def to_us(v, u):
@@ -32,7 +45,7 @@ def main():
         wr = to_mb(*d.get("dram__bytes_write.sum", (0, "byte")))
         a = agg.setdefault(name, [0, 0.0, 0.0, 0.0])
         a[0] += 1; a[1] += us; a[2] += rd; a[3] += wr
-        if name == "hist_build_k":
+        if name in HIST_KERNELS:
             hist.append({"id": i, "grid": grid, "us": us, "dram_read_mb": rd, "dram_write_mb": wr})
     tot = sum(a[1] for a in agg.values())
     print("kernel                      launches   total us   share   DRAM read MB  write MB   GB/s")
@@ -47,16 +60,22 @@ def main():
     # kernels launched inside ytk_gbdt_make_tree (the timed step); the rest of a bench.py run is the one-off
     # row upload, get_positions and the device-gradient rounds
     in_make = ("hist_", "csr_default_fix_k", "partition_", "plan_", "split_", "leaf_sums_k", "zero_segments_k",
-               "grad_absmax_k", "grad_quantize_k", "copy_segments_k", "peer_")
+               "grad_absmax_k", "grad_quantize_k", "copy_segments_k", "peer_", "lv_")
     make_tot = sum(a[1] for n, a in agg.items() if n.startswith(in_make))
-    print("kernels of make(): %.1f us; hist_build_k share of them: %.3f" % (make_tot, agg.get("hist_build_k", [0, 0])[1] / make_tot if make_tot else 0))
+    hist_us = sum(agg.get(k, [0, 0])[1] for k in HIST_KERNELS)
+    print("kernels of make(): %.1f us; histogram-build share of them: %.3f" % (make_tot, hist_us / make_tot if make_tot else 0))
     if hist:
-        out = {"kernel": "hist_build_k", "launches": len(hist),
-               "share_of_make_kernel_time": agg["hist_build_k"][1] / make_tot,
+        try:
+            commit = subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+        except Exception:
+            commit = ""
+        out = {"kernel": "+".join(k for k in HIST_KERNELS if k in agg), "launches": len(hist),
+               "share_of_make_kernel_time": hist_us / make_tot,
                "dram_bytes_per_launch": sum(h["dram_read_mb"] + h["dram_write_mb"] for h in hist) / len(hist) * 1e6,
                "us_per_launch_under_ncu": sum(h["us"] for h in hist) / len(hist),
-               "share_of_all_kernel_time_in_the_run": agg["hist_build_k"][1] / tot, "source": os.path.basename(sys.argv[1])}
-        json.dump(out, open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "profiles", "hist_build_ncu.json"), "w"), indent=1)
+               "share_of_all_kernel_time_in_the_run": hist_us / tot, "source": os.path.basename(sys.argv[1]),
+               "kernel_source_sha256_16": kernel_source_hash(), "summarised_at_commit": commit}
+        json.dump(out, open(os.path.join(ROOT, "profiles", "hist_build_ncu.json"), "w"), indent=1)
     if len(sys.argv) > 2:
         rows = list(csv.reader(open(sys.argv[2])))
         hdr = rows[0]

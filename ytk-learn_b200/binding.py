@@ -44,7 +44,7 @@ class TimeStats(C.Structure):
                 ("gpu_hist_ms", C.c_double),
                 ("kernel_launches", C.c_int32), ("hist_launches", C.c_int32), ("peer_collectives", C.c_int32), ("batches", C.c_int32), ("device_allocs", C.c_int32), ("max_batch_ms", C.c_double),
                 ("enqueue_ms", C.c_double), ("host_wait_ms", C.c_double), ("stage_times_from_gpu", C.c_int32),
-                ("graph_replayed", C.c_int32), ("device_span_ms", C.c_double), ("hist_events_ms", C.c_double)]
+                ("graph_replayed", C.c_int32), ("device_span_ms", C.c_double), ("hist_events_ms", C.c_double), ("rendezvous", C.c_int32), ("reserved", C.c_int32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

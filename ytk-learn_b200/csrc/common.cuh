@@ -217,7 +217,7 @@ cudaError_t launch_copy_segments(const long long* src, long long* const* dst, in
 
 // ---- collectives over NVLink peer memory (peer.cu) ----
 constexpr int kMaxPeers = 64;
-constexpr int kPeerFlagSets = 4;                   // counts, histogram staging, split records, leaf sums
+constexpr int kPeerFlagSets = 8;                   // host-planned path: counts, histogram staging, split records, leaf sums; 4..7: the same for the device-planned level loop
 constexpr size_t kPeerFlagBytes = kPeerFlagSets * kMaxPeers * 8;
 struct PeerTable {
     int rank, world;

@@ -18,7 +18,7 @@ size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 
 // kernels of a tree that report their own time span (device_util.cuh): stamp slot = kind * kStampLevels + level
 constexpr int kStampLevels = 20;
-enum StampKind { kStHist = 0, kStPart = 1, kStScan = 2, kStKinds = 3 };
+enum StampKind { kStHist = 0, kStPart = 1, kStScan = 2, kStComm = 3, kStSync = 4, kStKinds = 5 };
 constexpr int kMaxStamps = kStKinds * kStampLevels;
 
 // buffer the rows of level d live in: the root's (-1 identity / 0 after a row mask), then alternating
@@ -101,6 +101,11 @@ static int engine_reserve(ytk_gbdt* h, int D) {
     t.lh_local = reinterpret_cast<long long*>(e.dev + o_lh_local);
     t.epoch = reinterpret_cast<unsigned long long*>(e.dev + o_epoch);
     t.gid = reinterpret_cast<int*>(e.dev + o_gid);
+    // the exchange epochs outlive these tables: the peers' flags keep counting
+    if (!h->d_xctr) {
+        CK(cudaMalloc(&h->d_xctr, 8 * 2 * sizeof(unsigned long long)));
+        CK(cudaMemsetAsync(h->d_xctr, 0, 8 * 2 * sizeof(unsigned long long), h->st));
+    }
     e.h_nodes = reinterpret_cast<ytk::LvNode*>(e.host + o_nodes);
     e.h_recs = reinterpret_cast<ytk_split*>(e.host + o_recs);
     e.h_leaf = reinterpret_cast<long long*>(e.host + o_leaf);
@@ -125,7 +130,7 @@ public:
         // class index live on the device): it is recorded once as a CUDA graph and replayed, which takes the
         // per-launch gaps out of the ~60 short kernels of a tree.  (Not with a row mask: its table upload is per tree.)
         bool launched = false;
-        if (h->use_graph && h->world == 1 && !row_mask) {
+        if (h->use_graph && (h->world == 1 || h->peer_mode) && !row_mask) {
             const unsigned long long sig = signature();
             EngineGraph* g = nullptr;
             for (auto& c : h->eng.graphs) if (c.sig == sig) g = &c;
@@ -134,6 +139,7 @@ public:
                 CK(cudaGraphLaunch(g->exec, h->st));
                 marks = g->marks;
                 h->ev_stage_used = g->ev_stage_used; h->ev_used = g->ev_used; h->launches += g->launches;
+                T->rendezvous = g->rendezvous;
                 root_buf = -1;
                 launched = true;
                 replayed = true;
@@ -184,6 +190,8 @@ public:
         mix((unsigned long long)(uintptr_t)h->h_scale.h); mix((unsigned long long)(uintptr_t)h->d_gq);
         mix((unsigned long long)(first_owned + 7)); mix((unsigned long long)D); mix((unsigned long long)h->N);
         mix((unsigned long long)t.flush_cost);
+        mix((unsigned long long)h->world);
+        for (int r = 0; r < h->world && h->world > 1; r++) { mix((unsigned long long)(uintptr_t)h->pt.xchg[r]); mix((unsigned long long)(uintptr_t)h->pt.hist[r]); }
         return v;
     }
 
@@ -192,6 +200,7 @@ public:
         cudaGraph_t graph = nullptr;
         const int launches_before = h->launches;
         h->ev_used = 0;
+        T->rendezvous = 0;
         if (cudaStreamBeginCapture(h->st, cudaStreamCaptureModeRelaxed) != cudaSuccess) { cudaGetLastError(); h->use_graph = false; return YTK_OK; }
         capturing = true;
         const int rc = enqueue_tree(nullptr);
@@ -212,6 +221,7 @@ public:
         EngineGraph g;
         g.sig = sig; g.exec = exec; g.marks = marks; g.ev_stage_used = h->ev_stage_used; g.ev_used = h->ev_used;
         g.launches = h->launches - launches_before;
+        g.rendezvous = T->rendezvous;
         h->launches = launches_before;
         h->eng.graphs.push_back(g);
         *out = &h->eng.graphs.back();
@@ -324,33 +334,33 @@ public:
 
     // ---- exchanges (world > 1) ------------------------------------------------------------------------------
     int x_max(int phase) {
-        if (phase != ytk::kXReduce) ++h->epoch[0];
-        CK(ytk::launch_lv_xmax(h->pt, h->d_absmax, h->off_max, h->slot_max, 0, h->epoch[0], phase, h->d_peer_err, h->st));
+        if (phase != ytk::kXReduce) T->rendezvous++;
+        CK(ytk::launch_lv_xmax(h->pt, h->d_absmax, h->off_max, h->slot_max, 4, h->d_xctr + 0, phase, h->d_peer_err, h->st));
         h->launches++;
         return YTK_OK;
     }
     int x_hist(int d, int phase) {
-        if (phase != ytk::kXReduce) ++h->epoch[1];
-        CK(ytk::launch_lv_xhist(h->pt, t, d, d < 0 ? 1 : (1 << d), h->off_counts, h->slot_counts, 1, h->epoch[1], phase,
-                                h->d_peer_err, h->st));
+        if (phase != ytk::kXReduce) T->rendezvous++;
+        CK(ytk::launch_lv_xhist(h->pt, t, d, d < 0 ? 1 : (1 << d), h->off_counts, h->slot_counts, 5, h->d_xctr + 2, phase,
+                                h->d_peer_err, h->st, phase == ytk::kXPush ? nullptr : stamp(kStComm, d + 1)));
         h->launches++;
         if (phase != ytk::kXPush) RET(mark(kComm));
         return YTK_OK;
     }
     int x_recs(int d, int phase) {
-        if (phase != ytk::kXReduce) ++h->epoch[2];
+        if (phase != ytk::kXReduce) T->rendezvous++;
         const int n = d < 0 ? 1 : (2 << d);
         const long long first = d < 0 ? 0 : (2ll << d) - 1;
-        CK(ytk::launch_lv_xrecs(h->pt, t, n, first, h->off_recs, h->slot_recs, h->off_lh, h->slot_lh, 2, h->epoch[2], phase,
-                                h->d_peer_err, h->st));
+        CK(ytk::launch_lv_xrecs(h->pt, t, n, first, h->off_recs, h->slot_recs, h->off_lh, h->slot_lh, 6, h->d_xctr + 4, phase,
+                                h->d_peer_err, h->st, phase == ytk::kXPush ? nullptr : stamp(kStSync, d + 1)));
         h->launches++;
         if (phase != ytk::kXPush) RET(mark(kSync));
         return YTK_OK;
     }
     int x_leaf(int d, int phase) {
-        if (phase != ytk::kXReduce) ++h->epoch[3];
-        CK(ytk::launch_lv_xleaf(h->pt, t, d, h->off_leaf, h->slot_leaf, h->off_counts, h->slot_counts, 3, h->epoch[3], phase,
-                                h->d_peer_err, h->st));
+        if (phase != ytk::kXReduce) T->rendezvous++;
+        CK(ytk::launch_lv_xleaf(h->pt, t, d, h->off_leaf, h->slot_leaf, h->off_counts, h->slot_counts, 7, h->d_xctr + 6, phase,
+                                h->d_peer_err, h->st, phase == ytk::kXPush ? nullptr : stamp(kStComm, kStampLevels - 1)));
         h->launches++;
         if (phase != ytk::kXPush) RET(mark(kComm));
         return YTK_OK;
@@ -552,7 +562,7 @@ public:
     // sums, gaps) is the remainder of the tree's device time and goes to init_stats.
     int stage_times() {
         const unsigned long long* st = h->eng.h_stamps;
-        double ms[kStKinds] = {0, 0, 0};
+        double ms[kStKinds] = {0, 0, 0, 0, 0};
         unsigned long long first = ~0ull, last = 0;
         for (int k = 0; k < kStKinds; k++)
             for (int l = 0; l < kStampLevels; l++) {
@@ -567,17 +577,8 @@ public:
         for (int l = 0; l < kStampLevels; l++) T->hist_launches += st[2 * (kStHist * kStampLevels + l) + 1] != 0;
         T->partition = ms[kStPart];
         T->find_best_split = ms[kStScan];
-        T->communicate_hist = 0; T->sync_best_split = 0;
-        if (h->world > 1 && !replayed) {                  // exchanges: CUDA events around them (queued launch by launch)
-            double comm = 0, sync = 0;
-            for (int i = 0; i + 1 < h->ev_stage_used; i++) {
-                float e = 0.f;
-                if (marks[i + 1] != kComm && marks[i + 1] != kSync) continue;
-                CK(cudaEventElapsedTime(&e, h->ev_stage[i], h->ev_stage[i + 1]));
-                (marks[i + 1] == kComm ? comm : sync) += e;
-            }
-            T->communicate_hist = comm; T->sync_best_split = sync;
-        }
+        T->communicate_hist = ms[kStComm];      // exchange kernels: includes waiting for the slowest rank to arrive
+        T->sync_best_split = ms[kStSync];
         T->build_hist = T->compute_hist + T->communicate_hist;
         const double span = last > first ? (double)(last - first) * 1e-6 : 0.0;
         T->device_span_ms = span;

@@ -796,6 +796,7 @@ int ytk_gbdt_make_tree(ytk_gbdt* h, int32_t gid, const int32_t* fea_index, int32
     if (!T->stage_times_from_gpu) {
         T->gpu_hist_ms = gpu_ms;
         T->hist_launches = h->ev_used / 2;
+        T->rendezvous = h->evc_used / 2;
         T->communicate_hist = comm_ms;     // CUDA-event time of the collectives (stream time, includes waiting for peers)
         T->compute_hist = gpu_ms;
     }

@@ -233,7 +233,7 @@ struct EngineGraph {
     unsigned long long sig = 0;
     cudaGraphExec_t exec = nullptr;
     std::vector<int> marks;
-    int ev_stage_used = 0, ev_used = 0, launches = 0;
+    int ev_stage_used = 0, ev_used = 0, launches = 0, rendezvous = 0;
 };
 
 // device tables (and pinned mirrors of what comes back) of the device-driven level loop (engine.cu)
@@ -371,6 +371,7 @@ struct ytk_gbdt {
     bool clique_linked = false;
     ytk_gbdt** clique_members = nullptr;     // [world], owned by rank 0
     unsigned long long epoch[ytk::kPeerFlagSets] = {0, 0, 0, 0};
+    unsigned long long* d_xctr = nullptr;    // device-planned level loop: epoch counters of its exchange kinds, {last epoch, scratch} x 4
     int* d_peer_err = nullptr;               // mapped host memory: set by a peer kernel that gave up waiting
     double peer_timeout_ms = 10000.0;        // YTK_GBDT_PEER_TIMEOUT_MS
 

@@ -61,18 +61,22 @@ struct LvTables {
 // kXPush for every rank, then kXReduce for every rank, and needs no flags.
 constexpr int kXPush = 1, kXWait = 2, kXReduce = 4, kXAll = 7;
 // largest |g|, |h| of all ranks (float bits): absmax[2] in place
+// `xctr`: the exchange kind's epoch counter in device memory ([0] the last completed epoch, [1] scratch): every
+// rank runs the same sequence of exchanges, so the counters agree, and a launch recorded in a CUDA graph needs no
+// new argument per tree.
 cudaError_t launch_lv_xmax(const PeerTable& pt, unsigned* absmax, size_t area_off, size_t slot_bytes, int flag_set,
-                           unsigned long long epoch, int phase, int* err, cudaStream_t st);
+                           unsigned long long* xctr, int phase, int* err, cudaStream_t st);
 // histogram reduce-scatter of the `m` slots of a level (m = 1, d = -1: the root) + the global child counts
 cudaError_t launch_lv_xhist(const PeerTable& pt, LvTables t, int d, int m, size_t area_off, size_t slot_bytes, int flag_set,
-                            unsigned long long epoch, int phase, int* err, cudaStream_t st);
+                            unsigned long long* xctr, int phase, int* err, cudaStream_t st, unsigned long long* stamp = nullptr);
 // split records of `n` searched nodes whose first heap node is `first_heap`: all-gather + needReplace / MAX merge
 cudaError_t launch_lv_xrecs(const PeerTable& pt, LvTables t, int n, long long first_heap, size_t area_off, size_t slot_bytes,
-                            size_t lh_off, size_t lh_slot_bytes, int flag_set, unsigned long long epoch, int phase, int* err,
-                            cudaStream_t st);
+                            size_t lh_off, size_t lh_slot_bytes, int flag_set, unsigned long long* xctr, int phase, int* err,
+                            cudaStream_t st, unsigned long long* stamp = nullptr);
 // leaf sums of the 2m children of the last level (summed over ranks, in place) + the global child counts
 cudaError_t launch_lv_xleaf(const PeerTable& pt, LvTables t, int d, size_t area_off, size_t slot_bytes, size_t cnt_off,
-                            size_t cnt_slot_bytes, int flag_set, unsigned long long epoch, int phase, int* err, cudaStream_t st);
+                            size_t cnt_slot_bytes, int flag_set, unsigned long long* xctr, int phase, int* err, cudaStream_t st,
+                            unsigned long long* stamp = nullptr);
 
 // global child counts of split slot s of level d (d = -1: the root's own row count, in gc.left) into the nodes
 __device__ __forceinline__ void lv_apply_gcounts(const LvTables& t, int d, int s, PartitionCounts gc) {

@@ -163,9 +163,15 @@ __device__ __forceinline__ void lv_raise(const PeerTable& pt, int flag_set, unsi
     }
 }
 
+// this exchange's epoch: one more than the kind's last completed one
+__device__ __forceinline__ unsigned long long lv_epoch(const unsigned long long* xctr) {
+    return *reinterpret_cast<const volatile unsigned long long*>(xctr) + 1;
+}
+
 __global__ void lv_xmax_k(PeerTable pt, unsigned* __restrict__ absmax, size_t area_off, size_t slot_bytes, int flag_set,
-                          unsigned long long epoch, int phase, int* err) {
+                          unsigned long long* xctr, int phase, int* err) {
     __shared__ unsigned long long s_v;
+    const unsigned long long epoch = lv_epoch(xctr);
     if (phase & kXPush) {
         if (threadIdx.x == 0) s_v = (unsigned long long)absmax[0] | ((unsigned long long)absmax[1] << 32);
         __syncthreads();
@@ -182,6 +188,8 @@ __global__ void lv_xmax_k(PeerTable pt, unsigned* __restrict__ absmax, size_t ar
         }
         absmax[0] = g; absmax[1] = h;
     }
+    __syncthreads();
+    if ((phase & kXReduce) && threadIdx.x == 0) xctr[0] = epoch;
 }
 
 // grid (chunks, m).  Raises "my staging buffer is complete" (the histogram kernel ahead in the stream has
@@ -189,8 +197,23 @@ __global__ void lv_xmax_k(PeerTable pt, unsigned* __restrict__ absmax, size_t ar
 // straight out of all staging buffers into the slot's histogram.  Block (0,0) also exchanges the child
 // counts of the level's partition (d < 0: the root's row count).
 __global__ void lv_xhist_k(PeerTable pt, LvTables t, int d, int m, size_t area_off, size_t slot_bytes, int flag_set,
-                           unsigned long long epoch, int phase, int* err) {
+                           unsigned long long* xctr, int phase, int* err, unsigned long long* stamp) {
     const bool lead = blockIdx.x == 0 && blockIdx.y == 0;
+    const unsigned long long epoch = lv_epoch(xctr);
+    stamp_begin(stamp);
+    struct Done {      // the last block to leave completes the epoch
+        unsigned long long* xctr; unsigned long long epoch; int phase; unsigned long long* stamp;
+        __device__ ~Done() {
+            stamp_end(stamp);
+            if (!(phase & kXReduce)) return;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                __threadfence();
+                unsigned int* done = reinterpret_cast<unsigned int*>(xctr + 1);
+                if (atomicAdd(done, 1u) == gridDim.x * gridDim.y - 1) { *done = 0; xctr[0] = epoch; }
+            }
+        }
+    } on_exit{xctr, epoch, phase, stamp};
     if ((phase & kXPush) && lead) {
         lv_push_words(pt, reinterpret_cast<const unsigned long long*>(t.counts), area_off, slot_bytes, 2 * (size_t)m);
         if (phase & kXWait) lv_raise(pt, flag_set, epoch);
@@ -231,7 +254,18 @@ __global__ void lv_xhist_k(PeerTable pt, LvTables t, int d, int m, size_t area_o
 // as every rank's host would (ytk_gbdt_merge_splits: needReplace in rank order, element-wise MAX of the node
 // totals, DataParallelTreeMaker.java:560,640-653) into the heap arrays.
 __global__ void lv_xrecs_k(PeerTable pt, LvTables t, int n, long long first_heap, size_t area_off, size_t slot_bytes, size_t lh_off,
-                           size_t lh_slot_bytes, int flag_set, unsigned long long epoch, int phase, int* err) {
+                           size_t lh_slot_bytes, int flag_set, unsigned long long* xctr, int phase, int* err,
+                           unsigned long long* stamp) {
+    const unsigned long long epoch = lv_epoch(xctr);
+    stamp_begin(stamp);
+    struct Done {
+        unsigned long long* xctr; unsigned long long epoch; int phase; unsigned long long* stamp;
+        __device__ ~Done() {
+            stamp_end(stamp);
+            __syncthreads();
+            if ((phase & kXReduce) && threadIdx.x == 0) xctr[0] = epoch;
+        }
+    } on_exit{xctr, epoch, phase, stamp};
     if (phase & kXPush) {
         lv_push_words(pt, reinterpret_cast<const unsigned long long*>(t.recs_local), area_off, slot_bytes,
                       (size_t)n * sizeof(ytk_split) / 8);
@@ -273,7 +307,17 @@ __global__ void lv_xrecs_k(PeerTable pt, LvTables t, int n, long long first_heap
 // One CTA.  allreduceArray(double[2], SUM) of computeLeafStats (:375) for the 2m children of the last
 // level, exact in the integer domain, and the global child counts of the level's partition.
 __global__ void lv_xleaf_k(PeerTable pt, LvTables t, int d, size_t area_off, size_t slot_bytes, size_t cnt_off, size_t cnt_slot_bytes,
-                           int flag_set, unsigned long long epoch, int phase, int* err) {
+                           int flag_set, unsigned long long* xctr, int phase, int* err, unsigned long long* stamp) {
+    const unsigned long long epoch = lv_epoch(xctr);
+    stamp_begin(stamp);
+    struct Done {
+        unsigned long long* xctr; unsigned long long epoch; int phase; unsigned long long* stamp;
+        __device__ ~Done() {
+            stamp_end(stamp);
+            __syncthreads();
+            if ((phase & kXReduce) && threadIdx.x == 0) xctr[0] = epoch;
+        }
+    } on_exit{xctr, epoch, phase, stamp};
     const int m = 1 << d;
     const long long C0 = 2ll * m - 1;
     if (phase & kXPush) {
@@ -305,26 +349,27 @@ __global__ void lv_xleaf_k(PeerTable pt, LvTables t, int d, size_t area_off, siz
 }
 
 cudaError_t launch_lv_xmax(const PeerTable& pt, unsigned* absmax, size_t area_off, size_t slot_bytes, int flag_set,
-                           unsigned long long epoch, int phase, int* err, cudaStream_t st) {
-    lv_xmax_k<<<1, 64, 0, st>>>(pt, absmax, area_off, slot_bytes, flag_set, epoch, phase, err);
+                           unsigned long long* xctr, int phase, int* err, cudaStream_t st) {
+    lv_xmax_k<<<1, 64, 0, st>>>(pt, absmax, area_off, slot_bytes, flag_set, xctr, phase, err);
     return cudaGetLastError();
 }
 cudaError_t launch_lv_xhist(const PeerTable& pt, LvTables t, int d, int m, size_t area_off, size_t slot_bytes, int flag_set,
-                            unsigned long long epoch, int phase, int* err, cudaStream_t st) {
+                            unsigned long long* xctr, int phase, int* err, cudaStream_t st, unsigned long long* stamp) {
     dim3 grid((unsigned)std::max<long long>(1, std::min<long long>(16, (t.seg_max / 2 + 255) / 256)), (unsigned)m);
     if (phase == kXPush) grid = dim3(1, 1);
-    lv_xhist_k<<<grid, 256, 0, st>>>(pt, t, d, m, area_off, slot_bytes, flag_set, epoch, phase, err);
+    lv_xhist_k<<<grid, 256, 0, st>>>(pt, t, d, m, area_off, slot_bytes, flag_set, xctr, phase, err, stamp);
     return cudaGetLastError();
 }
 cudaError_t launch_lv_xrecs(const PeerTable& pt, LvTables t, int n, long long first_heap, size_t area_off, size_t slot_bytes,
-                            size_t lh_off, size_t lh_slot_bytes, int flag_set, unsigned long long epoch, int phase, int* err,
-                            cudaStream_t st) {
-    lv_xrecs_k<<<1, 256, 0, st>>>(pt, t, n, first_heap, area_off, slot_bytes, lh_off, lh_slot_bytes, flag_set, epoch, phase, err);
+                            size_t lh_off, size_t lh_slot_bytes, int flag_set, unsigned long long* xctr, int phase, int* err,
+                            cudaStream_t st, unsigned long long* stamp) {
+    lv_xrecs_k<<<1, 256, 0, st>>>(pt, t, n, first_heap, area_off, slot_bytes, lh_off, lh_slot_bytes, flag_set, xctr, phase, err, stamp);
     return cudaGetLastError();
 }
 cudaError_t launch_lv_xleaf(const PeerTable& pt, LvTables t, int d, size_t area_off, size_t slot_bytes, size_t cnt_off,
-                            size_t cnt_slot_bytes, int flag_set, unsigned long long epoch, int phase, int* err, cudaStream_t st) {
-    lv_xleaf_k<<<1, 256, 0, st>>>(pt, t, d, area_off, slot_bytes, cnt_off, cnt_slot_bytes, flag_set, epoch, phase, err);
+                            size_t cnt_slot_bytes, int flag_set, unsigned long long* xctr, int phase, int* err, cudaStream_t st,
+                            unsigned long long* stamp) {
+    lv_xleaf_k<<<1, 256, 0, st>>>(pt, t, d, area_off, slot_bytes, cnt_off, cnt_slot_bytes, flag_set, xctr, phase, err, stamp);
     return cudaGetLastError();
 }
 

@@ -100,7 +100,7 @@ void free_all(ytk_gbdt* h) {
     if (h->peer_mode)
         for (int r = 0; r < h->world; r++)
             if (r != h->rank) { cudaIpcCloseMemHandle(h->pt.xchg[r]); cudaIpcCloseMemHandle(h->pt.hist[r]); }
-    F(h->my_xchg); F(h->my_hist);
+    F(h->my_xchg); F(h->my_hist); F(h->d_xctr);
     if (h->d_peer_err) cudaFreeHost(h->d_peer_err);
     h->t_items.release();
     h->t_scan.release(); h->t_sub.release(); h->t_pos.release(); h->t_seg_out.release(); h->t_counts.release();
