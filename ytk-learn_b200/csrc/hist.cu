@@ -213,6 +213,100 @@ __device__ __forceinline__ void hist_rows(uint32_t* sh, const HistLane& L, const
     }
 }
 
+// Experiment (north_star: "TMA-staged tiles where that helps"; YTK_GBDT_HIST_TMA=1): the same rows for a run of
+// CONTIGUOUS rows of a single feature group (S8 == 32: the root of the Higgs shape), with the row data brought into
+// shared memory by the bulk-copy engine instead of LDG: a warp's block of 32 rows is 1 KB of slots + 256 B of
+// gradient pairs, both contiguous, copied by two cp.async.bulk into a per-warp ring (2 stages) and signalled on an
+// mbarrier; the lanes then read their 16 + 8 bytes with LDS.  begin must be a multiple of 32 rows (16-byte source
+// alignment of the pairs).  `ring`: kHistThreads/32 warps x 2 stages x 1280 bytes, `bars`: 2 mbarriers per warp.
+// Measured on the 11 M-row root (profiles/r02_tma_experiment.txt): no faster -- the LDS reads cost the LSU data pipe
+// what the coalesced LDG did, and that pipe (shared-memory atomics) is what bounds the kernel.
+constexpr int kTmaStageBytes = 32 * kGroup + 32 * 8;
+constexpr int kHistSpanSmemBytes = kHistSmemBytes + kHistWarps * 2 * kTmaStageBytes + kHistWarps * 2 * 8;     // 128 KB + 80 KB + 512 B
+__device__ __forceinline__ void hist_rows_tma(uint32_t* sh, const HistLane& L, const uint8_t* __restrict__ bins,
+                                              const int2* __restrict__ gq, long long begin, long long end, char* ring,
+                                              unsigned long long* bars, uint32_t (&phases)[2]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int half = L.half, r16 = L.r16, m = L.m;
+    char* const shb = reinterpret_cast<char*>(sh);
+    char* my_ring = ring + warp * 2 * kTmaStageBytes;
+    const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(my_ring);
+    const uint32_t bar_s = (uint32_t)__cvta_generic_to_shared(bars + 2 * warp);
+    auto accumulate16 = [&](const uint4 d, const int2 q) {
+        uint32_t w[4] = {d.x, d.y, d.z, d.w};
+        {
+            const bool c0 = m & 1, c1 = m & 2;
+            uint32_t t;
+            t = c0 ? w[1] : w[0]; w[1] = c0 ? w[0] : w[1]; w[0] = t;
+            t = c0 ? w[3] : w[2]; w[3] = c0 ? w[2] : w[3]; w[2] = t;
+            t = c1 ? w[2] : w[0]; w[2] = c1 ? w[0] : w[2]; w[0] = t;
+            t = c1 ? w[3] : w[1]; w[3] = c1 ? w[1] : w[3]; w[1] = t;
+        }
+        const uint32_t g_lo = (uint32_t)q.x & 0xffffu, h_lo = (uint32_t)q.y & 0xffffu;
+        const int32_t g_hi = q.x >> 16, h_hi = q.y >> 16;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint32_t word = w[j];
+#pragma unroll
+            for (int kk = 0; kk < 4; kk++) {
+                const uint32_t off = (__byte_perm(word, 0u, L.selk[kk]) | L.lane_off) ^ (uint32_t)((4 * j + kk) << 2);
+                uint32_t* p = reinterpret_cast<uint32_t*>(shb + off);
+                atomicAdd(p, g_lo);
+                atomicAdd(reinterpret_cast<int32_t*>(p + kGroup), g_hi);
+                atomicAdd(p + kHOff / 4, h_lo);
+                atomicAdd(reinterpret_cast<int32_t*>(p + kHOff / 4 + kGroup), h_hi);
+            }
+        }
+    };
+    // blocks of this warp: rows [begin + warp*32 + t*1024, +32); only whole blocks go through the ring
+    const long long n_full = end > begin + warp * 32 ? (end - begin - warp * 32 + kHistThreads - 32) / kHistThreads : 0;
+    auto issue = [&](long long t, int stage) {           // lane 0
+        const long long row = begin + warp * 32 + t * kHistThreads;
+        const uint32_t dst = ring_s + stage * kTmaStageBytes, bar = bar_s + stage * 8;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)kTmaStageBytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst), "l"(bins + row * kGroup), "r"(32u * kGroup), "r"(bar) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst + 32u * kGroup), "l"(gq + row), "r"(256u), "r"(bar) : "memory");
+    };
+    long long whole = 0;                                  // blocks of 32 rows that exist entirely
+    for (long long t = 0; t < n_full; t++)
+        if (begin + warp * 32 + t * kHistThreads + 32 <= end) whole = t + 1;
+    if (lane == 0) {
+        if (whole > 0) issue(0, 0);
+        if (whole > 1) issue(1, 1);
+    }
+    for (long long t = 0; t < whole; t++) {
+        const int stage = (int)(t & 1);
+        const uint32_t parity = phases[stage]++ & 1u;    // (completed phases of the stage's barrier so far, over all calls)
+        const uint32_t bar = bar_s + stage * 8;
+        uint32_t ok = 0;
+        while (!ok)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        const char* src = my_ring + stage * kTmaStageBytes;
+        const uint4 a = *reinterpret_cast<const uint4*>(src + r16 * kGroup + (half << 4));
+        const uint4 b = *reinterpret_cast<const uint4*>(src + (16 + r16) * kGroup + (half << 4));
+        const int2 qa = *reinterpret_cast<const int2*>(src + 32 * kGroup + r16 * 8);
+        const int2 qb = *reinterpret_cast<const int2*>(src + 32 * kGroup + (16 + r16) * 8);
+        __syncwarp();                                     // everybody has read the stage: it may be refilled
+        if (lane == 0 && t + 2 < whole) issue(t + 2, stage);
+        accumulate16(a, qa);
+        accumulate16(b, qb);
+    }
+    // a last partial block: plain loads
+    const long long tail = begin + warp * 32 + whole * kHistThreads;
+    if (tail < end) {
+        const long long ia = tail + r16, ib = tail + 16 + r16;
+        uint4 a = make_uint4(0, 0, 0, 0), b = a;
+        int2 qa = make_int2(0, 0), qb = qa;
+        if (ia < end) { a = *reinterpret_cast<const uint4*>(bins + ia * kGroup + (half << 4)); qa = gq[ia]; }
+        if (ib < end) { b = *reinterpret_cast<const uint4*>(bins + ib * kGroup + (half << 4)); qb = gq[ib]; }
+        accumulate16(a, qa);
+        accumulate16(b, qb);
+    }
+}
+
 // Flush: recombines the limbs, one 64-bit global reduction per non-empty (feature, bin, component) into
 // `out` (the node's histogram), and -- kRezero -- puts the words it read back to zero, so that the next
 // node's rows find a clean table without a separate zeroing pass.  (Cells of padding features and of
@@ -282,12 +376,25 @@ hist_span_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict
             const BuildNode* __restrict__ nodes, const int* __restrict__ n_nodes_dev, int32_t F,
             const uint32_t* __restrict__ group_mask, const int32_t* __restrict__ nbins,
             const int32_t* __restrict__ feat_owner, const int64_t* __restrict__ feat_inner, long long owner_stride,
-            long long* const* __restrict__ seg_out, unsigned long long* __restrict__ stamp) {
+            long long* const* __restrict__ seg_out, unsigned long long* __restrict__ stamp, int use_tma) {
     pdl_sync();
     extern __shared__ __align__(128) uint32_t sh[];
     const int nb = *n_nodes_dev;
     if (nb <= 0) return;
     stamp_begin(stamp);
+    // (experiment) per-warp rings + mbarriers of the bulk-copy variant sit behind the histogram
+    uint32_t tma_phases[2] = {0, 0};
+    char* const ring = reinterpret_cast<char*>(sh) + kHistSmemBytes;
+    unsigned long long* const bars = reinterpret_cast<unsigned long long*>(ring + kHistWarps * 2 * kTmaStageBytes);
+    if (use_tma) {
+        if ((threadIdx.x & 31) == 0) {
+            const uint32_t b = (uint32_t)__cvta_generic_to_shared(bars + 2 * (threadIdx.x >> 5));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(b));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(b + 8));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+    }
     const int fg = blockIdx.y;
     const long long total = nodes[nb - 1].cost_end;
     const long long c0 = total * blockIdx.x / gridDim.x, c1 = total * (blockIdx.x + 1) / gridDim.x;
@@ -309,13 +416,18 @@ hist_span_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict
         if (cost_begin >= c1) break;
         long long o0 = c0 - cost_begin, o1 = c1 - cost_begin;       // my share of the node, in rows from its begin
         o0 = o0 < 0 ? 0 : o0;
+        // shares begin on multiples of 32 rows (the neighbouring span rounds the same boundary the same way)
+        o0 = (o0 + 31) & ~31ll;
+        o1 = o1 >= n ? n : ((o1 + 31) & ~31ll);
+        o0 = o0 > n ? n : o0;
         o1 = o1 > n ? n : o1;
         if (o0 >= o1) continue;                                     // only (part of) its flush cost falls to me
         const int32_t* __restrict__ ridx = nd.buf < 0 ? nullptr : (nd.buf == 0 ? rowidx0 : rowidx1);
         long long* __restrict__ out = seg_out[nd.seg];
         for (long long b = nd.begin + o0; b < nd.begin + o1; b += kHistMaxRowsPerItem) {
             const long long e = min(nd.begin + o1, b + (long long)kHistMaxRowsPerItem);
-            hist_rows(sh, L, bins, S8, gq, ridx, fg, b, e);
+            if (use_tma && !ridx && S8 == kGroup && (b & 31) == 0) hist_rows_tma(sh, L, bins, gq, b, e, ring, bars, tma_phases);
+            else hist_rows(sh, L, bins, S8, gq, ridx, fg, b, e);
             __syncthreads();
             hist_flush<true>(sh, fg, F, gmask, nbins, feat_owner, feat_inner, owner_stride, out);
             __syncthreads();
@@ -499,7 +611,7 @@ cudaError_t launch_grad_quantize(const float* gp, int64_t n, int32_t K, int32_t 
 cudaError_t hist_kernels_init() {
     cudaError_t e = cudaFuncSetAttribute(hist_build_k, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemBytes);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(hist_span_k, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmemBytes);
+    return cudaFuncSetAttribute(hist_span_k, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSpanSmemBytes);
 }
 
 int64_t hist_rows_per_item(int64_t total_rows, int groups) {
@@ -530,8 +642,9 @@ cudaError_t launch_hist_span(const uint8_t* bins, int32_t S8, const int2* gq, co
                              long long* const* seg_out, cudaStream_t st, unsigned long long* stamp) {
     const int per_group = std::max(1, kNumSMs / std::max(1, groups));
     dim3 grid((unsigned)per_group, (unsigned)groups);
-    return launch_chain(hist_span_k, grid, dim3(kHistThreads), kHistSmemBytes, st, bins, S8, gq, rowidx0, rowidx1, nodes, n_nodes_dev,
-                        F, group_mask, nbins, feat_owner, feat_inner, owner_stride, seg_out, stamp);
+    static const int use_tma = [] { const char* e = getenv("YTK_GBDT_HIST_TMA"); return e ? atoi(e) : 0; }();
+    return launch_chain(hist_span_k, grid, dim3(kHistThreads), use_tma ? kHistSpanSmemBytes : kHistSmemBytes, st, bins, S8, gq, rowidx0, rowidx1, nodes, n_nodes_dev,
+                        F, group_mask, nbins, feat_owner, feat_inner, owner_stride, seg_out, stamp, use_tma);
 }
 
 cudaError_t launch_hist_wide(WideCols wide, const int32_t* wide_fids, int n_wide, const int2* gq, const int32_t* rowidx0,
