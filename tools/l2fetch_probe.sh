@@ -4,7 +4,7 @@
 for g in 32 64 128; do
   YTK_GBDT_L2_FETCH=$g YTK_GBDT_NO_GRAPH=1 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum --clock-control none \
      -k regex:"hist_span_k|partition_fused_k" -s 16 -c 16 --csv --log-file gpurun_out/l2f_$g.csv \
-     python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-loss-wise --no-parity-check --no-other-configs > /dev/null 2>&1
+     python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-loss-wise --no-parity-check --no-other-configs 2>&1 > /dev/null | grep -m1 cudaLimit
   python - $g <<'PY'
 import csv, collections, sys
 g = sys.argv[1]
