@@ -67,7 +67,12 @@ constexpr int kMaxSparseFeatures = 65536;
 
 // cseg >= 0: sample_cnt is the global row count of the smaller (which = 0) / larger (which = 1)
 // child of split segment cseg, read from the device counts
-struct ScanNode { const long long* hist; long long sample_cnt; int cseg; int which; };
+// sub != null: the node's histogram is hist - sub and the search writes it over hist (tot_parent: the exact totals
+// {G, H} of the parent, which hist still holds); tot_out (nullable): where the node's own exact totals go
+struct ScanNode {
+    const long long* hist; long long sample_cnt; int cseg; int which;
+    const long long* sub; const long long* tot_parent; long long* tot_out;
+};
 struct alignas(16) SplitPart { float lc; int fid, lo, hi; long long lh; long long pad; };   // best split of one slice of a node's features (lh: hessian left of it, fixed point)
 struct SubItem { const long long* parent; const long long* small; long long* out; };
 struct PosItem { long long begin, end; int buf; int nid; };

@@ -73,10 +73,10 @@ static int engine_reserve(ytk_gbdt* h, int D) {
     const size_t o_segs = take(slots * sizeof(ytk::SplitSeg)), o_tiles = take(tiles * sizeof(int)), o_ntiles = take(sizeof(int)),
                  o_counts = take(slots * sizeof(ytk::PartitionCounts)), o_gcounts = take(slots * sizeof(ytk::PartitionCounts)),
                  o_build = take(2 * slots * sizeof(ytk::BuildNode)), o_nbuild = take(sizeof(int)),
-                 o_subs = take(slots * sizeof(ytk::SubItem)), o_scans = take(2 * slots * sizeof(ytk::ScanNode)),
+                 o_scans = take(2 * slots * sizeof(ytk::ScanNode)),
                  o_segout = take(2 * slots * sizeof(long long*)), o_segfinal = take(2 * slots * sizeof(long long*)),
                  o_recs_local = take(2 * slots * sizeof(ytk_split)), o_lh_local = take(4 * slots * sizeof(long long)),
-                 o_epoch = take(sizeof(unsigned long long)), o_gid = take(sizeof(int));
+                 o_epoch = take(sizeof(unsigned long long)), o_gid = take(sizeof(int)), o_tot = take(heap * 2 * sizeof(long long));
     CK(cudaMalloc(&e.dev, off));
     CK(cudaMemsetAsync(e.dev, 0, off, h->st));
     CK(cudaHostAlloc((void**)&e.host, mirror_bytes, cudaHostAllocDefault));
@@ -93,7 +93,7 @@ static int engine_reserve(ytk_gbdt* h, int D) {
     t.gcounts = reinterpret_cast<ytk::PartitionCounts*>(e.dev + o_gcounts);
     t.build = reinterpret_cast<ytk::BuildNode*>(e.dev + o_build);
     t.n_build = reinterpret_cast<int*>(e.dev + o_nbuild);
-    t.subs = reinterpret_cast<ytk::SubItem*>(e.dev + o_subs);
+    t.tot = reinterpret_cast<long long*>(e.dev + o_tot);
     t.scans = reinterpret_cast<ytk::ScanNode*>(e.dev + o_scans);
     t.seg_out = reinterpret_cast<long long**>(e.dev + o_segout);
     t.seg_final = reinterpret_cast<long long**>(e.dev + o_segfinal);
@@ -444,11 +444,9 @@ public:
         RET(mark(kHist));
         return YTK_OK;
     }
-    // ... the larger ones by subtraction, and findBestSplit of both
+    // ... the larger ones by subtraction (inside the search: ScanNode::sub), and findBestSplit of both
     int level_scan(int d) {
         const int m = 1 << d;
-        CK(ytk::launch_hist_subtract(t.subs, m, h->seg_max, h->st));
-        h->launches++;
         RET(scan_launch(t.scans, 2 * m, (size_t)2 * m - 1, d + 1));
         RET(mark(kSplit));
         return YTK_OK;
@@ -584,6 +582,28 @@ public:
         T->device_span_ms = span;
         T->init_stats = std::max(0.0, span - ms[kStHist] - ms[kStPart] - ms[kStScan] - T->communicate_hist - T->sync_best_split);
         T->stage_times_from_gpu = 1;
+        // YTK_GBDT_TRACE_STAMPS=1: the tree's timeline on the GPU's own clock -- start (from the first stamp) and
+        // duration of every stamped kernel, in time order; what lies between two lines is unstamped (planners,
+        // gradient scales, memsets, leaf sums) or idle
+        static const bool trace = [] { const char* e = getenv("YTK_GBDT_TRACE_STAMPS"); return e && atoi(e); }();
+        if (trace) {
+            static const char* const names[kStKinds] = {"hist", "partition", "scan", "xhist", "xrecs"};
+            struct Ev { unsigned long long a, b; int k, l; };
+            std::vector<Ev> ev;
+            for (int k = 0; k < kStKinds; k++)
+                for (int l = 0; l < kStampLevels; l++) {
+                    const unsigned long long a = ~st[2 * (k * kStampLevels + l)], b = st[2 * (k * kStampLevels + l) + 1];
+                    if (b != 0 && b >= a) ev.push_back({a, b, k, l});
+                }
+            std::sort(ev.begin(), ev.end(), [](const Ev& x, const Ev& y) { return x.a < y.a; });
+            unsigned long long prev_end = first;
+            fprintf(stderr, "ytk_gbdt timeline (us): span %.1f\n", span * 1e3);
+            for (const Ev& e : ev) {
+                fprintf(stderr, "  +%8.1f  %-9s level %2d  %7.1f us   (gap before: %.1f)\n", (double)(e.a - first) * 1e-3, names[e.k], e.l,
+                        (double)(e.b - e.a) * 1e-3, (double)((long long)e.a - (long long)prev_end) * 1e-3);
+                prev_end = std::max(prev_end, e.b);
+            }
+        }
         return YTK_OK;
     }
     bool replayed = false;

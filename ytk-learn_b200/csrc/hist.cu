@@ -30,8 +30,26 @@ __global__ void grad_absmax_k(const float* __restrict__ gp, int64_t n, int32_t K
                               unsigned* __restrict__ absmax_bits) {
     if (gid_dev) gid = *gid_dev;
     float mg = 0.f, mh = 0.f;
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
-         i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+    int64_t i0 = 0;
+    if (K == 1 && (reinterpret_cast<unsigned long long>(gp) & 15ull) == 0) {
+        // one class: the pairs are contiguous -- two rows per 128-bit load, four loads in flight per thread
+        const float4* __restrict__ gp4 = reinterpret_cast<const float4*>(gp);
+        const int64_t n2 = n >> 1;
+        int64_t j = tid;
+        for (; j + 3 * nthr < n2; j += 4 * nthr) {
+            const float4 a = gp4[j], b = gp4[j + nthr], c = gp4[j + 2 * nthr], d = gp4[j + 3 * nthr];
+            mg = fmaxf(fmaxf(fmaxf(mg, fabsf(a.x)), fmaxf(fabsf(a.z), fabsf(b.x))), fmaxf(fmaxf(fabsf(b.z), fabsf(c.x)), fmaxf(fabsf(c.z), fmaxf(fabsf(d.x), fabsf(d.z)))));
+            mh = fmaxf(fmaxf(fmaxf(mh, fabsf(a.y)), fmaxf(fabsf(a.w), fabsf(b.y))), fmaxf(fmaxf(fabsf(b.w), fabsf(c.y)), fmaxf(fabsf(c.w), fmaxf(fabsf(d.y), fabsf(d.w)))));
+        }
+        for (; j < n2; j += nthr) {
+            const float4 a = gp4[j];
+            mg = fmaxf(mg, fmaxf(fabsf(a.x), fabsf(a.z)));
+            mh = fmaxf(mh, fmaxf(fabsf(a.y), fabsf(a.w)));
+        }
+        i0 = n2 << 1;                      // (an odd last row is left to the loop below)
+    }
+    for (int64_t i = i0 + tid; i < n; i += nthr) {
         float2 v = *reinterpret_cast<const float2*>(gp + (i * K + gid) * 2);
         mg = fmaxf(mg, fabsf(v.x));
         mh = fmaxf(mh, fabsf(v.y));
@@ -70,8 +88,26 @@ __global__ void grad_quantize_k(const float* __restrict__ gp, int64_t n, int32_t
         scale->mul_g = mg; scale->mul_h = mh;
         scale->inv_g = ldexp(1.0, -kg); scale->inv_h = ldexp(1.0, -kh);
     }
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
-         i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nthr = (int64_t)gridDim.x * blockDim.x;
+    int64_t i0 = 0;
+    if (K == 1 && ((reinterpret_cast<unsigned long long>(gp) | reinterpret_cast<unsigned long long>(gq)) & 15ull) == 0) {
+        // one class: two rows per 128-bit load and store, two in flight
+        const float4* __restrict__ gp4 = reinterpret_cast<const float4*>(gp);
+        int4* __restrict__ gq4 = reinterpret_cast<int4*>(gq);
+        const int64_t n2 = n >> 1;
+        int64_t j = tid;
+        for (; j + nthr < n2; j += 2 * nthr) {
+            const float4 a = gp4[j], b = gp4[j + nthr];
+            gq4[j] = make_int4(to_fixed(a.x, mg), to_fixed(a.y, mh), to_fixed(a.z, mg), to_fixed(a.w, mh));
+            gq4[j + nthr] = make_int4(to_fixed(b.x, mg), to_fixed(b.y, mh), to_fixed(b.z, mg), to_fixed(b.w, mh));
+        }
+        for (; j < n2; j += nthr) {
+            const float4 a = gp4[j];
+            gq4[j] = make_int4(to_fixed(a.x, mg), to_fixed(a.y, mh), to_fixed(a.z, mg), to_fixed(a.w, mh));
+        }
+        i0 = n2 << 1;
+    }
+    for (int64_t i = i0 + tid; i < n; i += nthr) {
         float2 v = *reinterpret_cast<const float2*>(gp + (i * K + gid) * 2);
         gq[i] = make_int2(to_fixed(v.x, mg), to_fixed(v.y, mh));
     }

@@ -46,7 +46,7 @@ __global__ void lv_root_k(LvTables t, long long begin, long long end, int buf, c
         t.seg_final[0] = t.pool;
         t.counts[0] = {n, 0};                                    // summed over the ranks beside the root histogram
     }
-    t.scans[0] = {t.pool, n, -1, 0};
+    t.scans[0] = {t.pool, n, -1, 0, nullptr, nullptr, t.tot};
 }
 
 // Which nodes of level d are split -- lossChg > min_split_loss (the depth rule is the host's: it does not
@@ -128,8 +128,7 @@ lv_plan_build_k(LvTables t, int d, int child_buf, int leaf) {
         if (s < m) {
             const int p = L0 + s;
             LvNode nd = t.nodes[p];
-            SubItem sub = {nullptr, nullptr, nullptr};
-            ScanNode sc_l = {nullptr, 0, -1, 0}, sc_r = sc_l;
+            ScanNode sc_l = {nullptr, 0, -1, 0, nullptr, nullptr, nullptr}, sc_r = sc_l;
             if (nd.flags & kLvSplit) {
                 const PartitionCounts c = t.counts[s];
                 const PartitionCounts gc = t.world == 1 ? c : t.gcounts[s];
@@ -165,17 +164,19 @@ lv_plan_build_k(LvTables t, int d, int child_buf, int leaf) {
                 if (!leaf) {
                     long long* parent_h = t.pool + (long long)nd.slot * t.seg_max;
                     long long* small_h = t.pool + (long long)slot_small * t.seg_max;
-                    sub = {parent_h, small_h, parent_h};                   // substract (:101-107), in place
                     sc_l.hist = small_left ? small_h : parent_h;
                     sc_r.hist = small_left ? parent_h : small_h;
                     sc_l.sample_cnt = gc.left; sc_r.sample_cnt = gc.right;
+                    sc_l.tot_out = t.tot + 2 * (2 * p + 1); sc_r.tot_out = t.tot + 2 * (2 * p + 2);
+                    ScanNode& large = small_left ? sc_r : sc_l;            // substract (:101-107): done by the search, in place
+                    large.sub = small_h; large.tot_parent = t.tot + 2 * p;
                     t.seg_out[s] = t.world == 1 ? small_h : t.staging + (long long)s * t.seg_max;
                     if (t.world > 1) t.seg_final[s] = small_h;
                 }
             } else if (!leaf && t.world > 1) {
                 t.seg_final[s] = nullptr;
             }
-            if (!leaf) { t.subs[s] = sub; t.scans[2 * s] = sc_l; t.scans[2 * s + 1] = sc_r; }
+            if (!leaf) { t.scans[2 * s] = sc_l; t.scans[2 * s + 1] = sc_r; }
         }
         int n_add;
         int j = s_cnt + block_excl_scan<int>((add ? 1 : 0) + (add2 ? 1 : 0), s_warp_i, &n_add);

@@ -41,8 +41,8 @@ struct LvTables {
     PartitionCounts* gcounts;       // [slots] global (== counts on one GPU)
     BuildNode* build;               // [slots] histogram build nodes of the level
     int* n_build;
-    SubItem* subs;                  // [slots]
-    ScanNode* scans;                // [2 * slots]
+    ScanNode* scans;                // [2 * slots] (the larger child's entry asks for parent - smaller sibling)
+    long long* tot;                 // [heap][2] exact fixed-point totals {G, H} of every searched node
     long long** seg_out;            // [slots] where hist_span_k accumulates node `seg`
     long long** seg_final;          // [slots] world > 1: the slot the reduced histogram of node `seg` goes to (null: none)
     ytk_split* recs_local;          // [2 * slots] world > 1: this rank's records of the level's children, before the merge

@@ -58,6 +58,14 @@ __device__ __forceinline__ double calc_gain(const GainParams& p, double G, doubl
 
 constexpr int kScanWarps = 4;     // features per CTA; a node's features are spread over several CTAs (slices)
 
+// One warp per feature.  Lane L holds bins [8L, 8L + 8) of a block of 256 bins (one block for a feature with uint8
+// slots): a lane-local prefix, ONE warp scan per block and eight independent gain evaluations per lane, instead of
+// eight dependent scan + gain rounds.  The feature's bins are requested before the node totals are known, so the
+// kernel's critical path is one table load, one histogram load and the arithmetic.
+// A node with `sub` set has no histogram yet: it is hist - sub (parent - smaller sibling, HistogramBuilder.substract,
+// J/data/gbdt/HistogramBuilder.java:101-107), formed here in registers and written over the parent's copy by the
+// feature's own warp -- no separate subtraction pass.  Nobody else reads those words during the launch: the node
+// totals of such a node come from tot_parent (the parent's exact integer totals) minus the sibling's.
 __global__ void __launch_bounds__(kScanWarps * 32)
 split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ start,
              const int64_t* __restrict__ feat_off, const uint8_t* __restrict__ fea_selected,
@@ -73,31 +81,64 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
     __shared__ int s_last;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int node = blockIdx.x, slice = blockIdx.y;
-    const double ig = scale->inv_g, ih = scale->inv_h;
-    const long long* __restrict__ hist = nodes[node].hist;
-    if (!hist) return;                      // an unused entry of a device-planned table (the whole CTA leaves)
+    const ScanNode nd = nodes[node];
+    if (!nd.hist) return;                   // an unused entry of a device-planned table (the whole CTA leaves)
     stamp_begin(stamp);
-    long long sample_cnt = nodes[node].sample_cnt;
-    if (nodes[node].cseg >= 0) {
-        const PartitionCounts g = cnt_global[nodes[node].cseg];
+    long long* const hist = const_cast<long long*>(nd.hist);       // written only where nd.sub asks for it
+    const long long* __restrict__ sub = nd.sub;
+    constexpr int kPer = kMaxBins / 32;     // bins per lane and block
+
+    // bins [blk + 8 * lane, +8) of the feature, zero past its end; with `sub`: the difference
+    auto load_block = [&](longlong2 (&v)[kPer], const long long* hp, const long long* sp, int blk, int nb) {
+        longlong2 b[kPer];
+#pragma unroll
+        for (int k = 0; k < kPer; k++) {
+            const int j = blk + lane * kPer + k;
+            v[k] = make_longlong2(0, 0); b[k] = v[k];
+            if (j < nb) v[k] = *reinterpret_cast<const longlong2*>(hp + 2 * j);
+            if (sp && j < nb) b[k] = *reinterpret_cast<const longlong2*>(sp + 2 * j);
+        }
+#pragma unroll
+        for (int k = 0; k < kPer; k++) { v[k].x -= b[k].x; v[k].y -= b[k].y; }
+    };
+    const int f = f_from + slice * kScanWarps + warp;       // one feature per warp
+    const bool mine = f < f_to && fea_selected[f];
+    long long* hp = nullptr;
+    const long long* sp = nullptr;
+    int nb = 0;
+    longlong2 cur[kPer];
+    if (mine) {
+        const long long off = feat_off[f];
+        hp = hist + off;
+        sp = sub ? sub + off : nullptr;
+        nb = start[f + 1] - start[f];
+        load_block(cur, hp, sp, 0, nb);
+    }
+    const double ig = scale->inv_g, ih = scale->inv_h;
+    long long sample_cnt = nd.sample_cnt;
+    if (nd.cseg >= 0) {
+        const PartitionCounts g = cnt_global[nd.cseg];
         const long long small = g.left < g.right ? g.left : g.right;
-        sample_cnt = nodes[node].which == 0 ? small : (g.left + g.right - small);
+        sample_cnt = nd.which == 0 ? small : (g.left + g.right - small);
     }
 
     if (warp == 0) {
         double G, H;
         if (first_fea >= 0) {
+            // every feature's bins add up to the node's totals: those of the first selected feature are taken
             long long g = 0, h = 0;
-            const long long* hp = hist + feat_off[first_fea];
-            int nb = start[first_fea + 1] - start[first_fea];
-            for (int j = lane; j < nb; j += 32) {
-                longlong2 gh = *reinterpret_cast<const longlong2*>(hp + 2 * j);
+            const long long* tp = (sub ? sub : hist) + feat_off[first_fea];
+            const int nb0 = start[first_fea + 1] - start[first_fea];
+            for (int j = lane; j < nb0; j += 32) {
+                longlong2 gh = *reinterpret_cast<const longlong2*>(tp + 2 * j);
                 g += gh.x; h += gh.y;
             }
             for (int d = 16; d > 0; d >>= 1) {
                 g += __shfl_xor_sync(0xffffffffu, g, d);
                 h += __shfl_xor_sync(0xffffffffu, h, d);
             }
+            if (sub) { g = nd.tot_parent[0] - g; h = nd.tot_parent[1] - h; }
+            if (nd.tot_out && slice == 0 && lane == 0) { nd.tot_out[0] = g; nd.tot_out[1] = h; }
             G = (double)g * ig; H = (double)h * ih;
             if (lane == 0) s_toth = h;
         } else {
@@ -115,57 +156,60 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
     float w_lc = -CUDART_INF_F;
     int w_fid = -1, w_lo = -1, w_hi = -1;
     long long w_lh = 0;                     // fixed-point hessian left of the best split (exact)
-    const int f = f_from + slice * kScanWarps + warp;       // one feature per warp
-    if (can_split && f < f_to && fea_selected[f]) {
-        const long long* hp = hist + feat_off[f];
-        const int nb = start[f + 1] - start[f];
+    if (can_split && mine) {
         long long carryG = 0, carryH = 0;
         int carry_last = -1;
         float b_lc = -CUDART_INF_F;
         int b_lo = -1, b_hi = 0x7fffffff;
         long long b_lh = 0;
-        // 256 bins at a time (one pass for a feature with uint8 slots) are fetched up front -- 8 loads
-        // in flight instead of one dependent memory round trip per 32-bin chunk
         for (int blk = 0; blk < nb; blk += kMaxBins) {
-        longlong2 pre[kMaxBins / 32];
+            if (blk > 0) load_block(cur, hp, sp, blk, nb);
+            const int j0 = blk + lane * kPer;
+            if (sp) {
 #pragma unroll
-        for (int c = 0; c < kMaxBins / 32; c++) {
-            const int j = blk + c * 32 + lane;
-            pre[c] = make_longlong2(0, 0);
-            if (j < nb) pre[c] = *reinterpret_cast<const longlong2*>(hp + 2 * j);
-        }
-#pragma unroll
-        for (int c = 0; c < kMaxBins / 32; c++) {
-            const int c0 = blk + c * 32;
-            if (c0 >= nb) break;
-            int j = c0 + lane;
-            long long g = pre[c].x, h = pre[c].y;
-            bool ne = (g | h) != 0;                                   // hasSample
-            long long pg = g, ph = h;
-            for (int d = 1; d < 32; d <<= 1) {
-                long long tg = __shfl_up_sync(0xffffffffu, pg, d);
-                long long th = __shfl_up_sync(0xffffffffu, ph, d);
-                if (lane >= d) { pg += tg; ph += th; }
+                for (int k = 0; k < kPer; k++)
+                    if (j0 + k < nb) *reinterpret_cast<longlong2*>(hp + 2 * (j0 + k)) = cur[k];
             }
-            long long exG = carryG + pg - g, exH = carryH + ph - h;   // left branch before bin j
-            unsigned m = __ballot_sync(0xffffffffu, ne);
-            unsigned lower = m & ((1u << lane) - 1u);
-            int prev = lower ? (c0 + 31 - __clz(lower)) : carry_last; // lastFeaValue
-            if (ne && exH != 0) {                                      // !leftBranchGradStats.empty()
-                double lG = (double)exG * ig, lH = (double)exH * ih;
-                if (lH >= gp.min_child_weight) {
-                    double rG = __dsub_rn(totG, lG), rH = __dsub_rn(totH, lH);
-                    if (rH >= gp.min_child_weight) {
-                        float lc = (float)__dsub_rn(__dadd_rn(calc_gain(gp, lG, lH), calc_gain(gp, rG, rH)),
-                                                    (double)root_gain);
-                        if (lc > b_lc) { b_lc = lc; b_lo = prev; b_hi = j; b_lh = exH; }
+            long long pg[kPer], ph[kPer];                   // sums of this lane's bins before bin k
+            long long lg = 0, lh = 0;
+            unsigned ne_mask = 0;                           // hasSample, bit k
+#pragma unroll
+            for (int k = 0; k < kPer; k++) {
+                pg[k] = lg; ph[k] = lh;
+                lg += cur[k].x; lh += cur[k].y;
+                ne_mask |= (unsigned)((cur[k].x | cur[k].y) != 0) << k;
+            }
+            long long sg = lg, sh = lh;                     // inclusive over the lanes
+            int pm = ne_mask ? j0 + 31 - __clz(ne_mask) : -1;   // last bin with samples up to and including this lane
+            for (int d = 1; d < 32; d <<= 1) {
+                const long long tg = __shfl_up_sync(0xffffffffu, sg, d);
+                const long long th = __shfl_up_sync(0xffffffffu, sh, d);
+                const int tm = __shfl_up_sync(0xffffffffu, pm, d);
+                if (lane >= d) { sg += tg; sh += th; pm = max(pm, tm); }
+            }
+            const long long baseG = carryG + sg - lg, baseH = carryH + sh - lh;    // left branch before this lane's bins
+            int prev = __shfl_up_sync(0xffffffffu, pm, 1);                        // lastFeaValue
+            prev = lane == 0 ? carry_last : max(prev, carry_last);
+#pragma unroll
+            for (int k = 0; k < kPer; k++) {
+                const bool ne = (ne_mask >> k) & 1u;
+                const long long exG = baseG + pg[k], exH = baseH + ph[k];
+                if (ne && exH != 0) {                                      // !leftBranchGradStats.empty()
+                    double lG = (double)exG * ig, lH = (double)exH * ih;
+                    if (lH >= gp.min_child_weight) {
+                        double rG = __dsub_rn(totG, lG), rH = __dsub_rn(totH, lH);
+                        if (rH >= gp.min_child_weight) {
+                            float lc = (float)__dsub_rn(__dadd_rn(calc_gain(gp, lG, lH), calc_gain(gp, rG, rH)),
+                                                        (double)root_gain);
+                            if (lc > b_lc) { b_lc = lc; b_lo = prev; b_hi = j0 + k; b_lh = exH; }
+                        }
                     }
                 }
+                if (ne) prev = j0 + k;
             }
-            carryG += __shfl_sync(0xffffffffu, pg, 31);
-            carryH += __shfl_sync(0xffffffffu, ph, 31);
-            if (m) carry_last = c0 + 31 - __clz(m);
-        }
+            carryG += __shfl_sync(0xffffffffu, sg, 31);
+            carryH += __shfl_sync(0xffffffffu, sh, 31);
+            carry_last = max(carry_last, __shfl_sync(0xffffffffu, pm, 31));
         }
         // first (lowest bin) maximum inside the feature
         for (int d = 16; d > 0; d >>= 1) {
