@@ -79,6 +79,15 @@ class Tree:
             setattr(t, name, getattr(self, name).ctypes.data)
         return t
 
+    def _trimmed_copy(self, n):
+        """A new Tree holding copies of the first n nodes (self stays a reusable full-capacity buffer)."""
+        t = Tree.__new__(Tree)
+        t.capacity = self.capacity
+        t.n_nodes = n
+        for name, _ in self.FIELDS:
+            setattr(t, name, getattr(self, name)[:n].copy())
+        return t
+
     def _trim(self, n):
         self.n_nodes = n
         for name, _ in self.FIELDS:

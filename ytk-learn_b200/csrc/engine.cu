@@ -285,10 +285,13 @@ public:
         RET(scan_done_counters(h, 2 << D));
         while ((int)h->ev_stage.size() < 6 * D + 16) { cudaEvent_t e; CK(cudaEventCreate(&e)); h->ev_stage.push_back(e); }
         while ((int)h->ev.size() < 2 * D + 4) { cudaEvent_t e; CK(cudaEventCreate(&e)); h->ev.push_back(e); }
-        int* stage = static_cast<int*>(h->arena.take(sizeof(int), h->st));
-        if (!stage) return fail(YTK_ERR_CUDA, "pinned staging allocation failed");
-        *stage = gid;
-        CK(cudaMemcpyAsync(t.gid, stage, sizeof(int), cudaMemcpyHostToDevice, h->st));
+        if (h->eng.gid_on_device != gid) {
+            int* stage = static_cast<int*>(h->arena.take(sizeof(int), h->st));
+            if (!stage) return fail(YTK_ERR_CUDA, "pinned staging allocation failed");
+            *stage = gid;
+            CK(cudaMemcpyAsync(t.gid, stage, sizeof(int), cudaMemcpyHostToDevice, h->st));
+            h->eng.gid_on_device = gid;
+        }
         return YTK_OK;
     }
 

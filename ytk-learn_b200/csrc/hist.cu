@@ -344,27 +344,52 @@ __device__ __forceinline__ void hist_rows_tma(uint32_t* sh, const HistLane& L, c
 }
 
 // Flush: recombines the limbs, one 64-bit global reduction per non-empty (feature, bin, component) into
-// `out` (the node's histogram), and -- kRezero -- puts the words it read back to zero, so that the next
-// node's rows find a clean table without a separate zeroing pass.  (Cells of padding features and of
-// bins a feature does not have are never read here, so they may hold anything.)
+// `out` (the node's histogram), and -- kRezero -- leaves the table zero for the next node's rows.
+// What bounds a flush is the number of 32 B sectors its reductions touch (one L1 tag cycle and one L2 request
+// each): the four values of a sector of `out` -- (g,h) of two neighbouring bins of one feature -- are therefore
+// sent by four neighbouring lanes of ONE instruction, which then covers 8 features x 2 bins in 8 sectors (a
+// lane per feature would touch 32).  The price is a 4-way bank conflict on the limb reads (bank = feature),
+// cheaper than the sectors it saves.  CTAs start at different bins so that they do not all hit the same
+// addresses of a shared node at the same time.
 template <bool kRezero>
 __device__ __forceinline__ void hist_flush(uint32_t* sh, int fg, int32_t F, uint32_t gmask, const int32_t* __restrict__ nbins,
                                            const int32_t* __restrict__ feat_owner, const int64_t* __restrict__ feat_inner,
                                            long long owner_stride, long long* __restrict__ out) {
-    for (int i = threadIdx.x; i < kMaxBins * kGroup; i += kHistThreads) {
-        int bin = i >> 5, ln = i & 31;
-        int ff = fg * kGroup + ln;
-        if (ff >= F || !((gmask >> ln) & 1u) || bin >= nbins[ff]) continue;
-        uint32_t* pg = sh + bin * (2 * kGroup) + ln;
-        uint32_t* ph = pg + kHOff / 4;
-        const uint32_t g0 = pg[0], g1 = pg[kGroup], h0 = ph[0], h1 = ph[kGroup];
-        if ((g0 | g1 | h0 | h1) == 0) continue;
-        if (kRezero) { pg[0] = 0; pg[kGroup] = 0; ph[0] = 0; ph[kGroup] = 0; }
-        long long g = (long long)(int32_t)g1 * 65536ll + (long long)g0;
-        long long h = (long long)(int32_t)h1 * 65536ll + (long long)h0;
-        long long* dst = out + feat_owner[ff] * owner_stride + feat_inner[ff] + 2 * bin;
-        if (g != 0) atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)g);
-        if (h != 0) atomicAdd(reinterpret_cast<unsigned long long*>(dst + 1), (unsigned long long)h);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int q = lane >> 2, s = (lane >> 1) & 1, c = lane & 1;
+    constexpr int kPairs = kMaxBins / 2 + 1;             // bin pairs of a feature, one more when its first cell is odd
+    // this lane's four features (one per quarter of the group): where their cells go, how many bins they have
+    long long* dst0[4];
+    int nb[4];
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+        const int ln = g * 8 + q, ff = fg * kGroup + ln;
+        const bool on = ff < F && ((gmask >> ln) & 1u);
+        nb[g] = on ? nbins[ff] : 0;
+        dst0[g] = on ? out + feat_owner[ff] * owner_stride + feat_inner[ff] : out;
+    }
+    const int rot = (int)(blockIdx.x * 37u % (unsigned)kPairs);
+    for (int w = warp; w < 4 * kPairs; w += kHistWarps) {
+        const int g = w & 3;
+        int j = (w >> 2) + rot;
+        j = j >= kPairs ? j - kPairs : j;
+        long long* const d0 = g == 0 ? dst0[0] : (g == 1 ? dst0[1] : (g == 2 ? dst0[2] : dst0[3]));
+        const int nbf = g == 0 ? nb[0] : (g == 1 ? nb[1] : (g == 2 ? nb[2] : nb[3]));
+        // pairs are aligned to the sectors of `out`: a feature whose first cell sits in the upper half of one starts
+        // with a single bin
+        const int odd = (int)((reinterpret_cast<unsigned long long>(d0) >> 4) & 1ull);
+        const int bin = 2 * j + s - odd;
+        if (bin < 0 || bin >= nbf) continue;
+        const uint32_t* p = sh + (c ? kHOff / 4 : 0) + bin * (2 * kGroup) + g * 8 + q;
+        const uint32_t lo = p[0], hi = p[kGroup];
+        if ((lo | hi) == 0) continue;
+        const long long v = (long long)(int32_t)hi * 65536ll + (long long)lo;
+        if (v != 0) atomicAdd(reinterpret_cast<unsigned long long*>(d0 + 2 * bin + c), (unsigned long long)v);
+    }
+    if (kRezero) {
+        __syncthreads();
+        uint4* z = reinterpret_cast<uint4*>(sh);
+        for (int i = threadIdx.x; i < kMaxBins * 4 * kGroup / 4; i += kHistThreads) z[i] = make_uint4(0, 0, 0, 0);
     }
 }
 

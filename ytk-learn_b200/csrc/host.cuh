@@ -249,6 +249,7 @@ struct EngineBuffers {
     long long* h_leaf = nullptr;
     unsigned long long* d_stamps = nullptr;      // {~start, end} of the tree's main kernels on the global timer
     unsigned long long* h_stamps = nullptr;
+    int gid_on_device = -1;                      // the class index t.gid holds
 };
 
 }  // namespace ytkh
@@ -325,6 +326,8 @@ struct ytk_gbdt {
     int n_wide = 0;
     std::vector<int32_t> wide_index;       // per feature: its uint16 column, -1 if it has at most 256 slots
     std::vector<int32_t> wide_sel;         // wide features selected for the current tree
+    std::vector<uint8_t> sel_on_device;    // the selection d_fea_sel / d_group_mask / d_wide_fids hold (empty: none yet)
+    int sel_first_owned = -1, sel_count = 0;
     uint16_t* d_wide = nullptr;            // [n_wide][N]
     int32_t* d_wide_index = nullptr;       // device copy of wide_index (null when n_wide == 0)
     int32_t* d_wide_fids = nullptr;        // device copy of wide_sel

@@ -102,17 +102,23 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
         for (int k = 0; k < kPer; k++) { v[k].x -= b[k].x; v[k].y -= b[k].y; }
     };
     const int f = f_from + slice * kScanWarps + warp;       // one feature per warp
-    const bool mine = f < f_to && fea_selected[f];
     long long* hp = nullptr;
     const long long* sp = nullptr;
     int nb = 0;
     longlong2 cur[kPer];
-    if (mine) {
+    bool mine = false;
+    if (f < f_to) {
+        // (the three table reads are independent: one round trip, not a chain, before the bins can be asked for)
+        const uint8_t sel = fea_selected[f];
         const long long off = feat_off[f];
-        hp = hist + off;
-        sp = sub ? sub + off : nullptr;
-        nb = start[f + 1] - start[f];
-        load_block(cur, hp, sp, 0, nb);
+        const int nbf = start[f + 1] - start[f];
+        mine = sel != 0;
+        if (mine) {
+            hp = hist + off;
+            sp = sub ? sub + off : nullptr;
+            nb = nbf;
+            load_block(cur, hp, sp, 0, nb);
+        }
     }
     const double ig = scale->inv_g, ih = scale->inv_h;
     long long sample_cnt = nd.sample_cnt;
@@ -121,7 +127,6 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
         const long long small = g.left < g.right ? g.left : g.right;
         sample_cnt = nd.which == 0 ? small : (g.left + g.right - small);
     }
-
     if (warp == 0) {
         double G, H;
         if (first_fea >= 0) {
@@ -170,12 +175,10 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
                 for (int k = 0; k < kPer; k++)
                     if (j0 + k < nb) *reinterpret_cast<longlong2*>(hp + 2 * (j0 + k)) = cur[k];
             }
-            long long pg[kPer], ph[kPer];                   // sums of this lane's bins before bin k
-            long long lg = 0, lh = 0;
+            long long lg = 0, lh = 0;                       // this lane's bins together
             unsigned ne_mask = 0;                           // hasSample, bit k
 #pragma unroll
             for (int k = 0; k < kPer; k++) {
-                pg[k] = lg; ph[k] = lh;
                 lg += cur[k].x; lh += cur[k].y;
                 ne_mask |= (unsigned)((cur[k].x | cur[k].y) != 0) << k;
             }
@@ -187,13 +190,15 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
                 const int tm = __shfl_up_sync(0xffffffffu, pm, d);
                 if (lane >= d) { sg += tg; sh += th; pm = max(pm, tm); }
             }
-            const long long baseG = carryG + sg - lg, baseH = carryH + sh - lh;    // left branch before this lane's bins
-            int prev = __shfl_up_sync(0xffffffffu, pm, 1);                        // lastFeaValue
+            long long exG = carryG + sg - lg, exH = carryH + sh - lh;     // left branch before bin j0 (+ k below)
+            int prev = __shfl_up_sync(0xffffffffu, pm, 1);                // lastFeaValue
             prev = lane == 0 ? carry_last : max(prev, carry_last);
-#pragma unroll
-            for (int k = 0; k < kPer; k++) {
+            // (a loop, not eight copies: two double-precision gains per bin are ~150 instructions, and a kernel this
+            // short pays for every instruction-cache line it touches; the bins move down a register queue)
+#pragma unroll 1
+            for (int k = 0; k < kPer && (ne_mask >> k) != 0; k++) {
+                const long long g = cur[0].x, h = cur[0].y;
                 const bool ne = (ne_mask >> k) & 1u;
-                const long long exG = baseG + pg[k], exH = baseH + ph[k];
                 if (ne && exH != 0) {                                      // !leftBranchGradStats.empty()
                     double lG = (double)exG * ig, lH = (double)exH * ih;
                     if (lH >= gp.min_child_weight) {
@@ -206,6 +211,9 @@ split_scan_k(const ScanNode* __restrict__ nodes, const int32_t* __restrict__ sta
                     }
                 }
                 if (ne) prev = j0 + k;
+                exG += g; exH += h;
+#pragma unroll
+                for (int i = 0; i + 1 < kPer; i++) cur[i] = cur[i + 1];
             }
             carryG += __shfl_sync(0xffffffffu, sg, 31);
             carryH += __shfl_sync(0xffffffffu, sh, 31);

@@ -146,6 +146,13 @@ int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* firs
             sel[fea_index[i]] = 1;
         }
     }
+    // the same selection as the last tree's (no feature sampling: every tree): the device copies stand
+    if (!h->sel_on_device.empty() && h->sel_on_device == sel) {
+        if (n_sel) *n_sel = h->sel_count;
+        *first_owned = h->sel_first_owned;
+        return YTK_OK;
+    }
+    h->sel_on_device.clear();
     std::vector<uint32_t> gm(h->groups, 0);
     int cnt = 0;
     h->wide_sel.clear();
@@ -171,6 +178,9 @@ int set_features(ytk_gbdt* h, const int32_t* fea_index, int32_t n_fea, int* firs
         memcpy(s3, h->wide_sel.data(), h->wide_sel.size() * sizeof(int32_t));
         CK(cudaMemcpyAsync(h->d_wide_fids, s3, h->wide_sel.size() * sizeof(int32_t), cudaMemcpyHostToDevice, h->st));
     }
+    h->sel_on_device = sel;
+    h->sel_first_owned = *first_owned;
+    h->sel_count = cnt;
     return YTK_OK;
 }
 
@@ -928,6 +938,7 @@ static int set_bins_impl(ytk_gbdt* h, const int32_t* start, int32_t F, int64_t n
         CK(cudaMalloc(&h->d_wide_fids, h->n_wide * sizeof(int32_t)));
     }
     CK(cudaMalloc(&h->d_fea_sel, F));
+    h->sel_on_device.clear();
     CK(cudaMalloc(&h->d_hist_flat, 2LL * h->B * sizeof(long long)));
     CK(cudaMalloc(&h->d_hist_flat2, 2LL * h->B * sizeof(long long)));
     CK(cudaMalloc(&h->d_hist_dbl, 2LL * h->B * sizeof(double)));

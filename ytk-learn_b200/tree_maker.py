@@ -166,8 +166,11 @@ class GpuTreeMaker:
     def make(self, group_id=0, fea_index=None, row_mask=None):
         cap = 2 * self.params.max_leaf_cnt - 1 if self.params.max_leaf_cnt > 0 \
             else 2 ** (self.params.max_depth + 1) - 1
-        tree = B.Tree(cap)
-        tc = tree._as_c()
+        buf = getattr(self, "_tree_buf", None)           # node arrays at full capacity, reused by every call
+        if buf is None or buf[0].capacity != cap:
+            tree = B.Tree(cap)
+            buf = self._tree_buf = (tree, tree._as_c())
+        tree, tc = buf
         ts = B.TimeStats()
         fi = None if fea_index is None else np.ascontiguousarray(fea_index, dtype=np.int32)
         rm = None if row_mask is None else np.ascontiguousarray(row_mask, dtype=np.uint8)
@@ -176,7 +179,7 @@ class GpuTreeMaker:
         B.check(B.lib().ytk_gbdt_make_tree(self._h, int(group_id), B.ptr(fi), 0 if fi is None else len(fi),
                                            B.ptr(rm), C.addressof(tc), C.addressof(ts)))
         self.last_stats = ts
-        return tree._trim(tc.n_nodes)
+        return tree._trimmed_copy(tc.n_nodes)
 
     def get_total_time_stats(self):
         return self.last_stats
