@@ -69,5 +69,8 @@ def test_kernel_time_spans_agree_with_cuda_events(monkeypatch):
     ts = tm.last_stats
     assert ts.stage_times_from_gpu == 1 and ts.hist_launches == 6
     assert ts.hist_events_ms > 0.05
-    assert abs(ts.gpu_hist_ms - ts.hist_events_ms) <= 0.10 * ts.hist_events_ms + 0.02, (ts.gpu_hist_ms, ts.hist_events_ms)
+    # the events also see what lies between a launch and its first CTA (a few us per launch), never less than the kernels
+    assert ts.gpu_hist_ms <= ts.hist_events_ms + 0.005, (ts.gpu_hist_ms, ts.hist_events_ms)
+    assert ts.hist_events_ms - ts.gpu_hist_ms <= 0.10 * ts.hist_events_ms + 0.010 * ts.hist_launches, \
+        (ts.gpu_hist_ms, ts.hist_events_ms)
     assert ts.device_span_ms >= ts.gpu_hist_ms + ts.partition + ts.find_best_split

@@ -14,7 +14,7 @@
 #include <cstdlib>
 
 #ifndef YTK_PART_MIN_BLOCKS
-#define YTK_PART_MIN_BLOCKS 3
+#define YTK_PART_MIN_BLOCKS 2
 #endif
 namespace ytk {
 
@@ -234,6 +234,9 @@ __device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned 
     asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// kSrc: where a row's slot comes from -- 0: uint8 slots only, 1: some features have uint16 columns, 2: sparse rows.
+// (One kernel per kind: the sparse look-up would cost the common case its registers.)
+template <int kSrc>
 __global__ void __launch_bounds__(kFusedThreads, YTK_PART_MIN_BLOCKS)
 partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_stride, WideCols wide, SparseRows sparse,
                   int32_t* __restrict__ rowidx0,
@@ -244,8 +247,9 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
                   unsigned long long* __restrict__ stamp) {
     pdl_sync();
     if (epoch_dev) epoch = *epoch_dev;       // kept on the device (a launch recorded in a CUDA graph cannot take a new value)
-    __shared__ int s_tile, s_prefix, s_found;
-    __shared__ int s_warp[kFusedThreads / 32], s_lb_sum[kFusedThreads / 32], s_lb_fp[kFusedThreads / 32];
+    __shared__ int s_tile, s_prefix, s_found, s_tile_left;
+    __shared__ int s_lb_sum[kFusedThreads / 32], s_lb_fp[kFusedThreads / 32];
+    __shared__ int s_cnt[kFusedItems * (kFusedThreads / 32)];
     __shared__ int32_t s_rows[kFusedTile];      // the tile, left rows first, both sides in input order
     // tables planned on the device (plan_next_partition_k): the grid is an upper bound, the real
     // number of tiles is read here, and the planner has reset the ticket and the empty nodes' counts
@@ -268,27 +272,14 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     const int j = tile - sg.tile0;
     const long long tile_begin = sg.begin + (long long)j * kFusedTile;
     const int tile_n = (int)min((long long)kFusedTile, sg.end - tile_begin);
-    // thread t owns kFusedItems consecutive items of the tile so that order is preserved
-    const int first = threadIdx.x * kFusedItems;
-    const int mine = max(0, min(kFusedItems, tile_n - first));      // items of this thread that exist
+    // Item i of the tile = k * kFusedThreads + thread: neighbouring lanes hold neighbouring rows, so that where the
+    // row-id list is (nearly) contiguous -- the upper levels -- a warp's 32 one-byte gathers fall into one or two
+    // sectors instead of sixteen (the gathers' L1 tag cycles were half of this kernel's time there).
     int32_t rid[kFusedItems];
-    if (!rowidx) {
 #pragma unroll
-        for (int k = 0; k < kFusedItems; k++) rid[k] = (int32_t)(tile_begin + first + k);
-    } else if (mine == kFusedItems && ((reinterpret_cast<unsigned long long>(rowidx + tile_begin + first) & 15ull) == 0)) {
-        const int4* rp = reinterpret_cast<const int4*>(rowidx + tile_begin + first);
-#pragma unroll
-        for (int q = 0; q < kFusedItems / 4; q++) {
-            const int4 r = rp[q];
-            rid[4 * q] = r.x; rid[4 * q + 1] = r.y; rid[4 * q + 2] = r.z; rid[4 * q + 3] = r.w;
-        }
-    } else {
-#pragma unroll
-        for (int k = 0; k < kFusedItems; k++) rid[k] = k < mine ? rowidx[tile_begin + first + k] : 0;
-    }
-    if (!rowidx && mine < kFusedItems) {
-#pragma unroll
-        for (int k = 0; k < kFusedItems; k++) if (k >= mine) rid[k] = 0;       // never read past the last row
+    for (int k = 0; k < kFusedItems; k++) {
+        const int i = k * kFusedThreads + threadIdx.x;
+        rid[k] = i < tile_n ? (rowidx ? rowidx[tile_begin + i] : (int32_t)(tile_begin + i)) : 0;   // (never read past the last row)
     }
     // one addressing form for the three sources: a byte mask over rows (left iff non-zero, i.e. NOT
     // below 0.5), the feature-major copy, row-major slots
@@ -297,10 +288,10 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     const int mul = (mask || col_stride > 0) ? 1 : S8;
     const float cond = mask ? 0.5f : sg.cond;
     unsigned short slot[kFusedItems];
-    if (sparse.row_ptr && !mask) {                       // sparse rows: look the feature up in the row
+    if (kSrc == 2 && !mask) {                            // sparse rows: look the feature up in the row
 #pragma unroll
         for (int k = 0; k < kFusedItems; k++) slot[k] = (unsigned short)sparse_slot(sparse, rid[k], sg.fid);
-    } else if (sg.wide > 0) {                            // a feature with more than 256 slots: its uint16 column
+    } else if (kSrc == 1 && sg.wide > 0) {               // a feature with more than 256 slots: its uint16 column
         const uint16_t* __restrict__ wb = wide.data + (long long)(sg.wide - 1) * wide.stride;
 #pragma unroll
         for (int k = 0; k < kFusedItems; k++) slot[k] = wb[rid[k]];
@@ -311,20 +302,31 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     unsigned fl = 0;                                     // bit k: item k goes left
 #pragma unroll
     for (int k = 0; k < kFusedItems; k++)
-        fl |= (unsigned)((k < mine) && (((float)slot[k] < cond) != mask)) << k;
-    const int cnt = __popc(fl);
-    int p = cnt;
-    for (int d = 1; d < 32; d <<= 1) {
-        int t = __shfl_up_sync(0xffffffffu, p, d);
-        if (lane >= d) p += t;
+        fl |= (unsigned)((k * kFusedThreads + (int)threadIdx.x < tile_n) && (((float)slot[k] < cond) != mask)) << k;
+    // lefts per (k, warp), in item order; their exclusive scan gives every item the number of lefts before it
+#pragma unroll
+    for (int k = 0; k < kFusedItems; k++) {
+        const unsigned m = __ballot_sync(0xffffffffu, (fl >> k) & 1u);
+        if (lane == 0) s_cnt[k * (kFusedThreads / 32) + warp] = __popc(m);
     }
-    if (lane == 31) s_warp[warp] = p;
     __syncthreads();
-    int woff = 0, tile_left = 0;
-    for (int w = 0; w < kFusedThreads / 32; w++) {
-        if (w < warp) woff += s_warp[w];
-        tile_left += s_warp[w];
+    if (warp == 0) {
+        constexpr int kPerLane = kFusedItems * (kFusedThreads / 32) / 32;
+        int v[kPerLane], sum = 0;
+#pragma unroll
+        for (int q = 0; q < kPerLane; q++) { v[q] = s_cnt[lane * kPerLane + q]; sum += v[q]; }
+        int p = sum;
+        for (int d = 1; d < 32; d <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, p, d);
+            if (lane >= d) p += t;
+        }
+        int excl = p - sum;
+#pragma unroll
+        for (int q = 0; q < kPerLane; q++) { s_cnt[lane * kPerLane + q] = excl; excl += v[q]; }
+        if (lane == 31) s_tile_left = p;
     }
+    __syncthreads();
+    const int tile_left = s_tile_left;
     // ---- chained scan: publish this tile's left count, then add up the tiles before it back to
     // the nearest one that already knows its prefix.  Every warp inspects its own window of 32
     // predecessors, so one round trip to L2 covers 512 tiles.
@@ -372,16 +374,13 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
             counts[seg] = {left, (sg.end - sg.begin) - left};
         }
     }
-    int lpos = woff + p - cnt;                           // lefts of this tile before my first item
-    int rpos = tile_left + (first - lpos);               // rights go after all lefts of the tile
 #pragma unroll
     for (int k = 0; k < kFusedItems; k++) {
-        if (k < mine) {
-            const bool l = (fl >> k) & 1u;
-            s_rows[l ? lpos : rpos] = rid[k];
-            lpos += l ? 1 : 0;
-            rpos += l ? 0 : 1;
-        }
+        const int i = k * kFusedThreads + threadIdx.x;
+        const bool l = (fl >> k) & 1u;
+        const unsigned m = __ballot_sync(0xffffffffu, l);
+        const int before = s_cnt[k * (kFusedThreads / 32) + warp] + __popc(m & ((1u << lane) - 1u));   // lefts before item i
+        if (i < tile_n) s_rows[l ? before : tile_left + (i - before)] = rid[k];           // rights go after all lefts of the tile
     }
     __syncthreads();
     const long long left_base = sg.begin + s_prefix;
@@ -391,13 +390,24 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     stamp_end(stamp);
 }
 
+// the kernel for the handle's kind of rows
+template <typename... Args>
+static cudaError_t launch_fused(dim3 grid, cudaStream_t st, const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide,
+                                SparseRows sparse, Args... args) {
+    if (sparse.row_ptr)
+        return launch_chain(partition_fused_k<2>, grid, dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse, args...);
+    if (wide.data)
+        return launch_chain(partition_fused_k<1>, grid, dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse, args...);
+    return launch_chain(partition_fused_k<0>, grid, dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse, args...);
+}
+
 cudaError_t launch_partition_fused(const uint8_t* src, int32_t S8, int64_t col_stride, WideCols wide, int32_t* rowidx0, int32_t* rowidx1,
                                    const SplitSeg* segs, int n_segs, const int* tile_seg, int n_tiles,
                                    unsigned long long* tile_state, unsigned int* ticket, unsigned long long epoch,
                                    PartitionCounts* counts, cudaStream_t st, SparseRows sparse) {
     if (n_segs <= 0) return cudaSuccess;
     if (n_tiles <= 0) return cudaMemsetAsync(counts, 0, (size_t)n_segs * sizeof(PartitionCounts), st);
-    return launch_chain(partition_fused_k, dim3(n_tiles), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
+    return launch_fused(dim3(n_tiles), st, src, S8, col_stride, wide, sparse,
                         rowidx0, rowidx1, segs, n_segs, tile_seg, n_tiles, (const int*)nullptr, tile_state, ticket, epoch, counts,
                         (const unsigned long long*)nullptr, (unsigned long long*)nullptr);
 }
@@ -515,7 +525,7 @@ cudaError_t launch_partition_planned_root(const uint8_t* src, int32_t S8, int64_
     cudaError_t e = launch_chain(plan_root_partition_k, dim3(1), dim3(256), 0, st, begin, end, buf, rec, min_split_loss,
                                  wide.index, out_segs, out_tile_seg, n_tiles_dev, ticket, next_counts);
     if (e != cudaSuccess || grid_bound <= 0) return e;
-    return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
+    return launch_fused(dim3(grid_bound), st, src, S8, col_stride, wide, sparse,
                         rowidx0, rowidx1, (const SplitSeg*)out_segs, 1, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
                         tile_state, ticket, epoch, next_counts, (const unsigned long long*)nullptr, (unsigned long long*)nullptr);
 }
@@ -531,7 +541,7 @@ cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col
     cudaError_t e = launch_chain(plan_next_partition_k, dim3(1), dim3(512), 0, st, cur_segs, cur_counts, cur_counts_global, jobs, m, recs,
                                  min_split_loss, wide.index, out_segs, out_tile_seg, n_tiles_dev, ticket, next_counts);
     if (e != cudaSuccess || grid_bound <= 0) return e;
-    return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
+    return launch_fused(dim3(grid_bound), st, src, S8, col_stride, wide, sparse,
                         rowidx0, rowidx1, (const SplitSeg*)out_segs, 2 * m, (const int*)out_tile_seg, 0, (const int*)n_tiles_dev,
                         tile_state, ticket, epoch, next_counts, (const unsigned long long*)nullptr, (unsigned long long*)nullptr);
 }
@@ -541,7 +551,10 @@ cudaError_t launch_partition_planned(const uint8_t* src, int32_t S8, int64_t col
 // which would allow more CTAs per SM, takes that cache away (measured: 0.64 -> 1.0 ms per tree).
 cudaError_t partition_kernels_init() {
     if (const char* e = getenv("YTK_GBDT_PART_CARVEOUT"))
-        return cudaFuncSetAttribute(partition_fused_k, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
+        for (const void* k : {(const void*)partition_fused_k<0>, (const void*)partition_fused_k<1>, (const void*)partition_fused_k<2>}) {
+            const cudaError_t err = cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
+            if (err != cudaSuccess) return err;
+        }
     return cudaSuccess;
 }
 
@@ -551,7 +564,7 @@ cudaError_t launch_partition_fused_planned(const uint8_t* src, int32_t S8, int64
                                            unsigned int* ticket, const unsigned long long* epoch_dev, PartitionCounts* counts,
                                            cudaStream_t st, SparseRows sparse, unsigned long long* stamp) {
     if (grid_bound <= 0) return cudaSuccess;
-    return launch_chain(partition_fused_k, dim3(grid_bound), dim3(kFusedThreads), 0, st, src, S8, col_stride, wide, sparse,
+    return launch_fused(dim3(grid_bound), st, src, S8, col_stride, wide, sparse,
                         rowidx0, rowidx1, segs, n_segs, tile_seg, 0, n_tiles_dev, tile_state, ticket, 0ull, counts, epoch_dev, stamp);
 }
 
