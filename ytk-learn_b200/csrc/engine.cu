@@ -397,9 +397,17 @@ public:
 
     // histogram slots that receive atomics start at zero: the slots themselves on one GPU, else the staging buffer
     int zero_build_targets(int first_slot, int m_slots) {
-        if (h->world == 1)
+        if (h->world == 1) {
+            // One GPU: level d builds into slots [2^d, 2^(d+1)) and the root into slot 0 -- all different, so the
+            // whole tree's targets are cleared by ONE memset ahead of the root instead of one per level on the
+            // tree's critical path (unless that is a lot of memory to touch at once: deep trees clear level by level)
+            const size_t all = ((size_t)1 << (D - 1)) * h->seg_max * sizeof(long long);
+            if (all <= ((size_t)64 << 20)) {
+                if (first_slot == 0) CK(cudaMemsetAsync(t.pool, 0, all, h->st));
+                return YTK_OK;
+            }
             CK(cudaMemsetAsync(t.pool + (size_t)first_slot * h->seg_max, 0, (size_t)m_slots * h->seg_max * sizeof(long long), h->st));
-        else
+        } else
             CK(cudaMemsetAsync(t.staging, 0, (size_t)m_slots * h->seg_max * h->world * sizeof(long long), h->st));
         return YTK_OK;
     }
