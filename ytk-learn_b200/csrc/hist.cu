@@ -393,6 +393,24 @@ __device__ __forceinline__ void hist_flush(uint32_t* sh, int fg, int32_t F, uint
     }
 }
 
+// Between two runs of rows on the same table: the low limbs' carries move into the high limbs (lo >> 16 added to hi,
+// lo kept below 2^16), after which a second run of up to kHistSecondRunRows rows fits -- |hi| <= 2^14 * (65536 + 65000)
+// + 65535 < 2^31 and lo <= 65535 + 65000 * 65535 < 2^32 -- and the node is flushed once instead of twice.
+constexpr int kHistSecondRunRows = 65000;
+__device__ __forceinline__ void hist_carry(uint32_t* sh) {
+    uint4* t = reinterpret_cast<uint4*>(sh);
+    for (int i = threadIdx.x; i < 2 * kMaxBins * (kGroup / 4); i += kHistThreads) {
+        const int region = i / (kMaxBins * (kGroup / 4)), r = i % (kMaxBins * (kGroup / 4));
+        const int bin = r / (kGroup / 4), q = r % (kGroup / 4);
+        uint4* lo = t + region * (int)(kHOff / 16) + bin * (2 * kGroup / 4) + q;
+        uint4* hi = lo + kGroup / 4;
+        uint4 l = *lo, h = *hi;
+        h.x += l.x >> 16; h.y += l.y >> 16; h.z += l.z >> 16; h.w += l.w >> 16;
+        l.x &= 0xffffu; l.y &= 0xffffu; l.z &= 0xffffu; l.w &= 0xffffu;
+        *lo = l; *hi = h;
+    }
+}
+
 __device__ __forceinline__ void hist_zero(uint32_t* sh) {
     uint4* z = reinterpret_cast<uint4*>(sh);
     for (int i = threadIdx.x; i < kMaxBins * 4 * kGroup / 4; i += kHistThreads) z[i] = make_uint4(0, 0, 0, 0);
@@ -485,12 +503,22 @@ hist_span_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict
         if (o0 >= o1) continue;                                     // only (part of) its flush cost falls to me
         const int32_t* __restrict__ ridx = nd.buf < 0 ? nullptr : (nd.buf == 0 ? rowidx0 : rowidx1);
         long long* __restrict__ out = seg_out[nd.seg];
-        for (long long b = nd.begin + o0; b < nd.begin + o1; b += kHistMaxRowsPerItem) {
-            const long long e = min(nd.begin + o1, b + (long long)kHistMaxRowsPerItem);
+        const long long share_end = nd.begin + o1;
+        long long b = nd.begin + o0;
+        int run = 0;                                     // runs of rows on the table since its last flush
+        while (b < share_end) {
+            const long long e = min(share_end, b + (long long)(run == 0 ? kHistMaxRowsPerItem : kHistSecondRunRows));
             if (use_tma && !ridx && S8 == kGroup && (b & 31) == 0) hist_rows_tma(sh, L, bins, gq, b, e, ring, bars, tma_phases);
             else hist_rows(sh, L, bins, S8, gq, ridx, fg, b, e);
             __syncthreads();
-            hist_flush<true>(sh, fg, F, gmask, nbins, feat_owner, feat_inner, owner_stride, out);
+            b = e;
+            if (run == 0 && b < share_end) {             // more rows of the node: a second run on the same table
+                hist_carry(sh);
+                run = 1;
+            } else {
+                hist_flush<true>(sh, fg, F, gmask, nbins, feat_owner, feat_inner, owner_stride, out);
+                run = 0;
+            }
             __syncthreads();
         }
     }
