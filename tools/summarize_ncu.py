@@ -35,7 +35,7 @@ def main():
     lines = [l for l in open(sys.argv[1]) if not l.startswith("==")]
     per = collections.OrderedDict()
     for row in csv.DictReader(lines):
-        key = (int(row["ID"]), row["Kernel Name"].split("(")[0].replace("ytk::", ""), row["Grid Size"])
+        key = (int(row["ID"]), row["Kernel Name"].split("(")[0].replace("ytk::", "").replace("void ", "").split("<")[0], row["Grid Size"])
         per.setdefault(key, {})[row["Metric Name"]] = (float(row["Metric Value"].replace(",", "")), row["Metric Unit"])
     agg = collections.OrderedDict()
     hist = []
