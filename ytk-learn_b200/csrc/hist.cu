@@ -530,7 +530,7 @@ hist_span_k(const uint8_t* __restrict__ bins, int32_t S8, const int2* __restrict
 // (J/dataflow/GBDTCoreData.java:164-168) and cannot hold that shape; here the rows are CSR, an
 // absent feature has its default slot, and the histogram is what the dense path would produce.
 // ------------------------------------------------------------------------------------
-// One CTA per work item (same items as hist_build_k), one warp per row at a time, lanes over the
+// One CTA per work item (same items as hist_build_k), one warp per row at a time, lane pairs over the
 // row's stored entries.  Thousands of bins per node: global 64-bit reductions, little contention.
 __global__ void __launch_bounds__(256)
 hist_csr_k(SparseRows sp, const uint8_t* __restrict__ fea_selected, const int2* __restrict__ gq,
@@ -566,13 +566,17 @@ hist_csr_k(SparseRows sp, const uint8_t* __restrict__ fea_selected, const int2* 
             nq = gq[nrid];
         }
         tg += q.x; th += q.y;
-        for (long long p = p0 + lane; p < p1; p += 32) {
+        // two neighbouring lanes per entry, one for g and one for h: the pair lies in one 32 B sector of the
+        // histogram, so a reduction instruction covers 16 entries in 16 sectors (a lane per entry took two
+        // instructions of 32 sectors each -- the sectors, i.e. L1 tag cycles and L2 requests, are what bounds this kernel)
+        const long long add = (lane & 1) ? (long long)q.y : (long long)q.x;
+        for (long long p = p0 + (lane >> 1); p < p1; p += 16) {
             const unsigned e = sp.nz[p];
             const int f = (int)(e >> 16), slot = (int)(e & 0xffffu);
             if (fea_selected[f]) {
-                unsigned long long* out = reinterpret_cast<unsigned long long*>(base + feat_owner[f] * owner_stride + feat_inner[f]) + 2 * slot;
-                atomicAdd(out, (unsigned long long)(long long)q.x);
-                atomicAdd(out + 1, (unsigned long long)(long long)q.y);
+                const long long own = owner_stride ? feat_owner[f] * owner_stride : 0;
+                unsigned long long* out = reinterpret_cast<unsigned long long*>(base + own + feat_inner[f]) + 2 * slot + (lane & 1);
+                atomicAdd(out, (unsigned long long)add);
             }
         }
         i = ni; rid = nrid; p0 = np0; p1 = np1; q = nq;
