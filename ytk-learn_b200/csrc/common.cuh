@@ -116,7 +116,7 @@ cudaError_t launch_hist_build(const uint8_t* bins, int32_t S8, const int2* gq, c
 // (cost of a node = its rows + kHistFlushCost), walked by hist_span_k in spans of equal cost.
 // cost of a node = its rows + flush_cost: what a node boundary inside a span costs (flush + re-zero of the shared
 // histogram, the dependent loads that start the next node's rows, two barriers), in rows' worth of time
-constexpr long long kHistFlushCost = 6144;     // measured on the Higgs shape: 512 -> 1.09 ms of histogram time per tree, 1536 -> 1.05, 3000 -> 1.01, 6000 and 12000 -> 0.97
+constexpr long long kHistFlushCost = 6144;     // measured on the Higgs shape when a flush took 14-21 us: 512 -> 1.09 ms of histogram time per tree, 1536 -> 1.05, 3000 -> 1.01, 6000 and 12000 -> 0.97; with the 6-7 us flush 2048..8192 all give 0.85
 struct BuildNode { long long begin, end; long long cost_end; long long cost; int buf; int seg; };
 cudaError_t launch_hist_span(const uint8_t* bins, int32_t S8, const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1,
                              const BuildNode* nodes, const int* n_nodes_dev, int groups, int32_t F, const uint32_t* group_mask,

@@ -634,12 +634,13 @@ hist_wide_k(WideCols wide, const int32_t* __restrict__ wide_fids, const int2* __
     const uint16_t* __restrict__ colp = wide.data + (long long)wide.index[f] * wide.stride;
     const int32_t* __restrict__ rows = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
     unsigned long long* out = reinterpret_cast<unsigned long long*>(seg_out[it.seg] + feat_owner[f] * owner_stride + feat_inner[f]);
-    for (long long i = it.begin + threadIdx.x; i < it.end; i += blockDim.x) {
+    // a lane pair per row, one lane for g and one for h (one sector per pair, see hist_csr_k)
+    const int c = threadIdx.x & 1;
+    for (long long i = it.begin + (threadIdx.x >> 1); i < it.end; i += blockDim.x >> 1) {
         const int32_t rid = rows ? rows[i] : (int32_t)i;
         const int2 q = gq[rid];
         const int slot = colp[rid];
-        atomicAdd(out + 2 * slot, (unsigned long long)(long long)q.x);
-        atomicAdd(out + 2 * slot + 1, (unsigned long long)(long long)q.y);
+        atomicAdd(out + 2 * slot + c, (unsigned long long)(long long)(c ? q.y : q.x));
     }
 }
 
