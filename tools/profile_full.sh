@@ -1,3 +1,5 @@
+# ncu --set full of the three main kernels (root + three levels); run under gpurun, then export with
+# ncu -i gpurun_out/r02_full.ncu-rep --page raw --csv > profiles/r02_full_raw.csv
 set -x
 export YTK_GBDT_NO_GRAPH=1
 ARGS="--steps 2 --warmup 1 --no-cpu-baseline --no-loss-wise --no-parity-check --no-other-configs --no-strong"

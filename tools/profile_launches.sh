@@ -1,3 +1,5 @@
+# ncu launch list of one bench run (every launch a kernel of its own: no CUDA graph) + one tree's timeline; run under gpurun,
+# then: cp gpurun_out/r02_launches.csv profiles/ && python tools/summarize_ncu.py profiles/r02_launches.csv profiles/r02_full_raw.csv > profiles/r02_summary.txt
 set -x
 export YTK_GBDT_NO_GRAPH=1
 ARGS="--steps 2 --warmup 1 --no-cpu-baseline --no-loss-wise --no-parity-check --no-other-configs --no-strong"

@@ -241,10 +241,19 @@ __global__ void lv_xhist_k(PeerTable pt, LvTables t, int d, int m, size_t area_o
     const size_t off = ((size_t)pt.rank * m + slot) * (size_t)t.seg_max;
     for (long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 2; i < t.seg_max;
          i += (long long)gridDim.x * blockDim.x * 2) {
+        // eight ranks' loads in flight at a time: a read over NVLink is a round trip of microseconds, and one after
+        // the other they were what an exchange on 8 GPUs took
         longlong2 s2 = make_longlong2(0, 0);
-        for (int r = 0; r < pt.world; r++) {
-            const longlong2 v = *reinterpret_cast<const longlong2*>(reinterpret_cast<const long long*>(pt.hist[r]) + off + i);
-            s2.x += v.x; s2.y += v.y;
+        for (int r0 = 0; r0 < pt.world; r0 += 8) {
+            longlong2 v[8];
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                v[q] = make_longlong2(0, 0);
+                if (r0 + q < pt.world)
+                    v[q] = *reinterpret_cast<const longlong2*>(reinterpret_cast<const long long*>(pt.hist[r0 + q]) + off + i);
+            }
+#pragma unroll
+            for (int q = 0; q < 8; q++) { s2.x += v[q].x; s2.y += v[q].y; }
         }
         *reinterpret_cast<longlong2*>(out + i) = s2;
     }
