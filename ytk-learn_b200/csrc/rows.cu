@@ -19,33 +19,57 @@ namespace ytk {
 //     -> uint8 row-major, rows padded to a multiple of 32 features (one 32 B sector per
 //     feature group and row).
 // ------------------------------------------------------------------------------------
-template <typename TIn>
-__global__ void repack_rows_k(const TIn* __restrict__ x, int64_t nrows, int32_t stride, int32_t F,
-                              const int32_t* __restrict__ nbins, uint8_t* __restrict__ bins, int32_t S8,
-                              uint8_t* __restrict__ col, int64_t col_stride, WideCols wide, int64_t row_base,
-                              int* bad_flag) {
-    int64_t total = nrows * S8;
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
-         i += (int64_t)gridDim.x * blockDim.x) {
-        int64_t r = i / S8;
-        int32_t f = (int32_t)(i - r * S8);
-        // padding columns get row-varying filler: the histogram kernel accumulates them too (and drops
-        // them at flush), and identical bins in consecutive rows would make consecutive atomics hit
-        // the same shared-memory word
-        uint8_t b = (uint8_t)((r + row_base) * 37 + f * 11);
-        if (f < F) {
-            int32_t v = (int32_t)x[r * stride + f];
-            if (v < 0 || v >= nbins[f]) { *bad_flag = 1; v = 0; }
-            const int wi = wide.index ? wide.index[f] : -1;
-            if (wi >= 0) {
-                wide.data[wi * wide.stride + r] = (uint16_t)v;     // its byte in the uint8 matrices stays filler
-            } else {
-                b = (uint8_t)v;
-                col[f * col_stride + r] = b;
+// Both upload kernels (slots in, original values in) write two copies of a row's slots: the row-major matrix the
+// histograms read and the feature-major copy the partition gathers from.  A CTA takes kRepackRows rows and one
+// 32-feature group at a time: a warp reads one row's 32 values (one line), writes its 32 B sector, and the group
+// goes through a transposing tile in shared memory so that the feature-major copy is written in runs of
+// kRepackRows consecutive bytes (a byte per thread straight to `col` was one sector per byte: 170 GB/s).
+constexpr int kRepackRows = 128;
+template <typename SlotOf>    // SlotOf(row, feature) -> the (validated) slot of a real feature
+__device__ __forceinline__ void repack_tile(SlotOf slot_of, int64_t nrows, int32_t F, uint8_t* __restrict__ bins, int32_t S8,
+                                            uint8_t* __restrict__ col, int64_t col_stride, WideCols wide, int64_t row_base) {
+    __shared__ uint8_t tile[kGroup][kRepackRows + 4];
+    const int64_t r0 = blockIdx.x * (int64_t)kRepackRows;
+    const int nr = (int)min((int64_t)kRepackRows, nrows - r0);
+    for (int g0 = 0; g0 < S8; g0 += kGroup) {
+        for (int e = threadIdx.x; e < nr * kGroup; e += blockDim.x) {
+            const int rl = e / kGroup, fl = e % kGroup;
+            const int64_t r = r0 + rl;
+            const int32_t f = g0 + fl;
+            // padding columns get row-varying filler: the histogram kernel accumulates them too (and drops
+            // them at flush), and identical bins in consecutive rows would make consecutive atomics hit
+            // the same shared-memory word
+            uint8_t b = (uint8_t)((r + row_base) * 37 + f * 11);
+            if (f < F) {
+                const int32_t v = slot_of(r, f);
+                const int wi = wide.index ? wide.index[f] : -1;
+                if (wi >= 0) wide.data[wi * wide.stride + r] = (uint16_t)v;     // its byte in the uint8 matrices stays filler
+                else b = (uint8_t)v;
             }
+            bins[r * S8 + f] = b;
+            tile[fl][rl] = b;
         }
-        bins[i] = b;
+        __syncthreads();
+        for (int e = threadIdx.x; e < kGroup * kRepackRows; e += blockDim.x) {
+            const int fl = e / kRepackRows, rl = e % kRepackRows;
+            const int32_t f = g0 + fl;
+            if (f < F && rl < nr && !(wide.index && wide.index[f] >= 0)) col[f * col_stride + r0 + rl] = tile[fl][rl];
+        }
+        __syncthreads();
     }
+}
+
+template <typename TIn>
+__global__ void __launch_bounds__(256)
+repack_rows_k(const TIn* __restrict__ x, int64_t nrows, int32_t stride, int32_t F,
+              const int32_t* __restrict__ nbins, uint8_t* __restrict__ bins, int32_t S8,
+              uint8_t* __restrict__ col, int64_t col_stride, WideCols wide, int64_t row_base,
+              int* bad_flag) {
+    repack_tile([&](int64_t r, int32_t f) -> int32_t {
+        int32_t v = (int32_t)x[r * stride + f];
+        if (v < 0 || v >= nbins[f]) { *bad_flag = 1; v = 0; }
+        return v;
+    }, nrows, F, bins, S8, col, col_stride, wide, row_base);
 }
 
 // ------------------------------------------------------------------------------------
@@ -71,30 +95,16 @@ __device__ __forceinline__ int32_t find_bin(const float* __restrict__ c, int32_t
     return idx;
 }
 
-__global__ void quantize_rows_k(const int32_t* __restrict__ xbits, int64_t nrows, int32_t stride, int32_t F,
-                                const float* __restrict__ cuts, const int32_t* __restrict__ start,
-                                uint8_t* __restrict__ bins, int32_t S8, uint8_t* __restrict__ col, int64_t col_stride,
-                                WideCols wide, int64_t row_base) {
-    int64_t total = nrows * S8;
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
-         i += (int64_t)gridDim.x * blockDim.x) {
-        int64_t r = i / S8;
-        int32_t f = (int32_t)(i - r * S8);
-        uint8_t b = (uint8_t)((r + row_base) * 37 + f * 11);     // see repack_rows_k
-        if (f < F) {
-            float v = __int_as_float(xbits[r * stride + f]);
-            int32_t s0 = start[f];
-            const int32_t slot = find_bin(cuts + s0, start[f + 1] - s0, v);
-            const int wi = wide.index ? wide.index[f] : -1;
-            if (wi >= 0) {
-                wide.data[wi * wide.stride + r] = (uint16_t)slot;
-            } else {
-                b = (uint8_t)slot;
-                col[f * col_stride + r] = b;
-            }
-        }
-        bins[i] = b;
-    }
+__global__ void __launch_bounds__(256)
+quantize_rows_k(const int32_t* __restrict__ xbits, int64_t nrows, int32_t stride, int32_t F,
+                const float* __restrict__ cuts, const int32_t* __restrict__ start,
+                uint8_t* __restrict__ bins, int32_t S8, uint8_t* __restrict__ col, int64_t col_stride,
+                WideCols wide, int64_t row_base) {
+    repack_tile([&](int64_t r, int32_t f) -> int32_t {
+        const float v = __int_as_float(xbits[r * stride + f]);
+        const int32_t s0 = start[f];
+        return find_bin(cuts + s0, start[f + 1] - s0, v);
+    }, nrows, F, bins, S8, col, col_stride, wide, row_base);
 }
 
 __global__ void unpack_rows_k(const uint8_t* __restrict__ bins, int32_t S8, int64_t nrows, int32_t F, WideCols wide,
@@ -142,7 +152,7 @@ cudaError_t launch_repack_rows(const int32_t* x, int64_t nrows, int32_t stride, 
                                uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, WideCols wide,
                                int64_t row_base, int* bad_flag, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    repack_rows_k<int32_t><<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, nbins, bins, S8, col, col_stride, wide,
+    repack_rows_k<int32_t><<<(unsigned)((nrows + kRepackRows - 1) / kRepackRows), 256, 0, st>>>(x, nrows, stride, F, nbins, bins, S8, col, col_stride, wide,
                                                                       row_base, bad_flag);
     return cudaGetLastError();
 }
@@ -150,7 +160,7 @@ cudaError_t launch_repack_rows_u8(const uint8_t* x, int64_t nrows, int32_t strid
                                   uint8_t* bins, int32_t S8, uint8_t* col, int64_t col_stride, WideCols wide,
                                   int64_t row_base, int* bad_flag, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    repack_rows_k<uint8_t><<<grid_for(nrows * S8, 256), 256, 0, st>>>(x, nrows, stride, F, nbins, bins, S8, col, col_stride, wide,
+    repack_rows_k<uint8_t><<<(unsigned)((nrows + kRepackRows - 1) / kRepackRows), 256, 0, st>>>(x, nrows, stride, F, nbins, bins, S8, col, col_stride, wide,
                                                                       row_base, bad_flag);
     return cudaGetLastError();
 }
@@ -158,7 +168,7 @@ cudaError_t launch_quantize_rows(const int32_t* xbits, int64_t nrows, int32_t st
                                  const float* cuts, const int32_t* start, uint8_t* bins, int32_t S8,
                                  uint8_t* col, int64_t col_stride, WideCols wide, int64_t row_base, cudaStream_t st) {
     if (nrows <= 0) return cudaSuccess;
-    quantize_rows_k<<<grid_for(nrows * S8, 256), 256, 0, st>>>(xbits, nrows, stride, F, cuts, start, bins, S8, col,
+    quantize_rows_k<<<(unsigned)((nrows + kRepackRows - 1) / kRepackRows), 256, 0, st>>>(xbits, nrows, stride, F, cuts, start, bins, S8, col,
                                                                col_stride, wide, row_base);
     return cudaGetLastError();
 }
