@@ -189,7 +189,7 @@ public:
         mix((unsigned long long)(uintptr_t)h->t_parts.d); mix((unsigned long long)(uintptr_t)h->t_scan_done.d);
         mix((unsigned long long)(uintptr_t)h->h_scale.h); mix((unsigned long long)(uintptr_t)h->d_gq);
         mix((unsigned long long)(first_owned + 7)); mix((unsigned long long)D); mix((unsigned long long)h->N);
-        mix((unsigned long long)t.flush_cost);
+        mix((unsigned long long)t.flush_cost); mix((unsigned long long)plan_in_xrecs());
         mix((unsigned long long)h->world);
         for (int r = 0; r < h->world && h->world > 1; r++) { mix((unsigned long long)(uintptr_t)h->pt.xchg[r]); mix((unsigned long long)(uintptr_t)h->pt.hist[r]); }
         return v;
@@ -354,8 +354,10 @@ public:
         if (phase != ytk::kXReduce) T->rendezvous++;
         const int n = d < 0 ? 1 : (2 << d);
         const long long first = d < 0 ? 0 : (2ll << d) - 1;
+        // (the level after these records is d + 1: its partition is planned in the tail of the merge)
         CK(ytk::launch_lv_xrecs(h->pt, t, n, first, h->off_recs, h->slot_recs, h->off_lh, h->slot_lh, 6, h->d_xctr + 4, phase,
-                                h->d_peer_err, h->st, phase == ytk::kXPush ? nullptr : stamp(kStSync, d + 1)));
+                                h->d_peer_err, h->st, phase == ytk::kXPush ? nullptr : stamp(kStSync, d + 1),
+                                plan_in_xrecs() ? d + 1 : -1, level_buf(root_buf, d + 1), p.min_split_loss));
         h->launches++;
         if (phase != ytk::kXPush) RET(mark(kSync));
         return YTK_OK;
@@ -430,15 +432,20 @@ public:
         const int m = 1 << d;
         const int buf = level_buf(root_buf, d), child_buf = buf == 0 ? 1 : 0;
         const bool leaf = d == D - 1;                     // the children are leaves (:266)
-        CK(ytk::launch_lv_plan_split(t, d, buf, p.min_split_loss, nullptr, ytk::kFusedTile, h->st));
+        if (!plan_in_xrecs()) CK(ytk::launch_lv_plan_split(t, d, buf, p.min_split_loss, nullptr, ytk::kFusedTile, h->st));
         const long long grid_bound = root_rows_bound / ytk::kFusedTile + m + 1;
         CK(ytk::launch_partition_fused_planned(h->d_bins_col, h->S8, h->N, wide_cols(h), h->d_rowidx[0], h->d_rowidx[1], t.segs, m,
                                                t.tile_seg, t.n_tiles, (int)grid_bound, h->d_tile_state, t.ticket, t.epoch,
                                                t.counts, h->st, sparse_rows(h), stamp(kStPart, d)));
         RET(mark(kPart));
         CK(ytk::launch_lv_plan_build(t, d, child_buf, leaf, h->st));
-        h->launches += 3;
+        h->launches += plan_in_xrecs() ? 2 : 3;
         return YTK_OK;
+    }
+    // several GPUs: the record exchange ahead of a level's partition plans it (lv_xrecs_k); YTK_GBDT_NO_FUSE_PLAN=1: a launch of its own
+    bool plan_in_xrecs() const {
+        static const bool off = [] { const char* e = getenv("YTK_GBDT_NO_FUSE_PLAN"); return e && atoi(e); }();
+        return h->world > 1 && !off;
     }
     // ... computeLeafStats (:341-385) when the children are leaves ...
     int level_leaf(int d) {

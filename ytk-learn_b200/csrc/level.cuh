@@ -72,7 +72,9 @@ cudaError_t launch_lv_xhist(const PeerTable& pt, LvTables t, int d, int m, size_
 // split records of `n` searched nodes whose first heap node is `first_heap`: all-gather + needReplace / MAX merge
 cudaError_t launch_lv_xrecs(const PeerTable& pt, LvTables t, int n, long long first_heap, size_t area_off, size_t slot_bytes,
                             size_t lh_off, size_t lh_slot_bytes, int flag_set, unsigned long long* xctr, int phase, int* err,
-                            cudaStream_t st, unsigned long long* stamp = nullptr);
+                            cudaStream_t st, unsigned long long* stamp = nullptr,
+                            int plan_d = -1 /* >= 0: the reduce step also plans the partition of that level (lv_plan_split_k's work) */,
+                            int plan_buf = 0, double min_split_loss = 0.0);
 // leaf sums of the 2m children of the last level (summed over ranks, in place) + the global child counts
 cudaError_t launch_lv_xleaf(const PeerTable& pt, LvTables t, int d, size_t area_off, size_t slot_bytes, size_t cnt_off,
                             size_t cnt_slot_bytes, int flag_set, unsigned long long* xctr, int phase, int* err, cudaStream_t st,

@@ -9,7 +9,7 @@
 // ====================================================================================
 #include "common.cuh"
 #include "device_util.cuh"
-#include "level.cuh"
+#include "level_plan.cuh"
 
 #include <math_constants.h>
 
@@ -170,6 +170,7 @@ __device__ __forceinline__ unsigned long long lv_epoch(const unsigned long long*
 
 __global__ void lv_xmax_k(PeerTable pt, unsigned* __restrict__ absmax, size_t area_off, size_t slot_bytes, int flag_set,
                           unsigned long long* xctr, int phase, int* err) {
+    pdl_sync();                                   // launched with programmatic stream serialization, like its neighbours
     __shared__ unsigned long long s_v;
     const unsigned long long epoch = lv_epoch(xctr);
     if (phase & kXPush) {
@@ -198,6 +199,7 @@ __global__ void lv_xmax_k(PeerTable pt, unsigned* __restrict__ absmax, size_t ar
 // counts of the level's partition (d < 0: the root's row count).
 __global__ void lv_xhist_k(PeerTable pt, LvTables t, int d, int m, size_t area_off, size_t slot_bytes, int flag_set,
                            unsigned long long* xctr, int phase, int* err, unsigned long long* stamp) {
+    pdl_sync();                                   // launched with programmatic stream serialization, like its neighbours
     const bool lead = blockIdx.x == 0 && blockIdx.y == 0;
     const unsigned long long epoch = lv_epoch(xctr);
     stamp_begin(stamp);
@@ -264,7 +266,8 @@ __global__ void lv_xhist_k(PeerTable pt, LvTables t, int d, int m, size_t area_o
 // totals, DataParallelTreeMaker.java:560,640-653) into the heap arrays.
 __global__ void lv_xrecs_k(PeerTable pt, LvTables t, int n, long long first_heap, size_t area_off, size_t slot_bytes, size_t lh_off,
                            size_t lh_slot_bytes, int flag_set, unsigned long long* xctr, int phase, int* err,
-                           unsigned long long* stamp) {
+                           unsigned long long* stamp, int plan_d, int plan_buf, double min_split_loss) {
+    pdl_sync();                                   // launched with programmatic stream serialization, like its neighbours
     const unsigned long long epoch = lv_epoch(xctr);
     stamp_begin(stamp);
     struct Done {
@@ -311,12 +314,17 @@ __global__ void lv_xrecs_k(PeerTable pt, LvTables t, int n, long long first_heap
         t.left_h[2 * (first_heap + k)] = reinterpret_cast<const long long*>(lbase + (size_t)best_r * lh_slot_bytes)[2 * k];
         t.left_h[2 * (first_heap + k) + 1] = tot_h;
     }
+    if (plan_d >= 0) {                                  // the merged records decide the next partition: it is planned here
+        __syncthreads();
+        lv_plan_split_dev(t, plan_d, plan_buf, min_split_loss, nullptr, kFusedTile);
+    }
 }
 
 // One CTA.  allreduceArray(double[2], SUM) of computeLeafStats (:375) for the 2m children of the last
 // level, exact in the integer domain, and the global child counts of the level's partition.
 __global__ void lv_xleaf_k(PeerTable pt, LvTables t, int d, size_t area_off, size_t slot_bytes, size_t cnt_off, size_t cnt_slot_bytes,
                            int flag_set, unsigned long long* xctr, int phase, int* err, unsigned long long* stamp) {
+    pdl_sync();                                   // launched with programmatic stream serialization, like its neighbours
     const unsigned long long epoch = lv_epoch(xctr);
     stamp_begin(stamp);
     struct Done {
@@ -359,27 +367,25 @@ __global__ void lv_xleaf_k(PeerTable pt, LvTables t, int d, size_t area_off, siz
 
 cudaError_t launch_lv_xmax(const PeerTable& pt, unsigned* absmax, size_t area_off, size_t slot_bytes, int flag_set,
                            unsigned long long* xctr, int phase, int* err, cudaStream_t st) {
-    lv_xmax_k<<<1, 64, 0, st>>>(pt, absmax, area_off, slot_bytes, flag_set, xctr, phase, err);
-    return cudaGetLastError();
+    return launch_chain(lv_xmax_k, dim3(1), dim3(64), 0, st, pt, absmax, area_off, slot_bytes, flag_set, xctr, phase, err);
 }
 cudaError_t launch_lv_xhist(const PeerTable& pt, LvTables t, int d, int m, size_t area_off, size_t slot_bytes, int flag_set,
                             unsigned long long* xctr, int phase, int* err, cudaStream_t st, unsigned long long* stamp) {
     dim3 grid((unsigned)std::max<long long>(1, std::min<long long>(16, (t.seg_max / 2 + 255) / 256)), (unsigned)m);
     if (phase == kXPush) grid = dim3(1, 1);
-    lv_xhist_k<<<grid, 256, 0, st>>>(pt, t, d, m, area_off, slot_bytes, flag_set, xctr, phase, err, stamp);
-    return cudaGetLastError();
+    return launch_chain(lv_xhist_k, grid, dim3(256), 0, st, pt, t, d, m, area_off, slot_bytes, flag_set, xctr, phase, err, stamp);
 }
 cudaError_t launch_lv_xrecs(const PeerTable& pt, LvTables t, int n, long long first_heap, size_t area_off, size_t slot_bytes,
                             size_t lh_off, size_t lh_slot_bytes, int flag_set, unsigned long long* xctr, int phase, int* err,
-                            cudaStream_t st, unsigned long long* stamp) {
-    lv_xrecs_k<<<1, 256, 0, st>>>(pt, t, n, first_heap, area_off, slot_bytes, lh_off, lh_slot_bytes, flag_set, xctr, phase, err, stamp);
-    return cudaGetLastError();
+                            cudaStream_t st, unsigned long long* stamp, int plan_d, int plan_buf, double min_split_loss) {
+    if (!(phase & kXReduce)) plan_d = -1;
+    return launch_chain(lv_xrecs_k, dim3(1), dim3(256), 0, st, pt, t, n, first_heap, area_off, slot_bytes, lh_off, lh_slot_bytes, flag_set,
+                        xctr, phase, err, stamp, plan_d, plan_buf, min_split_loss);
 }
 cudaError_t launch_lv_xleaf(const PeerTable& pt, LvTables t, int d, size_t area_off, size_t slot_bytes, size_t cnt_off,
                             size_t cnt_slot_bytes, int flag_set, unsigned long long* xctr, int phase, int* err, cudaStream_t st,
                             unsigned long long* stamp) {
-    lv_xleaf_k<<<1, 256, 0, st>>>(pt, t, d, area_off, slot_bytes, cnt_off, cnt_slot_bytes, flag_set, xctr, phase, err, stamp);
-    return cudaGetLastError();
+    return launch_chain(lv_xleaf_k, dim3(1), dim3(256), 0, st, pt, t, d, area_off, slot_bytes, cnt_off, cnt_slot_bytes, flag_set, xctr, phase, err, stamp);
 }
 
 cudaError_t launch_peer_allreduce(const PeerTable& pt, const void* src, size_t area_off, size_t slot_bytes, size_t words,
