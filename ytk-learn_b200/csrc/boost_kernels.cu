@@ -21,7 +21,8 @@ __global__ void add_leaf_values_k(const int32_t* __restrict__ rowidx0, const int
     for (long long i = it.begin + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < it.end;
          i += (long long)gridDim.x * blockDim.x) {
         const long long r = rowidx ? rowidx[i] : i;
-        score[r * K + gid] += it.value;
+        float* s = score + r * K + gid;
+        *s = ld_gather_f32_rw(s) + it.value;
     }
 }
 

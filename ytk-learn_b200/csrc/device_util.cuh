@@ -28,6 +28,36 @@ static cudaError_t launch_chain(void (*kernel)(KArgs...), dim3 grid, dim3 block,
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
+// Loads of data reached through a row-id list (a row's slots, its gradient pair, one slot of a column): a miss in L2
+// fetches 128 B from HBM by default, of which such a load uses 1..32; `.L2::64B` asks for 64 (SASS LDG.E.LTC64B).
+// Measured on the Higgs shape: DRAM bytes of the gathered histogram launches -40 %, their time -12 %
+// (cudaLimitMaxL2FetchGranularity, the device-wide hint, changes nothing: profiles/r02_hist_record_experiment.txt).
+__device__ __forceinline__ uint4 ld_gather_u4(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ int2 ld_gather_int2(const int2* p) {
+    int2 v;
+    asm volatile("ld.global.nc.L2::64B.v2.s32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ unsigned ld_gather_u8(const uint8_t* p) {
+    unsigned v;
+    asm volatile("ld.global.nc.L2::64B.u8 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float ld_gather_f32_rw(const float* p) {      // (of memory the same kernel writes: not .nc)
+    float v;
+    asm volatile("ld.global.L2::64B.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ unsigned ld_gather_u16(const uint16_t* p) {
+    unsigned short v;
+    asm volatile("ld.global.nc.L2::64B.u16 %0, [%1];" : "=h"(v) : "l"(p));
+    return v;
+}
+
 // A kernel's own account of when it ran: the first CTA's start and the last CTA's end on the GPU's global timer
 // (ns), kept as {max of ~start, max of end} so that an all-zero pair means "did not run".  Launches replayed
 // from a CUDA graph cannot be bracketed with CUDA events (cudaEventElapsedTime refuses events recorded by a

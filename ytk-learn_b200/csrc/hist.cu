@@ -195,8 +195,9 @@ __device__ __forceinline__ void hist_rows(uint32_t* sh, const HistLane& L, const
         // past the end of the run: zeros, i.e. "add zero to bin 0", which changes nothing
         f.a = make_uint4(0, 0, 0, 0); f.b = f.a;
         f.qa = make_int2(0, 0); f.qb = f.qa;
-        if (ra >= 0) { f.a = *reinterpret_cast<const uint4*>(gbase + (long long)ra * S8); f.qa = gq[ra]; }
-        if (rb >= 0) { f.b = *reinterpret_cast<const uint4*>(gbase + (long long)rb * S8); f.qb = gq[rb]; }
+        // (ld_gather_*: no more than 64 B of HBM per miss -- a gathered row uses 32 + 8 bytes of the lines it touches)
+        if (ra >= 0) { f.a = ld_gather_u4(gbase + (long long)ra * S8); f.qa = ld_gather_int2(gq + ra); }
+        if (rb >= 0) { f.b = ld_gather_u4(gbase + (long long)rb * S8); f.qb = ld_gather_int2(gq + rb); }
     };
     // 16 steps on one 16-row half block.  Register j must hold data word j ^ m (m = r16 >> 2), the
     // word with the features this lane visits at steps 4j..4j+3: two conditional swaps.
@@ -553,7 +554,7 @@ hist_csr_k(SparseRows sp, const uint8_t* __restrict__ fea_selected, const int2* 
     if (i < it.end) {
         rid = rows ? rows[i] : (int32_t)i;
         p0 = sp.row_ptr[rid]; p1 = sp.row_ptr[rid + 1];
-        q = gq[rid];
+        q = ld_gather_int2(gq + rid);
     }
     while (i < it.end) {
         const long long ni = i + nwarps;
@@ -563,7 +564,7 @@ hist_csr_k(SparseRows sp, const uint8_t* __restrict__ fea_selected, const int2* 
         if (ni < it.end) {
             nrid = rows ? rows[ni] : (int32_t)ni;
             np0 = sp.row_ptr[nrid]; np1 = sp.row_ptr[nrid + 1];
-            nq = gq[nrid];
+            nq = ld_gather_int2(gq + nrid);
         }
         tg += q.x; th += q.y;
         // two neighbouring lanes per entry, one for g and one for h: the pair lies in one 32 B sector of the
@@ -638,8 +639,8 @@ hist_wide_k(WideCols wide, const int32_t* __restrict__ wide_fids, const int2* __
     const int c = threadIdx.x & 1;
     for (long long i = it.begin + (threadIdx.x >> 1); i < it.end; i += blockDim.x >> 1) {
         const int32_t rid = rows ? rows[i] : (int32_t)i;
-        const int2 q = gq[rid];
-        const int slot = colp[rid];
+        const int2 q = ld_gather_int2(gq + rid);
+        const int slot = (int)ld_gather_u16(colp + rid);
         atomicAdd(out + 2 * slot + c, (unsigned long long)(long long)(c ? q.y : q.x));
     }
 }

@@ -150,7 +150,7 @@ lv_leaf_sums_k(LvTables t, int d, const int2* __restrict__ gq, const int32_t* __
         const int32_t* __restrict__ ridx = nd.buf < 0 ? nullptr : (nd.buf == 0 ? rowidx0 : rowidx1);
         long long g = 0, h = 0;
         for (long long i = nd.begin + o0 + threadIdx.x; i < nd.begin + o1; i += blockDim.x) {
-            const int2 q = gq[ridx ? ridx[i] : (int32_t)i];
+            const int2 q = ld_gather_int2(gq + (ridx ? ridx[i] : (int32_t)i));
             g += q.x; h += q.y;
         }
         for (int k = 16; k > 0; k >>= 1) {

@@ -190,7 +190,7 @@ __global__ void leaf_sums_k(const int2* __restrict__ gq, const int32_t* __restri
     const int32_t* __restrict__ rowidx = it.buf < 0 ? nullptr : (it.buf == 0 ? rowidx0 : rowidx1);
     long long g = 0, h = 0;
     for (long long i = it.begin + threadIdx.x; i < it.end; i += blockDim.x) {
-        int2 q = gq[rowidx ? rowidx[i] : (int32_t)i];
+        int2 q = ld_gather_int2(gq + (rowidx ? rowidx[i] : (int32_t)i));
         g += q.x; h += q.y;
     }
     for (int d = 16; d > 0; d >>= 1) {
@@ -294,10 +294,10 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     } else if (kSrc == 1 && sg.wide > 0) {               // a feature with more than 256 slots: its uint16 column
         const uint16_t* __restrict__ wb = wide.data + (long long)(sg.wide - 1) * wide.stride;
 #pragma unroll
-        for (int k = 0; k < kFusedItems; k++) slot[k] = wb[rid[k]];
+        for (int k = 0; k < kFusedItems; k++) slot[k] = (unsigned short)ld_gather_u16(wb + rid[k]);
     } else {
 #pragma unroll
-        for (int k = 0; k < kFusedItems; k++) slot[k] = base[(long long)rid[k] * mul];     // independent gathers in flight
+        for (int k = 0; k < kFusedItems; k++) slot[k] = (unsigned short)ld_gather_u8(base + (long long)rid[k] * mul);     // independent gathers in flight
     }
     unsigned fl = 0;                                     // bit k: item k goes left
 #pragma unroll
