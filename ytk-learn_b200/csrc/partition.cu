@@ -247,16 +247,18 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
                   unsigned long long* __restrict__ stamp) {
     pdl_sync();
     if (epoch_dev) epoch = *epoch_dev;       // kept on the device (a launch recorded in a CUDA graph cannot take a new value)
-    __shared__ int s_tile, s_prefix, s_found, s_tile_left;
+    __shared__ int s_tile, s_prefix, s_found, s_tile_left, s_total;
     __shared__ int s_lb_sum[kFusedThreads / 32], s_lb_fp[kFusedThreads / 32];
     __shared__ int s_cnt[kFusedItems * (kFusedThreads / 32)];
     __shared__ int32_t s_rows[kFusedTile];      // the tile, left rows first, both sides in input order
     // tables planned on the device (plan_next_partition_k): the grid is an upper bound, the real
     // number of tiles is read here, and the planner has reset the ticket and the empty nodes' counts
     if (n_tiles_dev) n_tiles = *n_tiles_dev;
-    if (threadIdx.x == 0)
+    if (threadIdx.x == 0) {
+        s_total = 0;
         s_tile = n_tiles_dev ? (int)atomicAdd(ticket, 1u)
                              : (int)atomicInc(ticket, (unsigned)n_tiles - 1u);        // back to 0 after the last tile
+    }
     __syncthreads();
     const int tile = s_tile;
     if (tile >= n_tiles) return;
@@ -304,12 +306,20 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     for (int k = 0; k < kFusedItems; k++)
         fl |= (unsigned)((k * kFusedThreads + (int)threadIdx.x < tile_n) && (((float)slot[k] < cond) != mask)) << k;
     // lefts per (k, warp), in item order; their exclusive scan gives every item the number of lefts before it
+    int warp_left = 0;
 #pragma unroll
     for (int k = 0; k < kFusedItems; k++) {
         const unsigned m = __ballot_sync(0xffffffffu, (fl >> k) & 1u);
         if (lane == 0) s_cnt[k * (kFusedThreads / 32) + warp] = __popc(m);
+        warp_left += __popc(m);
     }
+    if (lane == 0) atomicAdd(&s_total, warp_left);
     __syncthreads();
+    // the tile's own left count goes out as early as it is known (the tiles behind this one wait for it), by a warp
+    // that is not busy with the scan of the counts
+    const unsigned long long tag = epoch << 34;
+    if (threadIdx.x == kFusedThreads - 32)
+        st_volatile_u64(tile_state + tile, tag | ((j == 0 ? 2ull : 1ull) << 32) | (unsigned)s_total);
     if (warp == 0) {
         constexpr int kPerLane = kFusedItems * (kFusedThreads / 32) / 32;
         int v[kPerLane], sum = 0;
@@ -330,8 +340,6 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     // ---- chained scan: publish this tile's left count, then add up the tiles before it back to
     // the nearest one that already knows its prefix.  Every warp inspects its own window of 32
     // predecessors, so one round trip to L2 covers 512 tiles.
-    const unsigned long long tag = epoch << 34;
-    if (threadIdx.x == 0) st_volatile_u64(tile_state + tile, tag | ((j == 0 ? 2ull : 1ull) << 32) | (unsigned)tile_left);
     int excl = 0;                                        // thread 0's
     if (j > 0) {                                         // (uniform over the CTA)
         int look = tile - 1;
