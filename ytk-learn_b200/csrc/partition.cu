@@ -337,6 +337,16 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
     }
     __syncthreads();
     const int tile_left = s_tile_left;
+    // the rows take their places inside the tile (left rows first) while the tiles in front are still counting: ranks
+    // inside a tile need nothing from outside it
+#pragma unroll
+    for (int k = 0; k < kFusedItems; k++) {
+        const int i = k * kFusedThreads + threadIdx.x;
+        const bool l = (fl >> k) & 1u;
+        const unsigned m = __ballot_sync(0xffffffffu, l);
+        const int before = s_cnt[k * (kFusedThreads / 32) + warp] + __popc(m & ((1u << lane) - 1u));   // lefts before item i
+        if (i < tile_n) s_rows[l ? before : tile_left + (i - before)] = rid[k];           // rights go after all lefts of the tile
+    }
     // ---- chained scan: publish this tile's left count, then add up the tiles before it back to
     // the nearest one that already knows its prefix.  Every warp inspects its own window of 32
     // predecessors, so one round trip to L2 covers 512 tiles.
@@ -381,14 +391,6 @@ partition_fused_k(const uint8_t* __restrict__ src, int32_t S8, int64_t col_strid
             const long long left = (long long)excl + tile_left;
             counts[seg] = {left, (sg.end - sg.begin) - left};
         }
-    }
-#pragma unroll
-    for (int k = 0; k < kFusedItems; k++) {
-        const int i = k * kFusedThreads + threadIdx.x;
-        const bool l = (fl >> k) & 1u;
-        const unsigned m = __ballot_sync(0xffffffffu, l);
-        const int before = s_cnt[k * (kFusedThreads / 32) + warp] + __popc(m & ((1u << lane) - 1u));   // lefts before item i
-        if (i < tile_n) s_rows[l ? before : tile_left + (i - before)] = rid[k];           // rights go after all lefts of the tile
     }
     __syncthreads();
     const long long left_base = sg.begin + s_prefix;
