@@ -574,7 +574,7 @@ public:
     }
 
     // TimeStats (J/data/gbdt/TimeStats.java:69-78) from the kernels' own time spans on the device: histogram build,
-    // row partition, split search; everything else on the device (gradient fixed point, planners, subtraction, leaf
+    // row partition, split search (with the sibling subtraction); everything else on the device (gradient fixed point, planners, leaf
     // sums, gaps) is the remainder of the tree's device time and goes to init_stats.
     int stage_times() {
         const unsigned long long* st = h->eng.h_stamps;

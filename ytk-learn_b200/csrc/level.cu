@@ -36,7 +36,7 @@ lv_plan_split_k(LvTables t, int d, int buf, double min_split_loss, const int32_t
 // hessian sum of the parent's best split, which every GPU can evaluate without an exchange; integer
 // histograms make parent - child exact whichever child is built) goes on the level's build list.
 // leaf = false: the smaller child takes a fresh histogram slot, the larger one its parent's (sibling written
-// over its parent), and the subtraction pairs and the scan nodes of both children are laid down.
+// over its parent), and the scan nodes of both children are laid down (the larger child's asks the search for parent - sibling).
 __global__ void __launch_bounds__(kPlanThreads)
 lv_plan_build_k(LvTables t, int d, int child_buf, int leaf) {
     pdl_sync();

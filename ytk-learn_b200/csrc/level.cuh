@@ -1,5 +1,5 @@
 // Level-wise growth driven by the device: the tables of every kernel of a level (partition segments and
-// tiles, histogram build nodes, subtraction pairs, scan nodes, leaf-sum items) are functions of the split
+// tiles, histogram build nodes, scan nodes (with their subtractions), leaf-sum items) are functions of the split
 // records and child counts the device already holds, so the device plans them itself and the host
 // enqueues a whole tree without waiting (engine.cu).  Shared by level.cu (kernels) and engine.cu (host).
 //
@@ -94,7 +94,7 @@ cudaError_t launch_lv_root(LvTables t, long long begin, long long end, int buf, 
 cudaError_t launch_lv_plan_split(LvTables t, int d, int buf, double min_split_loss, const int32_t* wide_index, int tile_rows,
                                  cudaStream_t st);
 // after the partition of level d: children's intervals, smaller child, and the tables of the kernels that
-// follow: the build list (smaller children) and -- leaf = false -- subtraction pairs + scan nodes
+// follow: the build list (smaller children) and -- leaf = false -- scan nodes (the larger child: parent - sibling)
 cudaError_t launch_lv_plan_build(LvTables t, int d, int child_buf, bool leaf, cudaStream_t st);
 // leaf sums of the last level's build list into t.leaf (zero before)
 cudaError_t launch_lv_leaf_sums(LvTables t, int d, const int2* gq, const int32_t* rowidx0, const int32_t* rowidx1, int grid,
