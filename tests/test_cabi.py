@@ -110,3 +110,23 @@ def test_ctypes_structs_mirror_the_header(cname, pyname):
     assert [n for n, _ in want] == [n for n, _ in got]
     for (n, ct), (_, pt) in zip(want, got):
         assert pt is (C.c_void_p if ct.endswith("*") else ctypes_of[ct]), (n, ct, pt)
+
+
+def test_tree_buffer_is_reused_but_returned_trees_are_copies():
+    """GpuTreeMaker.make keeps one full-capacity node buffer per maker and hands out trimmed COPIES
+    (binding.Tree._trimmed_copy): a tree returned earlier must not change when the buffer is written again."""
+    yb = _pkg.load()
+    buf = yb.binding.Tree(7) if hasattr(yb, "binding") else None
+    if buf is None:
+        import importlib
+        buf = importlib.import_module("ytk-learn_b200.binding").Tree(7)
+    buf.fid[:] = np.arange(7)
+    buf.node_info[:] = 1.5
+    t1 = buf._trimmed_copy(3)
+    assert t1.n_nodes == 3 and t1.capacity == 7 and list(t1.fid) == [0, 1, 2]
+    buf.fid[:] = -1                      # the next make() overwrites the buffer
+    buf.node_info[:] = 9.0
+    assert list(t1.fid) == [0, 1, 2] and float(t1.node_info[0]) == 1.5
+    t2 = buf._trimmed_copy(5)
+    assert t2.n_nodes == 5 and list(t2.fid) == [-1] * 5
+    assert buf.fid.shape[0] == 7         # the buffer itself keeps its capacity
